@@ -1,0 +1,196 @@
+/*
+ * b200_nonbonded.h -- C ABI of the B200-native NonbondedForce/PME path.
+ *
+ * This is the drop-in boundary below the OpenMM `B200` Platform plugin
+ * (openmm_b200/plugin/): plain pointers and sizes, no C++/torch types.  Every entry
+ * point names the reference interface it replaces (paths relative to the OpenMM
+ * 8.6 tree).  All functions return B200_OK (0) or a negative error code; the text of
+ * the last error on the calling thread is available from b200_last_error().
+ *
+ * Conventions (same as the reference's device path):
+ *   units nm, ps, amu, kJ/mol, e;  ONE_4PI_EPS0 = 138.935456 (SimTKOpenMMRealType.h:84-89)
+ *   forces accumulate as int64 fixed point, value * 2^32 (platforms/cuda/src/kernels/common.cu:29-31),
+ *   SoA [x0..x_{Npad-1} | y.. | z..], Npad = 32*ceil(N/32) (CudaContext.cpp:209)
+ *   mixed precision: float positions + float correction, double velocities,
+ *   float pair math, int64 force sums, fixed-point energy sums.
+ */
+#ifndef B200_NONBONDED_H_
+#define B200_NONBONDED_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK                 0
+#define B200_ERR_INVALID       -1
+#define B200_ERR_CUDA          -2
+#define B200_ERR_OVERFLOW      -3
+#define B200_ERR_UNSUPPORTED   -4
+#define B200_ERR_NCCL          -5
+
+/* NonbondedForce::NonbondedMethod / CalcNonbondedForceKernel::NonbondedMethod (olla/include/openmm/kernels.h:628-635) */
+#define B200_NB_NOCUTOFF          0
+#define B200_NB_CUTOFF_NONPERIODIC 1
+#define B200_NB_CUTOFF_PERIODIC   2
+#define B200_NB_EWALD             3
+#define B200_NB_PME               4
+#define B200_NB_LJPME             5
+
+typedef struct b200_ctx b200_ctx;
+
+/* ---- System-level description: what ContextImpl hands a platform at contextCreated()
+ *      (openmmapi/src/ContextImpl.cpp:149-156) plus UpdateStateDataKernel::initialize (kernels.h:144). */
+typedef struct {
+    int32_t       num_atoms;
+    const double* mass;              /* [N]; 0 => immobile particle */
+    double        box[9];            /* a,b,c box vectors, reduced form (a=(ax,0,0), b=(bx,by,0), c=(cx,cy,cz)) */
+    int32_t       num_constraints;   /* System::getConstraintParameters */
+    const int32_t* constraint_atoms; /* [2*num_constraints] */
+    const double* constraint_dist;   /* [num_constraints] */
+    int32_t       device;            /* CUDA device ordinal ("DeviceIndex" platform property, CudaPlatform.cpp:116-141) */
+    uint32_t      flags;             /* B200_CTX_* */
+} b200_system_desc;
+
+#define B200_CTX_DISABLE_PME_STREAM  1u   /* "DisablePmeStream" property */
+
+/* ---- NonbondedForce description: what CalcNonbondedForceKernel::initialize(system, force)
+ *      (kernels.h:647; CommonCalcNonbondedForce.cpp:217-717) extracts from the force object. */
+typedef struct {
+    int32_t       method;            /* B200_NB_* */
+    double        cutoff;            /* nm */
+    double        ewald_alpha;       /* nm^-1 (NonbondedForceImpl::calcPMEParameters, NonbondedForceImpl.cpp:192-216) */
+    int32_t       grid[3];           /* PME mesh; each must factor into 2,3,5,7 */
+    double        dispersion_coefficient; /* C of E = C/V (NonbondedForceImpl::calcDispersionCorrection, :268-342); 0 = off */
+    int32_t       use_switch;        /* LJ switching function (coulombLennardJones.cc:32-40) */
+    double        switch_distance;
+    double        reaction_field_dielectric; /* CutoffPeriodic/NonPeriodic only */
+    const double* charge;            /* [N] e */
+    const double* sigma;             /* [N] nm */
+    const double* epsilon;           /* [N] kJ/mol */
+    int32_t       num_exclusions;    /* every exception (i,j): excluded from the direct-space loop */
+    const int32_t* exclusion_pairs;  /* [2*num_exclusions] */
+    int32_t       num_exceptions;    /* exceptions with non-zero chargeProd or epsilon ("1-4" pairs, nonbondedExceptions.cc:1-19) */
+    const int32_t* exception_pairs;  /* [2*num_exceptions] */
+    const double* exception_chargeprod; /* [num_exceptions] e^2 */
+    const double* exception_sigma;   /* nm */
+    const double* exception_epsilon; /* kJ/mol */
+    int32_t       exceptions_use_periodic; /* NonbondedForce::getExceptionsUsePeriodicBoundaryConditions */
+    double        ljpme_alpha;       /* LJPME only */
+    int32_t       ljpme_grid[3];
+} b200_nonbonded_desc;
+
+/* ---- context life cycle (Platform::contextCreated / contextDestroyed, olla/include/openmm/Platform.h:232-252) */
+int  b200_context_create(const b200_system_desc* desc, b200_ctx** out);
+void b200_context_destroy(b200_ctx* ctx);
+const char* b200_last_error(void);
+/* number of CUDA devices visible (Platform::getDevices, Platform.h:127-150); <0 on error */
+int  b200_device_count(void);
+
+/* CalcNonbondedForceKernel::initialize (kernels.h:647) */
+int  b200_nonbonded_create(b200_ctx* ctx, const b200_nonbonded_desc* desc);
+/* CalcNonbondedForceKernel::copyParametersToContext (kernels.h:669): new per-particle and exception parameters */
+int  b200_nonbonded_update_parameters(b200_ctx* ctx, const b200_nonbonded_desc* desc);
+/* CalcNonbondedForceKernel::getPMEParameters (kernels.h:678) */
+int  b200_nonbonded_get_pme_parameters(const b200_ctx* ctx, double* alpha, int32_t* nx, int32_t* ny, int32_t* nz);
+
+/* CalcHarmonicBondForceKernel::initialize (kernels.h:347), harmonicBondForce.cc: E = k/2 (r-r0)^2 */
+int  b200_harmonic_bonds_create(b200_ctx* ctx, int32_t n, const int32_t* atoms /*[2n]*/, const double* length, const double* k, int32_t group);
+/* CalcHarmonicAngleForceKernel::initialize (kernels.h:421), harmonicAngleForce.cc: E = k/2 (theta-theta0)^2 */
+int  b200_harmonic_angles_create(b200_ctx* ctx, int32_t n, const int32_t* atoms /*[3n]*/, const double* angle, const double* k, int32_t group);
+/* CalcPeriodicTorsionForceKernel::initialize (kernels.h:495), periodicTorsionForce.cc: E = k (1+cos(n phi - phi0)) */
+int  b200_periodic_torsions_create(b200_ctx* ctx, int32_t n, const int32_t* atoms /*[4n]*/, const int32_t* periodicity, const double* phase, const double* k, int32_t group);
+
+/* ---- state I/O: UpdateStateDataKernel (kernels.h:132-246; CommonKernels.cpp:95-297).
+ *      Host arrays are [3N] doubles in the caller's (original) particle order. */
+int  b200_set_positions(b200_ctx* ctx, const double* xyz);
+int  b200_get_positions(b200_ctx* ctx, double* xyz, int32_t enforce_periodic);
+int  b200_set_velocities(b200_ctx* ctx, const double* xyz);
+int  b200_get_velocities(b200_ctx* ctx, double* xyz);
+int  b200_get_forces(b200_ctx* ctx, double* xyz);
+int  b200_set_box(b200_ctx* ctx, const double* box9);
+int  b200_get_box(const b200_ctx* ctx, double* box9);
+int  b200_set_time(b200_ctx* ctx, double time_ps, int64_t step_count);
+int  b200_get_time(const b200_ctx* ctx, double* time_ps, int64_t* step_count);
+
+/* ---- force evaluation: CalcForcesAndEnergyKernel::beginComputation/finishComputation (kernels.h:110,125)
+ *      + CalcNonbondedForceKernel::execute (kernels.h:658).  `groups` bits as below.  Energy (kJ/mol) may be NULL. */
+#define B200_GROUP_DIRECT      1u   /* tile kernel + exclusion corrections... (includeDirect) */
+#define B200_GROUP_RECIPROCAL  2u   /* PME reciprocal space + self/plasma terms (includeReciprocal) */
+#define B200_GROUP_BONDED      4u   /* bonds, angles, torsions */
+#define B200_GROUP_ALL         7u
+int  b200_compute(b200_ctx* ctx, uint32_t groups, int32_t include_forces, int32_t include_energy, double* energy);
+
+/* Host-buffer convenience used by the end-to-end measurement: upload positions, evaluate, download forces.
+ * Same semantics as Context::setPositions + getState(Forces|Energy) (openmmapi/src/Context.cpp:87-227). */
+int  b200_compute_host(b200_ctx* ctx, const double* xyz_in, uint32_t groups, double* forces_out, double* energy);
+
+/* ---- integrator: IntegrateLangevinMiddleStepKernel (kernels.h:1392-1420; langevinMiddle.cc:9-95),
+ *      constraints ApplyConstraintsKernel (kernels.h:251-278; SETTLE integrationUtilities.cc:328-580, CCMA :582-804),
+ *      RemoveCMMotionKernel (kernels.h:1793; removeCM.cc). friction=0 gives velocity Verlet (IntegrateVerletStepKernel). */
+typedef struct {
+    double   dt;            /* ps */
+    double   temperature;   /* K */
+    double   friction;      /* 1/ps */
+    double   constraint_tol;
+    uint64_t seed;
+    int32_t  remove_cm_every; /* CMMotionRemover frequency; 0 = never */
+} b200_integrator_desc;
+int  b200_integrator_create(b200_ctx* ctx, const b200_integrator_desc* desc);
+int  b200_step(b200_ctx* ctx, int32_t nsteps);
+int  b200_apply_constraints(b200_ctx* ctx, double tol);              /* ApplyConstraintsKernel::apply */
+int  b200_apply_velocity_constraints(b200_ctx* ctx, double tol);     /* ApplyConstraintsKernel::applyToVelocities */
+int  b200_kinetic_energy(b200_ctx* ctx, double* ke);                 /* IntegrateLangevinMiddleStepKernel::computeKineticEnergy */
+int  b200_synchronize(b200_ctx* ctx);
+
+/* ---- parity probes (no counterpart kernel in the reference; they expose what its tests measure) */
+/* Set of unordered atom pairs (original indices, i<j) that the direct-space kernel treats as interacting
+ * (r < cutoff, not excluded).  Mirrors what computeNeighborListVoxelHash yields (ReferenceNeighborList.cpp:208-214).
+ * Call with pairs==NULL to get the count only. */
+int  b200_direct_pairs(b200_ctx* ctx, int64_t* count, int32_t* pairs /*[2*capacity]*/, int64_t capacity);
+/* Neighbour-list statistics after the last build: tiles, work units, j-slots, exclusion tiles, rebuild count. */
+typedef struct {
+    int64_t num_blocks, num_tiles, num_units, num_exclusion_tiles, rebuilds, steps, reorders;
+    int64_t tile_capacity, unit_capacity;
+} b200_nblist_stats;
+int  b200_nblist_get_stats(b200_ctx* ctx, b200_nblist_stats* out);
+
+/* ---- stage-level entry points for unit tests (CudaFFT3D::execFFT, CudaFFT3D.cpp:66-101; TestCudaFFT3D.cpp:56-121) */
+/* out-of-place unnormalised 3D real-to-complex / complex-to-real FFT on host buffers (row-major, z fastest;
+ * complex layout nx*ny*(nz/2+1) interleaved re,im). */
+int  b200_fft3d_r2c_host(int32_t device, int32_t nx, int32_t ny, int32_t nz, const float* in, float* out);
+int  b200_fft3d_c2r_host(int32_t device, int32_t nx, int32_t ny, int32_t nz, const float* in, float* out);
+/* smallest n' >= n whose only prime factors are 2,3,5,7 (ComputeContext::findLegalFFTDimension, ComputeContext.cpp:717-732) */
+int  b200_find_legal_fft_dimension(int32_t minimum);
+
+/* ---- measurement hooks: cumulative CUDA-event time (ms) and launch count per kernel family since the last reset */
+#define B200_T_TILE        0
+#define B200_T_NBLIST      1
+#define B200_T_SPREAD      2
+#define B200_T_FFT         3
+#define B200_T_CONVOLVE    4
+#define B200_T_INTERPOLATE 5
+#define B200_T_BONDED      6
+#define B200_T_INTEGRATE   7
+#define B200_T_REORDER     8
+#define B200_T_COMM        9
+#define B200_T_COUNT       10
+int  b200_timing_enable(b200_ctx* ctx, int32_t on);      /* when on, every family is bracketed by events (adds syncs at read time only) */
+int  b200_timing_read(b200_ctx* ctx, double* ms /*[B200_T_COUNT]*/, int64_t* launches /*[B200_T_COUNT]*/);
+int  b200_timing_reset(b200_ctx* ctx);
+/* time `nsteps` MD steps with CUDA events on the context's own stream; returns total ms */
+int  b200_timed_steps(b200_ctx* ctx, int32_t nsteps, double* total_ms);
+/* total kernels launched by this context since creation (the bench's gpu_launches claim) */
+int64_t b200_launch_count(const b200_ctx* ctx);
+
+/* ---- multi-GPU: direct-space rows are partitioned over ranks; forces are all-reduced as int64 over NCCL
+ *      (replaces CudaParallelKernels.cpp:183-269 + parallel.cu:5-13 sumForces). */
+int  b200_nccl_unique_id(char* id128);                                           /* rank 0 creates, caller broadcasts */
+int  b200_comm_init(b200_ctx* ctx, int32_t rank, int32_t nranks, const char* id128);
+int  b200_set_partition(b200_ctx* ctx, int32_t rank, int32_t nranks);            /* partition without NCCL (single-device emulation of N ranks) */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_NONBONDED_H_ */

@@ -1,0 +1,77 @@
+// b200_comm.cu -- multi-GPU: one process per GPU, direct-space rows dealt round-robin to ranks, fixed-point forces
+// summed with an NCCL all-reduce over NVLink.
+//
+// Replaces the reference's single-process multi-GPU path: peer-to-peer cuMemcpyAsync of posq and of each device's
+// force buffer into a slot on device 0, followed by the sumForces kernel
+// (platforms/cuda/src/CudaParallelKernels.cpp:183-269, platforms/cuda/src/kernels/parallel.cu:5-13).
+// Because the force sum is an integer sum it is exact and order independent: every rank ends up with bit-identical
+// forces, so each rank integrates its full replica redundantly (same Philox stream) and no position broadcast is
+// needed.  PME and the bonded terms run on rank 0 only (CommonCalcNonbondedForce.cpp:394,437).
+// NCCL is resolved at run time (dlopen) so the library has no hard dependency on a particular libnccl build;
+// inside a torch process this binds to the NCCL that torch already loaded.
+#include "b200_internal.cuh"
+#include <dlfcn.h>
+#include <cstring>
+
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+typedef int ncclResult_t;
+enum { ncclInt64 = 4, ncclSum = 0 };
+
+static struct NcclApi {
+    void* lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+} g_nccl;
+
+static void loadNccl() {
+    if (g_nccl.lib) return;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* n : names) { g_nccl.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (g_nccl.lib) break; }
+    if (!g_nccl.lib) throw B200Error(B200_ERR_NCCL, "cannot load libnccl.so.2");
+    g_nccl.GetUniqueId = (decltype(g_nccl.GetUniqueId))dlsym(g_nccl.lib, "ncclGetUniqueId");
+    g_nccl.CommInitRank = (decltype(g_nccl.CommInitRank))dlsym(g_nccl.lib, "ncclCommInitRank");
+    g_nccl.AllReduce = (decltype(g_nccl.AllReduce))dlsym(g_nccl.lib, "ncclAllReduce");
+    g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy))dlsym(g_nccl.lib, "ncclCommDestroy");
+    g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString))dlsym(g_nccl.lib, "ncclGetErrorString");
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.CommDestroy) throw B200Error(B200_ERR_NCCL, "libnccl is missing required symbols");
+}
+#define NCCL_CHECK(expr) do { ncclResult_t _r = (expr); if (_r != 0) throw B200Error(B200_ERR_NCCL, std::string(#expr) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(_r) : "NCCL error")); } while (0)
+
+extern "C" int b200_nccl_unique_id(char* id128) {
+    try { loadNccl(); ncclUniqueId id; NCCL_CHECK(g_nccl.GetUniqueId(&id)); memcpy(id128, id.internal, 128); }
+    catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
+    return B200_OK;
+}
+
+extern "C" int b200_set_partition(b200_ctx* c, int32_t rank, int32_t nranks) {
+    if (!c || nranks < 1 || rank < 0 || rank >= nranks) { b200_set_error("b200_set_partition: bad rank"); return B200_ERR_INVALID; }
+    c->partRank = rank; c->partRanks = nranks;
+    if (c->finalized) c->stepsSinceReorder = -1;   // forces a list rebuild with the new row assignment
+    return B200_OK;
+}
+
+extern "C" int b200_comm_init(b200_ctx* c, int32_t rank, int32_t nranks, const char* id128) {
+    try {
+        loadNccl();
+        CUDA_CHECK(cudaSetDevice(c->device));
+        ncclUniqueId id; memcpy(id.internal, id128, 128);
+        ncclComm_t comm;
+        NCCL_CHECK(g_nccl.CommInitRank(&comm, nranks, id, rank));
+        c->ncclComm = comm; c->commRank = rank; c->commRanks = nranks;
+        return b200_set_partition(c, rank, nranks);
+    } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
+}
+
+void b200_comm_allreduce_forces(b200_ctx* c) {
+    ScopedTimer tm(c, B200_T_COMM, c->stream);
+    NCCL_CHECK(g_nccl.AllReduce(c->force, c->force, 3 * (size_t)c->Npad, ncclInt64, ncclSum, (ncclComm_t)c->ncclComm, c->stream));
+}
+
+void b200_comm_destroy(b200_ctx* c) {
+    if (c->ncclComm && g_nccl.CommDestroy) g_nccl.CommDestroy((ncclComm_t)c->ncclComm);
+    c->ncclComm = nullptr;
+}

@@ -1,0 +1,687 @@
+// b200_context.cu -- context life cycle, state I/O, molecule/exclusion-tile set-up and the per-step orchestration.
+//
+// Host-side counterpart of CudaContext / ComputeContext (platforms/cuda/src/CudaContext.cpp,
+// platforms/common/src/ComputeContext.cpp), CommonUpdateStateDataKernel (platforms/common/src/CommonKernels.cpp:95-297),
+// CudaNonbondedUtilities::initialize (platforms/cuda/src/CudaNonbondedUtilities.cpp:161-371) and
+// CudaCalcForcesAndEnergyKernel (platforms/cuda/src/CudaKernels.cpp:63-91).
+#include "b200_internal.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <numeric>
+#include <set>
+#include <sstream>
+
+static thread_local std::string g_lastError;
+void b200_set_error(const std::string& msg) { g_lastError = msg; }
+extern "C" const char* b200_last_error(void) { return g_lastError.c_str(); }
+
+#define API_BEGIN try {
+#define API_END } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; } \
+                  catch (const std::exception& e) { b200_set_error(e.what()); return B200_ERR_INVALID; } return B200_OK;
+
+ScopedTimer::ScopedTimer(b200_ctx* c_, int slot_, cudaStream_t s_) : c(c_), slot(slot_), s(s_) {
+    if (!c->timing) return;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    cudaEventRecord(a, s);
+}
+ScopedTimer::~ScopedTimer() {
+    if (!c->timing || !a) return;
+    cudaEventRecord(b, s);
+    c->timers[slot].pending.emplace_back(a, b);
+}
+
+// ---------------------------------------------------------------------------------------------
+void b200_box_set(b200_ctx* c, const double* box) {
+    // reduced form is required (System::setDefaultPeriodicBoxVectors enforces it upstream)
+    if (box[1] != 0 || box[2] != 0 || box[5] != 0) throw B200Error(B200_ERR_INVALID, "periodic box vectors must be in reduced form");
+    if (!(box[0] > 0 && box[4] > 0 && box[8] > 0)) throw B200Error(B200_ERR_INVALID, "periodic box vectors must have positive diagonal");
+    memcpy(c->boxHost, box, sizeof(double) * 9);
+    BoxD d; d.ax = box[0]; d.bx = box[3]; d.by = box[4]; d.cx = box[6]; d.cy = box[7]; d.cz = box[8];
+    d.iax = 1.0 / d.ax; d.iby = 1.0 / d.by; d.icz = 1.0 / d.cz;
+    c->boxD = d;
+    BoxF f; f.ax = (float)d.ax; f.bx = (float)d.bx; f.by = (float)d.by; f.cx = (float)d.cx; f.cy = (float)d.cy; f.cz = (float)d.cz;
+    f.iax = (float)d.iax; f.iby = (float)d.iby; f.icz = (float)d.icz;
+    f.triclinic = (d.bx != 0 || d.cx != 0 || d.cy != 0) ? 1 : 0;
+    c->boxF = f;
+    if (c->hasNonbonded && c->nb.method >= B200_NB_CUTOFF_PERIODIC) {
+        // CudaNonbondedUtilities.cpp:391-396: the box must be at least twice the cutoff
+        const double m = std::min(d.ax, std::min(d.by, d.cz));
+        if (m < 2 * c->nb.cutoff) throw B200Error(B200_ERR_INVALID, "The periodic box size has decreased to less than twice the nonbonded cutoff.");
+    }
+}
+
+extern "C" int b200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { b200_set_error("cudaGetDeviceCount failed"); return B200_ERR_CUDA; }
+    return n;
+}
+
+extern "C" int b200_context_create(const b200_system_desc* desc, b200_ctx** out) {
+    API_BEGIN
+    if (!desc || !out || desc->num_atoms <= 0) throw B200Error(B200_ERR_INVALID, "b200_context_create: bad arguments");
+    int ndev = 0;
+    CUDA_CHECK(cudaGetDeviceCount(&ndev));
+    if (desc->device < 0 || desc->device >= ndev) throw B200Error(B200_ERR_CUDA, "b200_context_create: no such CUDA device");
+    CUDA_CHECK(cudaSetDevice(desc->device));
+    cudaDeviceProp prop;
+    CUDA_CHECK(cudaGetDeviceProperties(&prop, desc->device));
+    if (prop.major < 10) throw B200Error(B200_ERR_UNSUPPORTED, "the B200 platform needs a compute capability 10.x device");
+    b200_ctx* c = new b200_ctx();
+    *out = c;
+    c->device = desc->device; c->smCount = prop.multiProcessorCount;
+    c->N = desc->num_atoms; c->Npad = ((c->N + 31) / 32) * 32; c->B = c->Npad / 32; c->numSuper = (c->B + 31) / 32;
+    c->usePmeStream = !(desc->flags & B200_CTX_DISABLE_PME_STREAM);
+    CUDA_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CUDA_CHECK(cudaStreamCreateWithFlags(&c->pmeStream, cudaStreamNonBlocking));
+    CUDA_CHECK(cudaEventCreateWithFlags(&c->evFork, cudaEventDisableTiming));
+    CUDA_CHECK(cudaEventCreateWithFlags(&c->evPmeDone, cudaEventDisableTiming));
+    b200_box_set(c, desc->box);
+    c->mass.assign(desc->mass, desc->mass + c->N);
+    c->numConstraints = desc->num_constraints;
+    if (desc->num_constraints > 0) {
+        c->conAtoms.assign(desc->constraint_atoms, desc->constraint_atoms + 2 * desc->num_constraints);
+        c->conDist.assign(desc->constraint_dist, desc->constraint_dist + desc->num_constraints);
+    }
+    const size_t P = c->Npad;
+    dmalloc(c->posq, P); dmalloc(c->posqCorr, P); dmalloc(c->velm, P); dmalloc(c->sigEps, P); dmalloc(c->atomIndex, P); dmalloc(c->cellOffsets, P);
+    dmalloc(c->force, 3 * P); dmalloc(c->counters, 1);
+    dmalloc(c->posqTmp, P); dmalloc(c->posqCorrTmp, P); dmalloc(c->velmTmp, P); dmalloc(c->atomIndexTmp, P); dmalloc(c->cellOffsetsTmp, P);
+    dmalloc(c->blockCenter, (size_t)c->B); dmalloc(c->blockHalf, (size_t)c->B); dmalloc(c->superCenter, (size_t)c->numSuper); dmalloc(c->superHalf, (size_t)c->numSuper);
+    dmalloc(c->refPosq, P);
+    CUDA_CHECK(cudaMallocHost((void**)&c->countersHost, sizeof(DevCounters)));
+    CUDA_CHECK(cudaMemsetAsync(c->posq, 0, sizeof(float4) * P, c->stream));
+    CUDA_CHECK(cudaMemsetAsync(c->posqCorr, 0, sizeof(float4) * P, c->stream));
+    CUDA_CHECK(cudaMemsetAsync(c->sigEps, 0, sizeof(float2) * P, c->stream));
+    CUDA_CHECK(cudaMemsetAsync(c->cellOffsets, 0, sizeof(int4) * P, c->stream));
+    CUDA_CHECK(cudaMemsetAsync(c->force, 0, sizeof(long long) * 3 * P, c->stream));
+    CUDA_CHECK(cudaMemsetAsync(c->counters, 0, sizeof(DevCounters), c->stream));
+    CUDA_CHECK(cudaMemsetAsync(c->refPosq, 0, sizeof(float4) * P, c->stream));
+    std::vector<double4> v(P);
+    for (size_t i = 0; i < P; i++) { v[i].x = v[i].y = v[i].z = 0; v[i].w = (i < (size_t)c->N && c->mass[i] > 0) ? 1.0 / c->mass[i] : 0.0; }
+    CUDA_CHECK(cudaMemcpyAsync(c->velm, v.data(), sizeof(double4) * P, cudaMemcpyHostToDevice, c->stream));
+    c->hostAtomIndex.resize(P); std::iota(c->hostAtomIndex.begin(), c->hostAtomIndex.end(), 0);
+    c->hostSlotOf = c->hostAtomIndex;
+    CUDA_CHECK(cudaMemcpyAsync(c->atomIndex, c->hostAtomIndex.data(), sizeof(int) * P, cudaMemcpyHostToDevice, c->stream));
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    API_END
+}
+
+extern "C" void b200_context_destroy(b200_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    b200_comm_destroy(c);
+    b200_pme_destroy(c);
+    dfree(c->posq); dfree(c->posqCorr); dfree(c->velm); dfree(c->sigEps); dfree(c->atomIndex); dfree(c->cellOffsets); dfree(c->force); dfree(c->counters);
+    dfree(c->posqTmp); dfree(c->posqCorrTmp); dfree(c->velmTmp); dfree(c->atomIndexTmp); dfree(c->cellOffsetsTmp);
+    dfree(c->blockCenter); dfree(c->blockHalf); dfree(c->superCenter); dfree(c->superHalf); dfree(c->refPosq);
+    dfree(c->units); dfree(c->jAtoms); dfree(c->pairOut);
+    dfree(c->settleAtoms); dfree(c->settleParams); dfree(c->freeAtoms);
+    dfree(c->exclTiles); dfree(c->exclFlags); dfree(c->exclRowStart); dfree(c->exclRowCols); dfree(c->dExclPairs); dfree(c->dExcPairs); dfree(c->dExcParams);
+    dfree(c->bondAtoms); dfree(c->bondParams); dfree(c->angleAtoms); dfree(c->angleParams); dfree(c->torsionAtoms); dfree(c->torsionParams);
+    dfree(c->sortKeys); dfree(c->sortCount); dfree(c->sortStart); dfree(c->sortOrder);
+    for (auto& g : c->groups) dfree(g.dBase);
+    if (c->countersHost) cudaFreeHost(c->countersHost);
+    for (auto& t : c->timers) for (auto& p : t.pending) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+    cudaEventDestroy(c->evFork); cudaEventDestroy(c->evPmeDone);
+    cudaStreamDestroy(c->stream); cudaStreamDestroy(c->pmeStream);
+    delete c;
+}
+
+// ---------------------------------------------------------------------------------------------
+extern "C" int b200_nonbonded_create(b200_ctx* c, const b200_nonbonded_desc* d) {
+    API_BEGIN
+    if (!c || !d) throw B200Error(B200_ERR_INVALID, "b200_nonbonded_create: null argument");
+    if (c->hasNonbonded) throw B200Error(B200_ERR_UNSUPPORTED, "only one NonbondedForce per context is supported");
+    if (c->finalized) throw B200Error(B200_ERR_INVALID, "forces must be created before the first computation");
+    if (d->method != B200_NB_PME) throw B200Error(B200_ERR_UNSUPPORTED, "NonbondedForce: the B200 platform currently implements the PME method only");
+    if (d->use_switch) throw B200Error(B200_ERR_UNSUPPORTED, "NonbondedForce: switching function not implemented yet");
+    CUDA_CHECK(cudaSetDevice(c->device));
+    c->nb = *d;
+    c->nb.charge = c->nb.sigma = c->nb.epsilon = nullptr; c->nb.exclusion_pairs = c->nb.exception_pairs = nullptr;
+    c->nb.exception_chargeprod = c->nb.exception_sigma = c->nb.exception_epsilon = nullptr;
+    c->charge.assign(d->charge, d->charge + c->N); c->sigma.assign(d->sigma, d->sigma + c->N); c->epsilon.assign(d->epsilon, d->epsilon + c->N);
+    c->exclPairs.assign(d->exclusion_pairs, d->exclusion_pairs + 2 * (size_t)d->num_exclusions);
+    c->excPairs.assign(d->exception_pairs, d->exception_pairs + 2 * (size_t)d->num_exceptions);
+    c->excQQ.assign(d->exception_chargeprod, d->exception_chargeprod + d->num_exceptions);
+    c->excSig.assign(d->exception_sigma, d->exception_sigma + d->num_exceptions);
+    c->excEps.assign(d->exception_epsilon, d->exception_epsilon + d->num_exceptions);
+    for (int k = 0; k < 3; k++) {
+        if (d->grid[k] < 6 || b200_find_legal_fft_dimension(d->grid[k]) != d->grid[k])
+            throw B200Error(B200_ERR_INVALID, "PME grid dimensions must be >= 6 and factor into 2,3,5,7");
+    }
+    c->hasNonbonded = true;
+    // list cutoff = cutoff + padding (CudaNonbondedUtilities.cpp:380-383 uses 8% of the cutoff)
+    const char* padEnv = getenv("B200_NB_PADDING");
+    const double padFrac = padEnv ? atof(padEnv) : 0.10;
+    c->padding = padFrac * d->cutoff;
+    c->paddedCutoff = d->cutoff + c->padding;
+    c->exactEwald = d->ewald_alpha * d->cutoff > 3.95;
+    b200_box_set(c, c->boxHost);
+    // per-slot parameters (nonbondedParameters.cc:30-35: posq.w = q, sigmaEpsilon = (sigma/2, 2 sqrt(eps)))
+    std::vector<float2> se(c->Npad, make_float2(0.f, 0.f));
+    double sumQ = 0, sumQ2 = 0;
+    for (int i = 0; i < c->N; i++) {
+        se[i] = make_float2((float)(0.5 * c->sigma[i]), (float)(2.0 * sqrt(c->epsilon[i])));
+        sumQ += c->charge[i]; sumQ2 += c->charge[i] * c->charge[i];
+    }
+    CUDA_CHECK(cudaMemcpyAsync(c->sigEps, se.data(), sizeof(float2) * c->Npad, cudaMemcpyHostToDevice, c->stream));
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    c->totalCharge = sumQ;
+    // Ewald self energy (CommonCalcNonbondedForce.cpp:397-400)
+    c->selfEnergy = -B200_ONE_4PI_EPS0 * d->ewald_alpha * sumQ2 / sqrt(M_PI);
+    b200_pme_create(c);
+    API_END
+}
+
+extern "C" int b200_nonbonded_get_pme_parameters(const b200_ctx* c, double* alpha, int32_t* nx, int32_t* ny, int32_t* nz) {
+    API_BEGIN
+    if (!c || !c->hasNonbonded) throw B200Error(B200_ERR_INVALID, "no NonbondedForce in this context");
+    *alpha = c->nb.ewald_alpha; *nx = c->nb.grid[0]; *ny = c->nb.grid[1]; *nz = c->nb.grid[2];
+    API_END
+}
+
+extern "C" int b200_find_legal_fft_dimension(int32_t minimum) {
+    if (minimum < 1) return 1;
+    for (int n = minimum;; n++) {
+        int m = n;
+        for (int f : {2, 3, 5, 7}) while (m % f == 0) m /= f;
+        if (m == 1) return n;
+    }
+}
+
+extern "C" int b200_harmonic_bonds_create(b200_ctx* c, int32_t n, const int32_t* atoms, const double* length, const double* k, int32_t) {
+    API_BEGIN
+    if (c->finalized) throw B200Error(B200_ERR_INVALID, "forces must be created before the first computation");
+    for (int i = 0; i < n; i++) { c->hBondAtoms.push_back(atoms[2 * i]); c->hBondAtoms.push_back(atoms[2 * i + 1]); c->hBondParams.push_back(length[i]); c->hBondParams.push_back(k[i]); }
+    API_END
+}
+extern "C" int b200_harmonic_angles_create(b200_ctx* c, int32_t n, const int32_t* atoms, const double* angle, const double* k, int32_t) {
+    API_BEGIN
+    if (c->finalized) throw B200Error(B200_ERR_INVALID, "forces must be created before the first computation");
+    for (int i = 0; i < n; i++) { for (int j = 0; j < 3; j++) c->hAngleAtoms.push_back(atoms[3 * i + j]); c->hAngleParams.push_back(angle[i]); c->hAngleParams.push_back(k[i]); }
+    API_END
+}
+extern "C" int b200_periodic_torsions_create(b200_ctx* c, int32_t n, const int32_t* atoms, const int32_t* periodicity, const double* phase, const double* k, int32_t) {
+    API_BEGIN
+    if (c->finalized) throw B200Error(B200_ERR_INVALID, "forces must be created before the first computation");
+    for (int i = 0; i < n; i++) { for (int j = 0; j < 4; j++) c->hTorsionAtoms.push_back(atoms[4 * i + j]); c->hTorsionPeriod.push_back(periodicity[i]); c->hTorsionParams.push_back(phase[i]); c->hTorsionParams.push_back(k[i]); }
+    API_END
+}
+
+// ---------------------------------------------------------------------------------------------
+// finalize: molecules, identical-molecule groups, SETTLE clusters, exclusion tiles
+static int ufFind(std::vector<int>& p, int i) { while (p[i] != i) { p[i] = p[p[i]]; i = p[i]; } return i; }
+
+void b200_finalize(b200_ctx* c) {
+    if (c->finalized) return;
+    CUDA_CHECK(cudaSetDevice(c->device));
+    const int N = c->N;
+    // ---- molecules = connected components over every index-based term (ComputeContext::findMoleculeGroups, ComputeContext.cpp:228-369)
+    std::vector<int> parent(N); std::iota(parent.begin(), parent.end(), 0);
+    auto join = [&](int a, int b) { a = ufFind(parent, a); b = ufFind(parent, b); if (a != b) parent[std::max(a, b)] = std::min(a, b); };
+    for (int i = 0; i < c->numConstraints; i++) join(c->conAtoms[2 * i], c->conAtoms[2 * i + 1]);
+    for (size_t i = 0; i + 1 < c->exclPairs.size(); i += 2) join(c->exclPairs[i], c->exclPairs[i + 1]);
+    for (size_t i = 0; i + 1 < c->excPairs.size(); i += 2) join(c->excPairs[i], c->excPairs[i + 1]);
+    for (size_t i = 0; i + 1 < c->hBondAtoms.size(); i += 2) join(c->hBondAtoms[i], c->hBondAtoms[i + 1]);
+    for (size_t i = 0; i + 2 < c->hAngleAtoms.size(); i += 3) { join(c->hAngleAtoms[i], c->hAngleAtoms[i + 1]); join(c->hAngleAtoms[i], c->hAngleAtoms[i + 2]); }
+    for (size_t i = 0; i + 3 < c->hTorsionAtoms.size(); i += 4) for (int j = 1; j < 4; j++) join(c->hTorsionAtoms[i], c->hTorsionAtoms[i + j]);
+    std::vector<int> molOf(N), molFirst;
+    std::vector<std::vector<int>> molAtoms;
+    {
+        std::map<int, int> rootToMol;
+        for (int i = 0; i < N; i++) {
+            const int r = ufFind(parent, i);
+            auto it = rootToMol.find(r);
+            if (it == rootToMol.end()) { it = rootToMol.emplace(r, (int)molAtoms.size()).first; molAtoms.emplace_back(); }
+            molOf[i] = it->second; molAtoms[it->second].push_back(i);
+        }
+    }
+    c->numMolecules = (int)molAtoms.size();
+    // ---- signature of each molecule: everything that must match for two molecules to be exchangeable
+    std::vector<std::ostringstream> sig(molAtoms.size());
+    for (size_t m = 0; m < molAtoms.size(); m++) {
+        const auto& at = molAtoms[m];
+        sig[m] << at.size() << "|";
+        for (int a : at) {
+            sig[m] << (a - at[0]) << "," << c->mass[a];
+            if (c->hasNonbonded) sig[m] << "," << c->charge[a] << "," << c->sigma[a] << "," << c->epsilon[a];
+            sig[m] << ";";
+        }
+    }
+    sig.shrink_to_fit();
+    auto addTerm = [&](const char* tag, const int* atoms, int n, const std::string& params) {
+        const int m = molOf[atoms[0]]; const int base = molAtoms[m][0];
+        sig[m] << tag; for (int j = 0; j < n; j++) sig[m] << (atoms[j] - base) << ","; sig[m] << params << ";";
+    };
+    // terms are appended in list order; identical molecules created by the same builder list their terms in the same order
+    for (int i = 0; i < c->numConstraints; i++) addTerm("C", &c->conAtoms[2 * i], 2, std::to_string(c->conDist[i]));
+    for (size_t i = 0; i + 1 < c->exclPairs.size(); i += 2) { int a[2] = {std::min(c->exclPairs[i], c->exclPairs[i + 1]), std::max(c->exclPairs[i], c->exclPairs[i + 1])}; addTerm("X", a, 2, ""); }
+    for (size_t i = 0; i + 1 < c->excPairs.size(); i += 2) { std::ostringstream p; p << c->excQQ[i / 2] << "," << c->excSig[i / 2] << "," << c->excEps[i / 2]; addTerm("E", &c->excPairs[i], 2, p.str()); }
+    for (size_t i = 0; i + 1 < c->hBondAtoms.size(); i += 2) { std::ostringstream p; p << c->hBondParams[i] << "," << c->hBondParams[i + 1]; addTerm("B", &c->hBondAtoms[i], 2, p.str()); }
+    for (size_t i = 0; i + 2 < c->hAngleAtoms.size(); i += 3) { std::ostringstream p; p << c->hAngleParams[2 * (i / 3)] << "," << c->hAngleParams[2 * (i / 3) + 1]; addTerm("A", &c->hAngleAtoms[i], 3, p.str()); }
+    for (size_t i = 0; i + 3 < c->hTorsionAtoms.size(); i += 4) { std::ostringstream p; p << c->hTorsionPeriod[i / 4] << "," << c->hTorsionParams[2 * (i / 4)] << "," << c->hTorsionParams[2 * (i / 4) + 1]; addTerm("T", &c->hTorsionAtoms[i], 4, p.str()); }
+    std::map<std::string, int> groupOf;
+    c->groups.clear();
+    for (size_t m = 0; m < molAtoms.size(); m++) {
+        const auto& at = molAtoms[m];
+        bool contiguous = true;
+        for (size_t k = 1; k < at.size(); k++) contiguous &= (at[k] == at[0] + (int)k);
+        std::string key = sig[m].str();
+        if (!contiguous || at.size() > 128) key += "#unique" + std::to_string(m);   // only contiguous small molecules are exchanged
+        auto it = groupOf.find(key);
+        if (it == groupOf.end()) { it = groupOf.emplace(key, (int)c->groups.size()).first; c->groups.emplace_back(); c->groups.back().atomsPerMol = contiguous ? (int)at.size() : 0; c->groups.back().numMols = 0; }
+        auto& g = c->groups[it->second];
+        if (contiguous) { g.base.push_back(at[0]); g.numMols++; }
+    }
+    // drop groups that cannot be wrapped/sorted as contiguous runs
+    c->groups.erase(std::remove_if(c->groups.begin(), c->groups.end(), [](const b200_ctx::MolGroup& g) { return g.numMols == 0 || g.atomsPerMol == 0; }), c->groups.end());
+    c->maxGroupMols = 1;
+    for (auto& g : c->groups) {
+        dmalloc(g.dBase, (size_t)g.numMols);
+        CUDA_CHECK(cudaMemcpy(g.dBase, g.base.data(), sizeof(int) * g.numMols, cudaMemcpyHostToDevice));
+        c->maxGroupMols = std::max(c->maxGroupMols, g.numMols);
+    }
+    c->sortBits = 1;
+    while (c->sortBits < 8 && (1 << (3 * c->sortBits)) < 2 * c->maxGroupMols) c->sortBits++;
+    c->sortBuckets = 1 << (3 * c->sortBits);
+    dmalloc(c->sortKeys, (size_t)c->maxGroupMols); dmalloc(c->sortOrder, (size_t)c->maxGroupMols);
+    dmalloc(c->sortCount, (size_t)c->sortBuckets);
+    dmalloc(c->sortStart, (size_t)2 * c->sortBuckets + c->sortBuckets / 1024 + 64);
+
+    // ---- SETTLE clusters: three atoms joined by three constraints, two equal lengths (IntegrationUtilities, platforms/common/src/IntegrationUtilities.cpp)
+    {
+        std::vector<std::vector<std::pair<int, double>>> con(N);
+        for (int i = 0; i < c->numConstraints; i++) {
+            con[c->conAtoms[2 * i]].push_back({c->conAtoms[2 * i + 1], c->conDist[i]});
+            con[c->conAtoms[2 * i + 1]].push_back({c->conAtoms[2 * i], c->conDist[i]});
+        }
+        std::vector<char> inCluster(N, 0);
+        std::vector<int4> sa; std::vector<float2> sp;
+        for (int i = 0; i < N; i++) {
+            if (inCluster[i] || con[i].size() != 2) continue;
+            const int j = con[i][0].first, k = con[i][1].first;
+            if (con[j].size() != 2 || con[k].size() != 2) continue;
+            double djk = -1;
+            for (auto& e : con[j]) if (e.first == k) djk = e.second;
+            if (djk < 0) continue;
+            const double dij = con[i][0].second, dik = con[i][1].second;
+            int a0, a1, a2; double d01, d12;
+            if (dij == dik) { a0 = i; a1 = j; a2 = k; d01 = dij; d12 = djk; }
+            else if (dij == djk) { a0 = j; a1 = i; a2 = k; d01 = dij; d12 = dik; }
+            else if (dik == djk) { a0 = k; a1 = i; a2 = j; d01 = dik; d12 = dij; }
+            else continue;
+            if (c->mass[a0] <= 0 || c->mass[a1] <= 0 || c->mass[a2] <= 0) continue;
+            inCluster[i] = inCluster[j] = inCluster[k] = 1;
+            sa.push_back(make_int4(a0, a1, a2, 0)); sp.push_back(make_float2((float)d01, (float)d12));
+        }
+        c->numSettle = (int)sa.size();
+        dmalloc(c->settleAtoms, sa.size()); dmalloc(c->settleParams, sp.size());
+        if (!sa.empty()) {
+            CUDA_CHECK(cudaMemcpy(c->settleAtoms, sa.data(), sizeof(int4) * sa.size(), cudaMemcpyHostToDevice));
+            CUDA_CHECK(cudaMemcpy(c->settleParams, sp.data(), sizeof(float2) * sp.size(), cudaMemcpyHostToDevice));
+        }
+        std::vector<int> freeAtoms;
+        c->numOtherConstraints = 0;
+        for (int i = 0; i < N; i++) {
+            if (inCluster[i]) continue;
+            if (!con[i].empty()) c->numOtherConstraints += (int)con[i].size();
+            else if (c->mass[i] > 0) freeAtoms.push_back(i);
+        }
+        c->numOtherConstraints /= 2;
+        c->numFree = (int)freeAtoms.size();
+        dmalloc(c->freeAtoms, freeAtoms.size());
+        if (!freeAtoms.empty()) CUDA_CHECK(cudaMemcpy(c->freeAtoms, freeAtoms.data(), sizeof(int) * freeAtoms.size(), cudaMemcpyHostToDevice));
+    }
+
+    // ---- exclusion tiles (CudaNonbondedUtilities.cpp:178-243): every diagonal tile plus every block pair joined by an exclusion
+    if (c->hasNonbonded) {
+        std::map<std::pair<int, int>, std::vector<unsigned>> tiles;
+        auto tileOf = [&](int x, int y) -> std::vector<unsigned>& {
+            auto& t = tiles[{x, y}];
+            if (t.empty()) t.assign(32, 0u);
+            return t;
+        };
+        for (int b = 0; b < c->B; b++) {
+            auto& t = tileOf(b, b);
+            for (int i = 0; i < 32; i++) {
+                unsigned f = (i == 31) ? 0xffffffffu : ((2u << i) - 1u);     // j <= i: each pair once, no self term
+                for (int j = 0; j < 32; j++) if (b * 32 + j >= N || b * 32 + i >= N) f |= 1u << j;
+                t[i] = f;
+            }
+        }
+        for (size_t e = 0; e + 1 < c->exclPairs.size(); e += 2) {
+            int a = c->exclPairs[e], b = c->exclPairs[e + 1];
+            if (a == b) continue;
+            if (a > b) std::swap(a, b);
+            const int x = a / 32, y = b / 32;
+            auto& t = tileOf(x, y);
+            if (t[0] == 0 && x != y) {   // fresh off-diagonal tile: mask padding atoms
+                for (int i = 0; i < 32; i++) for (int j = 0; j < 32; j++) if (x * 32 + i >= N || y * 32 + j >= N) t[i] |= 1u << j;
+            }
+            if (x == y) { t[a % 32] |= 1u << (b % 32); t[b % 32] |= 1u << (a % 32); }
+            else t[a % 32] |= 1u << (b % 32);
+        }
+        // off-diagonal tiles created above may have been created by tileOf() with zero flags and no padding mask when t[0]==0 check failed: redo padding mask
+        for (auto& kv : tiles) {
+            const int x = kv.first.first, y = kv.first.second;
+            if (x == y) continue;
+            for (int i = 0; i < 32; i++) for (int j = 0; j < 32; j++) if (x * 32 + i >= N || y * 32 + j >= N) kv.second[i] |= 1u << j;
+        }
+        std::vector<int2> tl; std::vector<unsigned> fl; std::vector<int> rowStart(c->B + 1, 0), rowCols;
+        for (auto& kv : tiles) { tl.push_back(make_int2(kv.first.first, kv.first.second)); fl.insert(fl.end(), kv.second.begin(), kv.second.end()); }
+        for (auto& kv : tiles) if (kv.first.second > kv.first.first) rowStart[kv.first.first + 1]++;
+        for (int b = 0; b < c->B; b++) rowStart[b + 1] += rowStart[b];
+        rowCols.resize(rowStart[c->B]);
+        { std::vector<int> fill(rowStart.begin(), rowStart.end() - 1); for (auto& kv : tiles) if (kv.first.second > kv.first.first) rowCols[fill[kv.first.first]++] = kv.first.second; }
+        c->numExclTiles = (int)tl.size();
+        dmalloc(c->exclTiles, tl.size()); dmalloc(c->exclFlags, fl.size()); dmalloc(c->exclRowStart, rowStart.size()); dmalloc(c->exclRowCols, rowCols.size());
+        CUDA_CHECK(cudaMemcpy(c->exclTiles, tl.data(), sizeof(int2) * tl.size(), cudaMemcpyHostToDevice));
+        CUDA_CHECK(cudaMemcpy(c->exclFlags, fl.data(), sizeof(unsigned) * fl.size(), cudaMemcpyHostToDevice));
+        CUDA_CHECK(cudaMemcpy(c->exclRowStart, rowStart.data(), sizeof(int) * rowStart.size(), cudaMemcpyHostToDevice));
+        if (!rowCols.empty()) CUDA_CHECK(cudaMemcpy(c->exclRowCols, rowCols.data(), sizeof(int) * rowCols.size(), cudaMemcpyHostToDevice));
+        b200_nblist_alloc(c);
+    }
+    b200_bonded_upload(c);
+    c->finalized = true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// state I/O
+void b200_sync_host_order(b200_ctx* c) {
+    if (!c->hostOrderStale) return;
+    CUDA_CHECK(cudaMemcpyAsync(c->hostAtomIndex.data(), c->atomIndex, sizeof(int) * c->Npad, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    for (int s = 0; s < c->N; s++) c->hostSlotOf[c->hostAtomIndex[s]] = s;
+    c->hostOrderStale = false;
+}
+
+
+extern "C" int b200_set_positions(b200_ctx* c, const double* xyz) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    b200_sync_host_order(c);
+    // CommonKernels.cpp:182-227: float cast + correction, cell offsets reset, then reorder
+    std::vector<float4> p(c->Npad, make_float4(0, 0, 0, 0)), q(c->Npad, make_float4(0, 0, 0, 0));
+    for (int s = 0; s < c->N; s++) {
+        const int o = c->hostAtomIndex[s];
+        const double x = xyz[3 * o], y = xyz[3 * o + 1], z = xyz[3 * o + 2];
+        p[s] = make_float4((float)x, (float)y, (float)z, c->hasNonbonded ? (float)c->charge[o] : 0.f);
+        q[s] = make_float4((float)(x - (double)(float)x), (float)(y - (double)(float)y), (float)(z - (double)(float)z), 0.f);
+    }
+    CUDA_CHECK(cudaMemcpyAsync(c->posq, p.data(), sizeof(float4) * c->Npad, cudaMemcpyHostToDevice, c->stream));
+    CUDA_CHECK(cudaMemcpyAsync(c->posqCorr, q.data(), sizeof(float4) * c->Npad, cudaMemcpyHostToDevice, c->stream));
+    CUDA_CHECK(cudaMemsetAsync(c->cellOffsets, 0, sizeof(int4) * c->Npad, c->stream));
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    c->positionsSet = true; c->forcesValid = false;
+    c->stepsSinceReorder = -1;   // reorder before the next computation
+    API_END
+}
+
+extern "C" int b200_get_positions(b200_ctx* c, double* xyz, int32_t enforcePeriodic) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    b200_sync_host_order(c);
+    std::vector<float4> p(c->Npad), q(c->Npad); std::vector<int4> off(c->Npad);
+    d2h(p.data(), c->posq, c->Npad, c->stream); d2h(q.data(), c->posqCorr, c->Npad, c->stream); d2h(off.data(), c->cellOffsets, c->Npad, c->stream);
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    const double* b = c->boxHost;
+    for (int s = 0; s < c->N; s++) {
+        const int o = c->hostAtomIndex[s];
+        double x = (double)p[s].x + q[s].x, y = (double)p[s].y + q[s].y, z = (double)p[s].z + q[s].z;
+        if (!enforcePeriodic) {   // undo the wrapping (CommonKernels.cpp:151-177)
+            x += off[s].x * b[0] + off[s].y * b[3] + off[s].z * b[6];
+            y += off[s].y * b[4] + off[s].z * b[7];
+            z += off[s].z * b[8];
+        }
+        xyz[3 * o] = x; xyz[3 * o + 1] = y; xyz[3 * o + 2] = z;
+    }
+    API_END
+}
+
+extern "C" int b200_set_velocities(b200_ctx* c, const double* xyz) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    b200_sync_host_order(c);
+    std::vector<double4> v(c->Npad);
+    for (int s = 0; s < c->Npad; s++) {
+        if (s < c->N) { const int o = c->hostAtomIndex[s]; v[s].x = xyz[3 * o]; v[s].y = xyz[3 * o + 1]; v[s].z = xyz[3 * o + 2]; v[s].w = c->mass[o] > 0 ? 1.0 / c->mass[o] : 0.0; }
+        else v[s].x = v[s].y = v[s].z = v[s].w = 0;
+    }
+    CUDA_CHECK(cudaMemcpyAsync(c->velm, v.data(), sizeof(double4) * c->Npad, cudaMemcpyHostToDevice, c->stream));
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    API_END
+}
+
+extern "C" int b200_get_velocities(b200_ctx* c, double* xyz) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    b200_sync_host_order(c);
+    std::vector<double4> v(c->Npad);
+    d2h(v.data(), c->velm, c->Npad, c->stream);
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    for (int s = 0; s < c->N; s++) { const int o = c->hostAtomIndex[s]; xyz[3 * o] = v[s].x; xyz[3 * o + 1] = v[s].y; xyz[3 * o + 2] = v[s].z; }
+    API_END
+}
+
+extern "C" int b200_get_forces(b200_ctx* c, double* xyz) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    b200_sync_host_order(c);
+    std::vector<long long> f(3 * (size_t)c->Npad);
+    d2h(f.data(), c->force, f.size(), c->stream);
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    const double scale = 1.0 / B200_FORCE_SCALE;   // CommonKernels.cpp:286-297
+    for (int s = 0; s < c->N; s++) {
+        const int o = c->hostAtomIndex[s];
+        xyz[3 * o] = scale * f[s]; xyz[3 * o + 1] = scale * f[s + c->Npad]; xyz[3 * o + 2] = scale * f[s + 2 * (size_t)c->Npad];
+    }
+    API_END
+}
+
+extern "C" int b200_set_box(b200_ctx* c, const double* box9) {
+    API_BEGIN
+    b200_box_set(c, box9);
+    c->forcesValid = false;
+    if (c->finalized) c->stepsSinceReorder = -1;
+    API_END
+}
+extern "C" int b200_get_box(const b200_ctx* c, double* box9) { memcpy(box9, c->boxHost, sizeof(double) * 9); return B200_OK; }
+extern "C" int b200_set_time(b200_ctx* c, double t, int64_t steps) { c->timePs = t; c->stepCount = steps; return B200_OK; }
+extern "C" int b200_get_time(const b200_ctx* c, double* t, int64_t* steps) { if (t) *t = c->timePs; if (steps) *steps = c->stepCount; return B200_OK; }
+
+// ---------------------------------------------------------------------------------------------
+// force evaluation
+__global__ void zeroEnergy(DevCounters* c) { for (int i = 0; i < 8; i++) c->energy[i] = 0; c->pairCount = 0; }
+
+static void checkOverflow(b200_ctx* c) {
+    // sticky device flag set by the list builder when a capacity was exceeded (the analogue of
+    // CudaNonbondedUtilities::updateNeighborListSize, CudaNonbondedUtilities.cpp:441-479)
+    CUDA_CHECK(cudaMemcpyAsync(c->countersHost, c->counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+}
+
+static void prepareLists(b200_ctx* c, bool verify) {
+    // runs the (device-decided) rebuild; when `verify` is set it also reads the overflow flag back, grows the list
+    // storage and repeats while it overflowed.  b200_step verifies on its first step and every 64th step, and
+    // checks the sticky flag again before returning, so a (very unlikely) overflow in between is never silent.
+    for (int attempt = 0; attempt < 8; attempt++) {
+        b200_nblist_prepare(c);
+        if (!verify) return;
+        checkOverflow(c);
+        if (!c->countersHost->overflow) return;
+        c->tileCapacity = c->tileCapacity * 3 / 2 + 1024;
+        b200_nblist_alloc(c);
+        DevCounters z = *c->countersHost; z.overflow = 0; z.rebuild = 1;
+        CUDA_CHECK(cudaMemcpyAsync(c->counters, &z, sizeof(DevCounters), cudaMemcpyHostToDevice, c->stream));
+        CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    }
+    throw B200Error(B200_ERR_OVERFLOW, "neighbour list kept overflowing");
+}
+
+static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, double* energyOut, bool verify) {
+    CUDA_CHECK(cudaSetDevice(c->device));
+    if (!c->positionsSet) throw B200Error(B200_ERR_INVALID, "Particle positions have not been set");
+    b200_finalize(c);
+    if (c->stepsSinceReorder < 0 || c->stepsSinceReorder >= c->reorderInterval) b200_reorder(c);
+    cudaStream_t s = c->stream;
+    if (forces) CUDA_CHECK(cudaMemsetAsync(c->force, 0, sizeof(long long) * 3 * (size_t)c->Npad, s));
+    if (energy) { zeroEnergy<<<1, 1, 0, s>>>(c->counters); LAUNCH_COUNT(c, 1); }
+    const bool doRecip = c->hasNonbonded && (groups & B200_GROUP_RECIPROCAL) && c->partRank == 0;
+    const bool doDirect = c->hasNonbonded && (groups & B200_GROUP_DIRECT);
+    cudaStream_t ps = c->usePmeStream ? c->pmeStream : s;
+    if (doRecip) {
+        if (c->usePmeStream) { CUDA_CHECK(cudaEventRecord(c->evFork, s)); CUDA_CHECK(cudaStreamWaitEvent(ps, c->evFork, 0)); }
+        b200_pme_launch(c, ps, forces, energy);
+        if (c->usePmeStream) CUDA_CHECK(cudaEventRecord(c->evPmeDone, ps));
+    }
+    if (doDirect) {
+        prepareLists(c, verify);
+        b200_tile_launch(c, forces, energy, false);
+    }
+    if (c->partRank == 0) b200_bonded_launch(c, groups, forces, energy);
+    if (doRecip && c->usePmeStream) CUDA_CHECK(cudaStreamWaitEvent(s, c->evPmeDone, 0));
+    if (forces && c->commRanks > 1) b200_comm_allreduce_forces(c);
+    c->forcesValid = forces && groups == B200_GROUP_ALL;
+    if (energy) {
+        checkOverflow(c);
+        const DevCounters& h = *c->countersHost;
+        double e = 0;
+        const double inv = 1.0 / B200_ENERGY_SCALE;
+        if (doDirect) e += inv * (double)h.energy[E_DIRECT];
+        if (doDirect && c->partRank == 0) e += inv * ((double)h.energy[E_EXCLCORR] + (double)h.energy[E_EXCEPT]);
+        if (doRecip) {
+            e += inv * (double)h.energy[E_RECIP];
+            const double* b = c->boxHost; const double V = b[0] * b[4] * b[8];
+            // host-side constants (CommonCalcNonbondedForce.cpp:893-898): self energy and neutralising plasma
+            e += c->selfEnergy;
+            e -= c->totalCharge * c->totalCharge * M_PI * B200_ONE_4PI_EPS0 / (2.0 * V * c->nb.ewald_alpha * c->nb.ewald_alpha);
+        }
+        if (doDirect && c->partRank == 0 && c->nb.dispersion_coefficient != 0) {
+            const double* b = c->boxHost;
+            e += c->nb.dispersion_coefficient / (b[0] * b[4] * b[8]);   // CommonCalcNonbondedForce.cpp:1111-1115
+        }
+        if ((groups & B200_GROUP_BONDED) && c->partRank == 0) e += inv * (double)h.energy[E_BONDED];
+        if (energyOut) *energyOut = e;
+        if (h.overflow) throw B200Error(B200_ERR_OVERFLOW, "neighbour list overflow detected after the computation");
+    }
+}
+
+void b200_compute_impl(b200_ctx* c, unsigned groups, bool forces, bool energy, double* energyOut) { computeImpl(c, groups, forces, energy, energyOut, true); }
+
+extern "C" int b200_compute(b200_ctx* c, uint32_t groups, int32_t includeForces, int32_t includeEnergy, double* energy) {
+    API_BEGIN
+    b200_compute_impl(c, groups, includeForces != 0, includeEnergy != 0, energy);
+    API_END
+}
+
+extern "C" int b200_compute_host(b200_ctx* c, const double* xyzIn, uint32_t groups, double* forcesOut, double* energy) {
+    API_BEGIN
+    int rc = b200_set_positions(c, xyzIn); if (rc) return rc;
+    b200_compute_impl(c, groups, true, energy != nullptr, energy);
+    rc = b200_get_forces(c, forcesOut); if (rc) return rc;
+    API_END
+}
+
+extern "C" int b200_direct_pairs(b200_ctx* c, int64_t* count, int32_t* pairs, int64_t capacity) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    if (!c->positionsSet || !c->hasNonbonded) throw B200Error(B200_ERR_INVALID, "b200_direct_pairs: positions and a NonbondedForce are required");
+    b200_finalize(c);
+    if (c->stepsSinceReorder < 0) b200_reorder(c);
+    dfree(c->pairOut); c->pairCapacity = 0;
+    if (pairs && capacity > 0) { dmalloc(c->pairOut, (size_t)capacity); c->pairCapacity = capacity; }
+    zeroEnergy<<<1, 1, 0, c->stream>>>(c->counters);
+    prepareLists(c, true);
+    b200_tile_launch(c, false, false, true);
+    checkOverflow(c);
+    *count = (int64_t)c->countersHost->pairCount;
+    if (pairs && capacity > 0) {
+        const int64_t n = std::min<int64_t>(*count, capacity);
+        CUDA_CHECK(cudaMemcpy(pairs, c->pairOut, sizeof(int2) * (size_t)n, cudaMemcpyDeviceToHost));
+    }
+    dfree(c->pairOut); c->pairCapacity = 0;
+    API_END
+}
+
+extern "C" int b200_nblist_get_stats(b200_ctx* c, b200_nblist_stats* out) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    checkOverflow(c);
+    out->num_blocks = c->B; out->num_tiles = c->countersHost->numTiles; out->num_units = c->countersHost->numUnits;
+    out->num_exclusion_tiles = c->numExclTiles; out->rebuilds = c->countersHost->rebuildCount; out->steps = c->stepCount;
+    out->reorders = 0; out->tile_capacity = c->tileCapacity; out->unit_capacity = c->unitCapacity;
+    API_END
+}
+
+// ---------------------------------------------------------------------------------------------
+// stepping
+extern "C" int b200_integrator_create(b200_ctx* c, const b200_integrator_desc* d) {
+    API_BEGIN
+    c->integ = *d; c->hasIntegrator = true;
+    API_END
+}
+
+extern "C" int b200_step(b200_ctx* c, int32_t nsteps) {
+    API_BEGIN
+    if (!c->hasIntegrator) throw B200Error(B200_ERR_INVALID, "b200_step: no integrator");
+    CUDA_CHECK(cudaSetDevice(c->device));
+    b200_finalize(c);
+    if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
+    for (int i = 0; i < nsteps; i++) {
+        computeImpl(c, B200_GROUP_ALL, true, false, nullptr, i == 0 || (c->stepCount & 63) == 0);
+        b200_integrate_step(c);
+        c->stepCount++; c->timePs += c->integ.dt; c->stepsSinceReorder++;
+        c->forcesValid = false;
+    }
+    checkOverflow(c);
+    if (c->countersHost->overflow) throw B200Error(B200_ERR_OVERFLOW, "neighbour list overflowed during b200_step; state is not trustworthy");
+    API_END
+}
+
+extern "C" int b200_synchronize(b200_ctx* c) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    CUDA_CHECK(cudaStreamSynchronize(c->pmeStream));
+    API_END
+}
+
+// ---------------------------------------------------------------------------------------------
+// measurement
+extern "C" int b200_timing_enable(b200_ctx* c, int32_t on) { c->timing = on != 0; return B200_OK; }
+extern "C" int b200_timing_reset(b200_ctx* c) {
+    for (auto& t : c->timers) { for (auto& p : t.pending) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); } t.pending.clear(); t.ms = 0; t.launches = 0; }
+    return B200_OK;
+}
+extern "C" int b200_timing_read(b200_ctx* c, double* ms, int64_t* launches) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    CUDA_CHECK(cudaDeviceSynchronize());
+    for (int i = 0; i < B200_T_COUNT; i++) {
+        auto& t = c->timers[i];
+        for (auto& p : t.pending) { float m = 0; cudaEventElapsedTime(&m, p.first, p.second); t.ms += m; t.launches++; cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+        t.pending.clear();
+        if (ms) ms[i] = t.ms;
+        if (launches) launches[i] = t.launches;
+    }
+    API_END
+}
+extern "C" int b200_timed_steps(b200_ctx* c, int32_t nsteps, double* totalMs) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    cudaEvent_t a, b; CUDA_CHECK(cudaEventCreate(&a)); CUDA_CHECK(cudaEventCreate(&b));
+    CUDA_CHECK(cudaDeviceSynchronize());
+    CUDA_CHECK(cudaEventRecord(a, c->stream));
+    int rc = b200_step(c, nsteps);
+    CUDA_CHECK(cudaEventRecord(b, c->stream));
+    CUDA_CHECK(cudaEventSynchronize(b));
+    float ms = 0; cudaEventElapsedTime(&ms, a, b);
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    if (rc) return rc;
+    *totalMs = ms;
+    API_END
+}
+extern "C" int64_t b200_launch_count(const b200_ctx* c) { return c->launchCount; }

@@ -1,0 +1,244 @@
+// b200_fft.cu -- hand-written batched 3D real-to-complex / complex-to-real FFT for 2,3,5,7-smooth sizes.
+//
+// Replaces the cuFFT calls of CudaFFT3D::execFFT (platforms/cuda/src/CudaFFT3D.cpp:30-101).  Layout is cuFFT's:
+// real grid [nx][ny][nz] (z fastest), half-complex grid [nx][ny][nz/2+1]; both transforms are unnormalised.
+// Each 1D pass loads a batch of lines into shared memory, runs a Stockham auto-sort mixed-radix FFT (radix 4/2
+// specialised, 3/5/7 through the twiddle table) entirely in shared memory and writes the lines back, so a 3D
+// transform is three passes over the (L2-resident) grid.  The z pass of the forward transform reads the 64-bit
+// fixed-point charge grid directly (folding finishSpreadCharge, pme.cc:125-133, into the FFT).
+#include "b200_internal.cuh"
+#include <cmath>
+#include <vector>
+
+#define FFT_THREADS 256
+
+void b200_fft_make_plan(int n, FFTPlan1D& plan) {
+    plan.n = n; plan.nstages = 0;
+    int m = n;
+    while (m % 4 == 0) { plan.radix[plan.nstages++] = 4; m /= 4; }
+    for (int f : {2, 3, 5, 7}) while (m % f == 0) { plan.radix[plan.nstages++] = f; m /= f; }
+    if (m != 1) throw B200Error(B200_ERR_INVALID, "FFT size must factor into 2,3,5,7");
+}
+
+void b200_fft_make_twiddle(int n, float2*& dTw, cudaStream_t s) {
+    std::vector<float2> w(n);
+    for (int k = 0; k < n; k++) { const double a = -2.0 * M_PI * k / n; w[k] = make_float2((float)cos(a), (float)sin(a)); }
+    dmalloc(dTw, (size_t)n);
+    CUDA_CHECK(cudaMemcpy(dTw, w.data(), sizeof(float2) * n, cudaMemcpyHostToDevice));
+}
+
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+
+// One Stockham stage over `batch` lines held as buf[j*pitch + l].  W = exp(-2 pi i k/n) table (conjugated for inverse).
+template <bool INVERSE, int R>
+__device__ __forceinline__ void fftStage(const float2* __restrict__ in, float2* __restrict__ out, int n, int Ns, int batch, int pitch, const float2* __restrict__ W) {
+    const int nOverR = n / R;
+    const int twStep = n / (Ns * R);
+    float2 root[R];   // exp(-+2 pi i m/R)
+#pragma unroll
+    for (int m = 0; m < R; m++) { root[m] = W[m * nOverR]; if (INVERSE) root[m].y = -root[m].y; }
+    for (int idx = threadIdx.x; idx < batch * nOverR; idx += blockDim.x) {
+        const int l = idx % batch, j = idx / batch;
+        const int k = j % Ns;
+        const int j0 = (j - k) * R + k;
+        float2 x[R];
+#pragma unroll
+        for (int t = 0; t < R; t++) {
+            float2 v = in[(j + t * nOverR) * pitch + l];
+            if (t > 0 && k > 0) { float2 w = W[t * k * twStep]; if (INVERSE) w.y = -w.y; v = cmul(v, w); }
+            x[t] = v;
+        }
+        if (R == 2) {
+            out[j0 * pitch + l] = cadd(x[0], x[1]);
+            out[(j0 + Ns) * pitch + l] = csub(x[0], x[1]);
+        } else if (R == 4) {
+            const float2 a = cadd(x[0], x[2]), b = csub(x[0], x[2]), c = cadd(x[1], x[3]), d = csub(x[1], x[3]);
+            const float2 di = INVERSE ? make_float2(-d.y, d.x) : make_float2(d.y, -d.x);   // -i d (forward), +i d (inverse)
+            out[j0 * pitch + l] = cadd(a, c);
+            out[(j0 + Ns) * pitch + l] = cadd(b, di);
+            out[(j0 + 2 * Ns) * pitch + l] = csub(a, c);
+            out[(j0 + 3 * Ns) * pitch + l] = csub(b, di);
+        } else {
+#pragma unroll
+            for (int q = 0; q < R; q++) {
+                float2 acc = x[0];
+#pragma unroll
+                for (int t = 1; t < R; t++) acc = cadd(acc, cmul(x[t], root[(q * t) % R]));
+                out[(j0 + q * Ns) * pitch + l] = acc;
+            }
+        }
+    }
+}
+
+template <bool INVERSE>
+__device__ float2* fftLinesInSmem(float2* a, float2* b, const FFTPlan1D& plan, int batch, int pitch, const float2* W) {
+    int Ns = 1;
+    for (int s = 0; s < plan.nstages; s++) {
+        __syncthreads();
+        switch (plan.radix[s]) {
+            case 2: fftStage<INVERSE, 2>(a, b, plan.n, Ns, batch, pitch, W); break;
+            case 3: fftStage<INVERSE, 3>(a, b, plan.n, Ns, batch, pitch, W); break;
+            case 4: fftStage<INVERSE, 4>(a, b, plan.n, Ns, batch, pitch, W); break;
+            case 5: fftStage<INVERSE, 5>(a, b, plan.n, Ns, batch, pitch, W); break;
+            default: fftStage<INVERSE, 7>(a, b, plan.n, Ns, batch, pitch, W); break;
+        }
+        Ns *= plan.radix[s];
+        float2* t = a; a = b; b = t;
+    }
+    __syncthreads();
+    return a;   // result
+}
+
+// z pass, forward: real (float or fixed point) lines -> nzc complex
+__global__ void __launch_bounds__(FFT_THREADS) fftZForward(const float* __restrict__ inReal, const long long* __restrict__ inFix, float2* __restrict__ out,
+                                                            int numLines, FFTPlan1D plan, int batch, int pitch, const float2* __restrict__ W) {
+    extern __shared__ float2 smem[];
+    const int n = plan.n, nzc = n / 2 + 1;
+    float2* a = smem; float2* b = smem + (size_t)n * pitch;
+    const int line0 = blockIdx.x * batch;
+    const int nl = min(batch, numLines - line0);
+    const float fixScale = (float)(1.0 / B200_GRID_SCALE);
+    for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
+        const int l = idx / n, j = idx - l * n;
+        float v = 0.f;
+        if (l < nl) {
+            const size_t g = (size_t)(line0 + l) * n + j;
+            v = inFix ? (float)((double)inFix[g] * (1.0 / B200_GRID_SCALE)) : inReal[g];
+        }
+        a[j * pitch + l] = make_float2(v, 0.f);
+    }
+    (void)fixScale;
+    float2* r = fftLinesInSmem<false>(a, b, plan, batch, pitch, W);
+    for (int idx = threadIdx.x; idx < batch * nzc; idx += blockDim.x) {
+        const int l = idx / nzc, j = idx - l * nzc;
+        if (l < nl) out[(size_t)(line0 + l) * nzc + j] = r[j * pitch + l];
+    }
+}
+
+// z pass, inverse: nzc complex lines -> n real
+__global__ void __launch_bounds__(FFT_THREADS) fftZInverse(const float2* __restrict__ in, float* __restrict__ out, int numLines, FFTPlan1D plan, int batch, int pitch, const float2* __restrict__ W) {
+    extern __shared__ float2 smem[];
+    const int n = plan.n, nzc = n / 2 + 1;
+    float2* a = smem; float2* b = smem + (size_t)n * pitch;
+    const int line0 = blockIdx.x * batch;
+    const int nl = min(batch, numLines - line0);
+    for (int idx = threadIdx.x; idx < batch * nzc; idx += blockDim.x) {
+        const int l = idx / nzc, j = idx - l * nzc;
+        float2 v = make_float2(0.f, 0.f);
+        if (l < nl) v = in[(size_t)(line0 + l) * nzc + j];
+        a[j * pitch + l] = v;
+        if (j > 0 && j < n - j) a[(n - j) * pitch + l] = make_float2(v.x, -v.y);   // Hermitian half
+    }
+    float2* r = fftLinesInSmem<true>(a, b, plan, batch, pitch, W);
+    for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
+        const int l = idx / n, j = idx - l * n;
+        if (l < nl) out[(size_t)(line0 + l) * n + j] = r[j * pitch + l].x;
+    }
+}
+
+// strided complex pass (y or x direction), in place.  Lines are addressed as outer*outerStride + inner + j*stride.
+template <bool INVERSE>
+__global__ void __launch_bounds__(FFT_THREADS) fftStrided(float2* __restrict__ data, int innerCount, size_t outerStride, size_t stride,
+                                                           FFTPlan1D plan, int batch, int pitch, const float2* __restrict__ W) {
+    extern __shared__ float2 smem[];
+    const int n = plan.n;
+    float2* a = smem; float2* b = smem + (size_t)n * pitch;
+    const int inner0 = blockIdx.x * batch;
+    const int nl = min(batch, innerCount - inner0);
+    float2* base = data + (size_t)blockIdx.y * outerStride + inner0;
+    for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
+        const int j = idx / batch, l = idx - j * batch;
+        a[j * pitch + l] = l < nl ? base[(size_t)j * stride + l] : make_float2(0.f, 0.f);
+    }
+    float2* r = fftLinesInSmem<INVERSE>(a, b, plan, batch, pitch, W);
+    for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
+        const int j = idx / batch, l = idx - j * batch;
+        if (l < nl) base[(size_t)j * stride + l] = r[j * pitch + l];
+    }
+}
+
+static void pickBatch(int n, int& batch, int& pitch, size_t& smemBytes) {
+    batch = 16;
+    while (batch > 1 && (size_t)n * (batch + 1) * sizeof(float2) * 2 > 96 * 1024) batch >>= 1;
+    pitch = batch | 1;   // odd pitch: conflict-free transposed accesses
+    smemBytes = (size_t)n * pitch * sizeof(float2) * 2;
+    if (smemBytes > 200 * 1024) throw B200Error(B200_ERR_UNSUPPORTED, "FFT dimension too large for the shared-memory FFT");
+}
+
+template <typename K> static void allowSmem(K kernel, size_t bytes) {
+    if (bytes > 48 * 1024) CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+}
+
+void b200_fft3d_exec_r2c(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, const float* inReal, const long long* inFix, float2* out, float2*, cudaStream_t s) {
+    const int nzc = nz / 2 + 1;
+    int batch, pitch; size_t sm;
+    pickBatch(nz, batch, pitch, sm);
+    allowSmem(fftZForward, sm);
+    const int lines = nx * ny;
+    fftZForward<<<(lines + batch - 1) / batch, FFT_THREADS, sm, s>>>(inReal, inFix, out, lines, plan[2], batch, pitch, tw[2]);
+    pickBatch(ny, batch, pitch, sm);
+    allowSmem(fftStrided<false>, sm);
+    fftStrided<false><<<dim3((nzc + batch - 1) / batch, nx), FFT_THREADS, sm, s>>>(out, nzc, (size_t)ny * nzc, (size_t)nzc, plan[1], batch, pitch, tw[1]);
+    pickBatch(nx, batch, pitch, sm);
+    allowSmem(fftStrided<false>, sm);
+    const int inner = ny * nzc;
+    fftStrided<false><<<dim3((inner + batch - 1) / batch, 1), FFT_THREADS, sm, s>>>(out, inner, 0, (size_t)ny * nzc, plan[0], batch, pitch, tw[0]);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void b200_fft3d_exec_c2r(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, float2* in, float2*, float* out, cudaStream_t s) {
+    const int nzc = nz / 2 + 1;
+    int batch, pitch; size_t sm;
+    pickBatch(nx, batch, pitch, sm);
+    allowSmem(fftStrided<true>, sm);
+    const int inner = ny * nzc;
+    fftStrided<true><<<dim3((inner + batch - 1) / batch, 1), FFT_THREADS, sm, s>>>(in, inner, 0, (size_t)ny * nzc, plan[0], batch, pitch, tw[0]);
+    pickBatch(ny, batch, pitch, sm);
+    allowSmem(fftStrided<true>, sm);
+    fftStrided<true><<<dim3((nzc + batch - 1) / batch, nx), FFT_THREADS, sm, s>>>(in, nzc, (size_t)ny * nzc, (size_t)nzc, plan[1], batch, pitch, tw[1]);
+    pickBatch(nz, batch, pitch, sm);
+    allowSmem(fftZInverse, sm);
+    const int lines = nx * ny;
+    fftZInverse<<<(lines + batch - 1) / batch, FFT_THREADS, sm, s>>>(in, out, lines, plan[2], batch, pitch, tw[2]);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void b200_fft3d_forward(b200_ctx* c, cudaStream_t s) {
+    b200_fft3d_exec_r2c(c->gridN[0], c->gridN[1], c->gridN[2], c->plan, c->twiddle, nullptr, c->gridFix, c->gridC, c->gridC2, s);
+    LAUNCH_COUNT(c, 3);
+}
+void b200_fft3d_inverse(b200_ctx* c, cudaStream_t s) {
+    b200_fft3d_exec_c2r(c->gridN[0], c->gridN[1], c->gridN[2], c->plan, c->twiddle, c->gridC, c->gridC2, c->gridReal, s);
+    LAUNCH_COUNT(c, 3);
+}
+
+// ---- host-buffer entry points for unit tests (TestCudaFFT3D.cpp:56-121 compares against pocketfft the same way)
+static int fftHost(int device, int nx, int ny, int nz, const float* in, float* out, bool forward) {
+    try {
+        CUDA_CHECK(cudaSetDevice(device));
+        const int dims[3] = {nx, ny, nz};
+        FFTPlan1D plan[3]; float2* tw[3] = {nullptr, nullptr, nullptr};
+        for (int k = 0; k < 3; k++) { b200_fft_make_plan(dims[k], plan[k]); b200_fft_make_twiddle(dims[k], tw[k], 0); }
+        const size_t G = (size_t)nx * ny * nz, GC = (size_t)nx * ny * (nz / 2 + 1);
+        float* dReal = nullptr; float2* dC = nullptr;
+        dmalloc(dReal, G); dmalloc(dC, GC);
+        if (forward) {
+            CUDA_CHECK(cudaMemcpy(dReal, in, sizeof(float) * G, cudaMemcpyHostToDevice));
+            b200_fft3d_exec_r2c(nx, ny, nz, plan, tw, dReal, nullptr, dC, nullptr, 0);
+            CUDA_CHECK(cudaDeviceSynchronize());
+            CUDA_CHECK(cudaMemcpy(out, dC, sizeof(float2) * GC, cudaMemcpyDeviceToHost));
+        } else {
+            CUDA_CHECK(cudaMemcpy(dC, in, sizeof(float2) * GC, cudaMemcpyHostToDevice));
+            b200_fft3d_exec_c2r(nx, ny, nz, plan, tw, dC, nullptr, dReal, 0);
+            CUDA_CHECK(cudaDeviceSynchronize());
+            CUDA_CHECK(cudaMemcpy(out, dReal, sizeof(float) * G, cudaMemcpyDeviceToHost));
+        }
+        dfree(dReal); dfree(dC);
+        for (int k = 0; k < 3; k++) dfree(tw[k]);
+    } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
+    return B200_OK;
+}
+extern "C" int b200_fft3d_r2c_host(int32_t device, int32_t nx, int32_t ny, int32_t nz, const float* in, float* out) { return fftHost(device, nx, ny, nz, in, out, true); }
+extern "C" int b200_fft3d_c2r_host(int32_t device, int32_t nx, int32_t ny, int32_t nz, const float* in, float* out) { return fftHost(device, nx, ny, nz, in, out, false); }

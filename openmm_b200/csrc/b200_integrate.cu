@@ -1,0 +1,285 @@
+// b200_integrate.cu -- minimal LangevinMiddle integrator with SETTLE, centre-of-mass motion removal, kinetic energy.
+//
+// Supports whole-system runs of the NonbondedForce path; not an optimisation target (BASELINE.json north_star).
+// Mirrors IntegrateLangevinMiddleStepKernel (olla/include/openmm/kernels.h:1392-1420): the three parts of
+// platforms/common/src/kernels/langevinMiddle.cc:9-95 with the velocity and position constraint passes between
+// them (CommonKernels.cpp:3139-3206) are fused into ONE kernel per step: one thread integrates one rigid 3-site
+// molecule (SETTLE, Miyamoto & Kollman 1992; integrationUtilities.cc:328-580) or one unconstrained atom.
+// Noise comes from a counter-based Philox4x32-10 generator keyed by (seed, step, original particle index), so a
+// trajectory does not depend on the atom order on the device nor on the number of GPUs.
+#include "b200_internal.cuh"
+
+struct V3 { double x, y, z; };
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ V3 operator*(V3 a, double s) { return {a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ double dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ V3 cross(V3 a, V3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+__device__ __forceinline__ V3 unit(V3 a) { return a * rsqrt(dot(a, a)); }
+
+// ---- Philox4x32-10 (Salmon et al., SC'11)
+__device__ __forceinline__ uint4 philox(uint4 ctr, uint2 key) {
+#pragma unroll
+    for (int i = 0; i < 10; i++) {
+        const unsigned hi0 = __umulhi(0xD2511F53u, ctr.x), lo0 = 0xD2511F53u * ctr.x;
+        const unsigned hi1 = __umulhi(0xCD9E8D57u, ctr.z), lo1 = 0xCD9E8D57u * ctr.z;
+        ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+        key.x += 0x9E3779B9u; key.y += 0xBB67AE85u;
+    }
+    return ctr;
+}
+__device__ __forceinline__ V3 gaussian3(unsigned long long seed, unsigned long long step, int particle) {
+    const uint4 r = philox(make_uint4((unsigned)particle, (unsigned)step, (unsigned)(step >> 32), 0x5eedu), make_uint2((unsigned)seed, (unsigned)(seed >> 32)));
+    const double u0 = ((double)r.x + 0.5) * (1.0 / 4294967296.0), u1 = ((double)r.y + 0.5) * (1.0 / 4294967296.0);
+    const double u2 = ((double)r.z + 0.5) * (1.0 / 4294967296.0), u3 = ((double)r.w + 0.5) * (1.0 / 4294967296.0);
+    const double m0 = sqrt(-2.0 * log(u0)), m1 = sqrt(-2.0 * log(u2));
+    double s0, c0, s1, c1;
+    sincospi(2.0 * u1, &s0, &c0); sincospi(2.0 * u3, &s1, &c1);
+    (void)s1;
+    return {m0 * c0, m0 * s0, m1 * c1};
+}
+
+struct IntegArgs {
+    float4* posq; float4* posqCorr; double4* velm; const long long* force; const int* atomIndex;
+    int Npad;
+    double dt, vscale, noisescale;
+    unsigned long long seed, step;
+};
+
+__device__ __forceinline__ V3 loadPosD(const IntegArgs& a, int i) { const float4 p = a.posq[i], q = a.posqCorr[i]; return {(double)p.x + q.x, (double)p.y + q.y, (double)p.z + q.z}; }
+__device__ __forceinline__ void storePosD(const IntegArgs& a, int i, V3 p) {
+    const float w = a.posq[i].w;
+    a.posq[i] = make_float4((float)p.x, (float)p.y, (float)p.z, w);
+    a.posqCorr[i] = make_float4((float)(p.x - (double)(float)p.x), (float)(p.y - (double)(float)p.y), (float)(p.z - (double)(float)p.z), 0.f);
+}
+__device__ __forceinline__ V3 loadForce(const IntegArgs& a, int i) {
+    const double sc = 1.0 / B200_FORCE_SCALE;
+    return {sc * (double)a.force[i], sc * (double)a.force[i + a.Npad], sc * (double)a.force[i + 2 * a.Npad]};
+}
+
+// velocity constraints of a rigid triangle: solve the 3x3 system for the bond impulses
+__device__ __forceinline__ void settleVelocities(V3 pA, V3 pB, V3 pC, V3& vA, V3& vB, V3& vC, double iA, double iB, double iC) {
+    const V3 eAB = unit(pB - pA), eBC = unit(pC - pB), eCA = unit(pA - pC);
+    const double rAB = dot(vB - vA, eAB), rBC = dot(vC - vB, eBC), rCA = dot(vA - vC, eCA);
+    const double cAB_BC = dot(eAB, eBC), cBC_CA = dot(eBC, eCA), cCA_AB = dot(eCA, eAB);
+    // M t = r, symmetric
+    const double m00 = iA + iB, m11 = iB + iC, m22 = iC + iA;
+    const double m01 = -cAB_BC * iB, m12 = -cBC_CA * iC, m02 = -cCA_AB * iA;
+    const double det = m00 * (m11 * m22 - m12 * m12) - m01 * (m01 * m22 - m12 * m02) + m02 * (m01 * m12 - m11 * m02);
+    const double inv = 1.0 / det;
+    const double tAB = inv * (rAB * (m11 * m22 - m12 * m12) - m01 * (rBC * m22 - m12 * rCA) + m02 * (rBC * m12 - m11 * rCA));
+    const double tBC = inv * (m00 * (rBC * m22 - m12 * rCA) - rAB * (m01 * m22 - m12 * m02) + m02 * (m01 * rCA - rBC * m02));
+    const double tCA = inv * (m00 * (m11 * rCA - rBC * m12) - m01 * (m01 * rCA - rBC * m02) + rAB * (m01 * m12 - m11 * m02));
+    vA = vA + (eAB * tAB - eCA * tCA) * iA;
+    vB = vB + (eBC * tBC - eAB * tAB) * iB;
+    vC = vC + (eCA * tCA - eBC * tBC) * iC;
+}
+
+// SETTLE for positions: p* are the constrained old positions, d* the unconstrained displacements (updated in place)
+__device__ __forceinline__ void settlePositions(V3 p0, V3 p1, V3 p2, V3& d0, V3& d1, V3& d2, double m0, double m1, double m2, double dOH, double dHH) {
+    const V3 b0 = p1 - p0, c0 = p2 - p0;
+    const double invM = 1.0 / (m0 + m1 + m2);
+    const V3 A1 = d0, B1 = b0 + d1, C1 = c0 + d2;
+    const V3 com = (A1 * m0 + B1 * m1 + C1 * m2) * invM;
+    const V3 a1 = A1 - com, b1 = B1 - com, c1 = C1 - com;
+    // orthonormal frame: ez normal to the old molecular plane, ex in the plane of ez and a1
+    V3 ez = cross(b0, c0);
+    V3 ex = cross(a1, ez);
+    V3 ey = cross(ez, ex);
+    ex = unit(ex); ey = unit(ey); ez = unit(ez);
+    const double b0x = dot(ex, b0), b0y = dot(ey, b0), c0x = dot(ex, c0), c0y = dot(ey, c0);
+    const double a1z = dot(ez, a1);
+    const double b1x = dot(ex, b1), b1y = dot(ey, b1), b1z = dot(ez, b1);
+    const double c1x = dot(ex, c1), c1y = dot(ey, c1), c1z = dot(ez, c1);
+    // canonical triangle
+    const double rc = 0.5 * dHH;
+    const double rbt = sqrt(dOH * dOH - rc * rc);
+    const double ra = rbt * (m1 + m2) * invM, rb = rbt - ra;
+    const double sinphi = a1z / ra, cosphi = sqrt(1.0 - sinphi * sinphi);
+    const double sinpsi = (b1z - c1z) / (2.0 * rc * cosphi), cospsi = sqrt(1.0 - sinpsi * sinpsi);
+    const double ya2 = ra * cosphi;
+    double xb2 = -rc * cospsi;
+    const double yb2 = -rb * cosphi - rc * sinpsi * sinphi, yc2 = -rb * cosphi + rc * sinpsi * sinphi;
+    const double hh2 = 4.0 * xb2 * xb2 + (yb2 - yc2) * (yb2 - yc2) + (b1z - c1z) * (b1z - c1z);
+    xb2 -= 0.5 * (2.0 * xb2 + sqrt(4.0 * xb2 * xb2 - hh2 + dHH * dHH));   // keeps |b-c| exactly dHH for unequal masses
+    // in-plane rotation
+    const double al = xb2 * (b0x - c0x) + b0y * yb2 + c0y * yc2;
+    const double be = xb2 * (c0y - b0y) + b0x * yb2 + c0x * yc2;
+    const double ga = b0x * b1y - b1x * b0y + c0x * c1y - c1x * c0y;
+    const double ab2 = al * al + be * be;
+    const double sinth = (al * ga - be * sqrt(ab2 - ga * ga)) / ab2, costh = sqrt(1.0 - sinth * sinth);
+    const V3 a3 = {-ya2 * sinth, ya2 * costh, a1z};
+    const V3 b3 = {xb2 * costh - yb2 * sinth, xb2 * sinth + yb2 * costh, b1z};
+    const V3 c3 = {-xb2 * costh - yc2 * sinth, -xb2 * sinth + yc2 * costh, c1z};
+    d0 = com + ex * a3.x + ey * a3.y + ez * a3.z;
+    d1 = com + ex * b3.x + ey * b3.y + ez * b3.z - b0;
+    d2 = com + ex * c3.x + ey * c3.y + ez * c3.z - c0;
+}
+
+__global__ void __launch_bounds__(128) langevinMiddleStep(IntegArgs a, int numSettle, const int4* __restrict__ settleAtoms, const float2* __restrict__ settleParams,
+                                                           int numFree, const int* __restrict__ freeAtoms) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const double halfdt = 0.5 * a.dt, invDt = 1.0 / a.dt;
+    if (t < numSettle) {
+        const int4 at = settleAtoms[t]; const float2 prm = settleParams[t];
+        const int idx[3] = {at.x, at.y, at.z};
+        V3 p[3], v[3], d[3], old[3]; double im[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            p[k] = loadPosD(a, idx[k]);
+            const double4 vm = a.velm[idx[k]];
+            im[k] = vm.w;
+            v[k] = V3{vm.x, vm.y, vm.z} + loadForce(a, idx[k]) * (a.dt * vm.w);          // part 1
+        }
+        settleVelocities(p[0], p[1], p[2], v[0], v[1], v[2], im[0], im[1], im[2]);
+#pragma unroll
+        for (int k = 0; k < 3; k++) {                                                       // part 2
+            d[k] = v[k] * halfdt;
+            const V3 g = gaussian3(a.seed, a.step, a.atomIndex[idx[k]]);
+            v[k] = v[k] * a.vscale + g * (a.noisescale * sqrt(im[k]));
+            d[k] = d[k] + v[k] * halfdt;
+            old[k] = d[k];
+        }
+        settlePositions(p[0], p[1], p[2], d[0], d[1], d[2], 1.0 / im[0], 1.0 / im[1], 1.0 / im[2], prm.x, prm.y);
+#pragma unroll
+        for (int k = 0; k < 3; k++) {                                                       // part 3
+            v[k] = v[k] + (d[k] - old[k]) * invDt;
+            a.velm[idx[k]] = make_double4(v[k].x, v[k].y, v[k].z, im[k]);
+            storePosD(a, idx[k], p[k] + d[k]);
+        }
+    } else if (t < numSettle + numFree) {
+        const int i = freeAtoms[t - numSettle];
+        const double4 vm = a.velm[i];
+        V3 v = V3{vm.x, vm.y, vm.z} + loadForce(a, i) * (a.dt * vm.w);
+        V3 d = v * halfdt;
+        const V3 g = gaussian3(a.seed, a.step, a.atomIndex[i]);
+        v = v * a.vscale + g * (a.noisescale * sqrt(vm.w));
+        d = d + v * halfdt;
+        a.velm[i] = make_double4(v.x, v.y, v.z, vm.w);
+        storePosD(a, i, loadPosD(a, i) + d);
+    }
+}
+
+// ---- centre-of-mass motion removal (platforms/common/src/kernels/removeCM.cc)
+__global__ void __launch_bounds__(256) cmMomentum(const double4* __restrict__ velm, int N, DevCounters* counters) {
+    double px = 0, py = 0, pz = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+        const double4 v = velm[i];
+        if (v.w != 0.0) { const double m = 1.0 / v.w; px += m * v.x; py += m * v.y; pz += m * v.z; }
+    }
+    __shared__ double red[3][256];
+    red[0][threadIdx.x] = px; red[1][threadIdx.x] = py; red[2][threadIdx.x] = pz;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) for (int k = 0; k < 3; k++) red[k][threadIdx.x] += red[k][threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x < 3) atomicAddFixed(&counters->momentum[threadIdx.x], (long long)(red[threadIdx.x][0] * 1048576.0));   // 2^20 fixed point
+}
+__global__ void cmRemove(double4* velm, int N, double invTotalMass, DevCounters* counters) {
+    const double sc = invTotalMass / 1048576.0;
+    const double vx = sc * (double)counters->momentum[0], vy = sc * (double)counters->momentum[1], vz = sc * (double)counters->momentum[2];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+        double4 v = velm[i];
+        if (v.w != 0.0) { v.x -= vx; v.y -= vy; v.z -= vz; velm[i] = v; }
+    }
+}
+__global__ void cmZero(DevCounters* counters) { counters->momentum[0] = counters->momentum[1] = counters->momentum[2] = 0; }
+
+__global__ void __launch_bounds__(256) kineticEnergy(const double4* __restrict__ velm, int N, DevCounters* counters) {
+    double e = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+        const double4 v = velm[i];
+        if (v.w != 0.0) e += (v.x * v.x + v.y * v.y + v.z * v.z) / v.w;
+    }
+    __shared__ double red[256];
+    red[threadIdx.x] = e;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o]; __syncthreads(); }
+    if (threadIdx.x == 0) atomicAddFixed(&counters->energy[E_KINETIC], toFixedD(0.5 * red[0] * (1.0 / 1024.0)));   // scaled: KE of 1M atoms ~ 4e6 kJ/mol
+}
+__global__ void keZero(DevCounters* counters) { counters->energy[E_KINETIC] = 0; }
+
+// standalone constraint passes (ApplyConstraintsKernel::apply / applyToVelocities, kernels.h:251-278)
+__global__ void settleOnly(IntegArgs a, int numSettle, const int4* __restrict__ settleAtoms, const float2* __restrict__ settleParams, int velocities) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= numSettle) return;
+    const int4 at = settleAtoms[t]; const float2 prm = settleParams[t];
+    const int idx[3] = {at.x, at.y, at.z};
+    V3 p[3], v[3]; double im[3];
+    for (int k = 0; k < 3; k++) { p[k] = loadPosD(a, idx[k]); const double4 vm = a.velm[idx[k]]; v[k] = {vm.x, vm.y, vm.z}; im[k] = vm.w; }
+    if (velocities) {
+        settleVelocities(p[0], p[1], p[2], v[0], v[1], v[2], im[0], im[1], im[2]);
+        for (int k = 0; k < 3; k++) a.velm[idx[k]] = make_double4(v[k].x, v[k].y, v[k].z, im[k]);
+    } else {
+        // as ApplyConstraintsKernel::apply does: zero displacement, SETTLE, add the resulting displacement
+        V3 d0 = {0, 0, 0}, d1 = {0, 0, 0}, d2 = {0, 0, 0};
+        settlePositions(p[0], p[1], p[2], d0, d1, d2, 1.0 / im[0], 1.0 / im[1], 1.0 / im[2], prm.x, prm.y);
+        const V3 q0 = p[0] + d0, q1 = p[1] + d1, q2 = p[2] + d2;
+        storePosD(a, idx[0], q0); storePosD(a, idx[1], q1); storePosD(a, idx[2], q2);
+    }
+}
+
+static IntegArgs makeArgs(b200_ctx* c) {
+    IntegArgs a;
+    a.posq = c->posq; a.posqCorr = c->posqCorr; a.velm = c->velm; a.force = c->force; a.atomIndex = c->atomIndex; a.Npad = c->Npad;
+    a.dt = c->integ.dt;
+    const double kT = 0.00831446261815324 * c->integ.temperature;   // BOLTZ (SimTKOpenMMRealType.h)
+    a.vscale = exp(-c->integ.dt * c->integ.friction);
+    a.noisescale = sqrt(kT * (1.0 - a.vscale * a.vscale));
+    a.seed = c->integ.seed; a.step = (unsigned long long)c->stepCount;
+    return a;
+}
+
+void b200_integrate_step(b200_ctx* c) {
+    cudaStream_t s = c->stream;
+    ScopedTimer tm(c, B200_T_INTEGRATE, s);
+    if (c->integ.remove_cm_every > 0 && c->stepCount % c->integ.remove_cm_every == 0) {
+        double total = 0; for (double m : c->mass) total += m;
+        cmZero<<<1, 1, 0, s>>>(c->counters);
+        cmMomentum<<<c->smCount * 2, 256, 0, s>>>(c->velm, c->N, c->counters);
+        cmRemove<<<c->smCount * 4, 256, 0, s>>>(c->velm, c->N, 1.0 / total, c->counters);
+        LAUNCH_COUNT(c, 3);
+    }
+    const int units = c->numSettle + c->numFree;
+    if (units > 0) {
+        langevinMiddleStep<<<(units + 127) / 128, 128, 0, s>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, c->numFree, c->freeAtoms);
+        LAUNCH_COUNT(c, 1);
+    }
+    CUDA_CHECK(cudaGetLastError());
+}
+
+extern "C" int b200_apply_constraints(b200_ctx* c, double) {
+    try {
+        CUDA_CHECK(cudaSetDevice(c->device));
+        b200_finalize(c);
+        if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
+        if (c->numSettle > 0) { settleOnly<<<(c->numSettle + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, 0); LAUNCH_COUNT(c, 1); }
+        CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        c->stepsSinceReorder = -1;
+    } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
+    return B200_OK;
+}
+extern "C" int b200_apply_velocity_constraints(b200_ctx* c, double) {
+    try {
+        CUDA_CHECK(cudaSetDevice(c->device));
+        b200_finalize(c);
+        if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
+        if (c->numSettle > 0) { settleOnly<<<(c->numSettle + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, 1); LAUNCH_COUNT(c, 1); }
+        CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
+    return B200_OK;
+}
+extern "C" int b200_kinetic_energy(b200_ctx* c, double* ke) {
+    try {
+        CUDA_CHECK(cudaSetDevice(c->device));
+        keZero<<<1, 1, 0, c->stream>>>(c->counters);
+        kineticEnergy<<<c->smCount * 2, 256, 0, c->stream>>>(c->velm, c->N, c->counters);
+        LAUNCH_COUNT(c, 2);
+        CUDA_CHECK(cudaMemcpyAsync(c->countersHost, c->counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+        CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        *ke = (double)c->countersHost->energy[E_KINETIC] * (1024.0 / B200_ENERGY_SCALE);
+    } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
+    return B200_OK;
+}
+void b200_integrate_setup(b200_ctx*) {}

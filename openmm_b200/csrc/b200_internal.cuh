@@ -1,0 +1,237 @@
+// b200_internal.cuh -- shared declarations of the B200 NonbondedForce/PME library (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include <stdexcept>
+#include "../../include/b200_nonbonded.h"
+
+#define B200_TILE 32
+#define B200_UNIT_TILES 8            // tiles per work unit (fixed: the float partial-sum grouping must not depend on #GPUs)
+#define B200_ONE_4PI_EPS0 138.93545764438198
+#define B200_FORCE_SCALE 4294967296.0   // 2^32, platforms/cuda/src/kernels/common.cu:29-31
+#define B200_ENERGY_SCALE 4294967296.0
+#define B200_GRID_SCALE 4294967296.0
+
+struct B200Error : public std::runtime_error {
+    int code;
+    B200Error(int c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+void b200_set_error(const std::string& msg);
+
+#define CUDA_CHECK(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) \
+    throw B200Error(B200_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e) + " (" + __FILE__ + ":" + std::to_string(__LINE__) + ")"); } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// POD parameter blocks passed to kernels by value
+struct BoxF {            // reduced-form periodic box, float
+    float ax, bx, by, cx, cy, cz;
+    float iax, iby, icz; // 1/ax, 1/by, 1/cz
+    int   triclinic;
+};
+struct BoxD {
+    double ax, bx, by, cx, cy, cz;
+    double iax, iby, icz;
+};
+
+struct DevCounters {
+    unsigned int numUnits;      // work units in the neighbour list (after build)
+    unsigned int numTiles;      // 32-wide j tiles in the list
+    unsigned int workNext;      // dynamic work queue head of the tile kernel
+    unsigned int overflow;      // sticky: list capacity exceeded
+    int          rebuild;       // 1 => the list must be rebuilt before the next tile kernel
+    int          rebuildCount;
+    unsigned int maxHalfBits[3];// max block half extent per dim, float bits (positive floats order as uints)
+    unsigned int pad0;
+    unsigned long long pairCount;
+    long long    energy[8];     // fixed point 2^32: 0 direct tiles, 1 exclusion corr, 2 exceptions, 3 reciprocal, 4 bonded, 5 kinetic*2
+    long long    momentum[4];   // fixed point: sum m v (x,y,z), unused
+};
+#define E_DIRECT 0
+#define E_EXCLCORR 1
+#define E_EXCEPT 2
+#define E_RECIP 3
+#define E_BONDED 4
+#define E_KINETIC 5
+
+struct FFTPlan1D {
+    int n;
+    int nstages;
+    int radix[12];
+};
+
+struct TimerSlot {
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending;
+    double ms = 0; int64_t launches = 0;
+};
+
+// ---------------------------------------------------------------------------------------------
+struct b200_ctx {
+    int device = 0;
+    int N = 0, Npad = 0, B = 0, numSuper = 0;
+    cudaStream_t stream = nullptr, pmeStream = nullptr;
+    cudaEvent_t evFork = nullptr, evPmeDone = nullptr;
+    bool usePmeStream = true;
+    BoxD boxD; BoxF boxF;
+    double boxHost[9];
+
+    // per-slot state
+    float4* posq = nullptr;        // x,y,z,q
+    float4* posqCorr = nullptr;    // mixed-precision remainder
+    double4* velm = nullptr;       // vx,vy,vz, 1/m
+    float2* sigEps = nullptr;      // sigma/2, 2 sqrt(eps)
+    int*    atomIndex = nullptr;   // slot -> original particle
+    int4*   cellOffsets = nullptr; // box vectors subtracted by wrapping
+    long long* force = nullptr;    // [3*Npad] fixed point
+    DevCounters* counters = nullptr;
+    DevCounters* countersHost = nullptr;  // pinned
+    // scratch for reorder
+    float4* posqTmp = nullptr; float4* posqCorrTmp = nullptr; double4* velmTmp = nullptr; int* atomIndexTmp = nullptr; int4* cellOffsetsTmp = nullptr;
+
+    std::vector<int> hostAtomIndex;   // slot -> orig (host mirror)
+    std::vector<int> hostSlotOf;      // orig -> slot
+    bool hostOrderStale = false;
+    std::vector<double> mass;         // original order
+    bool positionsSet = false;
+
+    // constraints (slot indices == original indices at creation; permutation keeps them valid)
+    int numConstraints = 0;
+    std::vector<int> conAtoms; std::vector<double> conDist;
+    int numSettle = 0; int4* settleAtoms = nullptr; float2* settleParams = nullptr;  // (a0,a1,a2,-), (dist01, dist12)
+    int numFree = 0; int* freeAtoms = nullptr;      // unconstrained, mobile atoms
+    int numOtherConstraints = 0;
+
+    // molecules
+    bool finalized = false;
+    int numMolecules = 0;
+    struct MolGroup { int atomsPerMol; int numMols; int* dBase = nullptr; std::vector<int> base; };
+    std::vector<MolGroup> groups;
+    int* sortKeys = nullptr; int* sortCount = nullptr; int* sortStart = nullptr; int* sortOrder = nullptr; int sortBuckets = 0; int sortBits = 0;
+    int maxGroupMols = 0;
+    int reorderInterval = 250;
+    int64_t stepsSinceReorder = 0;
+
+    // nonbonded
+    bool hasNonbonded = false;
+    b200_nonbonded_desc nb;            // scalars only are valid after create (pointers nulled)
+    std::vector<double> charge, sigma, epsilon;
+    std::vector<int> exclPairs;        // all excluded pairs
+    std::vector<int> excPairs; std::vector<double> excQQ, excSig, excEps;
+    double paddedCutoff = 0, padding = 0;
+    double selfEnergy = 0, totalCharge = 0;
+    bool exactEwald = false;
+    // exclusion tiles
+    int numExclTiles = 0; int2* exclTiles = nullptr; unsigned int* exclFlags = nullptr;
+    int* exclRowStart = nullptr; int* exclRowCols = nullptr;
+    // exclusion correction list + exceptions
+    int numExclPairs = 0; int2* dExclPairs = nullptr;
+    int numExceptions = 0; int2* dExcPairs = nullptr; float4* dExcParams = nullptr;
+    // neighbour list
+    float4* blockCenter = nullptr; float4* blockHalf = nullptr; float4* superCenter = nullptr; float4* superHalf = nullptr;
+    float4* refPosq = nullptr;
+    int4* units = nullptr; int* jAtoms = nullptr; long long unitCapacity = 0, tileCapacity = 0;
+    int2* pairOut = nullptr; long long pairCapacity = 0;
+    int partRank = 0, partRanks = 1;
+
+    // PME
+    int gridN[3] = {0, 0, 0}; int nzc = 0;
+    long long* gridFix = nullptr;   // spread target, fixed point
+    float* gridReal = nullptr;      // potential grid after the inverse transform
+    float2* gridC = nullptr; float2* gridC2 = nullptr;
+    float* moduli[3] = {nullptr, nullptr, nullptr};
+    float2* twiddle[3] = {nullptr, nullptr, nullptr};
+    FFTPlan1D plan[3];
+
+    // bonded
+    int numBonds = 0; int2* bondAtoms = nullptr; float2* bondParams = nullptr;
+    int numAngles = 0; int4* angleAtoms = nullptr; float2* angleParams = nullptr;
+    int numTorsions = 0; int4* torsionAtoms = nullptr; float4* torsionParams = nullptr;
+    std::vector<int> hBondAtoms, hAngleAtoms, hTorsionAtoms; std::vector<double> hBondParams, hAngleParams, hTorsionParams; std::vector<int> hTorsionPeriod;
+
+    // integrator
+    bool hasIntegrator = false;
+    b200_integrator_desc integ;
+    double timePs = 0; int64_t stepCount = 0;
+    bool forcesValid = false;
+
+    // multi-GPU
+    void* ncclComm = nullptr; int commRank = 0, commRanks = 1;
+
+    // measurement
+    bool timing = false;
+    TimerSlot timers[B200_T_COUNT];
+    int64_t launchCount = 0;
+    int smCount = 148;
+};
+
+// RAII-less helpers
+template <typename T> static inline void dmalloc(T*& p, size_t n) { CUDA_CHECK(cudaMalloc((void**)&p, (n ? n : 1) * sizeof(T))); }
+template <typename T> static inline void dfree(T*& p) { if (p) cudaFree(p); p = nullptr; }
+template <typename T> static inline void h2d(T* d, const T* h, size_t n, cudaStream_t s) { if (n) CUDA_CHECK(cudaMemcpyAsync(d, h, n * sizeof(T), cudaMemcpyHostToDevice, s)); }
+template <typename T> static inline void d2h(T* h, const T* d, size_t n, cudaStream_t s) { if (n) CUDA_CHECK(cudaMemcpyAsync(h, d, n * sizeof(T), cudaMemcpyDeviceToHost, s)); }
+
+struct ScopedTimer {   // brackets a kernel family with events when ctx->timing is on
+    b200_ctx* c; int slot; cudaStream_t s; cudaEvent_t a = nullptr, b = nullptr;
+    ScopedTimer(b200_ctx* c_, int slot_, cudaStream_t s_);
+    ~ScopedTimer();
+};
+
+// module entry points (host side)
+void b200_box_set(b200_ctx* c, const double* box9);
+void b200_finalize(b200_ctx* c);                       // molecules, exclusion tiles, clusters (lazy, once)
+void b200_reorder(b200_ctx* c);                        // device-side Hilbert sort of identical molecules
+void b200_sync_host_order(b200_ctx* c);
+void b200_nblist_alloc(b200_ctx* c);
+void b200_nblist_prepare(b200_ctx* c);                 // displacement check + conditional rebuild (device-side decision)
+void b200_nblist_force_rebuild(b200_ctx* c);
+void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs);
+void b200_pme_create(b200_ctx* c);
+void b200_pme_destroy(b200_ctx* c);
+void b200_pme_launch(b200_ctx* c, cudaStream_t s, bool forces, bool energy);
+void b200_bonded_upload(b200_ctx* c);
+void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy);
+void b200_integrate_setup(b200_ctx* c);
+void b200_integrate_step(b200_ctx* c);
+void b200_comm_allreduce_forces(b200_ctx* c);
+void b200_comm_destroy(b200_ctx* c);
+void b200_fft_make_plan(int n, FFTPlan1D& plan);
+void b200_fft_make_twiddle(int n, float2*& dTw, cudaStream_t s);
+void b200_fft3d_forward(b200_ctx* c, cudaStream_t s);  // gridFix -> gridC
+void b200_fft3d_inverse(b200_ctx* c, cudaStream_t s);  // gridC -> gridReal
+void b200_fft3d_exec_r2c(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, const float* inReal, const long long* inFix, float2* out, float2* scratch, cudaStream_t s);
+void b200_fft3d_exec_c2r(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, float2* in, float2* scratch, float* out, cudaStream_t s);
+void b200_compute_impl(b200_ctx* c, unsigned groups, bool forces, bool energy, double* energyOut);
+
+#define LAUNCH_COUNT(c, n) ((c)->launchCount += (n))
+
+// ---------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ void imageDelta(float& dx, float& dy, float& dz, const BoxF& b) {
+    // nearest periodic image of a displacement in a reduced triclinic cell (z, then y, then x);
+    // same reduction order as the reference's APPLY_PERIODIC_TO_DELTA (platforms/common/src/kernels, triclinic branch)
+    float s = rintf(dz * b.icz); dx -= s * b.cx; dy -= s * b.cy; dz -= s * b.cz;
+    s = rintf(dy * b.iby); dx -= s * b.bx; dy -= s * b.by;
+    s = rintf(dx * b.iax); dx -= s * b.ax;
+}
+__device__ __forceinline__ void imageDeltaD(double& dx, double& dy, double& dz, const BoxD& b) {
+    double s = rint(dz * b.icz); dx -= s * b.cx; dy -= s * b.cy; dz -= s * b.cz;
+    s = rint(dy * b.iby); dx -= s * b.bx; dy -= s * b.by;
+    s = rint(dx * b.iax); dx -= s * b.ax;
+}
+__device__ __forceinline__ long long toFixed(float f) { return (long long)((double)f * B200_FORCE_SCALE); }
+__device__ __forceinline__ long long toFixedD(double f) { return (long long)(f * B200_FORCE_SCALE); }
+__device__ __forceinline__ void atomicAddFixed(long long* p, long long v) {
+    atomicAdd((unsigned long long*)p, (unsigned long long)v);
+}
+__device__ __forceinline__ float warpSum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warpSumD(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+#endif

@@ -1,0 +1,239 @@
+// b200_nblist.cu -- neighbour list: block bounding boxes, displacement (Verlet buffer) check, tile-list build.
+//
+// Replaces findBlockBounds / sortBoxData / findBlocksWithInteractions
+// (platforms/cuda/src/kernels/findInteractingBlocks.cu:41-542) and the host logic of
+// CudaNonbondedUtilities::prepareInteractions (CudaNonbondedUtilities.cpp:385-412).
+// Atoms are already ordered along a Hilbert curve (b200_reorder.cu), so 32 consecutive atoms form a compact
+// block and 32 consecutive blocks a compact "super block"; the build is a two-level bounding-box sweep
+// followed by an exact per-atom test against the 32 atoms of block X and a ballot/popc compaction of the
+// surviving j atoms into work units of up to 8 tiles.  Everything is decided on the device: the kernels
+// are launched every step and return immediately unless counters->rebuild is set.
+#include "b200_internal.cuh"
+
+#define NB_WARPS 4
+#define NB_THREADS (NB_WARPS * 32)
+#define NB_BUF (B200_UNIT_TILES * 32 + 32)
+
+// ---- displacement check (findInteractingBlocks.cu:176-185: rebuild when an atom moved more than padding/2)
+__global__ void nbCheckDisplacement(const float4* __restrict__ posq, const float4* __restrict__ refPosq, int N, float maxDisp2, DevCounters* counters) {
+    if (counters->rebuild) return;
+    bool moved = false;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+        const float4 p = posq[i], r = refPosq[i];
+        const float dx = p.x - r.x, dy = p.y - r.y, dz = p.z - r.z;
+        moved |= (dx * dx + dy * dy + dz * dz > maxDisp2);
+    }
+    if (__any_sync(0xffffffffu, moved) && (threadIdx.x & 31) == 0) counters->rebuild = 1;
+}
+
+// ---- per-block bounding boxes (findBlockBounds, findInteractingBlocks.cu:41-102), one warp per block
+__global__ void nbBlockBounds(const float4* __restrict__ posq, float4* __restrict__ refPosq, int N, int B, BoxF box,
+                              float4* __restrict__ blockCenter, float4* __restrict__ blockHalf, DevCounters* counters) {
+    if (!counters->rebuild) return;
+    const int lane = threadIdx.x & 31;
+    const int warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { counters->numUnits = 0; counters->numTiles = 0; counters->rebuildCount++; }
+    for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < B; b += warpsPerGrid) {
+        const int slot = b * 32 + lane;
+        const float4 p = posq[slot];
+        refPosq[slot] = p;
+        const float x0 = __shfl_sync(0xffffffffu, p.x, 0), y0 = __shfl_sync(0xffffffffu, p.y, 0), z0 = __shfl_sync(0xffffffffu, p.z, 0);
+        float dx = p.x - x0, dy = p.y - y0, dz = p.z - z0;
+        imageDelta(dx, dy, dz, box);
+        if (slot >= N) { dx = dy = dz = 0.f; }
+        float lx = dx, ly = dy, lz = dz, hx = dx, hy = dy, hz = dz;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lx = fminf(lx, __shfl_xor_sync(0xffffffffu, lx, o)); hx = fmaxf(hx, __shfl_xor_sync(0xffffffffu, hx, o));
+            ly = fminf(ly, __shfl_xor_sync(0xffffffffu, ly, o)); hy = fmaxf(hy, __shfl_xor_sync(0xffffffffu, hy, o));
+            lz = fminf(lz, __shfl_xor_sync(0xffffffffu, lz, o)); hz = fmaxf(hz, __shfl_xor_sync(0xffffffffu, hz, o));
+        }
+        if (lane == 0) {
+            blockCenter[b] = make_float4(x0 + 0.5f * (lx + hx), y0 + 0.5f * (ly + hy), z0 + 0.5f * (lz + hz), 0.f);
+            // half extents are rounded up a little so that float rounding can never exclude an atom from its own box
+            blockHalf[b] = make_float4(0.5f * (hx - lx) * 1.000001f + 1e-6f, 0.5f * (hy - ly) * 1.000001f + 1e-6f, 0.5f * (hz - lz) * 1.000001f + 1e-6f, 0.f);
+        }
+    }
+}
+
+// ---- bounding boxes of groups of 32 consecutive blocks ("large blocks", findInteractingBlocks.cu:138-175)
+__global__ void nbSuperBounds(const float4* __restrict__ blockCenter, const float4* __restrict__ blockHalf, int B, int numSuper, BoxF box,
+                              float4* __restrict__ superCenter, float4* __restrict__ superHalf, const DevCounters* counters) {
+    if (!counters->rebuild) return;
+    const int lane = threadIdx.x & 31;
+    const int warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
+    for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < numSuper; s += warpsPerGrid) {
+        const int b = min(s * 32 + lane, B - 1);
+        const float4 c = blockCenter[b], h = blockHalf[b];
+        const float x0 = __shfl_sync(0xffffffffu, c.x, 0), y0 = __shfl_sync(0xffffffffu, c.y, 0), z0 = __shfl_sync(0xffffffffu, c.z, 0);
+        float dx = c.x - x0, dy = c.y - y0, dz = c.z - z0;
+        imageDelta(dx, dy, dz, box);
+        float lx = dx - h.x, ly = dy - h.y, lz = dz - h.z, hx = dx + h.x, hy = dy + h.y, hz = dz + h.z;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lx = fminf(lx, __shfl_xor_sync(0xffffffffu, lx, o)); hx = fmaxf(hx, __shfl_xor_sync(0xffffffffu, hx, o));
+            ly = fminf(ly, __shfl_xor_sync(0xffffffffu, ly, o)); hy = fmaxf(hy, __shfl_xor_sync(0xffffffffu, hy, o));
+            lz = fminf(lz, __shfl_xor_sync(0xffffffffu, lz, o)); hz = fmaxf(hz, __shfl_xor_sync(0xffffffffu, hz, o));
+        }
+        if (lane == 0) {
+            superCenter[s] = make_float4(x0 + 0.5f * (lx + hx), y0 + 0.5f * (ly + hy), z0 + 0.5f * (lz + hz), 0.f);
+            superHalf[s] = make_float4(0.5f * (hx - lx) + 1e-6f, 0.5f * (hy - ly) + 1e-6f, 0.5f * (hz - lz) + 1e-6f, 0.f);
+        }
+    }
+}
+
+__device__ __forceinline__ float boxGap2(float4 cA, float4 hA, float4 cB, float4 hB, const BoxF& box) {
+    float dx = cB.x - cA.x, dy = cB.y - cA.y, dz = cB.z - cA.z;
+    imageDelta(dx, dy, dz, box);
+    dx = fmaxf(0.f, fabsf(dx) - hA.x - hB.x);
+    dy = fmaxf(0.f, fabsf(dy) - hA.y - hB.y);
+    dz = fmaxf(0.f, fabsf(dz) - hA.z - hB.z);
+    return dx * dx + dy * dy + dz * dz;
+}
+
+// ---- tile-list build (findBlocksWithInteractions, findInteractingBlocks.cu:289-542), one warp per block X
+__global__ void __launch_bounds__(NB_THREADS) nbBuild(
+        const float4* __restrict__ posq, int N, int B, int numSuper, BoxF box, float rcp2,
+        const float4* __restrict__ blockCenter, const float4* __restrict__ blockHalf,
+        const float4* __restrict__ superCenter, const float4* __restrict__ superHalf,
+        const int* __restrict__ exclRowStart, const int* __restrict__ exclRowCols,
+        int4* __restrict__ units, int* __restrict__ jAtoms, unsigned unitCapacity, unsigned tileCapacity,
+        int partRank, int partRanks, DevCounters* counters) {
+    if (!counters->rebuild) return;
+    __shared__ float4 sX[NB_WARPS][32];
+    __shared__ int sBuf[NB_WARPS][NB_BUF];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
+    const unsigned ltMask = (1u << lane) - 1u;
+    // rows are dealt round-robin to ranks: every rank gets a statistically identical share of the sweep
+    for (int xi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; xi * partRanks + partRank < B; xi += warpsPerGrid) {
+        const int X = xi * partRanks + partRank;
+        const float4 cX = blockCenter[X], hX = blockHalf[X];
+        const bool single = !box.triclinic && 0.5f * box.ax - hX.x >= sqrtf(rcp2) && 0.5f * box.by - hX.y >= sqrtf(rcp2) && 0.5f * box.cz - hX.z >= sqrtf(rcp2);
+        {
+            const int slot = X * 32 + lane;
+            const float4 p = posq[slot];
+            float dx = p.x - cX.x, dy = p.y - cX.y, dz = p.z - cX.z;
+            imageDelta(dx, dy, dz, box);
+            if (slot >= N) { dx = dy = dz = 1.0e9f; }   // padding atoms never attract neighbours
+            __syncwarp();
+            sX[warp][lane] = make_float4(dx, dy, dz, 0.f);
+            __syncwarp();
+        }
+        const int exBegin = exclRowStart[X], exEnd = exclRowStart[X + 1];
+        int nbuf = 0;
+        for (int s0 = (X >> 5) & ~31; s0 < numSuper; s0 += 32) {   // candidates Y > X live in super blocks >= X/32
+            const int s = s0 + lane;
+            bool sHit = false;
+            if (s < numSuper && s >= (X >> 5)) sHit = boxGap2(cX, hX, superCenter[s], superHalf[s], box) < rcp2;
+            unsigned sMask = __ballot_sync(0xffffffffu, sHit);
+            while (sMask) {
+                const int sb = s0 + __ffs(sMask) - 1; sMask &= sMask - 1;
+                const int Y = sb * 32 + lane;
+                bool bHit = false;
+                if (Y < B && Y > X) {
+                    bHit = boxGap2(cX, hX, blockCenter[Y], blockHalf[Y], box) < rcp2;
+                    for (int e = exBegin; e < exEnd && bHit; e++) if (exclRowCols[e] == Y) bHit = false;  // handled as an exclusion tile
+                }
+                unsigned bMask = __ballot_sync(0xffffffffu, bHit);
+                while (bMask) {
+                    const int Yb = sb * 32 + __ffs(bMask) - 1; bMask &= bMask - 1;
+                    const int slot = Yb * 32 + lane;
+                    bool hit = false;
+                    if (slot < N) {
+                        const float4 p = posq[slot];
+                        float rx = p.x - cX.x, ry = p.y - cX.y, rz = p.z - cX.z;
+                        imageDelta(rx, ry, rz, box);
+                        const float gx = fmaxf(0.f, fabsf(rx) - hX.x), gy = fmaxf(0.f, fabsf(ry) - hX.y), gz = fmaxf(0.f, fabsf(rz) - hX.z);
+                        if (gx * gx + gy * gy + gz * gz < rcp2) {
+                            if (single) {
+                                for (int i = 0; i < 32; i++) {
+                                    const float4 a = sX[warp][i];
+                                    const float dx = rx - a.x, dy = ry - a.y, dz = rz - a.z;
+                                    hit |= (dx * dx + dy * dy + dz * dz < rcp2);
+                                }
+                            } else {
+                                for (int i = 0; i < 32; i++) {
+                                    const float4 a = sX[warp][i];
+                                    float dx = rx - a.x, dy = ry - a.y, dz = rz - a.z;
+                                    imageDelta(dx, dy, dz, box);
+                                    hit |= (dx * dx + dy * dy + dz * dz < rcp2);
+                                }
+                            }
+                        }
+                    }
+                    const unsigned m = __ballot_sync(0xffffffffu, hit);
+                    if (hit) sBuf[warp][nbuf + __popc(m & ltMask)] = slot;
+                    nbuf += __popc(m);
+                    __syncwarp();
+                    if (nbuf >= B200_UNIT_TILES * 32) {   // flush one full work unit
+                        unsigned tileBase = 0, unit = 0;
+                        if (lane == 0) { tileBase = atomicAdd(&counters->numTiles, (unsigned)B200_UNIT_TILES); unit = atomicAdd(&counters->numUnits, 1u); }
+                        tileBase = __shfl_sync(0xffffffffu, tileBase, 0); unit = __shfl_sync(0xffffffffu, unit, 0);
+                        if (tileBase + B200_UNIT_TILES <= tileCapacity && unit < unitCapacity) {
+                            for (int k = lane; k < B200_UNIT_TILES * 32; k += 32) jAtoms[(size_t)tileBase * 32 + k] = sBuf[warp][k];
+                            if (lane == 0) units[unit] = make_int4(X, (int)tileBase, B200_UNIT_TILES, 0);
+                        } else if (lane == 0) counters->overflow = 1;
+                        const int rest = nbuf - B200_UNIT_TILES * 32;
+                        int carry = 0;
+                        if (lane < rest) carry = sBuf[warp][B200_UNIT_TILES * 32 + lane];
+                        __syncwarp();
+                        if (lane < rest) sBuf[warp][lane] = carry;
+                        nbuf = rest;
+                        __syncwarp();
+                    }
+                }
+            }
+        }
+        if (nbuf > 0) {
+            const int nt = (nbuf + 31) >> 5;
+            for (int k = nbuf + lane; k < nt * 32; k += 32) sBuf[warp][k] = -1;
+            __syncwarp();
+            unsigned tileBase = 0, unit = 0;
+            if (lane == 0) { tileBase = atomicAdd(&counters->numTiles, (unsigned)nt); unit = atomicAdd(&counters->numUnits, 1u); }
+            tileBase = __shfl_sync(0xffffffffu, tileBase, 0); unit = __shfl_sync(0xffffffffu, unit, 0);
+            if (tileBase + nt <= tileCapacity && unit < unitCapacity) {
+                for (int k = lane; k < nt * 32; k += 32) jAtoms[(size_t)tileBase * 32 + k] = sBuf[warp][k];
+                if (lane == 0) units[unit] = make_int4(X, (int)tileBase, nt, 0);
+            } else if (lane == 0) counters->overflow = 1;
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void nbFinish(DevCounters* counters) { counters->rebuild = 0; }
+__global__ void nbSetRebuild(DevCounters* counters) { counters->rebuild = 1; }
+
+void b200_nblist_alloc(b200_ctx* c) {
+    dfree(c->units); dfree(c->jAtoms);
+    if (c->tileCapacity == 0) {
+        c->tileCapacity = (long long)c->B * 28 + 1024;
+    }
+    c->unitCapacity = c->B + c->tileCapacity / B200_UNIT_TILES + 64;
+    dmalloc(c->units, (size_t)c->unitCapacity);
+    dmalloc(c->jAtoms, (size_t)c->tileCapacity * 32);
+}
+
+void b200_nblist_force_rebuild(b200_ctx* c) {
+    nbSetRebuild<<<1, 1, 0, c->stream>>>(c->counters);
+    LAUNCH_COUNT(c, 1);
+}
+
+void b200_nblist_prepare(b200_ctx* c) {
+    ScopedTimer tm(c, B200_T_NBLIST, c->stream);
+    const float maxDisp = 0.5f * (float)c->padding;
+    const int grid = c->smCount * 4;
+    nbCheckDisplacement<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, maxDisp * maxDisp, c->counters);
+    nbBlockBounds<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, c->B, c->boxF, c->blockCenter, c->blockHalf, c->counters);
+    nbSuperBounds<<<(c->numSuper + 7) / 8, 256, 0, c->stream>>>(c->blockCenter, c->blockHalf, c->B, c->numSuper, c->boxF, c->superCenter, c->superHalf, c->counters);
+    const float rcp = (float)c->paddedCutoff;
+    int rows = (c->B + c->partRanks - 1) / c->partRanks;
+    int buildGrid = (rows + NB_WARPS - 1) / NB_WARPS;
+    if (buildGrid > c->smCount * 16) buildGrid = c->smCount * 16;
+    nbBuild<<<buildGrid, NB_THREADS, 0, c->stream>>>(c->posq, c->N, c->B, c->numSuper, c->boxF, rcp * rcp,
+        c->blockCenter, c->blockHalf, c->superCenter, c->superHalf, c->exclRowStart, c->exclRowCols,
+        c->units, c->jAtoms, (unsigned)c->unitCapacity, (unsigned)c->tileCapacity, c->partRank, c->partRanks, c->counters);
+    nbFinish<<<1, 1, 0, c->stream>>>(c->counters);
+    LAUNCH_COUNT(c, 5);
+    CUDA_CHECK(cudaGetLastError());
+}

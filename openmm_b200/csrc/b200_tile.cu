@@ -1,0 +1,258 @@
+// b200_tile.cu -- direct-space 32x32 tile kernel (Coulomb erfc + Lennard-Jones, exclusions, int64 forces).
+//
+// Replaces computeNonbonded (platforms/cuda/src/kernels/nonbonded.cu:104-524) with the pair snippet
+// platforms/common/src/kernels/coulombLennardJones.cc:2-76.  Design differences (B200-first):
+//   * persistent CTAs, one warp per work unit taken from a device-side queue; a work unit is one block X
+//     plus up to 8 compacted 32-atom j tiles, so the i-force is flushed once per unit instead of once per tile;
+//   * j positions/parameters are staged in shared memory and read at a rotating index (conflict free),
+//     only the three j-force accumulators travel by warp shuffle (3 SHFL per pair step instead of 9);
+//   * coordinates are re-expressed relative to the block centre once per tile ("single periodic copy" done
+//     per atom, nonbonded.cu:298-301,353-358), the per-pair minimum image is only used for small boxes;
+//   * erfc/exp are replaced by a rational function of r^2 (b200_ewald_coeffs.h);
+//   * pairs within 3e-5 (relative, in r^2) of the cutoff are re-decided in FP64 from the stored coordinates, which
+//     makes the interacting pair set identical to the Reference platform's (ReferenceNeighborList.cpp:208-214);
+//   * energy is accumulated in fixed point so it is bit-reproducible.
+#include "b200_internal.cuh"
+#include "b200_ewald_coeffs.h"
+
+#define TILE_WARPS 8
+#define TILE_THREADS (TILE_WARPS * 32)
+
+struct TileArgs {
+    const float4* __restrict__ posq;
+    const float2* __restrict__ sigEps;
+    const float4* __restrict__ blockCenter;
+    const float4* __restrict__ blockHalf;
+    const int4* __restrict__ units;
+    const int* __restrict__ jAtoms;
+    const int2* __restrict__ exclTiles;
+    const unsigned int* __restrict__ exclFlags;
+    const int* __restrict__ atomIndex;
+    long long* force;
+    DevCounters* counters;
+    int2* pairOut; long long pairCapacity;
+    int N, Npad;
+    int exclBegin, exclEnd;      // exclusion tiles handled by this rank
+    BoxF box; BoxD boxD;
+    float rc2, rcPadded, alpha2, alpha3, alpha, kcoul;
+    double rc2d;
+    float borderTol;             // |r2-rc2| below this -> FP64 decision
+    int exact;                   // use erfcf/expf instead of the rational fit (alpha*rc > 4)
+    int periodic;
+};
+
+__device__ __forceinline__ float fast_rsqrt(float x) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float fast_rcp(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
+template <bool ENERGY>
+__device__ __forceinline__ void pairTerms(const TileArgs& a, float r2, float qq, float sig, float eps, float& s, float& e) {
+    // s = -(dE/dr)/r, e = pair energy
+    const float invR = fast_rsqrt(r2);
+    const float invR2 = invR * invR;
+    float sc, ec = 0.f;
+    if (!a.exact) {
+        const float t = a.alpha2 * r2;
+        float num = fmaf(F_N6, t, F_N5); num = fmaf(num, t, F_N4); num = fmaf(num, t, F_N3); num = fmaf(num, t, F_N2);
+        num = fmaf(num, t, F_N1); num = fmaf(num, t, F_N0);
+        float den = fmaf(F_D5, t, F_D4); den = fmaf(den, t, F_D3); den = fmaf(den, t, F_D2); den = fmaf(den, t, F_D1);
+        den = fmaf(den, t, 1.0f);
+        const float Fz = num * fast_rcp(den);
+        sc = qq * fmaf(-a.alpha3, Fz, invR * invR2);
+        if (ENERGY) {
+            float vn = fmaf(V_N6, t, V_N5); vn = fmaf(vn, t, V_N4); vn = fmaf(vn, t, V_N3); vn = fmaf(vn, t, V_N2);
+            vn = fmaf(vn, t, V_N1); vn = fmaf(vn, t, V_N0);
+            float vd = fmaf(V_D6, t, V_D5); vd = fmaf(vd, t, V_D4); vd = fmaf(vd, t, V_D3); vd = fmaf(vd, t, V_D2);
+            vd = fmaf(vd, t, V_D1); vd = fmaf(vd, t, 1.0f);
+            ec = qq * fmaf(-a.alpha, vn / vd, invR);
+        }
+    } else {
+        const float r = r2 * invR;
+        const float ar = a.alpha * r;
+        const float erfcAR = erfcf(ar);
+        const float ex = expf(-ar * ar);
+        sc = qq * invR * invR2 * fmaf(1.1283791670955126f * ar, ex, erfcAR);
+        if (ENERGY) ec = qq * invR * erfcAR;
+    }
+    const float sr2 = sig * sig * invR2;
+    const float sr6 = sr2 * sr2 * sr2;
+    const float es6 = eps * sr6;
+    s = fmaf(es6 * invR2, fmaf(12.0f, sr6, -6.0f), sc);
+    if (ENERGY) e = fmaf(es6, sr6 - 1.0f, ec);
+}
+
+// FP64 decision for pairs that fall within rounding distance of the cutoff (rare)
+__device__ __forceinline__ bool borderlineInside(const TileArgs& a, int slotI, int slotJ) {
+    const float4 pi = a.posq[slotI], pj = a.posq[slotJ];
+    double dx = (double)pj.x - (double)pi.x, dy = (double)pj.y - (double)pi.y, dz = (double)pj.z - (double)pi.z;
+    if (a.periodic) imageDeltaD(dx, dy, dz, a.boxD);
+    return dx * dx + dy * dy + dz * dz <= a.rc2d;
+}
+
+template <bool FORCES, bool ENERGY, bool EMIT>
+__global__ void __launch_bounds__(TILE_THREADS, 3) tileKernel(const TileArgs a) {
+    __shared__ float4 sPos[TILE_WARPS][32];
+    __shared__ float2 sPar[TILE_WARPS][32];
+    __shared__ int sIdx[TILE_WARPS][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned numExclUnits = (unsigned)(a.exclEnd - a.exclBegin);
+    const unsigned total = numExclUnits + a.counters->numUnits;
+    long long eAcc = 0; unsigned long long nPairs = 0;
+
+    unsigned u = 0;
+    if (lane == 0) u = atomicAdd(&a.counters->workNext, 1u);
+    u = __shfl_sync(0xffffffffu, u, 0);
+    while (u < total) {
+        unsigned uNext = 0;
+        if (lane == 0) uNext = atomicAdd(&a.counters->workNext, 1u);   // fetch ahead: latency hidden by this unit's work
+        int x, tileStart, nTiles; bool excl = u < numExclUnits; int yBlock = 0; unsigned exclBits = 0;
+        if (excl) {
+            const int2 t = a.exclTiles[a.exclBegin + u];
+            x = t.x; yBlock = t.y; tileStart = 0; nTiles = 1;
+            exclBits = a.exclFlags[(size_t)(a.exclBegin + u) * 32 + lane];
+        } else {
+            const int4 w = a.units[u - numExclUnits];
+            x = w.x; tileStart = w.y; nTiles = w.z;
+        }
+        const int slotI = x * 32 + lane;
+        const float4 pi = a.posq[slotI];
+        const float2 pri = a.sigEps[slotI];
+        const float4 cX = a.blockCenter[x];
+        const float4 hX = a.blockHalf[x];
+        // single periodic copy allowed when every interacting image is the one nearest to the block centre
+        const bool single = a.periodic && !a.box.triclinic &&
+            0.5f * a.box.ax - hX.x >= a.rcPadded && 0.5f * a.box.by - hX.y >= a.rcPadded && 0.5f * a.box.cz - hX.z >= a.rcPadded;
+        const bool validI = slotI < a.N;
+        float xi = pi.x, yi = pi.y, zi = pi.z;
+        if (single || !a.periodic) {
+            xi -= cX.x; yi -= cX.y; zi -= cX.z;
+            if (single) imageDelta(xi, yi, zi, a.box);
+            if (!validI) { xi = 3.0e4f; yi = 3.0e4f; zi = 3.0e4f; }
+        }
+        const float qik = a.kcoul * pi.w;
+        float fix = 0.f, fiy = 0.f, fiz = 0.f, eTile = 0.f;
+
+        // prefetch j data of the first tile
+        int ja = excl ? yBlock * 32 + lane : a.jAtoms[(size_t)tileStart * 32 + lane];
+        float4 pj = make_float4(0.f, 0.f, 0.f, 0.f); float2 prj = make_float2(0.f, 0.f);
+        if (ja >= 0) { pj = a.posq[ja]; prj = a.sigEps[ja]; }
+        for (int t = 0; t < nTiles; t++) {
+            const int jaCur = ja;
+            {   // stage tile t
+                float xj = pj.x, yj = pj.y, zj = pj.z;
+                if (single || !a.periodic) {
+                    xj -= cX.x; yj -= cX.y; zj -= cX.z;
+                    if (single) imageDelta(xj, yj, zj, a.box);
+                    if (jaCur < 0 || jaCur >= a.N) { xj = -3.0e4f; yj = -3.0e4f; zj = -3.0e4f; }
+                }
+                __syncwarp();
+                sPos[warp][lane] = make_float4(xj, yj, zj, pj.w);
+                sPar[warp][lane] = prj;
+                sIdx[warp][lane] = jaCur;
+                __syncwarp();
+            }
+            if (t + 1 < nTiles) {   // next tile's loads fly while this one is computed
+                ja = a.jAtoms[(size_t)(tileStart + t + 1) * 32 + lane];
+                pj = make_float4(0.f, 0.f, 0.f, 0.f); prj = make_float2(0.f, 0.f);
+                if (ja >= 0) { pj = a.posq[ja]; prj = a.sigEps[ja]; }
+            }
+            float fjx = 0.f, fjy = 0.f, fjz = 0.f;
+#pragma unroll 4
+            for (int k = 0; k < 32; k++) {
+                const int jj = (lane + k) & 31;
+                const float4 q = sPos[warp][jj];
+                const float2 pr = sPar[warp][jj];
+                float dx = q.x - xi, dy = q.y - yi, dz = q.z - zi;
+                bool ok = true;
+                if (!single && a.periodic) {
+                    imageDelta(dx, dy, dz, a.box);
+                    const int sj = sIdx[warp][jj];
+                    ok = validI && sj >= 0 && sj < a.N;
+                }
+                const float r2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+                const float dcut = r2 - a.rc2;
+                bool in = dcut < 0.f;
+                if (fabsf(dcut) < a.borderTol && ok) {
+                    const int sj = sIdx[warp][jj];
+                    if (sj >= 0 && sj < a.N && validI) in = borderlineInside(a, slotI, sj);
+                }
+                if (excl) in = in && !((exclBits >> jj) & 1u);
+                in = in && ok;
+                float s, e;
+                pairTerms<ENERGY>(a, r2, qik * q.w, pri.x + pr.x, pri.y * pr.y, s, e);
+                s = in ? s : 0.f;
+                if (FORCES) {
+                    fix = fmaf(-dx, s, fix); fiy = fmaf(-dy, s, fiy); fiz = fmaf(-dz, s, fiz);
+                    fjx = fmaf(dx, s, fjx); fjy = fmaf(dy, s, fjy); fjz = fmaf(dz, s, fjz);
+                    const int src = (lane + 1) & 31;
+                    fjx = __shfl_sync(0xffffffffu, fjx, src);
+                    fjy = __shfl_sync(0xffffffffu, fjy, src);
+                    fjz = __shfl_sync(0xffffffffu, fjz, src);
+                }
+                if (ENERGY) eTile += in ? e : 0.f;
+                if (EMIT && in) {
+                    nPairs++;
+                    if (a.pairOut) {
+                        const unsigned long long slot = atomicAdd(&a.counters->pairCount, 1ull);
+                        if ((long long)slot < a.pairCapacity) {
+                            const int oi = a.atomIndex[slotI], oj = a.atomIndex[sIdx[warp][jj]];
+                            a.pairOut[slot] = make_int2(min(oi, oj), max(oi, oj));
+                        }
+                    }
+                }
+            }
+            if (FORCES && jaCur >= 0 && jaCur < a.N) {
+                // after 32 rotations the accumulator for j = lane is back in this lane
+                atomicAddFixed(&a.force[jaCur], toFixed(fjx));
+                atomicAddFixed(&a.force[jaCur + a.Npad], toFixed(fjy));
+                atomicAddFixed(&a.force[jaCur + 2 * a.Npad], toFixed(fjz));
+            }
+            if (ENERGY) {   // per-tile float sum, reduced in a fixed order, then integer accumulation
+                const float es = warpSum(eTile);
+                eAcc += toFixed(es);
+                eTile = 0.f;
+            }
+        }
+        if (FORCES && validI) {
+            atomicAddFixed(&a.force[slotI], toFixed(fix));
+            atomicAddFixed(&a.force[slotI + a.Npad], toFixed(fiy));
+            atomicAddFixed(&a.force[slotI + 2 * a.Npad], toFixed(fiz));
+        }
+        u = __shfl_sync(0xffffffffu, uNext, 0);
+    }
+    if (ENERGY && lane == 0 && eAcc != 0) atomicAddFixed(&a.counters->energy[E_DIRECT], eAcc);
+    if (EMIT && !a.pairOut) {
+        for (int o = 16; o > 0; o >>= 1) nPairs += __shfl_xor_sync(0xffffffffu, nPairs, o);
+        if (lane == 0 && nPairs) atomicAdd(&a.counters->pairCount, nPairs);
+    }
+}
+
+__global__ void resetWorkQueue(DevCounters* c) { c->workNext = 0; }
+
+void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
+    TileArgs a;
+    a.posq = c->posq; a.sigEps = c->sigEps; a.blockCenter = c->blockCenter; a.blockHalf = c->blockHalf;
+    a.units = c->units; a.jAtoms = c->jAtoms; a.exclTiles = c->exclTiles; a.exclFlags = c->exclFlags;
+    a.atomIndex = c->atomIndex; a.force = c->force; a.counters = c->counters;
+    a.pairOut = c->pairOut; a.pairCapacity = c->pairCapacity;
+    a.N = c->N; a.Npad = c->Npad;
+    // exclusion tiles are split by index over ranks (CudaNonbondedUtilities.cpp:704-708)
+    a.exclBegin = (int)((long long)c->numExclTiles * c->partRank / c->partRanks);
+    a.exclEnd = (int)((long long)c->numExclTiles * (c->partRank + 1) / c->partRanks);
+    a.box = c->boxF; a.boxD = c->boxD;
+    const double rc = c->nb.cutoff, al = c->nb.ewald_alpha;
+    a.rc2 = (float)(rc * rc); a.rc2d = rc * rc; a.rcPadded = (float)c->paddedCutoff;
+    a.alpha = (float)al; a.alpha2 = (float)(al * al); a.alpha3 = (float)(al * al * al);
+    a.kcoul = (float)B200_ONE_4PI_EPS0;
+    a.borderTol = (float)(3e-5 * rc * rc);
+    a.exact = c->exactEwald ? 1 : 0;
+    a.periodic = 1;
+    resetWorkQueue<<<1, 1, 0, c->stream>>>(c->counters);
+    const int grid = c->smCount * 3;
+    ScopedTimer tm(c, B200_T_TILE, c->stream);
+    if (emitPairs) tileKernel<false, false, true><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    else if (forces && energy) tileKernel<true, true, false><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    else if (forces) tileKernel<true, false, false><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    else tileKernel<false, true, false><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    LAUNCH_COUNT(c, 2);
+    CUDA_CHECK(cudaGetLastError());
+}

@@ -1,0 +1,45 @@
+/* nonbonded_oracle.h -- TEST INFRASTRUCTURE ONLY (see nonbonded_oracle.c). */
+#ifndef NONBONDED_ORACLE_H_
+#define NONBONDED_ORACLE_H_
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct {
+    int n;
+    const double* pos;      /* [3n] nm */
+    const double* charge;   /* [n] */
+    const double* sigma;    /* [n] nm */
+    const double* epsilon;  /* [n] kJ/mol */
+    double box[9];          /* a, b, c (reduced form) */
+    double cutoff;
+    double alpha;
+    int grid[3];
+    int nexcl; const int* excl;          /* excluded pairs [2*nexcl] */
+    int nexc;  const int* exc;           /* exceptions with parameters [2*nexc] */
+    const double* exc_qq; const double* exc_sigma; const double* exc_eps;
+    int exceptions_periodic;
+} oracle_system;
+
+/* direct space, pairs with r <= cutoff that are not excluded; forces [3n] are ADDED to; returns pair count.
+   If pairs != NULL, up to `capacity` pairs (i<j) are written in (i,j) order of discovery. */
+long long oracle_direct(const oracle_system* s, double* forces, double* energy, int* pairs, long long capacity);
+/* -erf(alpha r)/r correction of every excluded pair */
+void oracle_exclusion_correction(const oracle_system* s, double* forces, double* energy);
+/* 1-4 exceptions: plain Coulomb + LJ, no cutoff */
+void oracle_exceptions(const oracle_system* s, double* forces, double* energy);
+/* smooth PME reciprocal space, order 5 */
+void oracle_reciprocal(const oracle_system* s, double* forces, double* energy);
+/* Ewald self energy + neutralising plasma */
+double oracle_self_energy(const oracle_system* s);
+/* everything above; `groups` bit 0 = direct(+exclusion corr+exceptions), bit 1 = reciprocal(+self) */
+void oracle_nonbonded(const oracle_system* s, int groups, double* forces, double* energy);
+/* complex 1D FFT used by the reciprocal sum (exposed for the FFT unit test): data = interleaved re,im */
+void oracle_fft1d(double* data, int n, int stride, int inverse);
+/* unnormalised 3D r2c FFT (out: nx*ny*(nz/2+1) complex) -- checker for b200_fft3d_r2c_host */
+void oracle_fft3d_r2c(const double* in, double* out, int nx, int ny, int nz);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,88 @@
+"""Regenerates the fixtures under tests/golden/ from the reference tree.  Runs only in the build container (needs
+/root/reference and oracle/_ref built by `make -C oracle reference`); the fixtures are committed, this script documents
+exactly how they were made.
+
+  tip3p_895.npy        float32 [895,3,3] nm: wrappers/python/openmm/app/data/tip3p.pdb (equilibrated 30 A TIP3P box)
+  nacl_amorph.npy      float32 [894,3] nm: tests/nacl_amorph.dat (testEwaldPME, tests/TestEwald.h:96-218)
+  ref_water_<N>.npz    outputs of the reference's own Reference platform (double precision) for water_box(N):
+                       positions (float32), energies and forces of the direct and reciprocal force groups, and the
+                       hash + count of the pair set of computeNeighborListVoxelHash.  N = 1536 (small box: per-pair
+                       minimum image), 6000 (single periodic copy), 23558 (DHFR size; forces stored as float32).
+  ref_ions_triclinic.npz  the 8-ion triclinic case of tests/TestEwald.h:220-269 evaluated by the Reference platform
+"""
+import os
+import re
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+REF = "/root/reference"
+
+
+def tip3p():
+    pos = []
+    for line in open(os.path.join(REF, "wrappers/python/openmm/app/data/tip3p.pdb")):
+        if line.startswith("ATOM"):
+            pos.append([float(line[30:38]), float(line[38:46]), float(line[46:54])])
+    a = 0.1 * np.array(pos).reshape(-1, 3, 3)
+    # make every molecule whole (hydrogens next to their oxygen) in the 3 nm cell
+    for k in (1, 2):
+        d = a[:, k, :] - a[:, 0, :]
+        a[:, k, :] -= 3.0 * np.round(d / 3.0)
+    np.save(os.path.join(HERE, "tip3p_895.npy"), a.astype(np.float32))
+
+
+def nacl():
+    pat = re.compile(r"Vec3\(([-\d.eE+]+),([-\d.eE+]+),([-\d.eE+]+)\)")
+    pos = [[float(x) for x in pat.search(l).groups()] for l in open(os.path.join(REF, "tests/nacl_amorph.dat")) if "Vec3" in l]
+    np.save(os.path.join(HERE, "nacl_amorph.npy"), np.array(pos, dtype=np.float32))
+
+
+def ref_eval(sysd, cutoff, alpha, grid, pairs=True):
+    from openmm_b200 import workloads
+    from oracle_lib import REF_DRIVER
+    with tempfile.TemporaryDirectory() as td:
+        sp, op = os.path.join(td, "s.bin"), os.path.join(td, "o.bin")
+        workloads.write_system_file(sp, sysd, cutoff, alpha, grid)
+        subprocess.check_call([REF_DRIVER, "eval", sp, op, "--platform", "Reference"] + (["--pairs"] if pairs else []))
+        return workloads.read_eval_file(op, sysd["n"])
+
+
+def water(n, f32=False):
+    import openmm_b200 as b
+    from openmm_b200 import workloads
+    from oracle_lib import pair_hash
+    sysd = workloads.water_box(n, seed=n)
+    alpha, grid = b.pme_parameters(0.9, sysd["box"])
+    r = ref_eval(sysd, 0.9, alpha, grid)
+    cnt, h = pair_hash(r["pairs"], n)
+    ft = np.float32 if f32 else np.float64
+    np.savez_compressed(os.path.join(HERE, f"ref_water_{n}.npz"), positions=sysd["positions"].astype(np.float32), box=sysd["box"],
+                        alpha=alpha, grid=np.array(grid), cutoff=0.9, e_direct=r["e_direct"], e_recip=r["e_recip"],
+                        f_direct=r["f_direct"].astype(ft), f_recip=r["f_recip"].astype(ft), pair_count=cnt, pair_hash=np.uint64(h))
+    print(n, "pairs", cnt, "E", r["e_direct"], r["e_recip"])
+
+
+def ions():
+    pos = np.array([[1.744, 2.788, 3.162], [1.048, 0.762, 2.340], [2.489, 1.570, 2.817], [1.027, 1.893, 3.271],
+                    [0.937, 0.825, 0.009], [2.290, 1.887, 3.352], [1.266, 1.111, 2.894], [0.933, 1.862, 3.490]])
+    sysd = dict(n=8, positions=pos, box=np.array([2.5, 0, 0, 0.5, 3.0, 0, 0.7, 0.9, 3.5]), charge=np.array([-1.0] * 4 + [1.0] * 4),
+                sigma=np.array([0.440104] * 4 + [0.332840] * 4), epsilon=np.array([0.4184] * 4 + [0.0115897] * 4), mass=np.ones(8),
+                exclusions=np.zeros((0, 2), dtype=np.int32))
+    r = ref_eval(sysd, 1.0, 3.45891, [32, 40, 48], pairs=False)
+    np.savez(os.path.join(HERE, "ref_ions_triclinic.npz"), e_direct=r["e_direct"], e_recip=r["e_recip"], f_direct=r["f_direct"], f_recip=r["f_recip"])
+    print("ions", r["e_direct"] + r["e_recip"])
+
+
+if __name__ == "__main__":
+    tip3p()
+    nacl()
+    ions()
+    for n, f32 in ((1536, False), (6000, False), (23558, True)):
+        water(n, f32)
