@@ -1,0 +1,311 @@
+#!/usr/bin/env python
+"""bench.py -- ns/day of the NonbondedForce PME path (PME, 2 fs, mixed precision, LangevinMiddle, rigid TIP3P water).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload stmv|cellulose|apoa1|dhfr] [--impl reference]
+
+One MD "step" = neighbour-list check/rebuild + direct-space tile kernel + PME (spread, 3D FFT, convolution, inverse FFT,
+interpolation) + exclusion correction + LangevinMiddle/SETTLE + COM-motion removal.  Default workload: the STMV-sized box
+(1,066,628 atoms, the configuration BASELINE.json's multi-GPU metric is quoted on; it fits one GPU).
+`value`   : whole-job ns/day with the state resident in HBM (CUDA events on the context's stream, max over ranks).
+`e2e`     : ns/day through the C ABI with HOST buffers: every step uploads the positions from host memory
+            (b200_set_positions), runs one step, and downloads the positions (b200_get_positions).
+`roofline`: the dominant kernel (direct-space tile kernel) against the FP32 pipe peak; PME kernels against measured HBM.
+`cpu_baseline` / `--impl reference`: the reference's own CPU platform (oracle/_ref, all host cores) on the same system.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+FLOP_PER_PAIR = 56.0          # force-only direct-space work per in-cutoff pair
+DT_PS = 0.002
+
+
+def ns_per_day(ms_per_step):
+    return DT_PS * 1e-3 * 86400.0 / (ms_per_step * 1e-3)
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("hbm_gbs", 6650.0), d.get("sm_max_mhz", 1965.0), "measured"
+    return 6650.0, 1965.0, "fallback"
+
+
+class ClockSampler:
+    def __init__(self, device):
+        self.path = os.path.join(tempfile.gettempdir(), f"b200_clocks_{os.getpid()}.csv")
+        self.proc = None
+        self.device = device
+
+    def start(self):
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device),
+                                          "--query-gpu=clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+                                          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+                                          "clocks_event_reasons.sw_power_cap", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.proc is None:
+            return out
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.f.close()
+        sm, mx, reasons = [], [], set()
+        for line in open(self.path):
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if sm:
+            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(np.max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        return out
+
+
+def build_system(workload):
+    from openmm_b200 import workloads
+    n = workloads.WORKLOADS[workload]
+    cache = os.path.join(tempfile.gettempdir(), f"b200_waterbox_{n}.npz")
+    if os.path.exists(cache):
+        z = np.load(cache)
+        sysd = {k: z[k] for k in z.files}
+        sysd["n"] = int(sysd["n"]); sysd["num_waters"] = int(sysd["num_waters"])
+        sysd["constraints"] = (sysd.pop("con_atoms"), sysd.pop("con_dist"))
+        return sysd
+    sysd = workloads.water_box(n, seed=n)
+    try:
+        np.savez(cache + f".{os.getpid()}.npz", con_atoms=sysd["constraints"][0], con_dist=sysd["constraints"][1],
+                 **{k: v for k, v in sysd.items() if k != "constraints"})
+        os.replace(cache + f".{os.getpid()}.npz", cache)
+    except Exception:
+        pass
+    return sysd
+
+
+def run_reference_cpu(sysd, alpha, grid, steps, warmup, threads=0, e2e=False):
+    """times the reference's own CPU platform (oracle/_ref/ref_driver, unmodified OpenMM built from /root/reference)"""
+    from openmm_b200 import workloads
+    from oracle_lib import REF_DRIVER, REF_PLUGINS
+    if not os.path.exists(REF_DRIVER):
+        return None
+    with tempfile.TemporaryDirectory() as td:
+        sp = os.path.join(td, "system.bin")
+        workloads.write_system_file(sp, sysd, 0.9, alpha, grid)
+        cmd = [REF_DRIVER, "bench", sp, "--platform", "CPU", "--plugin", os.path.join(REF_PLUGINS, "libOpenMMCPU.so"),
+               "--plugin", os.path.join(REF_PLUGINS, "libOpenMMPME.so"), "--steps", str(steps), "--warmup", str(warmup), "--dt", str(DT_PS)]
+        if threads:
+            cmd += ["--threads", str(threads)]
+        if e2e:
+            cmd += ["--e2e"]
+        out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+        if out.returncode != 0:
+            sys.stderr.write(out.stderr)
+            return None
+        return json.loads(out.stdout.strip().splitlines()[-1])
+
+
+def cpu_steps_for(n_atoms, budget_s=20.0):
+    est_ms = 1.3e-3 * n_atoms        # ~1.2 s/step for 1M atoms on 8 cores; rescaled below
+    cores = os.cpu_count() or 8
+    est_ms *= 8.0 / max(cores, 8) * 1.5
+    return max(3, min(200, int(budget_s * 1e3 / est_ms)))
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import openmm_b200 as b
+    sysd = build_system(args.workload)
+    alpha, grid = b.pme_parameters(0.9, sysd["box"])
+    n = sysd["n"]
+    steps = min(args.steps, cpu_steps_for(n, 60.0))
+    warm = min(args.warmup, max(2, steps // 3))
+    r = run_reference_cpu(sysd, alpha, grid, steps, warm)
+    if r is None:
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_driver missing or failed (reference not built)"}))
+        return 0
+    line = {
+        "impl": "reference", "metric": "ns/day (PME, 2 fs, mixed precision)", "value": r["ns_per_day"], "unit": "ns/day",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32 pair math / f64 integration (reference CPU platform)", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {n} atoms TIP3P water box, PME cutoff 0.9 nm, grid {grid}, LangevinMiddle 2 fs", "atoms": n,
+                   "platform": "reference CPU platform + CPU-PME plugin, unmodified OpenMM 8.6 (oracle/_ref)"},
+        "cpu_baseline": {"value": r["ns_per_day"], "unit": "ns/day", "cores": int(r["threads"]), "kind": "reference",
+                         "sample": f"{r['steps']} MD steps after {r['warmup']} warm-up steps of the full {n}-atom system"},
+        "e2e": {"value": r["ns_per_day"], "unit": "ns/day", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=30)
+    ap.add_argument("--workload", default="stmv", choices=["dhfr", "apoa1", "cellulose", "stmv"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-steps", type=int, default=20)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    import torch
+    import openmm_b200 as b
+    from openmm_b200 import workloads
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    sysd = build_system(args.workload)
+    n = sysd["n"]
+    alpha, grid = b.pme_parameters(0.9, sysd["box"])
+    ctx = workloads.make_context(sysd, device=local)
+    if world > 1:
+        ids = [b.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        ctx.comm_init(rank, world, ids[0])
+    ctx.set_positions(sysd["positions"])
+    ctx.set_velocities(sysd["velocities"])
+    ctx.set_integrator(dt=DT_PS, temperature=300.0, friction=1.0, constraint_tol=1e-5, seed=1, remove_cm_every=1)
+    ctx.compute(forces=True, energy=False)      # first list build + capacity sizing outside the timed region
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- warm-up, then the timed region
+    ctx.step(args.warmup)
+    ctx.synchronize()
+    launches0 = ctx.launch_count()
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    total_ms = ctx.timed_steps(args.steps)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    launches = ctx.launch_count() - launches0
+    if dist is not None:
+        t = torch.tensor([total_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    ms_per_step = total_ms / args.steps
+
+    # ---- per-kernel-family timing (CUDA events on the launching streams) over a second window of the same steps
+    ctx.timing_enable(True); ctx.timing_reset()
+    prof_steps = min(args.steps, 50)
+    ctx.step(prof_steps)
+    fam = ctx.timing_read()
+    ctx.timing_enable(False)
+    stats = ctx.nblist_stats()
+    pairs, _ = ctx.direct_pairs()
+    pairs *= 1 if world == 1 else 1   # each rank counts its own rows
+    if dist is not None:
+        t = torch.tensor([pairs], device="cuda", dtype=torch.int64)
+        dist.all_reduce(t)
+        pairs_total = int(t.item())
+    else:
+        pairs_total = pairs
+    tile_ms, tile_n = fam["tile"]
+    tile_avg_ms = tile_ms / max(tile_n, 1)
+    hbm_gbs, sm_max_mhz, peak_kind = measured_peaks()
+    fp32_peak = ctx_sm = None
+    sm_count = torch.cuda.get_device_properties(local).multi_processor_count
+    fp32_peak = sm_count * 128 * 2 * sm_max_mhz * 1e6 / 1e12
+    achieved_tflops = FLOP_PER_PAIR * pairs / (tile_avg_ms * 1e-3) / 1e12 if tile_avg_ms > 0 else 0.0
+    G = grid[0] * grid[1] * grid[2]
+    pme_bytes = 36.0 * G + 72.0 * n
+    pme_ms = sum(fam[k][0] for k in ("spread", "fft", "convolve", "interpolate")) / max(prof_steps, 1)
+    roofline = {"kernel": "tileKernel<forces>", "bound": "fp32", "achieved": achieved_tflops, "peak": fp32_peak, "unit": "TFLOP/s",
+                "frac": achieved_tflops / fp32_peak if fp32_peak else None, "traffic": None,
+                "peak_source": f"{sm_count} SMs x 128 lanes x 2 x {sm_max_mhz:.0f} MHz ({peak_kind} sm_max_mhz)",
+                "algorithmic": f"{FLOP_PER_PAIR:.0f} FLOP x {pairs} in-cutoff pairs per launch (this rank)",
+                "executed_pair_slots_per_launch": int(stats["num_tiles"]) * 1024 + int(stats["num_exclusion_tiles"]) * 1024,
+                "avg_launch_ms": tile_avg_ms,
+                "pme": {"bound": "hbm", "achieved": pme_bytes / (pme_ms * 1e-3) / 1e9 if pme_ms > 0 else None, "peak": hbm_gbs, "unit": "GB/s",
+                        "frac": (pme_bytes / (pme_ms * 1e-3) / 1e9 / hbm_gbs) if pme_ms > 0 else None, "bytes_per_step": pme_bytes, "ms_per_step": pme_ms}}
+
+    # ---- end to end through the C ABI with host buffers
+    e2e_steps = max(1, min(args.e2e_steps, args.steps))
+    pos = ctx.get_positions(enforce_periodic=True)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        ctx.set_positions(pos)
+        ctx.step(1)
+        pos = ctx.get_positions(enforce_periodic=True)
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+    if dist is not None:
+        t = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+    npad = ((n + 31) // 32) * 32
+    e2e = {"value": ns_per_day(e2e_ms), "unit": "ns/day", "ms_per_step": e2e_ms, "h2d_bytes_per_step": 32 * npad, "d2h_bytes_per_step": 32 * npad,
+           "api": "b200_set_positions(host) + b200_step(1) + b200_get_positions(host), pinned staging inside the library"}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        k = cpu_steps_for(n, 20.0)
+        r = run_reference_cpu(sysd, alpha, grid, k, max(2, k // 3))
+        if r is not None:
+            cpu = {"value": r["ns_per_day"], "unit": "ns/day", "cores": int(r["threads"]), "kind": "reference", "ms_per_step": r["ms_per_step"],
+                   "sample": f"{r['steps']} MD steps after {r['warmup']} warm-up steps of the full {n}-atom system on the reference CPU platform"}
+    if rank == 0:
+        line = {
+            "metric": "ns/day (PME, 2 fs, mixed precision)", "value": ns_per_day(ms_per_step), "unit": "ns/day", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32 pair math, int64 fixed-point force sums, f64 integration (mixed)", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {n} atoms TIP3P water box at 100 atoms/nm^3, PME cutoff 0.9 nm, alpha {alpha:.5f}, grid {grid}, "
+                                   "LangevinMiddle 300 K 1/ps 2 fs, SETTLE, CMMotionRemover", "atoms": n,
+                       "parallelism": f"direct-space rows round-robin over {world} rank(s), int64 all-reduce, PME on rank 0",
+                       "l2": "per-step working set ~285 MB for stmv (> 126 MB L2); steady-state MD loop, no explicit flush"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
+            "pair_interactions_per_s": pairs_total / (tile_avg_ms * 1e-3) if tile_avg_ms > 0 else None,
+            "in_cutoff_pairs": pairs_total,
+            "kernel_ms_per_step": {k: v[0] / prof_steps for k, v in fam.items()},
+            "nblist": {"tiles": int(stats["num_tiles"]), "units": int(stats["num_units"]), "exclusion_tiles": int(stats["num_exclusion_tiles"]),
+                       "rebuilds": int(stats["rebuilds"]), "steps": int(stats["steps"]),
+                       "tile_efficiency": pairs / max(1.0, (int(stats["num_tiles"]) + int(stats["num_exclusion_tiles"])) * 1024.0)},
+        }
+        print(json.dumps(line))
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -124,6 +124,7 @@ extern "C" void b200_context_destroy(b200_ctx* c) {
     dfree(c->sortKeys); dfree(c->sortCount); dfree(c->sortStart); dfree(c->sortOrder);
     for (auto& g : c->groups) dfree(g.dBase);
     if (c->countersHost) cudaFreeHost(c->countersHost);
+    if (c->stageA) { cudaFreeHost(c->stageA); cudaFreeHost(c->stageB); cudaFreeHost(c->stageOff); }
     for (auto& t : c->timers) for (auto& p : t.pending) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     cudaEventDestroy(c->evFork); cudaEventDestroy(c->evPmeDone);
     cudaStreamDestroy(c->stream); cudaStreamDestroy(c->pmeStream);
@@ -180,6 +181,44 @@ extern "C" int b200_nonbonded_get_pme_parameters(const b200_ctx* c, double* alph
     API_BEGIN
     if (!c || !c->hasNonbonded) throw B200Error(B200_ERR_INVALID, "no NonbondedForce in this context");
     *alpha = c->nb.ewald_alpha; *nx = c->nb.grid[0]; *ny = c->nb.grid[1]; *nz = c->nb.grid[2];
+    API_END
+}
+
+// CalcNonbondedForceKernel::copyParametersToContext (CommonCalcNonbondedForce.cpp:1119-1254): per-particle charge/sigma/epsilon
+// and exception parameters may change; the set of exceptions may not.
+extern "C" int b200_nonbonded_update_parameters(b200_ctx* c, const b200_nonbonded_desc* d) {
+    API_BEGIN
+    if (!c || !d || !c->hasNonbonded) throw B200Error(B200_ERR_INVALID, "b200_nonbonded_update_parameters: no NonbondedForce in this context");
+    if (d->num_exclusions * 2 != (int)c->exclPairs.size() || d->num_exceptions != (int)c->excQQ.size())
+        throw B200Error(B200_ERR_INVALID, "updateParametersInContext: The set of non-excluded exceptions has changed");
+    CUDA_CHECK(cudaSetDevice(c->device));
+    c->charge.assign(d->charge, d->charge + c->N); c->sigma.assign(d->sigma, d->sigma + c->N); c->epsilon.assign(d->epsilon, d->epsilon + c->N);
+    c->excQQ.assign(d->exception_chargeprod, d->exception_chargeprod + d->num_exceptions);
+    c->excSig.assign(d->exception_sigma, d->exception_sigma + d->num_exceptions);
+    c->excEps.assign(d->exception_epsilon, d->exception_epsilon + d->num_exceptions);
+    c->nb.dispersion_coefficient = d->dispersion_coefficient;
+    b200_sync_host_order(c);
+    std::vector<float2> se(c->Npad, make_float2(0.f, 0.f));
+    std::vector<float4> p(c->Npad);
+    d2h(p.data(), c->posq, c->Npad, c->stream);
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    double sumQ = 0, sumQ2 = 0;
+    for (int s = 0; s < c->N; s++) {
+        const int o = c->hostAtomIndex[s];
+        se[s] = make_float2((float)(0.5 * c->sigma[o]), (float)(2.0 * sqrt(c->epsilon[o])));
+        p[s].w = (float)c->charge[o];
+        sumQ += c->charge[o]; sumQ2 += c->charge[o] * c->charge[o];
+    }
+    h2d(c->sigEps, se.data(), c->Npad, c->stream); h2d(c->posq, p.data(), c->Npad, c->stream);
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    c->totalCharge = sumQ;
+    c->selfEnergy = -B200_ONE_4PI_EPS0 * c->nb.ewald_alpha * sumQ2 / sqrt(M_PI);
+    if (c->finalized && c->numExceptions > 0) {
+        std::vector<float4> xq;
+        for (size_t i = 0; i < c->excQQ.size(); i++) xq.push_back(make_float4((float)(B200_ONE_4PI_EPS0 * c->excQQ[i]), (float)c->excSig[i], (float)(4.0 * c->excEps[i]), 0.f));
+        CUDA_CHECK(cudaMemcpy(c->dExcParams, xq.data(), sizeof(float4) * xq.size(), cudaMemcpyHostToDevice));
+    }
+    c->forcesValid = false;
     API_END
 }
 
@@ -399,24 +438,38 @@ void b200_sync_host_order(b200_ctx* c) {
 }
 
 
+static void ensureStaging(b200_ctx* c) {
+    if (c->stageA) return;
+    CUDA_CHECK(cudaMallocHost((void**)&c->stageA, sizeof(float4) * c->Npad));
+    CUDA_CHECK(cudaMallocHost((void**)&c->stageB, sizeof(float4) * c->Npad));
+    CUDA_CHECK(cudaMallocHost((void**)&c->stageOff, sizeof(int4) * c->Npad));
+    memset(c->stageA, 0, sizeof(float4) * c->Npad); memset(c->stageB, 0, sizeof(float4) * c->Npad);
+}
+
 extern "C" int b200_set_positions(b200_ctx* c, const double* xyz) {
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
     b200_sync_host_order(c);
-    // CommonKernels.cpp:182-227: float cast + correction, cell offsets reset, then reorder
-    std::vector<float4> p(c->Npad, make_float4(0, 0, 0, 0)), q(c->Npad, make_float4(0, 0, 0, 0));
+    ensureStaging(c);
+    // CommonKernels.cpp:182-227: float cast + correction in the device order, cell offsets reset.  The data goes through
+    // pinned staging buffers so the copy runs at full PCIe speed.
+    float4* p = c->stageA; float4* q = c->stageB;
+    const bool hasQ = c->hasNonbonded;
     for (int s = 0; s < c->N; s++) {
         const int o = c->hostAtomIndex[s];
         const double x = xyz[3 * o], y = xyz[3 * o + 1], z = xyz[3 * o + 2];
-        p[s] = make_float4((float)x, (float)y, (float)z, c->hasNonbonded ? (float)c->charge[o] : 0.f);
+        p[s] = make_float4((float)x, (float)y, (float)z, hasQ ? (float)c->charge[o] : 0.f);
         q[s] = make_float4((float)(x - (double)(float)x), (float)(y - (double)(float)y), (float)(z - (double)(float)z), 0.f);
     }
-    CUDA_CHECK(cudaMemcpyAsync(c->posq, p.data(), sizeof(float4) * c->Npad, cudaMemcpyHostToDevice, c->stream));
-    CUDA_CHECK(cudaMemcpyAsync(c->posqCorr, q.data(), sizeof(float4) * c->Npad, cudaMemcpyHostToDevice, c->stream));
+    CUDA_CHECK(cudaMemcpyAsync(c->posq, p, sizeof(float4) * c->Npad, cudaMemcpyHostToDevice, c->stream));
+    CUDA_CHECK(cudaMemcpyAsync(c->posqCorr, q, sizeof(float4) * c->Npad, cudaMemcpyHostToDevice, c->stream));
     CUDA_CHECK(cudaMemsetAsync(c->cellOffsets, 0, sizeof(int4) * c->Npad, c->stream));
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    c->positionsSet = true; c->forcesValid = false;
-    c->stepsSinceReorder = -1;   // reorder before the next computation
+    c->forcesValid = false;
+    // Like ComputeContext::reorderAtoms the spatial sort is periodic, not forced by every setPositions: the displacement
+    // check against the last list build decides on the device whether the neighbour list must be rebuilt.
+    if (!c->positionsSet) c->stepsSinceReorder = -1;
+    c->positionsSet = true;
     API_END
 }
 
@@ -424,8 +477,10 @@ extern "C" int b200_get_positions(b200_ctx* c, double* xyz, int32_t enforcePerio
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
     b200_sync_host_order(c);
-    std::vector<float4> p(c->Npad), q(c->Npad); std::vector<int4> off(c->Npad);
-    d2h(p.data(), c->posq, c->Npad, c->stream); d2h(q.data(), c->posqCorr, c->Npad, c->stream); d2h(off.data(), c->cellOffsets, c->Npad, c->stream);
+    ensureStaging(c);
+    float4* p = c->stageA; float4* q = c->stageB; int4* off = c->stageOff;
+    d2h(p, c->posq, c->Npad, c->stream); d2h(q, c->posqCorr, c->Npad, c->stream);
+    if (!enforcePeriodic) d2h(off, c->cellOffsets, c->Npad, c->stream);
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
     const double* b = c->boxHost;
     for (int s = 0; s < c->N; s++) {

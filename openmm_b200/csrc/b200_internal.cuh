@@ -86,6 +86,7 @@ struct b200_ctx {
     long long* force = nullptr;    // [3*Npad] fixed point
     DevCounters* counters = nullptr;
     DevCounters* countersHost = nullptr;  // pinned
+    float4* stageA = nullptr; float4* stageB = nullptr; int4* stageOff = nullptr;   // pinned host staging for state I/O
     // scratch for reorder
     float4* posqTmp = nullptr; float4* posqCorrTmp = nullptr; double4* velmTmp = nullptr; int* atomIndexTmp = nullptr; int4* cellOffsetsTmp = nullptr;
 
