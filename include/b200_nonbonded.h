@@ -161,6 +161,13 @@ int  b200_nblist_get_stats(b200_ctx* ctx, b200_nblist_stats* out);
  * complex layout nx*ny*(nz/2+1) interleaved re,im). */
 int  b200_fft3d_r2c_host(int32_t device, int32_t nx, int32_t ny, int32_t nz, const float* in, float* out);
 int  b200_fft3d_c2r_host(int32_t device, int32_t nx, int32_t ny, int32_t nz, const float* in, float* out);
+/* Allocation-free variant of the complex-to-real transform.  It has no counterpart in the reference.  For callers that
+ * cannot call cudaMalloc when they need the transform (a memory pool owns the device, a latency-critical loop must stay
+ * off the allocator, a fixed memory budget): device pointers in and out, the working storage is a static ~8 MiB device
+ * array inside the library.  Limits: nx*ny*(nz/2+1) <= 1048576 and each dimension <= 1024, otherwise B200_ERR_INVALID.
+ * The first call on a device performs a one-time address look-up and should precede any stream capture; calls share the
+ * scratch, so calls that overlap on the GPU race.  d_in is not modified.  `stream` is a cudaStream_t (NULL = default). */
+int  b200_fft3d_c2r_noalloc(int32_t device, int32_t nx, int32_t ny, int32_t nz, const float* d_in, float* d_out, void* stream);
 /* smallest n' >= n whose only prime factors are 2,3,5,7 (ComputeContext::findLegalFFTDimension, ComputeContext.cpp:717-732) */
 int  b200_find_legal_fft_dimension(int32_t minimum);
 

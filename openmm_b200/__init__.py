@@ -64,7 +64,7 @@ EXPORTED_SYMBOLS = [
     "b200_set_velocities", "b200_get_velocities", "b200_get_forces", "b200_set_box", "b200_get_box", "b200_set_time",
     "b200_get_time", "b200_compute", "b200_compute_host", "b200_integrator_create", "b200_step", "b200_apply_constraints",
     "b200_apply_velocity_constraints", "b200_kinetic_energy", "b200_synchronize", "b200_direct_pairs", "b200_nblist_get_stats",
-    "b200_fft3d_r2c_host", "b200_fft3d_c2r_host", "b200_find_legal_fft_dimension", "b200_timing_enable", "b200_timing_read",
+    "b200_fft3d_r2c_host", "b200_fft3d_c2r_host", "b200_fft3d_c2r_noalloc", "b200_find_legal_fft_dimension", "b200_timing_enable", "b200_timing_read",
     "b200_timing_reset", "b200_timed_steps", "b200_launch_count", "b200_nccl_unique_id", "b200_comm_init", "b200_set_partition",
 ]
 
@@ -324,3 +324,11 @@ def fft3d_c2r(spec, nz, device=0):
     out = np.empty((nx, ny, nz), dtype=np.float32)
     _check(load_library().b200_fft3d_c2r_host(device, nx, ny, nz, spec.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), out.ctypes.data_as(ctypes.POINTER(ctypes.c_float))))
     return out
+
+
+def fft3d_c2r_noalloc(d_in_ptr, d_out_ptr, nx, ny, nz, device=0, stream=0):
+    """Allocation-free complex-to-real transform on DEVICE pointers (integers).  For callers that may not allocate device
+    memory; limits and sharing rules are in include/b200_nonbonded.h."""
+    lib = load_library()
+    lib.b200_fft3d_c2r_noalloc.argtypes = [ctypes.c_int32] * 4 + [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    _check(lib.b200_fft3d_c2r_noalloc(device, nx, ny, nz, ctypes.c_void_p(d_in_ptr), ctypes.c_void_p(d_out_ptr), ctypes.c_void_p(stream)))

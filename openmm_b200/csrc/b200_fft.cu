@@ -242,3 +242,65 @@ static int fftHost(int device, int nx, int ny, int nz, const float* in, float* o
 }
 extern "C" int b200_fft3d_r2c_host(int32_t device, int32_t nx, int32_t ny, int32_t nz, const float* in, float* out) { return fftHost(device, nx, ny, nz, in, out, true); }
 extern "C" int b200_fft3d_c2r_host(int32_t device, int32_t nx, int32_t ny, int32_t nz, const float* in, float* out) { return fftHost(device, nx, ny, nz, in, out, false); }
+
+// =================================================================================================================
+// Allocation-free entry point (no counterpart in the reference).
+//
+// Some callers must not allocate device memory at the moment they need a transform: code running while a memory pool
+// owns the whole device, real-time loops that may not hit the allocator's lock, or processes that were handed a fixed
+// memory budget by a scheduler.  b200_fft3d_c2r_noalloc serves them: the caller passes device input and output
+// buffers, and the working copy of the spectrum plus the three twiddle tables live in the file-scope array below,
+// which every GPU that loads this library holds (about 8 MiB) until the process exits.
+#define NOALLOC_MAX_COMPLEX (1 << 20)   // largest nx*ny*(nz/2+1) accepted: 1,048,576 complex values = 8 MiB
+#define NOALLOC_MAX_DIM 1024            // largest single dimension accepted
+#define NOALLOC_MAX_DEVICES 64
+static __device__ __align__(256) float2 g_noallocScratch[NOALLOC_MAX_COMPLEX + 3 * NOALLOC_MAX_DIM];
+static float2* g_noallocPtr[NOALLOC_MAX_DEVICES];   // device address of the array, per device (host code must not use the symbol itself)
+
+__global__ void noallocFillTwiddle(float2* tw, int n) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    double s, c;
+    sincospi(-2.0 * (double)k / (double)n, &s, &c);
+    tw[k] = make_float2((float)c, (float)s);
+}
+
+// Unnormalised 3D complex-to-real FFT, device buffers in, device buffer out, nothing allocated.
+//   d_in  : nx*ny*(nz/2+1) complex (interleaved re,im), left untouched
+//   d_out : nx*ny*nz floats
+//   stream: a cudaStream_t (0 = default stream) on `device`
+// The first call on each device looks up the device address of the scratch array (cudaGetSymbolAddress) and should
+// therefore be made before any stream capture begins.  Every call uses the same array: calls that overlap on the GPU
+// (different streams or threads) race and must be serialised by the caller.  Nothing in the array has to start at zero;
+// each call overwrites the part it reads.  Sizes beyond the limits above are rejected with B200_ERR_INVALID.
+extern "C" int b200_fft3d_c2r_noalloc(int32_t device, int32_t nx, int32_t ny, int32_t nz, const float* d_in, float* d_out, void* stream) {
+    try {
+        if (device < 0 || device >= NOALLOC_MAX_DEVICES) throw B200Error(B200_ERR_INVALID, "b200_fft3d_c2r_noalloc: device ordinal out of range");
+        if (nx < 1 || ny < 1 || nz < 1 || !d_in || !d_out) throw B200Error(B200_ERR_INVALID, "b200_fft3d_c2r_noalloc: bad arguments");
+        if (nx > NOALLOC_MAX_DIM || ny > NOALLOC_MAX_DIM || nz > NOALLOC_MAX_DIM)
+            throw B200Error(B200_ERR_INVALID, "b200_fft3d_c2r_noalloc: a grid dimension exceeds the built-in limit of 1024");
+        const size_t GC = (size_t)nx * ny * (nz / 2 + 1);
+        if (GC > (size_t)NOALLOC_MAX_COMPLEX)
+            throw B200Error(B200_ERR_INVALID, "b200_fft3d_c2r_noalloc: nx*ny*(nz/2+1) exceeds the built-in scratch of 1048576 complex values; use a context-owned transform instead");
+        CUDA_CHECK(cudaSetDevice(device));
+        if (!g_noallocPtr[device]) {
+            // once per device, with that device current: the symbol name is only a host-side handle, kernels need this address
+            float2* p = nullptr;
+            CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_noallocScratch));
+            g_noallocPtr[device] = p;
+        }
+        cudaStream_t s = (cudaStream_t)stream;
+        float2* work = g_noallocPtr[device];
+        float2* tw[3] = {work + NOALLOC_MAX_COMPLEX, work + NOALLOC_MAX_COMPLEX + NOALLOC_MAX_DIM, work + NOALLOC_MAX_COMPLEX + 2 * NOALLOC_MAX_DIM};
+        const int dims[3] = {nx, ny, nz};
+        FFTPlan1D plan[3];
+        for (int k = 0; k < 3; k++) {
+            b200_fft_make_plan(dims[k], plan[k]);
+            noallocFillTwiddle<<<(dims[k] + 127) / 128, 128, 0, s>>>(tw[k], dims[k]);
+        }
+        CUDA_CHECK(cudaMemcpyAsync(work, d_in, sizeof(float2) * GC, cudaMemcpyDeviceToDevice, s));
+        b200_fft3d_exec_c2r(nx, ny, nz, plan, tw, work, nullptr, d_out, s);
+        CUDA_CHECK(cudaGetLastError());
+    } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
+    return B200_OK;
+}
