@@ -118,8 +118,11 @@ int  b200_get_time(const b200_ctx* ctx, double* time_ps, int64_t* step_count);
  *      + CalcNonbondedForceKernel::execute (kernels.h:658).  `groups` bits as below.  Energy (kJ/mol) may be NULL. */
 #define B200_GROUP_DIRECT      1u   /* tile kernel + exclusion corrections... (includeDirect) */
 #define B200_GROUP_RECIPROCAL  2u   /* PME reciprocal space + self/plasma terms (includeReciprocal) */
-#define B200_GROUP_BONDED      4u   /* bonds, angles, torsions */
-#define B200_GROUP_ALL         7u
+#define B200_GROUP_BONDS       4u   /* HarmonicBondForce */
+#define B200_GROUP_ANGLES      8u   /* HarmonicAngleForce */
+#define B200_GROUP_TORSIONS   16u   /* PeriodicTorsionForce */
+#define B200_GROUP_BONDED     28u   /* bonds | angles | torsions */
+#define B200_GROUP_ALL        31u
 int  b200_compute(b200_ctx* ctx, uint32_t groups, int32_t include_forces, int32_t include_energy, double* energy);
 
 /* Host-buffer convenience used by the end-to-end measurement: upload positions, evaluate, download forces.
@@ -138,7 +141,9 @@ typedef struct {
     int32_t  remove_cm_every; /* CMMotionRemover frequency; 0 = never */
 } b200_integrator_desc;
 int  b200_integrator_create(b200_ctx* ctx, const b200_integrator_desc* desc);
-int  b200_step(b200_ctx* ctx, int32_t nsteps);
+int  b200_step(b200_ctx* ctx, int32_t nsteps);                      /* nsteps x (forces of all groups + COM removal + integration) */
+int  b200_integrate(b200_ctx* ctx);                                  /* IntegrateLangevinMiddleStepKernel::execute: integrate once with the forces in the buffer */
+int  b200_remove_cm_motion(b200_ctx* ctx);                           /* RemoveCMMotionKernel::execute (kernels.h:1793) */
 int  b200_apply_constraints(b200_ctx* ctx, double tol);              /* ApplyConstraintsKernel::apply */
 int  b200_apply_velocity_constraints(b200_ctx* ctx, double tol);     /* ApplyConstraintsKernel::applyToVelocities */
 int  b200_kinetic_energy(b200_ctx* ctx, double* ke);                 /* IntegrateLangevinMiddleStepKernel::computeKineticEnergy */

@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libb200nb.so")
 PLUGIN_PATH = os.path.join(_HERE, "lib", "libOpenMMB200.so")
 
 NB_NOCUTOFF, NB_CUTOFF_NONPERIODIC, NB_CUTOFF_PERIODIC, NB_EWALD, NB_PME, NB_LJPME = range(6)
-GROUP_DIRECT, GROUP_RECIPROCAL, GROUP_BONDED, GROUP_ALL = 1, 2, 4, 7
+GROUP_DIRECT, GROUP_RECIPROCAL, GROUP_BONDS, GROUP_ANGLES, GROUP_TORSIONS, GROUP_BONDED, GROUP_ALL = 1, 2, 4, 8, 16, 28, 31
 TIMER_NAMES = ["tile", "nblist", "spread", "fft", "convolve", "interpolate", "bonded", "integrate", "reorder", "comm"]
 
 c_double_p = ctypes.POINTER(ctypes.c_double)
@@ -62,7 +62,8 @@ EXPORTED_SYMBOLS = [
     "b200_nonbonded_update_parameters", "b200_nonbonded_get_pme_parameters", "b200_harmonic_bonds_create",
     "b200_harmonic_angles_create", "b200_periodic_torsions_create", "b200_set_positions", "b200_get_positions",
     "b200_set_velocities", "b200_get_velocities", "b200_get_forces", "b200_set_box", "b200_get_box", "b200_set_time",
-    "b200_get_time", "b200_compute", "b200_compute_host", "b200_integrator_create", "b200_step", "b200_apply_constraints",
+    "b200_get_time", "b200_compute", "b200_compute_host", "b200_integrator_create", "b200_step", "b200_integrate",
+    "b200_remove_cm_motion", "b200_apply_constraints",
     "b200_apply_velocity_constraints", "b200_kinetic_energy", "b200_synchronize", "b200_direct_pairs", "b200_nblist_get_stats",
     "b200_fft3d_r2c_host", "b200_fft3d_c2r_host", "b200_fft3d_c2r_noalloc", "b200_find_legal_fft_dimension", "b200_timing_enable", "b200_timing_read",
     "b200_timing_reset", "b200_timed_steps", "b200_launch_count", "b200_nccl_unique_id", "b200_comm_init", "b200_set_partition",

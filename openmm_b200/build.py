@@ -83,7 +83,7 @@ def build_plugin(force=False):
             return lib          # prebuilt copy travelled with the snapshot
         return None
     inc = ["-I" + os.path.join(REF, d, "include") for d in
-           ("openmmapi", "olla", "libraries/lepton", "libraries/sfmt", "libraries/vecmath", "platforms/reference")]
+           ("openmmapi", "olla", "serialization", "libraries/lepton", "libraries/sfmt", "libraries/vecmath", "platforms/reference")]
     inc += ["-I" + os.path.join(REF, "platforms/reference/src"), "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(REF, "tests")]
     srcs = sorted(os.path.join(PLUGIN, f) for f in os.listdir(PLUGIN) if f.endswith(".cpp") and not f.startswith("driver_"))
     hdrs = [os.path.join(PLUGIN, f) for f in os.listdir(PLUGIN) if f.endswith(".h")] + [os.path.join(ROOT, "include", "b200_nonbonded.h")]

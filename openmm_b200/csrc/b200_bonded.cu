@@ -199,10 +199,10 @@ void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy) 
         if (c->numExclPairs > 0) { exclusionCorrection<<<(c->numExclPairs + 127) / 128, 128, 0, s>>>(c->posq, c->dExclPairs, c->numExclPairs, c->boxD, c->nb.ewald_alpha, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
         if (c->numExceptions > 0) { exceptions14<<<(c->numExceptions + 127) / 128, 128, 0, s>>>(c->posq, c->dExcPairs, c->dExcParams, c->numExceptions, c->boxD, c->nb.exceptions_use_periodic, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
     }
-    if (groups & B200_GROUP_BONDED) {
-        if (c->numBonds > 0) { harmonicBonds<<<(c->numBonds + 127) / 128, 128, 0, s>>>(c->posq, c->bondAtoms, c->bondParams, c->numBonds, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
-        if (c->numAngles > 0) { harmonicAngles<<<(c->numAngles + 127) / 128, 128, 0, s>>>(c->posq, c->angleAtoms, c->angleParams, c->numAngles, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
-        if (c->numTorsions > 0) { periodicTorsions<<<(c->numTorsions + 127) / 128, 128, 0, s>>>(c->posq, c->torsionAtoms, c->torsionParams, c->numTorsions, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
+    {
+        if (c->numBonds > 0 && (groups & B200_GROUP_BONDS)) { harmonicBonds<<<(c->numBonds + 127) / 128, 128, 0, s>>>(c->posq, c->bondAtoms, c->bondParams, c->numBonds, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
+        if (c->numAngles > 0 && (groups & B200_GROUP_ANGLES)) { harmonicAngles<<<(c->numAngles + 127) / 128, 128, 0, s>>>(c->posq, c->angleAtoms, c->angleParams, c->numAngles, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
+        if (c->numTorsions > 0 && (groups & B200_GROUP_TORSIONS)) { periodicTorsions<<<(c->numTorsions + 127) / 128, 128, 0, s>>>(c->posq, c->torsionAtoms, c->torsionParams, c->numTorsions, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
     }
     CUDA_CHECK(cudaGetLastError());
 }

@@ -231,16 +231,43 @@ static IntegArgs makeArgs(b200_ctx* c) {
     return a;
 }
 
+static void removeCM(b200_ctx* c) {
+    cudaStream_t s = c->stream;
+    double total = 0; for (double m : c->mass) total += m;
+    cmZero<<<1, 1, 0, s>>>(c->counters);
+    cmMomentum<<<c->smCount * 2, 256, 0, s>>>(c->velm, c->N, c->counters);
+    cmRemove<<<c->smCount * 4, 256, 0, s>>>(c->velm, c->N, 1.0 / total, c->counters);
+    LAUNCH_COUNT(c, 3);
+}
+
+// RemoveCMMotionKernel::execute (kernels.h:1793)
+extern "C" int b200_remove_cm_motion(b200_ctx* c) {
+    try { CUDA_CHECK(cudaSetDevice(c->device)); removeCM(c); CUDA_CHECK(cudaGetLastError()); }
+    catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
+    return B200_OK;
+}
+
+// IntegrateLangevinMiddleStepKernel::execute (kernels.h:1412): one integration step with the forces already in the buffer
+extern "C" int b200_integrate(b200_ctx* c) {
+    try {
+        if (!c->hasIntegrator) throw B200Error(B200_ERR_INVALID, "b200_integrate: no integrator");
+        CUDA_CHECK(cudaSetDevice(c->device));
+        b200_finalize(c);
+        if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
+        const int keep = c->integ.remove_cm_every;
+        c->integ.remove_cm_every = 0;      // the caller (CMMotionRemover's own kernel) decides when to remove COM motion
+        b200_integrate_step(c);
+        c->integ.remove_cm_every = keep;
+        c->stepCount++; c->timePs += c->integ.dt; c->stepsSinceReorder++;
+        c->forcesValid = false;
+    } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
+    return B200_OK;
+}
+
 void b200_integrate_step(b200_ctx* c) {
     cudaStream_t s = c->stream;
     ScopedTimer tm(c, B200_T_INTEGRATE, s);
-    if (c->integ.remove_cm_every > 0 && c->stepCount % c->integ.remove_cm_every == 0) {
-        double total = 0; for (double m : c->mass) total += m;
-        cmZero<<<1, 1, 0, s>>>(c->counters);
-        cmMomentum<<<c->smCount * 2, 256, 0, s>>>(c->velm, c->N, c->counters);
-        cmRemove<<<c->smCount * 4, 256, 0, s>>>(c->velm, c->N, 1.0 / total, c->counters);
-        LAUNCH_COUNT(c, 3);
-    }
+    if (c->integ.remove_cm_every > 0 && c->stepCount % c->integ.remove_cm_every == 0) removeCM(c);
     const int units = c->numSettle + c->numFree;
     if (units > 0) {
         langevinMiddleStep<<<(units + 127) / 128, 128, 0, s>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, c->numFree, c->freeAtoms);

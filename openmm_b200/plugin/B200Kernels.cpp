@@ -1,0 +1,238 @@
+// B200Kernels.cpp -- the platform's kernels: thin adapters from OpenMM's kernel interfaces to the C ABI.
+// Reference host code being replaced for this path: platforms/common/src/CommonCalcNonbondedForce.cpp:217-717,1119-1254
+// (initialize / copyParametersToContext), platforms/common/src/CommonKernels.cpp:95-382 (state I/O, checkpoints),
+// platforms/cuda/src/CudaKernels.cpp:63-91 (CalcForcesAndEnergy).
+#include "B200Kernels.h"
+#include "openmm/OpenMMException.h"
+#include "openmm/NonbondedForce.h"
+#include "openmm/HarmonicBondForce.h"
+#include "openmm/HarmonicAngleForce.h"
+#include "openmm/PeriodicTorsionForce.h"
+#include "openmm/LangevinMiddleIntegrator.h"
+#include "openmm/VerletIntegrator.h"
+#include "openmm/internal/NonbondedForceImpl.h"
+#include "ReferenceMinimize.h"
+#include <cmath>
+#include <cstring>
+#include <iostream>
+#include <random>
+
+using namespace OpenMM;
+using namespace std;
+
+namespace B200Plugin {
+
+// ---------------------------------------------------------------------------------------------- forces and energy
+void B200CalcForcesAndEnergyKernel::beginComputation(ContextImpl&, bool, bool, int) {
+    d.pendingGroups = 0;   // every ForceImpl that takes part in this evaluation adds its bit from its kernel's execute()
+}
+
+double B200CalcForcesAndEnergyKernel::finishComputation(ContextImpl&, bool includeForce, bool includeEnergy, int, bool& valid) {
+    double energy = 0.0;
+    // the force buffer is cleared by the computation even when no group is requested, as clearAutoclearBuffers does (CudaKernels.cpp:66)
+    check(b200_compute(d.ctx, d.pendingGroups, includeForce ? 1 : 0, includeEnergy ? 1 : 0, &energy));
+    valid = true;            // list growth/retry is handled inside the library (CudaNonbondedUtilities.cpp:441-479 does it by invalidating)
+    return includeEnergy ? energy : 0.0;
+}
+
+// ---------------------------------------------------------------------------------------------- state
+double B200UpdateStateDataKernel::getTime(const ContextImpl&) const { double t; int64_t s; check(b200_get_time(d.ctx, &t, &s)); return t; }
+void B200UpdateStateDataKernel::setTime(ContextImpl&, double time) { double t; int64_t s; check(b200_get_time(d.ctx, &t, &s)); check(b200_set_time(d.ctx, time, s)); }
+long long B200UpdateStateDataKernel::getStepCount(const ContextImpl&) const { double t; int64_t s; check(b200_get_time(d.ctx, &t, &s)); return s; }
+void B200UpdateStateDataKernel::setStepCount(const ContextImpl&, long long count) { double t; int64_t s; check(b200_get_time(d.ctx, &t, &s)); check(b200_set_time(d.ctx, t, count)); }
+
+static void toVec3(const vector<double>& a, vector<Vec3>& v) { v.resize(a.size() / 3); for (size_t i = 0; i < v.size(); i++) v[i] = Vec3(a[3 * i], a[3 * i + 1], a[3 * i + 2]); }
+static vector<double> fromVec3(const vector<Vec3>& v) { vector<double> a(3 * v.size()); for (size_t i = 0; i < v.size(); i++) { a[3 * i] = v[i][0]; a[3 * i + 1] = v[i][1]; a[3 * i + 2] = v[i][2]; } return a; }
+
+void B200UpdateStateDataKernel::getPositions(ContextImpl&, vector<Vec3>& positions, bool) {
+    vector<double> a(3 * (size_t)numParticles);
+    check(b200_get_positions(d.ctx, a.data(), 0));
+    toVec3(a, positions);
+}
+void B200UpdateStateDataKernel::setPositions(ContextImpl&, const vector<Vec3>& positions) {
+    if ((int)positions.size() != numParticles) throw OpenMMException("Called setPositions() on a Context with the wrong number of positions");
+    vector<double> a = fromVec3(positions);
+    check(b200_set_positions(d.ctx, a.data()));
+    d.positionsValid = true;
+}
+void B200UpdateStateDataKernel::getVelocities(ContextImpl&, vector<Vec3>& velocities) {
+    vector<double> a(3 * (size_t)numParticles);
+    check(b200_get_velocities(d.ctx, a.data()));
+    toVec3(a, velocities);
+}
+void B200UpdateStateDataKernel::setVelocities(ContextImpl&, const vector<Vec3>& velocities) {
+    if ((int)velocities.size() != numParticles) throw OpenMMException("Called setVelocities() on a Context with the wrong number of velocities");
+    vector<double> a = fromVec3(velocities);
+    check(b200_set_velocities(d.ctx, a.data()));
+}
+void B200UpdateStateDataKernel::computeShiftedVelocities(ContextImpl& context, double timeShift, vector<Vec3>& velocities) {
+    // v(t + shift) ~ v + shift * F/m with the forces currently in the buffer (IntegrationUtilities::computeShiftedVelocities)
+    getVelocities(context, velocities);
+    if (timeShift == 0.0) return;
+    vector<Vec3> forces;
+    getForces(context, forces);
+    for (int i = 0; i < numParticles; i++)
+        if (masses[i] > 0) velocities[i] += forces[i] * (timeShift / masses[i]);
+}
+void B200UpdateStateDataKernel::getForces(ContextImpl&, vector<Vec3>& forces) {
+    vector<double> a(3 * (size_t)numParticles);
+    check(b200_get_forces(d.ctx, a.data()));
+    toVec3(a, forces);
+}
+void B200UpdateStateDataKernel::getPeriodicBoxVectors(ContextImpl&, Vec3& a, Vec3& b, Vec3& c) const {
+    double box[9];
+    check(b200_get_box(d.ctx, box));
+    a = Vec3(box[0], box[1], box[2]); b = Vec3(box[3], box[4], box[5]); c = Vec3(box[6], box[7], box[8]);
+}
+void B200UpdateStateDataKernel::setPeriodicBoxVectors(ContextImpl&, const Vec3& a, const Vec3& b, const Vec3& c) {
+    const double box[9] = {a[0], a[1], a[2], b[0], b[1], b[2], c[0], c[1], c[2]};
+    check(b200_set_box(d.ctx, box));
+}
+void B200UpdateStateDataKernel::createCheckpoint(ContextImpl& context, ostream& stream) {
+    // platform-specific binary state, as in CommonKernels.cpp:354-382 (version, time, step, positions, velocities, box)
+    const int version = 1;
+    stream.write((const char*)&version, sizeof(int));
+    double t; int64_t s;
+    check(b200_get_time(d.ctx, &t, &s));
+    stream.write((const char*)&t, sizeof(double)); stream.write((const char*)&s, sizeof(int64_t));
+    vector<double> p(3 * (size_t)numParticles), v(p.size());
+    check(b200_get_positions(d.ctx, p.data(), 0)); check(b200_get_velocities(d.ctx, v.data()));
+    stream.write((const char*)p.data(), sizeof(double) * p.size()); stream.write((const char*)v.data(), sizeof(double) * v.size());
+    double box[9]; check(b200_get_box(d.ctx, box));
+    stream.write((const char*)box, sizeof(box));
+}
+void B200UpdateStateDataKernel::loadCheckpoint(ContextImpl& context, istream& stream) {
+    int version = 0;
+    stream.read((char*)&version, sizeof(int));
+    if (version != 1) throw OpenMMException("Checkpoint was created with a different version of OpenMM");
+    double t; int64_t s;
+    stream.read((char*)&t, sizeof(double)); stream.read((char*)&s, sizeof(int64_t));
+    vector<double> p(3 * (size_t)numParticles), v(p.size());
+    stream.read((char*)p.data(), sizeof(double) * p.size()); stream.read((char*)v.data(), sizeof(double) * v.size());
+    double box[9]; stream.read((char*)box, sizeof(box));
+    check(b200_set_box(d.ctx, box)); check(b200_set_positions(d.ctx, p.data())); check(b200_set_velocities(d.ctx, v.data()));
+    check(b200_set_time(d.ctx, t, s));
+}
+
+void B200MinimizeKernel::execute(ContextImpl& context, double tolerance, int maxIterations, MinimizationReporter* reporter) {
+    ReferenceMinimize::minimize(context, tolerance, maxIterations, reporter);
+}
+
+// ---------------------------------------------------------------------------------------------- NonbondedForce
+struct B200CalcNonbondedForceKernel::Params {
+    vector<double> q, sigma, eps;
+    vector<int> exclusions, exceptions;
+    vector<double> excQQ, excSigma, excEps;
+    b200_nonbonded_desc desc;
+};
+
+void B200CalcNonbondedForceKernel::gather(const System& system, const NonbondedForce& force, Params& p) const {
+    if (force.getNumParticleParameterOffsets() > 0 || force.getNumExceptionParameterOffsets() > 0)
+        throw OpenMMException("The B200 platform does not support NonbondedForce parameter offsets yet");
+    if (force.getUseSwitchingFunction()) throw OpenMMException("The B200 platform does not support the NonbondedForce switching function yet");
+    if (force.getNonbondedMethod() != NonbondedForce::PME)
+        throw OpenMMException("The B200 platform implements NonbondedForce with the PME method only");
+    const int n = force.getNumParticles();
+    p.q.resize(n); p.sigma.resize(n); p.eps.resize(n);
+    for (int i = 0; i < n; i++) force.getParticleParameters(i, p.q[i], p.sigma[i], p.eps[i]);
+    // exceptions split as CommonCalcNonbondedForce.cpp:239-250: all of them are exclusions, those with parameters are 1-4 pairs
+    for (int i = 0; i < force.getNumExceptions(); i++) {
+        int a, b; double qq, s, e;
+        force.getExceptionParameters(i, a, b, qq, s, e);
+        p.exclusions.push_back(a); p.exclusions.push_back(b);
+        if (qq != 0.0 || e != 0.0) { p.exceptions.push_back(a); p.exceptions.push_back(b); p.excQQ.push_back(qq); p.excSigma.push_back(s); p.excEps.push_back(e); }
+    }
+    b200_nonbonded_desc& dd = p.desc;
+    memset(&dd, 0, sizeof(dd));
+    dd.method = B200_NB_PME;
+    dd.cutoff = force.getCutoffDistance();
+    int nx, ny, nz;
+    NonbondedForceImpl::calcPMEParameters(system, force, dd.ewald_alpha, nx, ny, nz, false);
+    dd.grid[0] = b200_find_legal_fft_dimension(max(nx, 6)); dd.grid[1] = b200_find_legal_fft_dimension(max(ny, 6)); dd.grid[2] = b200_find_legal_fft_dimension(max(nz, 6));
+    dd.dispersion_coefficient = force.getUseDispersionCorrection() ? NonbondedForceImpl::calcDispersionCorrection(system, force) : 0.0;
+    dd.charge = p.q.data(); dd.sigma = p.sigma.data(); dd.epsilon = p.eps.data();
+    dd.num_exclusions = (int)p.exclusions.size() / 2; dd.exclusion_pairs = p.exclusions.data();
+    dd.num_exceptions = (int)p.excQQ.size(); dd.exception_pairs = p.exceptions.data();
+    dd.exception_chargeprod = p.excQQ.data(); dd.exception_sigma = p.excSigma.data(); dd.exception_epsilon = p.excEps.data();
+    dd.exceptions_use_periodic = force.getExceptionsUsePeriodicBoundaryConditions() ? 1 : 0;
+}
+
+void B200CalcNonbondedForceKernel::initialize(const System& system, const NonbondedForce& force) {
+    Params p;
+    gather(system, force, p);
+    check(b200_nonbonded_create(d.ctx, &p.desc));
+}
+
+double B200CalcNonbondedForceKernel::execute(ContextImpl&, bool, bool, bool includeDirect, bool includeReciprocal) {
+    if (includeDirect) d.pendingGroups |= B200_GROUP_DIRECT;
+    if (includeReciprocal) d.pendingGroups |= B200_GROUP_RECIPROCAL;
+    return 0.0;   // the energy of this force is returned by CalcForcesAndEnergyKernel::finishComputation
+}
+
+void B200CalcNonbondedForceKernel::copyParametersToContext(ContextImpl& context, const NonbondedForce& force, int, int, int, int) {
+    Params p;
+    gather(context.getSystem(), force, p);
+    check(b200_nonbonded_update_parameters(d.ctx, &p.desc));
+}
+
+void B200CalcNonbondedForceKernel::getPMEParameters(double& alpha, int& nx, int& ny, int& nz) const {
+    int32_t x, y, z;
+    check(b200_nonbonded_get_pme_parameters(d.ctx, &alpha, &x, &y, &z));
+    nx = x; ny = y; nz = z;
+}
+void B200CalcNonbondedForceKernel::getLJPMEParameters(double&, int&, int&, int&) const {
+    throw OpenMMException("getLJPMEParameters: this Context is not using LJPME");
+}
+
+// ---------------------------------------------------------------------------------------------- bonded forces
+void B200CalcHarmonicBondForceKernel::initialize(const System&, const HarmonicBondForce& force) {
+    const int n = force.getNumBonds();
+    vector<int> atoms(2 * (size_t)n); vector<double> len(n), k(n);
+    for (int i = 0; i < n; i++) force.getBondParameters(i, atoms[2 * i], atoms[2 * i + 1], len[i], k[i]);
+    check(b200_harmonic_bonds_create(d.ctx, n, atoms.data(), len.data(), k.data(), force.getForceGroup()));
+}
+void B200CalcHarmonicBondForceKernel::copyParametersToContext(ContextImpl&, const HarmonicBondForce&, int, int) {
+    throw OpenMMException("The B200 platform does not support updateParametersInContext for HarmonicBondForce yet");
+}
+void B200CalcHarmonicAngleForceKernel::initialize(const System&, const HarmonicAngleForce& force) {
+    const int n = force.getNumAngles();
+    vector<int> atoms(3 * (size_t)n); vector<double> ang(n), k(n);
+    for (int i = 0; i < n; i++) force.getAngleParameters(i, atoms[3 * i], atoms[3 * i + 1], atoms[3 * i + 2], ang[i], k[i]);
+    check(b200_harmonic_angles_create(d.ctx, n, atoms.data(), ang.data(), k.data(), force.getForceGroup()));
+}
+void B200CalcHarmonicAngleForceKernel::copyParametersToContext(ContextImpl&, const HarmonicAngleForce&, int, int) {
+    throw OpenMMException("The B200 platform does not support updateParametersInContext for HarmonicAngleForce yet");
+}
+void B200CalcPeriodicTorsionForceKernel::initialize(const System&, const PeriodicTorsionForce& force) {
+    const int n = force.getNumTorsions();
+    vector<int> atoms(4 * (size_t)n), per(n); vector<double> phase(n), k(n);
+    for (int i = 0; i < n; i++) force.getTorsionParameters(i, atoms[4 * i], atoms[4 * i + 1], atoms[4 * i + 2], atoms[4 * i + 3], per[i], phase[i], k[i]);
+    check(b200_periodic_torsions_create(d.ctx, n, atoms.data(), per.data(), phase.data(), k.data(), force.getForceGroup()));
+}
+void B200CalcPeriodicTorsionForceKernel::copyParametersToContext(ContextImpl&, const PeriodicTorsionForce&, int, int) {
+    throw OpenMMException("The B200 platform does not support updateParametersInContext for PeriodicTorsionForce yet");
+}
+
+// ---------------------------------------------------------------------------------------------- integrators
+void B200IntegrateLangevinMiddleStepKernel::initialize(const System&, const LangevinMiddleIntegrator& integrator) {
+    int s = integrator.getRandomNumberSeed();
+    seed = s != 0 ? (unsigned long long)s : (unsigned long long)random_device{}();   // 0 means "pick one" (osrngseed in the reference)
+}
+void B200IntegrateLangevinMiddleStepKernel::execute(ContextImpl&, const LangevinMiddleIntegrator& integrator) {
+    b200_integrator_desc desc = {integrator.getStepSize(), integrator.getTemperature(), integrator.getFriction(), integrator.getConstraintTolerance(), seed, 0};
+    check(b200_integrator_create(d.ctx, &desc));
+    check(b200_integrate(d.ctx));
+}
+double B200IntegrateLangevinMiddleStepKernel::computeKineticEnergy(ContextImpl&, const LangevinMiddleIntegrator&) {
+    double ke; check(b200_kinetic_energy(d.ctx, &ke)); return ke;
+}
+void B200IntegrateVerletStepKernel::execute(ContextImpl&, const VerletIntegrator& integrator) {
+    b200_integrator_desc desc = {integrator.getStepSize(), 0.0, 0.0, integrator.getConstraintTolerance(), 0, 0};
+    check(b200_integrator_create(d.ctx, &desc));
+    check(b200_integrate(d.ctx));
+}
+double B200IntegrateVerletStepKernel::computeKineticEnergy(ContextImpl&, const VerletIntegrator&) {
+    double ke; check(b200_kinetic_energy(d.ctx, &ke)); return ke;
+}
+
+}  // namespace B200Plugin

@@ -1,0 +1,58 @@
+"""The OpenMM `B200` Platform plugin (openmm_b200/lib/libOpenMMB200.so) driven through the reference's own public API by
+oracle/_ref/ref_driver (unmodified OpenMM 8.6): an unmodified System/Context selects the platform by name."""
+import ctypes
+import json
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+import pytest
+
+import openmm_b200 as b
+from openmm_b200 import workloads
+from oracle_lib import REF_DRIVER, REF_PLUGINS
+
+
+def test_plugin_exports_the_loader_symbols():
+    assert os.path.exists(b.PLUGIN_PATH), "run python -m openmm_b200.build"
+    lib = ctypes.CDLL(b.PLUGIN_PATH)
+    assert hasattr(lib, "registerPlatforms") and hasattr(lib, "registerKernelFactories")   # PluginInitializer.h:46,56
+
+
+def _driver(args):
+    out = subprocess.run([REF_DRIVER] + args, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    assert out.returncode == 0, out.stderr
+    return json.loads(out.stdout.strip().splitlines()[-1])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [1536, 6000])
+def test_context_on_b200_platform_matches_reference_platform(n):
+    sysd = workloads.water_box(n, seed=n)
+    alpha, grid = b.pme_parameters(0.9, sysd["box"])
+    with tempfile.TemporaryDirectory() as td:
+        sp = os.path.join(td, "s.bin")
+        workloads.write_system_file(sp, sysd, 0.9, alpha, grid, dispersion=True)
+        r = _driver(["compare", sp, "--platform", "B200", "--plugin", b.PLUGIN_PATH, "--against", "Reference"])
+    print(r)
+    assert r["rel_rms_force_total"] < 1e-5 and r["rel_rms_force_direct"] < 1e-5 and r["rel_rms_force_recip"] < 2e-5
+    assert r["rel_energy"] < 1e-5
+    assert abs(r["e_direct"] - r["e_direct_ref"]) / abs(r["e_direct_ref"]) < 1e-5
+    assert abs(r["e_recip"] - r["e_recip_ref"]) / abs(r["e_recip_ref"]) < 1e-5
+
+
+@pytest.mark.gpu
+def test_langevin_middle_steps_through_the_plugin():
+    sysd = workloads.water_box(6000, seed=6000)
+    alpha, grid = b.pme_parameters(0.9, sysd["box"])
+    with tempfile.TemporaryDirectory() as td:
+        sp = os.path.join(td, "s.bin")
+        workloads.write_system_file(sp, sysd, 0.9, alpha, grid)
+        g = _driver(["bench", sp, "--platform", "B200", "--plugin", b.PLUGIN_PATH, "--steps", "200", "--warmup", "50"])
+        c = _driver(["bench", sp, "--platform", "CPU", "--plugin", os.path.join(REF_PLUGINS, "libOpenMMCPU.so"), "--plugin",
+                     os.path.join(REF_PLUGINS, "libOpenMMPME.so"), "--steps", "200", "--warmup", "50"])
+    print(g, c)
+    assert np.isfinite(g["potential_energy"])
+    # same ensemble after 250 steps: potential energies of the two platforms agree to within thermal fluctuations (~1%)
+    assert abs(g["potential_energy"] - c["potential_energy"]) / abs(c["potential_energy"]) < 0.03
