@@ -238,6 +238,9 @@ def main():
         pairs_total = int(t.item())
     else:
         pairs_total = pairs
+    sparse_tiles = int(stats["num_sparse_tiles"])
+    dense_tiles = int(stats["num_tiles"]) - 2 * sparse_tiles
+    dense_slots = (dense_tiles + int(stats["num_exclusion_tiles"])) * 1024
     tile_ms, tile_n = fam["tile"]
     tile_avg_ms = tile_ms / max(tile_n, 1)
     hbm_gbs, sm_max_mhz, peak_kind = measured_peaks()
@@ -252,7 +255,7 @@ def main():
                 "frac": achieved_tflops / fp32_peak if fp32_peak else None, "traffic": None,
                 "peak_source": f"{sm_count} SMs x 128 lanes x 2 x {sm_max_mhz:.0f} MHz ({peak_kind} sm_max_mhz)",
                 "algorithmic": f"{FLOP_PER_PAIR:.0f} FLOP x {pairs} in-cutoff pairs per launch (this rank)",
-                "executed_pair_slots_per_launch": int(stats["num_tiles"]) * 1024 + int(stats["num_exclusion_tiles"]) * 1024,
+                "executed_pair_slots_per_launch": dense_slots,
                 "avg_launch_ms": tile_avg_ms,
                 "pme": {"bound": "hbm", "achieved": pme_bytes / (pme_ms * 1e-3) / 1e9 if pme_ms > 0 else None, "peak": hbm_gbs, "unit": "GB/s",
                         "frac": (pme_bytes / (pme_ms * 1e-3) / 1e9 / hbm_gbs) if pme_ms > 0 else None, "bytes_per_step": pme_bytes, "ms_per_step": pme_ms}}
@@ -296,9 +299,9 @@ def main():
             "pair_interactions_per_s": pairs_total / (tile_avg_ms * 1e-3) if tile_avg_ms > 0 else None,
             "in_cutoff_pairs": pairs_total,
             "kernel_ms_per_step": {k: v[0] / prof_steps for k, v in fam.items()},
-            "nblist": {"tiles": int(stats["num_tiles"]), "units": int(stats["num_units"]), "exclusion_tiles": int(stats["num_exclusion_tiles"]),
+            "nblist": {"tiles": dense_tiles, "sparse_tiles": sparse_tiles, "units": int(stats["num_units"]), "exclusion_tiles": int(stats["num_exclusion_tiles"]),
                        "rebuilds": int(stats["rebuilds"]), "steps": int(stats["steps"]),
-                       "tile_efficiency": pairs / max(1.0, (int(stats["num_tiles"]) + int(stats["num_exclusion_tiles"])) * 1024.0)},
+                       "tile_efficiency": pairs / max(1.0, float(dense_slots))},
         }
         print(json.dumps(line))
     ctx.close()

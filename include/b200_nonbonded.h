@@ -158,6 +158,7 @@ int  b200_direct_pairs(b200_ctx* ctx, int64_t* count, int32_t* pairs /*[2*capaci
 typedef struct {
     int64_t num_blocks, num_tiles, num_units, num_exclusion_tiles, rebuilds, steps, reorders;
     int64_t tile_capacity, unit_capacity;
+    int64_t num_sparse_tiles;   /* of num_tiles (each sparse tile occupies two slots) */
 } b200_nblist_stats;
 int  b200_nblist_get_stats(b200_ctx* ctx, b200_nblist_stats* out);
 

@@ -53,7 +53,7 @@ class IntegratorDesc(ctypes.Structure):
 
 class NblistStats(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int64) for n in ("num_blocks", "num_tiles", "num_units", "num_exclusion_tiles", "rebuilds", "steps",
-                                              "reorders", "tile_capacity", "unit_capacity")]
+                                              "reorders", "tile_capacity", "unit_capacity", "num_sparse_tiles")]
 
 
 # every symbol include/b200_nonbonded.h declares (tests/test_abi.py checks the header against this list and the .so)

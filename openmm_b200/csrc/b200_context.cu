@@ -160,6 +160,7 @@ extern "C" int b200_nonbonded_create(b200_ctx* c, const b200_nonbonded_desc* d) 
     c->padding = padFrac * d->cutoff;
     c->paddedCutoff = d->cutoff + c->padding;
     c->exactEwald = d->ewald_alpha * d->cutoff > 3.95;
+    if (const char* sp = getenv("B200_SPARSE_MAX")) c->sparseMax = std::max(0, std::min(32, atoi(sp)));
     b200_box_set(c, c->boxHost);
     // per-slot parameters (nonbondedParameters.cc:30-35: posq.w = q, sigmaEpsilon = (sigma/2, 2 sqrt(eps)))
     std::vector<float2> se(c->Npad, make_float2(0.f, 0.f));
@@ -586,18 +587,20 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     if (energy) { zeroEnergy<<<1, 1, 0, s>>>(c->counters); LAUNCH_COUNT(c, 1); }
     const bool doRecip = c->hasNonbonded && (groups & B200_GROUP_RECIPROCAL) && c->partRank == 0;
     const bool doDirect = c->hasNonbonded && (groups & B200_GROUP_DIRECT);
-    cudaStream_t ps = c->usePmeStream ? c->pmeStream : s;
+    // per-family event timing needs the families serialised: overlapping streams would charge waiting time to the wrong family
+    const bool usePmeStream = c->usePmeStream && !c->timing;
+    cudaStream_t ps = usePmeStream ? c->pmeStream : s;
     if (doRecip) {
-        if (c->usePmeStream) { CUDA_CHECK(cudaEventRecord(c->evFork, s)); CUDA_CHECK(cudaStreamWaitEvent(ps, c->evFork, 0)); }
+        if (usePmeStream) { CUDA_CHECK(cudaEventRecord(c->evFork, s)); CUDA_CHECK(cudaStreamWaitEvent(ps, c->evFork, 0)); }
         b200_pme_launch(c, ps, forces, energy);
-        if (c->usePmeStream) CUDA_CHECK(cudaEventRecord(c->evPmeDone, ps));
+        if (usePmeStream) CUDA_CHECK(cudaEventRecord(c->evPmeDone, ps));
     }
     if (doDirect) {
         prepareLists(c, verify);
         b200_tile_launch(c, forces, energy, false);
     }
     if (c->partRank == 0) b200_bonded_launch(c, groups, forces, energy);
-    if (doRecip && c->usePmeStream) CUDA_CHECK(cudaStreamWaitEvent(s, c->evPmeDone, 0));
+    if (doRecip && usePmeStream) CUDA_CHECK(cudaStreamWaitEvent(s, c->evPmeDone, 0));
     if (forces && c->commRanks > 1) b200_comm_allreduce_forces(c);
     c->forcesValid = forces && groups == B200_GROUP_ALL;
     if (energy) {
@@ -667,7 +670,7 @@ extern "C" int b200_nblist_get_stats(b200_ctx* c, b200_nblist_stats* out) {
     checkOverflow(c);
     out->num_blocks = c->B; out->num_tiles = c->countersHost->numTiles; out->num_units = c->countersHost->numUnits;
     out->num_exclusion_tiles = c->numExclTiles; out->rebuilds = c->countersHost->rebuildCount; out->steps = c->stepCount;
-    out->reorders = 0; out->tile_capacity = c->tileCapacity; out->unit_capacity = c->unitCapacity;
+    out->reorders = 0; out->num_sparse_tiles = c->countersHost->numSparseTiles; out->tile_capacity = c->tileCapacity; out->unit_capacity = c->unitCapacity;
     API_END
 }
 

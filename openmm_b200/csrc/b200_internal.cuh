@@ -43,7 +43,7 @@ struct DevCounters {
     int          rebuild;       // 1 => the list must be rebuilt before the next tile kernel
     int          rebuildCount;
     unsigned int maxHalfBits[3];// max block half extent per dim, float bits (positive floats order as uints)
-    unsigned int pad0;
+    unsigned int numSparseTiles;// sparse tiles (each occupies two 32-int slots of jAtoms) among numTiles
     unsigned long long pairCount;
     long long    energy[8];     // fixed point 2^32: 0 direct tiles, 1 exclusion corr, 2 exceptions, 3 reciprocal, 4 bonded, 5 kinetic*2
     long long    momentum[4];   // fixed point: sum m v (x,y,z), unused
@@ -134,6 +134,7 @@ struct b200_ctx {
     int4* units = nullptr; int* jAtoms = nullptr; long long unitCapacity = 0, tileCapacity = 0;
     int2* pairOut = nullptr; long long pairCapacity = 0;
     int partRank = 0, partRanks = 1;
+    int sparseMax = 3;             // j atoms reaching at most this many atoms of X are handled as sparse pairs
 
     // PME
     int gridN[3] = {0, 0, 0}; int nzc = 0;

@@ -32,7 +32,7 @@ __global__ void nbBlockBounds(const float4* __restrict__ posq, float4* __restric
     if (!counters->rebuild) return;
     const int lane = threadIdx.x & 31;
     const int warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
-    if (blockIdx.x == 0 && threadIdx.x == 0) { counters->numUnits = 0; counters->numTiles = 0; counters->rebuildCount++; }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { counters->numUnits = 0; counters->numTiles = 0; counters->numSparseTiles = 0; counters->rebuildCount++; }
     for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < B; b += warpsPerGrid) {
         const int slot = b * 32 + lane;
         const float4 p = posq[slot];
@@ -91,9 +91,37 @@ __device__ __forceinline__ float boxGap2(float4 cA, float4 hA, float4 cB, float4
     return dx * dx + dy * dy + dz * dz;
 }
 
-// ---- tile-list build (findBlocksWithInteractions, findInteractingBlocks.cu:289-542), one warp per block X
+// ---- tile-list build (findBlocksWithInteractions, findInteractingBlocks.cu:289-542), one warp per block X.
+// Every candidate j atom gets the 32-bit mask of the atoms of X it can reach within the padded cutoff.  Atoms that reach
+// more than `sparseMax` atoms of X are compacted into dense 32-atom tiles; the others go, with their mask, into sparse
+// tiles (the reference's singlePairs, findInteractingBlocks.cu:188-238) that cost a few pair evaluations per atom.
+#define NB_SPARSE_TILES 4
+#define NB_SBUF (NB_SPARSE_TILES * 32 + 32)
+
+__device__ __forceinline__ void flushDense(int X, int* buf, int ntiles, int lane, int4* units, int* jAtoms, unsigned unitCapacity, unsigned tileCapacity, DevCounters* counters) {
+    unsigned tileBase = 0, unit = 0;
+    if (lane == 0) { tileBase = atomicAdd(&counters->numTiles, (unsigned)ntiles); unit = atomicAdd(&counters->numUnits, 1u); }
+    tileBase = __shfl_sync(0xffffffffu, tileBase, 0); unit = __shfl_sync(0xffffffffu, unit, 0);
+    if (tileBase + ntiles <= tileCapacity && unit < unitCapacity) {
+        for (int k = lane; k < ntiles * 32; k += 32) jAtoms[(size_t)tileBase * 32 + k] = buf[k];
+        if (lane == 0) units[unit] = make_int4(X, (int)tileBase, ntiles, 0);
+    } else if (lane == 0) counters->overflow = 1;
+}
+__device__ __forceinline__ void flushSparse(int X, int* slots, int* masks, int ntiles, int lane, int4* units, int* jAtoms, unsigned unitCapacity, unsigned tileCapacity, DevCounters* counters) {
+    unsigned tileBase = 0, unit = 0;
+    if (lane == 0) { tileBase = atomicAdd(&counters->numTiles, (unsigned)(2 * ntiles)); unit = atomicAdd(&counters->numUnits, 1u); atomicAdd(&counters->numSparseTiles, (unsigned)ntiles); }
+    tileBase = __shfl_sync(0xffffffffu, tileBase, 0); unit = __shfl_sync(0xffffffffu, unit, 0);
+    if (tileBase + 2 * ntiles <= tileCapacity && unit < unitCapacity) {
+        for (int t = 0; t < ntiles; t++) {   // layout per sparse tile: 32 atom slots, then their 32 masks
+            jAtoms[(size_t)(tileBase + 2 * t) * 32 + lane] = slots[t * 32 + lane];
+            jAtoms[(size_t)(tileBase + 2 * t + 1) * 32 + lane] = masks[t * 32 + lane];
+        }
+        if (lane == 0) units[unit] = make_int4(X, (int)tileBase, ntiles, 1);
+    } else if (lane == 0) counters->overflow = 1;
+}
+
 __global__ void __launch_bounds__(NB_THREADS) nbBuild(
-        const float4* __restrict__ posq, int N, int B, int numSuper, BoxF box, float rcp2,
+        const float4* __restrict__ posq, int N, int B, int numSuper, BoxF box, float rcp2, int sparseMax,
         const float4* __restrict__ blockCenter, const float4* __restrict__ blockHalf,
         const float4* __restrict__ superCenter, const float4* __restrict__ superHalf,
         const int* __restrict__ exclRowStart, const int* __restrict__ exclRowCols,
@@ -102,14 +130,17 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
     if (!counters->rebuild) return;
     __shared__ float4 sX[NB_WARPS][32];
     __shared__ int sBuf[NB_WARPS][NB_BUF];
+    __shared__ int sSlot[NB_WARPS][NB_SBUF];
+    __shared__ int sMask[NB_WARPS][NB_SBUF];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const unsigned ltMask = (1u << lane) - 1u;
+    const float rcp = sqrtf(rcp2);
     // rows are dealt round-robin to ranks: every rank gets a statistically identical share of the sweep
     for (int xi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; xi * partRanks + partRank < B; xi += warpsPerGrid) {
         const int X = xi * partRanks + partRank;
         const float4 cX = blockCenter[X], hX = blockHalf[X];
-        const bool single = !box.triclinic && 0.5f * box.ax - hX.x >= sqrtf(rcp2) && 0.5f * box.by - hX.y >= sqrtf(rcp2) && 0.5f * box.cz - hX.z >= sqrtf(rcp2);
+        const bool single = !box.triclinic && 0.5f * box.ax - hX.x >= rcp && 0.5f * box.by - hX.y >= rcp && 0.5f * box.cz - hX.z >= rcp;
         {
             const int slot = X * 32 + lane;
             const float4 p = posq[slot];
@@ -121,14 +152,14 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
             __syncwarp();
         }
         const int exBegin = exclRowStart[X], exEnd = exclRowStart[X + 1];
-        int nbuf = 0;
+        int nbuf = 0, nsp = 0;
         for (int s0 = (X >> 5) & ~31; s0 < numSuper; s0 += 32) {   // candidates Y > X live in super blocks >= X/32
             const int s = s0 + lane;
             bool sHit = false;
             if (s < numSuper && s >= (X >> 5)) sHit = boxGap2(cX, hX, superCenter[s], superHalf[s], box) < rcp2;
-            unsigned sMask = __ballot_sync(0xffffffffu, sHit);
-            while (sMask) {
-                const int sb = s0 + __ffs(sMask) - 1; sMask &= sMask - 1;
+            unsigned sMaskBits = __ballot_sync(0xffffffffu, sHit);
+            while (sMaskBits) {
+                const int sb = s0 + __ffs(sMaskBits) - 1; sMaskBits &= sMaskBits - 1;
                 const int Y = sb * 32 + lane;
                 bool bHit = false;
                 if (Y < B && Y > X) {
@@ -139,47 +170,59 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
                 while (bMask) {
                     const int Yb = sb * 32 + __ffs(bMask) - 1; bMask &= bMask - 1;
                     const int slot = Yb * 32 + lane;
-                    bool hit = false;
+                    unsigned imask = 0;
+                    bool cand = false;
+                    float rx = 0.f, ry = 0.f, rz = 0.f;
                     if (slot < N) {
                         const float4 p = posq[slot];
-                        float rx = p.x - cX.x, ry = p.y - cX.y, rz = p.z - cX.z;
+                        rx = p.x - cX.x; ry = p.y - cX.y; rz = p.z - cX.z;
                         imageDelta(rx, ry, rz, box);
                         const float gx = fmaxf(0.f, fabsf(rx) - hX.x), gy = fmaxf(0.f, fabsf(ry) - hX.y), gz = fmaxf(0.f, fabsf(rz) - hX.z);
-                        if (gx * gx + gy * gy + gz * gz < rcp2) {
-                            if (single) {
-                                for (int i = 0; i < 32; i++) {
-                                    const float4 a = sX[warp][i];
-                                    const float dx = rx - a.x, dy = ry - a.y, dz = rz - a.z;
-                                    hit |= (dx * dx + dy * dy + dz * dz < rcp2);
-                                }
-                            } else {
-                                for (int i = 0; i < 32; i++) {
-                                    const float4 a = sX[warp][i];
-                                    float dx = rx - a.x, dy = ry - a.y, dz = rz - a.z;
-                                    imageDelta(dx, dy, dz, box);
-                                    hit |= (dx * dx + dy * dy + dz * dz < rcp2);
-                                }
+                        cand = gx * gx + gy * gy + gz * gz < rcp2;
+                    }
+                    if (__any_sync(0xffffffffu, cand)) {
+                        if (single) {
+#pragma unroll 8
+                            for (int i = 0; i < 32; i++) {
+                                const float4 a = sX[warp][i];
+                                const float dx = rx - a.x, dy = ry - a.y, dz = rz - a.z;
+                                imask |= (dx * dx + dy * dy + dz * dz < rcp2 ? 1u : 0u) << i;
+                            }
+                        } else {
+                            for (int i = 0; i < 32; i++) {
+                                const float4 a = sX[warp][i];
+                                float dx = rx - a.x, dy = ry - a.y, dz = rz - a.z;
+                                imageDelta(dx, dy, dz, box);
+                                imask |= (dx * dx + dy * dy + dz * dz < rcp2 ? 1u : 0u) << i;
                             }
                         }
+                        if (!cand) imask = 0;
                     }
-                    const unsigned m = __ballot_sync(0xffffffffu, hit);
-                    if (hit) sBuf[warp][nbuf + __popc(m & ltMask)] = slot;
-                    nbuf += __popc(m);
+                    const int cnt = __popc(imask);
+                    const bool dense = cnt > sparseMax, sparse = cnt > 0 && !dense;
+                    const unsigned mD = __ballot_sync(0xffffffffu, dense), mS = __ballot_sync(0xffffffffu, sparse);
+                    if (dense) sBuf[warp][nbuf + __popc(mD & ltMask)] = slot;
+                    if (sparse) { const int k = nsp + __popc(mS & ltMask); sSlot[warp][k] = slot; sMask[warp][k] = (int)imask; }
+                    nbuf += __popc(mD); nsp += __popc(mS);
                     __syncwarp();
-                    if (nbuf >= B200_UNIT_TILES * 32) {   // flush one full work unit
-                        unsigned tileBase = 0, unit = 0;
-                        if (lane == 0) { tileBase = atomicAdd(&counters->numTiles, (unsigned)B200_UNIT_TILES); unit = atomicAdd(&counters->numUnits, 1u); }
-                        tileBase = __shfl_sync(0xffffffffu, tileBase, 0); unit = __shfl_sync(0xffffffffu, unit, 0);
-                        if (tileBase + B200_UNIT_TILES <= tileCapacity && unit < unitCapacity) {
-                            for (int k = lane; k < B200_UNIT_TILES * 32; k += 32) jAtoms[(size_t)tileBase * 32 + k] = sBuf[warp][k];
-                            if (lane == 0) units[unit] = make_int4(X, (int)tileBase, B200_UNIT_TILES, 0);
-                        } else if (lane == 0) counters->overflow = 1;
+                    if (nbuf >= B200_UNIT_TILES * 32) {   // flush one full dense work unit
+                        flushDense(X, sBuf[warp], B200_UNIT_TILES, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
                         const int rest = nbuf - B200_UNIT_TILES * 32;
                         int carry = 0;
                         if (lane < rest) carry = sBuf[warp][B200_UNIT_TILES * 32 + lane];
                         __syncwarp();
                         if (lane < rest) sBuf[warp][lane] = carry;
                         nbuf = rest;
+                        __syncwarp();
+                    }
+                    if (nsp >= NB_SPARSE_TILES * 32) {   // flush one full sparse work unit
+                        flushSparse(X, sSlot[warp], sMask[warp], NB_SPARSE_TILES, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
+                        const int rest = nsp - NB_SPARSE_TILES * 32;
+                        int c0 = 0, c1 = 0;
+                        if (lane < rest) { c0 = sSlot[warp][NB_SPARSE_TILES * 32 + lane]; c1 = sMask[warp][NB_SPARSE_TILES * 32 + lane]; }
+                        __syncwarp();
+                        if (lane < rest) { sSlot[warp][lane] = c0; sMask[warp][lane] = c1; }
+                        nsp = rest;
                         __syncwarp();
                     }
                 }
@@ -189,13 +232,13 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
             const int nt = (nbuf + 31) >> 5;
             for (int k = nbuf + lane; k < nt * 32; k += 32) sBuf[warp][k] = -1;
             __syncwarp();
-            unsigned tileBase = 0, unit = 0;
-            if (lane == 0) { tileBase = atomicAdd(&counters->numTiles, (unsigned)nt); unit = atomicAdd(&counters->numUnits, 1u); }
-            tileBase = __shfl_sync(0xffffffffu, tileBase, 0); unit = __shfl_sync(0xffffffffu, unit, 0);
-            if (tileBase + nt <= tileCapacity && unit < unitCapacity) {
-                for (int k = lane; k < nt * 32; k += 32) jAtoms[(size_t)tileBase * 32 + k] = sBuf[warp][k];
-                if (lane == 0) units[unit] = make_int4(X, (int)tileBase, nt, 0);
-            } else if (lane == 0) counters->overflow = 1;
+            flushDense(X, sBuf[warp], nt, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
+        }
+        if (nsp > 0) {
+            const int nt = (nsp + 31) >> 5;
+            for (int k = nsp + lane; k < nt * 32; k += 32) { sSlot[warp][k] = -1; sMask[warp][k] = 0; }
+            __syncwarp();
+            flushSparse(X, sSlot[warp], sMask[warp], nt, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
         }
         __syncwarp();
     }
@@ -209,7 +252,7 @@ void b200_nblist_alloc(b200_ctx* c) {
     if (c->tileCapacity == 0) {
         c->tileCapacity = (long long)c->B * 28 + 1024;
     }
-    c->unitCapacity = c->B + c->tileCapacity / B200_UNIT_TILES + 64;
+    c->unitCapacity = 2 * (long long)c->B + c->tileCapacity / 4 + 64;
     dmalloc(c->units, (size_t)c->unitCapacity);
     dmalloc(c->jAtoms, (size_t)c->tileCapacity * 32);
 }
@@ -230,7 +273,7 @@ void b200_nblist_prepare(b200_ctx* c) {
     int rows = (c->B + c->partRanks - 1) / c->partRanks;
     int buildGrid = (rows + NB_WARPS - 1) / NB_WARPS;
     if (buildGrid > c->smCount * 16) buildGrid = c->smCount * 16;
-    nbBuild<<<buildGrid, NB_THREADS, 0, c->stream>>>(c->posq, c->N, c->B, c->numSuper, c->boxF, rcp * rcp,
+    nbBuild<<<buildGrid, NB_THREADS, 0, c->stream>>>(c->posq, c->N, c->B, c->numSuper, c->boxF, rcp * rcp, c->sparseMax,
         c->blockCenter, c->blockHalf, c->superCenter, c->superHalf, c->exclRowStart, c->exclRowCols,
         c->units, c->jAtoms, (unsigned)c->unitCapacity, (unsigned)c->tileCapacity, c->partRank, c->partRanks, c->counters);
     nbFinish<<<1, 1, 0, c->stream>>>(c->counters);

@@ -2,10 +2,13 @@
 //
 // Replaces computeNonbonded (platforms/cuda/src/kernels/nonbonded.cu:104-524) with the pair snippet
 // platforms/common/src/kernels/coulombLennardJones.cc:2-76.  Design differences (B200-first):
-//   * persistent CTAs, one warp per work unit taken from a device-side queue; a work unit is one block X
+//   * persistent CTAs, one warp per work unit taken from a device-side queue; a dense work unit is one block X
 //     plus up to 8 compacted 32-atom j tiles, so the i-force is flushed once per unit instead of once per tile;
 //   * j positions/parameters are staged in shared memory and read at a rotating index (conflict free),
 //     only the three j-force accumulators travel by warp shuffle (3 SHFL per pair step instead of 9);
+//   * j atoms that touch only a few atoms of X go to "sparse" units instead (the reference's singlePairs,
+//     nonbonded.cu:479-519): one lane per j atom walks the bits of its i-mask, so they cost a few pair evaluations
+//     instead of a 32-wide row each;
 //   * coordinates are re-expressed relative to the block centre once per tile ("single periodic copy" done
 //     per atom, nonbonded.cu:298-301,353-358), the per-pair minimum image is only used for small boxes;
 //   * erfc/exp are replaced by a rational function of r^2 (b200_ewald_coeffs.h);
@@ -37,20 +40,19 @@ struct TileArgs {
     float rc2, rcPadded, alpha2, alpha3, alpha, kcoul;
     double rc2d;
     float borderTol;             // |r2-rc2| below this -> FP64 decision
-    int exact;                   // use erfcf/expf instead of the rational fit (alpha*rc > 4)
     int periodic;
 };
 
 __device__ __forceinline__ float fast_rsqrt(float x) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float fast_rcp(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
-template <bool ENERGY>
+// s = -(dE/dr)/r, e = pair energy
+template <bool ENERGY, bool EXACT>
 __device__ __forceinline__ void pairTerms(const TileArgs& a, float r2, float qq, float sig, float eps, float& s, float& e) {
-    // s = -(dE/dr)/r, e = pair energy
     const float invR = fast_rsqrt(r2);
     const float invR2 = invR * invR;
     float sc, ec = 0.f;
-    if (!a.exact) {
+    if (!EXACT) {
         const float t = a.alpha2 * r2;
         float num = fmaf(F_N6, t, F_N5); num = fmaf(num, t, F_N4); num = fmaf(num, t, F_N3); num = fmaf(num, t, F_N2);
         num = fmaf(num, t, F_N1); num = fmaf(num, t, F_N0);
@@ -65,7 +67,7 @@ __device__ __forceinline__ void pairTerms(const TileArgs& a, float r2, float qq,
             vd = fmaf(vd, t, V_D1); vd = fmaf(vd, t, 1.0f);
             ec = qq * fmaf(-a.alpha, vn / vd, invR);
         }
-    } else {
+    } else {   // alpha*rc beyond the range of the fit: libm-quality erfc/exp
         const float r = r2 * invR;
         const float ar = a.alpha * r;
         const float erfcAR = erfcf(ar);
@@ -88,12 +90,68 @@ __device__ __forceinline__ bool borderlineInside(const TileArgs& a, int slotI, i
     return dx * dx + dy * dy + dz * dz <= a.rc2d;
 }
 
-template <bool FORCES, bool ENERGY, bool EMIT>
+template <bool EMIT>
+__device__ __forceinline__ void emitPair(const TileArgs& a, int slotI, int slotJ, unsigned long long& nPairs) {
+    if (!EMIT) return;
+    nPairs++;
+    if (a.pairOut) {
+        const unsigned long long slot = atomicAdd(&a.counters->pairCount, 1ull);
+        if ((long long)slot < a.pairCapacity) {
+            const int oi = a.atomIndex[slotI], oj = a.atomIndex[slotJ];
+            a.pairOut[slot] = make_int2(min(oi, oj), max(oi, oj));
+        }
+    }
+}
+
+struct WarpSmem {
+    float4 pos[32];
+    float2 par[32];
+    int idx[32];
+};
+
+// one dense 32x32 tile: lane owns atom i = lane of block X; at step k it meets j = (lane+k)&31
+template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT, bool SINGLE, bool EXCL>
+__device__ __forceinline__ void denseTile(const TileArgs& a, const WarpSmem& sm, int lane, int slotI, bool validI, float xi, float yi, float zi, float qik, float2 pri,
+                                          unsigned exclBits, float& fix, float& fiy, float& fiz, float& fjx, float& fjy, float& fjz, float& eTile, unsigned long long& nPairs) {
+#pragma unroll 4
+    for (int k = 0; k < 32; k++) {
+        const int jj = (lane + k) & 31;
+        const float4 q = sm.pos[jj];
+        const float2 pr = sm.par[jj];
+        float dx = q.x - xi, dy = q.y - yi, dz = q.z - zi;
+        bool ok = true;
+        if (!SINGLE) {
+            if (a.periodic) imageDelta(dx, dy, dz, a.box);
+            const int sj = sm.idx[jj];
+            ok = validI && sj >= 0 && sj < a.N;
+        }
+        const float r2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+        const float dcut = r2 - a.rc2;
+        bool in = dcut < 0.f;
+        if (fabsf(dcut) < a.borderTol) { if (ok) in = borderlineInside(a, slotI, sm.idx[jj]); }
+        if (EXCL) in = in && !((exclBits >> jj) & 1u);
+        if (!SINGLE) in = in && ok;
+        float s, e;
+        pairTerms<ENERGY, EXACT>(a, r2, qik * q.w, pri.x + pr.x, pri.y * pr.y, s, e);
+        s = in ? s : 0.f;
+        if (FORCES) {
+            fix = fmaf(-dx, s, fix); fiy = fmaf(-dy, s, fiy); fiz = fmaf(-dz, s, fiz);
+            fjx = fmaf(dx, s, fjx); fjy = fmaf(dy, s, fjy); fjz = fmaf(dz, s, fjz);
+            const int src = (lane + 1) & 31;
+            fjx = __shfl_sync(0xffffffffu, fjx, src);
+            fjy = __shfl_sync(0xffffffffu, fjy, src);
+            fjz = __shfl_sync(0xffffffffu, fjz, src);
+        }
+        if (ENERGY) eTile += in ? e : 0.f;
+        if (EMIT && in) emitPair<EMIT>(a, slotI, sm.idx[jj], nPairs);
+    }
+}
+
+template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT>
 __global__ void __launch_bounds__(TILE_THREADS, 3) tileKernel(const TileArgs a) {
-    __shared__ float4 sPos[TILE_WARPS][32];
-    __shared__ float2 sPar[TILE_WARPS][32];
-    __shared__ int sIdx[TILE_WARPS][32];
+    __shared__ WarpSmem smAll[TILE_WARPS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    WarpSmem& sm = smAll[warp];
     const unsigned numExclUnits = (unsigned)(a.exclEnd - a.exclBegin);
     const unsigned total = numExclUnits + a.counters->numUnits;
     long long eAcc = 0; unsigned long long nPairs = 0;
@@ -104,14 +162,14 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) tileKernel(const TileArgs a) 
     while (u < total) {
         unsigned uNext = 0;
         if (lane == 0) uNext = atomicAdd(&a.counters->workNext, 1u);   // fetch ahead: latency hidden by this unit's work
-        int x, tileStart, nTiles; bool excl = u < numExclUnits; int yBlock = 0; unsigned exclBits = 0;
+        int x, tileStart, nTiles, kind = 0; const bool excl = u < numExclUnits; int yBlock = 0; unsigned exclBits = 0;
         if (excl) {
             const int2 t = a.exclTiles[a.exclBegin + u];
             x = t.x; yBlock = t.y; tileStart = 0; nTiles = 1;
             exclBits = a.exclFlags[(size_t)(a.exclBegin + u) * 32 + lane];
         } else {
             const int4 w = a.units[u - numExclUnits];
-            x = w.x; tileStart = w.y; nTiles = w.z;
+            x = w.x; tileStart = w.y; nTiles = w.z; kind = w.w;
         }
         const int slotI = x * 32 + lane;
         const float4 pi = a.posq[slotI];
@@ -123,99 +181,111 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) tileKernel(const TileArgs a) 
             0.5f * a.box.ax - hX.x >= a.rcPadded && 0.5f * a.box.by - hX.y >= a.rcPadded && 0.5f * a.box.cz - hX.z >= a.rcPadded;
         const bool validI = slotI < a.N;
         float xi = pi.x, yi = pi.y, zi = pi.z;
-        if (single || !a.periodic) {
+        if (single) {
             xi -= cX.x; yi -= cX.y; zi -= cX.z;
-            if (single) imageDelta(xi, yi, zi, a.box);
+            imageDelta(xi, yi, zi, a.box);
             if (!validI) { xi = 3.0e4f; yi = 3.0e4f; zi = 3.0e4f; }
         }
         const float qik = a.kcoul * pi.w;
-        float fix = 0.f, fiy = 0.f, fiz = 0.f, eTile = 0.f;
 
-        // prefetch j data of the first tile
-        int ja = excl ? yBlock * 32 + lane : a.jAtoms[(size_t)tileStart * 32 + lane];
-        float4 pj = make_float4(0.f, 0.f, 0.f, 0.f); float2 prj = make_float2(0.f, 0.f);
-        if (ja >= 0) { pj = a.posq[ja]; prj = a.sigEps[ja]; }
-        for (int t = 0; t < nTiles; t++) {
-            const int jaCur = ja;
-            {   // stage tile t
-                float xj = pj.x, yj = pj.y, zj = pj.z;
-                if (single || !a.periodic) {
-                    xj -= cX.x; yj -= cX.y; zj -= cX.z;
-                    if (single) imageDelta(xj, yj, zj, a.box);
-                    if (jaCur < 0 || jaCur >= a.N) { xj = -3.0e4f; yj = -3.0e4f; zj = -3.0e4f; }
-                }
-                __syncwarp();
-                sPos[warp][lane] = make_float4(xj, yj, zj, pj.w);
-                sPar[warp][lane] = prj;
-                sIdx[warp][lane] = jaCur;
-                __syncwarp();
-            }
-            if (t + 1 < nTiles) {   // next tile's loads fly while this one is computed
-                ja = a.jAtoms[(size_t)(tileStart + t + 1) * 32 + lane];
-                pj = make_float4(0.f, 0.f, 0.f, 0.f); prj = make_float2(0.f, 0.f);
-                if (ja >= 0) { pj = a.posq[ja]; prj = a.sigEps[ja]; }
-            }
-            float fjx = 0.f, fjy = 0.f, fjz = 0.f;
-#pragma unroll 4
-            for (int k = 0; k < 32; k++) {
-                const int jj = (lane + k) & 31;
-                const float4 q = sPos[warp][jj];
-                const float2 pr = sPar[warp][jj];
-                float dx = q.x - xi, dy = q.y - yi, dz = q.z - zi;
-                bool ok = true;
-                if (!single && a.periodic) {
-                    imageDelta(dx, dy, dz, a.box);
-                    const int sj = sIdx[warp][jj];
-                    ok = validI && sj >= 0 && sj < a.N;
-                }
-                const float r2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-                const float dcut = r2 - a.rc2;
-                bool in = dcut < 0.f;
-                if (fabsf(dcut) < a.borderTol && ok) {
-                    const int sj = sIdx[warp][jj];
-                    if (sj >= 0 && sj < a.N && validI) in = borderlineInside(a, slotI, sj);
-                }
-                if (excl) in = in && !((exclBits >> jj) & 1u);
-                in = in && ok;
-                float s, e;
-                pairTerms<ENERGY>(a, r2, qik * q.w, pri.x + pr.x, pri.y * pr.y, s, e);
-                s = in ? s : 0.f;
-                if (FORCES) {
-                    fix = fmaf(-dx, s, fix); fiy = fmaf(-dy, s, fiy); fiz = fmaf(-dz, s, fiz);
-                    fjx = fmaf(dx, s, fjx); fjy = fmaf(dy, s, fjy); fjz = fmaf(dz, s, fjz);
-                    const int src = (lane + 1) & 31;
-                    fjx = __shfl_sync(0xffffffffu, fjx, src);
-                    fjy = __shfl_sync(0xffffffffu, fjy, src);
-                    fjz = __shfl_sync(0xffffffffu, fjz, src);
-                }
-                if (ENERGY) eTile += in ? e : 0.f;
-                if (EMIT && in) {
-                    nPairs++;
-                    if (a.pairOut) {
-                        const unsigned long long slot = atomicAdd(&a.counters->pairCount, 1ull);
-                        if ((long long)slot < a.pairCapacity) {
-                            const int oi = a.atomIndex[slotI], oj = a.atomIndex[sIdx[warp][jj]];
-                            a.pairOut[slot] = make_int2(min(oi, oj), max(oi, oj));
-                        }
+        if (kind == 0) {
+            // ---------------- dense unit (or one exclusion tile)
+            float fix = 0.f, fiy = 0.f, fiz = 0.f, eTile = 0.f;
+            int ja = excl ? yBlock * 32 + lane : a.jAtoms[(size_t)tileStart * 32 + lane];
+            float4 pj = make_float4(0.f, 0.f, 0.f, 0.f); float2 prj = make_float2(0.f, 0.f);
+            if (ja >= 0) { pj = a.posq[ja]; prj = a.sigEps[ja]; }
+            for (int t = 0; t < nTiles; t++) {
+                const int jaCur = ja;
+                {   // stage tile t
+                    float xj = pj.x, yj = pj.y, zj = pj.z;
+                    if (single) {
+                        xj -= cX.x; yj -= cX.y; zj -= cX.z;
+                        imageDelta(xj, yj, zj, a.box);
+                        if (jaCur < 0 || jaCur >= a.N) { xj = -3.0e4f; yj = -3.0e4f; zj = -3.0e4f; }
                     }
+                    __syncwarp();
+                    sm.pos[lane] = make_float4(xj, yj, zj, pj.w);
+                    sm.par[lane] = prj;
+                    sm.idx[lane] = jaCur;
+                    __syncwarp();
+                }
+                if (t + 1 < nTiles) {   // next tile's loads fly while this one is computed
+                    ja = a.jAtoms[(size_t)(tileStart + t + 1) * 32 + lane];
+                    pj = make_float4(0.f, 0.f, 0.f, 0.f); prj = make_float2(0.f, 0.f);
+                    if (ja >= 0) { pj = a.posq[ja]; prj = a.sigEps[ja]; }
+                }
+                float fjx = 0.f, fjy = 0.f, fjz = 0.f;
+                if (excl) {
+                    if (single) denseTile<FORCES, ENERGY, EMIT, EXACT, true, true>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
+                    else denseTile<FORCES, ENERGY, EMIT, EXACT, false, true>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
+                } else {
+                    if (single) denseTile<FORCES, ENERGY, EMIT, EXACT, true, false>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
+                    else denseTile<FORCES, ENERGY, EMIT, EXACT, false, false>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
+                }
+                if (FORCES && jaCur >= 0 && jaCur < a.N) {
+                    // after 32 rotations the accumulator for j = lane is back in this lane
+                    atomicAddFixed(&a.force[jaCur], toFixed(fjx));
+                    atomicAddFixed(&a.force[jaCur + a.Npad], toFixed(fjy));
+                    atomicAddFixed(&a.force[jaCur + 2 * a.Npad], toFixed(fjz));
+                }
+                if (ENERGY) {   // per-tile float sum, reduced in a fixed order, then integer accumulation
+                    const float es = warpSum(eTile);
+                    eAcc += toFixed(es);
+                    eTile = 0.f;
                 }
             }
-            if (FORCES && jaCur >= 0 && jaCur < a.N) {
-                // after 32 rotations the accumulator for j = lane is back in this lane
-                atomicAddFixed(&a.force[jaCur], toFixed(fjx));
-                atomicAddFixed(&a.force[jaCur + a.Npad], toFixed(fjy));
-                atomicAddFixed(&a.force[jaCur + 2 * a.Npad], toFixed(fjz));
+            if (FORCES && validI) {
+                atomicAddFixed(&a.force[slotI], toFixed(fix));
+                atomicAddFixed(&a.force[slotI + a.Npad], toFixed(fiy));
+                atomicAddFixed(&a.force[slotI + 2 * a.Npad], toFixed(fiz));
             }
-            if (ENERGY) {   // per-tile float sum, reduced in a fixed order, then integer accumulation
-                const float es = warpSum(eTile);
-                eAcc += toFixed(es);
-                eTile = 0.f;
+        } else {
+            // ---------------- sparse unit: block X in shared memory, one lane per j atom, loop over the bits of its i-mask
+            __syncwarp();
+            sm.pos[lane] = make_float4(xi, yi, zi, qik);
+            sm.par[lane] = pri;
+            __syncwarp();
+            for (int t = 0; t < nTiles; t++) {
+                const size_t base = (size_t)(tileStart + 2 * t) * 32;
+                const int ja = a.jAtoms[base + lane];
+                unsigned mask = ja >= 0 ? (unsigned)a.jAtoms[base + 32 + lane] : 0u;
+                float4 pj = make_float4(0.f, 0.f, 0.f, 0.f); float2 prj = make_float2(0.f, 0.f);
+                if (ja >= 0) { pj = a.posq[ja]; prj = a.sigEps[ja]; }
+                float xj = pj.x, yj = pj.y, zj = pj.z;
+                if (single) { xj -= cX.x; yj -= cX.y; zj -= cX.z; imageDelta(xj, yj, zj, a.box); }
+                float fjx = 0.f, fjy = 0.f, fjz = 0.f, eLane = 0.f;
+                while (mask) {
+                    const int i = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    const float4 p = sm.pos[i];
+                    const float2 pr = sm.par[i];
+                    float dx = xj - p.x, dy = yj - p.y, dz = zj - p.z;
+                    if (!single && a.periodic) imageDelta(dx, dy, dz, a.box);
+                    const float r2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+                    const float dcut = r2 - a.rc2;
+                    bool in = dcut < 0.f;
+                    if (fabsf(dcut) < a.borderTol) in = borderlineInside(a, x * 32 + i, ja);
+                    float s, e;
+                    pairTerms<ENERGY, EXACT>(a, r2, p.w * pj.w, pr.x + prj.x, pr.y * prj.y, s, e);
+                    s = in ? s : 0.f;
+                    if (FORCES && in) {
+                        const float gx = dx * s, gy = dy * s, gz = dz * s;
+                        fjx += gx; fjy += gy; fjz += gz;
+                        const int si = x * 32 + i;
+                        atomicAddFixed(&a.force[si], toFixed(-gx));
+                        atomicAddFixed(&a.force[si + a.Npad], toFixed(-gy));
+                        atomicAddFixed(&a.force[si + 2 * a.Npad], toFixed(-gz));
+                    }
+                    if (ENERGY && in) eLane += e;
+                    if (EMIT && in) emitPair<EMIT>(a, x * 32 + i, ja, nPairs);
+                }
+                if (FORCES && ja >= 0) {
+                    atomicAddFixed(&a.force[ja], toFixed(fjx));
+                    atomicAddFixed(&a.force[ja + a.Npad], toFixed(fjy));
+                    atomicAddFixed(&a.force[ja + 2 * a.Npad], toFixed(fjz));
+                }
+                if (ENERGY) eAcc += toFixed(warpSum(eLane));
             }
-        }
-        if (FORCES && validI) {
-            atomicAddFixed(&a.force[slotI], toFixed(fix));
-            atomicAddFixed(&a.force[slotI + a.Npad], toFixed(fiy));
-            atomicAddFixed(&a.force[slotI + 2 * a.Npad], toFixed(fiz));
         }
         u = __shfl_sync(0xffffffffu, uNext, 0);
     }
@@ -227,6 +297,15 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) tileKernel(const TileArgs a) 
 }
 
 __global__ void resetWorkQueue(DevCounters* c) { c->workNext = 0; }
+
+template <bool EXACT>
+static void launchTile(b200_ctx* c, const TileArgs& a, bool forces, bool energy, bool emitPairs) {
+    const int grid = c->smCount * 3;
+    if (emitPairs) tileKernel<false, false, true, EXACT><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    else if (forces && energy) tileKernel<true, true, false, EXACT><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    else if (forces) tileKernel<true, false, false, EXACT><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    else tileKernel<false, true, false, EXACT><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+}
 
 void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
     TileArgs a;
@@ -244,15 +323,11 @@ void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
     a.alpha = (float)al; a.alpha2 = (float)(al * al); a.alpha3 = (float)(al * al * al);
     a.kcoul = (float)B200_ONE_4PI_EPS0;
     a.borderTol = (float)(3e-5 * rc * rc);
-    a.exact = c->exactEwald ? 1 : 0;
     a.periodic = 1;
     resetWorkQueue<<<1, 1, 0, c->stream>>>(c->counters);
-    const int grid = c->smCount * 3;
     ScopedTimer tm(c, B200_T_TILE, c->stream);
-    if (emitPairs) tileKernel<false, false, true><<<grid, TILE_THREADS, 0, c->stream>>>(a);
-    else if (forces && energy) tileKernel<true, true, false><<<grid, TILE_THREADS, 0, c->stream>>>(a);
-    else if (forces) tileKernel<true, false, false><<<grid, TILE_THREADS, 0, c->stream>>>(a);
-    else tileKernel<false, true, false><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    if (c->exactEwald) launchTile<true>(c, a, forces, energy, emitPairs);
+    else launchTile<false>(c, a, forces, energy, emitPairs);
     LAUNCH_COUNT(c, 2);
     CUDA_CHECK(cudaGetLastError());
 }
