@@ -92,24 +92,22 @@ __device__ float2* fftLinesInSmem(float2* a, float2* b, const FFTPlan1D& plan, i
 }
 
 // z pass, forward: real (float or fixed point) lines -> nzc complex
-__global__ void __launch_bounds__(FFT_THREADS) fftZForward(const float* __restrict__ inReal, const long long* __restrict__ inFix, float2* __restrict__ out,
+__global__ void __launch_bounds__(FFT_THREADS) fftZForward(const float* __restrict__ inReal, const int* __restrict__ inFix, float fixScaleInv, float2* __restrict__ out,
                                                             int numLines, FFTPlan1D plan, int batch, int pitch, const float2* __restrict__ W) {
     extern __shared__ float2 smem[];
     const int n = plan.n, nzc = n / 2 + 1;
     float2* a = smem; float2* b = smem + (size_t)n * pitch;
     const int line0 = blockIdx.x * batch;
     const int nl = min(batch, numLines - line0);
-    const float fixScale = (float)(1.0 / B200_GRID_SCALE);
     for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
         const int l = idx / n, j = idx - l * n;
         float v = 0.f;
         if (l < nl) {
             const size_t g = (size_t)(line0 + l) * n + j;
-            v = inFix ? (float)((double)inFix[g] * (1.0 / B200_GRID_SCALE)) : inReal[g];
+            v = inFix ? (float)inFix[g] * fixScaleInv : inReal[g];
         }
         a[j * pitch + l] = make_float2(v, 0.f);
     }
-    (void)fixScale;
     float2* r = fftLinesInSmem<false>(a, b, plan, batch, pitch, W);
     for (int idx = threadIdx.x; idx < batch * nzc; idx += blockDim.x) {
         const int l = idx / nzc, j = idx - l * nzc;
@@ -171,13 +169,13 @@ template <typename K> static void allowSmem(K kernel, size_t bytes) {
     if (bytes > 48 * 1024) CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
 }
 
-void b200_fft3d_exec_r2c(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, const float* inReal, const long long* inFix, float2* out, float2*, cudaStream_t s) {
+void b200_fft3d_exec_r2c(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, const float* inReal, const int* inFix, float fixScaleInv, float2* out, float2*, cudaStream_t s) {
     const int nzc = nz / 2 + 1;
     int batch, pitch; size_t sm;
     pickBatch(nz, batch, pitch, sm);
     allowSmem(fftZForward, sm);
     const int lines = nx * ny;
-    fftZForward<<<(lines + batch - 1) / batch, FFT_THREADS, sm, s>>>(inReal, inFix, out, lines, plan[2], batch, pitch, tw[2]);
+    fftZForward<<<(lines + batch - 1) / batch, FFT_THREADS, sm, s>>>(inReal, inFix, fixScaleInv, out, lines, plan[2], batch, pitch, tw[2]);
     pickBatch(ny, batch, pitch, sm);
     allowSmem(fftStrided<false>, sm);
     fftStrided<false><<<dim3((nzc + batch - 1) / batch, nx), FFT_THREADS, sm, s>>>(out, nzc, (size_t)ny * nzc, (size_t)nzc, plan[1], batch, pitch, tw[1]);
@@ -206,11 +204,11 @@ void b200_fft3d_exec_c2r(int nx, int ny, int nz, const FFTPlan1D* plan, float2* 
 }
 
 void b200_fft3d_forward(b200_ctx* c, cudaStream_t s) {
-    b200_fft3d_exec_r2c(c->gridN[0], c->gridN[1], c->gridN[2], c->plan, c->twiddle, nullptr, c->gridFix, c->gridC, c->gridC2, s);
+    b200_fft3d_exec_r2c(c->gridN[0], c->gridN[1], c->gridN[2], c->plan, c->twiddle, nullptr, c->gridI, 1.0f / c->spreadScale, c->gridC, nullptr, s);
     LAUNCH_COUNT(c, 3);
 }
 void b200_fft3d_inverse(b200_ctx* c, cudaStream_t s) {
-    b200_fft3d_exec_c2r(c->gridN[0], c->gridN[1], c->gridN[2], c->plan, c->twiddle, c->gridC, c->gridC2, c->gridReal, s);
+    b200_fft3d_exec_c2r(c->gridN[0], c->gridN[1], c->gridN[2], c->plan, c->twiddle, c->gridC, nullptr, c->gridReal, s);
     LAUNCH_COUNT(c, 3);
 }
 
@@ -226,7 +224,7 @@ static int fftHost(int device, int nx, int ny, int nz, const float* in, float* o
         dmalloc(dReal, G); dmalloc(dC, GC);
         if (forward) {
             CUDA_CHECK(cudaMemcpy(dReal, in, sizeof(float) * G, cudaMemcpyHostToDevice));
-            b200_fft3d_exec_r2c(nx, ny, nz, plan, tw, dReal, nullptr, dC, nullptr, 0);
+            b200_fft3d_exec_r2c(nx, ny, nz, plan, tw, dReal, nullptr, 1.0f, dC, nullptr, 0);
             CUDA_CHECK(cudaDeviceSynchronize());
             CUDA_CHECK(cudaMemcpy(out, dC, sizeof(float2) * GC, cudaMemcpyDeviceToHost));
         } else {

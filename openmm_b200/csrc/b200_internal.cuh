@@ -138,9 +138,10 @@ struct b200_ctx {
 
     // PME
     int gridN[3] = {0, 0, 0}; int nzc = 0;
-    long long* gridFix = nullptr;   // spread target, fixed point
+    int* gridI = nullptr;           // charge grid (spread target), 32-bit fixed point
+    float spreadScale = 67108864.f; // fixed-point scale of the shared-memory accumulation in the spread kernel
     float* gridReal = nullptr;      // potential grid after the inverse transform
-    float2* gridC = nullptr; float2* gridC2 = nullptr;
+    float2* gridC = nullptr;        // half-complex spectrum, transformed in place
     float* moduli[3] = {nullptr, nullptr, nullptr};
     float2* twiddle[3] = {nullptr, nullptr, nullptr};
     FFTPlan1D plan[3];
@@ -199,9 +200,9 @@ void b200_comm_allreduce_forces(b200_ctx* c);
 void b200_comm_destroy(b200_ctx* c);
 void b200_fft_make_plan(int n, FFTPlan1D& plan);
 void b200_fft_make_twiddle(int n, float2*& dTw, cudaStream_t s);
-void b200_fft3d_forward(b200_ctx* c, cudaStream_t s);  // gridFix -> gridC
+void b200_fft3d_forward(b200_ctx* c, cudaStream_t s);  // gridI -> gridC
 void b200_fft3d_inverse(b200_ctx* c, cudaStream_t s);  // gridC -> gridReal
-void b200_fft3d_exec_r2c(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, const float* inReal, const long long* inFix, float2* out, float2* scratch, cudaStream_t s);
+void b200_fft3d_exec_r2c(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, const float* inReal, const int* inFix, float fixScaleInv, float2* out, float2* scratch, cudaStream_t s);
 void b200_fft3d_exec_c2r(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, float2* in, float2* scratch, float* out, cudaStream_t s);
 void b200_compute_impl(b200_ctx* c, unsigned groups, bool forces, bool energy, double* energyOut);
 

@@ -3,11 +3,14 @@
 // Replaces gridSpreadCharge / finishSpreadCharge / reciprocalConvolution / gridEvaluateEnergy / gridInterpolateForce
 // (platforms/common/src/kernels/pme.cc:23-356) and the set-up in CommonCalcNonbondedForceKernel::commonInitialize
 // (platforms/common/src/CommonCalcNonbondedForce.cpp:482-558, B-spline moduli).  The FFTs are in b200_fft.cu.
-// Differences: atoms are already in Hilbert order, so no per-step sort by grid cell is needed (pme.cc:1-21 +
-// CudaSort are dropped); charges are always accumulated in 64-bit fixed point so the result is bit-reproducible
-// (the reference's USE_FIXED_POINT_CHARGE_SPREADING, pme.cc:106-107); the fixed-point -> float conversion is
-// folded into the first FFT pass; the Coulomb constant is applied once, in the convolution.
+// Differences: atoms are kept in Hilbert order, so no per-step sort by grid cell is needed (findAtomGridIndex + CudaSort,
+// pme.cc:1-21, are dropped) and 128 consecutive atoms cover a compact box of grid points.  Spreading accumulates that box in
+// SHARED memory with 32-bit fixed-point atomics (integer sums: bit-reproducible like USE_FIXED_POINT_CHARGE_SPREADING,
+// pme.cc:106-107; scale 2^26/max(1,|q|max/1.5): 1.5e-8 e resolution, head-room |sum| < 32 per point) and adds it to the
+// global integer grid once; the int -> float conversion is folded into the first FFT pass.  Interpolation stages the same
+// box of potential values in shared memory.  The Coulomb constant is applied once, in the convolution.
 #include "b200_internal.cuh"
+#include <algorithm>
 #include <cmath>
 #include <vector>
 
@@ -55,29 +58,107 @@ __device__ __forceinline__ void gridCoords(const float4 p, const PmeArgs& a, int
     ix = ix >= a.nx ? ix - a.nx : ix; iy = iy >= a.ny ? iy - a.ny : iy; iz = iz >= a.nz ? iz - a.nz : iz;
 }
 
-__global__ void pmeSpread(const float4* __restrict__ posq, int N, PmeArgs a, long long* __restrict__ grid) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= N) return;
-    const float4 p = posq[i];
-    if (p.w == 0.f) return;
-    int ix, iy, iz; float ux, uy, uz;
+// ---- chunked spreading / interpolation.  One CTA takes 128 consecutive atoms.  Because atoms are kept in Hilbert order
+// their stencils cover a compact box of grid points; when that box fits the shared-memory tile the CTA accumulates all
+// 125 contributions per atom there (native 32-bit shared atomics) and then adds the box to the global grid with one
+// coalesced integer atomic per touched point.  Boxes that do not fit (rare: atoms that drifted far apart between two
+// re-sorts) fall back to direct global atomics.  All sums are integer, so the grid is bit-reproducible.
+#define CHUNK 128
+#define TILE_MAX 8192
+struct ChunkBox { int ref[3]; int lo[3]; int ext[3]; int vol; };
+
+// t -> (x, y, z) in a box of extents (., ey, ez) without integer division (exact for the small integers involved)
+__device__ __forceinline__ void unflatten(int t, int ey, int ez, float invEy, float invEz, int& x, int& y, int& z) {
+    const int r = (int)(((float)t + 0.5f) * invEz);
+    z = t - r * ez;
+    x = (int)(((float)r + 0.5f) * invEy);
+    y = r - x * ey;
+}
+__device__ __forceinline__ int wrapDiff(int d, int n) { d += n / 2; d %= n; if (d < 0) d += n; return d - n / 2; }
+__device__ __forceinline__ int wrapIdx(int i, int n) { i %= n; return i < 0 ? i + n : i; }
+
+// bounding box (in grid points, relative to the first atom's base index) of the stencils of the chunk's atoms
+__device__ __forceinline__ void chunkBox(bool valid, int ix, int iy, int iz, const PmeArgs& a, ChunkBox& box, int* sh /*[10]*/, int& dx, int& dy, int& dz) {
+    if (threadIdx.x == 0) { sh[0] = ix; sh[1] = iy; sh[2] = iz; sh[3] = sh[4] = sh[5] = 1 << 30; sh[6] = sh[7] = sh[8] = -(1 << 30); }
+    __syncthreads();
+    box.ref[0] = sh[0]; box.ref[1] = sh[1]; box.ref[2] = sh[2];
+    dx = wrapDiff(ix - box.ref[0], a.nx); dy = wrapDiff(iy - box.ref[1], a.ny); dz = wrapDiff(iz - box.ref[2], a.nz);
+    if (valid) {
+        atomicMin(&sh[3], dx); atomicMin(&sh[4], dy); atomicMin(&sh[5], dz);
+        atomicMax(&sh[6], dx); atomicMax(&sh[7], dy); atomicMax(&sh[8], dz);
+    }
+    __syncthreads();
+    for (int k = 0; k < 3; k++) { box.lo[k] = sh[3 + k]; box.ext[k] = sh[6 + k] - sh[3 + k] + PME_ORDER; }
+    const int n[3] = {a.nx, a.ny, a.nz};
+    bool fits = sh[6] >= sh[3];
+    for (int k = 0; k < 3; k++) fits = fits && box.ext[k] <= n[k];      // a box wider than the grid would alias onto itself
+    const long long vol = (long long)box.ext[0] * box.ext[1] * box.ext[2];
+    box.vol = (fits && vol <= TILE_MAX) ? (int)vol : 0;
+}
+
+// charge spreading (gridSpreadCharge, pme.cc:23-121)
+__global__ void __launch_bounds__(CHUNK) pmeSpreadChunks(const float4* __restrict__ posq, int N, PmeArgs a, int* __restrict__ grid, float fixScale) {
+    __shared__ int tile[TILE_MAX];
+    __shared__ int sh[10];
+    const int i = blockIdx.x * CHUNK + threadIdx.x;
+    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < N) p = posq[i];
+    int ix = 0, iy = 0, iz = 0; float ux = 0.f, uy = 0.f, uz = 0.f;
     gridCoords(p, a, ix, iy, iz, ux, uy, uz);
+    const bool valid = i < N && p.w != 0.f;
+    ChunkBox box; int dx, dy, dz;
+    chunkBox(valid, ix, iy, iz, a, box, sh, dx, dy, dz);
     float wx[5], wy[5], wz[5], d[5];
     bspline5(ux, wx, d); bspline5(uy, wy, d); bspline5(uz, wz, d);
-    int zi[5];
+    const float q = p.w * fixScale;
+    if (box.vol > 0) {
+        for (int t = threadIdx.x; t < box.vol; t += CHUNK) tile[t] = 0;
+        __syncthreads();
+        if (valid) {
+            const int ey = box.ext[1], ez = box.ext[2];
+            const int base = ((dx - box.lo[0]) * ey + (dy - box.lo[1])) * ez + (dz - box.lo[2]);
 #pragma unroll
-    for (int k = 0; k < 5; k++) { int z = iz + k; zi[k] = z >= a.nz ? z - a.nz : z; }
+            for (int jx = 0; jx < 5; jx++) {
+                const float vx = q * wx[jx];
 #pragma unroll
-    for (int jx = 0; jx < 5; jx++) {
-        int x = ix + jx; x = x >= a.nx ? x - a.nx : x;
-        const float qx = p.w * wx[jx];
+                for (int jy = 0; jy < 5; jy++) {
+                    const float vxy = vx * wy[jy];
+                    int* row = &tile[base + (jx * ey + jy) * ez];
 #pragma unroll
-        for (int jy = 0; jy < 5; jy++) {
-            int y = iy + jy; y = y >= a.ny ? y - a.ny : y;
-            const float qxy = qx * wy[jy];
-            long long* row = grid + ((size_t)x * a.ny + y) * a.nz;
+                    for (int jz = 0; jz < 5; jz++) atomicAdd(&row[jz], __float2int_rn(vxy * wz[jz]));
+                }
+            }
+        }
+        __syncthreads();
+        const int ey = box.ext[1], ez = box.ext[2];
+        const int ox = wrapIdx(box.ref[0] + box.lo[0], a.nx), oy = wrapIdx(box.ref[1] + box.lo[1], a.ny), oz = wrapIdx(box.ref[2] + box.lo[2], a.nz);
+        const float invEy = 1.0f / ey, invEz = 1.0f / ez;
+        for (int t = threadIdx.x; t < box.vol; t += CHUNK) {
+            const int v = tile[t];
+            if (v == 0) continue;
+            int x, y, z;
+            unflatten(t, ey, ez, invEy, invEz, x, y, z);
+            int gx = ox + x; gx += gx < 0 ? a.nx : 0; gx -= gx >= a.nx ? a.nx : 0;
+            int gy = oy + y; gy += gy < 0 ? a.ny : 0; gy -= gy >= a.ny ? a.ny : 0;
+            int gz = oz + z; gz += gz < 0 ? a.nz : 0; gz -= gz >= a.nz ? a.nz : 0;
+            atomicAdd(&grid[((size_t)gx * a.ny + gy) * a.nz + gz], v);
+        }
+    } else if (valid) {
+        int zi[5];
 #pragma unroll
-            for (int jz = 0; jz < 5; jz++) atomicAddFixed(&row[zi[jz]], (long long)((double)(qxy * wz[jz]) * B200_GRID_SCALE));
+        for (int k = 0; k < 5; k++) { int z = iz + k; zi[k] = z >= a.nz ? z - a.nz : z; }
+#pragma unroll
+        for (int jx = 0; jx < 5; jx++) {
+            int x = ix + jx; x = x >= a.nx ? x - a.nx : x;
+            const float vx = q * wx[jx];
+#pragma unroll
+            for (int jy = 0; jy < 5; jy++) {
+                int y = iy + jy; y = y >= a.ny ? y - a.ny : y;
+                const float vxy = vx * wy[jy];
+                int* row = grid + ((size_t)x * a.ny + y) * a.nz;
+#pragma unroll
+                for (int jz = 0; jz < 5; jz++) atomicAdd(&row[zi[jz]], __float2int_rn(vxy * wz[jz]));
+            }
         }
     }
 }
@@ -112,35 +193,72 @@ __global__ void pmeConvolve(float2* __restrict__ grid, PmeArgs a, const float* _
     }
 }
 
-// force interpolation (pme.cc:255-356)
-__global__ void pmeInterpolate(const float4* __restrict__ posq, int N, int Npad, PmeArgs a, const float* __restrict__ phi, long long* __restrict__ force) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= N) return;
-    const float4 p = posq[i];
-    if (p.w == 0.f) return;
-    int ix, iy, iz; float ux, uy, uz;
+// force interpolation (gridInterpolateForce, pme.cc:255-356): same chunking; the box of potential values the chunk's atoms
+// read is staged in shared memory once (coalesced), then every atom gathers its 125 values from there
+__global__ void __launch_bounds__(CHUNK) pmeInterpolateChunks(const float4* __restrict__ posq, int N, int Npad, PmeArgs a, const float* __restrict__ phi, long long* __restrict__ force) {
+    __shared__ float tile[TILE_MAX];
+    __shared__ int sh[10];
+    const int i = blockIdx.x * CHUNK + threadIdx.x;
+    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < N) p = posq[i];
+    int ix = 0, iy = 0, iz = 0; float ux = 0.f, uy = 0.f, uz = 0.f;
     gridCoords(p, a, ix, iy, iz, ux, uy, uz);
-    float wx[5], wy[5], wz[5], dx[5], dy[5], dz[5];
-    bspline5(ux, wx, dx); bspline5(uy, wy, dy); bspline5(uz, wz, dz);
-    int zi[5];
-#pragma unroll
-    for (int k = 0; k < 5; k++) { int z = iz + k; zi[k] = z >= a.nz ? z - a.nz : z; }
+    const bool valid = i < N && p.w != 0.f;
+    ChunkBox box; int dx, dy, dz;
+    chunkBox(valid, ix, iy, iz, a, box, sh, dx, dy, dz);
+    float wx[5], wy[5], wz[5], ex[5], ey5[5], ez5[5];
+    bspline5(ux, wx, ex); bspline5(uy, wy, ey5); bspline5(uz, wz, ez5);
     float gx = 0.f, gy = 0.f, gz = 0.f;
+    if (box.vol > 0) {
+        const int ey = box.ext[1], ez = box.ext[2];
+        const int ox = wrapIdx(box.ref[0] + box.lo[0], a.nx), oy = wrapIdx(box.ref[1] + box.lo[1], a.ny), oz = wrapIdx(box.ref[2] + box.lo[2], a.nz);
+        const float invEy = 1.0f / ey, invEz = 1.0f / ez;
+        for (int t = threadIdx.x; t < box.vol; t += CHUNK) {
+            int x, y, z;
+            unflatten(t, ey, ez, invEy, invEz, x, y, z);
+            int gx = ox + x; gx += gx < 0 ? a.nx : 0; gx -= gx >= a.nx ? a.nx : 0;
+            int gy = oy + y; gy += gy < 0 ? a.ny : 0; gy -= gy >= a.ny ? a.ny : 0;
+            int gz = oz + z; gz += gz < 0 ? a.nz : 0; gz -= gz >= a.nz ? a.nz : 0;
+            tile[t] = phi[((size_t)gx * a.ny + gy) * a.nz + gz];
+        }
+        __syncthreads();
+        if (valid) {
+            const int base = ((dx - box.lo[0]) * ey + (dy - box.lo[1])) * ez + (dz - box.lo[2]);
 #pragma unroll
-    for (int jx = 0; jx < 5; jx++) {
-        int x = ix + jx; x = x >= a.nx ? x - a.nx : x;
+            for (int jx = 0; jx < 5; jx++) {
 #pragma unroll
-        for (int jy = 0; jy < 5; jy++) {
-            int y = iy + jy; y = y >= a.ny ? y - a.ny : y;
-            const float* row = phi + ((size_t)x * a.ny + y) * a.nz;
-            float s0 = 0.f, s1 = 0.f;
+                for (int jy = 0; jy < 5; jy++) {
+                    const float* row = &tile[base + (jx * ey + jy) * ez];
+                    float s0 = 0.f, s1 = 0.f;
 #pragma unroll
-            for (int jz = 0; jz < 5; jz++) { const float v = row[zi[jz]]; s0 = fmaf(wz[jz], v, s0); s1 = fmaf(dz[jz], v, s1); }
-            gx = fmaf(dx[jx] * wy[jy], s0, gx);
-            gy = fmaf(wx[jx] * dy[jy], s0, gy);
-            gz = fmaf(wx[jx] * wy[jy], s1, gz);
+                    for (int jz = 0; jz < 5; jz++) { const float v = row[jz]; s0 = fmaf(wz[jz], v, s0); s1 = fmaf(ez5[jz], v, s1); }
+                    gx = fmaf(ex[jx] * wy[jy], s0, gx);
+                    gy = fmaf(wx[jx] * ey5[jy], s0, gy);
+                    gz = fmaf(wx[jx] * wy[jy], s1, gz);
+                }
+            }
+        }
+    } else if (valid) {
+        int zi[5];
+#pragma unroll
+        for (int k = 0; k < 5; k++) { int z = iz + k; zi[k] = z >= a.nz ? z - a.nz : z; }
+#pragma unroll
+        for (int jx = 0; jx < 5; jx++) {
+            int x = ix + jx; x = x >= a.nx ? x - a.nx : x;
+#pragma unroll
+            for (int jy = 0; jy < 5; jy++) {
+                int y = iy + jy; y = y >= a.ny ? y - a.ny : y;
+                const float* row = phi + ((size_t)x * a.ny + y) * a.nz;
+                float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+                for (int jz = 0; jz < 5; jz++) { const float v = row[zi[jz]]; s0 = fmaf(wz[jz], v, s0); s1 = fmaf(ez5[jz], v, s1); }
+                gx = fmaf(ex[jx] * wy[jy], s0, gx);
+                gy = fmaf(wx[jx] * ey5[jy], s0, gy);
+                gz = fmaf(wx[jx] * wy[jy], s1, gz);
+            }
         }
     }
+    if (!valid) return;
     const float q = p.w;
     const float tx = gx * a.nx, ty = gy * a.ny, tz = gz * a.nz;
     const float fx = -q * (tx * (float)a.r0x);
@@ -176,7 +294,13 @@ void b200_pme_create(b200_ctx* c) {
     const int nx = c->gridN[0], ny = c->gridN[1], nz = c->gridN[2];
     c->nzc = nz / 2 + 1;
     const size_t G = (size_t)nx * ny * nz, GC = (size_t)nx * ny * c->nzc;
-    dmalloc(c->gridFix, G); dmalloc(c->gridReal, G); dmalloc(c->gridC, GC); dmalloc(c->gridC2, GC);
+    dmalloc(c->gridI, G); dmalloc(c->gridReal, G); dmalloc(c->gridC, GC);
+    {
+        double maxQ = 0; for (double q : c->charge) maxQ = std::max(maxQ, std::fabs(q));
+        int bits = 26; double lim = 1.5;
+        while (maxQ > lim && bits > 12) { bits--; lim *= 2; }
+        c->spreadScale = (float)std::ldexp(1.0, bits);
+    }
     for (int k = 0; k < 3; k++) {
         const std::vector<float> m = splineModuli(c->gridN[k]);
         dmalloc(c->moduli[k], m.size());
@@ -187,7 +311,7 @@ void b200_pme_create(b200_ctx* c) {
 }
 
 void b200_pme_destroy(b200_ctx* c) {
-    dfree(c->gridFix); dfree(c->gridReal); dfree(c->gridC); dfree(c->gridC2);
+    dfree(c->gridI); dfree(c->gridReal); dfree(c->gridC);
     for (int k = 0; k < 3; k++) { dfree(c->moduli[k]); dfree(c->twiddle[k]); }
 }
 
@@ -202,10 +326,12 @@ void b200_pme_launch(b200_ctx* c, cudaStream_t s, bool forces, bool energy) {
     a.alphaFactor = (float)(M_PI * M_PI / (c->nb.ewald_alpha * c->nb.ewald_alpha));
     a.scale = (float)(B200_ONE_4PI_EPS0 / (M_PI * det));
     const size_t G = (size_t)a.nx * a.ny * a.nz;
+    const int chunks = (c->N + CHUNK - 1) / CHUNK;
     {
         ScopedTimer tm(c, B200_T_SPREAD, s);
-        CUDA_CHECK(cudaMemsetAsync(c->gridFix, 0, sizeof(long long) * G, s));
-        pmeSpread<<<(c->N + 127) / 128, 128, 0, s>>>(c->posq, c->N, a, c->gridFix);
+        CUDA_CHECK(cudaMemsetAsync(c->gridI, 0, sizeof(int) * G, s));
+        pmeSpreadChunks<<<chunks, CHUNK, 0, s>>>(c->posq, c->N, a, c->gridI, c->spreadScale);
+        LAUNCH_COUNT(c, 1);
     }
     { ScopedTimer tm(c, B200_T_FFT, s); b200_fft3d_forward(c, s); }
     {
@@ -218,7 +344,7 @@ void b200_pme_launch(b200_ctx* c, cudaStream_t s, bool forces, bool energy) {
     if (forces) {
         { ScopedTimer tm(c, B200_T_FFT, s); b200_fft3d_inverse(c, s); }
         ScopedTimer tm(c, B200_T_INTERPOLATE, s);
-        pmeInterpolate<<<(c->N + 127) / 128, 128, 0, s>>>(c->posq, c->N, c->Npad, a, c->gridReal, c->force);
+        pmeInterpolateChunks<<<chunks, CHUNK, 0, s>>>(c->posq, c->N, c->Npad, a, c->gridReal, c->force);
         LAUNCH_COUNT(c, 1);
     }
     CUDA_CHECK(cudaGetLastError());
