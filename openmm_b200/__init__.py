@@ -14,7 +14,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libb200nb.so")
+LIB_PATH = os.environ.get("B200_LIB_PATH", os.path.join(_HERE, "lib", "libb200nb.so"))   # override: kernel-variant sweeps
 PLUGIN_PATH = os.path.join(_HERE, "lib", "libOpenMMB200.so")
 
 NB_NOCUTOFF, NB_CUTOFF_NONPERIODIC, NB_CUTOFF_PERIODIC, NB_EWALD, NB_PME, NB_LJPME = range(6)

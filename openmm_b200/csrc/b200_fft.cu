@@ -8,6 +8,7 @@
 // fixed-point charge grid directly (folding finishSpreadCharge, pme.cc:125-133, into the FFT).
 #include "b200_internal.cuh"
 #include <cmath>
+#include <map>
 #include <vector>
 
 #define FFT_THREADS 256
@@ -157,6 +158,60 @@ __global__ void __launch_bounds__(FFT_THREADS) fftStrided(float2* __restrict__ d
     }
 }
 
+// x pass fused with the reciprocal convolution: forward FFT along x, multiply by the influence function (and sum the energy),
+// inverse FFT along x, all on lines held in shared memory.  Replaces one forward pass, reciprocalConvolution/gridEvaluateEnergy
+// (pme.cc:137-253) and one inverse pass: the spectrum makes one round trip through memory instead of three.
+template <bool ENERGY, bool INVERSE_TOO>
+__global__ void __launch_bounds__(FFT_THREADS) fftXConvolve(float2* __restrict__ data, int innerCount, size_t stride, FFTPlan1D plan, int batch, int pitch,
+                                                             const float2* __restrict__ W, PmeArgs a, const float* __restrict__ modX, const float* __restrict__ modY,
+                                                             const float* __restrict__ modZ, DevCounters* counters) {
+    extern __shared__ float2 smem[];
+    const int n = plan.n;
+    float2* bufA = smem; float2* bufB = smem + (size_t)n * pitch;
+    const int inner0 = blockIdx.x * batch;
+    const int nl = min(batch, innerCount - inner0);
+    float2* base = data + inner0;
+    for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
+        const int j = idx / batch, l = idx - j * batch;
+        bufA[j * pitch + l] = l < nl ? base[(size_t)j * stride + l] : make_float2(0.f, 0.f);
+    }
+    float2* r = fftLinesInSmem<false>(bufA, bufB, plan, batch, pitch, W);
+    float e = 0.f;
+    for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
+        const int kx = idx / batch, l = idx - kx * batch;
+        if (l >= nl) continue;
+        const int q = inner0 + l;
+        const int ky = q / a.nzc, kz = q - ky * a.nzc;
+        const int mx = kx < (a.nx + 1) / 2 ? kx : kx - a.nx, my = ky < (a.ny + 1) / 2 ? ky : ky - a.ny, mz = kz;   // kz <= nz/2
+        const float mhx = mx * (float)a.r0x, mhy = mx * (float)a.r1x + my * (float)a.r1y, mhz = mx * (float)a.r2x + my * (float)a.r2y + mz * (float)a.r2z;
+        const float m2 = mhx * mhx + mhy * mhy + mhz * mhz;
+        const float denom = m2 * modX[kx] * modY[ky] * modZ[kz];
+        float eterm = a.scale * __expf(-a.alphaFactor * m2) / denom;
+        if (kx == 0 && q == 0) eterm = 0.f;
+        const float2 g = r[kx * pitch + l];
+        if (ENERGY) {
+            const float wgt = (kz == 0 || (2 * kz == a.nz)) ? 1.f : 2.f;   // Hermitian mirror of the missing half
+            e += wgt * eterm * (g.x * g.x + g.y * g.y);
+        }
+        r[kx * pitch + l] = make_float2(g.x * eterm, g.y * eterm);
+    }
+    if (ENERGY) {
+        __shared__ float red[FFT_THREADS];
+        red[threadIdx.x] = e;
+        __syncthreads();
+        for (int o = FFT_THREADS / 2; o > 0; o >>= 1) { if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o]; __syncthreads(); }
+        if (threadIdx.x == 0) atomicAddFixed(&counters->energy[E_RECIP], toFixedD(0.5 * (double)red[0]));
+    }
+    if (INVERSE_TOO) {
+        float2* other = (r == bufA) ? bufB : bufA;
+        r = fftLinesInSmem<true>(r, other, plan, batch, pitch, W);
+    } else __syncthreads();
+    for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
+        const int j = idx / batch, l = idx - j * batch;
+        if (l < nl) base[(size_t)j * stride + l] = r[j * pitch + l];
+    }
+}
+
 static void pickBatch(int n, int& batch, int& pitch, size_t& smemBytes) {
     batch = 16;
     while (batch > 1 && (size_t)n * (batch + 1) * sizeof(float2) * 2 > 96 * 1024) batch >>= 1;
@@ -166,7 +221,12 @@ static void pickBatch(int n, int& batch, int& pitch, size_t& smemBytes) {
 }
 
 template <typename K> static void allowSmem(K kernel, size_t bytes) {
-    if (bytes > 48 * 1024) CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    // opt in to > 48 KB of dynamic shared memory once per kernel and device (the attribute call is not free)
+    static std::map<std::pair<const void*, int>, size_t> granted;
+    if (bytes <= 48 * 1024) return;
+    int dev = 0; cudaGetDevice(&dev);
+    size_t& cur = granted[{(const void*)kernel, dev}];
+    if (bytes > cur) { CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); cur = bytes; }
 }
 
 void b200_fft3d_exec_r2c(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, const float* inReal, const int* inFix, float fixScaleInv, float2* out, float2*, cudaStream_t s) {
@@ -301,4 +361,36 @@ extern "C" int b200_fft3d_c2r_noalloc(int32_t device, int32_t nx, int32_t ny, in
         CUDA_CHECK(cudaGetLastError());
     } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
     return B200_OK;
+}
+
+// whole reciprocal-space pipeline on the context's grids: int charge grid -> spectrum -> convolution (+energy) -> potential grid
+void b200_fft3d_reciprocal(b200_ctx* c, cudaStream_t s, const PmeArgs& a, bool energy, bool forces) {
+    const int nx = c->gridN[0], ny = c->gridN[1], nz = c->gridN[2], nzc = nz / 2 + 1;
+    int batch, pitch; size_t sm;
+    pickBatch(nz, batch, pitch, sm);
+    allowSmem(fftZForward, sm);
+    const int lines = nx * ny;
+    fftZForward<<<(lines + batch - 1) / batch, FFT_THREADS, sm, s>>>(nullptr, c->gridI, 1.0f / c->spreadScale, c->gridC, lines, c->plan[2], batch, pitch, c->twiddle[2]);
+    pickBatch(ny, batch, pitch, sm);
+    allowSmem(fftStrided<false>, sm);
+    fftStrided<false><<<dim3((nzc + batch - 1) / batch, nx), FFT_THREADS, sm, s>>>(c->gridC, nzc, (size_t)ny * nzc, (size_t)nzc, c->plan[1], batch, pitch, c->twiddle[1]);
+    pickBatch(nx, batch, pitch, sm);
+    const int inner = ny * nzc;
+    const dim3 grid((inner + batch - 1) / batch);
+#define LAUNCH_XCONV(E, I) do { allowSmem(fftXConvolve<E, I>, sm); fftXConvolve<E, I><<<grid, FFT_THREADS, sm, s>>>(c->gridC, inner, (size_t)ny * nzc, c->plan[0], batch, pitch, c->twiddle[0], a, c->moduli[0], c->moduli[1], c->moduli[2], c->counters); } while (0)
+    if (energy && forces) LAUNCH_XCONV(true, true);
+    else if (energy) LAUNCH_XCONV(true, false);
+    else LAUNCH_XCONV(false, true);
+#undef LAUNCH_XCONV
+    LAUNCH_COUNT(c, 3);
+    if (forces) {
+        pickBatch(ny, batch, pitch, sm);
+        allowSmem(fftStrided<true>, sm);
+        fftStrided<true><<<dim3((nzc + batch - 1) / batch, nx), FFT_THREADS, sm, s>>>(c->gridC, nzc, (size_t)ny * nzc, (size_t)nzc, c->plan[1], batch, pitch, c->twiddle[1]);
+        pickBatch(nz, batch, pitch, sm);
+        allowSmem(fftZInverse, sm);
+        fftZInverse<<<(lines + batch - 1) / batch, FFT_THREADS, sm, s>>>(c->gridC, c->gridReal, lines, c->plan[2], batch, pitch, c->twiddle[2]);
+        LAUNCH_COUNT(c, 2);
+    }
+    CUDA_CHECK(cudaGetLastError());
 }

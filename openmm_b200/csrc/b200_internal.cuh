@@ -55,6 +55,13 @@ struct DevCounters {
 #define E_BONDED 4
 #define E_KINETIC 5
 
+struct PmeArgs {
+    int nx, ny, nz, nzc;
+    double r0x, r1x, r1y, r2x, r2y, r2z;   // reciprocal box (rows as in CommonCalcNonbondedForce.cpp:950-957)
+    float alphaFactor;                      // pi^2/alpha^2
+    float scale;                            // ONE_4PI_EPS0/(pi V)
+};
+
 struct FFTPlan1D {
     int n;
     int nstages;
@@ -202,6 +209,7 @@ void b200_fft_make_plan(int n, FFTPlan1D& plan);
 void b200_fft_make_twiddle(int n, float2*& dTw, cudaStream_t s);
 void b200_fft3d_forward(b200_ctx* c, cudaStream_t s);  // gridI -> gridC
 void b200_fft3d_inverse(b200_ctx* c, cudaStream_t s);  // gridC -> gridReal
+void b200_fft3d_reciprocal(b200_ctx* c, cudaStream_t s, const PmeArgs& a, bool energy, bool forces);   // gridI -> (convolution, energy) -> gridReal
 void b200_fft3d_exec_r2c(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, const float* inReal, const int* inFix, float fixScaleInv, float2* out, float2* scratch, cudaStream_t s);
 void b200_fft3d_exec_c2r(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, float2* in, float2* scratch, float* out, cudaStream_t s);
 void b200_compute_impl(b200_ctx* c, unsigned groups, bool forces, bool energy, double* energyOut);

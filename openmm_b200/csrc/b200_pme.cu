@@ -16,12 +16,6 @@
 
 #define PME_ORDER 5
 
-struct PmeArgs {
-    int nx, ny, nz, nzc;
-    double r0x, r1x, r1y, r2x, r2y, r2z;   // reciprocal box (rows as in CommonCalcNonbondedForce.cpp:950-957)
-    float alphaFactor;                      // pi^2/alpha^2
-    float scale;                            // ONE_4PI_EPS0/(pi V)
-};
 
 // order-5 cardinal B-spline weights w[k] = M5(u+4-k) and derivatives, by raising the order from 1
 // (same functions as pme.cc:67-81,297-314 / ReferencePME.cpp:166-201)
@@ -163,35 +157,7 @@ __global__ void __launch_bounds__(CHUNK) pmeSpreadChunks(const float4* __restric
     }
 }
 
-// reciprocal convolution (pme.cc:137-189) with the energy sum (pme.cc:191-253) folded in
-template <bool ENERGY>
-__global__ void pmeConvolve(float2* __restrict__ grid, PmeArgs a, const float* __restrict__ modX, const float* __restrict__ modY, const float* __restrict__ modZ, DevCounters* counters) {
-    const size_t total = (size_t)a.nx * a.ny * a.nzc;
-    float e = 0.f;
-    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-        const int kz = (int)(idx % a.nzc); const size_t r = idx / a.nzc; const int ky = (int)(r % a.ny), kx = (int)(r / a.ny);
-        const int mx = kx < (a.nx + 1) / 2 ? kx : kx - a.nx, my = ky < (a.ny + 1) / 2 ? ky : ky - a.ny, mz = kz;   // kz <= nz/2
-        const float mhx = mx * (float)a.r0x, mhy = mx * (float)a.r1x + my * (float)a.r1y, mhz = mx * (float)a.r2x + my * (float)a.r2y + mz * (float)a.r2z;
-        const float m2 = mhx * mhx + mhy * mhy + mhz * mhz;
-        const float denom = m2 * modX[kx] * modY[ky] * modZ[kz];
-        float eterm = a.scale * __expf(-a.alphaFactor * m2) / denom;
-        if (idx == 0) eterm = 0.f;
-        const float2 g = grid[idx];
-        if (ENERGY) {
-            const float wgt = (kz == 0 || (2 * kz == a.nz)) ? 1.f : 2.f;   // Hermitian mirror of the missing half
-            e += wgt * eterm * (g.x * g.x + g.y * g.y);
-        }
-        grid[idx] = make_float2(g.x * eterm, g.y * eterm);
-    }
-    if (ENERGY) {
-        // fixed-order block reduction, then an integer atomic: bit-reproducible for a fixed launch shape
-        __shared__ float red[256];
-        red[threadIdx.x] = e;
-        __syncthreads();
-        for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o]; __syncthreads(); }
-        if (threadIdx.x == 0) atomicAddFixed(&counters->energy[E_RECIP], toFixedD(0.5 * (double)red[0]));
-    }
-}
+// (the reciprocal convolution and energy sum, pme.cc:137-253, are fused into the x pass of the FFT: fftXConvolve in b200_fft.cu)
 
 // force interpolation (gridInterpolateForce, pme.cc:255-356): same chunking; the box of potential values the chunk's atoms
 // read is staged in shared memory once (coalesced), then every atom gathers its 125 values from there
@@ -333,16 +299,8 @@ void b200_pme_launch(b200_ctx* c, cudaStream_t s, bool forces, bool energy) {
         pmeSpreadChunks<<<chunks, CHUNK, 0, s>>>(c->posq, c->N, a, c->gridI, c->spreadScale);
         LAUNCH_COUNT(c, 1);
     }
-    { ScopedTimer tm(c, B200_T_FFT, s); b200_fft3d_forward(c, s); }
-    {
-        ScopedTimer tm(c, B200_T_CONVOLVE, s);
-        const int grid = c->smCount * 8;
-        if (energy) pmeConvolve<true><<<grid, 256, 0, s>>>(c->gridC, a, c->moduli[0], c->moduli[1], c->moduli[2], c->counters);
-        else pmeConvolve<false><<<grid, 256, 0, s>>>(c->gridC, a, c->moduli[0], c->moduli[1], c->moduli[2], c->counters);
-    }
-    LAUNCH_COUNT(c, 2);
+    { ScopedTimer tm(c, B200_T_FFT, s); b200_fft3d_reciprocal(c, s, a, energy, forces); }
     if (forces) {
-        { ScopedTimer tm(c, B200_T_FFT, s); b200_fft3d_inverse(c, s); }
         ScopedTimer tm(c, B200_T_INTERPOLATE, s);
         pmeInterpolateChunks<<<chunks, CHUNK, 0, s>>>(c->posq, c->N, c->Npad, a, c->gridReal, c->force);
         LAUNCH_COUNT(c, 1);

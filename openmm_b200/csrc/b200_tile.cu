@@ -18,7 +18,17 @@
 #include "b200_internal.cuh"
 #include "b200_ewald_coeffs.h"
 
+#ifndef TILE_WARPS
 #define TILE_WARPS 8
+#endif
+#ifndef TILE_MIN_BLOCKS
+#define TILE_MIN_BLOCKS 3
+#endif
+#ifndef TILE_UNROLL
+#define TILE_UNROLL 16
+#endif
+#define TILE_STR2(x) #x
+#define TILE_STR(x) TILE_STR2(x)
 #define TILE_THREADS (TILE_WARPS * 32)
 
 struct TileArgs {
@@ -104,32 +114,85 @@ __device__ __forceinline__ void emitPair(const TileArgs& a, int slotI, int slotJ
 }
 
 struct WarpSmem {
-    float4 pos[32];
-    float2 par[32];
-    int idx[32];
+    float4 pos[64];   // j positions (+charge), stored twice so that index lane+k never wraps
+    float2 par[64];   // j (sigma/2, 2 sqrt(eps)), stored twice
+    int idx[32];      // j atom slots
+    // packed layout for the FFMA2 path: entry m pairs atom m with atom m^16; entries 32..47 repeat 0..15 so lane+k never wraps
+    float4 xy[48];    // (x_m, x_m', y_m, y_m')
+    float4 zq[48];    // (z_m, z_m', q_m, q_m')
+    float4 se[48];    // (s_m, s_m', e_m, e_m')
 };
 
-// one dense 32x32 tile: lane owns atom i = lane of block X; at step k it meets j = (lane+k)&31
+// ---- packed FP32 pairs (sm_100 FFMA2/FMUL2/FADD2: two FP32 operations per issue slot; the kernel is issue bound)
+__device__ __forceinline__ unsigned long long asU64(float2 v) { return *reinterpret_cast<unsigned long long*>(&v); }
+__device__ __forceinline__ float2 asF2(unsigned long long v) { return *reinterpret_cast<float2*>(&v); }
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { unsigned long long d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(asU64(a)), "l"(asU64(b)), "l"(asU64(c))); return asF2(d); }
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) { unsigned long long d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(asU64(a)), "l"(asU64(b))); return asF2(d); }
+__device__ __forceinline__ float2 add2(float2 a, float2 b) { unsigned long long d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(asU64(a)), "l"(asU64(b))); return asF2(d); }
+__device__ __forceinline__ float2 dup(float v) { return make_float2(v, v); }
+
+// Rare: a pair whose r^2 is within rounding distance of the cutoff was decided in float inside the tile loop; re-decide it in
+// FP64 and, if the decision changes, add or remove that single pair (kept out of line so the hot loop stays small).
+template <bool FORCES, bool ENERGY, bool EXACT, bool EXCL>
+__device__ __forceinline__ void fixBorderline(const TileArgs& a, const WarpSmem& sm, int lane, unsigned borderMask, unsigned exclRot, int slotI, bool validI,
+                                           float xi, float yi, float zi, float qik, float2 pri, float& fix, float& fiy, float& fiz, float& eTile) {
+    while (borderMask) {
+        const int k = __ffs(borderMask) - 1;
+        borderMask &= borderMask - 1;
+        if (EXCL && ((exclRot >> k) & 1u)) continue;
+        const int jj = (lane + k) & 31;
+        const int sj = sm.idx[jj];
+        if (!validI || sj < 0 || sj >= a.N) continue;
+        const float4 q = sm.pos[jj];
+        const float2 pr = sm.par[jj];
+        const float dx = q.x - xi, dy = q.y - yi, dz = q.z - zi;
+        const float r2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+        const bool inF = r2 < a.rc2, inD = borderlineInside(a, slotI, sj);
+        if (inF == inD) continue;
+        float s, e;
+        pairTerms<ENERGY, EXACT>(a, r2, qik * q.w, pri.x + pr.x, pri.y * pr.y, s, e);
+        const float sg = inD ? 1.f : -1.f;
+        if (FORCES) {
+            const float gx = sg * dx * s, gy = sg * dy * s, gz = sg * dz * s;
+            fix -= gx; fiy -= gy; fiz -= gz;
+            atomicAddFixed(&a.force[sj], toFixed(gx));
+            atomicAddFixed(&a.force[sj + a.Npad], toFixed(gy));
+            atomicAddFixed(&a.force[sj + 2 * a.Npad], toFixed(gz));
+        }
+        if (ENERGY) eTile += sg * e;
+    }
+}
+
+// one dense 32x32 tile: lane owns atom i = lane of block X; at step k it meets j = (lane+k)&31.
+// FIXUP: decide the cutoff in float inside the loop, remember borderline pairs in a bit mask and correct them afterwards
+// (single-copy force/energy variants); otherwise decide exactly inside the loop.
 template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT, bool SINGLE, bool EXCL>
 __device__ __forceinline__ void denseTile(const TileArgs& a, const WarpSmem& sm, int lane, int slotI, bool validI, float xi, float yi, float zi, float qik, float2 pri,
                                           unsigned exclBits, float& fix, float& fiy, float& fiz, float& fjx, float& fjy, float& fjz, float& eTile, unsigned long long& nPairs) {
-#pragma unroll 4
+    constexpr bool FIXUP = SINGLE && !EMIT;
+    const float4* __restrict__ pp = &sm.pos[lane];
+    const float2* __restrict__ pq = &sm.par[lane];
+    const unsigned exclRot = EXCL ? __funnelshift_r(exclBits, exclBits, lane) : 0u;   // bit k <-> j = (lane+k)&31
+    unsigned borderMask = 0;
+_Pragma(TILE_STR(unroll TILE_UNROLL))
     for (int k = 0; k < 32; k++) {
-        const int jj = (lane + k) & 31;
-        const float4 q = sm.pos[jj];
-        const float2 pr = sm.par[jj];
+        const float4 q = pp[k];
+        const float2 pr = pq[k];
         float dx = q.x - xi, dy = q.y - yi, dz = q.z - zi;
         bool ok = true;
         if (!SINGLE) {
             if (a.periodic) imageDelta(dx, dy, dz, a.box);
-            const int sj = sm.idx[jj];
+            const int sj = sm.idx[(lane + k) & 31];
             ok = validI && sj >= 0 && sj < a.N;
         }
         const float r2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-        const float dcut = r2 - a.rc2;
-        bool in = dcut < 0.f;
-        if (fabsf(dcut) < a.borderTol) { if (ok) in = borderlineInside(a, slotI, sm.idx[jj]); }
-        if (EXCL) in = in && !((exclBits >> jj) & 1u);
+        bool in = r2 < a.rc2;
+        if (FIXUP) {
+            if (fabsf(r2 - a.rc2) < a.borderTol) borderMask |= 1u << k;
+        } else {
+            if (fabsf(r2 - a.rc2) < a.borderTol) { if (ok) in = borderlineInside(a, slotI, sm.idx[(lane + k) & 31]); }
+        }
+        if (EXCL) in = in && !((exclRot >> k) & 1u);
         if (!SINGLE) in = in && ok;
         float s, e;
         pairTerms<ENERGY, EXACT>(a, r2, qik * q.w, pri.x + pr.x, pri.y * pr.y, s, e);
@@ -143,13 +206,117 @@ __device__ __forceinline__ void denseTile(const TileArgs& a, const WarpSmem& sm,
             fjz = __shfl_sync(0xffffffffu, fjz, src);
         }
         if (ENERGY) eTile += in ? e : 0.f;
-        if (EMIT && in) emitPair<EMIT>(a, slotI, sm.idx[jj], nPairs);
+        if (EMIT && in) emitPair<EMIT>(a, slotI, sm.idx[(lane + k) & 31], nPairs);
+    }
+    if (FIXUP) {
+        if (__any_sync(0xffffffffu, borderMask != 0u))
+            fixBorderline<FORCES, ENERGY, EXACT, EXCL>(a, sm, lane, borderMask, exclRot, slotI, validI, xi, yi, zi, qik, pri, fix, fiy, fiz, eTile);
     }
 }
 
+
+// Borderline fix-up for the packed path: only a flag is kept in the loop, so re-scan the lane's 32 pairs (rare).
+template <bool FORCES, bool ENERGY, bool EXCL>
+__device__ __forceinline__ void fixBorderlinePacked(const TileArgs& a, const WarpSmem& sm, int lane, unsigned exclRot, int slotI, bool validI,
+                                                    float xi, float yi, float zi, float qik, float2 pri, float2& gix, float2& giy, float2& giz, float& eTile) {
+    if (!validI) return;
+    for (int k = 0; k < 32; k++) {
+        const int m = (lane + k) & 31;
+        const float4 A = sm.xy[m], B = sm.zq[m], C = sm.se[m];
+        const float dx = A.x - xi, dy = A.z - yi, dz = B.x - zi;
+        const float r2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+        if (!(fabsf(r2 - a.rc2) < a.borderTol)) continue;
+        if (EXCL && ((exclRot >> k) & 1u)) continue;
+        const int sj = sm.idx[m];
+        if (sj < 0 || sj >= a.N) continue;
+        const bool inF = r2 < a.rc2, inD = borderlineInside(a, slotI, sj);
+        if (inF == inD) continue;
+        float s, e;
+        pairTerms<ENERGY, false>(a, r2, qik * B.z, pri.x + C.x, pri.y * C.z, s, e);
+        const float sg = inD ? 1.f : -1.f;
+        if (FORCES) {
+            const float gx = sg * dx * s, gy = sg * dy * s, gz = sg * dz * s;
+            gix.x += gx; giy.x += gy; giz.x += gz;
+            atomicAddFixed(&a.force[sj], toFixed(gx));
+            atomicAddFixed(&a.force[sj + a.Npad], toFixed(gy));
+            atomicAddFixed(&a.force[sj + 2 * a.Npad], toFixed(gz));
+        }
+        if (ENERGY) eTile += sg * e;
+    }
+}
+
+// Dense 32x32 tile, two pairs per lane and step: at step k lane l meets j = (l+k)&31 and j' = j^16, all pair arithmetic in
+// packed FP32x2.  gi* accumulate +d*s for atom i (the caller negates), fj*.x / fj*.y travel with j / j'.
+template <bool FORCES, bool ENERGY, bool EXCL>
+__device__ __forceinline__ void denseTilePacked(const TileArgs& a, const WarpSmem& sm, int lane, int slotI, bool validI, float xi, float yi, float zi, float qik, float2 pri,
+                                                unsigned exclBits, float2& gix, float2& giy, float2& giz, float& fjxOut, float& fjyOut, float& fjzOut, float& eTile) {
+    const float4* __restrict__ pxy = &sm.xy[lane];
+    const float4* __restrict__ pzq = &sm.zq[lane];
+    const float4* __restrict__ pse = &sm.se[lane];
+    const unsigned exclRot = EXCL ? __funnelshift_r(exclBits, exclBits, lane) : 0u;   // bit k <-> j = (lane+k)&31
+    const float2 nxi = dup(-xi), nyi = dup(-yi), nzi = dup(-zi), qi2 = dup(qik), si2 = dup(pri.x), ei2 = dup(pri.y);
+    const float2 al2 = dup(a.alpha2), nal3 = dup(-a.alpha3), nrc2 = dup(-a.rc2);
+    float2 fjx = dup(0.f), fjy = dup(0.f), fjz = dup(0.f), e2 = dup(0.f);
+    bool border = false;
+    const int src = (lane + 1) & 31;
+_Pragma(TILE_STR(unroll TILE_UNROLL))
+    for (int k = 0; k < 16; k++) {
+        const float4 A = pxy[k], B = pzq[k], C = pse[k];
+        const float2 dx = add2(make_float2(A.x, A.y), nxi), dy = add2(make_float2(A.z, A.w), nyi), dz = add2(make_float2(B.x, B.y), nzi);
+        const float2 r2 = fma2(dx, dx, fma2(dy, dy, mul2(dz, dz)));
+        const float2 dcut = add2(r2, nrc2);
+        bool in0 = dcut.x < 0.f, in1 = dcut.y < 0.f;
+        border = border || (fabsf(dcut.x) < a.borderTol) || (fabsf(dcut.y) < a.borderTol);
+        if (EXCL) { in0 = in0 && !((exclRot >> k) & 1u); in1 = in1 && !((exclRot >> (k + 16)) & 1u); }
+        const float2 invR = make_float2(fast_rsqrt(r2.x), fast_rsqrt(r2.y));
+        const float2 invR2 = mul2(invR, invR);
+        const float2 t = mul2(al2, r2);
+        float2 num = fma2(dup(F_N6), t, dup(F_N5)); num = fma2(num, t, dup(F_N4)); num = fma2(num, t, dup(F_N3)); num = fma2(num, t, dup(F_N2));
+        num = fma2(num, t, dup(F_N1)); num = fma2(num, t, dup(F_N0));
+        float2 den = fma2(dup(F_D5), t, dup(F_D4)); den = fma2(den, t, dup(F_D3)); den = fma2(den, t, dup(F_D2)); den = fma2(den, t, dup(F_D1));
+        den = fma2(den, t, dup(1.0f));
+        const float2 Fz = mul2(num, make_float2(fast_rcp(den.x), fast_rcp(den.y)));
+        const float2 qq = mul2(qi2, make_float2(B.z, B.w));
+        const float2 sc = mul2(qq, fma2(nal3, Fz, mul2(invR, invR2)));
+        const float2 sig = add2(si2, make_float2(C.x, C.y));
+        const float2 sr2 = mul2(mul2(sig, sig), invR2);
+        const float2 sr6 = mul2(mul2(sr2, sr2), sr2);
+        const float2 es6 = mul2(mul2(ei2, make_float2(C.z, C.w)), sr6);
+        float2 s = fma2(mul2(es6, invR2), fma2(dup(12.0f), sr6, dup(-6.0f)), sc);
+        s.x = in0 ? s.x : 0.f; s.y = in1 ? s.y : 0.f;
+        if (ENERGY) {
+            float2 vn = fma2(dup(V_N6), t, dup(V_N5)); vn = fma2(vn, t, dup(V_N4)); vn = fma2(vn, t, dup(V_N3)); vn = fma2(vn, t, dup(V_N2));
+            vn = fma2(vn, t, dup(V_N1)); vn = fma2(vn, t, dup(V_N0));
+            float2 vd = fma2(dup(V_D6), t, dup(V_D5)); vd = fma2(vd, t, dup(V_D4)); vd = fma2(vd, t, dup(V_D3)); vd = fma2(vd, t, dup(V_D2));
+            vd = fma2(vd, t, dup(V_D1)); vd = fma2(vd, t, dup(1.0f));
+            const float2 ec = mul2(qq, fma2(dup(-a.alpha), make_float2(vn.x / vd.x, vn.y / vd.y), invR));
+            float2 e = fma2(es6, add2(sr6, dup(-1.0f)), ec);
+            e.x = in0 ? e.x : 0.f; e.y = in1 ? e.y : 0.f;
+            e2 = add2(e2, e);
+        }
+        if (FORCES) {
+            gix = fma2(dx, s, gix); giy = fma2(dy, s, giy); giz = fma2(dz, s, giz);
+            fjx = fma2(dx, s, fjx); fjy = fma2(dy, s, fjy); fjz = fma2(dz, s, fjz);
+            fjx.x = __shfl_sync(0xffffffffu, fjx.x, src); fjx.y = __shfl_sync(0xffffffffu, fjx.y, src);
+            fjy.x = __shfl_sync(0xffffffffu, fjy.x, src); fjy.y = __shfl_sync(0xffffffffu, fjy.y, src);
+            fjz.x = __shfl_sync(0xffffffffu, fjz.x, src); fjz.y = __shfl_sync(0xffffffffu, fjz.y, src);
+        }
+    }
+    if (ENERGY) eTile += e2.x + e2.y;
+    if (FORCES) {
+        // after 16 rotations the .y chain (j' = j^16) is home in lane j'; the .x chain sits 16 lanes away
+        fjxOut = fjx.y + __shfl_xor_sync(0xffffffffu, fjx.x, 16);
+        fjyOut = fjy.y + __shfl_xor_sync(0xffffffffu, fjy.x, 16);
+        fjzOut = fjz.y + __shfl_xor_sync(0xffffffffu, fjz.x, 16);
+    }
+    if (__any_sync(0xffffffffu, border))
+        fixBorderlinePacked<FORCES, ENERGY, EXCL>(a, sm, lane, exclRot, slotI, validI, xi, yi, zi, qik, pri, gix, giy, giz, eTile);
+}
+
 template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT>
-__global__ void __launch_bounds__(TILE_THREADS, 3) tileKernel(const TileArgs a) {
+__global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(const TileArgs a) {
     __shared__ WarpSmem smAll[TILE_WARPS];
+    constexpr bool PACKED = !EMIT && !EXACT;   // FFMA2 path for the single-periodic-copy force/energy variants
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem& sm = smAll[warp];
     const unsigned numExclUnits = (unsigned)(a.exclEnd - a.exclBegin);
@@ -191,6 +358,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) tileKernel(const TileArgs a) 
         if (kind == 0) {
             // ---------------- dense unit (or one exclusion tile)
             float fix = 0.f, fiy = 0.f, fiz = 0.f, eTile = 0.f;
+            float2 gix = dup(0.f), giy = dup(0.f), giz = dup(0.f);   // packed path: +sum of d*s for atom i (two partial sums)
             int ja = excl ? yBlock * 32 + lane : a.jAtoms[(size_t)tileStart * 32 + lane];
             float4 pj = make_float4(0.f, 0.f, 0.f, 0.f); float2 prj = make_float2(0.f, 0.f);
             if (ja >= 0) { pj = a.posq[ja]; prj = a.sigEps[ja]; }
@@ -204,8 +372,16 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) tileKernel(const TileArgs a) 
                         if (jaCur < 0 || jaCur >= a.N) { xj = -3.0e4f; yj = -3.0e4f; zj = -3.0e4f; }
                     }
                     __syncwarp();
-                    sm.pos[lane] = make_float4(xj, yj, zj, pj.w);
-                    sm.par[lane] = prj;
+                    if (PACKED && single) {
+                        const float xo = __shfl_xor_sync(0xffffffffu, xj, 16), yo = __shfl_xor_sync(0xffffffffu, yj, 16), zo = __shfl_xor_sync(0xffffffffu, zj, 16);
+                        const float qo = __shfl_xor_sync(0xffffffffu, pj.w, 16), so = __shfl_xor_sync(0xffffffffu, prj.x, 16), eo = __shfl_xor_sync(0xffffffffu, prj.y, 16);
+                        const float4 A = make_float4(xj, xo, yj, yo), B = make_float4(zj, zo, pj.w, qo), C = make_float4(prj.x, so, prj.y, eo);
+                        sm.xy[lane] = A; sm.zq[lane] = B; sm.se[lane] = C;
+                        if (lane < 16) { sm.xy[lane + 32] = A; sm.zq[lane + 32] = B; sm.se[lane + 32] = C; }
+                    } else {
+                        sm.pos[lane] = sm.pos[lane + 32] = make_float4(xj, yj, zj, pj.w);
+                        sm.par[lane] = sm.par[lane + 32] = prj;
+                    }
                     sm.idx[lane] = jaCur;
                     __syncwarp();
                 }
@@ -215,7 +391,10 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) tileKernel(const TileArgs a) 
                     if (ja >= 0) { pj = a.posq[ja]; prj = a.sigEps[ja]; }
                 }
                 float fjx = 0.f, fjy = 0.f, fjz = 0.f;
-                if (excl) {
+                if (PACKED && single) {
+                    if (excl) denseTilePacked<FORCES, ENERGY, true>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, gix, giy, giz, fjx, fjy, fjz, eTile);
+                    else denseTilePacked<FORCES, ENERGY, false>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, gix, giy, giz, fjx, fjy, fjz, eTile);
+                } else if (excl) {
                     if (single) denseTile<FORCES, ENERGY, EMIT, EXACT, true, true>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
                     else denseTile<FORCES, ENERGY, EMIT, EXACT, false, true>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
                 } else {
@@ -234,6 +413,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) tileKernel(const TileArgs a) 
                     eTile = 0.f;
                 }
             }
+            if (PACKED) { fix -= gix.x + gix.y; fiy -= giy.x + giy.y; fiz -= giz.x + giz.y; }
             if (FORCES && validI) {
                 atomicAddFixed(&a.force[slotI], toFixed(fix));
                 atomicAddFixed(&a.force[slotI + a.Npad], toFixed(fiy));
@@ -300,7 +480,7 @@ __global__ void resetWorkQueue(DevCounters* c) { c->workNext = 0; }
 
 template <bool EXACT>
 static void launchTile(b200_ctx* c, const TileArgs& a, bool forces, bool energy, bool emitPairs) {
-    const int grid = c->smCount * 3;
+    const int grid = c->smCount * TILE_MIN_BLOCKS;
     if (emitPairs) tileKernel<false, false, true, EXACT><<<grid, TILE_THREADS, 0, c->stream>>>(a);
     else if (forces && energy) tileKernel<true, true, false, EXACT><<<grid, TILE_THREADS, 0, c->stream>>>(a);
     else if (forces) tileKernel<true, false, false, EXACT><<<grid, TILE_THREADS, 0, c->stream>>>(a);
