@@ -32,17 +32,22 @@ __device__ __forceinline__ float2 cmul(float2 a, float2 b) { return make_float2(
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
 
-// One Stockham stage over `batch` lines held as buf[j*pitch + l].  W = exp(-2 pi i k/n) table (conjugated for inverse).
+// One Stockham stage over `batch` (a power of two) lines held as buf[j*pitch + l].  W = exp(-2 pi i k/n) table (conjugated
+// for the inverse).  Odd radices use the conjugate symmetry of the roots: with a_t = x_t + x_{R-t}, b_t = x_t - x_{R-t},
+//   y_q = x_0 + sum_t (a_t cos_qt + i b_t sin_qt),   y_{R-q} = x_0 + sum_t (a_t cos_qt - i b_t sin_qt),  t = 1..(R-1)/2
+// which needs about a quarter of the multiplications of the plain R x R product.
 template <bool INVERSE, int R>
 __device__ __forceinline__ void fftStage(const float2* __restrict__ in, float2* __restrict__ out, int n, int Ns, int batch, int pitch, const float2* __restrict__ W) {
     const int nOverR = n / R;
     const int twStep = n / (Ns * R);
+    const int logB = __ffs(batch) - 1;
+    const float invNs = 1.0f / (float)Ns;
     float2 root[R];   // exp(-+2 pi i m/R)
 #pragma unroll
     for (int m = 0; m < R; m++) { root[m] = W[m * nOverR]; if (INVERSE) root[m].y = -root[m].y; }
-    for (int idx = threadIdx.x; idx < batch * nOverR; idx += blockDim.x) {
-        const int l = idx % batch, j = idx / batch;
-        const int k = j % Ns;
+    for (int idx = threadIdx.x; idx < (nOverR << logB); idx += blockDim.x) {
+        const int l = idx & (batch - 1), j = idx >> logB;
+        const int k = j - (int)(((float)j + 0.5f) * invNs) * Ns;   // j % Ns without an integer division (exact for j < 2^22)
         const int j0 = (j - k) * R + k;
         float2 x[R];
 #pragma unroll
@@ -62,12 +67,23 @@ __device__ __forceinline__ void fftStage(const float2* __restrict__ in, float2* 
             out[(j0 + 2 * Ns) * pitch + l] = csub(a, c);
             out[(j0 + 3 * Ns) * pitch + l] = csub(b, di);
         } else {
+            constexpr int H = (R - 1) / 2;
+            float2 sa[H + 1], sb[H + 1];
+            float2 y0 = x[0];
 #pragma unroll
-            for (int q = 0; q < R; q++) {
-                float2 acc = x[0];
+            for (int t = 1; t <= H; t++) { sa[t] = cadd(x[t], x[R - t]); sb[t] = csub(x[t], x[R - t]); y0 = cadd(y0, sa[t]); }
+            out[j0 * pitch + l] = y0;
 #pragma unroll
-                for (int t = 1; t < R; t++) acc = cadd(acc, cmul(x[t], root[(q * t) % R]));
-                out[(j0 + q * Ns) * pitch + l] = acc;
+            for (int q = 1; q <= H; q++) {
+                float2 C = x[0], D = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int t = 1; t <= H; t++) {
+                    const float2 w = root[(q * t) % R];
+                    C.x = fmaf(sa[t].x, w.x, C.x); C.y = fmaf(sa[t].y, w.x, C.y);
+                    D.x = fmaf(sb[t].x, w.y, D.x); D.y = fmaf(sb[t].y, w.y, D.y);
+                }
+                out[(j0 + q * Ns) * pitch + l] = make_float2(C.x - D.y, C.y + D.x);          // C + i D
+                out[(j0 + (R - q) * Ns) * pitch + l] = make_float2(C.x + D.y, C.y - D.x);    // C - i D
             }
         }
     }
@@ -100,8 +116,9 @@ __global__ void __launch_bounds__(FFT_THREADS) fftZForward(const float* __restri
     float2* a = smem; float2* b = smem + (size_t)n * pitch;
     const int line0 = blockIdx.x * batch;
     const int nl = min(batch, numLines - line0);
+    const float invN = 1.0f / (float)n, invNzc = 1.0f / (float)nzc;
     for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
-        const int l = idx / n, j = idx - l * n;
+        const int l = (int)(((float)idx + 0.5f) * invN), j = idx - l * n;
         float v = 0.f;
         if (l < nl) {
             const size_t g = (size_t)(line0 + l) * n + j;
@@ -111,7 +128,7 @@ __global__ void __launch_bounds__(FFT_THREADS) fftZForward(const float* __restri
     }
     float2* r = fftLinesInSmem<false>(a, b, plan, batch, pitch, W);
     for (int idx = threadIdx.x; idx < batch * nzc; idx += blockDim.x) {
-        const int l = idx / nzc, j = idx - l * nzc;
+        const int l = (int)(((float)idx + 0.5f) * invNzc), j = idx - l * nzc;
         if (l < nl) out[(size_t)(line0 + l) * nzc + j] = r[j * pitch + l];
     }
 }
@@ -123,8 +140,9 @@ __global__ void __launch_bounds__(FFT_THREADS) fftZInverse(const float2* __restr
     float2* a = smem; float2* b = smem + (size_t)n * pitch;
     const int line0 = blockIdx.x * batch;
     const int nl = min(batch, numLines - line0);
+    const float invN = 1.0f / (float)n, invNzc = 1.0f / (float)nzc;
     for (int idx = threadIdx.x; idx < batch * nzc; idx += blockDim.x) {
-        const int l = idx / nzc, j = idx - l * nzc;
+        const int l = (int)(((float)idx + 0.5f) * invNzc), j = idx - l * nzc;
         float2 v = make_float2(0.f, 0.f);
         if (l < nl) v = in[(size_t)(line0 + l) * nzc + j];
         a[j * pitch + l] = v;
@@ -132,7 +150,7 @@ __global__ void __launch_bounds__(FFT_THREADS) fftZInverse(const float2* __restr
     }
     float2* r = fftLinesInSmem<true>(a, b, plan, batch, pitch, W);
     for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
-        const int l = idx / n, j = idx - l * n;
+        const int l = (int)(((float)idx + 0.5f) * invN), j = idx - l * n;
         if (l < nl) out[(size_t)(line0 + l) * n + j] = r[j * pitch + l].x;
     }
 }
@@ -143,17 +161,18 @@ __global__ void __launch_bounds__(FFT_THREADS) fftStrided(float2* __restrict__ d
                                                            FFTPlan1D plan, int batch, int pitch, const float2* __restrict__ W) {
     extern __shared__ float2 smem[];
     const int n = plan.n;
+    const int logB = __ffs(batch) - 1;
     float2* a = smem; float2* b = smem + (size_t)n * pitch;
     const int inner0 = blockIdx.x * batch;
     const int nl = min(batch, innerCount - inner0);
     float2* base = data + (size_t)blockIdx.y * outerStride + inner0;
     for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
-        const int j = idx / batch, l = idx - j * batch;
+        const int j = idx >> logB, l = idx & (batch - 1);
         a[j * pitch + l] = l < nl ? base[(size_t)j * stride + l] : make_float2(0.f, 0.f);
     }
     float2* r = fftLinesInSmem<INVERSE>(a, b, plan, batch, pitch, W);
     for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
-        const int j = idx / batch, l = idx - j * batch;
+        const int j = idx >> logB, l = idx & (batch - 1);
         if (l < nl) base[(size_t)j * stride + l] = r[j * pitch + l];
     }
 }
@@ -167,18 +186,19 @@ __global__ void __launch_bounds__(FFT_THREADS) fftXConvolve(float2* __restrict__
                                                              const float* __restrict__ modZ, DevCounters* counters) {
     extern __shared__ float2 smem[];
     const int n = plan.n;
+    const int logB = __ffs(batch) - 1;
     float2* bufA = smem; float2* bufB = smem + (size_t)n * pitch;
     const int inner0 = blockIdx.x * batch;
     const int nl = min(batch, innerCount - inner0);
     float2* base = data + inner0;
     for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
-        const int j = idx / batch, l = idx - j * batch;
+        const int j = idx >> logB, l = idx & (batch - 1);
         bufA[j * pitch + l] = l < nl ? base[(size_t)j * stride + l] : make_float2(0.f, 0.f);
     }
     float2* r = fftLinesInSmem<false>(bufA, bufB, plan, batch, pitch, W);
     float e = 0.f;
     for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
-        const int kx = idx / batch, l = idx - kx * batch;
+        const int kx = idx >> logB, l = idx & (batch - 1);
         if (l >= nl) continue;
         const int q = inner0 + l;
         const int ky = q / a.nzc, kz = q - ky * a.nzc;
@@ -207,7 +227,7 @@ __global__ void __launch_bounds__(FFT_THREADS) fftXConvolve(float2* __restrict__
         r = fftLinesInSmem<true>(r, other, plan, batch, pitch, W);
     } else __syncthreads();
     for (int idx = threadIdx.x; idx < batch * n; idx += blockDim.x) {
-        const int j = idx / batch, l = idx - j * batch;
+        const int j = idx >> logB, l = idx & (batch - 1);
         if (l < nl) base[(size_t)j * stride + l] = r[j * pitch + l];
     }
 }

@@ -120,6 +120,57 @@ __device__ __forceinline__ void flushSparse(int X, int* slots, int* masks, int n
     } else if (lane == 0) counters->overflow = 1;
 }
 
+// exact test of up to 32 queued candidate atoms (one per lane) against the 32 atoms of block X, then classification
+struct NbWarpBufs { int* dense; int* slots; int* masks; };
+__device__ __forceinline__ void nbProcessCandidates(int X, int lane, unsigned ltMask, bool have, int slot, float rx, float ry, float rz, const float4* sXw, bool single,
+                                                    const BoxF& box, float rcp2, int sparseMax, NbWarpBufs w, int& nbuf, int& nsp,
+                                                    int4* units, int* jAtoms, unsigned unitCapacity, unsigned tileCapacity, DevCounters* counters) {
+    unsigned imask = 0;
+    if (single) {
+#pragma unroll 8
+        for (int i = 0; i < 32; i++) {
+            const float4 a = sXw[i];
+            const float dx = rx - a.x, dy = ry - a.y, dz = rz - a.z;
+            imask |= (dx * dx + dy * dy + dz * dz < rcp2 ? 1u : 0u) << i;
+        }
+    } else {
+        for (int i = 0; i < 32; i++) {
+            const float4 a = sXw[i];
+            float dx = rx - a.x, dy = ry - a.y, dz = rz - a.z;
+            imageDelta(dx, dy, dz, box);
+            imask |= (dx * dx + dy * dy + dz * dz < rcp2 ? 1u : 0u) << i;
+        }
+    }
+    if (!have) imask = 0;
+    const int cnt = __popc(imask);
+    const bool dense = cnt > sparseMax, sparse = cnt > 0 && !dense;
+    const unsigned mD = __ballot_sync(0xffffffffu, dense), mS = __ballot_sync(0xffffffffu, sparse);
+    if (dense) w.dense[nbuf + __popc(mD & ltMask)] = slot;
+    if (sparse) { const int k = nsp + __popc(mS & ltMask); w.slots[k] = slot; w.masks[k] = (int)imask; }
+    nbuf += __popc(mD); nsp += __popc(mS);
+    __syncwarp();
+    if (nbuf >= B200_UNIT_TILES * 32) {   // flush one full dense work unit
+        flushDense(X, w.dense, B200_UNIT_TILES, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
+        const int rest = nbuf - B200_UNIT_TILES * 32;
+        int carry = 0;
+        if (lane < rest) carry = w.dense[B200_UNIT_TILES * 32 + lane];
+        __syncwarp();
+        if (lane < rest) w.dense[lane] = carry;
+        nbuf = rest;
+        __syncwarp();
+    }
+    if (nsp >= NB_SPARSE_TILES * 32) {   // flush one full sparse work unit
+        flushSparse(X, w.slots, w.masks, NB_SPARSE_TILES, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
+        const int rest = nsp - NB_SPARSE_TILES * 32;
+        int c0 = 0, c1 = 0;
+        if (lane < rest) { c0 = w.slots[NB_SPARSE_TILES * 32 + lane]; c1 = w.masks[NB_SPARSE_TILES * 32 + lane]; }
+        __syncwarp();
+        if (lane < rest) { w.slots[lane] = c0; w.masks[lane] = c1; }
+        nsp = rest;
+        __syncwarp();
+    }
+}
+
 __global__ void __launch_bounds__(NB_THREADS) nbBuild(
         const float4* __restrict__ posq, int N, int B, int numSuper, BoxF box, float rcp2, int sparseMax,
         const float4* __restrict__ blockCenter, const float4* __restrict__ blockHalf,
@@ -129,6 +180,7 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
         int partRank, int partRanks, DevCounters* counters) {
     if (!counters->rebuild) return;
     __shared__ float4 sX[NB_WARPS][32];
+    __shared__ float4 sQ[NB_WARPS][64];     // queue of candidate atoms that passed the box test: (rel. position, slot)
     __shared__ int sBuf[NB_WARPS][NB_BUF];
     __shared__ int sSlot[NB_WARPS][NB_SBUF];
     __shared__ int sMask[NB_WARPS][NB_SBUF];
@@ -136,6 +188,7 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
     const int warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const unsigned ltMask = (1u << lane) - 1u;
     const float rcp = sqrtf(rcp2);
+    NbWarpBufs wb = {sBuf[warp], sSlot[warp], sMask[warp]};
     // rows are dealt round-robin to ranks: every rank gets a statistically identical share of the sweep
     for (int xi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; xi * partRanks + partRank < B; xi += warpsPerGrid) {
         const int X = xi * partRanks + partRank;
@@ -152,7 +205,7 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
             __syncwarp();
         }
         const int exBegin = exclRowStart[X], exEnd = exclRowStart[X + 1];
-        int nbuf = 0, nsp = 0;
+        int nbuf = 0, nsp = 0, nq = 0;
         for (int s0 = (X >> 5) & ~31; s0 < numSuper; s0 += 32) {   // candidates Y > X live in super blocks >= X/32
             const int s = s0 + lane;
             bool sHit = false;
@@ -170,7 +223,6 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
                 while (bMask) {
                     const int Yb = sb * 32 + __ffs(bMask) - 1; bMask &= bMask - 1;
                     const int slot = Yb * 32 + lane;
-                    unsigned imask = 0;
                     bool cand = false;
                     float rx = 0.f, ry = 0.f, rz = 0.f;
                     if (slot < N) {
@@ -180,53 +232,30 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
                         const float gx = fmaxf(0.f, fabsf(rx) - hX.x), gy = fmaxf(0.f, fabsf(ry) - hX.y), gz = fmaxf(0.f, fabsf(rz) - hX.z);
                         cand = gx * gx + gy * gy + gz * gz < rcp2;
                     }
-                    if (__any_sync(0xffffffffu, cand)) {
-                        if (single) {
-#pragma unroll 8
-                            for (int i = 0; i < 32; i++) {
-                                const float4 a = sX[warp][i];
-                                const float dx = rx - a.x, dy = ry - a.y, dz = rz - a.z;
-                                imask |= (dx * dx + dy * dy + dz * dz < rcp2 ? 1u : 0u) << i;
-                            }
-                        } else {
-                            for (int i = 0; i < 32; i++) {
-                                const float4 a = sX[warp][i];
-                                float dx = rx - a.x, dy = ry - a.y, dz = rz - a.z;
-                                imageDelta(dx, dy, dz, box);
-                                imask |= (dx * dx + dy * dy + dz * dz < rcp2 ? 1u : 0u) << i;
-                            }
-                        }
-                        if (!cand) imask = 0;
-                    }
-                    const int cnt = __popc(imask);
-                    const bool dense = cnt > sparseMax, sparse = cnt > 0 && !dense;
-                    const unsigned mD = __ballot_sync(0xffffffffu, dense), mS = __ballot_sync(0xffffffffu, sparse);
-                    if (dense) sBuf[warp][nbuf + __popc(mD & ltMask)] = slot;
-                    if (sparse) { const int k = nsp + __popc(mS & ltMask); sSlot[warp][k] = slot; sMask[warp][k] = (int)imask; }
-                    nbuf += __popc(mD); nsp += __popc(mS);
+                    // queue the atoms that can reach X's box; the expensive per-atom test runs on full warps of them
+                    const unsigned mC = __ballot_sync(0xffffffffu, cand);
+                    if (cand) sQ[warp][nq + __popc(mC & ltMask)] = make_float4(rx, ry, rz, __int_as_float(slot));
+                    nq += __popc(mC);
                     __syncwarp();
-                    if (nbuf >= B200_UNIT_TILES * 32) {   // flush one full dense work unit
-                        flushDense(X, sBuf[warp], B200_UNIT_TILES, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
-                        const int rest = nbuf - B200_UNIT_TILES * 32;
-                        int carry = 0;
-                        if (lane < rest) carry = sBuf[warp][B200_UNIT_TILES * 32 + lane];
+                    if (nq >= 32) {
+                        const float4 q = sQ[warp][lane];
+                        nbProcessCandidates(X, lane, ltMask, true, __float_as_int(q.w), q.x, q.y, q.z, sX[warp], single, box, rcp2, sparseMax, wb, nbuf, nsp,
+                                            units, jAtoms, unitCapacity, tileCapacity, counters);
+                        const int rest = nq - 32;
+                        float4 carry = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (lane < rest) carry = sQ[warp][32 + lane];
                         __syncwarp();
-                        if (lane < rest) sBuf[warp][lane] = carry;
-                        nbuf = rest;
-                        __syncwarp();
-                    }
-                    if (nsp >= NB_SPARSE_TILES * 32) {   // flush one full sparse work unit
-                        flushSparse(X, sSlot[warp], sMask[warp], NB_SPARSE_TILES, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
-                        const int rest = nsp - NB_SPARSE_TILES * 32;
-                        int c0 = 0, c1 = 0;
-                        if (lane < rest) { c0 = sSlot[warp][NB_SPARSE_TILES * 32 + lane]; c1 = sMask[warp][NB_SPARSE_TILES * 32 + lane]; }
-                        __syncwarp();
-                        if (lane < rest) { sSlot[warp][lane] = c0; sMask[warp][lane] = c1; }
-                        nsp = rest;
+                        if (lane < rest) sQ[warp][lane] = carry;
+                        nq = rest;
                         __syncwarp();
                     }
                 }
             }
+        }
+        if (nq > 0) {
+            const float4 q = lane < nq ? sQ[warp][lane] : make_float4(0.f, 0.f, 0.f, 0.f);
+            nbProcessCandidates(X, lane, ltMask, lane < nq, __float_as_int(q.w), q.x, q.y, q.z, sX[warp], single, box, rcp2, sparseMax, wb, nbuf, nsp,
+                                units, jAtoms, unitCapacity, tileCapacity, counters);
         }
         if (nbuf > 0) {
             const int nt = (nbuf + 31) >> 5;
