@@ -201,8 +201,10 @@ class Context:
         assert a.size == 3 * self.n
         _check(self.lib.b200_set_positions(self.handle, p))
 
-    def get_positions(self, enforce_periodic=False):
-        out = np.empty(3 * self.n)
+    def get_positions(self, enforce_periodic=False, out=None):
+        if out is None:
+            out = np.empty((self.n, 3))
+        assert out.dtype == np.float64 and out.size == 3 * self.n and out.flags.c_contiguous
         _check(self.lib.b200_get_positions(self.handle, out.ctypes.data_as(c_double_p), 1 if enforce_periodic else 0))
         return out.reshape(-1, 3)
 

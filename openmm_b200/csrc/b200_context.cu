@@ -124,7 +124,8 @@ extern "C" void b200_context_destroy(b200_ctx* c) {
     dfree(c->sortKeys); dfree(c->sortCount); dfree(c->sortStart); dfree(c->sortOrder);
     for (auto& g : c->groups) dfree(g.dBase);
     if (c->countersHost) cudaFreeHost(c->countersHost);
-    if (c->stageA) { cudaFreeHost(c->stageA); cudaFreeHost(c->stageB); cudaFreeHost(c->stageOff); }
+    if (c->hStage) cudaFreeHost(c->hStage);
+    dfree(c->dStage);
     for (auto& t : c->timers) for (auto& p : t.pending) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     cudaEventDestroy(c->evFork); cudaEventDestroy(c->evPmeDone);
     cudaStreamDestroy(c->stream); cudaStreamDestroy(c->pmeStream);
@@ -156,7 +157,7 @@ extern "C" int b200_nonbonded_create(b200_ctx* c, const b200_nonbonded_desc* d) 
     c->hasNonbonded = true;
     // list cutoff = cutoff + padding (CudaNonbondedUtilities.cpp:380-383 uses 8% of the cutoff)
     const char* padEnv = getenv("B200_NB_PADDING");
-    const double padFrac = padEnv ? atof(padEnv) : 0.10;
+    const double padFrac = padEnv ? atof(padEnv) : 0.08;
     c->padding = padFrac * d->cutoff;
     c->paddedCutoff = d->cutoff + c->padding;
     c->exactEwald = d->ewald_alpha * d->cutoff > 3.95;
@@ -170,6 +171,13 @@ extern "C" int b200_nonbonded_create(b200_ctx* c, const b200_nonbonded_desc* d) 
         sumQ += c->charge[i]; sumQ2 += c->charge[i] * c->charge[i];
     }
     CUDA_CHECK(cudaMemcpyAsync(c->sigEps, se.data(), sizeof(float2) * c->Npad, cudaMemcpyHostToDevice, c->stream));
+    {   // posq.w = q; the device order is still the creation order here (no reorder before the first computation)
+        std::vector<float4> p(c->Npad, make_float4(0.f, 0.f, 0.f, 0.f));
+        d2h(p.data(), c->posq, c->Npad, c->stream);
+        CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        for (int i = 0; i < c->N; i++) p[i].w = (float)c->charge[i];
+        CUDA_CHECK(cudaMemcpyAsync(c->posq, p.data(), sizeof(float4) * c->Npad, cudaMemcpyHostToDevice, c->stream));
+    }
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
     c->totalCharge = sumQ;
     // Ewald self energy (CommonCalcNonbondedForce.cpp:397-400)
@@ -439,32 +447,96 @@ void b200_sync_host_order(b200_ctx* c) {
 }
 
 
+// ---- state I/O.  The permutation between the caller's particle order and the device order, the float/correction split of
+// mixed precision and the fixed-point -> double conversion all run on the GPU; the host only moves contiguous double arrays
+// (through a pinned staging buffer filled by a few threads, so both the memcpy and the PCIe copy run near full speed).
+#include <thread>
 static void ensureStaging(b200_ctx* c) {
-    if (c->stageA) return;
-    CUDA_CHECK(cudaMallocHost((void**)&c->stageA, sizeof(float4) * c->Npad));
-    CUDA_CHECK(cudaMallocHost((void**)&c->stageB, sizeof(float4) * c->Npad));
-    CUDA_CHECK(cudaMallocHost((void**)&c->stageOff, sizeof(int4) * c->Npad));
-    memset(c->stageA, 0, sizeof(float4) * c->Npad); memset(c->stageB, 0, sizeof(float4) * c->Npad);
+    if (c->hStage) return;
+    CUDA_CHECK(cudaMallocHost((void**)&c->hStage, sizeof(double) * 3 * (size_t)c->Npad));
+    dmalloc(c->dStage, 3 * (size_t)c->Npad);
+}
+static void parallelCopy(void* dst, const void* src, size_t bytes) {
+    const int nt = bytes > (4u << 20) ? 6 : 1;
+    if (nt == 1) { memcpy(dst, src, bytes); return; }
+    std::vector<std::thread> th;
+    const size_t chunk = (bytes / nt + 63) & ~(size_t)63;
+    for (int t = 0; t < nt; t++) {
+        const size_t off = (size_t)t * chunk;
+        if (off >= bytes) break;
+        const size_t len = std::min(chunk, bytes - off);
+        th.emplace_back([=] { memcpy((char*)dst + off, (const char*)src + off, len); });
+    }
+    for (auto& x : th) x.join();
+}
+static void stageIn(b200_ctx* c, const double* xyz) {
+    ensureStaging(c);
+    parallelCopy(c->hStage, xyz, sizeof(double) * 3 * (size_t)c->N);
+    CUDA_CHECK(cudaMemcpyAsync(c->dStage, c->hStage, sizeof(double) * 3 * (size_t)c->N, cudaMemcpyHostToDevice, c->stream));
+}
+static void stageOut(b200_ctx* c, double* xyz) {
+    CUDA_CHECK(cudaMemcpyAsync(c->hStage, c->dStage, sizeof(double) * 3 * (size_t)c->N, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    parallelCopy(xyz, c->hStage, sizeof(double) * 3 * (size_t)c->N);
+}
+
+// CommonKernels.cpp:182-227: float cast + correction in the device order, cell offsets reset
+__global__ void ioSetPositions(const double* __restrict__ stage, const int* __restrict__ atomIndex, int N, float4* posq, float4* posqCorr, int4* cellOffsets) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= N) return;
+    const int o = atomIndex[s];
+    const double x = stage[3 * (size_t)o], y = stage[3 * (size_t)o + 1], z = stage[3 * (size_t)o + 2];
+    const float w = posq[s].w;   // the charge belongs to the slot (identical molecules are exchanged), not to the moving particle
+    posq[s] = make_float4((float)x, (float)y, (float)z, w);
+    posqCorr[s] = make_float4((float)(x - (double)(float)x), (float)(y - (double)(float)y), (float)(z - (double)(float)z), 0.f);
+    cellOffsets[s] = make_int4(0, 0, 0, 0);
+}
+// CommonKernels.cpp:95-177: positions in the caller's order, optionally with the periodic wrapping undone
+__global__ void ioGetPositions(double* __restrict__ stage, const int* __restrict__ atomIndex, int N, const float4* __restrict__ posq, const float4* __restrict__ posqCorr,
+                               const int4* __restrict__ cellOffsets, BoxD box, int unwrap) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= N) return;
+    const int o = atomIndex[s];
+    const float4 p = posq[s], q = posqCorr[s];
+    double x = (double)p.x + q.x, y = (double)p.y + q.y, z = (double)p.z + q.z;
+    if (unwrap) {
+        const int4 off = cellOffsets[s];
+        x += off.x * box.ax + off.y * box.bx + off.z * box.cx;
+        y += off.y * box.by + off.z * box.cy;
+        z += off.z * box.cz;
+    }
+    stage[3 * (size_t)o] = x; stage[3 * (size_t)o + 1] = y; stage[3 * (size_t)o + 2] = z;
+}
+__global__ void ioSetVelocities(const double* __restrict__ stage, const int* __restrict__ atomIndex, int N, double4* velm) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= N) return;
+    const int o = atomIndex[s];
+    double4 v = velm[s];
+    v.x = stage[3 * (size_t)o]; v.y = stage[3 * (size_t)o + 1]; v.z = stage[3 * (size_t)o + 2];
+    velm[s] = v;
+}
+__global__ void ioGetVelocities(double* __restrict__ stage, const int* __restrict__ atomIndex, int N, const double4* __restrict__ velm) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= N) return;
+    const int o = atomIndex[s];
+    const double4 v = velm[s];
+    stage[3 * (size_t)o] = v.x; stage[3 * (size_t)o + 1] = v.y; stage[3 * (size_t)o + 2] = v.z;
+}
+// CommonKernels.cpp:286-297
+__global__ void ioGetForces(double* __restrict__ stage, const int* __restrict__ atomIndex, int N, int Npad, const long long* __restrict__ force) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= N) return;
+    const int o = atomIndex[s];
+    const double sc = 1.0 / B200_FORCE_SCALE;
+    stage[3 * (size_t)o] = sc * (double)force[s]; stage[3 * (size_t)o + 1] = sc * (double)force[s + Npad]; stage[3 * (size_t)o + 2] = sc * (double)force[s + 2 * (size_t)Npad];
 }
 
 extern "C" int b200_set_positions(b200_ctx* c, const double* xyz) {
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
-    b200_sync_host_order(c);
-    ensureStaging(c);
-    // CommonKernels.cpp:182-227: float cast + correction in the device order, cell offsets reset.  The data goes through
-    // pinned staging buffers so the copy runs at full PCIe speed.
-    float4* p = c->stageA; float4* q = c->stageB;
-    const bool hasQ = c->hasNonbonded;
-    for (int s = 0; s < c->N; s++) {
-        const int o = c->hostAtomIndex[s];
-        const double x = xyz[3 * o], y = xyz[3 * o + 1], z = xyz[3 * o + 2];
-        p[s] = make_float4((float)x, (float)y, (float)z, hasQ ? (float)c->charge[o] : 0.f);
-        q[s] = make_float4((float)(x - (double)(float)x), (float)(y - (double)(float)y), (float)(z - (double)(float)z), 0.f);
-    }
-    CUDA_CHECK(cudaMemcpyAsync(c->posq, p, sizeof(float4) * c->Npad, cudaMemcpyHostToDevice, c->stream));
-    CUDA_CHECK(cudaMemcpyAsync(c->posqCorr, q, sizeof(float4) * c->Npad, cudaMemcpyHostToDevice, c->stream));
-    CUDA_CHECK(cudaMemsetAsync(c->cellOffsets, 0, sizeof(int4) * c->Npad, c->stream));
+    stageIn(c, xyz);
+    ioSetPositions<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->posq, c->posqCorr, c->cellOffsets);
+    LAUNCH_COUNT(c, 1);
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
     c->forcesValid = false;
     // Like ComputeContext::reorderAtoms the spatial sort is periodic, not forced by every setPositions: the displacement
@@ -477,36 +549,19 @@ extern "C" int b200_set_positions(b200_ctx* c, const double* xyz) {
 extern "C" int b200_get_positions(b200_ctx* c, double* xyz, int32_t enforcePeriodic) {
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
-    b200_sync_host_order(c);
     ensureStaging(c);
-    float4* p = c->stageA; float4* q = c->stageB; int4* off = c->stageOff;
-    d2h(p, c->posq, c->Npad, c->stream); d2h(q, c->posqCorr, c->Npad, c->stream);
-    if (!enforcePeriodic) d2h(off, c->cellOffsets, c->Npad, c->stream);
-    CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    const double* b = c->boxHost;
-    for (int s = 0; s < c->N; s++) {
-        const int o = c->hostAtomIndex[s];
-        double x = (double)p[s].x + q[s].x, y = (double)p[s].y + q[s].y, z = (double)p[s].z + q[s].z;
-        if (!enforcePeriodic) {   // undo the wrapping (CommonKernels.cpp:151-177)
-            x += off[s].x * b[0] + off[s].y * b[3] + off[s].z * b[6];
-            y += off[s].y * b[4] + off[s].z * b[7];
-            z += off[s].z * b[8];
-        }
-        xyz[3 * o] = x; xyz[3 * o + 1] = y; xyz[3 * o + 2] = z;
-    }
+    ioGetPositions<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->posq, c->posqCorr, c->cellOffsets, c->boxD, enforcePeriodic ? 0 : 1);
+    LAUNCH_COUNT(c, 1);
+    stageOut(c, xyz);
     API_END
 }
 
 extern "C" int b200_set_velocities(b200_ctx* c, const double* xyz) {
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
-    b200_sync_host_order(c);
-    std::vector<double4> v(c->Npad);
-    for (int s = 0; s < c->Npad; s++) {
-        if (s < c->N) { const int o = c->hostAtomIndex[s]; v[s].x = xyz[3 * o]; v[s].y = xyz[3 * o + 1]; v[s].z = xyz[3 * o + 2]; v[s].w = c->mass[o] > 0 ? 1.0 / c->mass[o] : 0.0; }
-        else v[s].x = v[s].y = v[s].z = v[s].w = 0;
-    }
-    CUDA_CHECK(cudaMemcpyAsync(c->velm, v.data(), sizeof(double4) * c->Npad, cudaMemcpyHostToDevice, c->stream));
+    stageIn(c, xyz);
+    ioSetVelocities<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->velm);
+    LAUNCH_COUNT(c, 1);
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
     API_END
 }
@@ -514,26 +569,20 @@ extern "C" int b200_set_velocities(b200_ctx* c, const double* xyz) {
 extern "C" int b200_get_velocities(b200_ctx* c, double* xyz) {
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
-    b200_sync_host_order(c);
-    std::vector<double4> v(c->Npad);
-    d2h(v.data(), c->velm, c->Npad, c->stream);
-    CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    for (int s = 0; s < c->N; s++) { const int o = c->hostAtomIndex[s]; xyz[3 * o] = v[s].x; xyz[3 * o + 1] = v[s].y; xyz[3 * o + 2] = v[s].z; }
+    ensureStaging(c);
+    ioGetVelocities<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->velm);
+    LAUNCH_COUNT(c, 1);
+    stageOut(c, xyz);
     API_END
 }
 
 extern "C" int b200_get_forces(b200_ctx* c, double* xyz) {
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
-    b200_sync_host_order(c);
-    std::vector<long long> f(3 * (size_t)c->Npad);
-    d2h(f.data(), c->force, f.size(), c->stream);
-    CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    const double scale = 1.0 / B200_FORCE_SCALE;   // CommonKernels.cpp:286-297
-    for (int s = 0; s < c->N; s++) {
-        const int o = c->hostAtomIndex[s];
-        xyz[3 * o] = scale * f[s]; xyz[3 * o + 1] = scale * f[s + c->Npad]; xyz[3 * o + 2] = scale * f[s + 2 * (size_t)c->Npad];
-    }
+    ensureStaging(c);
+    ioGetForces<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->Npad, c->force);
+    LAUNCH_COUNT(c, 1);
+    stageOut(c, xyz);
     API_END
 }
 

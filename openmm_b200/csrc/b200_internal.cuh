@@ -93,7 +93,8 @@ struct b200_ctx {
     long long* force = nullptr;    // [3*Npad] fixed point
     DevCounters* counters = nullptr;
     DevCounters* countersHost = nullptr;  // pinned
-    float4* stageA = nullptr; float4* stageB = nullptr; int4* stageOff = nullptr;   // pinned host staging for state I/O
+    double* hStage = nullptr; double* dStage = nullptr;   // pinned host / device staging ([3N] doubles, caller's order) for state I/O
+    bool chargesUploaded = false;
     // scratch for reorder
     float4* posqTmp = nullptr; float4* posqCorrTmp = nullptr; double4* velmTmp = nullptr; int* atomIndexTmp = nullptr; int4* cellOffsetsTmp = nullptr;
 
@@ -141,7 +142,7 @@ struct b200_ctx {
     int4* units = nullptr; int* jAtoms = nullptr; long long unitCapacity = 0, tileCapacity = 0;
     int2* pairOut = nullptr; long long pairCapacity = 0;
     int partRank = 0, partRanks = 1;
-    int sparseMax = 3;             // j atoms reaching at most this many atoms of X are handled as sparse pairs
+    int sparseMax = 5;             // j atoms reaching at most this many atoms of X are handled as sparse pairs
 
     // PME
     int gridN[3] = {0, 0, 0}; int nzc = 0;
