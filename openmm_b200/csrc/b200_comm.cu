@@ -71,6 +71,11 @@ void b200_comm_allreduce_forces(b200_ctx* c) {
     NCCL_CHECK(g_nccl.AllReduce(c->force, c->force, 3 * (size_t)c->Npad, ncclInt64, ncclSum, (ncclComm_t)c->ncclComm, c->stream));
 }
 
+// energies are fixed-point integers too: one more exact integer all-reduce when an energy is requested
+void b200_comm_allreduce_energy(b200_ctx* c) {
+    NCCL_CHECK(g_nccl.AllReduce(c->counters->energy, c->counters->energy, 8, ncclInt64, ncclSum, (ncclComm_t)c->ncclComm, c->stream));
+}
+
 void b200_comm_destroy(b200_ctx* c) {
     if (c->ncclComm && g_nccl.CommDestroy) g_nccl.CommDestroy((ncclComm_t)c->ncclComm);
     c->ncclComm = nullptr;

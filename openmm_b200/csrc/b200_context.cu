@@ -651,26 +651,32 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     if (c->partRank == 0) b200_bonded_launch(c, groups, forces, energy);
     if (doRecip && usePmeStream) CUDA_CHECK(cudaStreamWaitEvent(s, c->evPmeDone, 0));
     if (forces && c->commRanks > 1) b200_comm_allreduce_forces(c);
+    if (energy && c->commRanks > 1) b200_comm_allreduce_energy(c);
     c->forcesValid = forces && groups == B200_GROUP_ALL;
     if (energy) {
         checkOverflow(c);
         const DevCounters& h = *c->countersHost;
         double e = 0;
         const double inv = 1.0 / B200_ENERGY_SCALE;
+// without a communicator a rank reports only what it computed (N logical ranks on one device are summed by the
+        // caller); with one, the integer all-reduce above gave every rank the full device sums and every rank adds the host terms
+        const bool all = c->commRanks > 1;
+        const bool wantRecip = c->hasNonbonded && (groups & B200_GROUP_RECIPROCAL) && (c->partRank == 0 || all);
+        const bool extras = c->partRank == 0 || all;
         if (doDirect) e += inv * (double)h.energy[E_DIRECT];
-        if (doDirect && c->partRank == 0) e += inv * ((double)h.energy[E_EXCLCORR] + (double)h.energy[E_EXCEPT]);
-        if (doRecip) {
+        if (doDirect && extras) e += inv * ((double)h.energy[E_EXCLCORR] + (double)h.energy[E_EXCEPT]);
+        if (wantRecip) {
             e += inv * (double)h.energy[E_RECIP];
             const double* b = c->boxHost; const double V = b[0] * b[4] * b[8];
             // host-side constants (CommonCalcNonbondedForce.cpp:893-898): self energy and neutralising plasma
             e += c->selfEnergy;
             e -= c->totalCharge * c->totalCharge * M_PI * B200_ONE_4PI_EPS0 / (2.0 * V * c->nb.ewald_alpha * c->nb.ewald_alpha);
         }
-        if (doDirect && c->partRank == 0 && c->nb.dispersion_coefficient != 0) {
+        if (doDirect && extras && c->nb.dispersion_coefficient != 0) {
             const double* b = c->boxHost;
             e += c->nb.dispersion_coefficient / (b[0] * b[4] * b[8]);   // CommonCalcNonbondedForce.cpp:1111-1115
         }
-        if ((groups & B200_GROUP_BONDED) && c->partRank == 0) e += inv * (double)h.energy[E_BONDED];
+        if ((groups & B200_GROUP_BONDED) && extras) e += inv * (double)h.energy[E_BONDED];
         if (energyOut) *energyOut = e;
         if (h.overflow) throw B200Error(B200_ERR_OVERFLOW, "neighbour list overflow detected after the computation");
     }

@@ -205,6 +205,7 @@ void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy);
 void b200_integrate_setup(b200_ctx* c);
 void b200_integrate_step(b200_ctx* c);
 void b200_comm_allreduce_forces(b200_ctx* c);
+void b200_comm_allreduce_energy(b200_ctx* c);
 void b200_comm_destroy(b200_ctx* c);
 void b200_fft_make_plan(int n, FFTPlan1D& plan);
 void b200_fft_make_twiddle(int n, float2*& dTw, cudaStream_t s);
