@@ -11,7 +11,11 @@
 // inside a torch process this binds to the NCCL that torch already loaded.
 #include "b200_internal.cuh"
 #include <dlfcn.h>
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <vector>
 
 typedef struct ncclComm* ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
@@ -50,6 +54,28 @@ extern "C" int b200_nccl_unique_id(char* id128) {
 extern "C" int b200_set_partition(b200_ctx* c, int32_t rank, int32_t nranks) {
     if (!c || nranks < 1 || rank < 0 || rank >= nranks) { b200_set_error("b200_set_partition: bad rank"); return B200_ERR_INVALID; }
     c->partRank = rank; c->partRanks = nranks;
+    // Rank 0 also runs PME, the exclusion corrections and the bonded terms, so it takes a smaller share s0 of the direct-space
+    // rows: balance s0*D + P = (1-s0)/(R-1)*D with rho = P/D  =>  s0 = (1 - (R-1) rho)/R  (clamped at 0: a PME-only rank).
+    // The reference balances dynamically from measured times (CudaParallelKernels.cpp:247-266); a fixed model suffices here
+    // because rows are sampled uniformly.  B200_PME_COST_RATIO overrides rho.
+    double rho = 0.5;
+    if (const char* e = getenv("B200_PME_COST_RATIO")) rho = atof(e);
+    std::vector<double> share(nranks, 1.0 / nranks);
+    if (nranks > 1 && c->commRanks > 1) {   // only with a communicator: logical ranks on one device are plain equal shares
+        const double s0 = std::max(0.0, (1.0 - (nranks - 1) * rho) / nranks);
+        share[0] = s0;
+        for (int r = 1; r < nranks; r++) share[r] = (1.0 - s0) / (nranks - 1);
+    }
+    // weighted round-robin over a period of 64 rows (largest-remainder / Bresenham spreading)
+    std::vector<double> credit(nranks, 0.0);
+    for (int i = 0; i < 64; i++) {
+        int best = 0;
+        for (int r = 0; r < nranks; r++) { credit[r] += share[r]; if (credit[r] > credit[best] + 1e-12) best = r; }
+        c->partTable.owner[i] = (unsigned char)best;
+        credit[best] -= 1.0;
+    }
+    double begin = 0; for (int r = 0; r < rank; r++) begin += share[r];
+    c->partShareBegin = begin; c->partShareEnd = (rank == nranks - 1) ? 1.0 : begin + share[rank];
     if (c->finalized) c->stepsSinceReorder = -1;   // forces a list rebuild with the new row assignment
     return B200_OK;
 }

@@ -77,6 +77,7 @@ extern "C" int b200_context_create(const b200_system_desc* desc, b200_ctx** out)
     CUDA_CHECK(cudaStreamCreateWithFlags(&c->pmeStream, cudaStreamNonBlocking));
     CUDA_CHECK(cudaEventCreateWithFlags(&c->evFork, cudaEventDisableTiming));
     CUDA_CHECK(cudaEventCreateWithFlags(&c->evPmeDone, cudaEventDisableTiming));
+    memset(c->partTable.owner, 0, sizeof(c->partTable.owner));
     b200_box_set(c, desc->box);
     c->mass.assign(desc->mass, desc->mass + c->N);
     c->numConstraints = desc->num_constraints;

@@ -142,6 +142,8 @@ struct b200_ctx {
     int4* units = nullptr; int* jAtoms = nullptr; long long unitCapacity = 0, tileCapacity = 0;
     int2* pairOut = nullptr; long long pairCapacity = 0;
     int partRank = 0, partRanks = 1;
+    struct OwnerTable { unsigned char owner[64]; } partTable;   // row X belongs to rank owner[X & 63] (weighted round-robin)
+    double partShareBegin = 0.0, partShareEnd = 1.0;           // this rank's slice of the exclusion-tile index range
     int sparseMax = 5;             // j atoms reaching at most this many atoms of X are handled as sparse pairs
 
     // PME

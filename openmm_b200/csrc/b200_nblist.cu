@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
         const float4* __restrict__ superCenter, const float4* __restrict__ superHalf,
         const int* __restrict__ exclRowStart, const int* __restrict__ exclRowCols,
         int4* __restrict__ units, int* __restrict__ jAtoms, unsigned unitCapacity, unsigned tileCapacity,
-        int partRank, int partRanks, DevCounters* counters) {
+        int partRank, b200_ctx::OwnerTable table, DevCounters* counters) {
     if (!counters->rebuild) return;
     __shared__ float4 sX[NB_WARPS][32];
     __shared__ float4 sQ[NB_WARPS][64];     // queue of candidate atoms that passed the box test: (rel. position, slot)
@@ -189,9 +189,9 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
     const unsigned ltMask = (1u << lane) - 1u;
     const float rcp = sqrtf(rcp2);
     NbWarpBufs wb = {sBuf[warp], sSlot[warp], sMask[warp]};
-    // rows are dealt round-robin to ranks: every rank gets a statistically identical share of the sweep
-    for (int xi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; xi * partRanks + partRank < B; xi += warpsPerGrid) {
-        const int X = xi * partRanks + partRank;
+    // rows are dealt (weighted) round-robin to ranks: every rank gets a statistically identical sample of the sweep
+    for (int X = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; X < B; X += warpsPerGrid) {
+        if (table.owner[X & 63] != partRank) continue;
         const float4 cX = blockCenter[X], hX = blockHalf[X];
         const bool single = !box.triclinic && 0.5f * box.ax - hX.x >= rcp && 0.5f * box.by - hX.y >= rcp && 0.5f * box.cz - hX.z >= rcp;
         {
@@ -299,12 +299,12 @@ void b200_nblist_prepare(b200_ctx* c) {
     nbBlockBounds<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, c->B, c->boxF, c->blockCenter, c->blockHalf, c->counters);
     nbSuperBounds<<<(c->numSuper + 7) / 8, 256, 0, c->stream>>>(c->blockCenter, c->blockHalf, c->B, c->numSuper, c->boxF, c->superCenter, c->superHalf, c->counters);
     const float rcp = (float)c->paddedCutoff;
-    int rows = (c->B + c->partRanks - 1) / c->partRanks;
+    int rows = c->B;
     int buildGrid = (rows + NB_WARPS - 1) / NB_WARPS;
     if (buildGrid > c->smCount * 16) buildGrid = c->smCount * 16;
     nbBuild<<<buildGrid, NB_THREADS, 0, c->stream>>>(c->posq, c->N, c->B, c->numSuper, c->boxF, rcp * rcp, c->sparseMax,
         c->blockCenter, c->blockHalf, c->superCenter, c->superHalf, c->exclRowStart, c->exclRowCols,
-        c->units, c->jAtoms, (unsigned)c->unitCapacity, (unsigned)c->tileCapacity, c->partRank, c->partRanks, c->counters);
+        c->units, c->jAtoms, (unsigned)c->unitCapacity, (unsigned)c->tileCapacity, c->partRank, c->partTable, c->counters);
     nbFinish<<<1, 1, 0, c->stream>>>(c->counters);
     LAUNCH_COUNT(c, 5);
     CUDA_CHECK(cudaGetLastError());

@@ -495,8 +495,8 @@ void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
     a.pairOut = c->pairOut; a.pairCapacity = c->pairCapacity;
     a.N = c->N; a.Npad = c->Npad;
     // exclusion tiles are split by index over ranks (CudaNonbondedUtilities.cpp:704-708)
-    a.exclBegin = (int)((long long)c->numExclTiles * c->partRank / c->partRanks);
-    a.exclEnd = (int)((long long)c->numExclTiles * (c->partRank + 1) / c->partRanks);
+    a.exclBegin = (int)llround(c->numExclTiles * c->partShareBegin);
+    a.exclEnd = (int)llround(c->numExclTiles * c->partShareEnd);
     a.box = c->boxF; a.boxD = c->boxD;
     const double rc = c->nb.cutoff, al = c->nb.ewald_alpha;
     a.rc2 = (float)(rc * rc); a.rc2d = rc * rc; a.rcPadded = (float)c->paddedCutoff;

@@ -1,7 +1,7 @@
 """Host-side mirror of how the direct-space work is partitioned over ranks (one process per GPU).
 
-  rows (32-atom blocks X of the tile list)  : dealt round-robin, rank r owns X with X % R == r            (b200_nblist.cu nbBuild)
-  exclusion tiles (static list, sorted)     : contiguous index ranges [n*r/R, n*(r+1)/R)                   (b200_tile.cu)
+  rows (32-atom blocks X of the tile list)  : weighted round-robin, rank = owner_table[X & 63]             (b200_nblist.cu nbBuild)
+  exclusion tiles (static list, sorted)     : contiguous index ranges proportional to the same shares      (b200_tile.cu)
   PME, exclusion corrections, bonded terms  : rank 0
   forces                                    : int64 fixed point (x 2^32), summed with one all-reduce       (b200_comm.cu)
 
@@ -14,12 +14,41 @@ import numpy as np
 FORCE_SCALE = 4294967296.0
 
 
-def rows_of_rank(num_blocks, rank, nranks):
-    return np.arange(rank, num_blocks, nranks)
+def shares(nranks, pme_cost_ratio=0.5, with_communicator=True):
+    """fraction of the direct-space rows each rank takes; rank 0 also runs PME (b200_comm.cu b200_set_partition)"""
+    if nranks == 1 or not with_communicator:
+        return [1.0 / nranks] * nranks
+    s0 = max(0.0, (1.0 - (nranks - 1) * pme_cost_ratio) / nranks)
+    return [s0] + [(1.0 - s0) / (nranks - 1)] * (nranks - 1)
 
 
-def exclusion_tile_range(num_tiles, rank, nranks):
-    return (num_tiles * rank) // nranks, (num_tiles * (rank + 1)) // nranks
+def owner_table(nranks, **kw):
+    """row X belongs to rank owner_table[X & 63]: weighted round-robin, same largest-credit rule as the C code"""
+    share = shares(nranks, **kw)
+    credit = [0.0] * nranks
+    table = []
+    for _ in range(64):
+        best = 0
+        for r in range(nranks):
+            credit[r] += share[r]
+            if credit[r] > credit[best] + 1e-12:
+                best = r
+        table.append(best)
+        credit[best] -= 1.0
+    return np.array(table)
+
+
+def rows_of_rank(num_blocks, rank, nranks, **kw):
+    table = owner_table(nranks, **kw)
+    x = np.arange(num_blocks)
+    return x[table[x & 63] == rank]
+
+
+def exclusion_tile_range(num_tiles, rank, nranks, **kw):
+    share = shares(nranks, **kw)
+    begin = sum(share[:rank])
+    end = 1.0 if rank == nranks - 1 else begin + share[rank]
+    return int(round(num_tiles * begin)), int(round(num_tiles * end))
 
 
 def to_fixed(f):
