@@ -561,6 +561,7 @@ extern "C" int b200_set_velocities(b200_ctx* c, const double* xyz) {
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
     stageIn(c, xyz);
+    c->cmValid = false;
     ioSetVelocities<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->velm);
     LAUNCH_COUNT(c, 1);
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
@@ -744,12 +745,15 @@ extern "C" int b200_step(b200_ctx* c, int32_t nsteps) {
     CUDA_CHECK(cudaSetDevice(c->device));
     b200_finalize(c);
     if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
+    c->fusedStepExtras = true;
     for (int i = 0; i < nsteps; i++) {
+        c->skipDispCheck = i > 0;     // from the second step on, the integrator kernel of the previous step did the check
         computeImpl(c, B200_GROUP_ALL, true, false, nullptr, i == 0 || (c->stepCount & 63) == 0);
         b200_integrate_step(c);
         c->stepCount++; c->timePs += c->integ.dt; c->stepsSinceReorder++;
         c->forcesValid = false;
     }
+    c->skipDispCheck = false; c->fusedStepExtras = false;
     checkOverflow(c);
     if (c->countersHost->overflow) throw B200Error(B200_ERR_OVERFLOW, "neighbour list overflowed during b200_step; state is not trustworthy");
     API_END

@@ -44,7 +44,12 @@ struct IntegArgs {
     int Npad;
     double dt, vscale, noisescale;
     unsigned long long seed, step;
+    // fused extras of the stepping loop: COM-motion removal (removeCM.cc) and the Verlet-buffer displacement check
+    // (findInteractingBlocks.cu:176-185) ride along, so a step needs no separate passes over the atoms for them
+    const float4* refPosq; float maxDisp2; DevCounters* counters;
+    int fuseCM; int cmCur, cmNext, cmClear; double invTotalMass;
 };
+#define CM_SCALE 1048576.0   // 2^20 fixed point for momentum sums
 
 __device__ __forceinline__ V3 loadPosD(const IntegArgs& a, int i) { const float4 p = a.posq[i], q = a.posqCorr[i]; return {(double)p.x + q.x, (double)p.y + q.y, (double)p.z + q.z}; }
 __device__ __forceinline__ void storePosD(const IntegArgs& a, int i, V3 p) {
@@ -116,10 +121,24 @@ __device__ __forceinline__ void settlePositions(V3 p0, V3 p1, V3 p2, V3& d0, V3&
     d2 = com + ex * c3.x + ey * c3.y + ez * c3.z - c0;
 }
 
+__device__ __forceinline__ void checkMoved(const IntegArgs& a, int i, V3 p, bool& moved) {
+    if (!a.refPosq) return;
+    const float4 r = a.refPosq[i];
+    const float dx = (float)p.x - r.x, dy = (float)p.y - r.y, dz = (float)p.z - r.z;
+    moved |= dx * dx + dy * dy + dz * dz > a.maxDisp2;
+}
+
 __global__ void __launch_bounds__(128) langevinMiddleStep(IntegArgs a, int numSettle, const int4* __restrict__ settleAtoms, const float2* __restrict__ settleParams,
                                                            int numFree, const int* __restrict__ freeAtoms) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const double halfdt = 0.5 * a.dt, invDt = 1.0 / a.dt;
+    V3 vcm = {0, 0, 0}, mom = {0, 0, 0};
+    if (a.fuseCM) {
+        const double sc = a.invTotalMass / CM_SCALE;
+        vcm = {sc * (double)a.counters->cm[a.cmCur][0], sc * (double)a.counters->cm[a.cmCur][1], sc * (double)a.counters->cm[a.cmCur][2]};
+        if (t == 0) { a.counters->cm[a.cmClear][0] = 0; a.counters->cm[a.cmClear][1] = 0; a.counters->cm[a.cmClear][2] = 0; }
+    }
+    bool moved = false;
     if (t < numSettle) {
         const int4 at = settleAtoms[t]; const float2 prm = settleParams[t];
         const int idx[3] = {at.x, at.y, at.z};
@@ -129,7 +148,7 @@ __global__ void __launch_bounds__(128) langevinMiddleStep(IntegArgs a, int numSe
             p[k] = loadPosD(a, idx[k]);
             const double4 vm = a.velm[idx[k]];
             im[k] = vm.w;
-            v[k] = V3{vm.x, vm.y, vm.z} + loadForce(a, idx[k]) * (a.dt * vm.w);          // part 1
+            v[k] = V3{vm.x, vm.y, vm.z} - vcm + loadForce(a, idx[k]) * (a.dt * vm.w);    // COM removal, then part 1
         }
         settleVelocities(p[0], p[1], p[2], v[0], v[1], v[2], im[0], im[1], im[2]);
 #pragma unroll
@@ -145,23 +164,40 @@ __global__ void __launch_bounds__(128) langevinMiddleStep(IntegArgs a, int numSe
         for (int k = 0; k < 3; k++) {                                                       // part 3
             v[k] = v[k] + (d[k] - old[k]) * invDt;
             a.velm[idx[k]] = make_double4(v[k].x, v[k].y, v[k].z, im[k]);
-            storePosD(a, idx[k], p[k] + d[k]);
+            const V3 pn = p[k] + d[k];
+            storePosD(a, idx[k], pn);
+            checkMoved(a, idx[k], pn, moved);
+            mom = mom + v[k] * (1.0 / im[k]);
         }
     } else if (t < numSettle + numFree) {
         const int i = freeAtoms[t - numSettle];
         const double4 vm = a.velm[i];
-        V3 v = V3{vm.x, vm.y, vm.z} + loadForce(a, i) * (a.dt * vm.w);
+        V3 v = V3{vm.x, vm.y, vm.z} - vcm + loadForce(a, i) * (a.dt * vm.w);
         V3 d = v * halfdt;
         const V3 g = gaussian3(a.seed, a.step, a.atomIndex[i]);
         v = v * a.vscale + g * (a.noisescale * sqrt(vm.w));
         d = d + v * halfdt;
         a.velm[i] = make_double4(v.x, v.y, v.z, vm.w);
-        storePosD(a, i, loadPosD(a, i) + d);
+        const V3 pn = loadPosD(a, i) + d;
+        storePosD(a, i, pn);
+        checkMoved(a, i, pn, moved);
+        mom = mom + v * (1.0 / vm.w);
+    }
+    if (a.refPosq && __any_sync(0xffffffffu, moved) && (threadIdx.x & 31) == 0) a.counters->rebuild = 1;
+    if (a.fuseCM) {   // momentum of the new velocities, removed at the start of the next step (fixed-order block sum, integer atomics)
+        __shared__ double red[3][128];
+        red[0][threadIdx.x] = mom.x; red[1][threadIdx.x] = mom.y; red[2][threadIdx.x] = mom.z;
+        __syncthreads();
+        for (int o = 64; o > 0; o >>= 1) {
+            if (threadIdx.x < o) for (int k = 0; k < 3; k++) red[k][threadIdx.x] += red[k][threadIdx.x + o];
+            __syncthreads();
+        }
+        if (threadIdx.x < 3) atomicAddFixed(&a.counters->cm[a.cmNext][threadIdx.x], (long long)(red[threadIdx.x][0] * CM_SCALE));
     }
 }
 
 // ---- centre-of-mass motion removal (platforms/common/src/kernels/removeCM.cc)
-__global__ void __launch_bounds__(256) cmMomentum(const double4* __restrict__ velm, int N, DevCounters* counters) {
+__global__ void __launch_bounds__(256) cmMomentum(const double4* __restrict__ velm, int N, DevCounters* counters, int slot) {
     double px = 0, py = 0, pz = 0;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
         const double4 v = velm[i];
@@ -174,17 +210,17 @@ __global__ void __launch_bounds__(256) cmMomentum(const double4* __restrict__ ve
         if (threadIdx.x < o) for (int k = 0; k < 3; k++) red[k][threadIdx.x] += red[k][threadIdx.x + o];
         __syncthreads();
     }
-    if (threadIdx.x < 3) atomicAddFixed(&counters->momentum[threadIdx.x], (long long)(red[threadIdx.x][0] * 1048576.0));   // 2^20 fixed point
+    if (threadIdx.x < 3) atomicAddFixed(&counters->cm[slot][threadIdx.x], (long long)(red[threadIdx.x][0] * CM_SCALE));
 }
-__global__ void cmRemove(double4* velm, int N, double invTotalMass, DevCounters* counters) {
-    const double sc = invTotalMass / 1048576.0;
-    const double vx = sc * (double)counters->momentum[0], vy = sc * (double)counters->momentum[1], vz = sc * (double)counters->momentum[2];
+__global__ void cmRemove(double4* velm, int N, double invTotalMass, DevCounters* counters, int slot) {
+    const double sc = invTotalMass / CM_SCALE;
+    const double vx = sc * (double)counters->cm[slot][0], vy = sc * (double)counters->cm[slot][1], vz = sc * (double)counters->cm[slot][2];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
         double4 v = velm[i];
         if (v.w != 0.0) { v.x -= vx; v.y -= vy; v.z -= vz; velm[i] = v; }
     }
 }
-__global__ void cmZero(DevCounters* counters) { counters->momentum[0] = counters->momentum[1] = counters->momentum[2] = 0; }
+__global__ void cmZero(DevCounters* counters, int slot) { counters->cm[slot][0] = counters->cm[slot][1] = counters->cm[slot][2] = 0; }
 
 __global__ void __launch_bounds__(256) kineticEnergy(const double4* __restrict__ velm, int N, DevCounters* counters) {
     double e = 0;
@@ -228,16 +264,18 @@ static IntegArgs makeArgs(b200_ctx* c) {
     a.vscale = exp(-c->integ.dt * c->integ.friction);
     a.noisescale = sqrt(kT * (1.0 - a.vscale * a.vscale));
     a.seed = c->integ.seed; a.step = (unsigned long long)c->stepCount;
+    a.refPosq = nullptr; a.maxDisp2 = 0.f; a.counters = c->counters; a.fuseCM = 0; a.cmCur = a.cmNext = a.cmClear = 0; a.invTotalMass = 0;
     return a;
 }
 
 static void removeCM(b200_ctx* c) {
     cudaStream_t s = c->stream;
     double total = 0; for (double m : c->mass) total += m;
-    cmZero<<<1, 1, 0, s>>>(c->counters);
-    cmMomentum<<<c->smCount * 2, 256, 0, s>>>(c->velm, c->N, c->counters);
-    cmRemove<<<c->smCount * 4, 256, 0, s>>>(c->velm, c->N, 1.0 / total, c->counters);
+    cmZero<<<1, 1, 0, s>>>(c->counters, 3);
+    cmMomentum<<<c->smCount * 2, 256, 0, s>>>(c->velm, c->N, c->counters, 3);
+    cmRemove<<<c->smCount * 4, 256, 0, s>>>(c->velm, c->N, 1.0 / total, c->counters, 3);
     LAUNCH_COUNT(c, 3);
+    c->cmValid = false;
 }
 
 // RemoveCMMotionKernel::execute (kernels.h:1793)
@@ -267,10 +305,23 @@ extern "C" int b200_integrate(b200_ctx* c) {
 void b200_integrate_step(b200_ctx* c) {
     cudaStream_t s = c->stream;
     ScopedTimer tm(c, B200_T_INTEGRATE, s);
-    if (c->integ.remove_cm_every > 0 && c->stepCount % c->integ.remove_cm_every == 0) removeCM(c);
+    IntegArgs a = makeArgs(c);
+    const bool fuse = c->integ.remove_cm_every == 1 && c->fusedStepExtras;
+    if (fuse) {
+        if (!c->cmValid) {   // momentum of the current velocities is not known on the device yet (first step, or velocities were set)
+            cmZero<<<1, 1, 0, s>>>(c->counters, 0); cmZero<<<1, 1, 0, s>>>(c->counters, 1); cmZero<<<1, 1, 0, s>>>(c->counters, 2);
+            cmMomentum<<<c->smCount * 2, 256, 0, s>>>(c->velm, c->N, c->counters, (int)(c->stepCount % 3));
+            LAUNCH_COUNT(c, 4);
+            c->cmValid = true;
+        }
+        double total = 0; for (double m : c->mass) total += m;
+        a.fuseCM = 1; a.invTotalMass = 1.0 / total;
+        a.cmCur = (int)(c->stepCount % 3); a.cmNext = (int)((c->stepCount + 1) % 3); a.cmClear = (int)((c->stepCount + 2) % 3);
+    } else if (c->integ.remove_cm_every > 0 && c->stepCount % c->integ.remove_cm_every == 0) removeCM(c);
+    if (c->fusedStepExtras && c->hasNonbonded) { a.refPosq = c->refPosq; const float md = 0.5f * (float)c->padding; a.maxDisp2 = md * md; }
     const int units = c->numSettle + c->numFree;
     if (units > 0) {
-        langevinMiddleStep<<<(units + 127) / 128, 128, 0, s>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, c->numFree, c->freeAtoms);
+        langevinMiddleStep<<<(units + 127) / 128, 128, 0, s>>>(a, c->numSettle, c->settleAtoms, c->settleParams, c->numFree, c->freeAtoms);
         LAUNCH_COUNT(c, 1);
     }
     CUDA_CHECK(cudaGetLastError());
@@ -293,6 +344,7 @@ extern "C" int b200_apply_velocity_constraints(b200_ctx* c, double) {
         b200_finalize(c);
         if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
         if (c->numSettle > 0) { settleOnly<<<(c->numSettle + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, 1); LAUNCH_COUNT(c, 1); }
+        c->cmValid = false;
         CUDA_CHECK(cudaStreamSynchronize(c->stream));
     } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
     return B200_OK;

@@ -46,7 +46,7 @@ struct DevCounters {
     unsigned int numSparseTiles;// sparse tiles (each occupies two 32-int slots of jAtoms) among numTiles
     unsigned long long pairCount;
     long long    energy[8];     // fixed point 2^32: 0 direct tiles, 1 exclusion corr, 2 exceptions, 3 reciprocal, 4 bonded, 5 kinetic*2
-    long long    momentum[4];   // fixed point: sum m v (x,y,z), unused
+    long long    cm[4][4];      // fixed point 2^20: sum m v (x,y,z); slots 0-2 rotate through the fused stepping loop, slot 3 is the stand-alone pass
 };
 #define E_DIRECT 0
 #define E_EXCLCORR 1
@@ -167,6 +167,9 @@ struct b200_ctx {
     b200_integrator_desc integ;
     double timePs = 0; int64_t stepCount = 0;
     bool forcesValid = false;
+    bool cmValid = false;          // device momentum buffer matches the current velocities (fused COM removal)
+    bool skipDispCheck = false;    // the previous step's integrator already ran the displacement check
+    bool fusedStepExtras = false;  // set by b200_step: COM removal and displacement check ride inside the integrator kernel
 
     // multi-GPU
     void* ncclComm = nullptr; int commRank = 0, commRanks = 1;

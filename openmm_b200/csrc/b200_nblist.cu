@@ -295,7 +295,7 @@ void b200_nblist_prepare(b200_ctx* c) {
     ScopedTimer tm(c, B200_T_NBLIST, c->stream);
     const float maxDisp = 0.5f * (float)c->padding;
     const int grid = c->smCount * 4;
-    nbCheckDisplacement<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, maxDisp * maxDisp, c->counters);
+    if (!c->skipDispCheck) { nbCheckDisplacement<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, maxDisp * maxDisp, c->counters); LAUNCH_COUNT(c, 1); }
     nbBlockBounds<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, c->B, c->boxF, c->blockCenter, c->blockHalf, c->counters);
     nbSuperBounds<<<(c->numSuper + 7) / 8, 256, 0, c->stream>>>(c->blockCenter, c->blockHalf, c->B, c->numSuper, c->boxF, c->superCenter, c->superHalf, c->counters);
     const float rcp = (float)c->paddedCutoff;
@@ -306,6 +306,6 @@ void b200_nblist_prepare(b200_ctx* c) {
         c->blockCenter, c->blockHalf, c->superCenter, c->superHalf, c->exclRowStart, c->exclRowCols,
         c->units, c->jAtoms, (unsigned)c->unitCapacity, (unsigned)c->tileCapacity, c->partRank, c->partTable, c->counters);
     nbFinish<<<1, 1, 0, c->stream>>>(c->counters);
-    LAUNCH_COUNT(c, 5);
+    LAUNCH_COUNT(c, 4);
     CUDA_CHECK(cudaGetLastError());
 }

@@ -359,11 +359,14 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
             // ---------------- dense unit (or one exclusion tile)
             float fix = 0.f, fiy = 0.f, fiz = 0.f, eTile = 0.f;
             float2 gix = dup(0.f), giy = dup(0.f), giz = dup(0.f);   // packed path: +sum of d*s for atom i (two partial sums)
+            // two-deep software pipeline over the unit's tiles: the index of tile t+2 and the atom data of tile t+1 are in
+            // flight while tile t is computed, so neither load latency is exposed (padding slots read atom 0 and are masked)
             int ja = excl ? yBlock * 32 + lane : a.jAtoms[(size_t)tileStart * 32 + lane];
-            float4 pj = make_float4(0.f, 0.f, 0.f, 0.f); float2 prj = make_float2(0.f, 0.f);
-            if (ja >= 0) { pj = a.posq[ja]; prj = a.sigEps[ja]; }
+            int jaNext = (nTiles > 1) ? a.jAtoms[(size_t)(tileStart + 1) * 32 + lane] : -1;
+            float4 pj = a.posq[max(ja, 0)]; float2 prj = a.sigEps[max(ja, 0)];
             for (int t = 0; t < nTiles; t++) {
                 const int jaCur = ja;
+                if (jaCur < 0) { pj.w = 0.f; prj = make_float2(0.f, 0.f); }
                 {   // stage tile t
                     float xj = pj.x, yj = pj.y, zj = pj.z;
                     if (single) {
@@ -386,9 +389,9 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
                     __syncwarp();
                 }
                 if (t + 1 < nTiles) {   // next tile's loads fly while this one is computed
-                    ja = a.jAtoms[(size_t)(tileStart + t + 1) * 32 + lane];
-                    pj = make_float4(0.f, 0.f, 0.f, 0.f); prj = make_float2(0.f, 0.f);
-                    if (ja >= 0) { pj = a.posq[ja]; prj = a.sigEps[ja]; }
+                    ja = jaNext;
+                    pj = a.posq[max(ja, 0)]; prj = a.sigEps[max(ja, 0)];
+                    if (t + 2 < nTiles) jaNext = a.jAtoms[(size_t)(tileStart + t + 2) * 32 + lane];
                 }
                 float fjx = 0.f, fjy = 0.f, fjz = 0.f;
                 if (PACKED && single) {
