@@ -115,11 +115,11 @@ def find_legal_fft_dimension(n):
         n += 1
 
 
-def pme_parameters(cutoff, box, tol=5e-4):
+def pme_parameters(cutoff, box, tol=5e-4, lj=False):
     """alpha and mesh as NonbondedForceImpl::calcPMEParameters (openmmapi/src/NonbondedForceImpl.cpp:192-216) followed by
     the 2,3,5,7-smooth rounding of the GPU platforms."""
     alpha = np.sqrt(-np.log(2 * tol)) / cutoff
-    grid = [find_legal_fft_dimension(int(np.ceil(2 * alpha * L / (3 * tol ** 0.2)))) for L in (box[0], box[4], box[8])]
+    grid = [find_legal_fft_dimension(int(np.ceil((1 if lj else 2) * alpha * L / (3 * tol ** 0.2)))) for L in (box[0], box[4], box[8])]
     return float(alpha), [max(g, 6) for g in grid]
 
 

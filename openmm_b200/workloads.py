@@ -125,6 +125,16 @@ def water_box(n_atoms, seed=0, density=100.0):
                 exclusions=excl.astype(np.int32), constraints=(excl.astype(np.int32), con_d), num_waters=nw)
 
 
+def ljpme_water_box(n_atoms):
+    """water_box(n_atoms, seed=n_atoms) with CHARMM-style hydrogens, so that the LJPME dispersion grid sees three particle types"""
+    sysd = water_box(n_atoms, seed=n_atoms)
+    nw = sysd["num_waters"]
+    for k in (1, 2):
+        sysd["sigma"][k:3 * nw:3] = 0.0400014
+        sysd["epsilon"][k:3 * nw:3] = 0.192464
+    return sysd
+
+
 def make_context(sysd, cutoff=0.9, tol=5e-4, device=0, grid=None, alpha=None, **kw):
     """Create an openmm_b200.Context for a water_box() system with the reference's default PME settings."""
     import openmm_b200 as b
@@ -138,17 +148,19 @@ def make_context(sysd, cutoff=0.9, tol=5e-4, device=0, grid=None, alpha=None, **
     return ctx
 
 
-def write_system_file(path, sysd, cutoff, alpha, grid, method=4, dispersion=False):
+def write_system_file(path, sysd, cutoff, alpha, grid, method=4, dispersion=False, lj_alpha=None, lj_grid=None):
     """Binary system description read by oracle/ref_driver.cpp (layout documented there)."""
     n = sysd["n"]
     exc = sysd.get("exceptions")
     with open(path, "wb") as f:
         f.write(b"B2SY")
-        f.write(struct.pack("<ii", 1, n))
+        f.write(struct.pack("<ii", 1 if lj_alpha is None else 2, n))
         f.write(np.asarray(sysd["box"], dtype="<f8").tobytes())
         f.write(struct.pack("<dd", cutoff, alpha))
         f.write(struct.pack("<iiii", int(grid[0]), int(grid[1]), int(grid[2]), method))
         f.write(struct.pack("<d", 1.0 if dispersion else 0.0))
+        if lj_alpha is not None:
+            f.write(struct.pack("<diii", lj_alpha, int(lj_grid[0]), int(lj_grid[1]), int(lj_grid[2])))
         for key in ("charge", "sigma", "epsilon", "mass"):
             f.write(np.asarray(sysd[key], dtype="<f8").tobytes())
         f.write(np.asarray(sysd["positions"], dtype="<f8").reshape(-1).tobytes())

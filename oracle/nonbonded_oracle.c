@@ -118,6 +118,22 @@ long long oracle_direct(const oracle_system* s, double* forces, double* energy, 
                     const double sig6 = sig2 * sig2 * sig2;
                     dEdR += eps * (12.0 * sig6 - 6.0) * sig6 * invR * invR;
                     esum += qq * invR * erfc(ar) + eps * (sig6 - 1.0) * sig6;
+                    if (s->ljpme) {
+                        /* ReferenceLJCoulombIxn.cpp:404-431: remove the multiplicative C6 term the dispersion grid adds, plus the
+                           potential shift between the additive and multiplicative forms at the cutoff */
+                        const double dar2 = s->lj_alpha * s->lj_alpha * r2, dar4 = dar2 * dar2, dar6 = dar4 * dar2;
+                        const double invR2 = invR * invR;
+                        const double c6i = 8.0 * pow(0.5 * s->sigma[i], 3.0) * 2.0 * sqrt(s->epsilon[i]);
+                        const double c6j = 8.0 * pow(0.5 * s->sigma[j], 3.0) * 2.0 * sqrt(s->epsilon[j]);
+                        const double emult = c6i * c6j * invR2 * invR2 * invR2 * (1.0 - exp(-dar2) * (1.0 + dar2 + 0.5 * dar4));
+                        dEdR += 6.0 * c6i * c6j * invR2 * invR2 * invR2 * invR2 * (1.0 - exp(-dar2) * (1.0 + dar2 + 0.5 * dar4 + dar6 / 6.0));
+                        const double invCut2 = 1.0 / rc2, invCut6 = invCut2 * invCut2 * invCut2;
+                        double s2 = sig * sig; const double s6 = s2 * s2 * s2;
+                        double shift = eps * (1.0 - s6 * invCut6) * s6 * invCut6;
+                        const double dc2 = s->lj_alpha * s->lj_alpha * rc2, dc4 = dc2 * dc2;
+                        shift -= c6i * c6j * invCut6 * (1.0 - exp(-dc2) * (1.0 + dc2 + 0.5 * dc4));
+                        esum += emult + shift;
+                    }
                     if (forces) for (int k = 0; k < 3; k++) { forces[3 * i + k] -= dEdR * d[k]; forces[3 * j + k] += dEdR * d[k]; }
                 }
             }
@@ -144,6 +160,15 @@ void oracle_exclusion_correction(const oracle_system* s, double* forces, double*
             esum += qq * invR * erf(ar);
         } else {
             esum += s->alpha * 2.0 / sqrt(M_PI) * qq;
+        }
+        if (s->ljpme) {
+            /* ReferenceLJCoulombIxn.cpp:497-513: back out the reciprocal-space dispersion of the excluded pair */
+            const double dar2 = s->lj_alpha * s->lj_alpha * r * r, dar4 = dar2 * dar2, dar6 = dar4 * dar2, invR2 = invR * invR;
+            const double c6i = 8.0 * pow(0.5 * s->sigma[i], 3.0) * 2.0 * sqrt(s->epsilon[i]);
+            const double c6j = 8.0 * pow(0.5 * s->sigma[j], 3.0) * 2.0 * sqrt(s->epsilon[j]);
+            esum -= c6i * c6j * invR2 * invR2 * invR2 * (1.0 - exp(-dar2) * (1.0 + dar2 + 0.5 * dar4));
+            const double dEdR = -6.0 * c6i * c6j * invR2 * invR2 * invR2 * invR2 * (1.0 - exp(-dar2) * (1.0 + dar2 + 0.5 * dar4 + dar6 / 6.0));
+            if (forces) for (int k = 0; k < 3; k++) { forces[3 * i + k] += dEdR * d[k]; forces[3 * j + k] -= dEdR * d[k]; }
         }
     }
     if (energy) *energy -= esum;
@@ -172,7 +197,10 @@ double oracle_self_energy(const oracle_system* s) {
     for (int i = 0; i < s->n; i++) { q2 += s->charge[i] * s->charge[i]; q += s->charge[i]; }
     const double V = s->box[0] * s->box[4] * s->box[8];
     const double eps0 = 1.0 / (4.0 * M_PI * ONE_4PI_EPS0);
-    return -ONE_4PI_EPS0 * q2 * s->alpha / sqrt(M_PI) - q * q / (8.0 * eps0 * V * s->alpha * s->alpha);
+    double e = -ONE_4PI_EPS0 * q2 * s->alpha / sqrt(M_PI) - q * q / (8.0 * eps0 * V * s->alpha * s->alpha);
+    if (s->ljpme)   /* dispersion self term, ReferenceLJCoulombIxn.cpp:224-227 */
+        for (int i = 0; i < s->n; i++) e += pow(s->lj_alpha, 6.0) * 64.0 * pow(0.5 * s->sigma[i], 6.0) * 4.0 * s->epsilon[i] / 12.0;
+    return e;
 }
 
 /* ---- FFT: recursive mixed radix (any n; O(n * sum of prime factors)) ------------------------------------------ */
@@ -256,8 +284,10 @@ static void moduli(int n, double* mod) {
     free(data);
 }
 
-void oracle_reciprocal(const oracle_system* s, double* forces, double* energy) {
-    const int n = s->n, nx = s->grid[0], ny = s->grid[1], nz = s->grid[2];
+/* one smooth-PME reciprocal sum: Coulomb (dispersion = 0; ReferencePME::exec) or dispersion (dispersion = 1; exec_dpme,
+   ReferencePME.cpp:336-410,594-674) with the given per-particle coefficients, Ewald coefficient and mesh */
+static void pme_sum(const oracle_system* s, const double* coef, double alpha, const int* mesh, int dispersion, double* forces, double* energy) {
+    const int n = s->n, nx = mesh[0], ny = mesh[1], nz = mesh[2];
     const double* b = s->box;
     /* reciprocal box vectors (ReferencePME.cpp invert_box_vectors) */
     const double det = b[0] * b[4] * b[8], sc = 1.0 / det;
@@ -280,7 +310,7 @@ void oracle_reciprocal(const oracle_system* s, double* forces, double* energy) {
         }
     }
     for (int i = 0; i < n; i++) {
-        const double q = s->charge[i];
+        const double q = coef[i];
         const double *tx = &th[(3 * (size_t)i) * PME_ORDER], *ty = tx + PME_ORDER, *tz = ty + PME_ORDER;
         for (int ix = 0; ix < PME_ORDER; ix++) { const int x = (idx[3 * i] + ix) % nx;
             for (int iy = 0; iy < PME_ORDER; iy++) { const int y = (idx[3 * i + 1] + iy) % ny;
@@ -290,23 +320,30 @@ void oracle_reciprocal(const oracle_system* s, double* forces, double* energy) {
     fft3d(grid, nx, ny, nz, 0);
     double* mx_ = (double*)malloc(sizeof(double) * nx); double* my_ = (double*)malloc(sizeof(double) * ny); double* mz_ = (double*)malloc(sizeof(double) * nz);
     moduli(nx, mx_); moduli(ny, my_); moduli(nz, mz_);
-    const double factor = M_PI * M_PI / (s->alpha * s->alpha), boxfactor = M_PI * det;
+    const double factor = M_PI * M_PI / (alpha * alpha), boxfactor = M_PI * det;
+    const double dboxfactor = -2.0 * M_PI * sqrt(M_PI) / (6.0 * det), bfac = M_PI / alpha;
+    const double fac1 = 2.0 * M_PI * M_PI * M_PI * sqrt(M_PI), fac2 = alpha * alpha * alpha, fac3 = -2.0 * alpha * M_PI * M_PI;
     double esum = 0;
     for (int kx = 0; kx < nx; kx++) { const double mx = kx < (nx + 1) / 2 ? kx : kx - nx;
         for (int ky = 0; ky < ny; ky++) { const double my = ky < (ny + 1) / 2 ? ky : ky - ny;
             for (int kz = 0; kz < nz; kz++) { const double mz = kz < (nz + 1) / 2 ? kz : kz - nz;
                 double* g = &grid[2 * (((size_t)kx * ny + ky) * nz + kz)];
-                if (kx == 0 && ky == 0 && kz == 0) { g[0] = g[1] = 0; continue; }
+                if (!dispersion && kx == 0 && ky == 0 && kz == 0) { g[0] = g[1] = 0; continue; }
                 const double mhx = mx * R[0][0], mhy = mx * R[1][0] + my * R[1][1], mhz = mx * R[2][0] + my * R[2][1] + mz * R[2][2];
                 const double m2 = mhx * mhx + mhy * mhy + mhz * mhz;
-                const double eterm = ONE_4PI_EPS0 * exp(-factor * m2) / (m2 * boxfactor * mx_[kx] * my_[ky] * mz_[kz]);
+                double eterm;
+                if (!dispersion) eterm = ONE_4PI_EPS0 * exp(-factor * m2) / (m2 * boxfactor * mx_[kx] * my_[ky] * mz_[kz]);
+                else {
+                    const double m = sqrt(m2), bb = bfac * m;
+                    eterm = (fac1 * erfc(bb) * m * m2 + exp(-bb * bb) * (fac2 + fac3 * m2)) * dboxfactor / (mx_[kx] * my_[ky] * mz_[kz]);
+                }
                 esum += eterm * (g[0] * g[0] + g[1] * g[1]);
                 g[0] *= eterm; g[1] *= eterm; } } }
     if (energy) *energy += 0.5 * esum;
     if (forces) {
         fft3d(grid, nx, ny, nz, 1);
         for (int i = 0; i < n; i++) {
-            const double q = s->charge[i];
+            const double q = coef[i];
             const double *tx = &th[(3 * (size_t)i) * PME_ORDER], *ty = tx + PME_ORDER, *tz = ty + PME_ORDER;
             const double *dx = &dth[(3 * (size_t)i) * PME_ORDER], *dy = dx + PME_ORDER, *dz = dy + PME_ORDER;
             double fx = 0, fy = 0, fz = 0;
@@ -321,6 +358,16 @@ void oracle_reciprocal(const oracle_system* s, double* forces, double* energy) {
         }
     }
     free(grid); free(idx); free(th); free(dth); free(mx_); free(my_); free(mz_);
+}
+
+void oracle_reciprocal(const oracle_system* s, double* forces, double* energy) {
+    pme_sum(s, s->charge, s->alpha, s->grid, 0, forces, energy);
+    if (s->ljpme) {
+        double* c6 = (double*)malloc(sizeof(double) * (size_t)s->n);
+        for (int i = 0; i < s->n; i++) c6[i] = 8.0 * pow(0.5 * s->sigma[i], 3.0) * 2.0 * sqrt(s->epsilon[i]);   /* ReferenceLJCoulombIxn.cpp:259-260 */
+        pme_sum(s, c6, s->lj_alpha, s->lj_grid, 1, forces, energy);
+        free(c6);
+    }
 }
 
 void oracle_nonbonded(const oracle_system* s, int groups, double* forces, double* energy) {

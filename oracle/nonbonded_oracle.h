@@ -19,6 +19,9 @@ typedef struct {
     int nexc;  const int* exc;           /* exceptions with parameters [2*nexc] */
     const double* exc_qq; const double* exc_sigma; const double* exc_eps;
     int exceptions_periodic;
+    int ljpme;              /* 1: LJPME (dispersion treated with a second PME grid) */
+    double lj_alpha;        /* dispersion Ewald coefficient */
+    int lj_grid[3];         /* dispersion mesh */
 } oracle_system;
 
 /* direct space, pairs with r <= cutoff that are not excluded; forces [3n] are ADDED to; returns pair count.

@@ -8,6 +8,9 @@ exactly how they were made.
                        positions (float32), energies and forces of the direct and reciprocal force groups, and the
                        hash + count of the pair set of computeNeighborListVoxelHash.  N = 1536 (small box: per-pair
                        minimum image), 6000 (single periodic copy), 23558 (DHFR size; forces stored as float32).
+  ref_ljpme_<N>.npz    the same for NonbondedForce::LJPME (method 5): water_box(N) with CHARMM-style hydrogens (sigma 0.04 nm,
+                       eps 0.192464 kJ/mol) so that three particle types enter the dispersion grid; dispersion mesh and alpha
+                       as NonbondedForceImpl::calcPMEParameters(lj=true).  N = 1538, 6002.
   ref_ions_triclinic.npz  the 8-ion triclinic case of tests/TestEwald.h:220-269 evaluated by the Reference platform
 """
 import os
@@ -44,12 +47,12 @@ def nacl():
     np.save(os.path.join(HERE, "nacl_amorph.npy"), np.array(pos, dtype=np.float32))
 
 
-def ref_eval(sysd, cutoff, alpha, grid, pairs=True):
+def ref_eval(sysd, cutoff, alpha, grid, pairs=True, **kw):
     from openmm_b200 import workloads
     from oracle_lib import REF_DRIVER
     with tempfile.TemporaryDirectory() as td:
         sp, op = os.path.join(td, "s.bin"), os.path.join(td, "o.bin")
-        workloads.write_system_file(sp, sysd, cutoff, alpha, grid)
+        workloads.write_system_file(sp, sysd, cutoff, alpha, grid, **kw)
         subprocess.check_call([REF_DRIVER, "eval", sp, op, "--platform", "Reference"] + (["--pairs"] if pairs else []))
         return workloads.read_eval_file(op, sysd["n"])
 
@@ -69,6 +72,19 @@ def water(n, f32=False):
     print(n, "pairs", cnt, "E", r["e_direct"], r["e_recip"])
 
 
+def water_ljpme(n):
+    import openmm_b200 as b
+    from openmm_b200 import workloads
+    sysd = workloads.ljpme_water_box(n)
+    alpha, grid = b.pme_parameters(0.9, sysd["box"])
+    lj_alpha, lj_grid = b.pme_parameters(0.9, sysd["box"], lj=True)
+    r = ref_eval(sysd, 0.9, alpha, grid, pairs=False, method=5, lj_alpha=lj_alpha, lj_grid=lj_grid)
+    np.savez_compressed(os.path.join(HERE, f"ref_ljpme_{n}.npz"), positions=sysd["positions"].astype(np.float32), box=sysd["box"],
+                        alpha=alpha, grid=np.array(grid), lj_alpha=lj_alpha, lj_grid=np.array(lj_grid), cutoff=0.9,
+                        e_direct=r["e_direct"], e_recip=r["e_recip"], f_direct=r["f_direct"], f_recip=r["f_recip"])
+    print("ljpme", n, "E", r["e_direct"], r["e_recip"])
+
+
 def ions():
     pos = np.array([[1.744, 2.788, 3.162], [1.048, 0.762, 2.340], [2.489, 1.570, 2.817], [1.027, 1.893, 3.271],
                     [0.937, 0.825, 0.009], [2.290, 1.887, 3.352], [1.266, 1.111, 2.894], [0.933, 1.862, 3.490]])
@@ -81,8 +97,13 @@ def ions():
 
 
 if __name__ == "__main__":
-    tip3p()
-    nacl()
-    ions()
-    for n, f32 in ((1536, False), (6000, False), (23558, True)):
-        water(n, f32)
+    only = sys.argv[1:]
+    if not only or "base" in only:
+        tip3p()
+        nacl()
+        ions()
+        for n, f32 in ((1536, False), (6000, False), (23558, True)):
+            water(n, f32)
+    if not only or "ljpme" in only:
+        for n in (1538, 6002):
+            water_ljpme(n)

@@ -20,7 +20,8 @@ class OracleSystem(ctypes.Structure):
     _fields_ = [("n", ctypes.c_int), ("pos", c_double_p), ("charge", c_double_p), ("sigma", c_double_p), ("epsilon", c_double_p),
                 ("box", ctypes.c_double * 9), ("cutoff", ctypes.c_double), ("alpha", ctypes.c_double), ("grid", ctypes.c_int * 3),
                 ("nexcl", ctypes.c_int), ("excl", c_int_p), ("nexc", ctypes.c_int), ("exc", c_int_p),
-                ("exc_qq", c_double_p), ("exc_sigma", c_double_p), ("exc_eps", c_double_p), ("exceptions_periodic", ctypes.c_int)]
+                ("exc_qq", c_double_p), ("exc_sigma", c_double_p), ("exc_eps", c_double_p), ("exceptions_periodic", ctypes.c_int),
+                ("ljpme", ctypes.c_int), ("lj_alpha", ctypes.c_double), ("lj_grid", ctypes.c_int * 3)]
 
 
 _lib = None
@@ -38,7 +39,7 @@ def lib():
 
 
 class Oracle:
-    def __init__(self, sysd, cutoff, alpha, grid):
+    def __init__(self, sysd, cutoff, alpha, grid, lj_alpha=None, lj_grid=None):
         self.keep = []
         s = OracleSystem()
 
@@ -63,6 +64,10 @@ class Oracle:
             s.nexc, s.exc = len(exc[1]), i32(np.asarray(exc[0]).reshape(-1))
             s.exc_qq, s.exc_sigma, s.exc_eps = dbl(exc[1]), dbl(exc[2]), dbl(exc[3])
         s.exceptions_periodic = 0
+        if lj_alpha is not None:
+            s.ljpme, s.lj_alpha = 1, lj_alpha
+            for k in range(3):
+                s.lj_grid[k] = int(lj_grid[k])
         self.s = s
 
     def nonbonded(self, groups=3):
