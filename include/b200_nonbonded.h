@@ -94,6 +94,9 @@ int  b200_nonbonded_create(b200_ctx* ctx, const b200_nonbonded_desc* desc);
 int  b200_nonbonded_update_parameters(b200_ctx* ctx, const b200_nonbonded_desc* desc);
 /* CalcNonbondedForceKernel::getPMEParameters (kernels.h:678) */
 int  b200_nonbonded_get_pme_parameters(const b200_ctx* ctx, double* alpha, int32_t* nx, int32_t* ny, int32_t* nz);
+/* CalcNonbondedForceKernel::getLJPMEParameters (kernels.h:687; CommonCalcNonbondedForce.cpp:1269-1281): dispersion mesh,
+   B200_ERR_INVALID unless the force was created with method B200_NB_LJPME */
+int  b200_nonbonded_get_ljpme_parameters(const b200_ctx* ctx, double* alpha, int32_t* nx, int32_t* ny, int32_t* nz);
 
 /* CalcHarmonicBondForceKernel::initialize (kernels.h:347), harmonicBondForce.cc: E = k/2 (r-r0)^2 */
 int  b200_harmonic_bonds_create(b200_ctx* ctx, int32_t n, const int32_t* atoms /*[2n]*/, const double* length, const double* k, int32_t group);

@@ -59,7 +59,7 @@ class NblistStats(ctypes.Structure):
 # every symbol include/b200_nonbonded.h declares (tests/test_abi.py checks the header against this list and the .so)
 EXPORTED_SYMBOLS = [
     "b200_context_create", "b200_context_destroy", "b200_last_error", "b200_device_count", "b200_nonbonded_create",
-    "b200_nonbonded_update_parameters", "b200_nonbonded_get_pme_parameters", "b200_harmonic_bonds_create",
+    "b200_nonbonded_update_parameters", "b200_nonbonded_get_pme_parameters", "b200_nonbonded_get_ljpme_parameters", "b200_harmonic_bonds_create",
     "b200_harmonic_angles_create", "b200_periodic_torsions_create", "b200_set_positions", "b200_get_positions",
     "b200_set_velocities", "b200_get_velocities", "b200_get_forces", "b200_set_box", "b200_get_box", "b200_set_time",
     "b200_get_time", "b200_compute", "b200_compute_host", "b200_integrator_create", "b200_step", "b200_integrate",
@@ -161,9 +161,14 @@ class Context:
 
     # CalcNonbondedForceKernel::initialize
     def add_nonbonded_force(self, charge, sigma, epsilon, cutoff, alpha, grid, exclusions=(), exceptions=None,
-                            method=NB_PME, dispersion_coefficient=0.0, exceptions_use_periodic=False):
+                            method=NB_PME, dispersion_coefficient=0.0, exceptions_use_periodic=False, lj_alpha=None, lj_grid=None):
         d = NonbondedDesc()
         d.method = method
+        if lj_alpha is not None:      # NonbondedForce::LJPME with setLJPMEParameters(lj_alpha, *lj_grid)
+            d.method = NB_LJPME
+            d.ljpme_alpha = lj_alpha
+            for k in range(3):
+                d.ljpme_grid[k] = int(lj_grid[k])
         d.cutoff = cutoff
         d.ewald_alpha = alpha
         for k in range(3):

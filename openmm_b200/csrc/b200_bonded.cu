@@ -26,21 +26,39 @@ __device__ __forceinline__ void blockEnergy(double e, long long* slot) {
     if (threadIdx.x == 0 && red[0] != 0.0) atomicAddFixed(slot, toFixedD(red[0]));
 }
 
-__global__ void __launch_bounds__(128) exclusionCorrection(const float4* __restrict__ posq, const int2* __restrict__ pairs, int n, BoxD box, double alpha,
-                                                            long long* force, int Npad, DevCounters* counters, int wantForce, int wantEnergy) {
+__global__ void __launch_bounds__(128) exclusionCorrection(const float4* __restrict__ posq, const float2* __restrict__ sigEps, const int2* __restrict__ pairs, int n, BoxD box, double alpha,
+                                                            double ljAlpha, long long* force, int Npad, DevCounters* counters, int wantForce, int wantEnergy) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     double e = 0;
     if (t < n) {
         const int2 p = pairs[t];
         const float4 a = posq[p.x], b = posq[p.y];
         const double qq = B200_ONE_4PI_EPS0 * (double)a.w * (double)b.w;
+        if (sigEps) {
+            // LJPME: back out the reciprocal-space dispersion of the excluded pair (ReferenceLJCoulombIxn.cpp:497-513,
+            // pmeExclusions.cc USE_LJPME branch)
+            const float2 sa = sigEps[p.x], sb = sigEps[p.y];
+            const double c6 = 64.0 * ((double)sa.x * sa.x * sa.x * sa.y) * ((double)sb.x * sb.x * sb.x * sb.y);
+            if (c6 != 0.0) {
+                double dx = (double)b.x - a.x, dy = (double)b.y - a.y, dz = (double)b.z - a.z;
+                imageDeltaD(dx, dy, dz, box);
+                const double r2 = dx * dx + dy * dy + dz * dz, invR2 = 1.0 / r2, invR6 = invR2 * invR2 * invR2;
+                const double x = ljAlpha * ljAlpha * r2, x2 = x * x, ex = exp(-x);
+                e += c6 * invR6 * (1.0 - ex * (1.0 + x + 0.5 * x2));
+                if (wantForce) {
+                    const double s = 6.0 * c6 * invR6 * invR2 * (1.0 - ex * (1.0 + x + 0.5 * x2 + x2 * x / 6.0));   // -(dE/dr)/r
+                    addForce(force, Npad, p.x, D3{-dx * s, -dy * s, -dz * s});
+                    addForce(force, Npad, p.y, D3{dx * s, dy * s, dz * s});
+                }
+            }
+        }
         if (qq != 0.0) {
             double dx = (double)b.x - a.x, dy = (double)b.y - a.y, dz = (double)b.z - a.z;
             imageDeltaD(dx, dy, dz, box);
             const double r2 = dx * dx + dy * dy + dz * dz, r = sqrt(r2), ar = alpha * r;
             if (ar > 1e-6) {
                 const double erfAR = erf(ar), invR = 1.0 / r;
-                e = -qq * invR * erfAR;
+                e += -qq * invR * erfAR;
                 if (wantForce) {
                     // s = -(dE/dr)/r of E = -qq erf(alpha r)/r
                     const double s = -qq * invR * invR * invR * (erfAR - ar * 1.1283791670955126 * exp(-ar * ar));
@@ -48,7 +66,7 @@ __global__ void __launch_bounds__(128) exclusionCorrection(const float4* __restr
                     addForce(force, Npad, p.y, D3{dx * s, dy * s, dz * s});
                 }
             } else {
-                e = -alpha * 1.1283791670955126 * qq;   // r -> 0 limit (pmeExclusions.cc:54-56)
+                e += -alpha * 1.1283791670955126 * qq;   // r -> 0 limit (pmeExclusions.cc:54-56)
             }
         }
     }
@@ -196,7 +214,7 @@ void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy) 
     ScopedTimer tm(c, B200_T_BONDED, s);
     const int wf = forces ? 1 : 0, we = energy ? 1 : 0;
     if (c->hasNonbonded && (groups & B200_GROUP_DIRECT)) {
-        if (c->numExclPairs > 0) { exclusionCorrection<<<(c->numExclPairs + 127) / 128, 128, 0, s>>>(c->posq, c->dExclPairs, c->numExclPairs, c->boxD, c->nb.ewald_alpha, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
+        if (c->numExclPairs > 0) { exclusionCorrection<<<(c->numExclPairs + 127) / 128, 128, 0, s>>>(c->posq, c->ljpme ? c->sigEps : nullptr, c->dExclPairs, c->numExclPairs, c->boxD, c->nb.ewald_alpha, c->nb.ljpme_alpha, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
         if (c->numExceptions > 0) { exceptions14<<<(c->numExceptions + 127) / 128, 128, 0, s>>>(c->posq, c->dExcPairs, c->dExcParams, c->numExceptions, c->boxD, c->nb.exceptions_use_periodic, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
     }
     {

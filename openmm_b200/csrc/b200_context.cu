@@ -133,13 +133,23 @@ extern "C" void b200_context_destroy(b200_ctx* c) {
     delete c;
 }
 
+// LJPME: dispersion self term + alpha_d^6/12 * sum_i c6_i^2 with c6_i = 8 (sigma_i/2)^3 2 sqrt(eps_i)
+// (ReferenceLJCoulombIxn.cpp:224-227; CommonCalcNonbondedForce.cpp:401-406)
+static void b200_lj_self_energy(b200_ctx* c) {
+    c->ljSelfEnergy = 0;
+    if (!c->ljpme) return;
+    const double a6 = pow(c->nb.ljpme_alpha, 6.0);
+    for (int i = 0; i < c->N; i++) c->ljSelfEnergy += a6 * 64.0 * pow(0.5 * c->sigma[i], 6.0) * 4.0 * c->epsilon[i] / 12.0;
+}
+
 // ---------------------------------------------------------------------------------------------
 extern "C" int b200_nonbonded_create(b200_ctx* c, const b200_nonbonded_desc* d) {
     API_BEGIN
     if (!c || !d) throw B200Error(B200_ERR_INVALID, "b200_nonbonded_create: null argument");
     if (c->hasNonbonded) throw B200Error(B200_ERR_UNSUPPORTED, "only one NonbondedForce per context is supported");
     if (c->finalized) throw B200Error(B200_ERR_INVALID, "forces must be created before the first computation");
-    if (d->method != B200_NB_PME) throw B200Error(B200_ERR_UNSUPPORTED, "NonbondedForce: the B200 platform currently implements the PME method only");
+    if (d->method != B200_NB_PME && d->method != B200_NB_LJPME)
+        throw B200Error(B200_ERR_UNSUPPORTED, "NonbondedForce: the B200 platform currently implements the PME and LJPME methods only");
     if (d->use_switch) throw B200Error(B200_ERR_UNSUPPORTED, "NonbondedForce: switching function not implemented yet");
     CUDA_CHECK(cudaSetDevice(c->device));
     c->nb = *d;
@@ -154,6 +164,14 @@ extern "C" int b200_nonbonded_create(b200_ctx* c, const b200_nonbonded_desc* d) 
     for (int k = 0; k < 3; k++) {
         if (d->grid[k] < 6 || b200_find_legal_fft_dimension(d->grid[k]) != d->grid[k])
             throw B200Error(B200_ERR_INVALID, "PME grid dimensions must be >= 6 and factor into 2,3,5,7");
+    }
+    c->ljpme = d->method == B200_NB_LJPME;
+    if (c->ljpme) {
+        if (!(d->ljpme_alpha > 0)) throw B200Error(B200_ERR_INVALID, "LJPME: the dispersion Ewald coefficient must be positive");
+        for (int k = 0; k < 3; k++)
+            if (d->ljpme_grid[k] < 6 || b200_find_legal_fft_dimension(d->ljpme_grid[k]) != d->ljpme_grid[k])
+                throw B200Error(B200_ERR_INVALID, "LJPME grid dimensions must be >= 6 and factor into 2,3,5,7");
+        c->nb.dispersion_coefficient = 0;   // no long-range correction with LJPME (CommonCalcNonbondedForce.cpp:360)
     }
     c->hasNonbonded = true;
     // list cutoff = cutoff + padding (CudaNonbondedUtilities.cpp:380-383 uses 8% of the cutoff)
@@ -183,6 +201,7 @@ extern "C" int b200_nonbonded_create(b200_ctx* c, const b200_nonbonded_desc* d) 
     c->totalCharge = sumQ;
     // Ewald self energy (CommonCalcNonbondedForce.cpp:397-400)
     c->selfEnergy = -B200_ONE_4PI_EPS0 * d->ewald_alpha * sumQ2 / sqrt(M_PI);
+    b200_lj_self_energy(c);
     b200_pme_create(c);
     API_END
 }
@@ -191,6 +210,13 @@ extern "C" int b200_nonbonded_get_pme_parameters(const b200_ctx* c, double* alph
     API_BEGIN
     if (!c || !c->hasNonbonded) throw B200Error(B200_ERR_INVALID, "no NonbondedForce in this context");
     *alpha = c->nb.ewald_alpha; *nx = c->nb.grid[0]; *ny = c->nb.grid[1]; *nz = c->nb.grid[2];
+    API_END
+}
+
+extern "C" int b200_nonbonded_get_ljpme_parameters(const b200_ctx* c, double* alpha, int32_t* nx, int32_t* ny, int32_t* nz) {
+    API_BEGIN
+    if (!c || !c->hasNonbonded || !c->ljpme) throw B200Error(B200_ERR_INVALID, "this context is not using LJPME");
+    *alpha = c->nb.ljpme_alpha; *nx = c->nb.ljpme_grid[0]; *ny = c->nb.ljpme_grid[1]; *nz = c->nb.ljpme_grid[2];
     API_END
 }
 
@@ -206,7 +232,7 @@ extern "C" int b200_nonbonded_update_parameters(b200_ctx* c, const b200_nonbonde
     c->excQQ.assign(d->exception_chargeprod, d->exception_chargeprod + d->num_exceptions);
     c->excSig.assign(d->exception_sigma, d->exception_sigma + d->num_exceptions);
     c->excEps.assign(d->exception_epsilon, d->exception_epsilon + d->num_exceptions);
-    c->nb.dispersion_coefficient = d->dispersion_coefficient;
+    c->nb.dispersion_coefficient = c->ljpme ? 0.0 : d->dispersion_coefficient;
     b200_sync_host_order(c);
     std::vector<float2> se(c->Npad, make_float2(0.f, 0.f));
     std::vector<float4> p(c->Npad);
@@ -223,6 +249,7 @@ extern "C" int b200_nonbonded_update_parameters(b200_ctx* c, const b200_nonbonde
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
     c->totalCharge = sumQ;
     c->selfEnergy = -B200_ONE_4PI_EPS0 * c->nb.ewald_alpha * sumQ2 / sqrt(M_PI);
+    b200_lj_self_energy(c);
     if (c->finalized && c->numExceptions > 0) {
         std::vector<float4> xq;
         for (size_t i = 0; i < c->excQQ.size(); i++) xq.push_back(make_float4((float)(B200_ONE_4PI_EPS0 * c->excQQ[i]), (float)c->excSig[i], (float)(4.0 * c->excEps[i]), 0.f));
@@ -671,7 +698,7 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
             e += inv * (double)h.energy[E_RECIP];
             const double* b = c->boxHost; const double V = b[0] * b[4] * b[8];
             // host-side constants (CommonCalcNonbondedForce.cpp:893-898): self energy and neutralising plasma
-            e += c->selfEnergy;
+            e += c->selfEnergy + c->ljSelfEnergy;
             e -= c->totalCharge * c->totalCharge * M_PI * B200_ONE_4PI_EPS0 / (2.0 * V * c->nb.ewald_alpha * c->nb.ewald_alpha);
         }
         if (doDirect && extras && c->nb.dispersion_coefficient != 0) {

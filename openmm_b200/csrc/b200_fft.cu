@@ -205,9 +205,15 @@ __global__ void __launch_bounds__(FFT_THREADS) fftXConvolve(float2* __restrict__
         const int mx = kx < (a.nx + 1) / 2 ? kx : kx - a.nx, my = ky < (a.ny + 1) / 2 ? ky : ky - a.ny, mz = kz;   // kz <= nz/2
         const float mhx = mx * (float)a.r0x, mhy = mx * (float)a.r1x + my * (float)a.r1y, mhz = mx * (float)a.r2x + my * (float)a.r2y + mz * (float)a.r2z;
         const float m2 = mhx * mhx + mhy * mhy + mhz * mhz;
-        const float denom = m2 * modX[kx] * modY[ky] * modZ[kz];
-        float eterm = a.scale * __expf(-a.alphaFactor * m2) / denom;
-        if (kx == 0 && q == 0) eterm = 0.f;
+        float eterm;
+        if (!a.dispersion) {
+            const float denom = m2 * modX[kx] * modY[ky] * modZ[kz];
+            eterm = a.scale * __expf(-a.alphaFactor * m2) / denom;
+            if (kx == 0 && q == 0) eterm = 0.f;
+        } else {   // dispersion mesh: k = 0 is kept (ReferencePME.cpp:336-410, pme.cc reciprocalConvolution USE_LJPME)
+            const float m = sqrtf(m2), bb = a.bfac * m;
+            eterm = a.scale * (a.fac1 * erfcf(bb) * m * m2 + expf(-bb * bb) * (a.fac2 + a.fac3 * m2)) / (modX[kx] * modY[ky] * modZ[kz]);
+        }
         const float2 g = r[kx * pitch + l];
         if (ENERGY) {
             const float wgt = (kz == 0 || (2 * kz == a.nz)) ? 1.f : 2.f;   // Hermitian mirror of the missing half
@@ -281,15 +287,6 @@ void b200_fft3d_exec_c2r(int nx, int ny, int nz, const FFTPlan1D* plan, float2* 
     const int lines = nx * ny;
     fftZInverse<<<(lines + batch - 1) / batch, FFT_THREADS, sm, s>>>(in, out, lines, plan[2], batch, pitch, tw[2]);
     CUDA_CHECK(cudaGetLastError());
-}
-
-void b200_fft3d_forward(b200_ctx* c, cudaStream_t s) {
-    b200_fft3d_exec_r2c(c->gridN[0], c->gridN[1], c->gridN[2], c->plan, c->twiddle, nullptr, c->gridI, 1.0f / c->spreadScale, c->gridC, nullptr, s);
-    LAUNCH_COUNT(c, 3);
-}
-void b200_fft3d_inverse(b200_ctx* c, cudaStream_t s) {
-    b200_fft3d_exec_c2r(c->gridN[0], c->gridN[1], c->gridN[2], c->plan, c->twiddle, c->gridC, nullptr, c->gridReal, s);
-    LAUNCH_COUNT(c, 3);
 }
 
 // ---- host-buffer entry points for unit tests (TestCudaFFT3D.cpp:56-121 compares against pocketfft the same way)
@@ -384,20 +381,20 @@ extern "C" int b200_fft3d_c2r_noalloc(int32_t device, int32_t nx, int32_t ny, in
 }
 
 // whole reciprocal-space pipeline on the context's grids: int charge grid -> spectrum -> convolution (+energy) -> potential grid
-void b200_fft3d_reciprocal(b200_ctx* c, cudaStream_t s, const PmeArgs& a, bool energy, bool forces) {
-    const int nx = c->gridN[0], ny = c->gridN[1], nz = c->gridN[2], nzc = nz / 2 + 1;
+void b200_fft3d_reciprocal(b200_ctx* c, PmeMesh& m, cudaStream_t s, const PmeArgs& a, bool energy, bool forces) {
+    const int nx = m.gridN[0], ny = m.gridN[1], nz = m.gridN[2], nzc = nz / 2 + 1;
     int batch, pitch; size_t sm;
     pickBatch(nz, batch, pitch, sm);
     allowSmem(fftZForward, sm);
     const int lines = nx * ny;
-    fftZForward<<<(lines + batch - 1) / batch, FFT_THREADS, sm, s>>>(nullptr, c->gridI, 1.0f / c->spreadScale, c->gridC, lines, c->plan[2], batch, pitch, c->twiddle[2]);
+    fftZForward<<<(lines + batch - 1) / batch, FFT_THREADS, sm, s>>>(nullptr, m.gridI, 1.0f / m.spreadScale, m.gridC, lines, m.plan[2], batch, pitch, m.twiddle[2]);
     pickBatch(ny, batch, pitch, sm);
     allowSmem(fftStrided<false>, sm);
-    fftStrided<false><<<dim3((nzc + batch - 1) / batch, nx), FFT_THREADS, sm, s>>>(c->gridC, nzc, (size_t)ny * nzc, (size_t)nzc, c->plan[1], batch, pitch, c->twiddle[1]);
+    fftStrided<false><<<dim3((nzc + batch - 1) / batch, nx), FFT_THREADS, sm, s>>>(m.gridC, nzc, (size_t)ny * nzc, (size_t)nzc, m.plan[1], batch, pitch, m.twiddle[1]);
     pickBatch(nx, batch, pitch, sm);
     const int inner = ny * nzc;
     const dim3 grid((inner + batch - 1) / batch);
-#define LAUNCH_XCONV(E, I) do { allowSmem(fftXConvolve<E, I>, sm); fftXConvolve<E, I><<<grid, FFT_THREADS, sm, s>>>(c->gridC, inner, (size_t)ny * nzc, c->plan[0], batch, pitch, c->twiddle[0], a, c->moduli[0], c->moduli[1], c->moduli[2], c->counters); } while (0)
+#define LAUNCH_XCONV(E, I) do { allowSmem(fftXConvolve<E, I>, sm); fftXConvolve<E, I><<<grid, FFT_THREADS, sm, s>>>(m.gridC, inner, (size_t)ny * nzc, m.plan[0], batch, pitch, m.twiddle[0], a, m.moduli[0], m.moduli[1], m.moduli[2], c->counters); } while (0)
     if (energy && forces) LAUNCH_XCONV(true, true);
     else if (energy) LAUNCH_XCONV(true, false);
     else LAUNCH_XCONV(false, true);
@@ -406,10 +403,10 @@ void b200_fft3d_reciprocal(b200_ctx* c, cudaStream_t s, const PmeArgs& a, bool e
     if (forces) {
         pickBatch(ny, batch, pitch, sm);
         allowSmem(fftStrided<true>, sm);
-        fftStrided<true><<<dim3((nzc + batch - 1) / batch, nx), FFT_THREADS, sm, s>>>(c->gridC, nzc, (size_t)ny * nzc, (size_t)nzc, c->plan[1], batch, pitch, c->twiddle[1]);
+        fftStrided<true><<<dim3((nzc + batch - 1) / batch, nx), FFT_THREADS, sm, s>>>(m.gridC, nzc, (size_t)ny * nzc, (size_t)nzc, m.plan[1], batch, pitch, m.twiddle[1]);
         pickBatch(nz, batch, pitch, sm);
         allowSmem(fftZInverse, sm);
-        fftZInverse<<<(lines + batch - 1) / batch, FFT_THREADS, sm, s>>>(c->gridC, c->gridReal, lines, c->plan[2], batch, pitch, c->twiddle[2]);
+        fftZInverse<<<(lines + batch - 1) / batch, FFT_THREADS, sm, s>>>(m.gridC, m.gridReal, lines, m.plan[2], batch, pitch, m.twiddle[2]);
         LAUNCH_COUNT(c, 2);
     }
     CUDA_CHECK(cudaGetLastError());

@@ -59,13 +59,29 @@ struct PmeArgs {
     int nx, ny, nz, nzc;
     double r0x, r1x, r1y, r2x, r2y, r2z;   // reciprocal box (rows as in CommonCalcNonbondedForce.cpp:950-957)
     float alphaFactor;                      // pi^2/alpha^2
-    float scale;                            // ONE_4PI_EPS0/(pi V)
+    float scale;                            // ONE_4PI_EPS0/(pi V); dispersion: -2 pi sqrt(pi)/(6 V)
+    int dispersion;                         // 1: dispersion mesh (reciprocalConvolution with USE_LJPME, pme.cc:137-200)
+    float bfac, fac1, fac2, fac3;           // dispersion convolution constants (ReferencePME.cpp:336-410)
 };
 
 struct FFTPlan1D {
     int n;
     int nstages;
     int radix[12];
+};
+
+// one reciprocal-space mesh with its transforms
+struct PmeMesh {
+    int gridN[3] = {0, 0, 0}; int nzc = 0;
+    int* gridI = nullptr;           // coefficient grid (spread target), 32-bit fixed point
+    float spreadScale = 67108864.f; // fixed-point scale of the shared-memory accumulation in the spread kernel
+    float* gridReal = nullptr;      // potential grid after the inverse transform
+    float2* gridC = nullptr;        // half-complex spectrum, transformed in place
+    float* moduli[3] = {nullptr, nullptr, nullptr};
+    float2* twiddle[3] = {nullptr, nullptr, nullptr};
+    FFTPlan1D plan[3];
+    double alpha = 0;
+    bool dispersion = false;        // spread 8 (sigma/2)^3 2 sqrt(eps) instead of the charge; dispersion convolution
 };
 
 struct TimerSlot {
@@ -146,15 +162,10 @@ struct b200_ctx {
     double partShareBegin = 0.0, partShareEnd = 1.0;           // this rank's slice of the exclusion-tile index range
     int sparseMax = 5;             // j atoms reaching at most this many atoms of X are handled as sparse pairs
 
-    // PME
-    int gridN[3] = {0, 0, 0}; int nzc = 0;
-    int* gridI = nullptr;           // charge grid (spread target), 32-bit fixed point
-    float spreadScale = 67108864.f; // fixed-point scale of the shared-memory accumulation in the spread kernel
-    float* gridReal = nullptr;      // potential grid after the inverse transform
-    float2* gridC = nullptr;        // half-complex spectrum, transformed in place
-    float* moduli[3] = {nullptr, nullptr, nullptr};
-    float2* twiddle[3] = {nullptr, nullptr, nullptr};
-    FFTPlan1D plan[3];
+    // PME: mesh[0] = Coulomb, mesh[1] = dispersion (LJPME only)
+    PmeMesh mesh[2];
+    bool ljpme = false;
+    double ljSelfEnergy = 0;        // + alpha_d^6/12 * sum c6_i^2 (ReferenceLJCoulombIxn.cpp:224-227)
 
     // bonded
     int numBonds = 0; int2* bondAtoms = nullptr; float2* bondParams = nullptr;
@@ -214,9 +225,7 @@ void b200_comm_allreduce_energy(b200_ctx* c);
 void b200_comm_destroy(b200_ctx* c);
 void b200_fft_make_plan(int n, FFTPlan1D& plan);
 void b200_fft_make_twiddle(int n, float2*& dTw, cudaStream_t s);
-void b200_fft3d_forward(b200_ctx* c, cudaStream_t s);  // gridI -> gridC
-void b200_fft3d_inverse(b200_ctx* c, cudaStream_t s);  // gridC -> gridReal
-void b200_fft3d_reciprocal(b200_ctx* c, cudaStream_t s, const PmeArgs& a, bool energy, bool forces);   // gridI -> (convolution, energy) -> gridReal
+void b200_fft3d_reciprocal(b200_ctx* c, PmeMesh& m, cudaStream_t s, const PmeArgs& a, bool energy, bool forces);   // gridI -> (convolution, energy) -> gridReal
 void b200_fft3d_exec_r2c(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, const float* inReal, const int* inFix, float fixScaleInv, float2* out, float2* scratch, cudaStream_t s);
 void b200_fft3d_exec_c2r(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, float2* in, float2* scratch, float* out, cudaStream_t s);
 void b200_compute_impl(b200_ctx* c, unsigned groups, bool forces, bool energy, double* energyOut);

@@ -42,6 +42,9 @@ __device__ __forceinline__ void bspline5(float u, float* w, float* dw) {
     for (int k = 0; k < PME_ORDER; k++) w[k] = a[k];
 }
 
+// LJPME: the quantity spread on the dispersion mesh is c6_i = 8 (sigma_i/2)^3 * 2 sqrt(eps_i)  (ReferenceLJCoulombIxn.cpp:259-260)
+__device__ __forceinline__ float dispersionCoefficient(float2 se) { return 8.0f * se.x * se.x * se.x * se.y; }
+
 __device__ __forceinline__ void gridCoords(const float4 p, const PmeArgs& a, int& ix, int& iy, int& iz, float& ux, float& uy, float& uz) {
     // fractional coordinates in double: the only error left is the float rounding of the stored position
     const double x = p.x, y = p.y, z = p.z;
@@ -91,12 +94,12 @@ __device__ __forceinline__ void chunkBox(bool valid, int ix, int iy, int iz, con
 }
 
 // charge spreading (gridSpreadCharge, pme.cc:23-121)
-__global__ void __launch_bounds__(CHUNK) pmeSpreadChunks(const float4* __restrict__ posq, int N, PmeArgs a, int* __restrict__ grid, float fixScale) {
+__global__ void __launch_bounds__(CHUNK) pmeSpreadChunks(const float4* __restrict__ posq, const float2* __restrict__ sigEps, int N, PmeArgs a, int* __restrict__ grid, float fixScale) {
     __shared__ int tile[TILE_MAX];
     __shared__ int sh[10];
     const int i = blockIdx.x * CHUNK + threadIdx.x;
     float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (i < N) p = posq[i];
+    if (i < N) { p = posq[i]; if (sigEps) p.w = dispersionCoefficient(sigEps[i]); }
     int ix = 0, iy = 0, iz = 0; float ux = 0.f, uy = 0.f, uz = 0.f;
     gridCoords(p, a, ix, iy, iz, ux, uy, uz);
     const bool valid = i < N && p.w != 0.f;
@@ -161,12 +164,12 @@ __global__ void __launch_bounds__(CHUNK) pmeSpreadChunks(const float4* __restric
 
 // force interpolation (gridInterpolateForce, pme.cc:255-356): same chunking; the box of potential values the chunk's atoms
 // read is staged in shared memory once (coalesced), then every atom gathers its 125 values from there
-__global__ void __launch_bounds__(CHUNK) pmeInterpolateChunks(const float4* __restrict__ posq, int N, int Npad, PmeArgs a, const float* __restrict__ phi, long long* __restrict__ force) {
+__global__ void __launch_bounds__(CHUNK) pmeInterpolateChunks(const float4* __restrict__ posq, const float2* __restrict__ sigEps, int N, int Npad, PmeArgs a, const float* __restrict__ phi, long long* __restrict__ force) {
     __shared__ float tile[TILE_MAX];
     __shared__ int sh[10];
     const int i = blockIdx.x * CHUNK + threadIdx.x;
     float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (i < N) p = posq[i];
+    if (i < N) { p = posq[i]; if (sigEps) p.w = dispersionCoefficient(sigEps[i]); }
     int ix = 0, iy = 0, iz = 0; float ux = 0.f, uy = 0.f, uz = 0.f;
     gridCoords(p, a, ix, iy, iz, ux, uy, uz);
     const bool valid = i < N && p.w != 0.f;
@@ -255,55 +258,77 @@ static std::vector<float> splineModuli(int n) {
     return out;
 }
 
-void b200_pme_create(b200_ctx* c) {
-    for (int k = 0; k < 3; k++) c->gridN[k] = c->nb.grid[k];
-    const int nx = c->gridN[0], ny = c->gridN[1], nz = c->gridN[2];
-    c->nzc = nz / 2 + 1;
-    const size_t G = (size_t)nx * ny * nz, GC = (size_t)nx * ny * c->nzc;
-    dmalloc(c->gridI, G); dmalloc(c->gridReal, G); dmalloc(c->gridC, GC);
-    {
-        double maxQ = 0; for (double q : c->charge) maxQ = std::max(maxQ, std::fabs(q));
+static void meshCreate(b200_ctx* c, PmeMesh& m, const int* grid, double alpha, bool dispersion, double maxCoef) {
+    for (int k = 0; k < 3; k++) m.gridN[k] = grid[k];
+    const int nx = m.gridN[0], ny = m.gridN[1], nz = m.gridN[2];
+    m.nzc = nz / 2 + 1; m.alpha = alpha; m.dispersion = dispersion;
+    const size_t G = (size_t)nx * ny * nz, GC = (size_t)nx * ny * m.nzc;
+    dmalloc(m.gridI, G); dmalloc(m.gridReal, G); dmalloc(m.gridC, GC);
+    {   // fixed-point scale: |coefficient| * scale <= 1.5 * 2^26 ~ 2^26.6, leaving a factor >= 21 of head-room for the sum at one point
         int bits = 26; double lim = 1.5;
-        while (maxQ > lim && bits > 12) { bits--; lim *= 2; }
-        c->spreadScale = (float)std::ldexp(1.0, bits);
+        while (maxCoef > lim && bits > 12) { bits--; lim *= 2; }
+        while (maxCoef > 0 && maxCoef <= 0.5 * lim && bits < 36) { bits++; lim *= 0.5; }
+        if (dispersion) bits -= 2;   // every coefficient is positive: sums do not cancel, keep more head-room
+        m.spreadScale = (float)std::ldexp(1.0, bits);
     }
     for (int k = 0; k < 3; k++) {
-        const std::vector<float> m = splineModuli(c->gridN[k]);
-        dmalloc(c->moduli[k], m.size());
-        CUDA_CHECK(cudaMemcpy(c->moduli[k], m.data(), sizeof(float) * m.size(), cudaMemcpyHostToDevice));
-        b200_fft_make_plan(c->gridN[k], c->plan[k]);
-        b200_fft_make_twiddle(c->gridN[k], c->twiddle[k], c->stream);
+        const std::vector<float> mod = splineModuli(m.gridN[k]);
+        dmalloc(m.moduli[k], mod.size());
+        CUDA_CHECK(cudaMemcpy(m.moduli[k], mod.data(), sizeof(float) * mod.size(), cudaMemcpyHostToDevice));
+        b200_fft_make_plan(m.gridN[k], m.plan[k]);
+        b200_fft_make_twiddle(m.gridN[k], m.twiddle[k], c->stream);
     }
 }
 
-void b200_pme_destroy(b200_ctx* c) {
-    dfree(c->gridI); dfree(c->gridReal); dfree(c->gridC);
-    for (int k = 0; k < 3; k++) { dfree(c->moduli[k]); dfree(c->twiddle[k]); }
+static void meshDestroy(PmeMesh& m) {
+    dfree(m.gridI); dfree(m.gridReal); dfree(m.gridC);
+    for (int k = 0; k < 3; k++) { dfree(m.moduli[k]); dfree(m.twiddle[k]); }
 }
 
-void b200_pme_launch(b200_ctx* c, cudaStream_t s, bool forces, bool energy) {
+void b200_pme_create(b200_ctx* c) {
+    double maxQ = 0; for (double q : c->charge) maxQ = std::max(maxQ, std::fabs(q));
+    meshCreate(c, c->mesh[0], c->nb.grid, c->nb.ewald_alpha, false, std::max(maxQ, 0.75 + 1e-9));
+    if (c->ljpme) {
+        double maxC6 = 0;
+        for (int i = 0; i < c->N; i++) maxC6 = std::max(maxC6, 8.0 * pow(0.5 * c->sigma[i], 3.0) * 2.0 * sqrt(c->epsilon[i]));
+        meshCreate(c, c->mesh[1], c->nb.ljpme_grid, c->nb.ljpme_alpha, true, maxC6);
+    }
+}
+
+void b200_pme_destroy(b200_ctx* c) { meshDestroy(c->mesh[0]); meshDestroy(c->mesh[1]); }
+
+static void meshLaunch(b200_ctx* c, PmeMesh& m, cudaStream_t s, bool forces, bool energy) {
     PmeArgs a;
-    a.nx = c->gridN[0]; a.ny = c->gridN[1]; a.nz = c->gridN[2]; a.nzc = c->nzc;
+    a.nx = m.gridN[0]; a.ny = m.gridN[1]; a.nz = m.gridN[2]; a.nzc = m.nzc;
     const BoxD& b = c->boxD;
     const double det = b.ax * b.by * b.cz, sc = 1.0 / det;
     a.r0x = b.by * b.cz * sc;
     a.r1x = -b.bx * b.cz * sc; a.r1y = b.ax * b.cz * sc;
     a.r2x = (b.bx * b.cy - b.by * b.cx) * sc; a.r2y = -b.ax * b.cy * sc; a.r2z = b.ax * b.by * sc;
-    a.alphaFactor = (float)(M_PI * M_PI / (c->nb.ewald_alpha * c->nb.ewald_alpha));
-    a.scale = (float)(B200_ONE_4PI_EPS0 / (M_PI * det));
+    a.alphaFactor = (float)(M_PI * M_PI / (m.alpha * m.alpha));
+    a.dispersion = m.dispersion ? 1 : 0;
+    a.scale = (float)(m.dispersion ? -2.0 * M_PI * sqrt(M_PI) / (6.0 * det) : B200_ONE_4PI_EPS0 / (M_PI * det));
+    a.bfac = (float)(M_PI / m.alpha); a.fac1 = (float)(2.0 * M_PI * M_PI * M_PI * sqrt(M_PI));
+    a.fac2 = (float)(m.alpha * m.alpha * m.alpha); a.fac3 = (float)(-2.0 * m.alpha * M_PI * M_PI);
     const size_t G = (size_t)a.nx * a.ny * a.nz;
     const int chunks = (c->N + CHUNK - 1) / CHUNK;
+    const float2* coef = m.dispersion ? c->sigEps : nullptr;
     {
         ScopedTimer tm(c, B200_T_SPREAD, s);
-        CUDA_CHECK(cudaMemsetAsync(c->gridI, 0, sizeof(int) * G, s));
-        pmeSpreadChunks<<<chunks, CHUNK, 0, s>>>(c->posq, c->N, a, c->gridI, c->spreadScale);
+        CUDA_CHECK(cudaMemsetAsync(m.gridI, 0, sizeof(int) * G, s));
+        pmeSpreadChunks<<<chunks, CHUNK, 0, s>>>(c->posq, coef, c->N, a, m.gridI, m.spreadScale);
         LAUNCH_COUNT(c, 1);
     }
-    { ScopedTimer tm(c, B200_T_FFT, s); b200_fft3d_reciprocal(c, s, a, energy, forces); }
+    { ScopedTimer tm(c, B200_T_FFT, s); b200_fft3d_reciprocal(c, m, s, a, energy, forces); }
     if (forces) {
         ScopedTimer tm(c, B200_T_INTERPOLATE, s);
-        pmeInterpolateChunks<<<chunks, CHUNK, 0, s>>>(c->posq, c->N, c->Npad, a, c->gridReal, c->force);
+        pmeInterpolateChunks<<<chunks, CHUNK, 0, s>>>(c->posq, coef, c->N, c->Npad, a, m.gridReal, c->force);
         LAUNCH_COUNT(c, 1);
     }
     CUDA_CHECK(cudaGetLastError());
+}
+
+void b200_pme_launch(b200_ctx* c, cudaStream_t s, bool forces, bool energy) {
+    meshLaunch(c, c->mesh[0], s, forces, energy);
+    if (c->ljpme) meshLaunch(c, c->mesh[1], s, forces, energy);
 }

@@ -50,6 +50,7 @@ struct TileArgs {
     float rc2, rcPadded, alpha2, alpha3, alpha, kcoul;
     double rc2d;
     float borderTol;             // |r2-rc2| below this -> FP64 decision
+    float ljAlpha2, invCut6, ljShift;   // LJPME: alpha_d^2, rc^-6, rc^-6 (1 - exp(-x)(1 + x + x^2/2)) at x = (alpha_d rc)^2
     int periodic;
 };
 
@@ -57,8 +58,10 @@ __device__ __forceinline__ float fast_rsqrt(float x) { float y; asm("rsqrt.appro
 __device__ __forceinline__ float fast_rcp(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
 // s = -(dE/dr)/r, e = pair energy
-template <bool ENERGY, bool EXACT>
-__device__ __forceinline__ void pairTerms(const TileArgs& a, float r2, float qq, float sig, float eps, float& s, float& e) {
+// LJPME (coulombLennardJones.cc:30-62, ReferenceLJCoulombIxn.cpp:352-376): sprod = (sigma_i/2)(sigma_j/2), so that
+// c6_i c6_j = 64 sprod^3 * eps with eps = 2 sqrt(eps_i) 2 sqrt(eps_j)
+template <bool ENERGY, bool EXACT, bool LJPME = false>
+__device__ __forceinline__ void pairTerms(const TileArgs& a, float r2, float qq, float sig, float eps, float& s, float& e, float sprod = 0.f) {
     const float invR = fast_rsqrt(r2);
     const float invR2 = invR * invR;
     float sc, ec = 0.f;
@@ -90,6 +93,19 @@ __device__ __forceinline__ void pairTerms(const TileArgs& a, float r2, float qq,
     const float es6 = eps * sr6;
     s = fmaf(es6 * invR2, fmaf(12.0f, sr6, -6.0f), sc);
     if (ENERGY) e = fmaf(es6, sr6 - 1.0f, ec);
+    if (LJPME) {
+        const float dar2 = a.ljAlpha2 * r2, dar4 = dar2 * dar2;
+        const float ex = __expf(-dar2);
+        const float c6 = 64.0f * sprod * sprod * sprod * eps;
+        const float coef = c6 * invR2 * invR2 * invR2;
+        const float epre = 1.0f + dar2 + 0.5f * dar4;
+        const float dpre = fmaf(dar4 * dar2, 1.0f / 6.0f, epre);
+        s = fmaf(6.0f * coef * invR2, fmaf(-ex, dpre, 1.0f), s);
+        if (ENERGY) {
+            const float sg2 = sig * sig, sc6 = sg2 * sg2 * sg2 * a.invCut6;
+            e += coef * fmaf(-ex, epre, 1.0f) + eps * (1.0f - sc6) * sc6 - c6 * a.ljShift;
+        }
+    }
 }
 
 // FP64 decision for pairs that fall within rounding distance of the cutoff (rare)
@@ -133,7 +149,7 @@ __device__ __forceinline__ float2 dup(float v) { return make_float2(v, v); }
 
 // Rare: a pair whose r^2 is within rounding distance of the cutoff was decided in float inside the tile loop; re-decide it in
 // FP64 and, if the decision changes, add or remove that single pair (kept out of line so the hot loop stays small).
-template <bool FORCES, bool ENERGY, bool EXACT, bool EXCL>
+template <bool FORCES, bool ENERGY, bool EXACT, bool EXCL, bool LJPME>
 __device__ __forceinline__ void fixBorderline(const TileArgs& a, const WarpSmem& sm, int lane, unsigned borderMask, unsigned exclRot, int slotI, bool validI,
                                            float xi, float yi, float zi, float qik, float2 pri, float& fix, float& fiy, float& fiz, float& eTile) {
     while (borderMask) {
@@ -150,7 +166,7 @@ __device__ __forceinline__ void fixBorderline(const TileArgs& a, const WarpSmem&
         const bool inF = r2 < a.rc2, inD = borderlineInside(a, slotI, sj);
         if (inF == inD) continue;
         float s, e;
-        pairTerms<ENERGY, EXACT>(a, r2, qik * q.w, pri.x + pr.x, pri.y * pr.y, s, e);
+        pairTerms<ENERGY, EXACT, LJPME>(a, r2, qik * q.w, pri.x + pr.x, pri.y * pr.y, s, e, pri.x * pr.x);
         const float sg = inD ? 1.f : -1.f;
         if (FORCES) {
             const float gx = sg * dx * s, gy = sg * dy * s, gz = sg * dz * s;
@@ -166,7 +182,7 @@ __device__ __forceinline__ void fixBorderline(const TileArgs& a, const WarpSmem&
 // one dense 32x32 tile: lane owns atom i = lane of block X; at step k it meets j = (lane+k)&31.
 // FIXUP: decide the cutoff in float inside the loop, remember borderline pairs in a bit mask and correct them afterwards
 // (single-copy force/energy variants); otherwise decide exactly inside the loop.
-template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT, bool SINGLE, bool EXCL>
+template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT, bool SINGLE, bool EXCL, bool LJPME>
 __device__ __forceinline__ void denseTile(const TileArgs& a, const WarpSmem& sm, int lane, int slotI, bool validI, float xi, float yi, float zi, float qik, float2 pri,
                                           unsigned exclBits, float& fix, float& fiy, float& fiz, float& fjx, float& fjy, float& fjz, float& eTile, unsigned long long& nPairs) {
     constexpr bool FIXUP = SINGLE && !EMIT;
@@ -195,7 +211,7 @@ _Pragma(TILE_STR(unroll TILE_UNROLL))
         if (EXCL) in = in && !((exclRot >> k) & 1u);
         if (!SINGLE) in = in && ok;
         float s, e;
-        pairTerms<ENERGY, EXACT>(a, r2, qik * q.w, pri.x + pr.x, pri.y * pr.y, s, e);
+        pairTerms<ENERGY, EXACT, LJPME>(a, r2, qik * q.w, pri.x + pr.x, pri.y * pr.y, s, e, pri.x * pr.x);
         s = in ? s : 0.f;
         if (FORCES) {
             fix = fmaf(-dx, s, fix); fiy = fmaf(-dy, s, fiy); fiz = fmaf(-dz, s, fiz);
@@ -210,7 +226,7 @@ _Pragma(TILE_STR(unroll TILE_UNROLL))
     }
     if (FIXUP) {
         if (__any_sync(0xffffffffu, borderMask != 0u))
-            fixBorderline<FORCES, ENERGY, EXACT, EXCL>(a, sm, lane, borderMask, exclRot, slotI, validI, xi, yi, zi, qik, pri, fix, fiy, fiz, eTile);
+            fixBorderline<FORCES, ENERGY, EXACT, EXCL, LJPME>(a, sm, lane, borderMask, exclRot, slotI, validI, xi, yi, zi, qik, pri, fix, fiy, fiz, eTile);
     }
 }
 
@@ -313,10 +329,10 @@ _Pragma(TILE_STR(unroll TILE_UNROLL))
         fixBorderlinePacked<FORCES, ENERGY, EXCL>(a, sm, lane, exclRot, slotI, validI, xi, yi, zi, qik, pri, gix, giy, giz, eTile);
 }
 
-template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT>
+template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT, bool LJPME>
 __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(const TileArgs a) {
     __shared__ WarpSmem smAll[TILE_WARPS];
-    constexpr bool PACKED = !EMIT && !EXACT;   // FFMA2 path for the single-periodic-copy force/energy variants
+    constexpr bool PACKED = !EMIT && !EXACT && !LJPME;   // FFMA2 path for the single-periodic-copy force/energy variants
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem& sm = smAll[warp];
     const unsigned numExclUnits = (unsigned)(a.exclEnd - a.exclBegin);
@@ -398,11 +414,11 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
                     if (excl) denseTilePacked<FORCES, ENERGY, true>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, gix, giy, giz, fjx, fjy, fjz, eTile);
                     else denseTilePacked<FORCES, ENERGY, false>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, gix, giy, giz, fjx, fjy, fjz, eTile);
                 } else if (excl) {
-                    if (single) denseTile<FORCES, ENERGY, EMIT, EXACT, true, true>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
-                    else denseTile<FORCES, ENERGY, EMIT, EXACT, false, true>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
+                    if (single) denseTile<FORCES, ENERGY, EMIT, EXACT, true, true, LJPME>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
+                    else denseTile<FORCES, ENERGY, EMIT, EXACT, false, true, LJPME>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
                 } else {
-                    if (single) denseTile<FORCES, ENERGY, EMIT, EXACT, true, false>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
-                    else denseTile<FORCES, ENERGY, EMIT, EXACT, false, false>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
+                    if (single) denseTile<FORCES, ENERGY, EMIT, EXACT, true, false, LJPME>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
+                    else denseTile<FORCES, ENERGY, EMIT, EXACT, false, false, LJPME>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
                 }
                 if (FORCES && jaCur >= 0 && jaCur < a.N) {
                     // after 32 rotations the accumulator for j = lane is back in this lane
@@ -449,7 +465,7 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
                     bool in = dcut < 0.f;
                     if (fabsf(dcut) < a.borderTol) in = borderlineInside(a, x * 32 + i, ja);
                     float s, e;
-                    pairTerms<ENERGY, EXACT>(a, r2, p.w * pj.w, pr.x + prj.x, pr.y * prj.y, s, e);
+                    pairTerms<ENERGY, EXACT, LJPME>(a, r2, p.w * pj.w, pr.x + prj.x, pr.y * prj.y, s, e, pr.x * prj.x);
                     s = in ? s : 0.f;
                     if (FORCES && in) {
                         const float gx = dx * s, gy = dy * s, gz = dz * s;
@@ -481,13 +497,13 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
 
 __global__ void resetWorkQueue(DevCounters* c) { c->workNext = 0; }
 
-template <bool EXACT>
+template <bool EXACT, bool LJPME>
 static void launchTile(b200_ctx* c, const TileArgs& a, bool forces, bool energy, bool emitPairs) {
     const int grid = c->smCount * TILE_MIN_BLOCKS;
-    if (emitPairs) tileKernel<false, false, true, EXACT><<<grid, TILE_THREADS, 0, c->stream>>>(a);
-    else if (forces && energy) tileKernel<true, true, false, EXACT><<<grid, TILE_THREADS, 0, c->stream>>>(a);
-    else if (forces) tileKernel<true, false, false, EXACT><<<grid, TILE_THREADS, 0, c->stream>>>(a);
-    else tileKernel<false, true, false, EXACT><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    if (emitPairs) tileKernel<false, false, true, EXACT, false><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    else if (forces && energy) tileKernel<true, true, false, EXACT, LJPME><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    else if (forces) tileKernel<true, false, false, EXACT, LJPME><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    else tileKernel<false, true, false, EXACT, LJPME><<<grid, TILE_THREADS, 0, c->stream>>>(a);
 }
 
 void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
@@ -509,8 +525,15 @@ void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
     a.periodic = 1;
     resetWorkQueue<<<1, 1, 0, c->stream>>>(c->counters);
     ScopedTimer tm(c, B200_T_TILE, c->stream);
-    if (c->exactEwald) launchTile<true>(c, a, forces, energy, emitPairs);
-    else launchTile<false>(c, a, forces, energy, emitPairs);
+    a.ljAlpha2 = a.invCut6 = a.ljShift = 0.f;
+    if (c->ljpme) {
+        const double x = c->nb.ljpme_alpha * c->nb.ljpme_alpha * rc * rc, ic6 = 1.0 / (rc * rc * rc * rc * rc * rc);
+        a.ljAlpha2 = (float)(c->nb.ljpme_alpha * c->nb.ljpme_alpha); a.invCut6 = (float)ic6;
+        a.ljShift = (float)(ic6 * (1.0 - exp(-x) * (1.0 + x + 0.5 * x * x)));
+    }
+    if (c->ljpme) { if (c->exactEwald) launchTile<true, true>(c, a, forces, energy, emitPairs); else launchTile<false, true>(c, a, forces, energy, emitPairs); }
+    else if (c->exactEwald) launchTile<true, false>(c, a, forces, energy, emitPairs);
+    else launchTile<false, false>(c, a, forces, energy, emitPairs);
     LAUNCH_COUNT(c, 2);
     CUDA_CHECK(cudaGetLastError());
 }

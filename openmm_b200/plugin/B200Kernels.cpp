@@ -130,8 +130,8 @@ void B200CalcNonbondedForceKernel::gather(const System& system, const NonbondedF
     if (force.getNumParticleParameterOffsets() > 0 || force.getNumExceptionParameterOffsets() > 0)
         throw OpenMMException("The B200 platform does not support NonbondedForce parameter offsets yet");
     if (force.getUseSwitchingFunction()) throw OpenMMException("The B200 platform does not support the NonbondedForce switching function yet");
-    if (force.getNonbondedMethod() != NonbondedForce::PME)
-        throw OpenMMException("The B200 platform implements NonbondedForce with the PME method only");
+    if (force.getNonbondedMethod() != NonbondedForce::PME && force.getNonbondedMethod() != NonbondedForce::LJPME)
+        throw OpenMMException("The B200 platform implements NonbondedForce with the PME and LJPME methods only");
     const int n = force.getNumParticles();
     p.q.resize(n); p.sigma.resize(n); p.eps.resize(n);
     for (int i = 0; i < n; i++) force.getParticleParameters(i, p.q[i], p.sigma[i], p.eps[i]);
@@ -144,12 +144,18 @@ void B200CalcNonbondedForceKernel::gather(const System& system, const NonbondedF
     }
     b200_nonbonded_desc& dd = p.desc;
     memset(&dd, 0, sizeof(dd));
-    dd.method = B200_NB_PME;
+    const bool ljpme = force.getNonbondedMethod() == NonbondedForce::LJPME;
+    dd.method = ljpme ? B200_NB_LJPME : B200_NB_PME;
+    if (ljpme) {   // CommonCalcNonbondedForce.cpp:380-396: dispersion mesh from calcPMEParameters(lj = true), rounded to a legal FFT size
+        int lx, ly, lz;
+        NonbondedForceImpl::calcPMEParameters(system, force, dd.ljpme_alpha, lx, ly, lz, true);
+        dd.ljpme_grid[0] = b200_find_legal_fft_dimension(max(lx, 6)); dd.ljpme_grid[1] = b200_find_legal_fft_dimension(max(ly, 6)); dd.ljpme_grid[2] = b200_find_legal_fft_dimension(max(lz, 6));
+    }
     dd.cutoff = force.getCutoffDistance();
     int nx, ny, nz;
     NonbondedForceImpl::calcPMEParameters(system, force, dd.ewald_alpha, nx, ny, nz, false);
     dd.grid[0] = b200_find_legal_fft_dimension(max(nx, 6)); dd.grid[1] = b200_find_legal_fft_dimension(max(ny, 6)); dd.grid[2] = b200_find_legal_fft_dimension(max(nz, 6));
-    dd.dispersion_coefficient = force.getUseDispersionCorrection() ? NonbondedForceImpl::calcDispersionCorrection(system, force) : 0.0;
+    dd.dispersion_coefficient = force.getUseDispersionCorrection() && !ljpme ? NonbondedForceImpl::calcDispersionCorrection(system, force) : 0.0;
     dd.charge = p.q.data(); dd.sigma = p.sigma.data(); dd.epsilon = p.eps.data();
     dd.num_exclusions = (int)p.exclusions.size() / 2; dd.exclusion_pairs = p.exclusions.data();
     dd.num_exceptions = (int)p.excQQ.size(); dd.exception_pairs = p.exceptions.data();
@@ -180,8 +186,11 @@ void B200CalcNonbondedForceKernel::getPMEParameters(double& alpha, int& nx, int&
     check(b200_nonbonded_get_pme_parameters(d.ctx, &alpha, &x, &y, &z));
     nx = x; ny = y; nz = z;
 }
-void B200CalcNonbondedForceKernel::getLJPMEParameters(double&, int&, int&, int&) const {
-    throw OpenMMException("getLJPMEParameters: this Context is not using LJPME");
+void B200CalcNonbondedForceKernel::getLJPMEParameters(double& alpha, int& nx, int& ny, int& nz) const {
+    int32_t x, y, z;
+    if (b200_nonbonded_get_ljpme_parameters(d.ctx, &alpha, &x, &y, &z) != B200_OK)
+        throw OpenMMException("getPMEParametersInContext: This Context is not using PME");   // message of CommonCalcNonbondedForce.cpp:1267
+    nx = x; ny = y; nz = z;
 }
 
 // ---------------------------------------------------------------------------------------------- bonded forces

@@ -92,6 +92,45 @@ def test_run_to_run_bit_identical():
     ctx2.close()
 
 
+@pytest.mark.parametrize("n", [1538, 6002])
+def test_ljpme_vs_reference_fixture(golden_dir, n):
+    # NonbondedForce::LJPME: dispersion on a second mesh (tests/TestNonbondedForce.h testLJPME; benchmark "apoa1pme" with LJPME)
+    g = np.load(os.path.join(golden_dir, f"ref_ljpme_{n}.npz"))
+    sysd = workloads.ljpme_water_box(n)
+    assert np.array_equal(sysd["positions"].astype(np.float32), g["positions"])
+    ctx = workloads.make_context(sysd, ljpme=True)
+    assert list(ctx.pme[1]) == [int(x) for x in g["grid"]] and list(ctx.lj_pme[1]) == [int(x) for x in g["lj_grid"]]
+    ctx.set_positions(sysd["positions"])
+    e_dir = ctx.compute(b.GROUP_DIRECT); f_dir = ctx.get_forces()
+    e_rec = ctx.compute(b.GROUP_RECIPROCAL); f_rec = ctx.get_forces()
+    e_tot = ctx.compute(b.GROUP_ALL); f_tot = ctx.get_forces()
+    ref_tot = g["f_direct"] + g["f_recip"]
+    print(n, "LJPME relRMS direct/recip/total", rel_rms(f_dir, g["f_direct"]), rel_rms(f_rec, g["f_recip"]), rel_rms(f_tot, ref_tot))
+    assert rel_rms(f_tot, ref_tot) < FORCE_TOL
+    assert rel_rms(f_dir, g["f_direct"]) < FORCE_TOL
+    assert rel_rms(f_rec, g["f_recip"]) < 2e-5
+    e_ref = float(g["e_direct"]) + float(g["e_recip"])
+    assert abs(e_tot - e_ref) / abs(e_ref) < ENERGY_TOL
+    assert abs(e_dir - float(g["e_direct"])) / abs(float(g["e_direct"])) < ENERGY_TOL
+    assert abs(e_rec - float(g["e_recip"])) / abs(float(g["e_recip"])) < ENERGY_TOL
+    # energy-only and forces+energy kernels agree; forces-only kernel gives the same forces
+    ctx.compute(b.GROUP_ALL, energy=False)
+    assert rel_rms(ctx.get_forces(), f_tot) < 1e-7
+    ctx.close()
+
+
+def test_ljpme_oracle_on_fresh_seed_and_determinism():
+    sysd = workloads.ljpme_water_box(3002)
+    ctx = workloads.make_context(sysd, ljpme=True)
+    ctx.set_positions(sysd["positions"])
+    e = ctx.compute(); f = ctx.get_forces()
+    fo, eo = Oracle(sysd, 0.9, ctx.pme[0], ctx.pme[1], ctx.lj_pme[0], ctx.lj_pme[1]).nonbonded()
+    assert rel_rms(f, fo) < FORCE_TOL and abs(e - eo) / abs(eo) < ENERGY_TOL
+    e2 = ctx.compute(); f2 = ctx.get_forces()
+    assert e2 == e and np.array_equal(f, f2)
+    ctx.close()
+
+
 def test_oracle_vs_gpu_on_fresh_seed():
     # same seeded inputs through the oracle restatement (not a stored fixture)
     sysd, ctx = make(3000, seed=77)

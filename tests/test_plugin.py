@@ -43,6 +43,21 @@ def test_context_on_b200_platform_matches_reference_platform(n):
 
 
 @pytest.mark.gpu
+def test_ljpme_context_on_b200_platform_matches_reference_platform():
+    # NonbondedForce::LJPME with explicit setLJPMEParameters, evaluated by both platforms inside one process
+    sysd = workloads.ljpme_water_box(3002)
+    alpha, grid = b.pme_parameters(0.9, sysd["box"])
+    lj_alpha, lj_grid = b.pme_parameters(0.9, sysd["box"], lj=True)
+    with tempfile.TemporaryDirectory() as td:
+        sp = os.path.join(td, "s.bin")
+        workloads.write_system_file(sp, sysd, 0.9, alpha, grid, method=5, lj_alpha=lj_alpha, lj_grid=lj_grid)
+        r = _driver(["compare", sp, "--platform", "B200", "--plugin", b.PLUGIN_PATH, "--against", "Reference"])
+    print(r)
+    assert r["rel_rms_force_total"] < 1e-5 and r["rel_rms_force_direct"] < 1e-5 and r["rel_rms_force_recip"] < 2e-5
+    assert r["rel_energy"] < 1e-5
+
+
+@pytest.mark.gpu
 def test_langevin_middle_steps_through_the_plugin():
     sysd = workloads.water_box(6000, seed=6000)
     alpha, grid = b.pme_parameters(0.9, sysd["box"])
