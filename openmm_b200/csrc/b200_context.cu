@@ -250,6 +250,7 @@ extern "C" int b200_nonbonded_update_parameters(b200_ctx* c, const b200_nonbonde
     c->totalCharge = sumQ;
     c->selfEnergy = -B200_ONE_4PI_EPS0 * c->nb.ewald_alpha * sumQ2 / sqrt(M_PI);
     b200_lj_self_energy(c);
+    b200_pme_rescale(c);
     if (c->finalized && c->numExceptions > 0) {
         std::vector<float4> xq;
         for (size_t i = 0; i < c->excQQ.size(); i++) xq.push_back(make_float4((float)(B200_ONE_4PI_EPS0 * c->excQQ[i]), (float)c->excSig[i], (float)(4.0 * c->excEps[i]), 0.f));

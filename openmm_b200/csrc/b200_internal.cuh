@@ -215,6 +215,7 @@ void b200_nblist_force_rebuild(b200_ctx* c);
 void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs);
 void b200_pme_create(b200_ctx* c);
 void b200_pme_destroy(b200_ctx* c);
+void b200_pme_rescale(b200_ctx* c);
 void b200_pme_launch(b200_ctx* c, cudaStream_t s, bool forces, bool energy);
 void b200_bonded_upload(b200_ctx* c);
 void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy);

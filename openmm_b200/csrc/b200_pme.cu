@@ -56,33 +56,34 @@ __device__ __forceinline__ void gridCoords(const float4 p, const PmeArgs& a, int
 }
 
 // ---- chunked spreading / interpolation.  One CTA takes 128 consecutive atoms.  Because atoms are kept in Hilbert order
-// their stencils cover a compact box of grid points; when that box fits the shared-memory tile the CTA accumulates all
-// 125 contributions per atom there (native 32-bit shared atomics) and then adds the box to the global grid with one
-// coalesced integer atomic per touched point.  Boxes that do not fit (rare: atoms that drifted far apart between two
-// re-sorts) fall back to direct global atomics.  All sums are integer, so the grid is bit-reproducible.
+// their stencils cover a compact box of grid points (about 17^3 for 128 atoms at 0.11 nm spacing); when that box fits the
+// shared-memory tile the CTA accumulates all 125 contributions per atom there (native 32-bit shared atomics) and then adds
+// the box to the global grid row by row (one warp per (x,y) row, lanes along z: coalesced integer atomics, no index
+// arithmetic per point).  Boxes that do not fit (rare: atoms that drifted far apart between two re-sorts) fall back to
+// direct global atomics.  All sums are integer, so the grid is bit-reproducible.
 #define CHUNK 128
+#define CHUNK_WARPS (CHUNK / 32)
 #define TILE_MAX 8192
-struct ChunkBox { int ref[3]; int lo[3]; int ext[3]; int vol; };
+struct ChunkBox { int org[3]; int lo[3]; int ext[3]; int vol; };   // org = wrapped grid index of tile entry (0,0,0)
 
-// t -> (x, y, z) in a box of extents (., ey, ez) without integer division (exact for the small integers involved)
-__device__ __forceinline__ void unflatten(int t, int ey, int ez, float invEy, float invEz, int& x, int& y, int& z) {
-    const int r = (int)(((float)t + 0.5f) * invEz);
-    z = t - r * ez;
-    x = (int)(((float)r + 0.5f) * invEy);
-    y = r - x * ey;
-}
-__device__ __forceinline__ int wrapDiff(int d, int n) { d += n / 2; d %= n; if (d < 0) d += n; return d - n / 2; }
-__device__ __forceinline__ int wrapIdx(int i, int n) { i %= n; return i < 0 ? i + n : i; }
+// d = difference of two indices in [0,n) -> representative in [-n/2, n/2]; i in (-n, 2n) -> [0,n)   (no integer division)
+__device__ __forceinline__ int wrapDiff(int d, int n) { const int h = n >> 1; d -= d > h ? n : 0; d += d < -h ? n : 0; return d; }
+__device__ __forceinline__ int wrapIdx(int i, int n) { i += i < 0 ? n : 0; i -= i >= n ? n : 0; return i; }
 
 // bounding box (in grid points, relative to the first atom's base index) of the stencils of the chunk's atoms
 __device__ __forceinline__ void chunkBox(bool valid, int ix, int iy, int iz, const PmeArgs& a, ChunkBox& box, int* sh /*[10]*/, int& dx, int& dy, int& dz) {
     if (threadIdx.x == 0) { sh[0] = ix; sh[1] = iy; sh[2] = iz; sh[3] = sh[4] = sh[5] = 1 << 30; sh[6] = sh[7] = sh[8] = -(1 << 30); }
     __syncthreads();
-    box.ref[0] = sh[0]; box.ref[1] = sh[1]; box.ref[2] = sh[2];
-    dx = wrapDiff(ix - box.ref[0], a.nx); dy = wrapDiff(iy - box.ref[1], a.ny); dz = wrapDiff(iz - box.ref[2], a.nz);
-    if (valid) {
-        atomicMin(&sh[3], dx); atomicMin(&sh[4], dy); atomicMin(&sh[5], dz);
-        atomicMax(&sh[6], dx); atomicMax(&sh[7], dy); atomicMax(&sh[8], dz);
+    const int r0 = sh[0], r1 = sh[1], r2 = sh[2];
+    dx = wrapDiff(ix - r0, a.nx); dy = wrapDiff(iy - r1, a.ny); dz = wrapDiff(iz - r2, a.nz);
+    {   // warp-level min/max first: six shared atomics per warp instead of six per thread on the same addresses
+        const int big = 1 << 30;
+        const int mnx = __reduce_min_sync(0xffffffffu, valid ? dx : big), mny = __reduce_min_sync(0xffffffffu, valid ? dy : big), mnz = __reduce_min_sync(0xffffffffu, valid ? dz : big);
+        const int mxx = __reduce_max_sync(0xffffffffu, valid ? dx : -big), mxy = __reduce_max_sync(0xffffffffu, valid ? dy : -big), mxz = __reduce_max_sync(0xffffffffu, valid ? dz : -big);
+        if ((threadIdx.x & 31) == 0 && mxx >= mnx) {
+            atomicMin(&sh[3], mnx); atomicMin(&sh[4], mny); atomicMin(&sh[5], mnz);
+            atomicMax(&sh[6], mxx); atomicMax(&sh[7], mxy); atomicMax(&sh[8], mxz);
+        }
     }
     __syncthreads();
     for (int k = 0; k < 3; k++) { box.lo[k] = sh[3 + k]; box.ext[k] = sh[6 + k] - sh[3 + k] + PME_ORDER; }
@@ -91,11 +92,84 @@ __device__ __forceinline__ void chunkBox(bool valid, int ix, int iy, int iz, con
     for (int k = 0; k < 3; k++) fits = fits && box.ext[k] <= n[k];      // a box wider than the grid would alias onto itself
     const long long vol = (long long)box.ext[0] * box.ext[1] * box.ext[2];
     box.vol = (fits && vol <= TILE_MAX) ? (int)vol : 0;
+    box.org[0] = wrapIdx(r0 + box.lo[0], a.nx); box.org[1] = wrapIdx(r1 + box.lo[1], a.ny); box.org[2] = wrapIdx(r2 + box.lo[2], a.nz);
 }
+
+// The tile is visited in units of half an x plane: unit u = (x = u>>1, lower or upper half of the y range); warp w takes
+// units w, w+CHUNK_WARPS, ...  Inside a unit the rows (x, y), (x, y+1), ... are one grid row apart, so the global row offset
+// is advanced by an add and one wrap test per row (no index arithmetic per point), lanes run along z, and rows are handled
+// ROW_BATCH at a time so that a warp keeps that many independent memory operations in flight.
+#define ROW_BATCH 3
+struct PlaneUnits {
+    int lane, warp, ey, ez, numUnits, yHalf, planeStride, gz;
+    const ChunkBox& box; const PmeArgs& a;
+    __device__ __forceinline__ PlaneUnits(const ChunkBox& b, const PmeArgs& args) : box(b), a(args) {
+        lane = threadIdx.x & 31; warp = threadIdx.x >> 5;
+        ey = b.ext[1]; ez = b.ext[2]; numUnits = 2 * b.ext[0]; yHalf = (ey + 1) >> 1; planeStride = args.ny * args.nz;
+    }
+    // f(tileIndex, globalIndex, rowValid) is called ROW_BATCH rows at a time, twice (phase 0: issue loads, phase 1: consume)
+    template <typename F0, typename F1>
+    __device__ __forceinline__ void run(F0 issue, F1 consume) {
+        for (int z0 = 0; z0 < ez; z0 += 32) {
+            const int z = z0 + lane;
+            const bool zOk = z < ez;
+            int gzl = box.org[2] + z; gzl -= gzl >= a.nz ? a.nz : 0;
+            for (int u = warp; u < numUnits; u += CHUNK_WARPS) {
+                const int x = u >> 1;
+                const int yBegin = (u & 1) ? yHalf : 0, yEnd = (u & 1) ? ey : yHalf;
+                int gx = box.org[0] + x; gx -= gx >= a.nx ? a.nx : 0;
+                int gy = box.org[1] + yBegin; gy -= gy >= a.ny ? a.ny : 0;
+                int g = (gx * a.ny + gy) * a.nz + gzl;            // global index of (x, yBegin, z)
+                int t = (x * ey + yBegin) * ez + z;               // tile index
+                for (int y = yBegin; y < yEnd; y += ROW_BATCH) {
+                    int gi[ROW_BATCH];
+#pragma unroll
+                    for (int k = 0; k < ROW_BATCH; k++) {
+                        gi[k] = g;
+                        issue(k, t + k * ez, g, zOk && (y + k) < yEnd);
+                        g += a.nz; gy++;
+                        if (gy == a.ny) { gy = 0; g -= planeStride; }
+                    }
+#pragma unroll
+                    for (int k = 0; k < ROW_BATCH; k++) consume(k, t + k * ez, gi[k], zOk && (y + k) < yEnd);
+                    t += ROW_BATCH * ez;
+                }
+            }
+        }
+    }
+};
+
+// Fast path for the usual case of an x plane of the tile holding at most 32*PLANE_SLOTS points: every lane precomputes, once,
+// the global offset (inside an x plane of the grid) of the plane entries lane, lane+32, ...; a plane is then moved with one
+// shared-memory access, one add and one global access per 32 points, all lanes busy.
+#define PLANE_SLOTS 16
+struct PlaneMap {
+    int off[PLANE_SLOTS];   // gy*nz + gz of plane entry lane + 32*m  (-1: beyond the plane)
+    int slots, planeSize, planeStride;
+    __device__ __forceinline__ bool init(const ChunkBox& box, const PmeArgs& a) {
+        const int ey = box.ext[1], ez = box.ext[2], lane = threadIdx.x & 31;
+        planeSize = ey * ez; planeStride = a.ny * a.nz; slots = (planeSize + 31) >> 5;
+        if (slots > PLANE_SLOTS) return false;
+        const float invEz = 1.0f / (float)ez;
+#pragma unroll
+        for (int m = 0; m < PLANE_SLOTS; m++) {
+            const int e = lane + 32 * m;
+            const int y = (int)(((float)e + 0.5f) * invEz), z = e - y * ez;     // exact for e < 2^20
+            int gy = box.org[1] + y; gy -= gy >= a.ny ? a.ny : 0;
+            int gz = box.org[2] + z; gz -= gz >= a.nz ? a.nz : 0;
+            off[m] = e < planeSize ? gy * a.nz + gz : -1;
+        }
+        return true;
+    }
+};
+
+// float -> nearest integer: F2I keeps the full 2^26 fixed-point resolution (a mantissa trick would cap it at 2^22 per
+// contribution, which was measured to triple the error of the reciprocal forces)
+__device__ __forceinline__ int spreadRound(float vxy, float w) { return __float2int_rn(vxy * w); }
 
 // charge spreading (gridSpreadCharge, pme.cc:23-121)
 __global__ void __launch_bounds__(CHUNK) pmeSpreadChunks(const float4* __restrict__ posq, const float2* __restrict__ sigEps, int N, PmeArgs a, int* __restrict__ grid, float fixScale) {
-    __shared__ int tile[TILE_MAX];
+    __shared__ __align__(16) int tile[TILE_MAX];
     __shared__ int sh[10];
     const int i = blockIdx.x * CHUNK + threadIdx.x;
     float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -109,7 +183,7 @@ __global__ void __launch_bounds__(CHUNK) pmeSpreadChunks(const float4* __restric
     bspline5(ux, wx, d); bspline5(uy, wy, d); bspline5(uz, wz, d);
     const float q = p.w * fixScale;
     if (box.vol > 0) {
-        for (int t = threadIdx.x; t < box.vol; t += CHUNK) tile[t] = 0;
+        for (int t = threadIdx.x * 4; t < box.vol; t += CHUNK * 4) *reinterpret_cast<int4*>(&tile[t]) = make_int4(0, 0, 0, 0);
         __syncthreads();
         if (valid) {
             const int ey = box.ext[1], ez = box.ext[2];
@@ -122,23 +196,28 @@ __global__ void __launch_bounds__(CHUNK) pmeSpreadChunks(const float4* __restric
                     const float vxy = vx * wy[jy];
                     int* row = &tile[base + (jx * ey + jy) * ez];
 #pragma unroll
-                    for (int jz = 0; jz < 5; jz++) atomicAdd(&row[jz], __float2int_rn(vxy * wz[jz]));
+                    for (int jz = 0; jz < 5; jz++) atomicAdd(&row[jz], spreadRound(vxy, wz[jz]));
                 }
             }
         }
         __syncthreads();
-        const int ey = box.ext[1], ez = box.ext[2];
-        const int ox = wrapIdx(box.ref[0] + box.lo[0], a.nx), oy = wrapIdx(box.ref[1] + box.lo[1], a.ny), oz = wrapIdx(box.ref[2] + box.lo[2], a.nz);
-        const float invEy = 1.0f / ey, invEz = 1.0f / ez;
-        for (int t = threadIdx.x; t < box.vol; t += CHUNK) {
-            const int v = tile[t];
-            if (v == 0) continue;
-            int x, y, z;
-            unflatten(t, ey, ez, invEy, invEz, x, y, z);
-            int gx = ox + x; gx += gx < 0 ? a.nx : 0; gx -= gx >= a.nx ? a.nx : 0;
-            int gy = oy + y; gy += gy < 0 ? a.ny : 0; gy -= gy >= a.ny ? a.ny : 0;
-            int gz = oz + z; gz += gz < 0 ? a.nz : 0; gz -= gz >= a.nz ? a.nz : 0;
-            atomicAdd(&grid[((size_t)gx * a.ny + gy) * a.nz + gz], v);
+        PlaneMap pm;
+        if (pm.init(box, a)) {
+            const int lane = threadIdx.x & 31;
+            for (int x = threadIdx.x >> 5; x < box.ext[0]; x += CHUNK_WARPS) {
+                int gx = box.org[0] + x; gx -= gx >= a.nx ? a.nx : 0;
+                int* gp = grid + (size_t)gx * pm.planeStride;
+                const int* tp = tile + x * pm.planeSize + lane;
+                int v[PLANE_SLOTS];
+#pragma unroll
+                for (int m = 0; m < PLANE_SLOTS; m++) v[m] = (m < pm.slots && pm.off[m] >= 0) ? tp[32 * m] : 0;
+#pragma unroll
+                for (int m = 0; m < PLANE_SLOTS; m++) if (v[m] != 0) atomicAdd(gp + pm.off[m], v[m]);
+            }
+        } else {
+            int v[ROW_BATCH];
+            PlaneUnits(box, a).run([&](int k, int t, int, bool ok) { v[k] = ok ? tile[t] : 0; },
+                                   [&](int k, int, int g, bool) { if (v[k] != 0) atomicAdd(&grid[g], v[k]); });
         }
     } else if (valid) {
         int zi[5];
@@ -154,7 +233,7 @@ __global__ void __launch_bounds__(CHUNK) pmeSpreadChunks(const float4* __restric
                 const float vxy = vx * wy[jy];
                 int* row = grid + ((size_t)x * a.ny + y) * a.nz;
 #pragma unroll
-                for (int jz = 0; jz < 5; jz++) atomicAdd(&row[zi[jz]], __float2int_rn(vxy * wz[jz]));
+                for (int jz = 0; jz < 5; jz++) atomicAdd(&row[zi[jz]], spreadRound(vxy, wz[jz]));
             }
         }
     }
@@ -163,8 +242,15 @@ __global__ void __launch_bounds__(CHUNK) pmeSpreadChunks(const float4* __restric
 // (the reciprocal convolution and energy sum, pme.cc:137-253, are fused into the x pass of the FFT: fftXConvolve in b200_fft.cu)
 
 // force interpolation (gridInterpolateForce, pme.cc:255-356): same chunking; the box of potential values the chunk's atoms
-// read is staged in shared memory once (coalesced), then every atom gathers its 125 values from there
-__global__ void __launch_bounds__(CHUNK) pmeInterpolateChunks(const float4* __restrict__ posq, const float2* __restrict__ sigEps, int N, int Npad, PmeArgs a, const float* __restrict__ phi, long long* __restrict__ force) {
+// read is staged in shared memory once (coalesced rows), then every atom gathers its 125 values from there.  The z sums of
+// the value and of the z derivative share each loaded value (one packed FMA); the y sums are kept per x plane.
+__device__ __forceinline__ float2 pmeFma2(float v, float2 w, float2 acc) {
+    unsigned long long d; const float2 vv = make_float2(v, v);
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(*reinterpret_cast<const unsigned long long*>(&vv)), "l"(*reinterpret_cast<const unsigned long long*>(&w)), "l"(*reinterpret_cast<const unsigned long long*>(&acc)));
+    return *reinterpret_cast<float2*>(&d);
+}
+
+__global__ void __launch_bounds__(CHUNK, 6) pmeInterpolateChunks(const float4* __restrict__ posq, const float2* __restrict__ sigEps, int N, int Npad, PmeArgs a, const float* __restrict__ phi, long long* __restrict__ force) {
     __shared__ float tile[TILE_MAX];
     __shared__ int sh[10];
     const int i = blockIdx.x * CHUNK + threadIdx.x;
@@ -176,38 +262,50 @@ __global__ void __launch_bounds__(CHUNK) pmeInterpolateChunks(const float4* __re
     ChunkBox box; int dx, dy, dz;
     chunkBox(valid, ix, iy, iz, a, box, sh, dx, dy, dz);
     float wx[5], wy[5], wz[5], ex[5], ey5[5], ez5[5];
-    bspline5(ux, wx, ex); bspline5(uy, wy, ey5); bspline5(uz, wz, ez5);
     float gx = 0.f, gy = 0.f, gz = 0.f;
     if (box.vol > 0) {
-        const int ey = box.ext[1], ez = box.ext[2];
-        const int ox = wrapIdx(box.ref[0] + box.lo[0], a.nx), oy = wrapIdx(box.ref[1] + box.lo[1], a.ny), oz = wrapIdx(box.ref[2] + box.lo[2], a.nz);
-        const float invEy = 1.0f / ey, invEz = 1.0f / ez;
-        for (int t = threadIdx.x; t < box.vol; t += CHUNK) {
-            int x, y, z;
-            unflatten(t, ey, ez, invEy, invEz, x, y, z);
-            int gx = ox + x; gx += gx < 0 ? a.nx : 0; gx -= gx >= a.nx ? a.nx : 0;
-            int gy = oy + y; gy += gy < 0 ? a.ny : 0; gy -= gy >= a.ny ? a.ny : 0;
-            int gz = oz + z; gz += gz < 0 ? a.nz : 0; gz -= gz >= a.nz ? a.nz : 0;
-            tile[t] = phi[((size_t)gx * a.ny + gy) * a.nz + gz];
+        PlaneMap pm;
+        if (pm.init(box, a)) {
+            const int lane = threadIdx.x & 31;
+            for (int x = threadIdx.x >> 5; x < box.ext[0]; x += CHUNK_WARPS) {
+                int gx = box.org[0] + x; gx -= gx >= a.nx ? a.nx : 0;
+                const float* gp = phi + (size_t)gx * pm.planeStride;
+                float* tp = tile + x * pm.planeSize + lane;
+                float v[PLANE_SLOTS];
+#pragma unroll
+                for (int m = 0; m < PLANE_SLOTS; m++) v[m] = (m < pm.slots && pm.off[m] >= 0) ? gp[pm.off[m]] : 0.f;
+#pragma unroll
+                for (int m = 0; m < PLANE_SLOTS; m++) if (m < pm.slots && pm.off[m] >= 0) tp[32 * m] = v[m];
+            }
+        } else {
+            float v[ROW_BATCH];
+            PlaneUnits(box, a).run([&](int k, int, int g, bool ok) { v[k] = ok ? phi[g] : 0.f; },
+                                   [&](int k, int t, int, bool ok) { if (ok) tile[t] = v[k]; });
         }
+        bspline5(ux, wx, ex); bspline5(uy, wy, ey5); bspline5(uz, wz, ez5);
         __syncthreads();
         if (valid) {
+            const int ey = box.ext[1], ez = box.ext[2];
             const int base = ((dx - box.lo[0]) * ey + (dy - box.lo[1])) * ez + (dz - box.lo[2]);
+            float2 wd[5];
+#pragma unroll
+            for (int jz = 0; jz < 5; jz++) wd[jz] = make_float2(wz[jz], ez5[jz]);
 #pragma unroll
             for (int jx = 0; jx < 5; jx++) {
+                float ax = 0.f, ay = 0.f, az = 0.f;   // sum_y wy*s0, sum_y dwy*s0, sum_y wy*s1
 #pragma unroll
                 for (int jy = 0; jy < 5; jy++) {
                     const float* row = &tile[base + (jx * ey + jy) * ez];
-                    float s0 = 0.f, s1 = 0.f;
+                    float2 s = make_float2(0.f, 0.f);
 #pragma unroll
-                    for (int jz = 0; jz < 5; jz++) { const float v = row[jz]; s0 = fmaf(wz[jz], v, s0); s1 = fmaf(ez5[jz], v, s1); }
-                    gx = fmaf(ex[jx] * wy[jy], s0, gx);
-                    gy = fmaf(wx[jx] * ey5[jy], s0, gy);
-                    gz = fmaf(wx[jx] * wy[jy], s1, gz);
+                    for (int jz = 0; jz < 5; jz++) s = pmeFma2(row[jz], wd[jz], s);
+                    ax = fmaf(wy[jy], s.x, ax); ay = fmaf(ey5[jy], s.x, ay); az = fmaf(wy[jy], s.y, az);
                 }
+                gx = fmaf(ex[jx], ax, gx); gy = fmaf(wx[jx], ay, gy); gz = fmaf(wx[jx], az, gz);
             }
         }
     } else if (valid) {
+        bspline5(ux, wx, ex); bspline5(uy, wy, ey5); bspline5(uz, wz, ez5);
         int zi[5];
 #pragma unroll
         for (int k = 0; k < 5; k++) { int z = iz + k; zi[k] = z >= a.nz ? z - a.nz : z; }
@@ -258,19 +356,22 @@ static std::vector<float> splineModuli(int n) {
     return out;
 }
 
+// fixed-point scale 2^bits: |coefficient| * 2^bits <= 1.5 * 2^26, so one contribution (weight product <= 0.215) stays below
+// 2^24.6 and about 80 maximal contributions of one sign would be needed to overflow a grid point
+static float spreadScaleFor(double maxCoef) {
+    int bits = 26; double lim = 1.5;
+    while (maxCoef > lim && bits > 8) { bits--; lim *= 2; }
+    while (maxCoef > 0 && maxCoef <= 0.5 * lim && bits < 40) { bits++; lim *= 0.5; }
+    return (float)std::ldexp(1.0, bits);
+}
+
 static void meshCreate(b200_ctx* c, PmeMesh& m, const int* grid, double alpha, bool dispersion, double maxCoef) {
     for (int k = 0; k < 3; k++) m.gridN[k] = grid[k];
     const int nx = m.gridN[0], ny = m.gridN[1], nz = m.gridN[2];
     m.nzc = nz / 2 + 1; m.alpha = alpha; m.dispersion = dispersion;
     const size_t G = (size_t)nx * ny * nz, GC = (size_t)nx * ny * m.nzc;
     dmalloc(m.gridI, G); dmalloc(m.gridReal, G); dmalloc(m.gridC, GC);
-    {   // fixed-point scale: |coefficient| * scale <= 1.5 * 2^26 ~ 2^26.6, leaving a factor >= 21 of head-room for the sum at one point
-        int bits = 26; double lim = 1.5;
-        while (maxCoef > lim && bits > 12) { bits--; lim *= 2; }
-        while (maxCoef > 0 && maxCoef <= 0.5 * lim && bits < 36) { bits++; lim *= 0.5; }
-        if (dispersion) bits -= 2;   // every coefficient is positive: sums do not cancel, keep more head-room
-        m.spreadScale = (float)std::ldexp(1.0, bits);
-    }
+    m.spreadScale = spreadScaleFor(maxCoef);
     for (int k = 0; k < 3; k++) {
         const std::vector<float> mod = splineModuli(m.gridN[k]);
         dmalloc(m.moduli[k], mod.size());
@@ -285,14 +386,23 @@ static void meshDestroy(PmeMesh& m) {
     for (int k = 0; k < 3; k++) { dfree(m.moduli[k]); dfree(m.twiddle[k]); }
 }
 
+static void maxCoefficients(const b200_ctx* c, double& maxQ, double& maxC6) {
+    maxQ = maxC6 = 0;
+    for (double q : c->charge) maxQ = std::max(maxQ, std::fabs(q));
+    for (int i = 0; i < c->N; i++) maxC6 = std::max(maxC6, 8.0 * pow(0.5 * c->sigma[i], 3.0) * 2.0 * sqrt(c->epsilon[i]));
+}
+
 void b200_pme_create(b200_ctx* c) {
-    double maxQ = 0; for (double q : c->charge) maxQ = std::max(maxQ, std::fabs(q));
-    meshCreate(c, c->mesh[0], c->nb.grid, c->nb.ewald_alpha, false, std::max(maxQ, 0.75 + 1e-9));
-    if (c->ljpme) {
-        double maxC6 = 0;
-        for (int i = 0; i < c->N; i++) maxC6 = std::max(maxC6, 8.0 * pow(0.5 * c->sigma[i], 3.0) * 2.0 * sqrt(c->epsilon[i]));
-        meshCreate(c, c->mesh[1], c->nb.ljpme_grid, c->nb.ljpme_alpha, true, maxC6);
-    }
+    double maxQ, maxC6; maxCoefficients(c, maxQ, maxC6);
+    meshCreate(c, c->mesh[0], c->nb.grid, c->nb.ewald_alpha, false, maxQ);
+    if (c->ljpme) meshCreate(c, c->mesh[1], c->nb.ljpme_grid, c->nb.ljpme_alpha, true, maxC6);
+}
+
+// per-particle parameters changed (updateParametersInContext): the fixed-point scales follow the new maxima
+void b200_pme_rescale(b200_ctx* c) {
+    double maxQ, maxC6; maxCoefficients(c, maxQ, maxC6);
+    c->mesh[0].spreadScale = spreadScaleFor(maxQ);
+    if (c->ljpme) c->mesh[1].spreadScale = spreadScaleFor(maxC6);
 }
 
 void b200_pme_destroy(b200_ctx* c) { meshDestroy(c->mesh[0]); meshDestroy(c->mesh[1]); }

@@ -339,21 +339,40 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
     const unsigned total = numExclUnits + a.counters->numUnits;
     long long eAcc = 0; unsigned long long nPairs = 0;
 
+    // Work units are taken from a device-side queue.  The descriptor of the NEXT unit is fetched while the current one is
+    // computed, and the lines its first loads will touch are pulled towards L1, so a unit starts with one global-latency hop
+    // (the j atom data) instead of three dependent ones (descriptor -> j index -> j atom data).
+    auto loadDesc = [&](unsigned w) -> int4 {
+        if (w >= total) return make_int4(0, 0, 0, 0);
+        if (w < numExclUnits) { const int2 t = a.exclTiles[a.exclBegin + w]; return make_int4(t.x, t.y, 1, 0); }
+        return a.units[w - numExclUnits];
+    };
     unsigned u = 0;
     if (lane == 0) u = atomicAdd(&a.counters->workNext, 1u);
     u = __shfl_sync(0xffffffffu, u, 0);
+    int4 desc = loadDesc(u);
     while (u < total) {
         unsigned uNext = 0;
         if (lane == 0) uNext = atomicAdd(&a.counters->workNext, 1u);   // fetch ahead: latency hidden by this unit's work
-        int x, tileStart, nTiles, kind = 0; const bool excl = u < numExclUnits; int yBlock = 0; unsigned exclBits = 0;
-        if (excl) {
-            const int2 t = a.exclTiles[a.exclBegin + u];
-            x = t.x; yBlock = t.y; tileStart = 0; nTiles = 1;
-            exclBits = a.exclFlags[(size_t)(a.exclBegin + u) * 32 + lane];
-        } else {
-            const int4 w = a.units[u - numExclUnits];
-            x = w.x; tileStart = w.y; nTiles = w.z; kind = w.w;
-        }
+        bool haveNext = false; int4 descNext = make_int4(0, 0, 0, 0);
+        auto fetchNext = [&]() {
+            if (haveNext) return;
+            haveNext = true;
+            uNext = __shfl_sync(0xffffffffu, uNext, 0);
+            descNext = loadDesc(uNext);
+        };
+        auto hintNext = [&]() {
+            if (uNext >= total) return;
+            const bool ex = uNext < numExclUnits;
+            const void* p0 = &a.posq[descNext.x * 32 + lane];
+            const void* p1 = ex ? (const void*)&a.posq[descNext.y * 32 + lane] : (const void*)&a.jAtoms[(size_t)descNext.y * 32 + lane];
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(p0));
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(p1));
+        };
+        const bool excl = u < numExclUnits;
+        const int x = desc.x, tileStart = excl ? 0 : desc.y, nTiles = desc.z, kind = desc.w, yBlock = desc.y;
+        unsigned exclBits = 0;
+        if (excl) exclBits = a.exclFlags[(size_t)(a.exclBegin + u) * 32 + lane];
         const int slotI = x * 32 + lane;
         const float4 pi = a.posq[slotI];
         const float2 pri = a.sigEps[slotI];
@@ -409,6 +428,8 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
                     pj = a.posq[max(ja, 0)]; prj = a.sigEps[max(ja, 0)];
                     if (t + 2 < nTiles) jaNext = a.jAtoms[(size_t)(tileStart + t + 2) * 32 + lane];
                 }
+                if (t == 0) fetchNext();                         // the queue atomic has long returned by now
+                if (t == nTiles - 1) hintNext();
                 float fjx = 0.f, fjy = 0.f, fjz = 0.f;
                 if (PACKED && single) {
                     if (excl) denseTilePacked<FORCES, ENERGY, true>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, gix, giy, giz, fjx, fjy, fjz, eTile);
@@ -445,6 +466,7 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
             sm.par[lane] = pri;
             __syncwarp();
             for (int t = 0; t < nTiles; t++) {
+                if (t == nTiles - 1) { fetchNext(); hintNext(); }
                 const size_t base = (size_t)(tileStart + 2 * t) * 32;
                 const int ja = a.jAtoms[base + lane];
                 unsigned mask = ja >= 0 ? (unsigned)a.jAtoms[base + 32 + lane] : 0u;
@@ -486,7 +508,8 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
                 if (ENERGY) eAcc += toFixed(warpSum(eLane));
             }
         }
-        u = __shfl_sync(0xffffffffu, uNext, 0);
+        fetchNext();
+        u = uNext; desc = descNext;
     }
     if (ENERGY && lane == 0 && eAcc != 0) atomicAddFixed(&a.counters->energy[E_DIRECT], eAcc);
     if (EMIT && !a.pairOut) {
