@@ -257,6 +257,13 @@ template <typename K> static void allowSmem(K kernel, size_t bytes) {
 
 void b200_fft3d_exec_r2c(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, const float* inReal, const int* inFix, float fixScaleInv, float2* out, float2*, cudaStream_t s) {
     const int nzc = nz / 2 + 1;
+    if (b200_fft2_supported(nx, ny, nz)) {
+        b200_fft2_z_forward(nx * ny, nz, inReal, inFix, fixScaleInv, out, tw[2], s);
+        b200_fft2_strided(false, out, ny, nzc, nx, (size_t)ny * nzc, (size_t)nzc, tw[1], s);
+        b200_fft2_strided(false, out, nx, ny * nzc, 1, 0, (size_t)ny * nzc, tw[0], s);
+        CUDA_CHECK(cudaGetLastError());
+        return;
+    }
     int batch, pitch; size_t sm;
     pickBatch(nz, batch, pitch, sm);
     allowSmem(fftZForward, sm);
@@ -274,6 +281,13 @@ void b200_fft3d_exec_r2c(int nx, int ny, int nz, const FFTPlan1D* plan, float2* 
 
 void b200_fft3d_exec_c2r(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, float2* in, float2*, float* out, cudaStream_t s) {
     const int nzc = nz / 2 + 1;
+    if (b200_fft2_supported(nx, ny, nz)) {
+        b200_fft2_strided(true, in, nx, ny * nzc, 1, 0, (size_t)ny * nzc, tw[0], s);
+        b200_fft2_strided(true, in, ny, nzc, nx, (size_t)ny * nzc, (size_t)nzc, tw[1], s);
+        b200_fft2_z_inverse(nx * ny, nz, in, out, tw[2], s);
+        CUDA_CHECK(cudaGetLastError());
+        return;
+    }
     int batch, pitch; size_t sm;
     pickBatch(nx, batch, pitch, sm);
     allowSmem(fftStrided<true>, sm);
@@ -383,6 +397,19 @@ extern "C" int b200_fft3d_c2r_noalloc(int32_t device, int32_t nx, int32_t ny, in
 // whole reciprocal-space pipeline on the context's grids: int charge grid -> spectrum -> convolution (+energy) -> potential grid
 void b200_fft3d_reciprocal(b200_ctx* c, PmeMesh& m, cudaStream_t s, const PmeArgs& a, bool energy, bool forces) {
     const int nx = m.gridN[0], ny = m.gridN[1], nz = m.gridN[2], nzc = nz / 2 + 1;
+    if (b200_fft2_supported(nx, ny, nz)) {
+        b200_fft2_z_forward(nx * ny, nz, nullptr, m.gridI, 1.0f / m.spreadScale, m.gridC, m.twiddle[2], s);
+        b200_fft2_strided(false, m.gridC, ny, nzc, nx, (size_t)ny * nzc, (size_t)nzc, m.twiddle[1], s);
+        b200_fft2_xconv(m.gridC, nx, ny * nzc, (size_t)ny * nzc, m.twiddle[0], a, m.moduli[0], m.moduli[1], m.moduli[2], c->counters, energy, forces, s);
+        LAUNCH_COUNT(c, 3);
+        if (forces) {
+            b200_fft2_strided(true, m.gridC, ny, nzc, nx, (size_t)ny * nzc, (size_t)nzc, m.twiddle[1], s);
+            b200_fft2_z_inverse(nx * ny, nz, m.gridC, m.gridReal, m.twiddle[2], s);
+            LAUNCH_COUNT(c, 2);
+        }
+        CUDA_CHECK(cudaGetLastError());
+        return;
+    }
     int batch, pitch; size_t sm;
     pickBatch(nz, batch, pitch, sm);
     allowSmem(fftZForward, sm);

@@ -229,6 +229,13 @@ void b200_fft_make_twiddle(int n, float2*& dTw, cudaStream_t s);
 void b200_fft3d_reciprocal(b200_ctx* c, PmeMesh& m, cudaStream_t s, const PmeArgs& a, bool energy, bool forces);   // gridI -> (convolution, energy) -> gridReal
 void b200_fft3d_exec_r2c(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, const float* inReal, const int* inFix, float fixScaleInv, float2* out, float2* scratch, cudaStream_t s);
 void b200_fft3d_exec_c2r(int nx, int ny, int nz, const FFTPlan1D* plan, float2* const* tw, float2* in, float2* scratch, float* out, cudaStream_t s);
+// register-resident two-stage passes (b200_fft2.cu); used when every dimension has a plan, else the generic passes of b200_fft.cu run
+bool b200_fft2_supported(int nx, int ny, int nz);
+void b200_fft2_strided(bool inverse, float2* data, int n, int innerCount, int outerCount, size_t outerStride, size_t stride, const float2* tw, cudaStream_t s);
+void b200_fft2_xconv(float2* data, int nx, int innerCount, size_t stride, const float2* tw, const PmeArgs& a, const float* modX, const float* modY, const float* modZ,
+                     DevCounters* counters, bool energy, bool inverseToo, cudaStream_t s);
+void b200_fft2_z_forward(int numLines, int nz, const float* inReal, const int* inFix, float fixScaleInv, float2* out, const float2* twZ, cudaStream_t s);
+void b200_fft2_z_inverse(int numLines, int nz, const float2* in, float* out, const float2* twZ, cudaStream_t s);
 void b200_compute_impl(b200_ctx* c, unsigned groups, bool forces, bool energy, double* energyOut);
 
 #define LAUNCH_COUNT(c, n) ((c)->launchCount += (n))
