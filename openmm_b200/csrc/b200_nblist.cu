@@ -120,18 +120,26 @@ __device__ __forceinline__ void flushSparse(int X, int* slots, int* masks, int n
     } else if (lane == 0) counters->overflow = 1;
 }
 
+__device__ __forceinline__ float2 nbFma2(float2 a, float2 b, float2 c) { unsigned long long d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)), "l"(*reinterpret_cast<unsigned long long*>(&c))); return *reinterpret_cast<float2*>(&d); }
+__device__ __forceinline__ float2 nbMul2(float2 a, float2 b) { unsigned long long d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b))); return *reinterpret_cast<float2*>(&d); }
+__device__ __forceinline__ float2 nbSub2(float2 a, float2 b) { b.x = -b.x; b.y = -b.y; unsigned long long d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b))); return *reinterpret_cast<float2*>(&d); }
+
 // exact test of up to 32 queued candidate atoms (one per lane) against the 32 atoms of block X, then classification
 struct NbWarpBufs { int* dense; int* slots; int* masks; };
-__device__ __forceinline__ void nbProcessCandidates(int X, int lane, unsigned ltMask, bool have, int slot, float rx, float ry, float rz, const float4* sXw, bool single,
+__device__ __forceinline__ void nbProcessCandidates(int X, int lane, unsigned ltMask, bool have, int slot, float rx, float ry, float rz, const float4* sXw, const float4* sXp, bool single,
                                                     const BoxF& box, float rcp2, int sparseMax, NbWarpBufs w, int& nbuf, int& nsp,
                                                     int4* units, int* jAtoms, unsigned unitCapacity, unsigned tileCapacity, DevCounters* counters) {
     unsigned imask = 0;
     if (single) {
-#pragma unroll 8
-        for (int i = 0; i < 32; i++) {
-            const float4 a = sXw[i];
-            const float dx = rx - a.x, dy = ry - a.y, dz = rz - a.z;
-            imask |= (dx * dx + dy * dy + dz * dz < rcp2 ? 1u : 0u) << i;
+        // packed FP32x2: atoms i and i+16 of X per step (sXp[i] = (x_i, x_i+16, y_i, y_i+16), sXp[16+i] = (z_i, z_i+16, -, -))
+        const float2 jx = make_float2(rx, rx), jy = make_float2(ry, ry), jz = make_float2(rz, rz);
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            const float4 a = sXp[i]; const float4 b = sXp[16 + i];
+            const float2 dx = nbSub2(jx, make_float2(a.x, a.y)), dy = nbSub2(jy, make_float2(a.z, a.w)), dz = nbSub2(jz, make_float2(b.x, b.y));
+            const float2 r2 = nbFma2(dx, dx, nbFma2(dy, dy, nbMul2(dz, dz)));
+            imask |= (r2.x < rcp2 ? 1u : 0u) << i;
+            imask |= (r2.y < rcp2 ? 1u : 0u) << (i + 16);
         }
     } else {
         for (int i = 0; i < 32; i++) {
@@ -180,6 +188,7 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
         int partRank, b200_ctx::OwnerTable table, DevCounters* counters) {
     if (!counters->rebuild) return;
     __shared__ float4 sX[NB_WARPS][32];
+    __shared__ float4 sXp[NB_WARPS][32];    // the same atoms packed in pairs (i, i+16) for the FP32x2 exact test
     __shared__ float4 sQ[NB_WARPS][64];     // queue of candidate atoms that passed the box test: (rel. position, slot)
     __shared__ int sBuf[NB_WARPS][NB_BUF];
     __shared__ int sSlot[NB_WARPS][NB_SBUF];
@@ -202,6 +211,10 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
             if (slot >= N) { dx = dy = dz = 1.0e9f; }   // padding atoms never attract neighbours
             __syncwarp();
             sX[warp][lane] = make_float4(dx, dy, dz, 0.f);
+            {
+                const float ox = __shfl_xor_sync(0xffffffffu, dx, 16), oy = __shfl_xor_sync(0xffffffffu, dy, 16), oz = __shfl_xor_sync(0xffffffffu, dz, 16);
+                if (lane < 16) { sXp[warp][lane] = make_float4(dx, ox, dy, oy); sXp[warp][16 + lane] = make_float4(dz, oz, 0.f, 0.f); }
+            }
             __syncwarp();
         }
         const int exBegin = exclRowStart[X], exEnd = exclRowStart[X + 1];
@@ -239,7 +252,7 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
                     __syncwarp();
                     if (nq >= 32) {
                         const float4 q = sQ[warp][lane];
-                        nbProcessCandidates(X, lane, ltMask, true, __float_as_int(q.w), q.x, q.y, q.z, sX[warp], single, box, rcp2, sparseMax, wb, nbuf, nsp,
+                        nbProcessCandidates(X, lane, ltMask, true, __float_as_int(q.w), q.x, q.y, q.z, sX[warp], sXp[warp], single, box, rcp2, sparseMax, wb, nbuf, nsp,
                                             units, jAtoms, unitCapacity, tileCapacity, counters);
                         const int rest = nq - 32;
                         float4 carry = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -254,7 +267,7 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
         }
         if (nq > 0) {
             const float4 q = lane < nq ? sQ[warp][lane] : make_float4(0.f, 0.f, 0.f, 0.f);
-            nbProcessCandidates(X, lane, ltMask, lane < nq, __float_as_int(q.w), q.x, q.y, q.z, sX[warp], single, box, rcp2, sparseMax, wb, nbuf, nsp,
+            nbProcessCandidates(X, lane, ltMask, lane < nq, __float_as_int(q.w), q.x, q.y, q.z, sX[warp], sXp[warp], single, box, rcp2, sparseMax, wb, nbuf, nsp,
                                 units, jAtoms, unitCapacity, tileCapacity, counters);
         }
         if (nbuf > 0) {
