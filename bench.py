@@ -229,6 +229,19 @@ def main():
     ctx.step(prof_steps)
     fam = ctx.timing_read()
     ctx.timing_enable(False)
+    if os.environ.get("B200_BENCH_VERBOSE"):
+        sys.stderr.write(f"[rank {rank}] ms/step {ms_per_step:.4f} | " + " ".join(f"{k}={v[0] / prof_steps * 1e3:.0f}us" for k, v in fam.items() if v[0] > 0) + "\n")
+        if dist is not None:   # raw NCCL all-reduce of a force-sized int64 buffer, for comparison with the library's own collective
+            buf = torch.zeros(3 * (((n + 31) // 32) * 32), dtype=torch.int64, device="cuda")
+            for _ in range(5):
+                dist.all_reduce(buf)
+            torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(20):
+                dist.all_reduce(buf)
+            e1.record(); torch.cuda.synchronize()
+            sys.stderr.write(f"[rank {rank}] torch all_reduce of {buf.numel() * 8 / 1e6:.1f} MB: {e0.elapsed_time(e1) / 20 * 1e3:.0f} us\n")
     stats = ctx.nblist_stats()
     pairs, _ = ctx.direct_pairs()
     pairs *= 1 if world == 1 else 1   # each rank counts its own rows

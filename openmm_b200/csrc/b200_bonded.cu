@@ -5,6 +5,7 @@
 // The reference compiles all of them into one computeBondedForces kernel (BondedUtilities.cpp:71-168); here they are
 // small FP64 kernels (a few terms per atom, not an optimisation target) that add into the same int64 force buffer.
 #include "b200_internal.cuh"
+#include <algorithm>
 #include <vector>
 
 struct D3 { double x, y, z; };
@@ -213,8 +214,21 @@ void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy) 
     cudaStream_t s = c->stream;
     ScopedTimer tm(c, B200_T_BONDED, s);
     const int wf = forces ? 1 : 0, we = energy ? 1 : 0;
+    // with a communicator the excluded-pair corrections are split over the ranks like the direct-space rows (the energies are
+    // all-reduced afterwards); everything else in this file runs on rank 0
+    const bool split = c->commRanks > 1;
+    if (c->hasNonbonded && (groups & B200_GROUP_DIRECT) && c->numExclPairs > 0) {
+        // slices start at multiples of the block size, so every block sums the same pairs as on one rank (bit-identical energy)
+        const int nblk = (c->numExclPairs + 127) / 128;
+        const int begin = split ? 128 * (int)llround(nblk * c->partShareBegin) : 0;
+        const int end = split ? std::min(c->numExclPairs, 128 * (int)llround(nblk * c->partShareEnd)) : c->numExclPairs;
+        if (end > begin && (split || c->partRank == 0)) {
+            exclusionCorrection<<<(end - begin + 127) / 128, 128, 0, s>>>(c->posq, c->ljpme ? c->sigEps : nullptr, c->dExclPairs + begin, end - begin, c->boxD, c->nb.ewald_alpha, c->nb.ljpme_alpha, c->force, c->Npad, c->counters, wf, we);
+            LAUNCH_COUNT(c, 1);
+        }
+    }
+    if (c->partRank != 0) { CUDA_CHECK(cudaGetLastError()); return; }
     if (c->hasNonbonded && (groups & B200_GROUP_DIRECT)) {
-        if (c->numExclPairs > 0) { exclusionCorrection<<<(c->numExclPairs + 127) / 128, 128, 0, s>>>(c->posq, c->ljpme ? c->sigEps : nullptr, c->dExclPairs, c->numExclPairs, c->boxD, c->nb.ewald_alpha, c->nb.ljpme_alpha, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
         if (c->numExceptions > 0) { exceptions14<<<(c->numExceptions + 127) / 128, 128, 0, s>>>(c->posq, c->dExcPairs, c->dExcParams, c->numExceptions, c->boxD, c->nb.exceptions_use_periodic, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
     }
     {

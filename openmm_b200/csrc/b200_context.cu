@@ -678,7 +678,7 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
         prepareLists(c, verify);
         b200_tile_launch(c, forces, energy, false);
     }
-    if (c->partRank == 0) b200_bonded_launch(c, groups, forces, energy);
+    if (c->partRank == 0 || c->commRanks > 1) b200_bonded_launch(c, groups, forces, energy);
     if (doRecip && usePmeStream) CUDA_CHECK(cudaStreamWaitEvent(s, c->evPmeDone, 0));
     if (forces && c->commRanks > 1) b200_comm_allreduce_forces(c);
     if (energy && c->commRanks > 1) b200_comm_allreduce_energy(c);

@@ -128,7 +128,7 @@ __device__ __forceinline__ void checkMoved(const IntegArgs& a, int i, V3 p, bool
     moved |= dx * dx + dy * dy + dz * dz > a.maxDisp2;
 }
 
-__global__ void __launch_bounds__(128) langevinMiddleStep(IntegArgs a, int numSettle, const int4* __restrict__ settleAtoms, const float2* __restrict__ settleParams,
+__global__ void __launch_bounds__(128, 4) langevinMiddleStep(IntegArgs a, int numSettle, const int4* __restrict__ settleAtoms, const float2* __restrict__ settleParams,
                                                            int numFree, const int* __restrict__ freeAtoms) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const double halfdt = 0.5 * a.dt, invDt = 1.0 / a.dt;

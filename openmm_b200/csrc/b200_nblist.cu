@@ -131,15 +131,17 @@ __device__ __forceinline__ void nbProcessCandidates(int X, int lane, unsigned lt
                                                     int4* units, int* jAtoms, unsigned unitCapacity, unsigned tileCapacity, DevCounters* counters) {
     unsigned imask = 0;
     if (single) {
-        // packed FP32x2: atoms i and i+16 of X per step (sXp[i] = (x_i, x_i+16, y_i, y_i+16), sXp[16+i] = (z_i, z_i+16, -, -))
-        const float2 jx = make_float2(rx, rx), jy = make_float2(ry, ry), jz = make_float2(rz, rz);
+        // packed FP32x2, atoms i and i+16 of X per step, in the expanded form |r_i|^2 - 2 r_i.r_j < rc^2 - |r_j|^2 (three packed FMAs
+        // per pair of atoms; coordinates are relative to the block centre, so the cancellation error, ~1e-7 nm^2, is far inside the
+        // list padding).  sXp[i] = (x_i, x_i+16, y_i, y_i+16), sXp[16+i] = (z_i, z_i+16, |r_i|^2, |r_i+16|^2)
+        const float2 jx = make_float2(-2.f * rx, -2.f * rx), jy = make_float2(-2.f * ry, -2.f * ry), jz = make_float2(-2.f * rz, -2.f * rz);
+        const float thr = rcp2 - (rx * rx + ry * ry + rz * rz);
 #pragma unroll
         for (int i = 0; i < 16; i++) {
             const float4 a = sXp[i]; const float4 b = sXp[16 + i];
-            const float2 dx = nbSub2(jx, make_float2(a.x, a.y)), dy = nbSub2(jy, make_float2(a.z, a.w)), dz = nbSub2(jz, make_float2(b.x, b.y));
-            const float2 r2 = nbFma2(dx, dx, nbFma2(dy, dy, nbMul2(dz, dz)));
-            imask |= (r2.x < rcp2 ? 1u : 0u) << i;
-            imask |= (r2.y < rcp2 ? 1u : 0u) << (i + 16);
+            const float2 t = nbFma2(jx, make_float2(a.x, a.y), nbFma2(jy, make_float2(a.z, a.w), nbFma2(jz, make_float2(b.x, b.y), make_float2(b.z, b.w))));
+            imask |= (t.x < thr ? 1u : 0u) << i;
+            imask |= (t.y < thr ? 1u : 0u) << (i + 16);
         }
     } else {
         for (int i = 0; i < 32; i++) {
@@ -198,9 +200,26 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
     const unsigned ltMask = (1u << lane) - 1u;
     const float rcp = sqrtf(rcp2);
     NbWarpBufs wb = {sBuf[warp], sSlot[warp], sMask[warp]};
-    // rows are dealt (weighted) round-robin to ranks: every rank gets a statistically identical sample of the sweep
-    for (int X = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; X < B; X += warpsPerGrid) {
-        if (table.owner[X & 63] != partRank) continue;
+    // rows are dealt (weighted) round-robin to ranks: every rank gets a statistically identical sample of the sweep.  The rows
+    // this rank owns are enumerated densely (k-th owned row = 64*(k/m) + res[k%m], m owned residues of the period-64 table), so
+    // that every warp of the grid has work whatever the share of the rank.
+    __shared__ unsigned char sRes[64];
+    __shared__ int sNumRes;
+    if (warp == 0) {
+        const bool o0 = table.owner[lane] == partRank, o1 = table.owner[32 + lane] == partRank;
+        const unsigned b0 = __ballot_sync(0xffffffffu, o0), b1 = __ballot_sync(0xffffffffu, o1);
+        if (o0) sRes[__popc(b0 & ltMask)] = (unsigned char)lane;
+        if (o1) sRes[__popc(b0) + __popc(b1 & ltMask)] = (unsigned char)(32 + lane);
+        if (lane == 0) sNumRes = __popc(b0) + __popc(b1);
+    }
+    __syncthreads();
+    const int numRes = sNumRes;
+    if (numRes == 0) return;
+    for (int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; ; k += warpsPerGrid) {
+        const int period = k / numRes;
+        if (period * 64 >= B) break;
+        const int X = period * 64 + sRes[k - period * numRes];
+        if (X >= B) continue;
         const float4 cX = blockCenter[X], hX = blockHalf[X];
         const bool single = !box.triclinic && 0.5f * box.ax - hX.x >= rcp && 0.5f * box.by - hX.y >= rcp && 0.5f * box.cz - hX.z >= rcp;
         {
@@ -213,7 +232,8 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
             sX[warp][lane] = make_float4(dx, dy, dz, 0.f);
             {
                 const float ox = __shfl_xor_sync(0xffffffffu, dx, 16), oy = __shfl_xor_sync(0xffffffffu, dy, 16), oz = __shfl_xor_sync(0xffffffffu, dz, 16);
-                if (lane < 16) { sXp[warp][lane] = make_float4(dx, ox, dy, oy); sXp[warp][16 + lane] = make_float4(dz, oz, 0.f, 0.f); }
+                const float n2 = dx * dx + dy * dy + dz * dz, on2 = ox * ox + oy * oy + oz * oz;
+                if (lane < 16) { sXp[warp][lane] = make_float4(dx, ox, dy, oy); sXp[warp][16 + lane] = make_float4(dz, oz, n2, on2); }
             }
             __syncwarp();
         }
@@ -233,13 +253,17 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
                     for (int e = exBegin; e < exEnd && bHit; e++) if (exclRowCols[e] == Y) bHit = false;  // handled as an exclusion tile
                 }
                 unsigned bMask = __ballot_sync(0xffffffffu, bHit);
+                // the atoms of the next hit block are loaded while the current one is tested (padding slots hold finite coordinates)
+                float4 pNext = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (bMask) pNext = posq[(sb * 32 + __ffs(bMask) - 1) * 32 + lane];
                 while (bMask) {
                     const int Yb = sb * 32 + __ffs(bMask) - 1; bMask &= bMask - 1;
                     const int slot = Yb * 32 + lane;
+                    const float4 p = pNext;
+                    if (bMask) pNext = posq[(sb * 32 + __ffs(bMask) - 1) * 32 + lane];
                     bool cand = false;
                     float rx = 0.f, ry = 0.f, rz = 0.f;
                     if (slot < N) {
-                        const float4 p = posq[slot];
                         rx = p.x - cX.x; ry = p.y - cX.y; rz = p.z - cX.z;
                         imageDelta(rx, ry, rz, box);
                         const float gx = fmaxf(0.f, fabsf(rx) - hX.x), gy = fmaxf(0.f, fabsf(ry) - hX.y), gz = fmaxf(0.f, fabsf(rz) - hX.z);
@@ -312,7 +336,9 @@ void b200_nblist_prepare(b200_ctx* c) {
     nbBlockBounds<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, c->B, c->boxF, c->blockCenter, c->blockHalf, c->counters);
     nbSuperBounds<<<(c->numSuper + 7) / 8, 256, 0, c->stream>>>(c->blockCenter, c->blockHalf, c->B, c->numSuper, c->boxF, c->superCenter, c->superHalf, c->counters);
     const float rcp = (float)c->paddedCutoff;
-    int rows = c->B;
+    int owned = 0;
+    for (int i = 0; i < 64; i++) owned += c->partTable.owner[i] == c->partRank ? 1 : 0;
+    int rows = (int)(((long long)c->B * owned + 63) / 64) + 1;
     int buildGrid = (rows + NB_WARPS - 1) / NB_WARPS;
     if (buildGrid > c->smCount * 16) buildGrid = c->smCount * 16;
     nbBuild<<<buildGrid, NB_THREADS, 0, c->stream>>>(c->posq, c->N, c->B, c->numSuper, c->boxF, rcp * rcp, c->sparseMax,
