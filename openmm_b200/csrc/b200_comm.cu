@@ -58,7 +58,7 @@ extern "C" int b200_set_partition(b200_ctx* c, int32_t rank, int32_t nranks) {
     // rows: balance s0*D + P = (1-s0)/(R-1)*D with rho = P/D  =>  s0 = (1 - (R-1) rho)/R  (clamped at 0: a PME-only rank).
     // The reference balances dynamically from measured times (CudaParallelKernels.cpp:247-266); a fixed model suffices here
     // because rows are sampled uniformly.  B200_PME_COST_RATIO overrides rho.
-    double rho = 0.5;
+    double rho = 0.38;   // measured on STMV, 2 ranks: flat optimum between 0.30 and 0.40
     if (const char* e = getenv("B200_PME_COST_RATIO")) rho = atof(e);
     std::vector<double> share(nranks, 1.0 / nranks);
     if (nranks > 1 && c->commRanks > 1) {   // only with a communicator: logical ranks on one device are plain equal shares

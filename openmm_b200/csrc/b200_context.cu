@@ -126,6 +126,7 @@ extern "C" void b200_context_destroy(b200_ctx* c) {
     for (auto& g : c->groups) dfree(g.dBase);
     if (c->countersHost) cudaFreeHost(c->countersHost);
     if (c->hStage) cudaFreeHost(c->hStage);
+    for (auto& e : c->ioEvents) cudaEventDestroy(e);
     dfree(c->dStage);
     for (auto& t : c->timers) for (auto& p : t.pending) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     cudaEventDestroy(c->evFork); cudaEventDestroy(c->evPmeDone);
@@ -479,34 +480,87 @@ void b200_sync_host_order(b200_ctx* c) {
 // ---- state I/O.  The permutation between the caller's particle order and the device order, the float/correction split of
 // mixed precision and the fixed-point -> double conversion all run on the GPU; the host only moves contiguous double arrays
 // (through a pinned staging buffer filled by a few threads, so both the memcpy and the PCIe copy run near full speed).
+#include <atomic>
 #include <thread>
 static void ensureStaging(b200_ctx* c) {
     if (c->hStage) return;
     CUDA_CHECK(cudaMallocHost((void**)&c->hStage, sizeof(double) * 3 * (size_t)c->Npad));
     dmalloc(c->dStage, 3 * (size_t)c->Npad);
 }
-static void parallelCopy(void* dst, const void* src, size_t bytes) {
-    const int nt = bytes > (4u << 20) ? 6 : 1;
-    if (nt == 1) { memcpy(dst, src, bytes); return; }
-    std::vector<std::thread> th;
-    const size_t chunk = (bytes / nt + 63) & ~(size_t)63;
-    for (int t = 0; t < nt; t++) {
-        const size_t off = (size_t)t * chunk;
-        if (off >= bytes) break;
-        const size_t len = std::min(chunk, bytes - off);
-        th.emplace_back([=] { memcpy((char*)dst + off, (const char*)src + off, len); });
-    }
-    for (auto& x : th) x.join();
+// Host <-> device staging of the caller's double[3N] arrays.
+//   * a caller buffer that is already page-locked (cudaHostAlloc / cudaHostRegister, e.g. a pinned torch tensor) is used by the
+//     DMA engine directly;
+//   * a pageable buffer goes through the context's pinned staging area in chunks: worker threads copy chunk k+1.. while the
+//     DMA of chunk k is in flight, so the cost is max(host copy, PCIe) instead of their sum.
+static bool isPinned(const void* p) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeHost;
 }
+#define IO_CHUNKS 16
+#define IO_THREADS 8
 static void stageIn(b200_ctx* c, const double* xyz) {
     ensureStaging(c);
-    parallelCopy(c->hStage, xyz, sizeof(double) * 3 * (size_t)c->N);
-    CUDA_CHECK(cudaMemcpyAsync(c->dStage, c->hStage, sizeof(double) * 3 * (size_t)c->N, cudaMemcpyHostToDevice, c->stream));
+    const size_t bytes = sizeof(double) * 3 * (size_t)c->N;
+    if (isPinned(xyz)) { CUDA_CHECK(cudaMemcpyAsync(c->dStage, xyz, bytes, cudaMemcpyHostToDevice, c->stream)); return; }
+    if (bytes < (4u << 20)) {
+        memcpy(c->hStage, xyz, bytes);
+        CUDA_CHECK(cudaMemcpyAsync(c->dStage, c->hStage, bytes, cudaMemcpyHostToDevice, c->stream));
+        return;
+    }
+    const size_t chunk = ((bytes + IO_CHUNKS - 1) / IO_CHUNKS + 4095) & ~(size_t)4095;
+    std::atomic<int> done[IO_CHUNKS];
+    for (auto& d : done) d.store(0);
+    std::vector<std::thread> th;
+    for (int t = 0; t < IO_THREADS; t++) th.emplace_back([&, t] {
+        for (int k = t; k < IO_CHUNKS; k += IO_THREADS) {
+            const size_t off = (size_t)k * chunk;
+            if (off < bytes) memcpy((char*)c->hStage + off, (const char*)xyz + off, std::min(chunk, bytes - off));
+            done[k].store(1, std::memory_order_release);
+        }
+    });
+    cudaError_t err = cudaSuccess;
+    for (int k = 0; k < IO_CHUNKS; k++) {
+        while (!done[k].load(std::memory_order_acquire)) std::this_thread::yield();
+        const size_t off = (size_t)k * chunk;
+        if (off < bytes && err == cudaSuccess)
+            err = cudaMemcpyAsync((char*)c->dStage + off, (const char*)c->hStage + off, std::min(chunk, bytes - off), cudaMemcpyHostToDevice, c->stream);
+    }
+    for (auto& x : th) x.join();
+    CUDA_CHECK(err);
 }
 static void stageOut(b200_ctx* c, double* xyz) {
-    CUDA_CHECK(cudaMemcpyAsync(c->hStage, c->dStage, sizeof(double) * 3 * (size_t)c->N, cudaMemcpyDeviceToHost, c->stream));
+    const size_t bytes = sizeof(double) * 3 * (size_t)c->N;
+    if (isPinned(xyz)) {
+        CUDA_CHECK(cudaMemcpyAsync(xyz, c->dStage, bytes, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        return;
+    }
+    if (bytes < (4u << 20)) {
+        CUDA_CHECK(cudaMemcpyAsync(c->hStage, c->dStage, bytes, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        memcpy(xyz, c->hStage, bytes);
+        return;
+    }
+    const size_t chunk = ((bytes + IO_CHUNKS - 1) / IO_CHUNKS + 4095) & ~(size_t)4095;
+    if (c->ioEvents.empty()) { c->ioEvents.resize(IO_CHUNKS); for (auto& e : c->ioEvents) CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); }
+    for (int k = 0; k < IO_CHUNKS; k++) {
+        const size_t off = (size_t)k * chunk;
+        if (off < bytes) CUDA_CHECK(cudaMemcpyAsync((char*)c->hStage + off, (const char*)c->dStage + off, std::min(chunk, bytes - off), cudaMemcpyDeviceToHost, c->stream));
+        CUDA_CHECK(cudaEventRecord(c->ioEvents[k], c->stream));
+    }
+    std::vector<std::thread> th;
+    std::atomic<int> failed(0);
+    for (int t = 0; t < IO_THREADS; t++) th.emplace_back([&, t] {
+        for (int k = t; k < IO_CHUNKS; k += IO_THREADS) {
+            if (cudaEventSynchronize(c->ioEvents[k]) != cudaSuccess) { failed.store(1); continue; }
+            const size_t off = (size_t)k * chunk;
+            if (off < bytes) memcpy((char*)xyz + off, (const char*)c->hStage + off, std::min(chunk, bytes - off));
+        }
+    });
+    for (auto& x : th) x.join();
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    parallelCopy(xyz, c->hStage, sizeof(double) * 3 * (size_t)c->N);
+    if (failed.load()) throw B200Error(B200_ERR_CUDA, "device to host copy failed");
 }
 
 // CommonKernels.cpp:182-227: float cast + correction in the device order, cell offsets reset

@@ -110,6 +110,7 @@ struct b200_ctx {
     DevCounters* counters = nullptr;
     DevCounters* countersHost = nullptr;  // pinned
     double* hStage = nullptr; double* dStage = nullptr;   // pinned host / device staging ([3N] doubles, caller's order) for state I/O
+    std::vector<cudaEvent_t> ioEvents;                    // one per chunk of a pipelined device-to-host copy
     bool chargesUploaded = false;
     // scratch for reorder
     float4* posqTmp = nullptr; float4* posqCorrTmp = nullptr; double4* velmTmp = nullptr; int* atomIndexTmp = nullptr; int4* cellOffsetsTmp = nullptr;

@@ -14,7 +14,7 @@ import numpy as np
 FORCE_SCALE = 4294967296.0
 
 
-def shares(nranks, pme_cost_ratio=0.5, with_communicator=True):
+def shares(nranks, pme_cost_ratio=0.38, with_communicator=True):
     """fraction of the direct-space rows each rank takes; rank 0 also runs PME (b200_comm.cu b200_set_partition)"""
     if nranks == 1 or not with_communicator:
         return [1.0 / nranks] * nranks
