@@ -7,6 +7,7 @@
 #include "b200_internal.cuh"
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstring>
 #include <map>
 #include <numeric>
@@ -396,6 +397,8 @@ void b200_finalize(b200_ctx* c) {
             sa.push_back(make_int4(a0, a1, a2, 0)); sp.push_back(make_float2((float)d01, (float)d12));
         }
         c->numSettle = (int)sa.size();
+        c->hSettleAtoms.clear();
+        for (const int4& q : sa) { c->hSettleAtoms.push_back(q.x); c->hSettleAtoms.push_back(q.y); c->hSettleAtoms.push_back(q.z); c->hSettleAtoms.push_back(q.w); }
         dmalloc(c->settleAtoms, sa.size()); dmalloc(c->settleParams, sp.size());
         if (!sa.empty()) {
             CUDA_CHECK(cudaMemcpy(c->settleAtoms, sa.data(), sizeof(int4) * sa.size(), cudaMemcpyHostToDevice));
@@ -410,6 +413,7 @@ void b200_finalize(b200_ctx* c) {
         }
         c->numOtherConstraints /= 2;
         c->numFree = (int)freeAtoms.size();
+        c->hFreeAtoms = freeAtoms;
         dmalloc(c->freeAtoms, freeAtoms.size());
         if (!freeAtoms.empty()) CUDA_CHECK(cudaMemcpy(c->freeAtoms, freeAtoms.data(), sizeof(int) * freeAtoms.size(), cudaMemcpyHostToDevice));
     }
@@ -632,6 +636,7 @@ extern "C" int b200_set_positions(b200_ctx* c, const double* xyz) {
 extern "C" int b200_get_positions(b200_ctx* c, double* xyz, int32_t enforcePeriodic) {
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
+    b200_peer_sync_state(c);
     ensureStaging(c);
     ioGetPositions<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->posq, c->posqCorr, c->cellOffsets, c->boxD, enforcePeriodic ? 0 : 1);
     LAUNCH_COUNT(c, 1);
@@ -653,6 +658,7 @@ extern "C" int b200_set_velocities(b200_ctx* c, const double* xyz) {
 extern "C" int b200_get_velocities(b200_ctx* c, double* xyz) {
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
+    b200_peer_sync_state(c);
     ensureStaging(c);
     ioGetVelocities<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->velm);
     LAUNCH_COUNT(c, 1);
@@ -714,7 +720,7 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     CUDA_CHECK(cudaSetDevice(c->device));
     if (!c->positionsSet) throw B200Error(B200_ERR_INVALID, "Particle positions have not been set");
     b200_finalize(c);
-    if (c->stepsSinceReorder < 0 || c->stepsSinceReorder >= c->reorderInterval) b200_reorder(c);
+    if (c->stepsSinceReorder < 0 || c->stepsSinceReorder >= c->reorderInterval) { b200_peer_sync_state(c); b200_reorder(c); }   // the sort moves whole-state rows
     cudaStream_t s = c->stream;
     if (forces) CUDA_CHECK(cudaMemsetAsync(c->force, 0, sizeof(long long) * 3 * (size_t)c->Npad, s));
     if (energy) { zeroEnergy<<<1, 1, 0, s>>>(c->counters); LAUNCH_COUNT(c, 1); }
@@ -734,7 +740,7 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     }
     if (c->partRank == 0 || c->commRanks > 1) b200_bonded_launch(c, groups, forces, energy);
     if (doRecip && usePmeStream) CUDA_CHECK(cudaStreamWaitEvent(s, c->evPmeDone, 0));
-    if (forces && c->commRanks > 1) b200_comm_allreduce_forces(c);
+    if (forces && c->commRanks > 1 && !c->peerStepActive) b200_comm_allreduce_forces(c);   // peer step: the integration kernel sums the ranks' forces itself
     if (energy && c->commRanks > 1) b200_comm_allreduce_energy(c);
     c->forcesValid = forces && groups == B200_GROUP_ALL;
     if (energy) {
@@ -828,14 +834,45 @@ extern "C" int b200_step(b200_ctx* c, int32_t nsteps) {
     b200_finalize(c);
     if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
     c->fusedStepExtras = true;
+    // peer-memory step: needs the fused COM/displacement extras (they are what keeps the ranks' flags and momenta in step)
+    c->peerStepActive = c->peerMode && c->commRanks > 1 && c->integ.remove_cm_every <= 1 && c->hasNonbonded;
+    if (c->peerStepActive) b200_peer_plan_shard(c);
+    // B200_PEER_TRACE=1: event time line of the last step of this call (debug aid for the multi-GPU step)
+    static const bool trace = getenv("B200_PEER_TRACE") != nullptr;
+    cudaEvent_t ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     for (int i = 0; i < nsteps; i++) {
+        const bool tr = trace && i == nsteps - 1 && nsteps > 1;
+        auto mark = [&](int k) { if (tr) { cudaEventCreate(&ev[k]); cudaEventRecord(ev[k], c->stream); } };
         c->skipDispCheck = i > 0;     // from the second step on, the integrator kernel of the previous step did the check
+        mark(0);
         computeImpl(c, B200_GROUP_ALL, true, false, nullptr, i == 0 || (c->stepCount & 63) == 0);
+        mark(1);
+        if (c->peerStepActive) {
+            b200_peer_barrier(c, PEER_SLOT_FORCES);                           // every rank's partial forces are complete
+            mark(2);
+            if (c->shardContiguous) b200_peer_reduce_forces(c);               // reduce-scatter over NVLink into the local array
+        }
+        mark(3);
         b200_integrate_step(c);
+        mark(4);
+        if (c->peerStepActive) {
+            if (c->shardContiguous) b200_peer_publish_positions(c);           // all-gather
+            mark(5);
+            b200_peer_barrier(c, PEER_SLOT_POSITIONS);                        // every rank's slice of new positions has arrived everywhere
+        }
+        mark(6);
         c->stepCount++; c->timePs += c->integ.dt; c->stepsSinceReorder++;
         c->forcesValid = false;
+        if (tr) {
+            cudaStreamSynchronize(c->stream);
+            float t[7] = {0, 0, 0, 0, 0, 0, 0};
+            for (int k = 1; k < 7; k++) if (ev[k] && ev[0]) cudaEventElapsedTime(&t[k], ev[0], ev[k]);
+            fprintf(stderr, "[b200 rank %d] step time line (us): forces %.0f | barrier %.0f | reduce %.0f | integrate %.0f | publish %.0f | barrier %.0f\n", c->commRank,
+                    1e3 * t[1], 1e3 * (t[2] - t[1]), 1e3 * (t[3] - t[2]), 1e3 * (t[4] - t[3]), 1e3 * (t[5] - t[4]), 1e3 * (t[6] - t[5]));
+            for (auto& e : ev) if (e) { cudaEventDestroy(e); e = nullptr; }
+        }
     }
-    c->skipDispCheck = false; c->fusedStepExtras = false;
+    c->skipDispCheck = false; c->fusedStepExtras = false; c->peerStepActive = false;
     checkOverflow(c);
     if (c->countersHost->overflow) throw B200Error(B200_ERR_OVERFLOW, "neighbour list overflowed during b200_step; state is not trustworthy");
     API_END

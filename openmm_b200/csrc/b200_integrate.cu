@@ -8,6 +8,8 @@
 // Noise comes from a counter-based Philox4x32-10 generator keyed by (seed, step, original particle index), so a
 // trajectory does not depend on the atom order on the device nor on the number of GPUs.
 #include "b200_internal.cuh"
+#include <algorithm>
+#include <cstring>
 
 struct V3 { double x, y, z; };
 __device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
@@ -48,17 +50,27 @@ struct IntegArgs {
     // (findInteractingBlocks.cu:176-185) ride along, so a step needs no separate passes over the atoms for them
     const float4* refPosq; float maxDisp2; DevCounters* counters;
     int fuseCM; int cmCur, cmNext, cmClear; double invTotalMass;
+    // peer-memory step (b200_comm.cu): this rank integrates units [unitBegin, unitEnd) only, sums the force contributions of all
+    // ranks out of their memories and stores the new positions into every rank's posq
+    int usePeers, unitBegin, unitEnd; PeerSet peers;
 };
 #define CM_SCALE 1048576.0   // 2^20 fixed point for momentum sums
 
 __device__ __forceinline__ V3 loadPosD(const IntegArgs& a, int i) { const float4 p = a.posq[i], q = a.posqCorr[i]; return {(double)p.x + q.x, (double)p.y + q.y, (double)p.z + q.z}; }
 __device__ __forceinline__ void storePosD(const IntegArgs& a, int i, V3 p) {
     const float w = a.posq[i].w;
-    a.posq[i] = make_float4((float)p.x, (float)p.y, (float)p.z, w);
+    const float4 np = make_float4((float)p.x, (float)p.y, (float)p.z, w);
+    a.posq[i] = np;
+    if (a.usePeers == 1) for (int r = 0; r < a.peers.n; r++) if (r != a.peers.rank) a.peers.posq[r][i] = np;      // the all-gather (scattered form)
     a.posqCorr[i] = make_float4((float)(p.x - (double)(float)p.x), (float)(p.y - (double)(float)p.y), (float)(p.z - (double)(float)p.z), 0.f);
 }
 __device__ __forceinline__ V3 loadForce(const IntegArgs& a, int i) {
     const double sc = 1.0 / B200_FORCE_SCALE;
+    if (a.usePeers == 1) {   // the reduce-scatter (scattered form): exact integer sum of every rank's partial forces for this atom
+        long long fx = 0, fy = 0, fz = 0;
+        for (int r = 0; r < a.peers.n; r++) { const long long* f = a.peers.force[r]; fx += f[i]; fy += f[i + a.Npad]; fz += f[i + 2 * a.Npad]; }
+        return {sc * (double)fx, sc * (double)fy, sc * (double)fz};
+    }
     return {sc * (double)a.force[i], sc * (double)a.force[i + a.Npad], sc * (double)a.force[i + 2 * a.Npad]};
 }
 
@@ -130,16 +142,17 @@ __device__ __forceinline__ void checkMoved(const IntegArgs& a, int i, V3 p, bool
 
 __global__ void __launch_bounds__(128, 4) langevinMiddleStep(IntegArgs a, int numSettle, const int4* __restrict__ settleAtoms, const float2* __restrict__ settleParams,
                                                            int numFree, const int* __restrict__ freeAtoms) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int t = a.unitBegin + blockIdx.x * blockDim.x + threadIdx.x;   // unitBegin is a multiple of the block size: blocks group the same units on any rank count
     const double halfdt = 0.5 * a.dt, invDt = 1.0 / a.dt;
     V3 vcm = {0, 0, 0}, mom = {0, 0, 0};
     if (a.fuseCM) {
         const double sc = a.invTotalMass / CM_SCALE;
         vcm = {sc * (double)a.counters->cm[a.cmCur][0], sc * (double)a.counters->cm[a.cmCur][1], sc * (double)a.counters->cm[a.cmCur][2]};
-        if (t == 0) { a.counters->cm[a.cmClear][0] = 0; a.counters->cm[a.cmClear][1] = 0; a.counters->cm[a.cmClear][2] = 0; }
+        if (blockIdx.x == 0 && threadIdx.x == 0) { a.counters->cm[a.cmClear][0] = 0; a.counters->cm[a.cmClear][1] = 0; a.counters->cm[a.cmClear][2] = 0; }
     }
     bool moved = false;
-    if (t < numSettle) {
+    if (t >= a.unitEnd) {
+    } else if (t < numSettle) {
         const int4 at = settleAtoms[t]; const float2 prm = settleParams[t];
         const int idx[3] = {at.x, at.y, at.z};
         V3 p[3], v[3], d[3], old[3]; double im[3];
@@ -183,7 +196,10 @@ __global__ void __launch_bounds__(128, 4) langevinMiddleStep(IntegArgs a, int nu
         checkMoved(a, i, pn, moved);
         mom = mom + v * (1.0 / vm.w);
     }
-    if (a.refPosq && __any_sync(0xffffffffu, moved) && (threadIdx.x & 31) == 0) a.counters->rebuild = 1;
+    if (a.refPosq && __any_sync(0xffffffffu, moved) && (threadIdx.x & 31) == 0) {
+        a.counters->rebuild = 1;
+        if (a.usePeers) for (int r = 0; r < a.peers.n; r++) if (r != a.peers.rank) a.peers.counters[r]->rebuild = 1;
+    }
     if (a.fuseCM) {   // momentum of the new velocities, removed at the start of the next step (fixed-order block sum, integer atomics)
         __shared__ double red[3][128];
         red[0][threadIdx.x] = mom.x; red[1][threadIdx.x] = mom.y; red[2][threadIdx.x] = mom.z;
@@ -192,7 +208,11 @@ __global__ void __launch_bounds__(128, 4) langevinMiddleStep(IntegArgs a, int nu
             if (threadIdx.x < o) for (int k = 0; k < 3; k++) red[k][threadIdx.x] += red[k][threadIdx.x + o];
             __syncthreads();
         }
-        if (threadIdx.x < 3) atomicAddFixed(&a.counters->cm[a.cmNext][threadIdx.x], (long long)(red[threadIdx.x][0] * CM_SCALE));
+        if (threadIdx.x < 3) {
+            const long long v = (long long)(red[threadIdx.x][0] * CM_SCALE);
+            atomicAddFixed(&a.counters->cm[a.cmNext][threadIdx.x], v);
+            if (a.usePeers) for (int r = 0; r < a.peers.n; r++) if (r != a.peers.rank) atomicAddFixed(&a.peers.counters[r]->cm[a.cmNext][threadIdx.x], v);
+        }
     }
 }
 
@@ -265,12 +285,19 @@ static IntegArgs makeArgs(b200_ctx* c) {
     a.noisescale = sqrt(kT * (1.0 - a.vscale * a.vscale));
     a.seed = c->integ.seed; a.step = (unsigned long long)c->stepCount;
     a.refPosq = nullptr; a.maxDisp2 = 0.f; a.counters = c->counters; a.fuseCM = 0; a.cmCur = a.cmNext = a.cmClear = 0; a.invTotalMass = 0;
+    a.usePeers = 0; a.unitBegin = 0; a.unitEnd = c->numSettle + c->numFree; memset(&a.peers, 0, sizeof(a.peers));
     return a;
+}
+
+// sum of the particle masses, computed once (this is on the per-step host path)
+static double totalMass(b200_ctx* c) {
+    if (c->totalMassCached <= 0) { double t = 0; for (double m : c->mass) t += m; c->totalMassCached = t; }
+    return c->totalMassCached;
 }
 
 static void removeCM(b200_ctx* c) {
     cudaStream_t s = c->stream;
-    double total = 0; for (double m : c->mass) total += m;
+    const double total = totalMass(c);
     cmZero<<<1, 1, 0, s>>>(c->counters, 3);
     cmMomentum<<<c->smCount * 2, 256, 0, s>>>(c->velm, c->N, c->counters, 3);
     cmRemove<<<c->smCount * 4, 256, 0, s>>>(c->velm, c->N, 1.0 / total, c->counters, 3);
@@ -280,7 +307,7 @@ static void removeCM(b200_ctx* c) {
 
 // RemoveCMMotionKernel::execute (kernels.h:1793)
 extern "C" int b200_remove_cm_motion(b200_ctx* c) {
-    try { CUDA_CHECK(cudaSetDevice(c->device)); removeCM(c); CUDA_CHECK(cudaGetLastError()); }
+    try { CUDA_CHECK(cudaSetDevice(c->device)); b200_peer_sync_state(c); removeCM(c); CUDA_CHECK(cudaGetLastError()); }
     catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
     return B200_OK;
 }
@@ -290,6 +317,7 @@ extern "C" int b200_integrate(b200_ctx* c) {
     try {
         if (!c->hasIntegrator) throw B200Error(B200_ERR_INVALID, "b200_integrate: no integrator");
         CUDA_CHECK(cudaSetDevice(c->device));
+        b200_peer_sync_state(c);
         b200_finalize(c);
         if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
         const int keep = c->integ.remove_cm_every;
@@ -314,13 +342,21 @@ void b200_integrate_step(b200_ctx* c) {
             LAUNCH_COUNT(c, 4);
             c->cmValid = true;
         }
-        double total = 0; for (double m : c->mass) total += m;
+        const double total = totalMass(c);
         a.fuseCM = 1; a.invTotalMass = 1.0 / total;
         a.cmCur = (int)(c->stepCount % 3); a.cmNext = (int)((c->stepCount + 1) % 3); a.cmClear = (int)((c->stepCount + 2) % 3);
     } else if (c->integ.remove_cm_every > 0 && c->stepCount % c->integ.remove_cm_every == 0) removeCM(c);
     if (c->fusedStepExtras && c->hasNonbonded) { a.refPosq = c->refPosq; const float md = 0.5f * (float)c->padding; a.maxDisp2 = md * md; }
     const int units = c->numSettle + c->numFree;
-    if (units > 0) {
+    if (c->peerStepActive) {
+        // a.usePeers = 1: per-atom loads/stores through peer memory; 2: the forces of this slice were already reduced into the local
+        // array and the positions are published afterwards by range copies (slice = one contiguous range of slots)
+        a.usePeers = c->shardContiguous ? 2 : 1; a.peers = c->peers; a.unitBegin = c->shardBegin; a.unitEnd = c->shardEnd;
+        const int mine = c->shardEnd - c->shardBegin;
+        langevinMiddleStep<<<std::max(1, (mine + 127) / 128), 128, 0, s>>>(a, c->numSettle, c->settleAtoms, c->settleParams, c->numFree, c->freeAtoms);
+        LAUNCH_COUNT(c, 1);
+        c->shardsDirty = true;
+    } else if (units > 0) {
         langevinMiddleStep<<<(units + 127) / 128, 128, 0, s>>>(a, c->numSettle, c->settleAtoms, c->settleParams, c->numFree, c->freeAtoms);
         LAUNCH_COUNT(c, 1);
     }
@@ -330,6 +366,7 @@ void b200_integrate_step(b200_ctx* c) {
 extern "C" int b200_apply_constraints(b200_ctx* c, double) {
     try {
         CUDA_CHECK(cudaSetDevice(c->device));
+        b200_peer_sync_state(c);
         b200_finalize(c);
         if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
         if (c->numSettle > 0) { settleOnly<<<(c->numSettle + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, 0); LAUNCH_COUNT(c, 1); }
@@ -341,6 +378,7 @@ extern "C" int b200_apply_constraints(b200_ctx* c, double) {
 extern "C" int b200_apply_velocity_constraints(b200_ctx* c, double) {
     try {
         CUDA_CHECK(cudaSetDevice(c->device));
+        b200_peer_sync_state(c);
         b200_finalize(c);
         if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
         if (c->numSettle > 0) { settleOnly<<<(c->numSettle + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, 1); LAUNCH_COUNT(c, 1); }
@@ -352,6 +390,7 @@ extern "C" int b200_apply_velocity_constraints(b200_ctx* c, double) {
 extern "C" int b200_kinetic_energy(b200_ctx* c, double* ke) {
     try {
         CUDA_CHECK(cudaSetDevice(c->device));
+        b200_peer_sync_state(c);
         keZero<<<1, 1, 0, c->stream>>>(c->counters);
         kineticEnergy<<<c->smCount * 2, 256, 0, c->stream>>>(c->velm, c->N, c->counters);
         LAUNCH_COUNT(c, 2);

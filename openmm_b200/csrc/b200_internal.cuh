@@ -70,6 +70,17 @@ struct FFTPlan1D {
     int radix[12];
 };
 
+// peer-memory view of the other ranks' state arrays (CUDA IPC over NVLink), see b200_comm.cu
+#define B200_MAX_PEERS 8
+struct PeerSet {
+    long long* force[B200_MAX_PEERS]; float4* posq[B200_MAX_PEERS]; float4* posqCorr[B200_MAX_PEERS]; double4* velm[B200_MAX_PEERS];
+    struct DevCounters* counters[B200_MAX_PEERS]; unsigned long long* flags[B200_MAX_PEERS];
+    int n, rank;
+};
+#define PEER_SLOT_FORCES 0      // "my forces of step seq are complete"
+#define PEER_SLOT_POSITIONS 1   // "my shard of step seq is integrated and written to every rank"
+#define PEER_SLOT_STATE 2       // "my shard's velocities / position remainders are written to every rank"
+
 // one reciprocal-space mesh with its transforms
 struct PmeMesh {
     int gridN[3] = {0, 0, 0}; int nzc = 0;
@@ -126,6 +137,8 @@ struct b200_ctx {
     std::vector<int> conAtoms; std::vector<double> conDist;
     int numSettle = 0; int4* settleAtoms = nullptr; float2* settleParams = nullptr;  // (a0,a1,a2,-), (dist01, dist12)
     int numFree = 0; int* freeAtoms = nullptr;      // unconstrained, mobile atoms
+    double totalMassCached = 0;
+    std::vector<int> hSettleAtoms, hFreeAtoms;      // host copies (4 ints per cluster), used to plan the multi-GPU integration slices
     int numOtherConstraints = 0;
 
     // molecules
@@ -162,6 +175,16 @@ struct b200_ctx {
     struct OwnerTable { unsigned char owner[64]; } partTable;   // row X belongs to rank owner[X & 63] (weighted round-robin)
     double partShareBegin = 0.0, partShareEnd = 1.0;           // this rank's slice of the exclusion-tile index range
     int sparseMax = 5;             // j atoms reaching at most this many atoms of X are handled as sparse pairs
+
+    // fused reduce + integrate + gather over peer memory (b200_comm.cu, b200_integrate.cu)
+    bool peerMode = false;          // IPC mappings established on every rank
+    bool peerStepActive = false;    // inside b200_step in peer mode: no NCCL all-reduce of the forces
+    bool shardsDirty = false;       // velm / posqCorr are current only for this rank's shard of the integration units
+    PeerSet peers;
+    unsigned long long* peerFlags = nullptr;
+    unsigned long long peerSeq[3] = {0, 0, 0};
+    int shardBegin = 0, shardEnd = 0;   // this rank's range of integration units (SETTLE clusters, then free atoms)
+    int shardAtomBegin = 0, shardAtomEnd = 0; bool shardContiguous = false; int shardUnitsFor = -1;   // atoms of those units, when they form one slot range
 
     // PME: mesh[0] = Coulomb, mesh[1] = dispersion (LJPME only)
     PmeMesh mesh[2];
@@ -225,6 +248,11 @@ void b200_integrate_step(b200_ctx* c);
 void b200_comm_allreduce_forces(b200_ctx* c);
 void b200_comm_allreduce_energy(b200_ctx* c);
 void b200_comm_destroy(b200_ctx* c);
+void b200_peer_barrier(b200_ctx* c, int slot);        // signal + wait on the compute stream (device-side, no host sync)
+void b200_peer_sync_state(b200_ctx* c);
+void b200_peer_plan_shard(b200_ctx* c);               // unit slice of this rank and whether its atoms are one contiguous slot range
+void b200_peer_reduce_forces(b200_ctx* c);            // sum of all ranks' partial forces for this rank's atom range -> local force array
+void b200_peer_publish_positions(b200_ctx* c);        // this rank's slice of posq -> every rank               // all-gather of the sharded velocities / position remainders (collective)
 void b200_fft_make_plan(int n, FFTPlan1D& plan);
 void b200_fft_make_twiddle(int n, float2*& dTw, cudaStream_t s);
 void b200_fft3d_reciprocal(b200_ctx* c, PmeMesh& m, cudaStream_t s, const PmeArgs& a, bool energy, bool forces);   // gridI -> (convolution, energy) -> gridReal
