@@ -57,16 +57,18 @@ struct IntegArgs {
 #define CM_SCALE 1048576.0   // 2^20 fixed point for momentum sums
 
 __device__ __forceinline__ V3 loadPosD(const IntegArgs& a, int i) { const float4 p = a.posq[i], q = a.posqCorr[i]; return {(double)p.x + q.x, (double)p.y + q.y, (double)p.z + q.z}; }
+template <bool PEER = false>
 __device__ __forceinline__ void storePosD(const IntegArgs& a, int i, V3 p) {
     const float w = a.posq[i].w;
     const float4 np = make_float4((float)p.x, (float)p.y, (float)p.z, w);
     a.posq[i] = np;
-    if (a.usePeers == 1) for (int r = 0; r < a.peers.n; r++) if (r != a.peers.rank) a.peers.posq[r][i] = np;      // the all-gather (scattered form)
+    if (PEER && a.usePeers == 1) for (int r = 0; r < a.peers.n; r++) if (r != a.peers.rank) a.peers.posq[r][i] = np;      // the all-gather (scattered form)
     a.posqCorr[i] = make_float4((float)(p.x - (double)(float)p.x), (float)(p.y - (double)(float)p.y), (float)(p.z - (double)(float)p.z), 0.f);
 }
+template <bool PEER = false>
 __device__ __forceinline__ V3 loadForce(const IntegArgs& a, int i) {
     const double sc = 1.0 / B200_FORCE_SCALE;
-    if (a.usePeers == 1) {   // the reduce-scatter (scattered form): exact integer sum of every rank's partial forces for this atom
+    if (PEER && a.usePeers == 1) {   // the reduce-scatter (scattered form): exact integer sum of every rank's partial forces for this atom
         long long fx = 0, fy = 0, fz = 0;
         for (int r = 0; r < a.peers.n; r++) { const long long* f = a.peers.force[r]; fx += f[i]; fy += f[i + a.Npad]; fz += f[i + 2 * a.Npad]; }
         return {sc * (double)fx, sc * (double)fy, sc * (double)fz};
@@ -140,6 +142,8 @@ __device__ __forceinline__ void checkMoved(const IntegArgs& a, int i, V3 p, bool
     moved |= dx * dx + dy * dy + dz * dz > a.maxDisp2;
 }
 
+// PEER: multi-GPU instantiation (peer-memory accesses compiled in); the single-GPU kernel carries none of that code
+template <bool PEER>
 __global__ void __launch_bounds__(128, 4) langevinMiddleStep(IntegArgs a, int numSettle, const int4* __restrict__ settleAtoms, const float2* __restrict__ settleParams,
                                                            int numFree, const int* __restrict__ freeAtoms) {
     const int t = a.unitBegin + blockIdx.x * blockDim.x + threadIdx.x;   // unitBegin is a multiple of the block size: blocks group the same units on any rank count
@@ -161,7 +165,7 @@ __global__ void __launch_bounds__(128, 4) langevinMiddleStep(IntegArgs a, int nu
             p[k] = loadPosD(a, idx[k]);
             const double4 vm = a.velm[idx[k]];
             im[k] = vm.w;
-            v[k] = V3{vm.x, vm.y, vm.z} - vcm + loadForce(a, idx[k]) * (a.dt * vm.w);    // COM removal, then part 1
+            v[k] = V3{vm.x, vm.y, vm.z} - vcm + loadForce<PEER>(a, idx[k]) * (a.dt * vm.w);    // COM removal, then part 1
         }
         settleVelocities(p[0], p[1], p[2], v[0], v[1], v[2], im[0], im[1], im[2]);
 #pragma unroll
@@ -178,27 +182,27 @@ __global__ void __launch_bounds__(128, 4) langevinMiddleStep(IntegArgs a, int nu
             v[k] = v[k] + (d[k] - old[k]) * invDt;
             a.velm[idx[k]] = make_double4(v[k].x, v[k].y, v[k].z, im[k]);
             const V3 pn = p[k] + d[k];
-            storePosD(a, idx[k], pn);
+            storePosD<PEER>(a, idx[k], pn);
             checkMoved(a, idx[k], pn, moved);
             mom = mom + v[k] * (1.0 / im[k]);
         }
     } else if (t < numSettle + numFree) {
         const int i = freeAtoms[t - numSettle];
         const double4 vm = a.velm[i];
-        V3 v = V3{vm.x, vm.y, vm.z} - vcm + loadForce(a, i) * (a.dt * vm.w);
+        V3 v = V3{vm.x, vm.y, vm.z} - vcm + loadForce<PEER>(a, i) * (a.dt * vm.w);
         V3 d = v * halfdt;
         const V3 g = gaussian3(a.seed, a.step, a.atomIndex[i]);
         v = v * a.vscale + g * (a.noisescale * sqrt(vm.w));
         d = d + v * halfdt;
         a.velm[i] = make_double4(v.x, v.y, v.z, vm.w);
         const V3 pn = loadPosD(a, i) + d;
-        storePosD(a, i, pn);
+        storePosD<PEER>(a, i, pn);
         checkMoved(a, i, pn, moved);
         mom = mom + v * (1.0 / vm.w);
     }
     if (a.refPosq && __any_sync(0xffffffffu, moved) && (threadIdx.x & 31) == 0) {
         a.counters->rebuild = 1;
-        if (a.usePeers) for (int r = 0; r < a.peers.n; r++) if (r != a.peers.rank) a.peers.counters[r]->rebuild = 1;
+        if (PEER && a.usePeers) for (int r = 0; r < a.peers.n; r++) if (r != a.peers.rank) a.peers.counters[r]->rebuild = 1;
     }
     if (a.fuseCM) {   // momentum of the new velocities, removed at the start of the next step (fixed-order block sum, integer atomics)
         __shared__ double red[3][128];
@@ -211,7 +215,7 @@ __global__ void __launch_bounds__(128, 4) langevinMiddleStep(IntegArgs a, int nu
         if (threadIdx.x < 3) {
             const long long v = (long long)(red[threadIdx.x][0] * CM_SCALE);
             atomicAddFixed(&a.counters->cm[a.cmNext][threadIdx.x], v);
-            if (a.usePeers) for (int r = 0; r < a.peers.n; r++) if (r != a.peers.rank) atomicAddFixed(&a.peers.counters[r]->cm[a.cmNext][threadIdx.x], v);
+            if (PEER && a.usePeers) for (int r = 0; r < a.peers.n; r++) if (r != a.peers.rank) atomicAddFixed(&a.peers.counters[r]->cm[a.cmNext][threadIdx.x], v);
         }
     }
 }
@@ -353,11 +357,11 @@ void b200_integrate_step(b200_ctx* c) {
         // array and the positions are published afterwards by range copies (slice = one contiguous range of slots)
         a.usePeers = c->shardContiguous ? 2 : 1; a.peers = c->peers; a.unitBegin = c->shardBegin; a.unitEnd = c->shardEnd;
         const int mine = c->shardEnd - c->shardBegin;
-        langevinMiddleStep<<<std::max(1, (mine + 127) / 128), 128, 0, s>>>(a, c->numSettle, c->settleAtoms, c->settleParams, c->numFree, c->freeAtoms);
+        langevinMiddleStep<true><<<std::max(1, (mine + 127) / 128), 128, 0, s>>>(a, c->numSettle, c->settleAtoms, c->settleParams, c->numFree, c->freeAtoms);
         LAUNCH_COUNT(c, 1);
         c->shardsDirty = true;
     } else if (units > 0) {
-        langevinMiddleStep<<<(units + 127) / 128, 128, 0, s>>>(a, c->numSettle, c->settleAtoms, c->settleParams, c->numFree, c->freeAtoms);
+        langevinMiddleStep<false><<<(units + 127) / 128, 128, 0, s>>>(a, c->numSettle, c->settleAtoms, c->settleParams, c->numFree, c->freeAtoms);
         LAUNCH_COUNT(c, 1);
     }
     CUDA_CHECK(cudaGetLastError());
