@@ -11,6 +11,8 @@ exactly how they were made.
   ref_ljpme_<N>.npz    the same for NonbondedForce::LJPME (method 5): water_box(N) with CHARMM-style hydrogens (sigma 0.04 nm,
                        eps 0.192464 kJ/mol) so that three particle types enter the dispersion grid; dispersion mesh and alpha
                        as NonbondedForceImpl::calcPMEParameters(lj=true).  N = 1538, 6002.
+  water125_dpme.npy    float64 [375,3] Angstrom: the 125-water coordinates of tests/TestDispersionPME.h:406-783 (make_waterbox),
+                       used by the LJPME known-answer tests testWater125DpmeVsLongCutoff{No,With}Exclusions
   ref_ions_triclinic.npz  the 8-ion triclinic case of tests/TestEwald.h:220-269 evaluated by the Reference platform
 """
 import os
@@ -85,6 +87,20 @@ def water_ljpme(n):
     print("ljpme", n, "E", r["e_direct"], r["e_recip"])
 
 
+def water125():
+    lines = open(os.path.join(REF, "tests/TestDispersionPME.h")).read().split("\n")
+    start = next(i for i, l in enumerate(lines) if "const double coords[375][3]" in l)
+    pat = re.compile(r"\{\s*([-\d.]+),\s*([-\d.]+),\s*([-\d.]+)\s*\}")
+    pos = []
+    for l in lines[start + 1:]:
+        m = pat.search(l)
+        if not m:
+            break
+        pos.append([float(x) for x in m.groups()])
+    assert len(pos) == 375
+    np.save(os.path.join(HERE, "water125_dpme.npy"), np.array(pos))
+
+
 def ions():
     pos = np.array([[1.744, 2.788, 3.162], [1.048, 0.762, 2.340], [2.489, 1.570, 2.817], [1.027, 1.893, 3.271],
                     [0.937, 0.825, 0.009], [2.290, 1.887, 3.352], [1.266, 1.111, 2.894], [0.933, 1.862, 3.490]])
@@ -98,6 +114,8 @@ def ions():
 
 if __name__ == "__main__":
     only = sys.argv[1:]
+    if not only or "water125" in only:
+        water125()
     if not only or "base" in only:
         tip3p()
         nacl()
