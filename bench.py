@@ -265,7 +265,9 @@ def main():
     pme_bytes = 36.0 * G + 72.0 * n
     pme_ms = sum(fam[k][0] for k in ("spread", "fft", "convolve", "interpolate")) / max(prof_steps, 1)
     roofline = {"kernel": "tileKernel<forces>", "bound": "fp32", "achieved": achieved_tflops, "peak": fp32_peak, "unit": "TFLOP/s",
-                "frac": achieved_tflops / fp32_peak if fp32_peak else None, "traffic": None,
+                "frac": achieved_tflops / fp32_peak if fp32_peak else None,
+                # dram__bytes_read.sum + dram__bytes_write.sum of one launch on the stmv workload (profiles/r01_ncu_full_step_kernels_stmv.csv)
+                "traffic": 1.994e8 if (args.workload == "stmv" and world == 1) else None,
                 "peak_source": f"{sm_count} SMs x 128 lanes x 2 x {sm_max_mhz:.0f} MHz ({peak_kind} sm_max_mhz)",
                 "algorithmic": f"{FLOP_PER_PAIR:.0f} FLOP x {pairs} in-cutoff pairs per launch (this rank)",
                 "executed_pair_slots_per_launch": dense_slots,
