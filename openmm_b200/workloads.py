@@ -151,19 +151,23 @@ def make_context(sysd, cutoff=0.9, tol=5e-4, device=0, grid=None, alpha=None, lj
     return ctx
 
 
-def write_system_file(path, sysd, cutoff, alpha, grid, method=4, dispersion=False, lj_alpha=None, lj_grid=None):
+def write_system_file(path, sysd, cutoff, alpha, grid, method=4, dispersion=False, lj_alpha=None, lj_grid=None, switch_distance=None):
     """Binary system description read by oracle/ref_driver.cpp (layout documented there)."""
     n = sysd["n"]
     exc = sysd.get("exceptions")
     with open(path, "wb") as f:
         f.write(b"B2SY")
-        f.write(struct.pack("<ii", 1 if lj_alpha is None else 2, n))
+        version = 3 if switch_distance is not None else (1 if lj_alpha is None else 2)
+        f.write(struct.pack("<ii", version, n))
         f.write(np.asarray(sysd["box"], dtype="<f8").tobytes())
         f.write(struct.pack("<dd", cutoff, alpha))
         f.write(struct.pack("<iiii", int(grid[0]), int(grid[1]), int(grid[2]), method))
         f.write(struct.pack("<d", 1.0 if dispersion else 0.0))
-        if lj_alpha is not None:
-            f.write(struct.pack("<diii", lj_alpha, int(lj_grid[0]), int(lj_grid[1]), int(lj_grid[2])))
+        if version >= 2:
+            lg = lj_grid if lj_grid is not None else (0, 0, 0)
+            f.write(struct.pack("<diii", lj_alpha if lj_alpha is not None else 0.0, int(lg[0]), int(lg[1]), int(lg[2])))
+        if version >= 3:
+            f.write(struct.pack("<d", switch_distance))
         for key in ("charge", "sigma", "epsilon", "mass"):
             f.write(np.asarray(sysd[key], dtype="<f8").tobytes())
         f.write(np.asarray(sysd["positions"], dtype="<f8").reshape(-1).tobytes())

@@ -116,8 +116,16 @@ long long oracle_direct(const oracle_system* s, double* forces, double* energy, 
                     const double eps = 4.0 * sqrt(s->epsilon[i] * s->epsilon[j]);
                     double sig2 = invR * sig; sig2 *= sig2;
                     const double sig6 = sig2 * sig2 * sig2;
-                    dEdR += eps * (12.0 * sig6 - 6.0) * sig6 * invR * invR;
-                    esum += qq * invR * erfc(ar) + eps * (sig6 - 1.0) * sig6;
+                    /* switching function on the Lennard-Jones part, ReferenceLJCoulombIxn.cpp:385-390,436-439 */
+                    double switchValue = 1.0, switchDeriv = 0.0;
+                    if (s->use_switch && r > s->switch_distance) {
+                        const double w = s->cutoff - s->switch_distance, t = (r - s->switch_distance) / w;
+                        switchValue = 1.0 + t * t * t * (-10.0 + t * (15.0 - t * 6.0));
+                        switchDeriv = t * t * (-30.0 + t * (60.0 - t * 30.0)) / w;
+                    }
+                    dEdR += switchValue * eps * (12.0 * sig6 - 6.0) * sig6 * invR * invR;
+                    double vdw = eps * (sig6 - 1.0) * sig6;
+                    esum += qq * invR * erfc(ar);
                     if (s->ljpme) {
                         /* ReferenceLJCoulombIxn.cpp:404-431: remove the multiplicative C6 term the dispersion grid adds, plus the
                            potential shift between the additive and multiplicative forms at the cutoff */
@@ -132,8 +140,10 @@ long long oracle_direct(const oracle_system* s, double* forces, double* energy, 
                         double shift = eps * (1.0 - s6 * invCut6) * s6 * invCut6;
                         const double dc2 = s->lj_alpha * s->lj_alpha * rc2, dc4 = dc2 * dc2;
                         shift -= c6i * c6j * invCut6 * (1.0 - exp(-dc2) * (1.0 + dc2 + 0.5 * dc4));
-                        esum += emult + shift;
+                        vdw += emult + shift;
                     }
+                    if (s->use_switch) { dEdR -= vdw * switchDeriv * invR; vdw *= switchValue; }
+                    esum += vdw;
                     if (forces) for (int k = 0; k < 3; k++) { forces[3 * i + k] -= dEdR * d[k]; forces[3 * j + k] += dEdR * d[k]; }
                 }
             }

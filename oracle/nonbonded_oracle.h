@@ -22,6 +22,8 @@ typedef struct {
     int ljpme;              /* 1: LJPME (dispersion treated with a second PME grid) */
     double lj_alpha;        /* dispersion Ewald coefficient */
     int lj_grid[3];         /* dispersion mesh */
+    int use_switch;         /* 1: Lennard-Jones switching function between switch_distance and cutoff */
+    double switch_distance;
 } oracle_system;
 
 /* direct space, pairs with r <= cutoff that are not excluded; forces [3n] are ADDED to; returns pair count.

@@ -11,7 +11,7 @@
 //
 // system.bin layout (little endian), written by openmm_b200/system_io.py:
 //   char[4] "B2SY"; int32 version=1; int32 N; double box[9]; double cutoff; double alpha; int32 grid[3]; int32 method;
-//   double dispersionCorrection(0/1); [version 2 only: double ljAlpha; int32 ljGrid[3];] double charge[N], sigma[N], epsilon[N], mass[N]; double pos[3N]; double vel[3N];
+//   double dispersionCorrection(0/1); [version >= 2: double ljAlpha; int32 ljGrid[3];] [version >= 3: double switchDistance;] double charge[N], sigma[N], epsilon[N], mass[N]; double pos[3N]; double vel[3N];
 //   int32 nexc; {int32 i, j; double qq, sigma, eps}[nexc]; int32 ncon; {int32 i, j; double d}[ncon]
 #include "OpenMM.h"
 #include "openmm/internal/ContextImpl.h"
@@ -29,7 +29,7 @@ using namespace OpenMM;
 using namespace std;
 
 struct SystemFile {
-    int N = 0; double box[9]; double cutoff = 0, alpha = 0; int grid[3]; int method = 4; double dispersion = 0; double ljAlpha = 0; int ljGrid[3] = {0, 0, 0};
+    int N = 0; double box[9]; double cutoff = 0, alpha = 0; int grid[3]; int method = 4; double dispersion = 0; double ljAlpha = 0; int ljGrid[3] = {0, 0, 0}; double switchDistance = -1;
     vector<double> charge, sigma, eps, mass, pos, vel;
     struct Exc { int i, j; double qq, sig, eps; }; vector<Exc> exc;
     struct Con { int i, j; double d; }; vector<Con> con;
@@ -46,6 +46,7 @@ static SystemFile readSystem(const string& path) {
     SystemFile s;
     rd(f, &s.N, 1); rd(f, s.box, 9); rd(f, &s.cutoff, 1); rd(f, &s.alpha, 1); rd(f, s.grid, 3); rd(f, &s.method, 1); rd(f, &s.dispersion, 1);
     if (version >= 2) { rd(f, &s.ljAlpha, 1); rd(f, s.ljGrid, 3); }
+    if (version >= 3) rd(f, &s.switchDistance, 1);
     const size_t N = s.N;
     s.charge.resize(N); s.sigma.resize(N); s.eps.resize(N); s.mass.resize(N); s.pos.resize(3 * N); s.vel.resize(3 * N);
     rd(f, s.charge.data(), N); rd(f, s.sigma.data(), N); rd(f, s.eps.data(), N); rd(f, s.mass.data(), N); rd(f, s.pos.data(), 3 * N); rd(f, s.vel.data(), 3 * N);
@@ -66,6 +67,7 @@ static System* buildSystem(const SystemFile& s, bool cmRemover) {
     nb->setCutoffDistance(s.cutoff);
     nb->setPMEParameters(s.alpha, s.grid[0], s.grid[1], s.grid[2]);   // identical grid on every platform (SURVEY 8c gotcha 1)
     if (s.method == 5) nb->setLJPMEParameters(s.ljAlpha, s.ljGrid[0], s.ljGrid[1], s.ljGrid[2]);
+    if (s.switchDistance >= 0) { nb->setUseSwitchingFunction(true); nb->setSwitchingDistance(s.switchDistance); }
     nb->setUseDispersionCorrection(s.dispersion != 0);
     nb->setReciprocalSpaceForceGroup(1);                              // tests/TestNonbondedForce.h:969-1011 testDirectAndReciprocal
     for (int i = 0; i < s.N; i++) nb->addParticle(s.charge[i], s.sigma[i], s.eps[i]);

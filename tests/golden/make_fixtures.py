@@ -13,6 +13,7 @@ exactly how they were made.
                        as NonbondedForceImpl::calcPMEParameters(lj=true).  N = 1538, 6002.
   water125_dpme.npy    float64 [375,3] Angstrom: the 125-water coordinates of tests/TestDispersionPME.h:406-783 (make_waterbox),
                        used by the LJPME known-answer tests testWater125DpmeVsLongCutoff{No,With}Exclusions
+  ref_switch_1536.npz  water_box(1536), PME, Lennard-Jones switching function from 0.75 nm to the 0.9 nm cutoff (Reference platform)
   ref_ions_triclinic.npz  the 8-ion triclinic case of tests/TestEwald.h:220-269 evaluated by the Reference platform
 """
 import os
@@ -87,6 +88,17 @@ def water_ljpme(n):
     print("ljpme", n, "E", r["e_direct"], r["e_recip"])
 
 
+def water_switch(n=1536, sw=0.75):
+    import openmm_b200 as b
+    from openmm_b200 import workloads
+    sysd = workloads.water_box(n, seed=n)
+    alpha, grid = b.pme_parameters(0.9, sysd["box"])
+    r = ref_eval(sysd, 0.9, alpha, grid, pairs=False, switch_distance=sw)
+    np.savez_compressed(os.path.join(HERE, f"ref_switch_{n}.npz"), positions=sysd["positions"].astype(np.float32), box=sysd["box"], alpha=alpha,
+                        grid=np.array(grid), cutoff=0.9, switch_distance=sw, e_direct=r["e_direct"], e_recip=r["e_recip"], f_direct=r["f_direct"], f_recip=r["f_recip"])
+    print("switch", n, "E", r["e_direct"], r["e_recip"])
+
+
 def water125():
     lines = open(os.path.join(REF, "tests/TestDispersionPME.h")).read().split("\n")
     start = next(i for i, l in enumerate(lines) if "const double coords[375][3]" in l)
@@ -114,6 +126,8 @@ def ions():
 
 if __name__ == "__main__":
     only = sys.argv[1:]
+    if not only or "switch" in only:
+        water_switch()
     if not only or "water125" in only:
         water125()
     if not only or "base" in only:

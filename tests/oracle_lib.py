@@ -21,7 +21,8 @@ class OracleSystem(ctypes.Structure):
                 ("box", ctypes.c_double * 9), ("cutoff", ctypes.c_double), ("alpha", ctypes.c_double), ("grid", ctypes.c_int * 3),
                 ("nexcl", ctypes.c_int), ("excl", c_int_p), ("nexc", ctypes.c_int), ("exc", c_int_p),
                 ("exc_qq", c_double_p), ("exc_sigma", c_double_p), ("exc_eps", c_double_p), ("exceptions_periodic", ctypes.c_int),
-                ("ljpme", ctypes.c_int), ("lj_alpha", ctypes.c_double), ("lj_grid", ctypes.c_int * 3)]
+                ("ljpme", ctypes.c_int), ("lj_alpha", ctypes.c_double), ("lj_grid", ctypes.c_int * 3),
+                ("use_switch", ctypes.c_int), ("switch_distance", ctypes.c_double)]
 
 
 _lib = None
@@ -39,7 +40,7 @@ def lib():
 
 
 class Oracle:
-    def __init__(self, sysd, cutoff, alpha, grid, lj_alpha=None, lj_grid=None):
+    def __init__(self, sysd, cutoff, alpha, grid, lj_alpha=None, lj_grid=None, switch_distance=None):
         self.keep = []
         s = OracleSystem()
 
@@ -68,6 +69,8 @@ class Oracle:
             s.ljpme, s.lj_alpha = 1, lj_alpha
             for k in range(3):
                 s.lj_grid[k] = int(lj_grid[k])
+        if switch_distance is not None:
+            s.use_switch, s.switch_distance = 1, switch_distance
         self.s = s
 
     def nonbonded(self, groups=3):
