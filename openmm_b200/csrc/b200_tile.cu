@@ -232,7 +232,7 @@ _Pragma(TILE_STR(unroll TILE_UNROLL))
 
 
 // Borderline fix-up for the packed path: only a flag is kept in the loop, so re-scan the lane's 32 pairs (rare).
-template <bool FORCES, bool ENERGY, bool EXCL>
+template <bool FORCES, bool ENERGY, bool EXCL, bool LJPME>
 __device__ __forceinline__ void fixBorderlinePacked(const TileArgs& a, const WarpSmem& sm, int lane, unsigned exclRot, int slotI, bool validI,
                                                     float xi, float yi, float zi, float qik, float2 pri, float2& gix, float2& giy, float2& giz, float& eTile) {
     if (!validI) return;
@@ -248,7 +248,7 @@ __device__ __forceinline__ void fixBorderlinePacked(const TileArgs& a, const War
         const bool inF = r2 < a.rc2, inD = borderlineInside(a, slotI, sj);
         if (inF == inD) continue;
         float s, e;
-        pairTerms<ENERGY, false>(a, r2, qik * B.z, pri.x + C.x, pri.y * C.z, s, e);
+        pairTerms<ENERGY, false, LJPME>(a, r2, qik * B.z, pri.x + C.x, pri.y * C.z, s, e, pri.x * C.x);
         const float sg = inD ? 1.f : -1.f;
         if (FORCES) {
             const float gx = sg * dx * s, gy = sg * dy * s, gz = sg * dz * s;
@@ -263,7 +263,7 @@ __device__ __forceinline__ void fixBorderlinePacked(const TileArgs& a, const War
 
 // Dense 32x32 tile, two pairs per lane and step: at step k lane l meets j = (l+k)&31 and j' = j^16, all pair arithmetic in
 // packed FP32x2.  gi* accumulate +d*s for atom i (the caller negates), fj*.x / fj*.y travel with j / j'.
-template <bool FORCES, bool ENERGY, bool EXCL>
+template <bool FORCES, bool ENERGY, bool EXCL, bool LJPME>
 __device__ __forceinline__ void denseTilePacked(const TileArgs& a, const WarpSmem& sm, int lane, int slotI, bool validI, float xi, float yi, float zi, float qik, float2 pri,
                                                 unsigned exclBits, float2& gix, float2& giy, float2& giz, float& fjxOut, float& fjyOut, float& fjzOut, float& eTile) {
     const float4* __restrict__ pxy = &sm.xy[lane];
@@ -297,8 +297,26 @@ _Pragma(TILE_STR(unroll TILE_UNROLL))
         const float2 sig = add2(si2, make_float2(C.x, C.y));
         const float2 sr2 = mul2(mul2(sig, sig), invR2);
         const float2 sr6 = mul2(mul2(sr2, sr2), sr2);
-        const float2 es6 = mul2(mul2(ei2, make_float2(C.z, C.w)), sr6);
+        const float2 eps = mul2(ei2, make_float2(C.z, C.w));
+        const float2 es6 = mul2(eps, sr6);
         float2 s = fma2(mul2(es6, invR2), fma2(dup(12.0f), sr6, dup(-6.0f)), sc);
+        float2 eLj = dup(0.f);   // LJPME: damped multiplicative r^-6 term + potential shift (same arithmetic as pairTerms<.., LJPME>)
+        if (LJPME) {
+            const float2 dar2 = mul2(dup(a.ljAlpha2), r2), dar4 = mul2(dar2, dar2);
+            const float2 ex = make_float2(__expf(-dar2.x), __expf(-dar2.y));
+            const float2 sp = mul2(si2, make_float2(C.x, C.y));
+            const float2 c6 = mul2(mul2(dup(64.0f), mul2(mul2(sp, sp), sp)), eps);
+            const float2 coef = mul2(mul2(c6, invR2), mul2(invR2, invR2));
+            const float2 epre = add2(add2(dup(1.0f), dar2), mul2(dup(0.5f), dar4));
+            const float2 dpre = fma2(mul2(dar4, dar2), dup(1.0f / 6.0f), epre);
+            const float2 nex = make_float2(-ex.x, -ex.y);
+            s = fma2(mul2(mul2(dup(6.0f), coef), invR2), fma2(nex, dpre, dup(1.0f)), s);
+            if (ENERGY) {
+                const float2 sg2 = mul2(sig, sig);
+                const float2 sc6 = mul2(mul2(mul2(sg2, sg2), sg2), dup(a.invCut6));
+                eLj = add2(fma2(coef, fma2(nex, epre, dup(1.0f)), mul2(mul2(eps, add2(dup(1.0f), make_float2(-sc6.x, -sc6.y))), sc6)), mul2(c6, dup(-a.ljShift)));
+            }
+        }
         s.x = in0 ? s.x : 0.f; s.y = in1 ? s.y : 0.f;
         if (ENERGY) {
             float2 vn = fma2(dup(V_N6), t, dup(V_N5)); vn = fma2(vn, t, dup(V_N4)); vn = fma2(vn, t, dup(V_N3)); vn = fma2(vn, t, dup(V_N2));
@@ -307,6 +325,7 @@ _Pragma(TILE_STR(unroll TILE_UNROLL))
             vd = fma2(vd, t, dup(V_D1)); vd = fma2(vd, t, dup(1.0f));
             const float2 ec = mul2(qq, fma2(dup(-a.alpha), make_float2(vn.x / vd.x, vn.y / vd.y), invR));
             float2 e = fma2(es6, add2(sr6, dup(-1.0f)), ec);
+            if (LJPME) e = add2(e, eLj);
             e.x = in0 ? e.x : 0.f; e.y = in1 ? e.y : 0.f;
             e2 = add2(e2, e);
         }
@@ -326,13 +345,13 @@ _Pragma(TILE_STR(unroll TILE_UNROLL))
         fjzOut = fjz.y + __shfl_xor_sync(0xffffffffu, fjz.x, 16);
     }
     if (__any_sync(0xffffffffu, border))
-        fixBorderlinePacked<FORCES, ENERGY, EXCL>(a, sm, lane, exclRot, slotI, validI, xi, yi, zi, qik, pri, gix, giy, giz, eTile);
+        fixBorderlinePacked<FORCES, ENERGY, EXCL, LJPME>(a, sm, lane, exclRot, slotI, validI, xi, yi, zi, qik, pri, gix, giy, giz, eTile);
 }
 
 template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT, bool LJPME>
 __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(const TileArgs a) {
     __shared__ WarpSmem smAll[TILE_WARPS];
-    constexpr bool PACKED = !EMIT && !EXACT && !LJPME;   // FFMA2 path for the single-periodic-copy force/energy variants
+    constexpr bool PACKED = !EMIT && !EXACT;   // FFMA2 path for the single-periodic-copy force/energy variants
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem& sm = smAll[warp];
     const unsigned numExclUnits = (unsigned)(a.exclEnd - a.exclBegin);
@@ -432,8 +451,8 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
                 if (t == nTiles - 1) hintNext();
                 float fjx = 0.f, fjy = 0.f, fjz = 0.f;
                 if (PACKED && single) {
-                    if (excl) denseTilePacked<FORCES, ENERGY, true>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, gix, giy, giz, fjx, fjy, fjz, eTile);
-                    else denseTilePacked<FORCES, ENERGY, false>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, gix, giy, giz, fjx, fjy, fjz, eTile);
+                    if (excl) denseTilePacked<FORCES, ENERGY, true, LJPME>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, gix, giy, giz, fjx, fjy, fjz, eTile);
+                    else denseTilePacked<FORCES, ENERGY, false, LJPME>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, gix, giy, giz, fjx, fjy, fjz, eTile);
                 } else if (excl) {
                     if (single) denseTile<FORCES, ENERGY, EMIT, EXACT, true, true, LJPME>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
                     else denseTile<FORCES, ENERGY, EMIT, EXACT, false, true, LJPME>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
