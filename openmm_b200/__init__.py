@@ -161,9 +161,11 @@ class Context:
 
     # CalcNonbondedForceKernel::initialize
     def add_nonbonded_force(self, charge, sigma, epsilon, cutoff, alpha, grid, exclusions=(), exceptions=None,
-                            method=NB_PME, dispersion_coefficient=0.0, exceptions_use_periodic=False, lj_alpha=None, lj_grid=None):
+                            method=NB_PME, dispersion_coefficient=0.0, exceptions_use_periodic=False, lj_alpha=None, lj_grid=None, switch_distance=None):
         d = NonbondedDesc()
         d.method = method
+        if switch_distance is not None:    # NonbondedForce::setUseSwitchingFunction(true) + setSwitchingDistance
+            d.use_switch, d.switch_distance = 1, switch_distance
         if lj_alpha is not None:      # NonbondedForce::LJPME with setLJPMEParameters(lj_alpha, *lj_grid)
             d.method = NB_LJPME
             d.ljpme_alpha = lj_alpha

@@ -152,7 +152,11 @@ extern "C" int b200_nonbonded_create(b200_ctx* c, const b200_nonbonded_desc* d) 
     if (c->finalized) throw B200Error(B200_ERR_INVALID, "forces must be created before the first computation");
     if (d->method != B200_NB_PME && d->method != B200_NB_LJPME)
         throw B200Error(B200_ERR_UNSUPPORTED, "NonbondedForce: the B200 platform currently implements the PME and LJPME methods only");
-    if (d->use_switch) throw B200Error(B200_ERR_UNSUPPORTED, "NonbondedForce: switching function not implemented yet");
+    if (d->use_switch) {
+        if (d->method == B200_NB_LJPME) throw B200Error(B200_ERR_UNSUPPORTED, "NonbondedForce: the switching function together with LJPME is not implemented");
+        if (!(d->switch_distance >= 0) || !(d->switch_distance < d->cutoff))
+            throw B200Error(B200_ERR_INVALID, "NonbondedForce: Switching distance must satisfy 0 <= r_switch < r_cutoff");   // NonbondedForceImpl.cpp:70-74
+    }
     CUDA_CHECK(cudaSetDevice(c->device));
     c->nb = *d;
     c->nb.charge = c->nb.sigma = c->nb.epsilon = nullptr; c->nb.exclusion_pairs = c->nb.exception_pairs = nullptr;

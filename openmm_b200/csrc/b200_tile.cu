@@ -50,6 +50,7 @@ struct TileArgs {
     float rc2, rcPadded, alpha2, alpha3, alpha, kcoul;
     double rc2d;
     float borderTol;             // |r2-rc2| below this -> FP64 decision
+    float switchDist, switchInvWidth;   // LJMODE 2: switching distance, 1/(cutoff - switching distance)
     float ljAlpha2, invCut6, ljShift;   // LJPME: alpha_d^2, rc^-6, rc^-6 (1 - exp(-x)(1 + x + x^2/2)) at x = (alpha_d rc)^2
     int periodic;
 };
@@ -60,7 +61,7 @@ __device__ __forceinline__ float fast_rcp(float x) { float y; asm("rcp.approx.ft
 // s = -(dE/dr)/r, e = pair energy
 // LJPME (coulombLennardJones.cc:30-62, ReferenceLJCoulombIxn.cpp:352-376): sprod = (sigma_i/2)(sigma_j/2), so that
 // c6_i c6_j = 64 sprod^3 * eps with eps = 2 sqrt(eps_i) 2 sqrt(eps_j)
-template <bool ENERGY, bool EXACT, bool LJPME = false>
+template <bool ENERGY, bool EXACT, int LJMODE = 0>
 __device__ __forceinline__ void pairTerms(const TileArgs& a, float r2, float qq, float sig, float eps, float& s, float& e, float sprod = 0.f) {
     const float invR = fast_rsqrt(r2);
     const float invR2 = invR * invR;
@@ -91,9 +92,25 @@ __device__ __forceinline__ void pairTerms(const TileArgs& a, float r2, float qq,
     const float sr2 = sig * sig * invR2;
     const float sr6 = sr2 * sr2 * sr2;
     const float es6 = eps * sr6;
+    if (LJMODE == 2) {
+        // Lennard-Jones switching function (coulombLennardJones.cc USE_LJ_SWITCH, ReferenceLJCoulombIxn.cpp:385-390,436-439):
+        // S(t) = 1 - 10 t^3 + 15 t^4 - 6 t^5 on t = (r - r_switch)/(r_cut - r_switch); force = S * F_lj - E_lj * S'(r) / r
+        float sLj = es6 * invR2 * fmaf(12.0f, sr6, -6.0f), eLj = es6 * (sr6 - 1.0f);
+        const float r = r2 * invR;
+        if (r > a.switchDist) {
+            const float t = (r - a.switchDist) * a.switchInvWidth;
+            const float sv = fmaf(t * t * t, fmaf(t, fmaf(t, -6.0f, 15.0f), -10.0f), 1.0f);
+            const float sd = t * t * fmaf(t, fmaf(t, -30.0f, 60.0f), -30.0f) * a.switchInvWidth;
+            sLj = fmaf(sv, sLj, -eLj * sd * invR);
+            eLj *= sv;
+        }
+        s = sc + sLj;
+        if (ENERGY) e = ec + eLj;
+        return;
+    }
     s = fmaf(es6 * invR2, fmaf(12.0f, sr6, -6.0f), sc);
     if (ENERGY) e = fmaf(es6, sr6 - 1.0f, ec);
-    if (LJPME) {
+    if (LJMODE == 1) {
         const float dar2 = a.ljAlpha2 * r2, dar4 = dar2 * dar2;
         const float ex = __expf(-dar2);
         const float c6 = 64.0f * sprod * sprod * sprod * eps;
@@ -149,7 +166,7 @@ __device__ __forceinline__ float2 dup(float v) { return make_float2(v, v); }
 
 // Rare: a pair whose r^2 is within rounding distance of the cutoff was decided in float inside the tile loop; re-decide it in
 // FP64 and, if the decision changes, add or remove that single pair (kept out of line so the hot loop stays small).
-template <bool FORCES, bool ENERGY, bool EXACT, bool EXCL, bool LJPME>
+template <bool FORCES, bool ENERGY, bool EXACT, bool EXCL, int LJMODE>
 __device__ __forceinline__ void fixBorderline(const TileArgs& a, const WarpSmem& sm, int lane, unsigned borderMask, unsigned exclRot, int slotI, bool validI,
                                            float xi, float yi, float zi, float qik, float2 pri, float& fix, float& fiy, float& fiz, float& eTile) {
     while (borderMask) {
@@ -166,7 +183,7 @@ __device__ __forceinline__ void fixBorderline(const TileArgs& a, const WarpSmem&
         const bool inF = r2 < a.rc2, inD = borderlineInside(a, slotI, sj);
         if (inF == inD) continue;
         float s, e;
-        pairTerms<ENERGY, EXACT, LJPME>(a, r2, qik * q.w, pri.x + pr.x, pri.y * pr.y, s, e, pri.x * pr.x);
+        pairTerms<ENERGY, EXACT, LJMODE>(a, r2, qik * q.w, pri.x + pr.x, pri.y * pr.y, s, e, pri.x * pr.x);
         const float sg = inD ? 1.f : -1.f;
         if (FORCES) {
             const float gx = sg * dx * s, gy = sg * dy * s, gz = sg * dz * s;
@@ -182,7 +199,7 @@ __device__ __forceinline__ void fixBorderline(const TileArgs& a, const WarpSmem&
 // one dense 32x32 tile: lane owns atom i = lane of block X; at step k it meets j = (lane+k)&31.
 // FIXUP: decide the cutoff in float inside the loop, remember borderline pairs in a bit mask and correct them afterwards
 // (single-copy force/energy variants); otherwise decide exactly inside the loop.
-template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT, bool SINGLE, bool EXCL, bool LJPME>
+template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT, bool SINGLE, bool EXCL, int LJMODE>
 __device__ __forceinline__ void denseTile(const TileArgs& a, const WarpSmem& sm, int lane, int slotI, bool validI, float xi, float yi, float zi, float qik, float2 pri,
                                           unsigned exclBits, float& fix, float& fiy, float& fiz, float& fjx, float& fjy, float& fjz, float& eTile, unsigned long long& nPairs) {
     constexpr bool FIXUP = SINGLE && !EMIT;
@@ -211,7 +228,7 @@ _Pragma(TILE_STR(unroll TILE_UNROLL))
         if (EXCL) in = in && !((exclRot >> k) & 1u);
         if (!SINGLE) in = in && ok;
         float s, e;
-        pairTerms<ENERGY, EXACT, LJPME>(a, r2, qik * q.w, pri.x + pr.x, pri.y * pr.y, s, e, pri.x * pr.x);
+        pairTerms<ENERGY, EXACT, LJMODE>(a, r2, qik * q.w, pri.x + pr.x, pri.y * pr.y, s, e, pri.x * pr.x);
         s = in ? s : 0.f;
         if (FORCES) {
             fix = fmaf(-dx, s, fix); fiy = fmaf(-dy, s, fiy); fiz = fmaf(-dz, s, fiz);
@@ -226,13 +243,13 @@ _Pragma(TILE_STR(unroll TILE_UNROLL))
     }
     if (FIXUP) {
         if (__any_sync(0xffffffffu, borderMask != 0u))
-            fixBorderline<FORCES, ENERGY, EXACT, EXCL, LJPME>(a, sm, lane, borderMask, exclRot, slotI, validI, xi, yi, zi, qik, pri, fix, fiy, fiz, eTile);
+            fixBorderline<FORCES, ENERGY, EXACT, EXCL, LJMODE>(a, sm, lane, borderMask, exclRot, slotI, validI, xi, yi, zi, qik, pri, fix, fiy, fiz, eTile);
     }
 }
 
 
 // Borderline fix-up for the packed path: only a flag is kept in the loop, so re-scan the lane's 32 pairs (rare).
-template <bool FORCES, bool ENERGY, bool EXCL, bool LJPME>
+template <bool FORCES, bool ENERGY, bool EXCL, int LJMODE>
 __device__ __forceinline__ void fixBorderlinePacked(const TileArgs& a, const WarpSmem& sm, int lane, unsigned exclRot, int slotI, bool validI,
                                                     float xi, float yi, float zi, float qik, float2 pri, float2& gix, float2& giy, float2& giz, float& eTile) {
     if (!validI) return;
@@ -248,7 +265,7 @@ __device__ __forceinline__ void fixBorderlinePacked(const TileArgs& a, const War
         const bool inF = r2 < a.rc2, inD = borderlineInside(a, slotI, sj);
         if (inF == inD) continue;
         float s, e;
-        pairTerms<ENERGY, false, LJPME>(a, r2, qik * B.z, pri.x + C.x, pri.y * C.z, s, e, pri.x * C.x);
+        pairTerms<ENERGY, false, LJMODE>(a, r2, qik * B.z, pri.x + C.x, pri.y * C.z, s, e, pri.x * C.x);
         const float sg = inD ? 1.f : -1.f;
         if (FORCES) {
             const float gx = sg * dx * s, gy = sg * dy * s, gz = sg * dz * s;
@@ -263,7 +280,7 @@ __device__ __forceinline__ void fixBorderlinePacked(const TileArgs& a, const War
 
 // Dense 32x32 tile, two pairs per lane and step: at step k lane l meets j = (l+k)&31 and j' = j^16, all pair arithmetic in
 // packed FP32x2.  gi* accumulate +d*s for atom i (the caller negates), fj*.x / fj*.y travel with j / j'.
-template <bool FORCES, bool ENERGY, bool EXCL, bool LJPME>
+template <bool FORCES, bool ENERGY, bool EXCL, int LJMODE>
 __device__ __forceinline__ void denseTilePacked(const TileArgs& a, const WarpSmem& sm, int lane, int slotI, bool validI, float xi, float yi, float zi, float qik, float2 pri,
                                                 unsigned exclBits, float2& gix, float2& giy, float2& giz, float& fjxOut, float& fjyOut, float& fjzOut, float& eTile) {
     const float4* __restrict__ pxy = &sm.xy[lane];
@@ -300,8 +317,8 @@ _Pragma(TILE_STR(unroll TILE_UNROLL))
         const float2 eps = mul2(ei2, make_float2(C.z, C.w));
         const float2 es6 = mul2(eps, sr6);
         float2 s = fma2(mul2(es6, invR2), fma2(dup(12.0f), sr6, dup(-6.0f)), sc);
-        float2 eLj = dup(0.f);   // LJPME: damped multiplicative r^-6 term + potential shift (same arithmetic as pairTerms<.., LJPME>)
-        if (LJPME) {
+        float2 eLj = dup(0.f);   // LJPME: damped multiplicative r^-6 term + potential shift (same arithmetic as pairTerms<.., LJMODE>)
+        if (LJMODE == 1) {
             const float2 dar2 = mul2(dup(a.ljAlpha2), r2), dar4 = mul2(dar2, dar2);
             const float2 ex = make_float2(__expf(-dar2.x), __expf(-dar2.y));
             const float2 sp = mul2(si2, make_float2(C.x, C.y));
@@ -325,7 +342,7 @@ _Pragma(TILE_STR(unroll TILE_UNROLL))
             vd = fma2(vd, t, dup(V_D1)); vd = fma2(vd, t, dup(1.0f));
             const float2 ec = mul2(qq, fma2(dup(-a.alpha), make_float2(vn.x / vd.x, vn.y / vd.y), invR));
             float2 e = fma2(es6, add2(sr6, dup(-1.0f)), ec);
-            if (LJPME) e = add2(e, eLj);
+            if (LJMODE == 1) e = add2(e, eLj);
             e.x = in0 ? e.x : 0.f; e.y = in1 ? e.y : 0.f;
             e2 = add2(e2, e);
         }
@@ -345,13 +362,13 @@ _Pragma(TILE_STR(unroll TILE_UNROLL))
         fjzOut = fjz.y + __shfl_xor_sync(0xffffffffu, fjz.x, 16);
     }
     if (__any_sync(0xffffffffu, border))
-        fixBorderlinePacked<FORCES, ENERGY, EXCL, LJPME>(a, sm, lane, exclRot, slotI, validI, xi, yi, zi, qik, pri, gix, giy, giz, eTile);
+        fixBorderlinePacked<FORCES, ENERGY, EXCL, LJMODE>(a, sm, lane, exclRot, slotI, validI, xi, yi, zi, qik, pri, gix, giy, giz, eTile);
 }
 
-template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT, bool LJPME>
+template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT, int LJMODE>
 __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(const TileArgs a) {
     __shared__ WarpSmem smAll[TILE_WARPS];
-    constexpr bool PACKED = !EMIT && !EXACT;   // FFMA2 path for the single-periodic-copy force/energy variants
+    constexpr bool PACKED = !EMIT && !EXACT && LJMODE != 2;   // (the switching-function variant uses the scalar loop)   // FFMA2 path for the single-periodic-copy force/energy variants
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem& sm = smAll[warp];
     const unsigned numExclUnits = (unsigned)(a.exclEnd - a.exclBegin);
@@ -451,14 +468,14 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
                 if (t == nTiles - 1) hintNext();
                 float fjx = 0.f, fjy = 0.f, fjz = 0.f;
                 if (PACKED && single) {
-                    if (excl) denseTilePacked<FORCES, ENERGY, true, LJPME>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, gix, giy, giz, fjx, fjy, fjz, eTile);
-                    else denseTilePacked<FORCES, ENERGY, false, LJPME>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, gix, giy, giz, fjx, fjy, fjz, eTile);
+                    if (excl) denseTilePacked<FORCES, ENERGY, true, LJMODE>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, gix, giy, giz, fjx, fjy, fjz, eTile);
+                    else denseTilePacked<FORCES, ENERGY, false, LJMODE>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, gix, giy, giz, fjx, fjy, fjz, eTile);
                 } else if (excl) {
-                    if (single) denseTile<FORCES, ENERGY, EMIT, EXACT, true, true, LJPME>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
-                    else denseTile<FORCES, ENERGY, EMIT, EXACT, false, true, LJPME>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
+                    if (single) denseTile<FORCES, ENERGY, EMIT, EXACT, true, true, LJMODE>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
+                    else denseTile<FORCES, ENERGY, EMIT, EXACT, false, true, LJMODE>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, exclBits, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
                 } else {
-                    if (single) denseTile<FORCES, ENERGY, EMIT, EXACT, true, false, LJPME>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
-                    else denseTile<FORCES, ENERGY, EMIT, EXACT, false, false, LJPME>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
+                    if (single) denseTile<FORCES, ENERGY, EMIT, EXACT, true, false, LJMODE>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
+                    else denseTile<FORCES, ENERGY, EMIT, EXACT, false, false, LJMODE>(a, sm, lane, slotI, validI, xi, yi, zi, qik, pri, 0u, fix, fiy, fiz, fjx, fjy, fjz, eTile, nPairs);
                 }
                 if (FORCES && jaCur >= 0 && jaCur < a.N) {
                     // after 32 rotations the accumulator for j = lane is back in this lane
@@ -506,7 +523,7 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
                     bool in = dcut < 0.f;
                     if (fabsf(dcut) < a.borderTol) in = borderlineInside(a, x * 32 + i, ja);
                     float s, e;
-                    pairTerms<ENERGY, EXACT, LJPME>(a, r2, p.w * pj.w, pr.x + prj.x, pr.y * prj.y, s, e, pr.x * prj.x);
+                    pairTerms<ENERGY, EXACT, LJMODE>(a, r2, p.w * pj.w, pr.x + prj.x, pr.y * prj.y, s, e, pr.x * prj.x);
                     s = in ? s : 0.f;
                     if (FORCES && in) {
                         const float gx = dx * s, gy = dy * s, gz = dz * s;
@@ -539,13 +556,13 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
 
 __global__ void resetWorkQueue(DevCounters* c) { c->workNext = 0; }
 
-template <bool EXACT, bool LJPME>
+template <bool EXACT, int LJMODE>
 static void launchTile(b200_ctx* c, const TileArgs& a, bool forces, bool energy, bool emitPairs) {
     const int grid = c->smCount * TILE_MIN_BLOCKS;
-    if (emitPairs) tileKernel<false, false, true, EXACT, false><<<grid, TILE_THREADS, 0, c->stream>>>(a);
-    else if (forces && energy) tileKernel<true, true, false, EXACT, LJPME><<<grid, TILE_THREADS, 0, c->stream>>>(a);
-    else if (forces) tileKernel<true, false, false, EXACT, LJPME><<<grid, TILE_THREADS, 0, c->stream>>>(a);
-    else tileKernel<false, true, false, EXACT, LJPME><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    if (emitPairs) tileKernel<false, false, true, EXACT, 0><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    else if (forces && energy) tileKernel<true, true, false, EXACT, LJMODE><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    else if (forces) tileKernel<true, false, false, EXACT, LJMODE><<<grid, TILE_THREADS, 0, c->stream>>>(a);
+    else tileKernel<false, true, false, EXACT, LJMODE><<<grid, TILE_THREADS, 0, c->stream>>>(a);
 }
 
 void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
@@ -573,9 +590,12 @@ void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
         a.ljAlpha2 = (float)(c->nb.ljpme_alpha * c->nb.ljpme_alpha); a.invCut6 = (float)ic6;
         a.ljShift = (float)(ic6 * (1.0 - exp(-x) * (1.0 + x + 0.5 * x * x)));
     }
-    if (c->ljpme) { if (c->exactEwald) launchTile<true, true>(c, a, forces, energy, emitPairs); else launchTile<false, true>(c, a, forces, energy, emitPairs); }
-    else if (c->exactEwald) launchTile<true, false>(c, a, forces, energy, emitPairs);
-    else launchTile<false, false>(c, a, forces, energy, emitPairs);
+    a.switchDist = 0.f; a.switchInvWidth = 0.f;
+    if (c->nb.use_switch) { a.switchDist = (float)c->nb.switch_distance; a.switchInvWidth = (float)(1.0 / (rc - c->nb.switch_distance)); }
+    if (c->ljpme) { if (c->exactEwald) launchTile<true, 1>(c, a, forces, energy, emitPairs); else launchTile<false, 1>(c, a, forces, energy, emitPairs); }
+    else if (c->nb.use_switch) { if (c->exactEwald) launchTile<true, 2>(c, a, forces, energy, emitPairs); else launchTile<false, 2>(c, a, forces, energy, emitPairs); }
+    else if (c->exactEwald) launchTile<true, 0>(c, a, forces, energy, emitPairs);
+    else launchTile<false, 0>(c, a, forces, energy, emitPairs);
     LAUNCH_COUNT(c, 2);
     CUDA_CHECK(cudaGetLastError());
 }

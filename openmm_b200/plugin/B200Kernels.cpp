@@ -129,7 +129,8 @@ struct B200CalcNonbondedForceKernel::Params {
 void B200CalcNonbondedForceKernel::gather(const System& system, const NonbondedForce& force, Params& p) const {
     if (force.getNumParticleParameterOffsets() > 0 || force.getNumExceptionParameterOffsets() > 0)
         throw OpenMMException("The B200 platform does not support NonbondedForce parameter offsets yet");
-    if (force.getUseSwitchingFunction()) throw OpenMMException("The B200 platform does not support the NonbondedForce switching function yet");
+    if (force.getUseSwitchingFunction() && force.getNonbondedMethod() == NonbondedForce::LJPME)
+        throw OpenMMException("The B200 platform does not support the NonbondedForce switching function together with LJPME yet");
     if (force.getNonbondedMethod() != NonbondedForce::PME && force.getNonbondedMethod() != NonbondedForce::LJPME)
         throw OpenMMException("The B200 platform implements NonbondedForce with the PME and LJPME methods only");
     const int n = force.getNumParticles();
@@ -152,6 +153,8 @@ void B200CalcNonbondedForceKernel::gather(const System& system, const NonbondedF
         dd.ljpme_grid[0] = b200_find_legal_fft_dimension(max(lx, 6)); dd.ljpme_grid[1] = b200_find_legal_fft_dimension(max(ly, 6)); dd.ljpme_grid[2] = b200_find_legal_fft_dimension(max(lz, 6));
     }
     dd.cutoff = force.getCutoffDistance();
+    dd.use_switch = force.getUseSwitchingFunction() ? 1 : 0;
+    dd.switch_distance = force.getSwitchingDistance();
     int nx, ny, nz;
     NonbondedForceImpl::calcPMEParameters(system, force, dd.ewald_alpha, nx, ny, nz, false);
     dd.grid[0] = b200_find_legal_fft_dimension(max(nx, 6)); dd.grid[1] = b200_find_legal_fft_dimension(max(ny, 6)); dd.grid[2] = b200_find_legal_fft_dimension(max(nz, 6));

@@ -135,7 +135,7 @@ def ljpme_water_box(n_atoms):
     return sysd
 
 
-def make_context(sysd, cutoff=0.9, tol=5e-4, device=0, grid=None, alpha=None, ljpme=False, lj_alpha=None, lj_grid=None, **kw):
+def make_context(sysd, cutoff=0.9, tol=5e-4, device=0, grid=None, alpha=None, ljpme=False, lj_alpha=None, lj_grid=None, switch_distance=None, **kw):
     """Create an openmm_b200.Context for a water_box() system with the reference's default PME settings."""
     import openmm_b200 as b
     a, g = b.pme_parameters(cutoff, sysd["box"], tol)
@@ -145,7 +145,7 @@ def make_context(sysd, cutoff=0.9, tol=5e-4, device=0, grid=None, alpha=None, lj
     if ljpme and lj_alpha is None:
         lj_alpha, lj_grid = b.pme_parameters(cutoff, sysd["box"], tol, lj=True)
     ctx.add_nonbonded_force(sysd["charge"], sysd["sigma"], sysd["epsilon"], cutoff, alpha, grid, exclusions=sysd["exclusions"],
-                            exceptions=sysd.get("exceptions"), lj_alpha=lj_alpha, lj_grid=lj_grid)
+                            exceptions=sysd.get("exceptions"), lj_alpha=lj_alpha, lj_grid=lj_grid, switch_distance=switch_distance)
     ctx.lj_pme = (lj_alpha, lj_grid)
     ctx.pme = (alpha, grid)
     return ctx

@@ -131,6 +131,28 @@ def test_ljpme_oracle_on_fresh_seed_and_determinism():
     ctx.close()
 
 
+def test_switching_function_vs_reference_fixture(golden_dir):
+    # setUseSwitchingFunction(true), switching distance 0.75 nm: direct-space forces/energy against the Reference platform,
+    # the energy-only kernel agrees with forces+energy, and a larger system (single periodic copy path) against the oracle
+    g = np.load(os.path.join(golden_dir, "ref_switch_1536.npz"))
+    sysd = workloads.water_box(1536, seed=1536)
+    ctx = workloads.make_context(sysd, switch_distance=float(g["switch_distance"]))
+    ctx.set_positions(sysd["positions"])
+    e_dir = ctx.compute(b.GROUP_DIRECT); f_dir = ctx.get_forces()
+    assert rel_rms(f_dir, g["f_direct"]) < FORCE_TOL
+    assert abs(e_dir - float(g["e_direct"])) / abs(float(g["e_direct"])) < ENERGY_TOL
+    e_only = ctx.compute(b.GROUP_DIRECT, forces=False)
+    assert abs(e_only - e_dir) / abs(e_dir) < 1e-7
+    ctx.close()
+    sysd = workloads.water_box(6000, seed=11)
+    ctx = workloads.make_context(sysd, switch_distance=0.8)
+    ctx.set_positions(sysd["positions"])
+    e = ctx.compute(); f = ctx.get_forces()
+    fo, eo = Oracle(sysd, 0.9, ctx.pme[0], ctx.pme[1], switch_distance=0.8).nonbonded()
+    assert rel_rms(f, fo) < FORCE_TOL and abs(e - eo) / abs(eo) < ENERGY_TOL
+    ctx.close()
+
+
 def test_oracle_vs_gpu_on_fresh_seed():
     # same seeded inputs through the oracle restatement (not a stored fixture)
     sysd, ctx = make(3000, seed=77)

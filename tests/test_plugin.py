@@ -58,6 +58,20 @@ def test_ljpme_context_on_b200_platform_matches_reference_platform():
 
 
 @pytest.mark.gpu
+def test_switching_function_context_on_b200_platform_matches_reference_platform():
+    # setUseSwitchingFunction + dispersion correction (calcDispersionCorrection integrates the switched tail on the host)
+    sysd = workloads.water_box(3000, seed=5)
+    alpha, grid = b.pme_parameters(0.9, sysd["box"])
+    with tempfile.TemporaryDirectory() as td:
+        sp = os.path.join(td, "s.bin")
+        workloads.write_system_file(sp, sysd, 0.9, alpha, grid, dispersion=True, switch_distance=0.75)
+        r = _driver(["compare", sp, "--platform", "B200", "--plugin", b.PLUGIN_PATH, "--against", "Reference"])
+    print(r)
+    assert r["rel_rms_force_total"] < 1e-5 and r["rel_rms_force_direct"] < 1e-5
+    assert r["rel_energy"] < 1e-5
+
+
+@pytest.mark.gpu
 def test_langevin_middle_steps_through_the_plugin():
     sysd = workloads.water_box(6000, seed=6000)
     alpha, grid = b.pme_parameters(0.9, sysd["box"])
