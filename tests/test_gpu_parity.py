@@ -178,6 +178,34 @@ def test_triclinic_ions_gromacs_and_reference(golden_dir):
     ctx.close()
 
 
+def test_nacl_known_answers(golden_dir):
+    # tests/TestEwald.h:47-94: rock-salt crystal, Madelung energy (tolerance 1e-3 there); every ion is equivalent, so forces vanish
+    idx = np.array([(i, j, k) for i in range(10) for j in range(10) for k in range(10)])
+    q = np.where(idx.sum(1) % 2 == 0, 1.0, -1.0)
+    sysd = dict(n=1000, positions=0.141 + 0.282 * idx, box=np.array([2.82, 0, 0, 0, 2.82, 0, 0, 0, 2.82]), charge=q, sigma=np.ones(1000),
+                epsilon=np.zeros(1000), mass=np.ones(1000), exclusions=np.zeros((0, 2), dtype=np.int32))
+    ctx = workloads.make_context(sysd, cutoff=1.0, alpha=float(np.sqrt(-np.log(2e-5)) / 1.0), grid=[60, 60, 60])
+    ctx.set_positions(sysd["positions"])
+    e = ctx.compute(); f = ctx.get_forces()
+    exact = -(1.7476 * 1.6022e-19 * 1.6022e-19 * 6.02214076e23 * 1000) / (1.112e-10 * 0.282e-9 * 2 * 1000)
+    assert abs(e - exact) / abs(exact) < 1e-3
+    assert np.abs(f).max() < 1e-2 * 138.935 / 0.282 ** 2     # << the nearest-neighbour pair force
+    ctx.close()
+    # tests/TestEwald.h:96-141: 894 amorphous ions, cutoff 1.2 nm, Gromacs energy -3.82047e5; forces against the oracle
+    pos = np.load(os.path.join(golden_dir, "nacl_amorph.npy")).astype(np.float64)
+    n, L = 894, 3.00646
+    sysd = dict(n=n, positions=pos, box=np.array([L, 0, 0, 0, L, 0, 0, 0, L]), charge=np.array([1.0] * (n // 2) + [-1.0] * (n // 2)), sigma=np.ones(n),
+                epsilon=np.zeros(n), mass=np.ones(n), exclusions=np.zeros((0, 2), dtype=np.int32))
+    alpha = float(np.sqrt(-np.log(2e-5)) / 1.2)
+    ctx = workloads.make_context(sysd, cutoff=1.2, alpha=alpha, grid=[96, 96, 96])
+    ctx.set_positions(pos)
+    e = ctx.compute(); f = ctx.get_forces()
+    assert abs(e - (-3.82047e5)) / 3.82047e5 < 2e-5
+    fo, eo = Oracle(sysd, 1.2, alpha, [96, 96, 96]).nonbonded()
+    assert rel_rms(f, fo) < FORCE_TOL and abs(e - eo) / abs(eo) < ENERGY_TOL
+    ctx.close()
+
+
 def test_oracle_vs_gpu_on_fresh_seed():
     # same seeded inputs through the oracle restatement (not a stored fixture)
     sysd, ctx = make(3000, seed=77)
