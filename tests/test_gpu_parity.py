@@ -206,6 +206,36 @@ def test_nacl_known_answers(golden_dir):
     ctx.close()
 
 
+def test_ljpme_gromacs_known_answers(golden_dir):
+    # tests/TestDispersionPME.h:812-965, 1221-1274 (uncharged CHARMM water dimer, tolerances 1e-4 / 5e-4 there) and :1773-2267
+    # (125 waters with exclusions, Gromacs energy, 5e-5), same data as tests/test_oracle.py
+    from test_oracle import _water2_ljpme, _assert_vec
+    alpha = 4.0124063605
+    for excl, e_ref, tol, f_ref in (
+            (False, 1.34804e+03, 1e-4, [[3.15301e-01, -3.91114e-03, -6.68965e+04], [1.67241e+04, -3.79846e-02, 3.34487e+04], [-1.67243e+04, -9.55931e-02, 3.34486e+04],
+                                        [-1.71643e+00, -1.76696e+00, -6.68993e+04], [1.67254e+04, 1.59080e+00, 3.34495e+04], [-1.67239e+04, 3.13897e-01, 3.34491e+04]]),
+            (True, -7.78060e-01, 5e-4, [[3.15301e-01, -3.91114e-03, 9.48373e-01], [-4.74745e-02, -3.79846e-02, -5.69616e-02], [-7.16866e-02, -9.55931e-02, -1.43348e-01],
+                                        [-1.78136e+00, -1.76696e+00, -1.70022e+00], [1.19309e+00, 1.59080e+00, 7.95443e-01], [3.92366e-01, 3.13897e-01, 1.56962e-01]])):
+        sysd = _water2_ljpme(excl)
+        ctx = workloads.make_context(sysd, cutoff=0.7, alpha=alpha, grid=[32] * 3, lj_alpha=alpha, lj_grid=[32] * 3)
+        ctx.set_positions(sysd["positions"])
+        e = ctx.compute(); f = ctx.get_forces()
+        assert abs(e - e_ref) / max(abs(e_ref), 1.0) < tol
+        _assert_vec(np.array(f_ref), f, tol)
+        ctx.close()
+    pos = np.load(os.path.join(golden_dir, "water125_dpme.npy")) * 0.1
+    ow = 3 * np.arange(125)
+    ex = np.stack([np.stack([ow, ow + 1], 1), np.stack([ow, ow + 2], 1), np.stack([ow + 1, ow + 2], 1)], 1).reshape(-1, 2).astype(np.int32)
+    sysd = dict(n=375, positions=pos, box=np.array([2.301, 0, 0, 0, 2.301, 0, 0, 0, 2.301]), charge=np.zeros(375),
+                sigma=2.0 * 2.0 ** (-1.0 / 6.0) * np.array([1.7682, 0.2245, 0.2245] * 125) * 0.1, epsilon=np.array([0.1521, 0.046, 0.046] * 125) * 4.184,
+                mass=np.ones(375), exclusions=ex)
+    ctx = workloads.make_context(sysd, cutoff=1.15, alpha=4.5, grid=[60] * 3, lj_alpha=4.2760443169, lj_grid=[60] * 3)
+    ctx.set_positions(pos)
+    e = ctx.compute()
+    assert abs(e - (-2.17481e+02)) / 2.17481e+02 < 5e-5
+    ctx.close()
+
+
 def test_oracle_vs_gpu_on_fresh_seed():
     # same seeded inputs through the oracle restatement (not a stored fixture)
     sysd, ctx = make(3000, seed=77)
