@@ -1,12 +1,12 @@
-// b200_comm.cu -- multi-GPU: one process per GPU, direct-space rows dealt round-robin to ranks, fixed-point forces
-// summed with an NCCL all-reduce over NVLink.
+// b200_comm.cu -- multi-GPU: one process per GPU, direct-space rows dealt round-robin to ranks.  Inside the stepping loop the
+// fixed-point forces are reduced, the system integrated and the positions exchanged by kernels working on peer memory (see
+// "Peer-memory step" below); force/energy evaluations outside it (getState) sum the forces with an NCCL all-reduce over NVLink.
 //
 // Replaces the reference's single-process multi-GPU path: peer-to-peer cuMemcpyAsync of posq and of each device's
 // force buffer into a slot on device 0, followed by the sumForces kernel
 // (platforms/cuda/src/CudaParallelKernels.cpp:183-269, platforms/cuda/src/kernels/parallel.cu:5-13).
-// Because the force sum is an integer sum it is exact and order independent: every rank ends up with bit-identical
-// forces, so each rank integrates its full replica redundantly (same Philox stream) and no position broadcast is
-// needed.  PME and the bonded terms run on rank 0 only (CommonCalcNonbondedForce.cpp:394,437).
+// Because the force sum is an integer sum it is exact and order independent: results are bit-identical to a one-rank run
+// whichever way the sum is taken.  PME and the bonded terms run on rank 0 only (CommonCalcNonbondedForce.cpp:394,437).
 // NCCL is resolved at run time (dlopen) so the library has no hard dependency on a particular libnccl build;
 // inside a torch process this binds to the NCCL that torch already loaded.
 #include "b200_internal.cuh"

@@ -2,10 +2,12 @@
 //
 // Replaces the cuFFT calls of CudaFFT3D::execFFT (platforms/cuda/src/CudaFFT3D.cpp:30-101).  Layout is cuFFT's:
 // real grid [nx][ny][nz] (z fastest), half-complex grid [nx][ny][nz/2+1]; both transforms are unnormalised.
-// Each 1D pass loads a batch of lines into shared memory, runs a Stockham auto-sort mixed-radix FFT (radix 4/2
-// specialised, 3/5/7 through the twiddle table) entirely in shared memory and writes the lines back, so a 3D
-// transform is three passes over the (L2-resident) grid.  The z pass of the forward transform reads the 64-bit
-// fixed-point charge grid directly (folding finishSpreadCharge, pme.cc:125-133, into the FFT).
+// This file holds the host drivers and the GENERIC passes: each 1D pass loads a batch of lines into shared memory, runs a
+// Stockham auto-sort mixed-radix FFT (radix 4/2 specialised, 3/5/7 through the twiddle table) entirely in shared memory and
+// writes the lines back, so a 3D transform is three passes over the (L2-resident) grid.  The drivers use the register-resident
+// two-stage passes of b200_fft2.cu whenever every dimension has a two-stage plan (b200_fft2_supported) and these generic
+// passes otherwise.  The z pass of the forward transform reads the 32-bit fixed-point charge grid directly (folding
+// finishSpreadCharge, pme.cc:125-133, into the FFT).
 #include "b200_internal.cuh"
 #include <cmath>
 #include <map>
