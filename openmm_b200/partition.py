@@ -3,7 +3,8 @@
   rows (32-atom blocks X of the tile list)  : weighted round-robin, rank = owner_table[X & 63]             (b200_nblist.cu nbBuild)
   exclusion tiles (static list, sorted)     : contiguous index ranges proportional to the same shares      (b200_tile.cu)
   PME, exclusion corrections, bonded terms  : rank 0
-  forces                                    : int64 fixed point (x 2^32), summed with one all-reduce       (b200_comm.cu)
+  forces                                    : int64 fixed point (x 2^32); stepping: reduce-scatter over peer memory, sharded
+                                              integration, position all-gather; getState: one all-reduce  (b200_comm.cu)
 
 The reference partitions contiguous tile ranges and rebalances them dynamically (CudaNonbondedUtilities::setAtomBlockRange,
 CudaNonbondedUtilities.cpp:485-493; CudaParallelKernels.cpp:162-166,247-266); round-robin rows need no balancer because every
@@ -49,6 +50,26 @@ def exclusion_tile_range(num_tiles, rank, nranks, **kw):
     begin = sum(share[:rank])
     end = 1.0 if rank == nranks - 1 else begin + share[rank]
     return int(round(num_tiles * begin)), int(round(num_tiles * end))
+
+
+def unit_shard(num_units, rank, nranks, block=128):
+    """slice [begin, end) of the integration units (SETTLE clusters, then free atoms) that rank integrates in the peer-memory step:
+    cut at multiples of the 128-unit thread block so that block-level partial sums group the same units on any rank count
+    (b200_comm.cu b200_peer_plan_shard)"""
+    nblk = (num_units + block - 1) // block
+    begin = min(num_units, block * ((nblk * rank) // nranks))
+    end = min(num_units, block * ((nblk * (rank + 1)) // nranks))
+    return begin, end
+
+
+def excluded_pair_slice(num_pairs, rank, nranks, block=128, **kw):
+    """slice of the excluded-pair corrections a rank evaluates: same shares as the rows, aligned to the 128-pair blocks
+    (b200_bonded.cu b200_bonded_launch)"""
+    share = shares(nranks, **kw)
+    begin = sum(share[:rank])
+    end = 1.0 if rank == nranks - 1 else begin + share[rank]
+    nblk = (num_pairs + block - 1) // block
+    return block * int(round(nblk * begin)), min(num_pairs, block * int(round(nblk * end)))
 
 
 def to_fixed(f):

@@ -72,3 +72,46 @@ def test_two_rank_partition_and_integer_reduction(tmp_path):
     assert bool(r["cover"]), "every block row must belong to exactly one rank"
     assert int(r["span"]) == 101, "exclusion tiles must be split without gaps or overlap"
     assert bool(r["same"]), "int64 all-reduce over ranks must equal the single-rank fixed-point sum bit for bit"
+
+
+def _shard_worker(rank, world, port, result_file):
+    """CPU emulation of the peer-memory step: partial int64 forces per rank -> reduce-scatter by integration-unit slice ->
+    slice-local position update -> all-gather; must equal the one-rank update bit for bit."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rng = np.random.default_rng(5)
+    nmol, extra = 1000, 2                        # 3-site molecules (one unit each) followed by free atoms (one unit each)
+    n, units = 3 * nmol + extra, nmol + extra
+    pos = rng.random((n, 3))
+    partial = [rng.integers(-2 ** 40, 2 ** 40, size=(n, 3), dtype=np.int64) for _ in range(world)]   # every rank's contribution
+    total = sum(partial)
+    begin, end = partition.unit_shard(units, rank, world)
+    atoms = np.concatenate([np.arange(3 * min(begin, nmol), 3 * min(end, nmol)), 3 * nmol + np.arange(max(begin, nmol) - nmol, max(end, nmol) - nmol)]).astype(np.int64)
+    gathered = [torch.zeros((n, 3), dtype=torch.int64) for _ in range(world)]
+    dist.all_gather(gathered, torch.from_numpy(partial[rank]))      # stands for the NVLink loads out of the peers' force arrays
+    mine = sum(g.numpy()[atoms] for g in gathered)                  # exact integer sum for this rank's atoms only
+    new = pos.copy()
+    new[atoms] += partition.from_fixed(mine) * 1e-6                 # "integration" of the slice
+    pub = [torch.zeros((n, 3), dtype=torch.float64) for _ in range(world)]
+    dist.all_gather(pub, torch.from_numpy(new))
+    owner = np.full(n, -1)
+    for r in range(world):
+        b, e = partition.unit_shard(units, r, world)
+        a = np.concatenate([np.arange(3 * min(b, nmol), 3 * min(e, nmol)), 3 * nmol + np.arange(max(b, nmol) - nmol, max(e, nmol) - nmol)]).astype(np.int64)
+        assert (owner[a] == -1).all()
+        owner[a] = r
+    merged = np.stack([pub[owner[i]].numpy()[i] for i in range(n)])
+    if rank == 0:
+        ref = pos + partition.from_fixed(total) * 1e-6
+        lo, hi = zip(*[partition.excluded_pair_slice(3000, r, world) for r in range(world)])
+        np.savez(result_file, same=np.array_equal(ref, merged), cover=bool((owner >= 0).all()), aligned=all(b % 128 == 0 for b in lo),
+                 contiguous=all(hi[r] == lo[r + 1] for r in range(world - 1)) and lo[0] == 0 and hi[-1] == 3000)
+    dist.destroy_process_group()
+
+
+def test_two_rank_sharded_integration_matches_one_rank(tmp_path):
+    out = str(tmp_path / "s.npz")
+    mp.spawn(_shard_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    r = np.load(out)
+    assert bool(r["cover"]) and bool(r["same"]), "slices must cover every atom once and reproduce the one-rank update exactly"
+    assert bool(r["aligned"]) and bool(r["contiguous"]), "excluded-pair slices must be block aligned and gap free"
