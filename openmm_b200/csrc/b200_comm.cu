@@ -94,26 +94,6 @@ extern "C" int b200_set_partition(b200_ctx* c, int32_t rank, int32_t nranks) {
 // STMV) + R redundant integrations.  The barriers are device-side flag exchanges in peer memory; the host never waits.
 struct IpcBundle { cudaIpcMemHandle_t h[6]; };
 
-__global__ void peerSignalKernel(PeerSet p, int slot, unsigned long long seq) {
-    if ((int)threadIdx.x < p.n) {
-        __threadfence_system();
-        volatile unsigned long long* f = p.flags[threadIdx.x] + slot * B200_MAX_PEERS + p.rank;
-        *f = seq;
-        __threadfence_system();
-    }
-}
-__global__ void peerWaitKernel(unsigned long long* flags, int n, int slot, unsigned long long seq, DevCounters* counters) {
-    if ((int)threadIdx.x < n) {
-        volatile unsigned long long* f = flags + slot * B200_MAX_PEERS + threadIdx.x;
-        unsigned long long t0; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-        while (*f < seq) {
-            unsigned long long t1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-            if (t1 - t0 > 20000000000ull) { counters->overflow = 2; break; }   // 20 s: a rank died; fail loudly instead of hanging the GPU
-        }
-        __threadfence_system();
-    }
-}
-
 // signal and wait in one launch: lane r tells rank r that this rank reached `seq`, then waits for rank r's flag
 __global__ void peerBarrierKernel(PeerSet p, unsigned long long* flags, int slot, unsigned long long seq, DevCounters* counters) {
     if ((int)threadIdx.x < p.n) {
