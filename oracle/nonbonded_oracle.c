@@ -380,7 +380,57 @@ void oracle_reciprocal(const oracle_system* s, double* forces, double* energy) {
     }
 }
 
+/* ReferenceLJCoulombIxn.cpp:70-80 (krf, crf) and :582-639 (calculateOneIxn): plain or reaction-field Coulomb + Lennard-Jones with
+   optional switching function; excluded pairs are skipped, pairs beyond the cutoff too (methods 2, 3) */
+void oracle_direct_cutoff(const oracle_system* s, double* forces, double* energy) {
+    const int n = s->n, cutoff = s->nb_method >= 2, periodic = s->nb_method == 3;
+    const double rc2 = s->cutoff * s->cutoff;
+    const double krf = cutoff ? pow(s->cutoff, -3.0) * (s->rf_dielectric - 1.0) / (2.0 * s->rf_dielectric + 1.0) : 0.0;
+    const double crf = cutoff ? (1.0 / s->cutoff) * (3.0 * s->rf_dielectric) / (2.0 * s->rf_dielectric + 1.0) : 0.0;
+    int* ex = (int*)malloc(sizeof(int) * 2 * (size_t)(s->nexcl > 0 ? s->nexcl : 1));
+    for (int k = 0; k < s->nexcl; k++) {
+        const int a = s->excl[2 * k], b = s->excl[2 * k + 1];
+        ex[2 * k] = a < b ? a : b; ex[2 * k + 1] = a < b ? b : a;
+    }
+    qsort(ex, (size_t)s->nexcl, 2 * sizeof(int), cmp_pair);
+    double esum = 0;
+    for (int i = 0; i < n; i++) for (int j = i + 1; j < n; j++) {
+        double d[3];
+        if (periodic) delta_periodic(&s->pos[3 * i], &s->pos[3 * j], s->box, d);
+        else for (int k = 0; k < 3; k++) d[k] = s->pos[3 * j + k] - s->pos[3 * i + k];
+        const double r2 = d[0] * d[0] + d[1] * d[1] + d[2] * d[2];
+        if (cutoff && r2 > rc2) continue;
+        int key[2] = {i, j};
+        if (s->nexcl > 0 && bsearch(key, ex, (size_t)s->nexcl, 2 * sizeof(int), cmp_pair)) continue;
+        const double r = sqrt(r2), invR = 1.0 / r;
+        double switchValue = 1.0, switchDeriv = 0.0;
+        if (s->use_switch && r > s->switch_distance) {
+            const double w = s->cutoff - s->switch_distance, t = (r - s->switch_distance) / w;
+            switchValue = 1.0 + t * t * t * (-10.0 + t * (15.0 - t * 6.0));
+            switchDeriv = t * t * (-30.0 + t * (60.0 - t * 30.0)) / w;
+        }
+        const double qq = ONE_4PI_EPS0 * s->charge[i] * s->charge[j];
+        const double sig = 0.5 * (s->sigma[i] + s->sigma[j]), eps = 4.0 * sqrt(s->epsilon[i] * s->epsilon[j]);
+        double sig2 = invR * sig; sig2 *= sig2;
+        const double sig6 = sig2 * sig2 * sig2;
+        double dEdR = switchValue * eps * (12.0 * sig6 - 6.0) * sig6;
+        dEdR += cutoff ? qq * (invR - 2.0 * krf * r2) : qq * invR;
+        dEdR *= invR * invR;
+        double e = eps * (sig6 - 1.0) * sig6;
+        if (s->use_switch) { dEdR -= e * switchDeriv * invR; e *= switchValue; }
+        e += cutoff ? qq * (invR + krf * r2 - crf) : qq * invR;
+        esum += e;
+        if (forces) for (int k = 0; k < 3; k++) { forces[3 * i + k] -= dEdR * d[k]; forces[3 * j + k] += dEdR * d[k]; }
+    }
+    free(ex);
+    if (energy) *energy += esum;
+}
+
 void oracle_nonbonded(const oracle_system* s, int groups, double* forces, double* energy) {
+    if (s->nb_method != 0) {
+        if (groups & 1) { oracle_direct_cutoff(s, forces, energy); oracle_exceptions(s, forces, energy); }
+        return;
+    }
     if (groups & 1) {
         oracle_direct(s, forces, energy, 0, 0);
         oracle_exclusion_correction(s, forces, energy);

@@ -24,6 +24,8 @@ typedef struct {
     int lj_grid[3];         /* dispersion mesh */
     int use_switch;         /* 1: Lennard-Jones switching function between switch_distance and cutoff */
     double switch_distance;
+    int nb_method;          /* 0: PME / LJPME (everything above); 1: NoCutoff; 2: CutoffNonPeriodic; 3: CutoffPeriodic (reaction field) */
+    double rf_dielectric;   /* reaction-field dielectric of the cutoff methods (NonbondedForce default 78.3) */
 } oracle_system;
 
 /* direct space, pairs with r <= cutoff that are not excluded; forces [3n] are ADDED to; returns pair count.
@@ -37,6 +39,8 @@ void oracle_exceptions(const oracle_system* s, double* forces, double* energy);
 void oracle_reciprocal(const oracle_system* s, double* forces, double* energy);
 /* Ewald self energy + neutralising plasma */
 double oracle_self_energy(const oracle_system* s);
+/* NoCutoff / CutoffNonPeriodic / CutoffPeriodic direct sum (ReferenceLJCoulombIxn::calculateOneIxn), O(N^2): small systems only */
+void oracle_direct_cutoff(const oracle_system* s, double* forces, double* energy);
 /* everything above; `groups` bit 0 = direct(+exclusion corr+exceptions), bit 1 = reciprocal(+self) */
 void oracle_nonbonded(const oracle_system* s, int groups, double* forces, double* energy);
 /* complex 1D FFT used by the reciprocal sum (exposed for the FFT unit test): data = interleaved re,im */

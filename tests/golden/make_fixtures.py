@@ -14,6 +14,8 @@ exactly how they were made.
   water125_dpme.npy    float64 [375,3] Angstrom: the 125-water coordinates of tests/TestDispersionPME.h:406-783 (make_waterbox),
                        used by the LJPME known-answer tests testWater125DpmeVsLongCutoff{No,With}Exclusions
   ref_switch_1536.npz  water_box(1536), PME, Lennard-Jones switching function from 0.75 nm to the 0.9 nm cutoff (Reference platform)
+  ref_cutoff_methods_768.npz  water_box(768) evaluated by the Reference platform with NoCutoff, CutoffNonPeriodic and CutoffPeriodic
+                       (reaction field, dielectric 78.3): energies and forces per method (oracle groundwork for the next scope rows)
   ref_ions_triclinic.npz  the 8-ion triclinic case of tests/TestEwald.h:220-269 evaluated by the Reference platform
 """
 import os
@@ -99,6 +101,19 @@ def water_switch(n=1536, sw=0.75):
     print("switch", n, "E", r["e_direct"], r["e_recip"])
 
 
+def cutoff_methods(n=768):
+    import openmm_b200 as b
+    from openmm_b200 import workloads
+    sysd = workloads.water_box(n, seed=n)
+    alpha, grid = b.pme_parameters(0.9, sysd["box"])
+    out = dict(positions=sysd["positions"].astype(np.float32), box=sysd["box"], cutoff=0.9)
+    for method, name in ((0, "nocutoff"), (1, "cutoff_nonperiodic"), (2, "cutoff_periodic")):
+        r = ref_eval(sysd, 0.9, alpha, grid, pairs=False, method=method)
+        out["e_" + name] = r["e_direct"] + r["e_recip"]; out["f_" + name] = r["f_direct"] + r["f_recip"]
+        print(name, out["e_" + name])
+    np.savez_compressed(os.path.join(HERE, f"ref_cutoff_methods_{n}.npz"), **out)
+
+
 def water125():
     lines = open(os.path.join(REF, "tests/TestDispersionPME.h")).read().split("\n")
     start = next(i for i, l in enumerate(lines) if "const double coords[375][3]" in l)
@@ -126,6 +141,8 @@ def ions():
 
 if __name__ == "__main__":
     only = sys.argv[1:]
+    if not only or "cutoff" in only:
+        cutoff_methods()
     if not only or "switch" in only:
         water_switch()
     if not only or "water125" in only:

@@ -22,7 +22,8 @@ class OracleSystem(ctypes.Structure):
                 ("nexcl", ctypes.c_int), ("excl", c_int_p), ("nexc", ctypes.c_int), ("exc", c_int_p),
                 ("exc_qq", c_double_p), ("exc_sigma", c_double_p), ("exc_eps", c_double_p), ("exceptions_periodic", ctypes.c_int),
                 ("ljpme", ctypes.c_int), ("lj_alpha", ctypes.c_double), ("lj_grid", ctypes.c_int * 3),
-                ("use_switch", ctypes.c_int), ("switch_distance", ctypes.c_double)]
+                ("use_switch", ctypes.c_int), ("switch_distance", ctypes.c_double),
+                ("nb_method", ctypes.c_int), ("rf_dielectric", ctypes.c_double)]
 
 
 _lib = None
@@ -40,7 +41,7 @@ def lib():
 
 
 class Oracle:
-    def __init__(self, sysd, cutoff, alpha, grid, lj_alpha=None, lj_grid=None, switch_distance=None):
+    def __init__(self, sysd, cutoff, alpha, grid, lj_alpha=None, lj_grid=None, switch_distance=None, method=None, rf_dielectric=78.3):
         self.keep = []
         s = OracleSystem()
 
@@ -71,6 +72,9 @@ class Oracle:
                 s.lj_grid[k] = int(lj_grid[k])
         if switch_distance is not None:
             s.use_switch, s.switch_distance = 1, switch_distance
+        if method is not None:       # NonbondedForce::NonbondedMethod 0 NoCutoff, 1 CutoffNonPeriodic, 2 CutoffPeriodic (3, 4, 5: the Ewald family)
+            s.nb_method = {0: 1, 1: 2, 2: 3}.get(int(method), 0)
+            s.rf_dielectric = rf_dielectric
         self.s = s
 
     def nonbonded(self, groups=3):
