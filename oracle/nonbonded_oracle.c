@@ -370,7 +370,44 @@ static void pme_sum(const oracle_system* s, const double* coef, double alpha, co
     free(grid); free(idx); free(th); free(dth); free(mx_); free(my_); free(mz_);
 }
 
+/* NonbondedForce::Ewald: explicit half-space sum over k vectors, ReferenceLJCoulombIxn.cpp:272-368 (rectangular boxes) */
+static void ewald_sum(const oracle_system* s, double* forces, double* energy) {
+    const int n = s->n, nrx = s->ewald_kmax[0], nry = s->ewald_kmax[1], nrz = s->ewald_kmax[2];
+    const double rb[3] = {2.0 * M_PI / s->box[0], 2.0 * M_PI / s->box[4], 2.0 * M_PI / s->box[8]};
+    const double factor = -1.0 / (4.0 * s->alpha * s->alpha);
+    const double coeff = ONE_4PI_EPS0 * 4.0 * M_PI / (s->box[0] * s->box[4] * s->box[8]);
+    double* cr = (double*)malloc(sizeof(double) * (size_t)n), *ci = (double*)malloc(sizeof(double) * (size_t)n);
+    double esum = 0;
+    int lowry = 0, lowrz = 1;
+    for (int rx = 0; rx < nrx; rx++) {
+        const double kx = rx * rb[0];
+        for (int ry = lowry; ry < nry; ry++) {
+            const double ky = ry * rb[1];
+            for (int rz = lowrz; rz < nrz; rz++) {
+                const double kz = rz * rb[2];
+                double cs = 0, ss = 0;
+                for (int i = 0; i < n; i++) {
+                    const double ph = kx * s->pos[3 * i] + ky * s->pos[3 * i + 1] + kz * s->pos[3 * i + 2];
+                    cr[i] = s->charge[i] * cos(ph); ci[i] = s->charge[i] * sin(ph);
+                    cs += cr[i]; ss += ci[i];
+                }
+                const double k2 = kx * kx + ky * ky + kz * kz, ak = exp(k2 * factor) / k2;
+                if (forces) for (int i = 0; i < n; i++) {
+                    const double f = 2.0 * coeff * ak * (cs * ci[i] - ss * cr[i]);
+                    forces[3 * i] += f * kx; forces[3 * i + 1] += f * ky; forces[3 * i + 2] += f * kz;
+                }
+                esum += coeff * ak * (cs * cs + ss * ss);
+                lowrz = 1 - nrz;
+            }
+            lowry = 1 - nry;
+        }
+    }
+    free(cr); free(ci);
+    if (energy) *energy += esum;
+}
+
 void oracle_reciprocal(const oracle_system* s, double* forces, double* energy) {
+    if (s->ewald_kmax[0] > 0) { ewald_sum(s, forces, energy); return; }
     pme_sum(s, s->charge, s->alpha, s->grid, 0, forces, energy);
     if (s->ljpme) {
         double* c6 = (double*)malloc(sizeof(double) * (size_t)s->n);

@@ -26,6 +26,7 @@ typedef struct {
     double switch_distance;
     int nb_method;          /* 0: PME / LJPME (everything above); 1: NoCutoff; 2: CutoffNonPeriodic; 3: CutoffPeriodic (reaction field) */
     double rf_dielectric;   /* reaction-field dielectric of the cutoff methods (NonbondedForce default 78.3) */
+    int ewald_kmax[3];      /* non-zero: NonbondedForce::Ewald, explicit k-space sum with these limits instead of the mesh */
 } oracle_system;
 
 /* direct space, pairs with r <= cutoff that are not excluded; forces [3n] are ADDED to; returns pair count.

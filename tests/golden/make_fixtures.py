@@ -16,6 +16,7 @@ exactly how they were made.
   ref_switch_1536.npz  water_box(1536), PME, Lennard-Jones switching function from 0.75 nm to the 0.9 nm cutoff (Reference platform)
   ref_cutoff_methods_768.npz  water_box(768) evaluated by the Reference platform with NoCutoff, CutoffNonPeriodic and CutoffPeriodic
                        (reaction field, dielectric 78.3): energies and forces per method (oracle groundwork for the next scope rows)
+  ref_ewald_768.npz    water_box(768) with NonbondedForce::Ewald (explicit k-space sum, kmax from calcEwaldParameters), Reference platform
   ref_ions_triclinic.npz  the 8-ion triclinic case of tests/TestEwald.h:220-269 evaluated by the Reference platform
 """
 import os
@@ -114,6 +115,17 @@ def cutoff_methods(n=768):
     np.savez_compressed(os.path.join(HERE, f"ref_cutoff_methods_{n}.npz"), **out)
 
 
+def ewald(n=768):
+    from openmm_b200 import workloads
+    from oracle_lib import ewald_parameters
+    sysd = workloads.water_box(n, seed=n)
+    alpha, kmax = ewald_parameters(0.9, sysd["box"])
+    r = ref_eval(sysd, 0.9, alpha, [8, 8, 8], pairs=False, method=3)      # NonbondedForce::Ewald, default tolerance 5e-4
+    np.savez_compressed(os.path.join(HERE, f"ref_ewald_{n}.npz"), positions=sysd["positions"].astype(np.float32), box=sysd["box"], alpha=alpha, kmax=np.array(kmax),
+                        cutoff=0.9, e_direct=r["e_direct"], e_recip=r["e_recip"], f_direct=r["f_direct"], f_recip=r["f_recip"])
+    print("ewald", n, alpha, kmax, r["e_direct"], r["e_recip"])
+
+
 def water125():
     lines = open(os.path.join(REF, "tests/TestDispersionPME.h")).read().split("\n")
     start = next(i for i, l in enumerate(lines) if "const double coords[375][3]" in l)
@@ -141,6 +153,8 @@ def ions():
 
 if __name__ == "__main__":
     only = sys.argv[1:]
+    if not only or "ewald" in only:
+        ewald()
     if not only or "cutoff" in only:
         cutoff_methods()
     if not only or "switch" in only:

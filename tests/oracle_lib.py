@@ -23,7 +23,7 @@ class OracleSystem(ctypes.Structure):
                 ("exc_qq", c_double_p), ("exc_sigma", c_double_p), ("exc_eps", c_double_p), ("exceptions_periodic", ctypes.c_int),
                 ("ljpme", ctypes.c_int), ("lj_alpha", ctypes.c_double), ("lj_grid", ctypes.c_int * 3),
                 ("use_switch", ctypes.c_int), ("switch_distance", ctypes.c_double),
-                ("nb_method", ctypes.c_int), ("rf_dielectric", ctypes.c_double)]
+                ("nb_method", ctypes.c_int), ("rf_dielectric", ctypes.c_double), ("ewald_kmax", ctypes.c_int * 3)]
 
 
 _lib = None
@@ -41,7 +41,7 @@ def lib():
 
 
 class Oracle:
-    def __init__(self, sysd, cutoff, alpha, grid, lj_alpha=None, lj_grid=None, switch_distance=None, method=None, rf_dielectric=78.3):
+    def __init__(self, sysd, cutoff, alpha, grid, lj_alpha=None, lj_grid=None, switch_distance=None, method=None, rf_dielectric=78.3, ewald_kmax=None):
         self.keep = []
         s = OracleSystem()
 
@@ -75,6 +75,9 @@ class Oracle:
         if method is not None:       # NonbondedForce::NonbondedMethod 0 NoCutoff, 1 CutoffNonPeriodic, 2 CutoffPeriodic (3, 4, 5: the Ewald family)
             s.nb_method = {0: 1, 1: 2, 2: 3}.get(int(method), 0)
             s.rf_dielectric = rf_dielectric
+        if ewald_kmax is not None:   # NonbondedForce::Ewald: explicit k-space sum
+            for k in range(3):
+                s.ewald_kmax[k] = int(ewald_kmax[k])
         self.s = s
 
     def nonbonded(self, groups=3):
@@ -89,6 +92,28 @@ class Oracle:
         cnt = lib().oracle_direct(ctypes.byref(self.s), None, None, buf.ctypes.data_as(c_int_p), ctypes.c_longlong(cap))
         assert cnt <= cap
         return buf[:cnt]
+
+
+def ewald_parameters(cutoff, box, tol=5e-4):
+    """alpha and kmax as NonbondedForceImpl::calcEwaldParameters (openmmapi/src/NonbondedForceImpl.cpp:159-190,218-230)"""
+    alpha = np.sqrt(-np.log(2.0 * tol)) / cutoff
+
+    def find_zero(width):
+        f = lambda a: tol - 0.05 * np.sqrt(width * alpha) * a * np.exp(-(a * np.pi / (width * alpha)) ** 2)
+        arg = 10
+        v = f(arg)
+        if v > 0.0:
+            while v > 0.0 and arg > 0:
+                arg -= 1
+                v = f(arg)
+            return arg + 1
+        while v < 0.0:
+            arg += 1
+            v = f(arg)
+        return arg
+
+    kmax = [find_zero(w) for w in (box[0], box[4], box[8])]
+    return float(alpha), [k + 1 if k % 2 == 0 else k for k in kmax]
 
 
 def pair_hash(pairs, n):
