@@ -840,7 +840,13 @@ extern "C" int b200_step(b200_ctx* c, int32_t nsteps) {
     c->fusedStepExtras = true;
     // peer-memory step: needs the fused COM/displacement extras (they are what keeps the ranks' flags and momenta in step)
     c->peerStepActive = c->peerMode && c->commRanks > 1 && c->integ.remove_cm_every <= 1 && c->hasNonbonded;
-    if (c->peerStepActive) b200_peer_plan_shard(c);
+    if (c->peerStepActive) {
+        b200_peer_plan_shard(c);
+        // Slices whose atoms are not one contiguous range of slots (units listed out of slot order) would need the per-atom peer
+        // accesses inside the integrator; that variant is compiled but has no multi-GPU test yet, so such systems take the
+        // NCCL all-reduce + replicated integration path (every rank reaches the same decision: the flag is all-reduced).
+        if (!c->shardContiguous) c->peerStepActive = false;
+    }
     // B200_PEER_TRACE=1: event time line of the last step of this call (debug aid for the multi-GPU step)
     static const bool trace = getenv("B200_PEER_TRACE") != nullptr;
     cudaEvent_t ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
