@@ -190,6 +190,23 @@ class Context:
         d.exceptions_use_periodic = 1 if exceptions_use_periodic else 0
         _check(self.lib.b200_nonbonded_create(self.handle, ctypes.byref(d)))
 
+    def update_nonbonded_parameters(self, charge, sigma, epsilon, num_exclusions, exceptions=None, dispersion_coefficient=0.0):
+        """NonbondedForce::updateParametersInContext (CalcNonbondedForceKernel::copyParametersToContext, kernels.h:669): new per-particle
+        parameters and exception parameters; the SET of exclusions/exceptions must be the one the force was created with."""
+        d = NonbondedDesc()
+        d.dispersion_coefficient = dispersion_coefficient
+        q, d.charge = _d(charge)
+        s, d.sigma = _d(sigma)
+        e, d.epsilon = _d(epsilon)
+        d.num_exclusions = int(num_exclusions)
+        if exceptions is not None and len(exceptions[0]) > 0:
+            xp, d.exception_pairs = _i(np.asarray(exceptions[0]).reshape(-1))
+            xq, d.exception_chargeprod = _d(exceptions[1])
+            xs, d.exception_sigma = _d(exceptions[2])
+            xe, d.exception_epsilon = _d(exceptions[3])
+            d.num_exceptions = len(xq)
+        _check(self.lib.b200_nonbonded_update_parameters(self.handle, ctypes.byref(d)))
+
     def add_harmonic_bonds(self, atoms, length, k):
         a, ap = _i(np.asarray(atoms).reshape(-1)); l, lp = _d(length); kk, kp = _d(k)
         _check(self.lib.b200_harmonic_bonds_create(self.handle, len(l), ap, lp, kp, 0))

@@ -257,6 +257,29 @@ extern "C" int b200_nonbonded_update_parameters(b200_ctx* c, const b200_nonbonde
     c->selfEnergy = -B200_ONE_4PI_EPS0 * c->nb.ewald_alpha * sumQ2 / sqrt(M_PI);
     b200_lj_self_energy(c);
     b200_pme_rescale(c);
+    if (c->finalized) {
+        // Molecules of a group are exchanged among the group's slots when atoms are re-sorted, which is only valid while they are
+        // identical.  New parameters may have made some of them different (the reference recomputes its molecule groups:
+        // ComputeContext::invalidateMolecules); a group that is no longer homogeneous is simply taken out of the sort from now on.
+        std::map<int, std::string> excSig;   // molecule -> its exception parameters, in list order
+        for (size_t i = 0; i < c->excQQ.size(); i++) {
+            std::ostringstream p; p << c->excQQ[i] << "," << c->excSig[i] << "," << c->excEps[i] << ";";
+            excSig[c->molBaseOf[c->excPairs[2 * i]]] += p.str();
+        }
+        for (size_t gi = 0; gi < c->groups.size();) {
+            auto& g = c->groups[gi];
+            bool same = true;
+            const int b0 = g.base.empty() ? 0 : g.base[0];
+            for (int m = 1; m < g.numMols && same; m++) {
+                const int bm = g.base[m];
+                for (int k = 0; k < g.atomsPerMol && same; k++)
+                    same = c->charge[bm + k] == c->charge[b0 + k] && c->sigma[bm + k] == c->sigma[b0 + k] && c->epsilon[bm + k] == c->epsilon[b0 + k];
+                if (same) { auto a = excSig.find(b0), b = excSig.find(bm); same = (a == excSig.end() ? std::string() : a->second) == (b == excSig.end() ? std::string() : b->second); }
+            }
+            if (same) gi++;
+            else { dfree(g.dBase); c->groups.erase(c->groups.begin() + gi); }
+        }
+    }
     if (c->finalized && c->numExceptions > 0) {
         std::vector<float4> xq;
         for (size_t i = 0; i < c->excQQ.size(); i++) xq.push_back(make_float4((float)(B200_ONE_4PI_EPS0 * c->excQQ[i]), (float)c->excSig[i], (float)(4.0 * c->excEps[i]), 0.f));
@@ -323,6 +346,8 @@ void b200_finalize(b200_ctx* c) {
         }
     }
     c->numMolecules = (int)molAtoms.size();
+    c->molBaseOf.resize(N);
+    for (int i = 0; i < N; i++) c->molBaseOf[i] = molAtoms[molOf[i]][0];
     // ---- signature of each molecule: everything that must match for two molecules to be exchangeable
     std::vector<std::ostringstream> sig(molAtoms.size());
     for (size_t m = 0; m < molAtoms.size(); m++) {

@@ -146,6 +146,7 @@ struct b200_ctx {
     int numMolecules = 0;
     struct MolGroup { int atomsPerMol; int numMols; int* dBase = nullptr; std::vector<int> base; };
     std::vector<MolGroup> groups;
+    std::vector<int> molBaseOf;     // particle -> first particle of its molecule (creation order), for re-checking group homogeneity
     int* sortKeys = nullptr; int* sortCount = nullptr; int* sortStart = nullptr; int* sortOrder = nullptr; int sortBuckets = 0; int sortBits = 0;
     int maxGroupMols = 0;
     int reorderInterval = 250;

@@ -236,6 +236,44 @@ def test_ljpme_gromacs_known_answers(golden_dir):
     ctx.close()
 
 
+def test_update_parameters_in_context():
+    # updateParametersInContext (tests/TestNonbondedForce.h testChangingParameters): new charges and LJ parameters after a few
+    # steps (the device order has been re-sorted by then), compared with the oracle evaluated on the new parameters
+    sysd, ctx = make(3000, seed=21)
+    ctx.set_velocities(sysd["velocities"])
+    ctx.set_integrator(dt=0.002, seed=3)
+    ctx.step(5)
+    pos = ctx.get_positions()
+    new = dict(sysd)
+    new["charge"] = sysd["charge"] * 0.9
+    new["sigma"] = sysd["sigma"] * 1.05
+    new["epsilon"] = sysd["epsilon"] * 1.2
+    ctx.update_nonbonded_parameters(new["charge"], new["sigma"], new["epsilon"], len(sysd["exclusions"]))
+    e = ctx.compute(); f = ctx.get_forces()
+    new["positions"] = pos
+
+    def check(f, e):
+        # with the enlarged sigma the direct (+1e5) and reciprocal (-1e5) energies nearly cancel, so the energy is judged
+        # against the size of the parts rather than against their small sum
+        o = Oracle(new, 0.9, *ctx.pme)
+        (fd, ed), (fr, er) = o.nonbonded(1), o.nonbonded(2)
+        assert rel_rms(f, fd + fr) < FORCE_TOL and abs(e - (ed + er)) / (abs(ed) + abs(er)) < ENERGY_TOL
+
+    check(f, e)
+    # one molecule made different from all others: its group must drop out of the re-sort (identical molecules only are exchanged),
+    # so after the next re-sort (every 250 steps) every particle still carries its own parameters
+    new["charge"] = new["charge"].copy(); new["charge"][0:3] *= 1.1
+    ctx.update_nonbonded_parameters(new["charge"], new["sigma"], new["epsilon"], len(sysd["exclusions"]))
+    ctx.step(260)
+    new["positions"] = ctx.get_positions()
+    e = ctx.compute(); f = ctx.get_forces()
+    check(f, e)
+    # changing the number of exclusions is refused with the reference's message
+    with pytest.raises(b.B200Error, match="set of non-excluded exceptions has changed"):
+        ctx.update_nonbonded_parameters(new["charge"], new["sigma"], new["epsilon"], len(sysd["exclusions"]) + 1)
+    ctx.close()
+
+
 def test_oracle_vs_gpu_on_fresh_seed():
     # same seeded inputs through the oracle restatement (not a stored fixture)
     sysd, ctx = make(3000, seed=77)
