@@ -89,22 +89,7 @@ class ClockSampler:
 
 def build_system(workload):
     from openmm_b200 import workloads
-    n = workloads.WORKLOADS[workload]
-    cache = os.path.join(tempfile.gettempdir(), f"b200_waterbox_{n}.npz")
-    if os.path.exists(cache):
-        z = np.load(cache)
-        sysd = {k: z[k] for k in z.files}
-        sysd["n"] = int(sysd["n"]); sysd["num_waters"] = int(sysd["num_waters"])
-        sysd["constraints"] = (sysd.pop("con_atoms"), sysd.pop("con_dist"))
-        return sysd
-    sysd = workloads.water_box(n, seed=n)
-    try:
-        np.savez(cache + f".{os.getpid()}.npz", con_atoms=sysd["constraints"][0], con_dist=sysd["constraints"][1],
-                 **{k: v for k, v in sysd.items() if k != "constraints"})
-        os.replace(cache + f".{os.getpid()}.npz", cache)
-    except Exception:
-        pass
-    return sysd
+    return workloads.cached_water_box(workloads.WORKLOADS[workload])
 
 
 def run_reference_cpu(sysd, alpha, grid, steps, warmup, threads=0, e2e=False):

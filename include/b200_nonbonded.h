@@ -157,6 +157,10 @@ int  b200_synchronize(b200_ctx* ctx);
  * (r < cutoff, not excluded).  Mirrors what computeNeighborListVoxelHash yields (ReferenceNeighborList.cpp:208-214).
  * Call with pairs==NULL to get the count only. */
 int  b200_direct_pairs(b200_ctx* ctx, int64_t* count, int32_t* pairs /*[2*capacity]*/, int64_t capacity);
+/* The same set reduced on the device to its size and an order-independent 64-bit hash, sum over pairs of splitmix64(i*N + j)
+ * mod 2^64 with i<j original indices (what tests/TestNonbondedForce.h testLargeSystem needs at a million atoms, where the list
+ * itself is > 1 GB).  oracle/ref_driver.cpp --pair-hash computes the same number from computeNeighborListVoxelHash. */
+int  b200_direct_pairs_hash(b200_ctx* ctx, int64_t* count, uint64_t* hash);
 /* Neighbour-list statistics after the last build: tiles, work units, j-slots, exclusion tiles, rebuild count. */
 typedef struct {
     int64_t num_blocks, num_tiles, num_units, num_exclusion_tiles, rebuilds, steps, reorders;

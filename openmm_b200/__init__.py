@@ -64,7 +64,7 @@ EXPORTED_SYMBOLS = [
     "b200_set_velocities", "b200_get_velocities", "b200_get_forces", "b200_set_box", "b200_get_box", "b200_set_time",
     "b200_get_time", "b200_compute", "b200_compute_host", "b200_integrator_create", "b200_step", "b200_integrate",
     "b200_remove_cm_motion", "b200_apply_constraints",
-    "b200_apply_velocity_constraints", "b200_kinetic_energy", "b200_synchronize", "b200_direct_pairs", "b200_nblist_get_stats",
+    "b200_apply_velocity_constraints", "b200_kinetic_energy", "b200_synchronize", "b200_direct_pairs", "b200_direct_pairs_hash", "b200_nblist_get_stats",
     "b200_fft3d_r2c_host", "b200_fft3d_c2r_host", "b200_fft3d_c2r_noalloc", "b200_find_legal_fft_dimension", "b200_timing_enable", "b200_timing_read",
     "b200_timing_reset", "b200_timed_steps", "b200_launch_count", "b200_nccl_unique_id", "b200_comm_init", "b200_set_partition",
 ]
@@ -271,6 +271,12 @@ class Context:
             return cnt.value, buf[:min(cnt.value, capacity)]
         _check(self.lib.b200_direct_pairs(self.handle, ctypes.byref(cnt), None, 0))
         return cnt.value, None
+
+    def direct_pairs_hash(self):
+        """(count, hash) of the interacting pair set, reduced on the device (same hash as tests/oracle_lib.py pair_hash)"""
+        cnt, h = ctypes.c_int64(0), ctypes.c_uint64(0)
+        _check(self.lib.b200_direct_pairs_hash(self.handle, ctypes.byref(cnt), ctypes.byref(h)))
+        return cnt.value, h.value
 
     def nblist_stats(self):
         s = NblistStats()

@@ -718,7 +718,7 @@ extern "C" int b200_get_time(const b200_ctx* c, double* t, int64_t* steps) { if 
 
 // ---------------------------------------------------------------------------------------------
 // force evaluation
-__global__ void zeroEnergy(DevCounters* c) { for (int i = 0; i < 8; i++) c->energy[i] = 0; c->pairCount = 0; }
+__global__ void zeroEnergy(DevCounters* c) { for (int i = 0; i < 8; i++) c->energy[i] = 0; c->pairCount = 0; c->pairHash = 0; }
 
 static void checkOverflow(b200_ctx* c) {
     // sticky device flag set by the list builder when a capacity was exceeded (the analogue of
@@ -835,6 +835,13 @@ extern "C" int b200_direct_pairs(b200_ctx* c, int64_t* count, int32_t* pairs, in
         CUDA_CHECK(cudaMemcpy(pairs, c->pairOut, sizeof(int2) * (size_t)n, cudaMemcpyDeviceToHost));
     }
     dfree(c->pairOut); c->pairCapacity = 0;
+    API_END
+}
+
+extern "C" int b200_direct_pairs_hash(b200_ctx* c, int64_t* count, uint64_t* hash) {
+    API_BEGIN
+    int rc = b200_direct_pairs(c, count, nullptr, 0); if (rc) return rc;
+    *hash = (uint64_t)c->countersHost->pairHash;
     API_END
 }
 

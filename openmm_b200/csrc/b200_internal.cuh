@@ -45,6 +45,7 @@ struct DevCounters {
     unsigned int maxHalfBits[3];// max block half extent per dim, float bits (positive floats order as uints)
     unsigned int numSparseTiles;// sparse tiles (each occupies two 32-int slots of jAtoms) among numTiles
     unsigned long long pairCount;
+    unsigned long long pairHash;   // order-independent hash of the emitted pair set (parity probe)
     long long    energy[8];     // fixed point 2^32: 0 direct tiles, 1 exclusion corr, 2 exceptions, 3 reciprocal, 4 bonded, 5 kinetic*2
     long long    cm[4][4];      // fixed point 2^20: sum m v (x,y,z); slots 0-2 rotate through the fused stepping loop, slot 3 is the stand-alone pass
 };

@@ -133,16 +133,21 @@ __device__ __forceinline__ bool borderlineInside(const TileArgs& a, int slotI, i
     return dx * dx + dy * dy + dz * dz <= a.rc2d;
 }
 
+// count (.x) and order-independent hash (.y) of the emitted pairs: sum over pairs of splitmix64(lo * N + hi) mod 2^64 on the
+// original particle indices -- the same hash tests/oracle_lib.py and oracle/ref_driver.cpp compute for the reference's pair set
+typedef ulonglong2 PairAcc;
 template <bool EMIT>
-__device__ __forceinline__ void emitPair(const TileArgs& a, int slotI, int slotJ, unsigned long long& nPairs) {
+__device__ __forceinline__ void emitPair(const TileArgs& a, int slotI, int slotJ, PairAcc& acc) {
     if (!EMIT) return;
-    nPairs++;
+    acc.x++;
+    const int oi = a.atomIndex[slotI], oj = a.atomIndex[slotJ];
     if (a.pairOut) {
         const unsigned long long slot = atomicAdd(&a.counters->pairCount, 1ull);
-        if ((long long)slot < a.pairCapacity) {
-            const int oi = a.atomIndex[slotI], oj = a.atomIndex[slotJ];
-            a.pairOut[slot] = make_int2(min(oi, oj), max(oi, oj));
-        }
+        if ((long long)slot < a.pairCapacity) a.pairOut[slot] = make_int2(min(oi, oj), max(oi, oj));
+    } else {
+        unsigned long long z = (unsigned long long)min(oi, oj) * (unsigned long long)a.N + (unsigned long long)max(oi, oj) + 0x9E3779B97F4A7C15ull;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; z ^= z >> 31;
+        acc.y += z;
     }
 }
 
@@ -201,7 +206,7 @@ __device__ __forceinline__ void fixBorderline(const TileArgs& a, const WarpSmem&
 // (single-copy force/energy variants); otherwise decide exactly inside the loop.
 template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT, bool SINGLE, bool EXCL, int LJMODE>
 __device__ __forceinline__ void denseTile(const TileArgs& a, const WarpSmem& sm, int lane, int slotI, bool validI, float xi, float yi, float zi, float qik, float2 pri,
-                                          unsigned exclBits, float& fix, float& fiy, float& fiz, float& fjx, float& fjy, float& fjz, float& eTile, unsigned long long& nPairs) {
+                                          unsigned exclBits, float& fix, float& fiy, float& fiz, float& fjx, float& fjy, float& fjz, float& eTile, PairAcc& nPairs) {
     constexpr bool FIXUP = SINGLE && !EMIT;
     const float4* __restrict__ pp = &sm.pos[lane];
     const float2* __restrict__ pq = &sm.par[lane];
@@ -373,7 +378,7 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
     WarpSmem& sm = smAll[warp];
     const unsigned numExclUnits = (unsigned)(a.exclEnd - a.exclBegin);
     const unsigned total = numExclUnits + a.counters->numUnits;
-    long long eAcc = 0; unsigned long long nPairs = 0;
+    long long eAcc = 0; PairAcc nPairs = make_ulonglong2(0ull, 0ull);
 
     // Work units are taken from a device-side queue.  The descriptor of the NEXT unit is fetched while the current one is
     // computed, and the lines its first loads will touch are pulled towards L1, so a unit starts with one global-latency hop
@@ -549,8 +554,8 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
     }
     if (ENERGY && lane == 0 && eAcc != 0) atomicAddFixed(&a.counters->energy[E_DIRECT], eAcc);
     if (EMIT && !a.pairOut) {
-        for (int o = 16; o > 0; o >>= 1) nPairs += __shfl_xor_sync(0xffffffffu, nPairs, o);
-        if (lane == 0 && nPairs) atomicAdd(&a.counters->pairCount, nPairs);
+        for (int o = 16; o > 0; o >>= 1) { nPairs.x += __shfl_xor_sync(0xffffffffu, nPairs.x, o); nPairs.y += __shfl_xor_sync(0xffffffffu, nPairs.y, o); }
+        if (lane == 0 && nPairs.x) { atomicAdd(&a.counters->pairCount, nPairs.x); atomicAdd(&a.counters->pairHash, nPairs.y); }
     }
 }
 

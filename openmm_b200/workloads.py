@@ -8,6 +8,7 @@ trimmed to the exact count, centres scaled (<~1 %) to 100 atoms/nm^3.  Left-over
 """
 import os
 import struct
+import tempfile
 
 import numpy as np
 
@@ -135,6 +136,49 @@ def ljpme_water_box(n_atoms):
     return sysd
 
 
+SYSCACHE_DIRS = [os.path.join(os.path.dirname(HERE), ".syscache"), os.path.join(tempfile.gettempdir(), "b200_syscache")]
+
+
+def cached_water_box(n_atoms, ljpme=False):
+    """water_box(n, seed=n) through an on-disk cache: building the million-atom box takes minutes of host time (24 croppings with
+    a k-d tree), so the result is kept under <repo>/.syscache (git-ignored; it travels to the GPU box with the snapshot) or the
+    temporary directory.  The cache holds exactly what water_box() returned."""
+    name = f"waterbox_{n_atoms}.npz"
+    sysd = None
+    for d in SYSCACHE_DIRS:
+        path = os.path.join(d, name)
+        if os.path.exists(path):
+            try:
+                z = np.load(path)
+                sysd = {k: z[k] for k in z.files}
+                sysd["n"] = int(sysd["n"]); sysd["num_waters"] = int(sysd["num_waters"])
+                sysd["positions"] = sysd["positions"].astype(np.float64); sysd["velocities"] = sysd["velocities"].astype(np.float64)
+                sysd["constraints"] = (sysd.pop("con_atoms"), sysd.pop("con_dist"))
+                break
+            except Exception:
+                sysd = None
+    if sysd is None:
+        sysd = water_box(n_atoms, seed=n_atoms)
+        for d in SYSCACHE_DIRS:
+            try:
+                os.makedirs(d, exist_ok=True)
+                tmp = os.path.join(d, f".{name}.{os.getpid()}.npz")
+                # positions are float32-representable by construction; velocities are kept in full precision
+                np.savez_compressed(tmp, con_atoms=sysd["constraints"][0], con_dist=sysd["constraints"][1],
+                                    **{k: (v.astype(np.float32) if k == "positions" else v) for k, v in sysd.items() if k != "constraints"})
+                os.replace(tmp, os.path.join(d, name))
+                break
+            except Exception:
+                continue
+    if ljpme:      # same modification as ljpme_water_box()
+        nw = sysd["num_waters"]
+        sysd["sigma"] = sysd["sigma"].copy(); sysd["epsilon"] = sysd["epsilon"].copy()
+        for k in (1, 2):
+            sysd["sigma"][k:3 * nw:3] = 0.0400014
+            sysd["epsilon"][k:3 * nw:3] = 0.192464
+    return sysd
+
+
 def make_context(sysd, cutoff=0.9, tol=5e-4, device=0, grid=None, alpha=None, ljpme=False, lj_alpha=None, lj_grid=None, switch_distance=None, **kw):
     """Create an openmm_b200.Context for a water_box() system with the reference's default PME settings."""
     import openmm_b200 as b
@@ -199,6 +243,10 @@ def read_eval_file(path, n):
         fr = np.frombuffer(f.read(24 * n), dtype="<f8").reshape(n, 3)
         npairs, = struct.unpack("<q", f.read(8))
         pairs = None
+        pair_count = pair_hash = None
         if npairs >= 0:
             pairs = np.frombuffer(f.read(8 * npairs), dtype="<i4").reshape(npairs, 2)
-    return dict(e_direct=e_direct, e_recip=e_recip, f_direct=fd, f_recip=fr, pairs=pairs)
+        elif npairs < -1:       # --pair-hash: count and order-independent hash instead of the list
+            pair_count = -2 - npairs
+            pair_hash, = struct.unpack("<Q", f.read(8))
+    return dict(e_direct=e_direct, e_recip=e_recip, f_direct=fd, f_recip=fr, pairs=pairs, pair_count=pair_count, pair_hash=pair_hash)

@@ -5,7 +5,7 @@
 // reference's Reference/CPU platforms inside one process (tests/test_plugin.py), and how `bench.py --impl reference`
 // times the reference's CPU platform.  It contains no algorithm of its own.
 //
-//   ref_driver eval  <system.bin> <out.bin> [--platform NAME] [--plugin lib.so]... [--pairs]
+//   ref_driver eval  <system.bin> <out.bin> [--platform NAME] [--plugin lib.so]... [--pairs | --pair-hash]
 //   ref_driver compare <system.bin> --platform B200 --plugin libOpenMMB200.so [--against Reference]
 //   ref_driver bench <system.bin> --platform NAME [--plugin lib.so]... --steps K --warmup W [--threads T] [--dt ps] [--e2e]
 //
@@ -101,10 +101,11 @@ static Eval evaluate(const SystemFile& s, Platform& platform, const map<string, 
 }
 
 static int cmdEval(int argc, char** argv) {
-    string sysPath = argv[2], outPath = argv[3], platformName = "Reference"; vector<string> plugins; bool pairs = false;
+    string sysPath = argv[2], outPath = argv[3], platformName = "Reference"; vector<string> plugins; bool pairs = false, pairHash = false;
     for (int i = 4; i < argc; i++) {
         string a = argv[i];
         if (a == "--platform") platformName = argv[++i]; else if (a == "--plugin") plugins.push_back(argv[++i]); else if (a == "--pairs") pairs = true;
+        else if (a == "--pair-hash") pairs = pairHash = true;   // count + order-independent hash only (million-atom systems: the list itself is > 1 GB)
     }
     SystemFile s = readSystem(sysPath);
     Platform& platform = pickPlatform(platformName, plugins);
@@ -122,8 +123,21 @@ static int cmdEval(int argc, char** argv) {
         Vec3 bv[3] = {Vec3(s.box[0], s.box[1], s.box[2]), Vec3(s.box[3], s.box[4], s.box[5]), Vec3(s.box[6], s.box[7], s.box[8])};
         computeNeighborListVoxelHash(nl, s.N, toVec3(s.pos), excl, bv, true, s.cutoff, 0.0, false);
         npairs = (long long)nl.size();
-        out.write((char*)&npairs, 8);
-        for (auto& p : nl) { int a = min((int)p.first, (int)p.second), b = max((int)p.first, (int)p.second); out.write((char*)&a, 4); out.write((char*)&b, 4); }
+        if (pairHash) {
+            // same hash as tests/oracle_lib.py pair_hash: sum over pairs of splitmix64(lo*N + hi) mod 2^64
+            unsigned long long h = 0;
+            for (auto& p : nl) {
+                unsigned long long lo = min(p.first, p.second), hi = max(p.first, p.second);
+                unsigned long long z = lo * (unsigned long long)s.N + hi + 0x9E3779B97F4A7C15ULL;
+                z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL; z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL; z ^= z >> 31;
+                h += z;
+            }
+            long long marker = -2 - npairs;      // < -1: "hash follows instead of the list"; count = -2 - marker
+            out.write((char*)&marker, 8); out.write((char*)&h, 8);
+        } else {
+            out.write((char*)&npairs, 8);
+            for (auto& p : nl) { int a = min((int)p.first, (int)p.second), b = max((int)p.first, (int)p.second); out.write((char*)&a, 4); out.write((char*)&b, 4); }
+        }
     } else out.write((char*)&npairs, 8);
     printf("{\"platform\": \"%s\", \"n\": %d, \"e_direct\": %.10g, \"e_recip\": %.10g, \"pairs\": %lld}\n", platformName.c_str(), s.N, e.eDirect, e.eRecip, npairs);
     return 0;

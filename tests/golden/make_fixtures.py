@@ -18,6 +18,9 @@ exactly how they were made.
                        (reaction field, dielectric 78.3): energies and forces per method (oracle groundwork for the next scope rows)
   ref_ewald_768.npz    water_box(768) with NonbondedForce::Ewald (explicit k-space sum, kmax from calcEwaldParameters), Reference platform
   ref_ions_triclinic.npz  the 8-ion triclinic case of tests/TestEwald.h:220-269 evaluated by the Reference platform
+  ref_large_<N>.npz / ref_large_ljpme_<N>.npz  the BASELINE.json configurations themselves (92 224, 408 609, 1 066 628 atoms; LJPME at
+                       92 224 with a 45^3 dispersion mesh) evaluated once by the Reference platform, in compact form: energies, pair
+                       count + hash, sha256 of the float32 positions, and the direct / reciprocal forces of every 16th atom (float32)
 """
 import os
 import re
@@ -53,14 +56,45 @@ def nacl():
     np.save(os.path.join(HERE, "nacl_amorph.npy"), np.array(pos, dtype=np.float32))
 
 
-def ref_eval(sysd, cutoff, alpha, grid, pairs=True, **kw):
+def ref_eval(sysd, cutoff, alpha, grid, pairs=True, pair_hash_only=False, **kw):
     from openmm_b200 import workloads
     from oracle_lib import REF_DRIVER
     with tempfile.TemporaryDirectory() as td:
         sp, op = os.path.join(td, "s.bin"), os.path.join(td, "o.bin")
         workloads.write_system_file(sp, sysd, cutoff, alpha, grid, **kw)
-        subprocess.check_call([REF_DRIVER, "eval", sp, op, "--platform", "Reference"] + (["--pairs"] if pairs else []))
+        subprocess.check_call([REF_DRIVER, "eval", sp, op, "--platform", "Reference"] + ((["--pair-hash"] if pair_hash_only else ["--pairs"]) if pairs else []))
         return workloads.read_eval_file(op, sysd["n"])
+
+
+LARGE_STRIDE = 16
+
+
+def large(n, ljpme=False):
+    """One Reference-platform evaluation of a BASELINE.json configuration, stored compactly (SURVEY.md 8c gotcha 6)."""
+    import hashlib
+    import time
+    import openmm_b200 as b
+    from openmm_b200 import workloads
+    t0 = time.time()
+    sysd = workloads.ljpme_water_box(n) if ljpme else workloads.water_box(n, seed=n)
+    alpha, grid = b.pme_parameters(0.9, sysd["box"])
+    kw = {}
+    extra = {}
+    if ljpme:
+        lj_alpha, lj_grid = b.pme_parameters(0.9, sysd["box"], lj=True)
+        kw = dict(method=5, lj_alpha=lj_alpha, lj_grid=lj_grid)
+        extra = dict(lj_alpha=lj_alpha, lj_grid=np.array(lj_grid))
+    print(n, "built in", time.time() - t0, "s; grid", grid, extra, flush=True)
+    r = ref_eval(sysd, 0.9, alpha, grid, pairs=True, pair_hash_only=True, **kw)
+    sha = hashlib.sha256(sysd["positions"].astype(np.float32).tobytes()).hexdigest()
+    name = f"ref_large_ljpme_{n}.npz" if ljpme else f"ref_large_{n}.npz"
+    np.savez_compressed(os.path.join(HERE, name), n=n, box=sysd["box"], alpha=alpha, grid=np.array(grid), cutoff=0.9, stride=LARGE_STRIDE,
+                        positions_sha256=sha, e_direct=r["e_direct"], e_recip=r["e_recip"],
+                        f_direct=r["f_direct"][::LARGE_STRIDE].astype(np.float32), f_recip=r["f_recip"][::LARGE_STRIDE].astype(np.float32),
+                        f_direct_norm2=float(np.sum(r["f_direct"] ** 2)), f_recip_norm2=float(np.sum(r["f_recip"] ** 2)),
+                        f_total_norm2=float(np.sum((r["f_direct"] + r["f_recip"]) ** 2)),
+                        pair_count=r["pair_count"], pair_hash=np.uint64(r["pair_hash"]), **extra)
+    print("large", n, "ljpme" if ljpme else "pme", "pairs", r["pair_count"], "E", r["e_direct"], r["e_recip"], "in", time.time() - t0, "s", flush=True)
 
 
 def water(n, f32=False):
@@ -170,3 +204,6 @@ if __name__ == "__main__":
     if not only or "ljpme" in only:
         for n in (1538, 6002):
             water_ljpme(n)
+    for key, n, lj in (("large_apoa1", 92224, False), ("large_apoa1_ljpme", 92224, True), ("large_cellulose", 408609, False), ("large_stmv", 1066628, False)):
+        if key in only or "large" in only:      # minutes each (the STMV evaluation alone is several minutes): never part of the default run
+            large(n, lj)

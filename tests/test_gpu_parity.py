@@ -22,7 +22,10 @@ def make(n, seed=None, **kw):
     return sysd, ctx
 
 
-@pytest.mark.parametrize("shape", [(28, 25, 30), (25, 25, 28), (21, 25, 27), (56, 56, 56), (90, 98, 70), (144, 36, 48)])
+# the last four are the meshes of the BASELINE.json configurations: STMV 196^3 (14 x 14 two-stage plan), Cellulose 144^3, ApoA1 90^3 and
+# its LJPME dispersion mesh 45^3 (odd nz: generic shared-memory passes)
+@pytest.mark.parametrize("shape", [(28, 25, 30), (25, 25, 28), (21, 25, 27), (56, 56, 56), (90, 98, 70), (144, 36, 48),
+                                   (196, 196, 196), (144, 144, 144), (90, 90, 90), (45, 45, 45)])
 def test_fft3d_r2c_c2r(shape):
     # platforms/cuda/tests/TestCudaFFT3D.cpp:56-121 (same sizes, vs pocketfft there; vs the oracle FFT + numpy here)
     rng = np.random.default_rng(1)
@@ -74,6 +77,53 @@ def test_pair_set_bit_exact(golden_dir, n):
         ref = Oracle(sysd, 0.9, *ctx.pme).pairs()
         key = lambda p: np.sort(p[:, 0].astype(np.int64) * n + p[:, 1])
         assert np.array_equal(key(pairs), key(ref))
+    ctx.close()
+
+
+LARGE = [("apoa1", 92224, False), ("apoa1_ljpme", 92224, True), ("cellulose", 408609, False), ("stmv", 1066628, False)]
+
+
+@pytest.mark.parametrize("name,n,ljpme", LARGE, ids=[x[0] for x in LARGE])
+def test_baseline_configs_vs_reference_fixture(golden_dir, name, n, ljpme):
+    """The BASELINE.json configurations themselves (tests/TestNonbondedForce.h:447-537 testLargeSystem at the benchmarked sizes): forces,
+    energies and the pair set against one Reference-platform evaluation stored compactly by tests/golden/make_fixtures.py large()
+    (forces of every 16th atom; count + hash of the pair set)."""
+    import hashlib
+    g = np.load(os.path.join(golden_dir, f"ref_large_ljpme_{n}.npz" if ljpme else f"ref_large_{n}.npz"))
+    sysd = workloads.cached_water_box(n, ljpme=ljpme)
+    assert hashlib.sha256(sysd["positions"].astype(np.float32).tobytes()).hexdigest() == str(g["positions_sha256"])
+    ctx = workloads.make_context(sysd, ljpme=ljpme)
+    assert list(ctx.pme[1]) == [int(x) for x in g["grid"]]
+    if ljpme:
+        assert list(ctx.lj_pme[1]) == [int(x) for x in g["lj_grid"]]
+    ctx.set_positions(sysd["positions"])
+    st = int(g["stride"])
+    e_dir = ctx.compute(b.GROUP_DIRECT); f_dir = ctx.get_forces()[::st]
+    e_rec = ctx.compute(b.GROUP_RECIPROCAL); f_rec = ctx.get_forces()[::st]
+    e_tot = ctx.compute(b.GROUP_ALL); f_tot = ctx.get_forces()[::st]
+    rd, rr = g["f_direct"].astype(np.float64), g["f_recip"].astype(np.float64)
+    # the stored forces are float32 (6e-8 relative): far below the tolerance
+    errs = rel_rms(f_dir, rd), rel_rms(f_rec, rr), rel_rms(f_tot, rd + rr)
+    print(name, "relRMS direct/recip/total", errs)
+    assert errs[0] < FORCE_TOL and errs[2] < FORCE_TOL
+    assert errs[1] < 2e-5      # reciprocal part alone is ~8x smaller than the total force
+    e_ref = float(g["e_direct"]) + float(g["e_recip"])
+    assert abs(e_tot - e_ref) / abs(e_ref) < ENERGY_TOL
+    assert abs(e_dir - float(g["e_direct"])) / abs(float(g["e_direct"])) < ENERGY_TOL
+    assert abs(e_rec - float(g["e_recip"])) / abs(float(g["e_recip"])) < ENERGY_TOL
+    if not ljpme:   # same positions and exclusions as the PME case
+        cnt, h = ctx.direct_pairs_hash()
+        assert (cnt, h) == (int(g["pair_count"]), int(g["pair_hash"]))
+    # a second evaluation is bit-identical (fixed-point sums) at this size too
+    e2 = ctx.compute(b.GROUP_ALL)
+    assert e2 == e_tot and np.array_equal(ctx.get_forces()[::st], f_tot)
+    ctx.close()
+
+
+def test_pair_hash_on_device_matches_list(golden_dir):
+    g = np.load(os.path.join(golden_dir, "ref_water_6000.npz"))
+    sysd, ctx = make(6000)
+    assert ctx.direct_pairs_hash() == (int(g["pair_count"]), int(g["pair_hash"]))
     ctx.close()
 
 
