@@ -177,7 +177,8 @@ int  b200_fft3d_c2r_host(int32_t device, int32_t nx, int32_t ny, int32_t nz, con
 /* Allocation-free variant of the complex-to-real transform.  It has no counterpart in the reference.  For callers that
  * cannot call cudaMalloc when they need the transform (a memory pool owns the device, a latency-critical loop must stay
  * off the allocator, a fixed memory budget): device pointers in and out, the working storage is a static ~8 MiB device
- * array inside the library.  Limits: nx*ny*(nz/2+1) <= 1048576 and each dimension <= 1024, otherwise B200_ERR_INVALID.
+ * array inside the library.  Limits: nx*ny*(nz/2+1) <= 1048576, each dimension <= 1024 and a product of 2, 3, 5, 7 only,
+ * otherwise B200_ERR_INVALID.  The caller's current CUDA device is restored before returning.
  * The first call on a device performs a one-time address look-up and should precede any stream capture; calls share the
  * scratch, so calls that overlap on the GPU race.  d_in is not modified.  `stream` is a cudaStream_t (NULL = default). */
 int  b200_fft3d_c2r_noalloc(int32_t device, int32_t nx, int32_t ny, int32_t nz, const float* d_in, float* d_out, void* stream);

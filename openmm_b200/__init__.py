@@ -273,7 +273,7 @@ class Context:
         return cnt.value, None
 
     def direct_pairs_hash(self):
-        """(count, hash) of the interacting pair set, reduced on the device (same hash as tests/oracle_lib.py pair_hash)"""
+        """(count, hash) of the interacting pair set, reduced on the device (sum of splitmix64(i*N+j) over the pairs, mod 2^64)"""
         cnt, h = ctypes.c_int64(0), ctypes.c_uint64(0)
         _check(self.lib.b200_direct_pairs_hash(self.handle, ctypes.byref(cnt), ctypes.byref(h)))
         return cnt.value, h.value

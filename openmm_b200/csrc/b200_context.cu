@@ -654,7 +654,7 @@ extern "C" int b200_set_positions(b200_ctx* c, const double* xyz) {
     ioSetPositions<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->posq, c->posqCorr, c->cellOffsets);
     LAUNCH_COUNT(c, 1);
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    c->forcesValid = false;
+    c->forcesValid = false; c->dispChecked = false; c->listVerified = false;
     // Like ComputeContext::reorderAtoms the spatial sort is periodic, not forced by every setPositions: the displacement
     // check against the last list build decides on the device whether the neighbour list must be rebuilt.
     if (!c->positionsSet) c->stepsSinceReorder = -1;
@@ -677,7 +677,7 @@ extern "C" int b200_set_velocities(b200_ctx* c, const double* xyz) {
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
     stageIn(c, xyz);
-    c->cmValid = false;
+    c->cmValid = false; c->cmDeferred = false;    // a pending COM removal concerned the velocities that are being replaced
     ioSetVelocities<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->velm);
     LAUNCH_COUNT(c, 1);
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
@@ -688,6 +688,7 @@ extern "C" int b200_get_velocities(b200_ctx* c, double* xyz) {
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
     b200_peer_sync_state(c);
+    b200_flush_cm(c);
     ensureStaging(c);
     ioGetVelocities<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->velm);
     LAUNCH_COUNT(c, 1);
@@ -708,12 +709,17 @@ extern "C" int b200_get_forces(b200_ctx* c, double* xyz) {
 extern "C" int b200_set_box(b200_ctx* c, const double* box9) {
     API_BEGIN
     b200_box_set(c, box9);
-    c->forcesValid = false;
+    c->forcesValid = false; c->dispChecked = false; c->listVerified = false;
     if (c->finalized) c->stepsSinceReorder = -1;
     API_END
 }
 extern "C" int b200_get_box(const b200_ctx* c, double* box9) { memcpy(box9, c->boxHost, sizeof(double) * 9); return B200_OK; }
-extern "C" int b200_set_time(b200_ctx* c, double t, int64_t steps) { c->timePs = t; c->stepCount = steps; return B200_OK; }
+extern "C" int b200_set_time(b200_ctx* c, double t, int64_t steps) {
+    API_BEGIN
+    if (steps != c->stepCount) { CUDA_CHECK(cudaSetDevice(c->device)); b200_flush_cm(c); c->cmValid = false; }   // the momentum slot is indexed by the step count
+    c->timePs = t; c->stepCount = steps;
+    API_END
+}
 extern "C" int b200_get_time(const b200_ctx* c, double* t, int64_t* steps) { if (t) *t = c->timePs; if (steps) *steps = c->stepCount; return B200_OK; }
 
 // ---------------------------------------------------------------------------------------------
@@ -727,20 +733,37 @@ static void checkOverflow(b200_ctx* c) {
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
 }
 
+__global__ void nbClearOverflow(DevCounters* c) { c->overflow = 0; c->rebuild = 1; }
+
 static void prepareLists(b200_ctx* c, bool verify) {
-    // runs the (device-decided) rebuild; when `verify` is set it also reads the overflow flag back, grows the list
-    // storage and repeats while it overflowed.  b200_step verifies on its first step and every 64th step, and
-    // checks the sticky flag again before returning, so a (very unlikely) overflow in between is never silent.
+    // Runs the (device-decided) rebuild.  When `verify` is set the host also reads the list counters: an overflow flag that is
+    // ALREADY set belongs to an earlier, unverified evaluation whose forces were incomplete -> error, never cleared silently.
+    // Otherwise the storage follows the measured need: it grows (25 % head room) when the build overflowed and also as soon as
+    // the list fills more than 80 % of it, so that an overflow between two checks would take a 25 % jump within 64 steps.
+    // Unverified evaluations stay memory-safe (the builder writes an empty descriptor for a dropped unit, the tile kernel
+    // clamps the unit count).  (Host-side analogue of CudaNonbondedUtilities::updateNeighborListSize, CudaNonbondedUtilities.cpp:441-479.)
+    if (verify) {
+        checkOverflow(c);
+        if (c->countersHost->overflow) {
+            nbClearOverflow<<<1, 1, 0, c->stream>>>(c->counters);
+            throw B200Error(B200_ERR_OVERFLOW, "the neighbour list overflowed during an earlier, unverified force evaluation; the state computed since the last check is not trustworthy");
+        }
+    }
     for (int attempt = 0; attempt < 8; attempt++) {
         b200_nblist_prepare(c);
+        c->dispChecked = true;     // the positions have been compared with the list's reference positions
         if (!verify) return;
         checkOverflow(c);
-        if (!c->countersHost->overflow) return;
-        c->tileCapacity = c->tileCapacity * 3 / 2 + 1024;
+        const DevCounters& h = *c->countersHost;
+        const bool over = h.overflow != 0;
+        const bool tight = (long long)h.numTiles * 5 > c->tileCapacity * 4 || (long long)h.numUnits * 5 > c->unitCapacity * 4;
+        c->listVerified = true;
+        if (!over && !tight) return;
+        c->tileCapacity = std::max(c->tileCapacity, (long long)h.numTiles * 5 / 4 + 1024);
+        c->unitCapacity = std::max(c->unitCapacity, (long long)h.numUnits * 5 / 4 + 1024);
         b200_nblist_alloc(c);
-        DevCounters z = *c->countersHost; z.overflow = 0; z.rebuild = 1;
-        CUDA_CHECK(cudaMemcpyAsync(c->counters, &z, sizeof(DevCounters), cudaMemcpyHostToDevice, c->stream));
-        CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        nbClearOverflow<<<1, 1, 0, c->stream>>>(c->counters);     // only these two fields: energy sums and momenta are live on other streams
+        LAUNCH_COUNT(c, 1);
     }
     throw B200Error(B200_ERR_OVERFLOW, "neighbour list kept overflowing");
 }
@@ -751,6 +774,7 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     b200_finalize(c);
     if (c->stepsSinceReorder < 0 || c->stepsSinceReorder >= c->reorderInterval) { b200_peer_sync_state(c); b200_reorder(c); }   // the sort moves whole-state rows
     cudaStream_t s = c->stream;
+    c->computeCount++;
     if (forces) CUDA_CHECK(cudaMemsetAsync(c->force, 0, sizeof(long long) * 3 * (size_t)c->Npad, s));
     if (energy) { zeroEnergy<<<1, 1, 0, s>>>(c->counters); LAUNCH_COUNT(c, 1); }
     const bool doRecip = c->hasNonbonded && (groups & B200_GROUP_RECIPROCAL) && c->partRank == 0;
@@ -801,7 +825,12 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     }
 }
 
-void b200_compute_impl(b200_ctx* c, unsigned groups, bool forces, bool energy, double* energyOut) { computeImpl(c, groups, forces, energy, energyOut, true); }
+// The host reads the list counters (one small copy + stream sync) when new positions came from outside, on every 64th
+// evaluation and whenever an energy is returned anyway; in between, evaluations are queued without any host synchronisation.
+void b200_compute_impl(b200_ctx* c, unsigned groups, bool forces, bool energy, double* energyOut) {
+    const bool verify = !c->listVerified || energy || (c->computeCount & 63) == 0;
+    computeImpl(c, groups, forces, energy, energyOut, verify);
+}
 
 extern "C" int b200_compute(b200_ctx* c, uint32_t groups, int32_t includeForces, int32_t includeEnergy, double* energy) {
     API_BEGIN
@@ -869,8 +898,7 @@ extern "C" int b200_step(b200_ctx* c, int32_t nsteps) {
     CUDA_CHECK(cudaSetDevice(c->device));
     b200_finalize(c);
     if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
-    c->fusedStepExtras = true;
-    // peer-memory step: needs the fused COM/displacement extras (they are what keeps the ranks' flags and momenta in step)
+    // peer-memory step: the momentum bookkeeping inside the integration kernel is what keeps the ranks' momenta in step
     c->peerStepActive = c->peerMode && c->commRanks > 1 && c->integ.remove_cm_every <= 1 && c->hasNonbonded;
     if (c->peerStepActive) {
         b200_peer_plan_shard(c);
@@ -885,9 +913,9 @@ extern "C" int b200_step(b200_ctx* c, int32_t nsteps) {
     for (int i = 0; i < nsteps; i++) {
         const bool tr = trace && i == nsteps - 1 && nsteps > 1;
         auto mark = [&](int k) { if (tr) { cudaEventCreate(&ev[k]); cudaEventRecord(ev[k], c->stream); } };
-        c->skipDispCheck = i > 0;     // from the second step on, the integrator kernel of the previous step did the check
         mark(0);
-        computeImpl(c, B200_GROUP_ALL, true, false, nullptr, i == 0 || (c->stepCount & 63) == 0);
+        if (c->integ.remove_cm_every > 0 && c->stepCount % c->integ.remove_cm_every == 0) b200_request_cm_removal(c);
+        computeImpl(c, B200_GROUP_ALL, true, false, nullptr, !c->listVerified || (c->stepCount & 63) == 0);
         mark(1);
         if (c->peerStepActive) {
             b200_peer_barrier(c, PEER_SLOT_FORCES);                           // every rank's partial forces are complete
@@ -914,7 +942,7 @@ extern "C" int b200_step(b200_ctx* c, int32_t nsteps) {
             for (auto& e : ev) if (e) { cudaEventDestroy(e); e = nullptr; }
         }
     }
-    c->skipDispCheck = false; c->fusedStepExtras = false; c->peerStepActive = false;
+    c->peerStepActive = false;
     checkOverflow(c);
     if (c->countersHost->overflow) throw B200Error(B200_ERR_OVERFLOW, "neighbour list overflowed during b200_step; state is not trustworthy");
     API_END

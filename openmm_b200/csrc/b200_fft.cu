@@ -363,8 +363,12 @@ __global__ void noallocFillTwiddle(float2* tw, int n) {
 // The first call on each device looks up the device address of the scratch array (cudaGetSymbolAddress) and should
 // therefore be made before any stream capture begins.  Every call uses the same array: calls that overlap on the GPU
 // (different streams or threads) race and must be serialised by the caller.  Nothing in the array has to start at zero;
-// each call overwrites the part it reads.  Sizes beyond the limits above are rejected with B200_ERR_INVALID.
+// each call overwrites the part it reads.  Sizes beyond the limits above, and dimensions with a prime factor other than
+// 2, 3, 5, 7, are rejected with B200_ERR_INVALID.  The caller's current CUDA device is left as it was found.
 extern "C" int b200_fft3d_c2r_noalloc(int32_t device, int32_t nx, int32_t ny, int32_t nz, const float* d_in, float* d_out, void* stream) {
+    int previousDevice = -1;
+    cudaGetDevice(&previousDevice);
+    struct RestoreDevice { int d; ~RestoreDevice() { if (d >= 0) cudaSetDevice(d); } } restore{previousDevice};
     try {
         if (device < 0 || device >= NOALLOC_MAX_DEVICES) throw B200Error(B200_ERR_INVALID, "b200_fft3d_c2r_noalloc: device ordinal out of range");
         if (nx < 1 || ny < 1 || nz < 1 || !d_in || !d_out) throw B200Error(B200_ERR_INVALID, "b200_fft3d_c2r_noalloc: bad arguments");
@@ -373,6 +377,8 @@ extern "C" int b200_fft3d_c2r_noalloc(int32_t device, int32_t nx, int32_t ny, in
         const size_t GC = (size_t)nx * ny * (nz / 2 + 1);
         if (GC > (size_t)NOALLOC_MAX_COMPLEX)
             throw B200Error(B200_ERR_INVALID, "b200_fft3d_c2r_noalloc: nx*ny*(nz/2+1) exceeds the built-in scratch of 1048576 complex values; use a context-owned transform instead");
+        for (int n : {nx, ny, nz})
+            if (b200_find_legal_fft_dimension(n) != n) throw B200Error(B200_ERR_INVALID, "b200_fft3d_c2r_noalloc: every grid dimension must factor into 2, 3, 5 and 7");
         CUDA_CHECK(cudaSetDevice(device));
         if (!g_noallocPtr[device]) {
             // once per device, with that device current: the symbol name is only a host-side handle, kernels need this address

@@ -49,7 +49,8 @@ struct IntegArgs {
     // fused extras of the stepping loop: COM-motion removal (removeCM.cc) and the Verlet-buffer displacement check
     // (findInteractingBlocks.cu:176-185) ride along, so a step needs no separate passes over the atoms for them
     const float4* refPosq; float maxDisp2; DevCounters* counters;
-    int fuseCM; int cmCur, cmNext, cmClear; double invTotalMass;
+    int fuseCM;        // 0: no momentum bookkeeping; 1: accumulate the new momentum; 2: also subtract the current COM velocity first
+    int cmCur, cmNext, cmClear; double invTotalMass;
     // peer-memory step (b200_comm.cu): this rank integrates units [unitBegin, unitEnd) only, sums the force contributions of all
     // ranks out of their memories and stores the new positions into every rank's posq
     int usePeers, unitBegin, unitEnd; PeerSet peers;
@@ -150,7 +151,7 @@ __global__ void __launch_bounds__(128, 4) langevinMiddleStep(IntegArgs a, int nu
     const double halfdt = 0.5 * a.dt, invDt = 1.0 / a.dt;
     V3 vcm = {0, 0, 0}, mom = {0, 0, 0};
     if (a.fuseCM) {
-        const double sc = a.invTotalMass / CM_SCALE;
+        const double sc = a.fuseCM == 2 ? a.invTotalMass / CM_SCALE : 0.0;
         vcm = {sc * (double)a.counters->cm[a.cmCur][0], sc * (double)a.counters->cm[a.cmCur][1], sc * (double)a.counters->cm[a.cmCur][2]};
         if (blockIdx.x == 0 && threadIdx.x == 0) { a.counters->cm[a.cmClear][0] = 0; a.counters->cm[a.cmClear][1] = 0; a.counters->cm[a.cmClear][2] = 0; }
     }
@@ -306,12 +307,40 @@ static void removeCM(b200_ctx* c) {
     cmMomentum<<<c->smCount * 2, 256, 0, s>>>(c->velm, c->N, c->counters, 3);
     cmRemove<<<c->smCount * 4, 256, 0, s>>>(c->velm, c->N, 1.0 / total, c->counters, 3);
     LAUNCH_COUNT(c, 3);
-    c->cmValid = false;
+    c->cmValid = false; c->cmDeferred = false;
+}
+
+// The momentum of the current velocities lives in cm[stepCount % 3] (written by the previous integration kernel).  A removal
+// request only raises a flag: the next integration kernel subtracts the COM velocity while it loads the velocities anyway.
+// Forces do not depend on velocities, so this equals removing it before the force evaluation (CMMotionRemover::updateContextState).
+void b200_request_cm_removal(b200_ctx* c) {
+    cudaStream_t s = c->stream;
+    if (!c->cmValid) {   // first step, or the velocities were set from outside
+        cmZero<<<1, 1, 0, s>>>(c->counters, 0); cmZero<<<1, 1, 0, s>>>(c->counters, 1); cmZero<<<1, 1, 0, s>>>(c->counters, 2);
+        cmMomentum<<<c->smCount * 2, 256, 0, s>>>(c->velm, c->N, c->counters, (int)(c->stepCount % 3));
+        LAUNCH_COUNT(c, 4);
+        c->cmValid = true;
+    }
+    c->cmDeferred = true;
+}
+// anything that reads or replaces the velocities applies a pending removal first
+void b200_flush_cm(b200_ctx* c) {
+    if (!c->cmDeferred) return;
+    const int slot = (int)(c->stepCount % 3);
+    cmRemove<<<c->smCount * 4, 256, 0, c->stream>>>(c->velm, c->N, 1.0 / totalMass(c), c->counters, slot);
+    cmZero<<<1, 1, 0, c->stream>>>(c->counters, slot);     // the momentum of the corrected velocities is zero
+    LAUNCH_COUNT(c, 2);
+    c->cmDeferred = false;
 }
 
 // RemoveCMMotionKernel::execute (kernels.h:1793)
 extern "C" int b200_remove_cm_motion(b200_ctx* c) {
-    try { CUDA_CHECK(cudaSetDevice(c->device)); b200_peer_sync_state(c); removeCM(c); CUDA_CHECK(cudaGetLastError()); }
+    try {
+        CUDA_CHECK(cudaSetDevice(c->device));
+        if (c->commRanks > 1) { b200_peer_sync_state(c); removeCM(c); }   // velocities are sharded between steps: remove on the gathered copy
+        else b200_request_cm_removal(c);
+        CUDA_CHECK(cudaGetLastError());
+    }
     catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
     return B200_OK;
 }
@@ -324,10 +353,7 @@ extern "C" int b200_integrate(b200_ctx* c) {
         b200_peer_sync_state(c);
         b200_finalize(c);
         if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
-        const int keep = c->integ.remove_cm_every;
-        c->integ.remove_cm_every = 0;      // the caller (CMMotionRemover's own kernel) decides when to remove COM motion
-        b200_integrate_step(c);
-        c->integ.remove_cm_every = keep;
+        b200_integrate_step(c);            // the caller (CMMotionRemover's own kernel) decides when COM motion is removed
         c->stepCount++; c->timePs += c->integ.dt; c->stepsSinceReorder++;
         c->forcesValid = false;
     } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
@@ -338,19 +364,14 @@ void b200_integrate_step(b200_ctx* c) {
     cudaStream_t s = c->stream;
     ScopedTimer tm(c, B200_T_INTEGRATE, s);
     IntegArgs a = makeArgs(c);
-    const bool fuse = c->integ.remove_cm_every == 1 && c->fusedStepExtras;
-    if (fuse) {
-        if (!c->cmValid) {   // momentum of the current velocities is not known on the device yet (first step, or velocities were set)
-            cmZero<<<1, 1, 0, s>>>(c->counters, 0); cmZero<<<1, 1, 0, s>>>(c->counters, 1); cmZero<<<1, 1, 0, s>>>(c->counters, 2);
-            cmMomentum<<<c->smCount * 2, 256, 0, s>>>(c->velm, c->N, c->counters, (int)(c->stepCount % 3));
-            LAUNCH_COUNT(c, 4);
-            c->cmValid = true;
-        }
-        const double total = totalMass(c);
-        a.fuseCM = 1; a.invTotalMass = 1.0 / total;
+    // momentum bookkeeping rides in the kernel whenever the buffer is in step with the velocities; a pending removal is applied there
+    if (c->cmValid) {
+        a.fuseCM = c->cmDeferred ? 2 : 1; a.invTotalMass = 1.0 / totalMass(c);
         a.cmCur = (int)(c->stepCount % 3); a.cmNext = (int)((c->stepCount + 1) % 3); a.cmClear = (int)((c->stepCount + 2) % 3);
-    } else if (c->integ.remove_cm_every > 0 && c->stepCount % c->integ.remove_cm_every == 0) removeCM(c);
-    if (c->fusedStepExtras && c->hasNonbonded) { a.refPosq = c->refPosq; const float md = 0.5f * (float)c->padding; a.maxDisp2 = md * md; }
+    }
+    c->cmDeferred = false;
+    // so does the Verlet-buffer displacement check of the next force evaluation
+    if (c->hasNonbonded) { a.refPosq = c->refPosq; const float md = 0.5f * (float)c->padding; a.maxDisp2 = md * md; c->dispChecked = true; }
     const int units = c->numSettle + c->numFree;
     if (c->peerStepActive) {
         // a.usePeers = 1: per-atom loads/stores through peer memory; 2: the forces of this slice were already reduced into the local
@@ -375,7 +396,7 @@ extern "C" int b200_apply_constraints(b200_ctx* c, double) {
         if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
         if (c->numSettle > 0) { settleOnly<<<(c->numSettle + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, 0); LAUNCH_COUNT(c, 1); }
         CUDA_CHECK(cudaStreamSynchronize(c->stream));
-        c->stepsSinceReorder = -1;
+        c->stepsSinceReorder = -1; c->dispChecked = false; c->listVerified = false; c->forcesValid = false;
     } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
     return B200_OK;
 }
@@ -384,6 +405,7 @@ extern "C" int b200_apply_velocity_constraints(b200_ctx* c, double) {
         CUDA_CHECK(cudaSetDevice(c->device));
         b200_peer_sync_state(c);
         b200_finalize(c);
+        b200_flush_cm(c);
         if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
         if (c->numSettle > 0) { settleOnly<<<(c->numSettle + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, 1); LAUNCH_COUNT(c, 1); }
         c->cmValid = false;
@@ -395,6 +417,7 @@ extern "C" int b200_kinetic_energy(b200_ctx* c, double* ke) {
     try {
         CUDA_CHECK(cudaSetDevice(c->device));
         b200_peer_sync_state(c);
+        b200_flush_cm(c);
         keZero<<<1, 1, 0, c->stream>>>(c->counters);
         kineticEnergy<<<c->smCount * 2, 256, 0, c->stream>>>(c->velm, c->N, c->counters);
         LAUNCH_COUNT(c, 2);

@@ -204,9 +204,11 @@ struct b200_ctx {
     b200_integrator_desc integ;
     double timePs = 0; int64_t stepCount = 0;
     bool forcesValid = false;
-    bool cmValid = false;          // device momentum buffer matches the current velocities (fused COM removal)
-    bool skipDispCheck = false;    // the previous step's integrator already ran the displacement check
-    bool fusedStepExtras = false;  // set by b200_step: COM removal and displacement check ride inside the integrator kernel
+    bool cmValid = false;          // device momentum buffer cm[stepCount % 3] matches the current velocities
+    bool cmDeferred = false;       // a COM-motion removal was requested; the next integration kernel subtracts it (b200_flush_cm applies it early)
+    bool dispChecked = false;      // the last integration kernel already ran the displacement check on the current positions
+    bool listVerified = false;     // the host has read the list counters since the positions were last set from outside
+    int64_t computeCount = 0;      // force evaluations since creation (lazy overflow check every 64th)
 
     // multi-GPU
     void* ncclComm = nullptr; int commRank = 0, commRanks = 1;
@@ -247,6 +249,8 @@ void b200_bonded_upload(b200_ctx* c);
 void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy);
 void b200_integrate_setup(b200_ctx* c);
 void b200_integrate_step(b200_ctx* c);
+void b200_request_cm_removal(b200_ctx* c);           // RemoveCMMotion: deferred into the next integration kernel when possible
+void b200_flush_cm(b200_ctx* c);                        // apply a deferred COM-motion removal now (before anything reads the velocities)
 void b200_comm_allreduce_forces(b200_ctx* c);
 void b200_comm_allreduce_energy(b200_ctx* c);
 void b200_comm_destroy(b200_ctx* c);

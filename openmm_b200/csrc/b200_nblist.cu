@@ -9,6 +9,7 @@
 // surviving j atoms into work units of up to 8 tiles.  Everything is decided on the device: the kernels
 // are launched every step and return immediately unless counters->rebuild is set.
 #include "b200_internal.cuh"
+#include <algorithm>
 
 #define NB_WARPS 4
 #define NB_THREADS (NB_WARPS * 32)
@@ -105,7 +106,7 @@ __device__ __forceinline__ void flushDense(int X, int* buf, int ntiles, int lane
     if (tileBase + ntiles <= tileCapacity && unit < unitCapacity) {
         for (int k = lane; k < ntiles * 32; k += 32) jAtoms[(size_t)tileBase * 32 + k] = buf[k];
         if (lane == 0) units[unit] = make_int4(X, (int)tileBase, ntiles, 0);
-    } else if (lane == 0) counters->overflow = 1;
+    } else if (lane == 0) { counters->overflow = 1; if (unit < unitCapacity) units[unit] = make_int4(X, 0, 0, 0); }   // dropped: leave an empty descriptor, never a stale one
 }
 __device__ __forceinline__ void flushSparse(int X, int* slots, int* masks, int ntiles, int lane, int4* units, int* jAtoms, unsigned unitCapacity, unsigned tileCapacity, DevCounters* counters) {
     unsigned tileBase = 0, unit = 0;
@@ -117,7 +118,7 @@ __device__ __forceinline__ void flushSparse(int X, int* slots, int* masks, int n
             jAtoms[(size_t)(tileBase + 2 * t + 1) * 32 + lane] = masks[t * 32 + lane];
         }
         if (lane == 0) units[unit] = make_int4(X, (int)tileBase, ntiles, 1);
-    } else if (lane == 0) counters->overflow = 1;
+    } else if (lane == 0) { counters->overflow = 1; if (unit < unitCapacity) units[unit] = make_int4(X, 0, 0, 1); }
 }
 
 __device__ __forceinline__ float2 nbFma2(float2 a, float2 b, float2 c) { unsigned long long d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)), "l"(*reinterpret_cast<unsigned long long*>(&c))); return *reinterpret_cast<float2*>(&d); }
@@ -318,7 +319,7 @@ void b200_nblist_alloc(b200_ctx* c) {
     if (c->tileCapacity == 0) {
         c->tileCapacity = (long long)c->B * 28 + 1024;
     }
-    c->unitCapacity = 2 * (long long)c->B + c->tileCapacity / 4 + 64;
+    c->unitCapacity = std::max(c->unitCapacity, 2 * (long long)c->B + c->tileCapacity / 4 + 64);
     dmalloc(c->units, (size_t)c->unitCapacity);
     dmalloc(c->jAtoms, (size_t)c->tileCapacity * 32);
 }
@@ -332,7 +333,7 @@ void b200_nblist_prepare(b200_ctx* c) {
     ScopedTimer tm(c, B200_T_NBLIST, c->stream);
     const float maxDisp = 0.5f * (float)c->padding;
     const int grid = c->smCount * 4;
-    if (!c->skipDispCheck) { nbCheckDisplacement<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, maxDisp * maxDisp, c->counters); LAUNCH_COUNT(c, 1); }
+    if (!c->dispChecked) { nbCheckDisplacement<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, maxDisp * maxDisp, c->counters); LAUNCH_COUNT(c, 1); }
     nbBlockBounds<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, c->B, c->boxF, c->blockCenter, c->blockHalf, c->counters);
     nbSuperBounds<<<(c->numSuper + 7) / 8, 256, 0, c->stream>>>(c->blockCenter, c->blockHalf, c->B, c->numSuper, c->boxF, c->superCenter, c->superHalf, c->counters);
     const float rcp = (float)c->paddedCutoff;

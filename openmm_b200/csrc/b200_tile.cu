@@ -45,6 +45,7 @@ struct TileArgs {
     DevCounters* counters;
     int2* pairOut; long long pairCapacity;
     int N, Npad;
+    unsigned unitCapacity;
     int exclBegin, exclEnd;      // exclusion tiles handled by this rank
     BoxF box; BoxD boxD;
     float rc2, rcPadded, alpha2, alpha3, alpha, kcoul;
@@ -134,7 +135,7 @@ __device__ __forceinline__ bool borderlineInside(const TileArgs& a, int slotI, i
 }
 
 // count (.x) and order-independent hash (.y) of the emitted pairs: sum over pairs of splitmix64(lo * N + hi) mod 2^64 on the
-// original particle indices -- the same hash tests/oracle_lib.py and oracle/ref_driver.cpp compute for the reference's pair set
+// original particle indices (the test side computes the same number from the reference's pair set)
 typedef ulonglong2 PairAcc;
 template <bool EMIT>
 __device__ __forceinline__ void emitPair(const TileArgs& a, int slotI, int slotJ, PairAcc& acc) {
@@ -377,7 +378,7 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem& sm = smAll[warp];
     const unsigned numExclUnits = (unsigned)(a.exclEnd - a.exclBegin);
-    const unsigned total = numExclUnits + a.counters->numUnits;
+    const unsigned total = numExclUnits + min(a.counters->numUnits, a.unitCapacity);   // (an overflowed build counts past its storage)
     long long eAcc = 0; PairAcc nPairs = make_ulonglong2(0ull, 0ull);
 
     // Work units are taken from a device-side queue.  The descriptor of the NEXT unit is fetched while the current one is
@@ -576,7 +577,7 @@ void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
     a.units = c->units; a.jAtoms = c->jAtoms; a.exclTiles = c->exclTiles; a.exclFlags = c->exclFlags;
     a.atomIndex = c->atomIndex; a.force = c->force; a.counters = c->counters;
     a.pairOut = c->pairOut; a.pairCapacity = c->pairCapacity;
-    a.N = c->N; a.Npad = c->Npad;
+    a.N = c->N; a.Npad = c->Npad; a.unitCapacity = (unsigned)c->unitCapacity;
     // exclusion tiles are split by index over ranks (CudaNonbondedUtilities.cpp:704-708)
     a.exclBegin = (int)llround(c->numExclTiles * c->partShareBegin);
     a.exclEnd = (int)llround(c->numExclTiles * c->partShareEnd);

@@ -41,29 +41,28 @@ void B200UpdateStateDataKernel::setTime(ContextImpl&, double time) { double t; i
 long long B200UpdateStateDataKernel::getStepCount(const ContextImpl&) const { double t; int64_t s; check(b200_get_time(d.ctx, &t, &s)); return s; }
 void B200UpdateStateDataKernel::setStepCount(const ContextImpl&, long long count) { double t; int64_t s; check(b200_get_time(d.ctx, &t, &s)); check(b200_set_time(d.ctx, t, count)); }
 
-static void toVec3(const vector<double>& a, vector<Vec3>& v) { v.resize(a.size() / 3); for (size_t i = 0; i < v.size(); i++) v[i] = Vec3(a[3 * i], a[3 * i + 1], a[3 * i + 2]); }
-static vector<double> fromVec3(const vector<Vec3>& v) { vector<double> a(3 * v.size()); for (size_t i = 0; i < v.size(); i++) { a[3 * i] = v[i][0]; a[3 * i + 1] = v[i][1]; a[3 * i + 2] = v[i][2]; } return a; }
+// A vector<Vec3> IS a contiguous double[3N] (Vec3 holds exactly three doubles, openmmapi/include/openmm/Vec3.h), so the C ABI
+// reads and writes the caller's vectors in place: no intermediate copy on the state I/O path.
+static_assert(sizeof(Vec3) == 3 * sizeof(double), "Vec3 must be three packed doubles");
+static double* asDoubles(vector<Vec3>& v) { return reinterpret_cast<double*>(v.data()); }
+static const double* asDoubles(const vector<Vec3>& v) { return reinterpret_cast<const double*>(v.data()); }
 
 void B200UpdateStateDataKernel::getPositions(ContextImpl&, vector<Vec3>& positions, bool) {
-    vector<double> a(3 * (size_t)numParticles);
-    check(b200_get_positions(d.ctx, a.data(), 0));
-    toVec3(a, positions);
+    positions.resize(numParticles);
+    check(b200_get_positions(d.ctx, asDoubles(positions), 0));
 }
 void B200UpdateStateDataKernel::setPositions(ContextImpl&, const vector<Vec3>& positions) {
     if ((int)positions.size() != numParticles) throw OpenMMException("Called setPositions() on a Context with the wrong number of positions");
-    vector<double> a = fromVec3(positions);
-    check(b200_set_positions(d.ctx, a.data()));
+    check(b200_set_positions(d.ctx, asDoubles(positions)));
     d.positionsValid = true;
 }
 void B200UpdateStateDataKernel::getVelocities(ContextImpl&, vector<Vec3>& velocities) {
-    vector<double> a(3 * (size_t)numParticles);
-    check(b200_get_velocities(d.ctx, a.data()));
-    toVec3(a, velocities);
+    velocities.resize(numParticles);
+    check(b200_get_velocities(d.ctx, asDoubles(velocities)));
 }
 void B200UpdateStateDataKernel::setVelocities(ContextImpl&, const vector<Vec3>& velocities) {
     if ((int)velocities.size() != numParticles) throw OpenMMException("Called setVelocities() on a Context with the wrong number of velocities");
-    vector<double> a = fromVec3(velocities);
-    check(b200_set_velocities(d.ctx, a.data()));
+    check(b200_set_velocities(d.ctx, asDoubles(velocities)));
 }
 void B200UpdateStateDataKernel::computeShiftedVelocities(ContextImpl& context, double timeShift, vector<Vec3>& velocities) {
     // v(t + shift) ~ v + shift * F/m with the forces currently in the buffer (IntegrationUtilities::computeShiftedVelocities)
@@ -75,9 +74,8 @@ void B200UpdateStateDataKernel::computeShiftedVelocities(ContextImpl& context, d
         if (masses[i] > 0) velocities[i] += forces[i] * (timeShift / masses[i]);
 }
 void B200UpdateStateDataKernel::getForces(ContextImpl&, vector<Vec3>& forces) {
-    vector<double> a(3 * (size_t)numParticles);
-    check(b200_get_forces(d.ctx, a.data()));
-    toVec3(a, forces);
+    forces.resize(numParticles);
+    check(b200_get_forces(d.ctx, asDoubles(forces)));
 }
 void B200UpdateStateDataKernel::getPeriodicBoxVectors(ContextImpl&, Vec3& a, Vec3& b, Vec3& c) const {
     double box[9];

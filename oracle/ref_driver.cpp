@@ -7,7 +7,7 @@
 //
 //   ref_driver eval  <system.bin> <out.bin> [--platform NAME] [--plugin lib.so]... [--pairs | --pair-hash]
 //   ref_driver compare <system.bin> --platform B200 --plugin libOpenMMB200.so [--against Reference]
-//   ref_driver bench <system.bin> --platform NAME [--plugin lib.so]... --steps K --warmup W [--threads T] [--dt ps] [--e2e]
+//   ref_driver bench <system.bin> --platform NAME [--plugin lib.so]... --steps K --warmup W [--threads T] [--dt ps] [--e2e] [--prop Key=Value]...
 //
 // system.bin layout (little endian), written by openmm_b200/system_io.py:
 //   char[4] "B2SY"; int32 version=1; int32 N; double box[9]; double cutoff; double alpha; int32 grid[3]; int32 method;
@@ -170,15 +170,17 @@ static int cmdCompare(int argc, char** argv) {
 
 static int cmdBench(int argc, char** argv) {
     string sysPath = argv[2], platformName = "CPU"; vector<string> plugins; int steps = 10, warmup = 3, threads = 0; double dt = 0.002; bool e2e = false;
+    map<string, string> extraProps;
     for (int i = 3; i < argc; i++) {
         string a = argv[i];
         if (a == "--platform") platformName = argv[++i]; else if (a == "--plugin") plugins.push_back(argv[++i]);
         else if (a == "--steps") steps = atoi(argv[++i]); else if (a == "--warmup") warmup = atoi(argv[++i]);
         else if (a == "--threads") threads = atoi(argv[++i]); else if (a == "--dt") dt = atof(argv[++i]); else if (a == "--e2e") e2e = true;
+        else if (a == "--prop") { string kv = argv[++i]; size_t eq = kv.find('='); if (eq != string::npos) extraProps[kv.substr(0, eq)] = kv.substr(eq + 1); }
     }
     SystemFile s = readSystem(sysPath);
     Platform& platform = pickPlatform(platformName, plugins);
-    map<string, string> props;
+    map<string, string> props = extraProps;
     if (threads > 0 && platformName == "CPU") props["Threads"] = to_string(threads);
     System* sys = buildSystem(s, true);
     // examples/benchmarks/benchmark.py:314-337: LangevinMiddle 300 K, 1/ps, constraint tolerance 1e-5
@@ -195,11 +197,13 @@ static int cmdBench(int argc, char** argv) {
     vector<Vec3> pos;
     t0 = chrono::steady_clock::now();
     if (!e2e) { integ.step(steps); ctx.getState(State::Energy); }   // benchmark.py:99-108
-    else for (int i = 0; i < steps; i++) {                           // host round trip every step
-        State st = ctx.getState(State::Positions);
-        ctx.setPositions(st.getPositions());
-        integ.step(1);
-        ctx.getState(State::Energy);
+    else {                                                           // host buffers in and out every step: setPositions + step + getState(Positions)
+        pos = ctx.getState(State::Positions).getPositions();
+        for (int i = 0; i < steps; i++) {
+            ctx.setPositions(pos);
+            integ.step(1);
+            pos = ctx.getState(State::Positions).getPositions();
+        }
     }
     double secs = chrono::duration<double>(chrono::steady_clock::now() - t0).count();
     double e = ctx.getState(State::Energy).getPotentialEnergy();

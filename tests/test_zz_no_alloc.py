@@ -17,7 +17,9 @@ pytestmark = pytest.mark.gpu
 def test_noalloc_matches_host_entry_point_twice():
     import torch
     rng = np.random.default_rng(11)
-    for call, shape in enumerate([(28, 25, 30), (56, 56, 56)]):
+    side = torch.cuda.Stream()      # the last shape runs on a stream of the caller's instead of the default one
+    # (25, 25, 27): odd nz, so the generic shared-memory passes run instead of the two-stage register passes
+    for call, shape in enumerate([(28, 25, 30), (56, 56, 56), (25, 25, 27), (90, 90, 90)]):
         nx, ny, nz = shape
         real = rng.normal(size=shape).astype(np.float32)
         spec = np.fft.rfftn(real.astype(np.float64)).astype(np.complex64)
@@ -28,11 +30,13 @@ def test_noalloc_matches_host_entry_point_twice():
         for rep in range(2):                                          # two calls in a row share the static scratch
             d_out.zero_()
             torch.cuda.synchronize()
-            b.fft3d_c2r_noalloc(d_in.data_ptr(), d_out.data_ptr(), nx, ny, nz)
+            b.fft3d_c2r_noalloc(d_in.data_ptr(), d_out.data_ptr(), nx, ny, nz, stream=side.cuda_stream if call == 3 else 0)
             torch.cuda.synchronize()
             got = d_out.cpu().numpy().reshape(shape)
             scale = np.abs(ref).max()
             assert np.abs(got - ref).max() / scale < 5e-6, (call, rep)
+            # and against the exact answer: the unnormalised inverse of the forward transform is the input times the grid size
+            assert np.abs(got / (nx * ny * nz) - real).max() < 5e-6, (call, rep)
         # the input spectrum is left untouched
         assert np.array_equal(d_in.cpu().numpy().ravel(), spec.view(np.float32).ravel())
 
@@ -44,3 +48,5 @@ def test_noalloc_rejects_oversized_grids():
         b.fft3d_c2r_noalloc(d.data_ptr(), d.data_ptr(), 196, 196, 196)
     with pytest.raises(b.B200Error, match="limit of 1024"):
         b.fft3d_c2r_noalloc(d.data_ptr(), d.data_ptr(), 2048, 2, 2)
+    with pytest.raises(b.B200Error, match="factor into 2, 3, 5 and 7"):
+        b.fft3d_c2r_noalloc(d.data_ptr(), d.data_ptr(), 22, 8, 8)
