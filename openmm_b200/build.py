@@ -69,6 +69,10 @@ def build_oracle(force=False):
     _run(["make", "-C", odir, "restatement"])
     if os.path.isdir(REF):
         _run(["make", "-C", odir, "-j8", "reference", "REF=" + REF])
+        try:   # the reference's CUDA platform (bench.py's "reference_gpu" row); its absence only removes that row
+            _run(["make", "-C", odir, "-j8", "reference_cuda", "REF=" + REF], log=os.path.join(odir, "_ref", "reference_cuda_build.log"))
+        except RuntimeError as e:
+            sys.stderr.write("reference CUDA platform not built: %s\n" % e)
     return os.path.join(odir, "liboracle_nb.so")
 
 

@@ -108,14 +108,28 @@ __device__ __forceinline__ void flushDense(int X, int* buf, int ntiles, int lane
         if (lane == 0) units[unit] = make_int4(X, (int)tileBase, ntiles, 0);
     } else if (lane == 0) { counters->overflow = 1; if (unit < unitCapacity) units[unit] = make_int4(X, 0, 0, 0); }   // dropped: leave an empty descriptor, never a stale one
 }
-__device__ __forceinline__ void flushSparse(int X, int* slots, int* masks, int ntiles, int lane, int4* units, int* jAtoms, unsigned unitCapacity, unsigned tileCapacity, DevCounters* counters) {
+// Sparse tiles are written sorted by the number of atoms of X each j atom reaches (descending): the tile kernel gives one lane
+// to each j atom and loops over the set bits of its mask, so a tile costs as many iterations as its LARGEST bit count; with
+// equal counts side by side the lanes of a warp finish together.  (Counting sort with ballots; the order is deterministic.)
+__device__ __forceinline__ void flushSparse(int X, int* slots, int* masks, int ntiles, int lane, int sparseMax, int4* units, int* jAtoms, unsigned unitCapacity, unsigned tileCapacity, DevCounters* counters) {
     unsigned tileBase = 0, unit = 0;
     if (lane == 0) { tileBase = atomicAdd(&counters->numTiles, (unsigned)(2 * ntiles)); unit = atomicAdd(&counters->numUnits, 1u); atomicAdd(&counters->numSparseTiles, (unsigned)ntiles); }
     tileBase = __shfl_sync(0xffffffffu, tileBase, 0); unit = __shfl_sync(0xffffffffu, unit, 0);
     if (tileBase + 2 * ntiles <= tileCapacity && unit < unitCapacity) {
-        for (int t = 0; t < ntiles; t++) {   // layout per sparse tile: 32 atom slots, then their 32 masks
-            jAtoms[(size_t)(tileBase + 2 * t) * 32 + lane] = slots[t * 32 + lane];
-            jAtoms[(size_t)(tileBase + 2 * t + 1) * 32 + lane] = masks[t * 32 + lane];
+        const unsigned ltMask = (1u << lane) - 1u;
+        int base = 0;
+        for (int v = sparseMax; v >= 0; v--) {   // layout per sparse tile: 32 atom slots, then their 32 masks; padding entries (count 0) go last
+            for (int t = 0; t < ntiles; t++) {
+                const int m = masks[t * 32 + lane];
+                const bool hit = __popc(m) == v;
+                const unsigned b = __ballot_sync(0xffffffffu, hit);
+                if (hit) {
+                    const int d = base + __popc(b & ltMask);
+                    const size_t o = (size_t)(tileBase + 2 * (d >> 5)) * 32 + (d & 31);
+                    jAtoms[o] = slots[t * 32 + lane]; jAtoms[o + 32] = m;
+                }
+                base += __popc(b);
+            }
         }
         if (lane == 0) units[unit] = make_int4(X, (int)tileBase, ntiles, 1);
     } else if (lane == 0) { counters->overflow = 1; if (unit < unitCapacity) units[unit] = make_int4(X, 0, 0, 1); }
@@ -171,7 +185,7 @@ __device__ __forceinline__ void nbProcessCandidates(int X, int lane, unsigned lt
         __syncwarp();
     }
     if (nsp >= NB_SPARSE_TILES * 32) {   // flush one full sparse work unit
-        flushSparse(X, w.slots, w.masks, NB_SPARSE_TILES, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
+        flushSparse(X, w.slots, w.masks, NB_SPARSE_TILES, lane, sparseMax, units, jAtoms, unitCapacity, tileCapacity, counters);
         const int rest = nsp - NB_SPARSE_TILES * 32;
         int c0 = 0, c1 = 0;
         if (lane < rest) { c0 = w.slots[NB_SPARSE_TILES * 32 + lane]; c1 = w.masks[NB_SPARSE_TILES * 32 + lane]; }
@@ -305,7 +319,7 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
             const int nt = (nsp + 31) >> 5;
             for (int k = nsp + lane; k < nt * 32; k += 32) { sSlot[warp][k] = -1; sMask[warp][k] = 0; }
             __syncwarp();
-            flushSparse(X, sSlot[warp], sMask[warp], nt, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
+            flushSparse(X, sSlot[warp], sMask[warp], nt, lane, sparseMax, units, jAtoms, unitCapacity, tileCapacity, counters);
         }
         __syncwarp();
     }

@@ -22,6 +22,7 @@
 #include <cstring>
 #include <fstream>
 #include <iostream>
+#include <sstream>
 #include <string>
 #include <vector>
 
@@ -215,11 +216,51 @@ static int cmdBench(int argc, char** argv) {
     return 0;
 }
 
+// createCheckpoint / loadCheckpoint round trip (UpdateStateDataKernel, kernels.h:239-245): run A steps, checkpoint, run B steps and
+// remember the state; load the checkpoint, run B steps again: both runs must agree (bit for bit on a deterministic platform).
+static int cmdCheckpoint(int argc, char** argv) {
+    string sysPath = argv[2], platformName = "B200"; vector<string> plugins; int stepsA = 20, stepsB = 30;
+    for (int i = 3; i < argc; i++) {
+        string a = argv[i];
+        if (a == "--platform") platformName = argv[++i]; else if (a == "--plugin") plugins.push_back(argv[++i]);
+        else if (a == "--steps") { stepsA = atoi(argv[++i]); stepsB = stepsA; }
+    }
+    SystemFile s = readSystem(sysPath);
+    Platform& platform = pickPlatform(platformName, plugins);
+    System* sys = buildSystem(s, true);
+    LangevinMiddleIntegrator integ(300.0, 1.0, 0.002);
+    integ.setConstraintTolerance(1e-5);
+    integ.setRandomNumberSeed(11);
+    Context ctx(*sys, integ, platform);
+    ctx.setPositions(toVec3(s.pos)); ctx.setVelocities(toVec3(s.vel));
+    integ.step(stepsA);
+    stringstream chk(ios::in | ios::out | ios::binary);
+    ctx.createCheckpoint(chk);
+    const double tChk = ctx.getState(0).getTime();
+    integ.step(stepsB);
+    State a = ctx.getState(State::Positions | State::Velocities);
+    chk.seekg(0);
+    ctx.loadCheckpoint(chk);
+    const double tLoaded = ctx.getState(0).getTime();
+    integ.step(stepsB);
+    State b = ctx.getState(State::Positions | State::Velocities);
+    double dp = 0, dv = 0;
+    for (int i = 0; i < s.N; i++) {
+        Vec3 d = a.getPositions()[i] - b.getPositions()[i], e = a.getVelocities()[i] - b.getVelocities()[i];
+        dp = max(dp, sqrt(d.dot(d))); dv = max(dv, sqrt(e.dot(e)));
+    }
+    printf("{\"platform\": \"%s\", \"n\": %d, \"max_position_difference\": %.3e, \"max_velocity_difference\": %.3e, \"time_restored\": %s, \"final_time_equal\": %s}\n",
+           platformName.c_str(), s.N, dp, dv, fabs(tChk - tLoaded) < 1e-12 ? "true" : "false", a.getTime() == b.getTime() ? "true" : "false");
+    delete sys;
+    return 0;
+}
+
 int main(int argc, char** argv) {
     try {
         if (argc >= 4 && string(argv[1]) == "eval") return cmdEval(argc, argv);
         if (argc >= 3 && string(argv[1]) == "compare") return cmdCompare(argc, argv);
         if (argc >= 3 && string(argv[1]) == "bench") return cmdBench(argc, argv);
+        if (argc >= 3 && string(argv[1]) == "checkpoint") return cmdCheckpoint(argc, argv);
         fprintf(stderr, "usage: ref_driver eval|compare|bench ...\n");
         return 2;
     } catch (const exception& e) {

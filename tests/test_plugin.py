@@ -85,3 +85,18 @@ def test_langevin_middle_steps_through_the_plugin():
     assert np.isfinite(g["potential_energy"])
     # same ensemble after 250 steps: potential energies of the two platforms agree to within thermal fluctuations (~1%)
     assert abs(g["potential_energy"] - c["potential_energy"]) / abs(c["potential_energy"]) < 0.03
+
+
+@pytest.mark.gpu
+def test_checkpoint_round_trip_through_the_plugin():
+    # Context::createCheckpoint / loadCheckpoint on the B200 platform: the continuation from a loaded checkpoint repeats the original
+    # continuation exactly (positions, velocities, time and the step counter that keys the integrator's noise are all restored)
+    sysd = workloads.water_box(3000, seed=8)
+    alpha, grid = b.pme_parameters(0.9, sysd["box"])
+    with tempfile.TemporaryDirectory() as td:
+        sp = os.path.join(td, "s.bin")
+        workloads.write_system_file(sp, sysd, 0.9, alpha, grid)
+        r = _driver(["checkpoint", sp, "--platform", "B200", "--plugin", b.PLUGIN_PATH, "--steps", "25"])
+    print(r)
+    assert r["time_restored"] and r["final_time_equal"]
+    assert r["max_position_difference"] == 0.0 and r["max_velocity_difference"] == 0.0
