@@ -61,7 +61,7 @@ typedef struct {
     int32_t       method;            /* B200_NB_* */
     double        cutoff;            /* nm */
     double        ewald_alpha;       /* nm^-1 (NonbondedForceImpl::calcPMEParameters, NonbondedForceImpl.cpp:192-216) */
-    int32_t       grid[3];           /* PME mesh; each must factor into 2,3,5,7 */
+    int32_t       grid[3];           /* PME / LJPME: mesh, each dimension must factor into 2,3,5,7 */
     double        dispersion_coefficient; /* C of E = C/V (NonbondedForceImpl::calcDispersionCorrection, :268-342); 0 = off */
     int32_t       use_switch;        /* LJ switching function (coulombLennardJones.cc:32-40) */
     double        switch_distance;
@@ -79,6 +79,7 @@ typedef struct {
     int32_t       exceptions_use_periodic; /* NonbondedForce::getExceptionsUsePeriodicBoundaryConditions */
     double        ljpme_alpha;       /* LJPME only */
     int32_t       ljpme_grid[3];
+    int32_t       ewald_kmax[3];     /* Ewald only: number of k vectors per direction (NonbondedForceImpl::calcEwaldParameters, NonbondedForceImpl.cpp:159-190) */
 } b200_nonbonded_desc;
 
 /* ---- context life cycle (Platform::contextCreated / contextDestroyed, olla/include/openmm/Platform.h:232-252) */

@@ -43,7 +43,8 @@ class NonbondedDesc(ctypes.Structure):
                 ("num_exclusions", ctypes.c_int32), ("exclusion_pairs", c_int32_p),
                 ("num_exceptions", ctypes.c_int32), ("exception_pairs", c_int32_p),
                 ("exception_chargeprod", c_double_p), ("exception_sigma", c_double_p), ("exception_epsilon", c_double_p),
-                ("exceptions_use_periodic", ctypes.c_int32), ("ljpme_alpha", ctypes.c_double), ("ljpme_grid", ctypes.c_int32 * 3)]
+                ("exceptions_use_periodic", ctypes.c_int32), ("ljpme_alpha", ctypes.c_double), ("ljpme_grid", ctypes.c_int32 * 3),
+                ("ewald_kmax", ctypes.c_int32 * 3)]
 
 
 class IntegratorDesc(ctypes.Structure):
@@ -161,9 +162,14 @@ class Context:
 
     # CalcNonbondedForceKernel::initialize
     def add_nonbonded_force(self, charge, sigma, epsilon, cutoff, alpha, grid, exclusions=(), exceptions=None,
-                            method=NB_PME, dispersion_coefficient=0.0, exceptions_use_periodic=False, lj_alpha=None, lj_grid=None, switch_distance=None):
+                            method=NB_PME, dispersion_coefficient=0.0, exceptions_use_periodic=False, lj_alpha=None, lj_grid=None, switch_distance=None,
+                            reaction_field_dielectric=78.3, ewald_kmax=None):
         d = NonbondedDesc()
         d.method = method
+        d.reaction_field_dielectric = reaction_field_dielectric
+        if ewald_kmax is not None:    # NonbondedForce::Ewald: explicit sum over k vectors
+            for k in range(3):
+                d.ewald_kmax[k] = int(ewald_kmax[k])
         if switch_distance is not None:    # NonbondedForce::setUseSwitchingFunction(true) + setSwitchingDistance
             d.use_switch, d.switch_distance = 1, switch_distance
         if lj_alpha is not None:      # NonbondedForce::LJPME with setLJPMEParameters(lj_alpha, *lj_grid)

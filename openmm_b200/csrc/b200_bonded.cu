@@ -28,7 +28,7 @@ __device__ __forceinline__ void blockEnergy(double e, long long* slot) {
 }
 
 __global__ void __launch_bounds__(128) exclusionCorrection(const float4* __restrict__ posq, const float2* __restrict__ sigEps, const int2* __restrict__ pairs, int n, BoxD box, double alpha,
-                                                            double ljAlpha, long long* force, int Npad, DevCounters* counters, int wantForce, int wantEnergy) {
+                                                            double ljAlpha, int periodic, long long* force, int Npad, DevCounters* counters, int wantForce, int wantEnergy) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     double e = 0;
     if (t < n) {
@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(128) exclusionCorrection(const float4* __restr
             const double c6 = 64.0 * ((double)sa.x * sa.x * sa.x * sa.y) * ((double)sb.x * sb.x * sb.x * sb.y);
             if (c6 != 0.0) {
                 double dx = (double)b.x - a.x, dy = (double)b.y - a.y, dz = (double)b.z - a.z;
-                imageDeltaD(dx, dy, dz, box);
+                if (periodic) imageDeltaD(dx, dy, dz, box);
                 const double r2 = dx * dx + dy * dy + dz * dz, invR2 = 1.0 / r2, invR6 = invR2 * invR2 * invR2;
                 const double x = ljAlpha * ljAlpha * r2, x2 = x * x, ex = exp(-x);
                 e += c6 * invR6 * (1.0 - ex * (1.0 + x + 0.5 * x2));
@@ -54,8 +54,10 @@ __global__ void __launch_bounds__(128) exclusionCorrection(const float4* __restr
             }
         }
         if (qq != 0.0) {
+            // like the 1-4 terms, the correction of an excluded pair uses the plain displacement unless the force asks for periodic
+            // exceptions (pmeExclusions.cc:3, USE_PERIODIC = getExceptionsUsePeriodicBoundaryConditions; molecules are kept whole)
             double dx = (double)b.x - a.x, dy = (double)b.y - a.y, dz = (double)b.z - a.z;
-            imageDeltaD(dx, dy, dz, box);
+            if (periodic) imageDeltaD(dx, dy, dz, box);
             const double r2 = dx * dx + dy * dy + dz * dz, r = sqrt(r2), ar = alpha * r;
             if (ar > 1e-6) {
                 const double erfAR = erf(ar), invR = 1.0 / r;
@@ -217,13 +219,14 @@ void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy) 
     // with a communicator the excluded-pair corrections are split over the ranks like the direct-space rows (the energies are
     // all-reduced afterwards); everything else in this file runs on rank 0
     const bool split = c->commRanks > 1;
-    if (c->hasNonbonded && (groups & B200_GROUP_DIRECT) && c->numExclPairs > 0) {
+    // (the erf correction of excluded pairs exists only where a reciprocal sum includes them: the Ewald family)
+    if (c->hasNonbonded && c->nb.method >= B200_NB_EWALD && (groups & B200_GROUP_DIRECT) && c->numExclPairs > 0) {
         // slices start at multiples of the block size, so every block sums the same pairs as on one rank (bit-identical energy)
         const int nblk = (c->numExclPairs + 127) / 128;
         const int begin = split ? 128 * (int)llround(nblk * c->partShareBegin) : 0;
         const int end = split ? std::min(c->numExclPairs, 128 * (int)llround(nblk * c->partShareEnd)) : c->numExclPairs;
         if (end > begin && (split || c->partRank == 0)) {
-            exclusionCorrection<<<(end - begin + 127) / 128, 128, 0, s>>>(c->posq, c->ljpme ? c->sigEps : nullptr, c->dExclPairs + begin, end - begin, c->boxD, c->nb.ewald_alpha, c->nb.ljpme_alpha, c->force, c->Npad, c->counters, wf, we);
+            exclusionCorrection<<<(end - begin + 127) / 128, 128, 0, s>>>(c->posq, c->ljpme ? c->sigEps : nullptr, c->dExclPairs + begin, end - begin, c->boxD, c->nb.ewald_alpha, c->nb.ljpme_alpha, c->nb.exceptions_use_periodic, c->force, c->Npad, c->counters, wf, we);
             LAUNCH_COUNT(c, 1);
         }
     }

@@ -46,6 +46,8 @@ void b200_box_set(b200_ctx* c, const double* box) {
     f.iax = (float)d.iax; f.iby = (float)d.iby; f.icz = (float)d.icz;
     f.triclinic = (d.bx != 0 || d.cx != 0 || d.cy != 0) ? 1 : 0;
     c->boxF = f;
+    if (c->hasNonbonded && c->nb.method == B200_NB_EWALD && f.triclinic)
+        throw B200Error(B200_ERR_UNSUPPORTED, "NonbondedForce::Ewald needs a rectangular periodic box (use PME for triclinic cells)");
     if (c->hasNonbonded && c->nb.method >= B200_NB_CUTOFF_PERIODIC) {
         // CudaNonbondedUtilities.cpp:391-396: the box must be at least twice the cutoff
         const double m = std::min(d.ax, std::min(d.by, d.cz));
@@ -120,10 +122,10 @@ extern "C" void b200_context_destroy(b200_ctx* c) {
     dfree(c->posqTmp); dfree(c->posqCorrTmp); dfree(c->velmTmp); dfree(c->atomIndexTmp); dfree(c->cellOffsetsTmp);
     dfree(c->blockCenter); dfree(c->blockHalf); dfree(c->superCenter); dfree(c->superHalf); dfree(c->refPosq);
     dfree(c->units); dfree(c->jAtoms); dfree(c->pairOut);
-    dfree(c->settleAtoms); dfree(c->settleParams); dfree(c->freeAtoms);
+    dfree(c->settleAtoms); dfree(c->settleParams); dfree(c->freeAtoms); dfree(c->shakeAtoms); dfree(c->shakeDist);
     dfree(c->exclTiles); dfree(c->exclFlags); dfree(c->exclRowStart); dfree(c->exclRowCols); dfree(c->dExclPairs); dfree(c->dExcPairs); dfree(c->dExcParams);
     dfree(c->bondAtoms); dfree(c->bondParams); dfree(c->angleAtoms); dfree(c->angleParams); dfree(c->torsionAtoms); dfree(c->torsionParams);
-    dfree(c->sortKeys); dfree(c->sortCount); dfree(c->sortStart); dfree(c->sortOrder);
+    dfree(c->ewaldS); dfree(c->sortKeys); dfree(c->sortCount); dfree(c->sortStart); dfree(c->sortOrder);
     for (auto& g : c->groups) dfree(g.dBase);
     if (c->countersHost) cudaFreeHost(c->countersHost);
     if (c->hStage) cudaFreeHost(c->hStage);
@@ -150,10 +152,9 @@ extern "C" int b200_nonbonded_create(b200_ctx* c, const b200_nonbonded_desc* d) 
     if (!c || !d) throw B200Error(B200_ERR_INVALID, "b200_nonbonded_create: null argument");
     if (c->hasNonbonded) throw B200Error(B200_ERR_UNSUPPORTED, "only one NonbondedForce per context is supported");
     if (c->finalized) throw B200Error(B200_ERR_INVALID, "forces must be created before the first computation");
-    if (d->method != B200_NB_PME && d->method != B200_NB_LJPME)
-        throw B200Error(B200_ERR_UNSUPPORTED, "NonbondedForce: the B200 platform currently implements the PME and LJPME methods only");
-    if (d->use_switch) {
-        if (d->method == B200_NB_LJPME) throw B200Error(B200_ERR_UNSUPPORTED, "NonbondedForce: the switching function together with LJPME is not implemented");
+    if (d->method < B200_NB_NOCUTOFF || d->method > B200_NB_LJPME) throw B200Error(B200_ERR_INVALID, "NonbondedForce: unknown nonbonded method");
+    if (d->method != B200_NB_NOCUTOFF && !(d->cutoff > 0)) throw B200Error(B200_ERR_INVALID, "NonbondedForce: the cutoff distance must be positive");
+    if (d->use_switch && d->method != B200_NB_NOCUTOFF) {
         if (!(d->switch_distance >= 0) || !(d->switch_distance < d->cutoff))
             throw B200Error(B200_ERR_INVALID, "NonbondedForce: Switching distance must satisfy 0 <= r_switch < r_cutoff");   // NonbondedForceImpl.cpp:70-74
     }
@@ -167,10 +168,15 @@ extern "C" int b200_nonbonded_create(b200_ctx* c, const b200_nonbonded_desc* d) 
     c->excQQ.assign(d->exception_chargeprod, d->exception_chargeprod + d->num_exceptions);
     c->excSig.assign(d->exception_sigma, d->exception_sigma + d->num_exceptions);
     c->excEps.assign(d->exception_epsilon, d->exception_epsilon + d->num_exceptions);
-    for (int k = 0; k < 3; k++) {
+    const bool usesMesh = d->method == B200_NB_PME || d->method == B200_NB_LJPME;
+    for (int k = 0; k < 3 && usesMesh; k++) {
         if (d->grid[k] < 6 || b200_find_legal_fft_dimension(d->grid[k]) != d->grid[k])
             throw B200Error(B200_ERR_INVALID, "PME grid dimensions must be >= 6 and factor into 2,3,5,7");
     }
+    if (d->method == B200_NB_EWALD) {
+        for (int k = 0; k < 3; k++) if (d->ewald_kmax[k] < 1) throw B200Error(B200_ERR_INVALID, "Ewald: kmax must be at least 1 in every direction");
+    }
+    if (d->method == B200_NB_NOCUTOFF) c->nb.use_switch = 0;     // no cutoff, nothing to switch (NonbondedForceImpl ignores it as well)
     c->ljpme = d->method == B200_NB_LJPME;
     if (c->ljpme) {
         if (!(d->ljpme_alpha > 0)) throw B200Error(B200_ERR_INVALID, "LJPME: the dispersion Ewald coefficient must be positive");
@@ -185,7 +191,10 @@ extern "C" int b200_nonbonded_create(b200_ctx* c, const b200_nonbonded_desc* d) 
     const double padFrac = padEnv ? atof(padEnv) : 0.08;
     c->padding = padFrac * d->cutoff;
     c->paddedCutoff = d->cutoff + c->padding;
-    c->exactEwald = d->ewald_alpha * d->cutoff > 3.95;
+    if (d->method == B200_NB_NOCUTOFF) { c->padding = INFINITY; c->paddedCutoff = INFINITY; }   // the list holds every pair and never needs a rebuild
+    const bool ewaldType = d->method >= B200_NB_EWALD;
+    // the rational fit covers alpha*rc <= 3.95; the other Coulomb forms live in the scalar ("exact") instantiation of the tile kernel
+    c->exactEwald = !ewaldType || d->ewald_alpha * d->cutoff > 3.95;
     if (const char* sp = getenv("B200_SPARSE_MAX")) c->sparseMax = std::max(0, std::min(32, atoi(sp)));
     b200_box_set(c, c->boxHost);
     // per-slot parameters (nonbondedParameters.cc:30-35: posq.w = q, sigmaEpsilon = (sigma/2, 2 sqrt(eps)))
@@ -206,15 +215,15 @@ extern "C" int b200_nonbonded_create(b200_ctx* c, const b200_nonbonded_desc* d) 
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
     c->totalCharge = sumQ;
     // Ewald self energy (CommonCalcNonbondedForce.cpp:397-400)
-    c->selfEnergy = -B200_ONE_4PI_EPS0 * d->ewald_alpha * sumQ2 / sqrt(M_PI);
+    c->selfEnergy = ewaldType ? -B200_ONE_4PI_EPS0 * d->ewald_alpha * sumQ2 / sqrt(M_PI) : 0.0;
     b200_lj_self_energy(c);
-    b200_pme_create(c);
+    if (usesMesh) b200_pme_create(c);
     API_END
 }
 
 extern "C" int b200_nonbonded_get_pme_parameters(const b200_ctx* c, double* alpha, int32_t* nx, int32_t* ny, int32_t* nz) {
     API_BEGIN
-    if (!c || !c->hasNonbonded) throw B200Error(B200_ERR_INVALID, "no NonbondedForce in this context");
+    if (!c || !c->hasNonbonded || c->nb.method < B200_NB_PME) throw B200Error(B200_ERR_INVALID, "getPMEParametersInContext: This Context is not using PME");
     *alpha = c->nb.ewald_alpha; *nx = c->nb.grid[0]; *ny = c->nb.grid[1]; *nz = c->nb.grid[2];
     API_END
 }
@@ -254,9 +263,9 @@ extern "C" int b200_nonbonded_update_parameters(b200_ctx* c, const b200_nonbonde
     h2d(c->sigEps, se.data(), c->Npad, c->stream); h2d(c->posq, p.data(), c->Npad, c->stream);
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
     c->totalCharge = sumQ;
-    c->selfEnergy = -B200_ONE_4PI_EPS0 * c->nb.ewald_alpha * sumQ2 / sqrt(M_PI);
+    c->selfEnergy = c->nb.method >= B200_NB_EWALD ? -B200_ONE_4PI_EPS0 * c->nb.ewald_alpha * sumQ2 / sqrt(M_PI) : 0.0;
     b200_lj_self_energy(c);
-    b200_pme_rescale(c);
+    if (c->nb.method >= B200_NB_PME) b200_pme_rescale(c);
     if (c->finalized) {
         // Molecules of a group are exchanged among the group's slots when atoms are re-sorted, which is only valid while they are
         // identical.  New parameters may have made some of them different (the reference recomputes its molecule groups:
@@ -432,6 +441,28 @@ void b200_finalize(b200_ctx* c) {
         if (!sa.empty()) {
             CUDA_CHECK(cudaMemcpy(c->settleAtoms, sa.data(), sizeof(int4) * sa.size(), cudaMemcpyHostToDevice));
             CUDA_CHECK(cudaMemcpy(c->settleParams, sp.data(), sizeof(float2) * sp.size(), cudaMemcpyHostToDevice));
+        }
+        // ---- SHAKE clusters (integrationUtilities.cc:99-240 applyShakeToHydrogens; the HBonds constraints of a solvated protein):
+        // a central atom whose 1-3 constrained partners are constrained to nothing else
+        {
+            std::vector<int4> ka; std::vector<float4> kd;
+            for (int i = 0; i < N; i++) {
+                if (inCluster[i] || con[i].empty() || con[i].size() > 3) continue;
+                bool star = true;
+                for (auto& e : con[i]) star = star && !inCluster[e.first] && con[e.first].size() == 1 && c->mass[e.first] > 0;
+                if (!star || c->mass[i] <= 0) continue;
+                if (con[i].size() == 1 && con[i][0].first < i) continue;     // a lone pair: its lower index is the centre
+                int a[4] = {i, -1, -1, -1}; float dd[4] = {0.f, 0.f, 0.f, 0.f};
+                for (size_t k = 0; k < con[i].size(); k++) { a[k + 1] = con[i][k].first; dd[k] = (float)con[i][k].second; inCluster[con[i][k].first] = 1; }
+                inCluster[i] = 1;
+                ka.push_back(make_int4(a[0], a[1], a[2], a[3])); kd.push_back(make_float4(dd[0], dd[1], dd[2], 0.f));
+            }
+            c->numShake = (int)ka.size();
+            dmalloc(c->shakeAtoms, ka.size()); dmalloc(c->shakeDist, kd.size());
+            if (!ka.empty()) {
+                CUDA_CHECK(cudaMemcpy(c->shakeAtoms, ka.data(), sizeof(int4) * ka.size(), cudaMemcpyHostToDevice));
+                CUDA_CHECK(cudaMemcpy(c->shakeDist, kd.data(), sizeof(float4) * kd.size(), cudaMemcpyHostToDevice));
+            }
         }
         std::vector<int> freeAtoms;
         c->numOtherConstraints = 0;
@@ -777,14 +808,14 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     c->computeCount++;
     if (forces) CUDA_CHECK(cudaMemsetAsync(c->force, 0, sizeof(long long) * 3 * (size_t)c->Npad, s));
     if (energy) { zeroEnergy<<<1, 1, 0, s>>>(c->counters); LAUNCH_COUNT(c, 1); }
-    const bool doRecip = c->hasNonbonded && (groups & B200_GROUP_RECIPROCAL) && c->partRank == 0;
+    const bool doRecip = c->hasNonbonded && c->nb.method >= B200_NB_EWALD && (groups & B200_GROUP_RECIPROCAL) && c->partRank == 0;
     const bool doDirect = c->hasNonbonded && (groups & B200_GROUP_DIRECT);
     // per-family event timing needs the families serialised: overlapping streams would charge waiting time to the wrong family
     const bool usePmeStream = c->usePmeStream && !c->timing;
     cudaStream_t ps = usePmeStream ? c->pmeStream : s;
     if (doRecip) {
         if (usePmeStream) { CUDA_CHECK(cudaEventRecord(c->evFork, s)); CUDA_CHECK(cudaStreamWaitEvent(ps, c->evFork, 0)); }
-        b200_pme_launch(c, ps, forces, energy);
+        if (c->nb.method == B200_NB_EWALD) b200_ewald_launch(c, ps, forces, energy); else b200_pme_launch(c, ps, forces, energy);
         if (usePmeStream) CUDA_CHECK(cudaEventRecord(c->evPmeDone, ps));
     }
     if (doDirect) {
@@ -804,7 +835,7 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
 // without a communicator a rank reports only what it computed (N logical ranks on one device are summed by the
         // caller); with one, the integer all-reduce above gave every rank the full device sums and every rank adds the host terms
         const bool all = c->commRanks > 1;
-        const bool wantRecip = c->hasNonbonded && (groups & B200_GROUP_RECIPROCAL) && (c->partRank == 0 || all);
+        const bool wantRecip = c->hasNonbonded && c->nb.method >= B200_NB_EWALD && (groups & B200_GROUP_RECIPROCAL) && (c->partRank == 0 || all);
         const bool extras = c->partRank == 0 || all;
         if (doDirect) e += inv * (double)h.energy[E_DIRECT];
         if (doDirect && extras) e += inv * ((double)h.energy[E_EXCLCORR] + (double)h.energy[E_EXCEPT]);
@@ -897,9 +928,9 @@ extern "C" int b200_step(b200_ctx* c, int32_t nsteps) {
     if (!c->hasIntegrator) throw B200Error(B200_ERR_INVALID, "b200_step: no integrator");
     CUDA_CHECK(cudaSetDevice(c->device));
     b200_finalize(c);
-    if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
+    if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints that are neither rigid 3-site molecules (SETTLE) nor clusters of one central atom with up to three singly-constrained partners (SHAKE) are not implemented");
     // peer-memory step: the momentum bookkeeping inside the integration kernel is what keeps the ranks' momenta in step
-    c->peerStepActive = c->peerMode && c->commRanks > 1 && c->integ.remove_cm_every <= 1 && c->hasNonbonded;
+    c->peerStepActive = c->peerMode && c->commRanks > 1 && c->integ.remove_cm_every <= 1 && c->hasNonbonded && c->numShake == 0;   // (SHAKE clusters are not sharded yet)
     if (c->peerStepActive) {
         b200_peer_plan_shard(c);
         // Slices whose atoms are not one contiguous range of slots (units listed out of slot order) would need the per-atom peer

@@ -221,6 +221,110 @@ __global__ void __launch_bounds__(128, 4) langevinMiddleStep(IntegArgs a, int nu
     }
 }
 
+// ---- SHAKE clusters: a central atom (index 0) with up to three partners, each constrained to the centre only -- the HBonds
+// constraints of a solvated protein (integrationUtilities.cc:99-240 applyShakeToHydrogens).  One thread owns a cluster and
+// iterates the classic SHAKE / RATTLE updates over its constraints until all of them are met to the tolerance.
+#define SHAKE_MAX_ITER 60
+__device__ __forceinline__ void shakeVelocities(int n, const V3* p, V3* v, const double* im, double tol, double dt) {
+    for (int it = 0; it < SHAKE_MAX_ITER; it++) {
+        bool done = true;
+        for (int k = 1; k < n; k++) {
+            const V3 s = p[k] - p[0];
+            const double s2 = dot(s, s), vrel = dot(v[k] - v[0], s);
+            if (fabs(vrel) * dt > tol * s2) done = false;
+            const double lam = -vrel / ((im[0] + im[k]) * s2);
+            v[k] = v[k] + s * (lam * im[k]); v[0] = v[0] - s * (lam * im[0]);
+        }
+        if (done) break;
+    }
+}
+// p: constrained old positions, d: unconstrained displacements (updated in place)
+__device__ __forceinline__ void shakePositions(int n, const V3* p, V3* d, const double* im, const float* dist, double tol) {
+    for (int it = 0; it < SHAKE_MAX_ITER; it++) {
+        bool done = true;
+        for (int k = 1; k < n; k++) {
+            const V3 s = p[k] - p[0], sp = s + d[k] - d[0];
+            const double d2 = (double)dist[k - 1] * (double)dist[k - 1], diff = d2 - dot(sp, sp);
+            if (fabs(diff) > 2.0 * tol * d2) done = false;
+            const double lam = diff / (2.0 * (im[0] + im[k]) * dot(s, sp));
+            d[k] = d[k] + s * (lam * im[k]); d[0] = d[0] - s * (lam * im[0]);
+        }
+        if (done) break;
+    }
+}
+
+// LangevinMiddle step of the SHAKE clusters (same three parts and the same fused extras as langevinMiddleStep)
+__global__ void __launch_bounds__(128) langevinMiddleShake(IntegArgs a, int numShake, const int4* __restrict__ shakeAtoms, const float4* __restrict__ shakeDist, double tol) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const double halfdt = 0.5 * a.dt, invDt = 1.0 / a.dt;
+    V3 vcm = {0, 0, 0}, mom = {0, 0, 0};
+    if (a.fuseCM == 2) {
+        const double sc = a.invTotalMass / CM_SCALE;
+        vcm = {sc * (double)a.counters->cm[a.cmCur][0], sc * (double)a.counters->cm[a.cmCur][1], sc * (double)a.counters->cm[a.cmCur][2]};
+    }
+    bool moved = false;
+    if (t < numShake) {
+        const int4 at = shakeAtoms[t]; const float4 dd = shakeDist[t];
+        const int idx[4] = {at.x, at.y, at.z, at.w};
+        const float dist[3] = {dd.x, dd.y, dd.z};
+        const int n = at.w >= 0 ? 4 : at.z >= 0 ? 3 : 2;
+        V3 p[4], v[4], d[4], old[4]; double im[4];
+        for (int k = 0; k < n; k++) {
+            p[k] = loadPosD(a, idx[k]);
+            const double4 vm = a.velm[idx[k]];
+            im[k] = vm.w;
+            v[k] = V3{vm.x, vm.y, vm.z} - vcm + loadForce<false>(a, idx[k]) * (a.dt * vm.w);
+        }
+        shakeVelocities(n, p, v, im, tol, a.dt);
+        for (int k = 0; k < n; k++) {
+            d[k] = v[k] * halfdt;
+            const V3 g = gaussian3(a.seed, a.step, a.atomIndex[idx[k]]);
+            v[k] = v[k] * a.vscale + g * (a.noisescale * sqrt(im[k]));
+            d[k] = d[k] + v[k] * halfdt;
+            old[k] = d[k];
+        }
+        shakePositions(n, p, d, im, dist, tol);
+        for (int k = 0; k < n; k++) {
+            v[k] = v[k] + (d[k] - old[k]) * invDt;
+            a.velm[idx[k]] = make_double4(v[k].x, v[k].y, v[k].z, im[k]);
+            const V3 pn = p[k] + d[k];
+            storePosD<false>(a, idx[k], pn);
+            checkMoved(a, idx[k], pn, moved);
+            mom = mom + v[k] * (1.0 / im[k]);
+        }
+    }
+    if (a.refPosq && __any_sync(0xffffffffu, moved) && (threadIdx.x & 31) == 0) a.counters->rebuild = 1;
+    if (a.fuseCM) {
+        __shared__ double red[3][128];
+        red[0][threadIdx.x] = mom.x; red[1][threadIdx.x] = mom.y; red[2][threadIdx.x] = mom.z;
+        __syncthreads();
+        for (int o = 64; o > 0; o >>= 1) {
+            if (threadIdx.x < o) for (int k = 0; k < 3; k++) red[k][threadIdx.x] += red[k][threadIdx.x + o];
+            __syncthreads();
+        }
+        if (threadIdx.x < 3) atomicAddFixed(&a.counters->cm[a.cmNext][threadIdx.x], (long long)(red[threadIdx.x][0] * CM_SCALE));
+    }
+}
+
+// stand-alone constraint passes over the SHAKE clusters (ApplyConstraintsKernel::apply / applyToVelocities)
+__global__ void shakeOnly(IntegArgs a, int numShake, const int4* __restrict__ shakeAtoms, const float4* __restrict__ shakeDist, double tol, int velocities) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= numShake) return;
+    const int4 at = shakeAtoms[t]; const float4 dd = shakeDist[t];
+    const int idx[4] = {at.x, at.y, at.z, at.w};
+    const float dist[3] = {dd.x, dd.y, dd.z};
+    const int n = at.w >= 0 ? 4 : at.z >= 0 ? 3 : 2;
+    V3 p[4], v[4], d[4]; double im[4];
+    for (int k = 0; k < n; k++) { p[k] = loadPosD(a, idx[k]); const double4 vm = a.velm[idx[k]]; v[k] = {vm.x, vm.y, vm.z}; im[k] = vm.w; d[k] = {0, 0, 0}; }
+    if (velocities) {
+        shakeVelocities(n, p, v, im, tol, a.dt > 0 ? a.dt : 0.001);
+        for (int k = 0; k < n; k++) a.velm[idx[k]] = make_double4(v[k].x, v[k].y, v[k].z, im[k]);
+    } else {
+        shakePositions(n, p, d, im, dist, tol);
+        for (int k = 0; k < n; k++) storePosD(a, idx[k], p[k] + d[k]);
+    }
+}
+
 // ---- centre-of-mass motion removal (platforms/common/src/kernels/removeCM.cc)
 __global__ void __launch_bounds__(256) cmMomentum(const double4* __restrict__ velm, int N, DevCounters* counters, int slot) {
     double px = 0, py = 0, pz = 0;
@@ -352,7 +456,7 @@ extern "C" int b200_integrate(b200_ctx* c) {
         CUDA_CHECK(cudaSetDevice(c->device));
         b200_peer_sync_state(c);
         b200_finalize(c);
-        if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
+        if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints that are neither rigid 3-site molecules (SETTLE) nor SHAKE clusters are not implemented");
         b200_integrate_step(c);            // the caller (CMMotionRemover's own kernel) decides when COM motion is removed
         c->stepCount++; c->timePs += c->integ.dt; c->stepsSinceReorder++;
         c->forcesValid = false;
@@ -385,29 +489,35 @@ void b200_integrate_step(b200_ctx* c) {
         langevinMiddleStep<false><<<(units + 127) / 128, 128, 0, s>>>(a, c->numSettle, c->settleAtoms, c->settleParams, c->numFree, c->freeAtoms);
         LAUNCH_COUNT(c, 1);
     }
+    if (c->numShake > 0) {
+        langevinMiddleShake<<<(c->numShake + 127) / 128, 128, 0, s>>>(a, c->numShake, c->shakeAtoms, c->shakeDist, c->integ.constraint_tol > 0 ? c->integ.constraint_tol : 1e-5);
+        LAUNCH_COUNT(c, 1);
+    }
     CUDA_CHECK(cudaGetLastError());
 }
 
-extern "C" int b200_apply_constraints(b200_ctx* c, double) {
+extern "C" int b200_apply_constraints(b200_ctx* c, double tol) {
     try {
         CUDA_CHECK(cudaSetDevice(c->device));
         b200_peer_sync_state(c);
         b200_finalize(c);
-        if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
+        if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints that are neither rigid 3-site molecules (SETTLE) nor SHAKE clusters are not implemented");
         if (c->numSettle > 0) { settleOnly<<<(c->numSettle + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, 0); LAUNCH_COUNT(c, 1); }
+        if (c->numShake > 0) { shakeOnly<<<(c->numShake + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numShake, c->shakeAtoms, c->shakeDist, tol > 0 ? tol : 1e-5, 0); LAUNCH_COUNT(c, 1); }
         CUDA_CHECK(cudaStreamSynchronize(c->stream));
         c->stepsSinceReorder = -1; c->dispChecked = false; c->listVerified = false; c->forcesValid = false;
     } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
     return B200_OK;
 }
-extern "C" int b200_apply_velocity_constraints(b200_ctx* c, double) {
+extern "C" int b200_apply_velocity_constraints(b200_ctx* c, double tol) {
     try {
         CUDA_CHECK(cudaSetDevice(c->device));
         b200_peer_sync_state(c);
         b200_finalize(c);
         b200_flush_cm(c);
-        if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints other than rigid 3-site molecules (SETTLE) are not implemented yet");
+        if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints that are neither rigid 3-site molecules (SETTLE) nor SHAKE clusters are not implemented");
         if (c->numSettle > 0) { settleOnly<<<(c->numSettle + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, 1); LAUNCH_COUNT(c, 1); }
+        if (c->numShake > 0) { shakeOnly<<<(c->numShake + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numShake, c->shakeAtoms, c->shakeDist, tol > 0 ? tol : 1e-5, 1); LAUNCH_COUNT(c, 1); }
         c->cmValid = false;
         CUDA_CHECK(cudaStreamSynchronize(c->stream));
     } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }

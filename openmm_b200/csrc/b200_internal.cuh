@@ -138,6 +138,7 @@ struct b200_ctx {
     std::vector<int> conAtoms; std::vector<double> conDist;
     int numSettle = 0; int4* settleAtoms = nullptr; float2* settleParams = nullptr;  // (a0,a1,a2,-), (dist01, dist12)
     int numFree = 0; int* freeAtoms = nullptr;      // unconstrained, mobile atoms
+    int numShake = 0; int4* shakeAtoms = nullptr; float4* shakeDist = nullptr;   // SHAKE clusters: (central, up to three partners or -1), their distances
     double totalMassCached = 0;
     std::vector<int> hSettleAtoms, hFreeAtoms;      // host copies (4 ints per cluster), used to plan the multi-GPU integration slices
     int numOtherConstraints = 0;
@@ -191,6 +192,7 @@ struct b200_ctx {
     // PME: mesh[0] = Coulomb, mesh[1] = dispersion (LJPME only)
     PmeMesh mesh[2];
     bool ljpme = false;
+    double2* ewaldS = nullptr; int ewaldNumK = 0;   // NonbondedForce::Ewald: structure factors of the k vectors
     double ljSelfEnergy = 0;        // + alpha_d^6/12 * sum c6_i^2 (ReferenceLJCoulombIxn.cpp:224-227)
 
     // bonded
@@ -245,6 +247,7 @@ void b200_pme_create(b200_ctx* c);
 void b200_pme_destroy(b200_ctx* c);
 void b200_pme_rescale(b200_ctx* c);
 void b200_pme_launch(b200_ctx* c, cudaStream_t s, bool forces, bool energy);
+void b200_ewald_launch(b200_ctx* c, cudaStream_t s, bool forces, bool energy);   // NonbondedForce::Ewald reciprocal sum (b200_ewald.cu)
 void b200_bonded_upload(b200_ctx* c);
 void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy);
 void b200_integrate_setup(b200_ctx* c);

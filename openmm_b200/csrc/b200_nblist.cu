@@ -347,16 +347,21 @@ void b200_nblist_prepare(b200_ctx* c) {
     ScopedTimer tm(c, B200_T_NBLIST, c->stream);
     const float maxDisp = 0.5f * (float)c->padding;
     const int grid = c->smCount * 4;
+    // NoCutoff / CutoffNonPeriodic: no periodic images -- the builder sees a cell so large that no displacement is ever wrapped
+    BoxF nbBox = c->boxF;
+    if (c->nb.method == B200_NB_NOCUTOFF || c->nb.method == B200_NB_CUTOFF_NONPERIODIC) {
+        nbBox.ax = nbBox.by = nbBox.cz = 1.0e18f; nbBox.bx = nbBox.cx = nbBox.cy = 0.f; nbBox.iax = nbBox.iby = nbBox.icz = 1.0e-18f; nbBox.triclinic = 0;
+    }
     if (!c->dispChecked) { nbCheckDisplacement<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, maxDisp * maxDisp, c->counters); LAUNCH_COUNT(c, 1); }
-    nbBlockBounds<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, c->B, c->boxF, c->blockCenter, c->blockHalf, c->counters);
-    nbSuperBounds<<<(c->numSuper + 7) / 8, 256, 0, c->stream>>>(c->blockCenter, c->blockHalf, c->B, c->numSuper, c->boxF, c->superCenter, c->superHalf, c->counters);
+    nbBlockBounds<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, c->B, nbBox, c->blockCenter, c->blockHalf, c->counters);
+    nbSuperBounds<<<(c->numSuper + 7) / 8, 256, 0, c->stream>>>(c->blockCenter, c->blockHalf, c->B, c->numSuper, nbBox, c->superCenter, c->superHalf, c->counters);
     const float rcp = (float)c->paddedCutoff;
     int owned = 0;
     for (int i = 0; i < 64; i++) owned += c->partTable.owner[i] == c->partRank ? 1 : 0;
     int rows = (int)(((long long)c->B * owned + 63) / 64) + 1;
     int buildGrid = (rows + NB_WARPS - 1) / NB_WARPS;
     if (buildGrid > c->smCount * 16) buildGrid = c->smCount * 16;
-    nbBuild<<<buildGrid, NB_THREADS, 0, c->stream>>>(c->posq, c->N, c->B, c->numSuper, c->boxF, rcp * rcp, c->sparseMax,
+    nbBuild<<<buildGrid, NB_THREADS, 0, c->stream>>>(c->posq, c->N, c->B, c->numSuper, nbBox, rcp * rcp, c->sparseMax,
         c->blockCenter, c->blockHalf, c->superCenter, c->superHalf, c->exclRowStart, c->exclRowCols,
         c->units, c->jAtoms, (unsigned)c->unitCapacity, (unsigned)c->tileCapacity, c->partRank, c->partTable, c->counters);
     nbFinish<<<1, 1, 0, c->stream>>>(c->counters);

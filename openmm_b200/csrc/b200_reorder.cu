@@ -35,7 +35,7 @@ __device__ __forceinline__ unsigned hilbertIndex3(unsigned x, unsigned y, unsign
 
 // wrap each molecule into the box (ComputeContext.cpp:605-636) and compute its bucket
 __global__ void molWrapAndKey(int numMols, int atomsPerMol, const int* __restrict__ molBase, float4* posq, float4* posqCorr, int4* cellOffsets,
-                              BoxD box, int bits, int* __restrict__ keys, int* __restrict__ count) {
+                              BoxD box, int bits, int* __restrict__ keys, int* __restrict__ count, int wrap) {
     const int m = blockIdx.x * blockDim.x + threadIdx.x;
     if (m >= numMols) return;
     const int base = molBase[m];
@@ -46,10 +46,11 @@ __global__ void molWrapAndKey(int numMols, int atomsPerMol, const int* __restric
     }
     const double inv = 1.0 / atomsPerMol;
     cx *= inv; cy *= inv; cz *= inv;
+    // (the centre is always reduced into the cell for the sort key; the atoms themselves move only in periodic systems)
     const int sz = (int)floor(cz * box.icz); cx -= sz * box.cx; cy -= sz * box.cy; cz -= sz * box.cz;
     const int sy = (int)floor(cy * box.iby); cx -= sy * box.bx; cy -= sy * box.by;
     const int sx = (int)floor(cx * box.iax); cx -= sx * box.ax;
-    if (sx != 0 || sy != 0 || sz != 0) {
+    if (wrap && (sx != 0 || sy != 0 || sz != 0)) {
         const double tx = sx * box.ax + sy * box.bx + sz * box.cx, ty = sy * box.by + sz * box.cy, tz = sz * box.cz;
         for (int k = 0; k < atomsPerMol; k++) {
             const float4 p = posq[base + k], q = posqCorr[base + k];
@@ -147,7 +148,8 @@ void b200_reorder(b200_ctx* c) {
         const int nb = c->sortBuckets;
         const int grid = (g.numMols + 255) / 256;
         CUDA_CHECK(cudaMemsetAsync(c->sortCount, 0, sizeof(int) * (size_t)nb, s));
-        molWrapAndKey<<<grid, 256, 0, s>>>(g.numMols, g.atomsPerMol, g.dBase, c->posq, c->posqCorr, c->cellOffsets, c->boxD, c->sortBits, c->sortKeys, c->sortCount);
+        molWrapAndKey<<<grid, 256, 0, s>>>(g.numMols, g.atomsPerMol, g.dBase, c->posq, c->posqCorr, c->cellOffsets, c->boxD, c->sortBits, c->sortKeys, c->sortCount,
+                                          (c->hasNonbonded && (c->nb.method == B200_NB_NOCUTOFF || c->nb.method == B200_NB_CUTOFF_NONPERIODIC)) ? 0 : 1);
         LAUNCH_COUNT(c, 1);
         if (g.numMols < 2) continue;   // unique molecules are only wrapped into the box
         const int nblk = (nb + SCAN_BLOCK - 1) / SCAN_BLOCK;

@@ -54,6 +54,8 @@ struct TileArgs {
     float switchDist, switchInvWidth;   // LJMODE 2: switching distance, 1/(cutoff - switching distance)
     float ljAlpha2, invCut6, ljShift;   // LJPME: alpha_d^2, rc^-6, rc^-6 (1 - exp(-x)(1 + x + x^2/2)) at x = (alpha_d rc)^2
     int periodic;
+    int coulombMode;                    // 0 Ewald direct space (erfc), 1 reaction field (CutoffPeriodic / CutoffNonPeriodic), 2 plain Coulomb (NoCutoff)
+    float krf, crf;                     // reaction field constants (ReferenceLJCoulombIxn.cpp:70-80)
 };
 
 __device__ __forceinline__ float fast_rsqrt(float x) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
@@ -82,6 +84,12 @@ __device__ __forceinline__ void pairTerms(const TileArgs& a, float r2, float qq,
             vd = fmaf(vd, t, V_D1); vd = fmaf(vd, t, 1.0f);
             ec = qq * fmaf(-a.alpha, vn / vd, invR);
         }
+    } else if (a.coulombMode == 1) {   // reaction field (coulombLennardJones.cc, USE_CUTOFF branch)
+        sc = qq * fmaf(-2.0f * a.krf, 1.0f, invR * invR2);
+        if (ENERGY) ec = qq * (invR + a.krf * r2 - a.crf);
+    } else if (a.coulombMode == 2) {   // no cutoff: plain Coulomb
+        sc = qq * invR * invR2;
+        if (ENERGY) ec = qq * invR;
     } else {   // alpha*rc beyond the range of the fit: libm-quality erfc/exp
         const float r = r2 * invR;
         const float ar = a.alpha * r;
@@ -93,37 +101,37 @@ __device__ __forceinline__ void pairTerms(const TileArgs& a, float r2, float qq,
     const float sr2 = sig * sig * invR2;
     const float sr6 = sr2 * sr2 * sr2;
     const float es6 = eps * sr6;
-    if (LJMODE == 2) {
-        // Lennard-Jones switching function (coulombLennardJones.cc USE_LJ_SWITCH, ReferenceLJCoulombIxn.cpp:385-390,436-439):
-        // S(t) = 1 - 10 t^3 + 15 t^4 - 6 t^5 on t = (r - r_switch)/(r_cut - r_switch); force = S * F_lj - E_lj * S'(r) / r
-        float sLj = es6 * invR2 * fmaf(12.0f, sr6, -6.0f), eLj = es6 * (sr6 - 1.0f);
+    // LJMODE bits: 1 = LJPME (damped multiplicative r^-6 term + potential shift), 2 = switching function.  With both, the order of
+    // the Reference platform is kept (ReferenceLJCoulombIxn.cpp:385-440): the switch value scales the plain LJ force, the LJPME terms
+    // are added, then the switch derivative acts on the whole van der Waals energy and the switch value scales that energy.
+    float sLj = es6 * invR2 * fmaf(12.0f, sr6, -6.0f), eLj = es6 * (sr6 - 1.0f);
+    float sv = 1.0f, sd = 0.0f;
+    if (LJMODE & 2) {
+        // S(t) = 1 - 10 t^3 + 15 t^4 - 6 t^5 on t = (r - r_switch)/(r_cut - r_switch)   (coulombLennardJones.cc USE_LJ_SWITCH)
         const float r = r2 * invR;
         if (r > a.switchDist) {
             const float t = (r - a.switchDist) * a.switchInvWidth;
-            const float sv = fmaf(t * t * t, fmaf(t, fmaf(t, -6.0f, 15.0f), -10.0f), 1.0f);
-            const float sd = t * t * fmaf(t, fmaf(t, -30.0f, 60.0f), -30.0f) * a.switchInvWidth;
-            sLj = fmaf(sv, sLj, -eLj * sd * invR);
-            eLj *= sv;
+            sv = fmaf(t * t * t, fmaf(t, fmaf(t, -6.0f, 15.0f), -10.0f), 1.0f);
+            sd = t * t * fmaf(t, fmaf(t, -30.0f, 60.0f), -30.0f) * a.switchInvWidth;
         }
-        s = sc + sLj;
-        if (ENERGY) e = ec + eLj;
-        return;
+        sLj *= sv;
     }
-    s = fmaf(es6 * invR2, fmaf(12.0f, sr6, -6.0f), sc);
-    if (ENERGY) e = fmaf(es6, sr6 - 1.0f, ec);
-    if (LJMODE == 1) {
+    if (LJMODE & 1) {
         const float dar2 = a.ljAlpha2 * r2, dar4 = dar2 * dar2;
         const float ex = __expf(-dar2);
         const float c6 = 64.0f * sprod * sprod * sprod * eps;
         const float coef = c6 * invR2 * invR2 * invR2;
         const float epre = 1.0f + dar2 + 0.5f * dar4;
         const float dpre = fmaf(dar4 * dar2, 1.0f / 6.0f, epre);
-        s = fmaf(6.0f * coef * invR2, fmaf(-ex, dpre, 1.0f), s);
-        if (ENERGY) {
+        sLj = fmaf(6.0f * coef * invR2, fmaf(-ex, dpre, 1.0f), sLj);
+        if (ENERGY || (LJMODE & 2)) {
             const float sg2 = sig * sig, sc6 = sg2 * sg2 * sg2 * a.invCut6;
-            e += coef * fmaf(-ex, epre, 1.0f) + eps * (1.0f - sc6) * sc6 - c6 * a.ljShift;
+            eLj += coef * fmaf(-ex, epre, 1.0f) + eps * (1.0f - sc6) * sc6 - c6 * a.ljShift;
         }
     }
+    if (LJMODE & 2) { sLj = fmaf(-eLj * sd, invR, sLj); eLj *= sv; }
+    s = sc + sLj;
+    if (ENERGY) e = ec + eLj;
 }
 
 // FP64 decision for pairs that fall within rounding distance of the cutoff (rare)
@@ -374,7 +382,7 @@ _Pragma(TILE_STR(unroll TILE_UNROLL))
 template <bool FORCES, bool ENERGY, bool EMIT, bool EXACT, int LJMODE>
 __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(const TileArgs a) {
     __shared__ WarpSmem smAll[TILE_WARPS];
-    constexpr bool PACKED = !EMIT && !EXACT && LJMODE != 2;   // (the switching-function variant uses the scalar loop)   // FFMA2 path for the single-periodic-copy force/energy variants
+    constexpr bool PACKED = !EMIT && !EXACT && !(LJMODE & 2);   // (the switching-function variant uses the scalar loop)   // FFMA2 path for the single-periodic-copy force/energy variants
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem& sm = smAll[warp];
     const unsigned numExclUnits = (unsigned)(a.exclEnd - a.exclBegin);
@@ -587,7 +595,16 @@ void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
     a.alpha = (float)al; a.alpha2 = (float)(al * al); a.alpha3 = (float)(al * al * al);
     a.kcoul = (float)B200_ONE_4PI_EPS0;
     a.borderTol = (float)(3e-5 * rc * rc);
-    a.periodic = 1;
+    // NoCutoff / CutoffNonPeriodic: no periodic images; NoCutoff: every non-excluded pair interacts
+    const int method = c->nb.method;
+    a.periodic = (method == B200_NB_NOCUTOFF || method == B200_NB_CUTOFF_NONPERIODIC) ? 0 : 1;
+    a.coulombMode = method == B200_NB_NOCUTOFF ? 2 : (method == B200_NB_CUTOFF_NONPERIODIC || method == B200_NB_CUTOFF_PERIODIC) ? 1 : 0;
+    a.krf = a.crf = 0.f;
+    if (a.coulombMode == 1) {
+        const double eps = c->nb.reaction_field_dielectric;
+        a.krf = (float)(pow(rc, -3.0) * (eps - 1.0) / (2.0 * eps + 1.0)); a.crf = (float)((1.0 / rc) * 3.0 * eps / (2.0 * eps + 1.0));
+    }
+    if (method == B200_NB_NOCUTOFF) { a.rc2 = INFINITY; a.rc2d = INFINITY; a.rcPadded = INFINITY; a.borderTol = 0.f; }
     resetWorkQueue<<<1, 1, 0, c->stream>>>(c->counters);
     ScopedTimer tm(c, B200_T_TILE, c->stream);
     a.ljAlpha2 = a.invCut6 = a.ljShift = 0.f;
@@ -598,7 +615,8 @@ void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
     }
     a.switchDist = 0.f; a.switchInvWidth = 0.f;
     if (c->nb.use_switch) { a.switchDist = (float)c->nb.switch_distance; a.switchInvWidth = (float)(1.0 / (rc - c->nb.switch_distance)); }
-    if (c->ljpme) { if (c->exactEwald) launchTile<true, 1>(c, a, forces, energy, emitPairs); else launchTile<false, 1>(c, a, forces, energy, emitPairs); }
+    if (c->ljpme && c->nb.use_switch) launchTile<true, 3>(c, a, forces, energy, emitPairs);   // (scalar loop either way; one instantiation)
+    else if (c->ljpme) { if (c->exactEwald) launchTile<true, 1>(c, a, forces, energy, emitPairs); else launchTile<false, 1>(c, a, forces, energy, emitPairs); }
     else if (c->nb.use_switch) { if (c->exactEwald) launchTile<true, 2>(c, a, forces, energy, emitPairs); else launchTile<false, 2>(c, a, forces, energy, emitPairs); }
     else if (c->exactEwald) launchTile<true, 0>(c, a, forces, energy, emitPairs);
     else launchTile<false, 0>(c, a, forces, energy, emitPairs);

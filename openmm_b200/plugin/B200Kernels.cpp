@@ -124,27 +124,41 @@ struct B200CalcNonbondedForceKernel::Params {
     b200_nonbonded_desc desc;
 };
 
-void B200CalcNonbondedForceKernel::gather(const System& system, const NonbondedForce& force, Params& p) const {
-    if (force.getNumParticleParameterOffsets() > 0 || force.getNumExceptionParameterOffsets() > 0)
-        throw OpenMMException("The B200 platform does not support NonbondedForce parameter offsets yet");
-    if (force.getUseSwitchingFunction() && force.getNonbondedMethod() == NonbondedForce::LJPME)
-        throw OpenMMException("The B200 platform does not support the NonbondedForce switching function together with LJPME yet");
-    if (force.getNonbondedMethod() != NonbondedForce::PME && force.getNonbondedMethod() != NonbondedForce::LJPME)
-        throw OpenMMException("The B200 platform implements NonbondedForce with the PME and LJPME methods only");
+// Effective parameters = base parameters + sum over offsets of scale * (current value of the global parameter)
+// (NonbondedForce::addParticleParameterOffset / addExceptionParameterOffset; CommonCalcNonbondedForce.cpp:653-704 and the
+// computeParameters kernel nonbondedParameters.cc:1-76 do this on the device; here it is a host loop that runs only when a
+// global parameter actually changed).
+void B200CalcNonbondedForceKernel::gather(const System& system, const NonbondedForce& force, Params& p, const map<string, double>& globals) const {
     const int n = force.getNumParticles();
     p.q.resize(n); p.sigma.resize(n); p.eps.resize(n);
     for (int i = 0; i < n; i++) force.getParticleParameters(i, p.q[i], p.sigma[i], p.eps[i]);
-    // exceptions split as CommonCalcNonbondedForce.cpp:239-250: all of them are exclusions, those with parameters are 1-4 pairs
-    for (int i = 0; i < force.getNumExceptions(); i++) {
-        int a, b; double qq, s, e;
-        force.getExceptionParameters(i, a, b, qq, s, e);
-        p.exclusions.push_back(a); p.exclusions.push_back(b);
-        if (qq != 0.0 || e != 0.0) { p.exceptions.push_back(a); p.exceptions.push_back(b); p.excQQ.push_back(qq); p.excSigma.push_back(s); p.excEps.push_back(e); }
+    auto value = [&](const string& name) { auto it = globals.find(name); if (it == globals.end()) throw OpenMMException("NonbondedForce: unknown global parameter '" + name + "'"); return it->second; };
+    for (int i = 0; i < force.getNumParticleParameterOffsets(); i++) {
+        string name; int particle; double cq, cs, ce;
+        force.getParticleParameterOffset(i, name, particle, cq, cs, ce);
+        const double v = value(name);
+        p.q[particle] += cq * v; p.sigma[particle] += cs * v; p.eps[particle] += ce * v;
+    }
+    // exceptions split as CommonCalcNonbondedForce.cpp:239-250: all of them are exclusions; those with parameters (or with an
+    // offset that can give them parameters later) are 1-4 pairs
+    const int ne = force.getNumExceptions();
+    vector<double> xq(ne), xs(ne), xe(ne); vector<int> xa(ne), xb(ne); vector<char> hasOffset(ne, 0);
+    for (int i = 0; i < ne; i++) force.getExceptionParameters(i, xa[i], xb[i], xq[i], xs[i], xe[i]);
+    for (int i = 0; i < force.getNumExceptionParameterOffsets(); i++) {
+        string name; int exception; double cq, cs, ce;
+        force.getExceptionParameterOffset(i, name, exception, cq, cs, ce);
+        const double v = value(name);
+        xq[exception] += cq * v; xs[exception] += cs * v; xe[exception] += ce * v; hasOffset[exception] = 1;
+    }
+    for (int i = 0; i < ne; i++) {
+        p.exclusions.push_back(xa[i]); p.exclusions.push_back(xb[i]);
+        if (xq[i] != 0.0 || xe[i] != 0.0 || hasOffset[i]) { p.exceptions.push_back(xa[i]); p.exceptions.push_back(xb[i]); p.excQQ.push_back(xq[i]); p.excSigma.push_back(xs[i]); p.excEps.push_back(xe[i]); }
     }
     b200_nonbonded_desc& dd = p.desc;
     memset(&dd, 0, sizeof(dd));
-    const bool ljpme = force.getNonbondedMethod() == NonbondedForce::LJPME;
-    dd.method = ljpme ? B200_NB_LJPME : B200_NB_PME;
+    const NonbondedForce::NonbondedMethod method = force.getNonbondedMethod();
+    dd.method = (int)method;     // the B200_NB_* values are NonbondedForce::NonbondedMethod's
+    const bool ljpme = method == NonbondedForce::LJPME;
     if (ljpme) {   // CommonCalcNonbondedForce.cpp:380-396: dispersion mesh from calcPMEParameters(lj = true), rounded to a legal FFT size
         int lx, ly, lz;
         NonbondedForceImpl::calcPMEParameters(system, force, dd.ljpme_alpha, lx, ly, lz, true);
@@ -153,10 +167,20 @@ void B200CalcNonbondedForceKernel::gather(const System& system, const NonbondedF
     dd.cutoff = force.getCutoffDistance();
     dd.use_switch = force.getUseSwitchingFunction() ? 1 : 0;
     dd.switch_distance = force.getSwitchingDistance();
-    int nx, ny, nz;
-    NonbondedForceImpl::calcPMEParameters(system, force, dd.ewald_alpha, nx, ny, nz, false);
-    dd.grid[0] = b200_find_legal_fft_dimension(max(nx, 6)); dd.grid[1] = b200_find_legal_fft_dimension(max(ny, 6)); dd.grid[2] = b200_find_legal_fft_dimension(max(nz, 6));
-    dd.dispersion_coefficient = force.getUseDispersionCorrection() && !ljpme ? NonbondedForceImpl::calcDispersionCorrection(system, force) : 0.0;
+    dd.reaction_field_dielectric = force.getReactionFieldDielectric();
+    if (method == NonbondedForce::PME || ljpme) {
+        int nx, ny, nz;
+        NonbondedForceImpl::calcPMEParameters(system, force, dd.ewald_alpha, nx, ny, nz, false);
+        dd.grid[0] = b200_find_legal_fft_dimension(max(nx, 6)); dd.grid[1] = b200_find_legal_fft_dimension(max(ny, 6)); dd.grid[2] = b200_find_legal_fft_dimension(max(nz, 6));
+    }
+    else if (method == NonbondedForce::Ewald) {
+        int kx, ky, kz;
+        NonbondedForceImpl::calcEwaldParameters(system, force, dd.ewald_alpha, kx, ky, kz);     // CommonCalcNonbondedForce.cpp:333-343
+        dd.ewald_kmax[0] = kx; dd.ewald_kmax[1] = ky; dd.ewald_kmax[2] = kz;
+    }
+    // long-range correction only with a periodic cutoff method and never with LJPME (CommonCalcNonbondedForce.cpp:305-312)
+    const bool periodic = method == NonbondedForce::CutoffPeriodic || method == NonbondedForce::Ewald || method == NonbondedForce::PME;
+    dd.dispersion_coefficient = force.getUseDispersionCorrection() && periodic ? NonbondedForceImpl::calcDispersionCorrection(system, force) : 0.0;
     dd.charge = p.q.data(); dd.sigma = p.sigma.data(); dd.epsilon = p.eps.data();
     dd.num_exclusions = (int)p.exclusions.size() / 2; dd.exclusion_pairs = p.exclusions.data();
     dd.num_exceptions = (int)p.excQQ.size(); dd.exception_pairs = p.exceptions.data();
@@ -165,12 +189,21 @@ void B200CalcNonbondedForceKernel::gather(const System& system, const NonbondedF
 }
 
 void B200CalcNonbondedForceKernel::initialize(const System& system, const NonbondedForce& force) {
+    forceRef = &force; systemRef = &system;      // both outlive the kernel (they belong to the user's System)
+    hasOffsets = force.getNumParticleParameterOffsets() > 0 || force.getNumExceptionParameterOffsets() > 0;
+    globals.clear();
+    for (int i = 0; i < force.getNumGlobalParameters(); i++) globals[force.getGlobalParameterName(i)] = force.getGlobalParameterDefaultValue(i);
     Params p;
-    gather(system, force, p);
+    gather(system, force, p, globals);
     check(b200_nonbonded_create(d.ctx, &p.desc));
 }
 
-double B200CalcNonbondedForceKernel::execute(ContextImpl&, bool, bool, bool includeDirect, bool includeReciprocal) {
+double B200CalcNonbondedForceKernel::execute(ContextImpl& context, bool, bool, bool includeDirect, bool includeReciprocal) {
+    if (hasOffsets) {   // a global parameter that moved since the last evaluation changes the effective parameters
+        bool changed = false;
+        for (auto& g : globals) { const double v = context.getParameter(g.first); if (v != g.second) { g.second = v; changed = true; } }
+        if (changed) { Params p; gather(*systemRef, *forceRef, p, globals); check(b200_nonbonded_update_parameters(d.ctx, &p.desc)); }
+    }
     if (includeDirect) d.pendingGroups |= B200_GROUP_DIRECT;
     if (includeReciprocal) d.pendingGroups |= B200_GROUP_RECIPROCAL;
     return 0.0;   // the energy of this force is returned by CalcForcesAndEnergyKernel::finishComputation
@@ -178,7 +211,8 @@ double B200CalcNonbondedForceKernel::execute(ContextImpl&, bool, bool, bool incl
 
 void B200CalcNonbondedForceKernel::copyParametersToContext(ContextImpl& context, const NonbondedForce& force, int, int, int, int) {
     Params p;
-    gather(context.getSystem(), force, p);
+    for (auto& g : globals) g.second = context.getParameter(g.first);
+    gather(context.getSystem(), force, p, globals);
     check(b200_nonbonded_update_parameters(d.ctx, &p.desc));
 }
 

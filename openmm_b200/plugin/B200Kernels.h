@@ -2,6 +2,8 @@
 #pragma once
 #include "B200Platform.h"
 #include "openmm/kernels.h"
+#include <map>
+#include <string>
 
 namespace B200Plugin {
 using OpenMM::ContextImpl; using OpenMM::Platform; using OpenMM::System; using OpenMM::Vec3;
@@ -82,8 +84,11 @@ public:
     void getLJPMEParameters(double& alpha, int& nx, int& ny, int& nz) const override;
 private:
     struct Params;
-    void gather(const System& system, const OpenMM::NonbondedForce& force, Params& p) const;
+    void gather(const System& system, const OpenMM::NonbondedForce& force, Params& p, const std::map<std::string, double>& globals) const;
     PData& d;
+    const OpenMM::NonbondedForce* forceRef = nullptr; const System* systemRef = nullptr;
+    bool hasOffsets = false;
+    std::map<std::string, double> globals;      // global parameters of the force and the values the device parameters were computed with
 };
 
 // kernels.h:334-366, 408-440, 482-514

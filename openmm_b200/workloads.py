@@ -179,7 +179,8 @@ def cached_water_box(n_atoms, ljpme=False):
     return sysd
 
 
-def make_context(sysd, cutoff=0.9, tol=5e-4, device=0, grid=None, alpha=None, ljpme=False, lj_alpha=None, lj_grid=None, switch_distance=None, **kw):
+def make_context(sysd, cutoff=0.9, tol=5e-4, device=0, grid=None, alpha=None, ljpme=False, lj_alpha=None, lj_grid=None, switch_distance=None,
+                 method=None, ewald_kmax=None, reaction_field_dielectric=78.3, dispersion_coefficient=0.0, **kw):
     """Create an openmm_b200.Context for a water_box() system with the reference's default PME settings."""
     import openmm_b200 as b
     a, g = b.pme_parameters(cutoff, sysd["box"], tol)
@@ -188,8 +189,10 @@ def make_context(sysd, cutoff=0.9, tol=5e-4, device=0, grid=None, alpha=None, lj
     ctx = b.Context(sysd["mass"], sysd["box"], constraints=sysd.get("constraints"), device=device, **kw)
     if ljpme and lj_alpha is None:
         lj_alpha, lj_grid = b.pme_parameters(cutoff, sysd["box"], tol, lj=True)
+    extra = {} if method is None else dict(method=method)
     ctx.add_nonbonded_force(sysd["charge"], sysd["sigma"], sysd["epsilon"], cutoff, alpha, grid, exclusions=sysd["exclusions"],
-                            exceptions=sysd.get("exceptions"), lj_alpha=lj_alpha, lj_grid=lj_grid, switch_distance=switch_distance)
+                            exceptions=sysd.get("exceptions"), lj_alpha=lj_alpha, lj_grid=lj_grid, switch_distance=switch_distance,
+                            ewald_kmax=ewald_kmax, reaction_field_dielectric=reaction_field_dielectric, dispersion_coefficient=dispersion_coefficient, **extra)
     ctx.lj_pme = (lj_alpha, lj_grid)
     ctx.pme = (alpha, grid)
     return ctx
