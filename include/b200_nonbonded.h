@@ -151,6 +151,9 @@ int  b200_remove_cm_motion(b200_ctx* ctx);                           /* RemoveCM
 int  b200_apply_constraints(b200_ctx* ctx, double tol);              /* ApplyConstraintsKernel::apply */
 int  b200_apply_velocity_constraints(b200_ctx* ctx, double tol);     /* ApplyConstraintsKernel::applyToVelocities */
 int  b200_kinetic_energy(b200_ctx* ctx, double* ke);                 /* IntegrateLangevinMiddleStepKernel::computeKineticEnergy */
+/* kinetic energy of v + shift*F/m (forces of the last b200_compute) after the velocity constraints: what leapfrog integrators report,
+   IntegrateVerletStepKernel::computeKineticEnergy -> IntegrationUtilities::computeKineticEnergy(0.5*dt) (CommonKernels.cpp:3117) */
+int  b200_kinetic_energy_shifted(b200_ctx* ctx, double shift_ps, double* ke);
 int  b200_synchronize(b200_ctx* ctx);
 
 /* ---- parity probes (no counterpart kernel in the reference; they expose what its tests measure) */

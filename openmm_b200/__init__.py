@@ -65,7 +65,7 @@ EXPORTED_SYMBOLS = [
     "b200_set_velocities", "b200_get_velocities", "b200_get_forces", "b200_set_box", "b200_get_box", "b200_set_time",
     "b200_get_time", "b200_compute", "b200_compute_host", "b200_integrator_create", "b200_step", "b200_integrate",
     "b200_remove_cm_motion", "b200_apply_constraints",
-    "b200_apply_velocity_constraints", "b200_kinetic_energy", "b200_synchronize", "b200_direct_pairs", "b200_direct_pairs_hash", "b200_nblist_get_stats",
+    "b200_apply_velocity_constraints", "b200_kinetic_energy", "b200_kinetic_energy_shifted", "b200_synchronize", "b200_direct_pairs", "b200_direct_pairs_hash", "b200_nblist_get_stats",
     "b200_fft3d_r2c_host", "b200_fft3d_c2r_host", "b200_fft3d_c2r_noalloc", "b200_find_legal_fft_dimension", "b200_timing_enable", "b200_timing_read",
     "b200_timing_reset", "b200_timed_steps", "b200_launch_count", "b200_nccl_unique_id", "b200_comm_init", "b200_set_partition",
 ]
@@ -305,6 +305,12 @@ class Context:
     def kinetic_energy(self):
         e = ctypes.c_double(0.0)
         _check(self.lib.b200_kinetic_energy(self.handle, ctypes.byref(e)))
+        return e.value
+
+    def kinetic_energy_shifted(self, shift_ps):
+        """kinetic energy of v + shift*F/m with the forces of the last compute() (leapfrog integrators: shift = dt/2)"""
+        e = ctypes.c_double(0.0)
+        _check(self.lib.b200_kinetic_energy_shifted(self.handle, ctypes.c_double(shift_ps), ctypes.byref(e)))
         return e.value
 
     def apply_constraints(self, tol=1e-5):

@@ -537,4 +537,38 @@ extern "C" int b200_kinetic_energy(b200_ctx* c, double* ke) {
     } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
     return B200_OK;
 }
+// Kinetic energy of velocities shifted in time by `shift` with the forces in the buffer, v + shift * F/m, after the velocity
+// constraints: what a leapfrog integrator reports (IntegrationUtilities::computeKineticEnergy(0.5 * dt), CommonKernels.cpp:3117,
+// called by IntegrateVerletStepKernel::computeKineticEnergy), because its stored velocities lag the positions by half a step.
+__global__ void shiftVelocities(double4* velm, const long long* __restrict__ force, int N, int Npad, double shift) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    double4 v = velm[i];
+    const double sc = shift * v.w / B200_FORCE_SCALE;
+    v.x += sc * (double)force[i]; v.y += sc * (double)force[i + Npad]; v.z += sc * (double)force[i + 2 * (size_t)Npad];
+    velm[i] = v;
+}
+extern "C" int b200_kinetic_energy_shifted(b200_ctx* c, double shift, double* ke) {
+    try {
+        if (shift == 0.0) return b200_kinetic_energy(c, ke);
+        CUDA_CHECK(cudaSetDevice(c->device));
+        b200_peer_sync_state(c);
+        b200_finalize(c);
+        b200_flush_cm(c);
+        cudaStream_t s = c->stream;
+        CUDA_CHECK(cudaMemcpyAsync(c->velmTmp, c->velm, sizeof(double4) * c->Npad, cudaMemcpyDeviceToDevice, s));
+        shiftVelocities<<<(c->N + 255) / 256, 256, 0, s>>>(c->velm, c->force, c->N, c->Npad, shift);
+        const double tol = c->hasIntegrator && c->integ.constraint_tol > 0 ? c->integ.constraint_tol : 1e-5;
+        if (c->numSettle > 0) settleOnly<<<(c->numSettle + 127) / 128, 128, 0, s>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, 1);
+        if (c->numShake > 0) shakeOnly<<<(c->numShake + 127) / 128, 128, 0, s>>>(makeArgs(c), c->numShake, c->shakeAtoms, c->shakeDist, tol, 1);
+        keZero<<<1, 1, 0, s>>>(c->counters);
+        kineticEnergy<<<c->smCount * 2, 256, 0, s>>>(c->velm, c->N, c->counters);
+        CUDA_CHECK(cudaMemcpyAsync(c->velm, c->velmTmp, sizeof(double4) * c->Npad, cudaMemcpyDeviceToDevice, s));
+        LAUNCH_COUNT(c, 5);
+        CUDA_CHECK(cudaMemcpyAsync(c->countersHost, c->counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaStreamSynchronize(s));
+        *ke = (double)c->countersHost->energy[E_KINETIC] * (1024.0 / B200_ENERGY_SCALE);
+    } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
+    return B200_OK;
+}
 void b200_integrate_setup(b200_ctx*) {}

@@ -65,7 +65,8 @@ void B200UpdateStateDataKernel::setVelocities(ContextImpl&, const vector<Vec3>& 
     check(b200_set_velocities(d.ctx, asDoubles(velocities)));
 }
 void B200UpdateStateDataKernel::computeShiftedVelocities(ContextImpl& context, double timeShift, vector<Vec3>& velocities) {
-    // v(t + shift) ~ v + shift * F/m with the forces currently in the buffer (IntegrationUtilities::computeShiftedVelocities)
+    // v(t + shift) ~ v + shift * F/m with the forces currently in the buffer (IntegrationUtilities::computeShiftedVelocities;
+    // unlike the kinetic-energy path above this host-side variant does not re-apply the velocity constraints)
     getVelocities(context, velocities);
     if (timeShift == 0.0) return;
     vector<Vec3> forces;
@@ -275,8 +276,11 @@ void B200IntegrateVerletStepKernel::execute(ContextImpl&, const VerletIntegrator
     check(b200_integrator_create(d.ctx, &desc));
     check(b200_integrate(d.ctx));
 }
-double B200IntegrateVerletStepKernel::computeKineticEnergy(ContextImpl&, const VerletIntegrator&) {
-    double ke; check(b200_kinetic_energy(d.ctx, &ke)); return ke;
+double B200IntegrateVerletStepKernel::computeKineticEnergy(ContextImpl& context, const VerletIntegrator& integrator) {
+    // leapfrog: the stored velocities are half a step behind the positions; report the energy of velocities shifted forward by dt/2
+    // with the current forces and constrained again (CommonKernels.cpp:3117 -> IntegrationUtilities::computeKineticEnergy)
+    context.calcForcesAndEnergy(true, false, integrator.getIntegrationForceGroups());
+    double ke; check(b200_kinetic_energy_shifted(d.ctx, 0.5 * integrator.getStepSize(), &ke)); return ke;
 }
 
 }  // namespace B200Plugin

@@ -207,12 +207,17 @@ def test_verlet_limit_conserves_energy():
     ctx.set_integrator(dt=0.002, temperature=300.0, friction=5.0, seed=1)
     ctx.step(200)            # equilibrate the synthetic start with a thermostat first
     ctx.set_integrator(dt=0.001, temperature=0.0, friction=0.0, seed=1, remove_cm_every=0)
-    tot = []
+    # the stored velocities lag the positions by half a step; the kinetic energy that belongs to the positions is that of velocities
+    # shifted by dt/2 with the current forces (what IntegrateVerletStepKernel::computeKineticEnergy reports).  With the unshifted
+    # velocities the sum fluctuates by ~20 kJ/mol (first order in dt; measured), which would hide a drift.
+    tot, raw = [], []
     for _ in range(8):
         ctx.step(50)
-        tot.append(ctx.compute(forces=False) + ctx.kinetic_energy())
+        pe = ctx.compute()
+        tot.append(pe + ctx.kinetic_energy_shifted(0.0005)); raw.append(pe + ctx.kinetic_energy())
     tot = np.array(tot)
-    assert np.abs(tot - tot[0]).max() < 2e-4 * abs(tot[0]), tot
+    print("total energy, shifted KE:", tot - tot[0], " unshifted:", np.array(raw) - raw[0])
+    assert np.abs(tot - tot[0]).max() < 1e-4 * abs(tot[0]), tot
     ctx.close()
 
 
@@ -302,10 +307,10 @@ def test_shake_clusters_hold_their_constraints_and_conserve_energy():
     tot = []
     for _ in range(6):
         ctx.step(50)
-        tot.append(ctx.compute(forces=False) + ctx.kinetic_energy())
+        tot.append(ctx.compute() + ctx.kinetic_energy_shifted(0.0005))
     tot = np.array(tot)
     scale = abs(ctx.kinetic_energy())
-    assert np.abs(tot - tot[0]).max() < 5e-3 * scale, tot
+    assert np.abs(tot - tot[0]).max() < 2e-3 * scale, tot
     # ApplyConstraintsKernel::apply on perturbed coordinates
     ctx.set_positions(ctx.get_positions() + rng.normal(scale=0.002, size=p.shape))
     ctx.apply_constraints(1e-7)
