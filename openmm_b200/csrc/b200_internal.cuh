@@ -8,7 +8,9 @@
 #include "../../include/b200_nonbonded.h"
 
 #define B200_TILE 32
+#ifndef B200_UNIT_TILES
 #define B200_UNIT_TILES 8            // tiles per work unit (fixed: the float partial-sum grouping must not depend on #GPUs)
+#endif
 #define B200_ONE_4PI_EPS0 138.93545764438198
 #define B200_FORCE_SCALE 4294967296.0   // 2^32, platforms/cuda/src/kernels/common.cu:29-31
 #define B200_ENERGY_SCALE 4294967296.0
