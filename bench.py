@@ -303,6 +303,8 @@ def main():
     fam = ctx.timing_read()
     ctx.timing_enable(False)
     if os.environ.get("B200_BENCH_VERBOSE"):
+        singles = [ctx.timed_steps(1) for _ in range(24)]      # step-by-step times: shows rebuild steps and any one-off stall
+        sys.stderr.write(f"[rank {rank}] single steps (ms): " + " ".join(f"{x:.2f}" for x in singles) + "\n")
         sys.stderr.write(f"[rank {rank}] ms/step {ms_per_step:.4f} | " + " ".join(f"{k}={v[0] / prof_steps * 1e3:.0f}us" for k, v in fam.items() if v[0] > 0) + "\n")
         if dist is not None:   # raw NCCL all-reduce of a force-sized int64 buffer, for comparison with the library's own collective
             buf = torch.zeros(3 * (((n + 31) // 32) * 32), dtype=torch.int64, device="cuda")

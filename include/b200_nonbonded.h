@@ -156,6 +156,14 @@ int  b200_kinetic_energy(b200_ctx* ctx, double* ke);                 /* Integrat
 int  b200_kinetic_energy_shifted(b200_ctx* ctx, double shift_ps, double* ke);
 int  b200_synchronize(b200_ctx* ctx);
 
+/* ---- Monte Carlo barostat: ApplyMonteCarloBarostatKernel (kernels.h:1723-1788; CommonKernels.cpp:4255-4400, monteCarloBarostat.cc).
+ *      save: keep the state for a possible rejection; scale: move every molecule (rigid_molecules != 0) or every atom so that its centre
+ *      r goes to (sx x + sxy y + sxz z, sy y + syz z, sz z), scale6 = {sx, sy, sz, sxy, sxz, syz}; restore: undo a rejected move.
+ *      The box itself is changed with b200_set_box (the PME reciprocal vectors and the neighbour list follow on the next evaluation). */
+int  b200_barostat_save(b200_ctx* ctx);
+int  b200_barostat_scale(b200_ctx* ctx, const double* scale6, int32_t rigid_molecules);
+int  b200_barostat_restore(b200_ctx* ctx);
+
 /* ---- parity probes (no counterpart kernel in the reference; they expose what its tests measure) */
 /* Set of unordered atom pairs (original indices, i<j) that the direct-space kernel treats as interacting
  * (r < cutoff, not excluded).  Mirrors what computeNeighborListVoxelHash yields (ReferenceNeighborList.cpp:208-214).

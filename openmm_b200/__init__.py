@@ -65,7 +65,7 @@ EXPORTED_SYMBOLS = [
     "b200_set_velocities", "b200_get_velocities", "b200_get_forces", "b200_set_box", "b200_get_box", "b200_set_time",
     "b200_get_time", "b200_compute", "b200_compute_host", "b200_integrator_create", "b200_step", "b200_integrate",
     "b200_remove_cm_motion", "b200_apply_constraints",
-    "b200_apply_velocity_constraints", "b200_kinetic_energy", "b200_kinetic_energy_shifted", "b200_synchronize", "b200_direct_pairs", "b200_direct_pairs_hash", "b200_nblist_get_stats",
+    "b200_apply_velocity_constraints", "b200_kinetic_energy", "b200_kinetic_energy_shifted", "b200_synchronize", "b200_barostat_save", "b200_barostat_scale", "b200_barostat_restore", "b200_direct_pairs", "b200_direct_pairs_hash", "b200_nblist_get_stats",
     "b200_fft3d_r2c_host", "b200_fft3d_c2r_host", "b200_fft3d_c2r_noalloc", "b200_find_legal_fft_dimension", "b200_timing_enable", "b200_timing_read",
     "b200_timing_reset", "b200_timed_steps", "b200_launch_count", "b200_nccl_unique_id", "b200_comm_init", "b200_set_partition",
 ]
@@ -318,6 +318,17 @@ class Context:
 
     def apply_velocity_constraints(self, tol=1e-5):
         _check(self.lib.b200_apply_velocity_constraints(self.handle, ctypes.c_double(tol)))
+
+    # ApplyMonteCarloBarostatKernel
+    def barostat_save(self):
+        _check(self.lib.b200_barostat_save(self.handle))
+
+    def barostat_scale(self, sx, sy, sz, sxy=0.0, sxz=0.0, syz=0.0, rigid_molecules=True):
+        a = (ctypes.c_double * 6)(sx, sy, sz, sxy, sxz, syz)
+        _check(self.lib.b200_barostat_scale(self.handle, a, 1 if rigid_molecules else 0))
+
+    def barostat_restore(self):
+        _check(self.lib.b200_barostat_restore(self.handle))
 
     def synchronize(self):
         _check(self.lib.b200_synchronize(self.handle))

@@ -125,6 +125,7 @@ extern "C" void b200_context_destroy(b200_ctx* c) {
     dfree(c->settleAtoms); dfree(c->settleParams); dfree(c->freeAtoms); dfree(c->shakeAtoms); dfree(c->shakeDist);
     dfree(c->exclTiles); dfree(c->exclFlags); dfree(c->exclRowStart); dfree(c->exclRowCols); dfree(c->dExclPairs); dfree(c->dExcPairs); dfree(c->dExcParams);
     dfree(c->bondAtoms); dfree(c->bondParams); dfree(c->angleAtoms); dfree(c->angleParams); dfree(c->torsionAtoms); dfree(c->torsionParams);
+    dfree(c->molStart); dfree(c->molSlots); dfree(c->savedPosq); dfree(c->savedPosqCorr); dfree(c->savedVelm); dfree(c->savedAtomIndex); dfree(c->savedCellOffsets);
     dfree(c->ewaldS); dfree(c->sortKeys); dfree(c->sortCount); dfree(c->sortStart); dfree(c->sortOrder);
     for (auto& g : c->groups) dfree(g.dBase);
     if (c->countersHost) cudaFreeHost(c->countersHost);
@@ -355,6 +356,14 @@ void b200_finalize(b200_ctx* c) {
         }
     }
     c->numMolecules = (int)molAtoms.size();
+    {   // molecules as slot lists on the device (slot == particle index at creation; re-sorting only exchanges identical molecules)
+        std::vector<int> start(molAtoms.size() + 1, 0), slots; slots.reserve(N);
+        for (size_t m = 0; m < molAtoms.size(); m++) { start[m] = (int)slots.size(); slots.insert(slots.end(), molAtoms[m].begin(), molAtoms[m].end()); }
+        start[molAtoms.size()] = (int)slots.size();
+        dmalloc(c->molStart, start.size()); dmalloc(c->molSlots, slots.size());
+        CUDA_CHECK(cudaMemcpy(c->molStart, start.data(), sizeof(int) * start.size(), cudaMemcpyHostToDevice));
+        CUDA_CHECK(cudaMemcpy(c->molSlots, slots.data(), sizeof(int) * slots.size(), cudaMemcpyHostToDevice));
+    }
     c->molBaseOf.resize(N);
     for (int i = 0; i < N; i++) c->molBaseOf[i] = molAtoms[molOf[i]][0];
     // ---- signature of each molecule: everything that must match for two molecules to be exchangeable
@@ -752,6 +761,85 @@ extern "C" int b200_set_time(b200_ctx* c, double t, int64_t steps) {
     API_END
 }
 extern "C" int b200_get_time(const b200_ctx* c, double* t, int64_t* steps) { if (t) *t = c->timePs; if (steps) *steps = c->stepCount; return B200_OK; }
+
+// ---------------------------------------------------------------------------------------------
+// Monte Carlo barostat support: ApplyMonteCarloBarostatKernel (kernels.h:1723-1788; CommonKernels.cpp:4255-4400, monteCarloBarostat.cc)
+// One thread per molecule: centre = plain average of the atom positions, displaced by the upper-triangular deformation; all atoms of
+// the molecule move by the same vector (rigid molecules) or every atom is its own "molecule".
+__global__ void barostatScale(int numMols, const int* __restrict__ molStart, const int* __restrict__ molSlots, int perAtom, int N,
+                              float4* posq, float4* posqCorr, double sx, double sy, double sz, double sxy, double sxz, double syz) {
+    const int m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= (perAtom ? N : numMols)) return;
+    const int first = perAtom ? m : molStart[m], last = perAtom ? m + 1 : molStart[m + 1];
+    double cx = 0, cy = 0, cz = 0;
+    for (int k = first; k < last; k++) {
+        const int s = perAtom ? k : molSlots[k];
+        const float4 p = posq[s], q = posqCorr[s];
+        cx += (double)p.x + q.x; cy += (double)p.y + q.y; cz += (double)p.z + q.z;
+    }
+    const double inv = 1.0 / (last - first);
+    cx *= inv; cy *= inv; cz *= inv;
+    const double dx = cx * (sx - 1.0) + cy * sxy + cz * sxz, dy = cy * (sy - 1.0) + cz * syz, dz = cz * (sz - 1.0);
+    for (int k = first; k < last; k++) {
+        const int s = perAtom ? k : molSlots[k];
+        const float4 p = posq[s], q = posqCorr[s];
+        const double x = (double)p.x + q.x + dx, y = (double)p.y + q.y + dy, z = (double)p.z + q.z + dz;
+        posq[s] = make_float4((float)x, (float)y, (float)z, p.w);
+        posqCorr[s] = make_float4((float)(x - (double)(float)x), (float)(y - (double)(float)y), (float)(z - (double)(float)z), 0.f);
+    }
+}
+
+static void invalidateAfterMove(b200_ctx* c) {
+    c->forcesValid = false; c->dispChecked = false; c->listVerified = false;
+    c->stepsSinceReorder = -1;      // the next evaluation re-sorts and rebuilds the list
+}
+
+extern "C" int b200_barostat_save(b200_ctx* c) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    b200_peer_sync_state(c);
+    const size_t P = c->Npad;
+    if (!c->savedPosq) { dmalloc(c->savedPosq, P); dmalloc(c->savedPosqCorr, P); dmalloc(c->savedVelm, P); dmalloc(c->savedAtomIndex, P); dmalloc(c->savedCellOffsets, P); }
+    cudaStream_t s = c->stream;
+    CUDA_CHECK(cudaMemcpyAsync(c->savedPosq, c->posq, sizeof(float4) * P, cudaMemcpyDeviceToDevice, s));
+    CUDA_CHECK(cudaMemcpyAsync(c->savedPosqCorr, c->posqCorr, sizeof(float4) * P, cudaMemcpyDeviceToDevice, s));
+    CUDA_CHECK(cudaMemcpyAsync(c->savedVelm, c->velm, sizeof(double4) * P, cudaMemcpyDeviceToDevice, s));
+    CUDA_CHECK(cudaMemcpyAsync(c->savedAtomIndex, c->atomIndex, sizeof(int) * P, cudaMemcpyDeviceToDevice, s));
+    CUDA_CHECK(cudaMemcpyAsync(c->savedCellOffsets, c->cellOffsets, sizeof(int4) * P, cudaMemcpyDeviceToDevice, s));
+    c->savedValid = true; c->savedStepsSinceReorder = c->stepsSinceReorder;
+    API_END
+}
+
+extern "C" int b200_barostat_scale(b200_ctx* c, const double* scale6, int32_t rigidMolecules) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    if (!c->positionsSet) throw B200Error(B200_ERR_INVALID, "Particle positions have not been set");
+    b200_finalize(c);
+    b200_peer_sync_state(c);
+    const int n = rigidMolecules ? c->numMolecules : c->N;
+    barostatScale<<<(n + 127) / 128, 128, 0, c->stream>>>(c->numMolecules, c->molStart, c->molSlots, rigidMolecules ? 0 : 1, c->N, c->posq, c->posqCorr,
+                                                         scale6[0], scale6[1], scale6[2], scale6[3], scale6[4], scale6[5]);
+    LAUNCH_COUNT(c, 1);
+    CUDA_CHECK(cudaGetLastError());
+    invalidateAfterMove(c);
+    API_END
+}
+
+extern "C" int b200_barostat_restore(b200_ctx* c) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    if (!c->savedValid) throw B200Error(B200_ERR_INVALID, "b200_barostat_restore: nothing was saved");
+    const size_t P = c->Npad;
+    cudaStream_t s = c->stream;
+    CUDA_CHECK(cudaMemcpyAsync(c->posq, c->savedPosq, sizeof(float4) * P, cudaMemcpyDeviceToDevice, s));
+    CUDA_CHECK(cudaMemcpyAsync(c->posqCorr, c->savedPosqCorr, sizeof(float4) * P, cudaMemcpyDeviceToDevice, s));
+    CUDA_CHECK(cudaMemcpyAsync(c->velm, c->savedVelm, sizeof(double4) * P, cudaMemcpyDeviceToDevice, s));
+    CUDA_CHECK(cudaMemcpyAsync(c->atomIndex, c->savedAtomIndex, sizeof(int) * P, cudaMemcpyDeviceToDevice, s));
+    CUDA_CHECK(cudaMemcpyAsync(c->cellOffsets, c->savedCellOffsets, sizeof(int4) * P, cudaMemcpyDeviceToDevice, s));
+    c->hostOrderStale = true;
+    invalidateAfterMove(c);
+    API_END
+}
 
 // ---------------------------------------------------------------------------------------------
 // force evaluation

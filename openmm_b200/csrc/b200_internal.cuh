@@ -153,6 +153,11 @@ struct b200_ctx {
     std::vector<int> molBaseOf;     // particle -> first particle of its molecule (creation order), for re-checking group homogeneity
     int* sortKeys = nullptr; int* sortCount = nullptr; int* sortStart = nullptr; int* sortOrder = nullptr; int sortBuckets = 0; int sortBits = 0;
     int maxGroupMols = 0;
+    // every molecule as a list of slots (CSR), for the Monte Carlo barostat's rigid-molecule scaling
+    int* molStart = nullptr; int* molSlots = nullptr;
+    // state saved by b200_barostat_save (rejected Monte Carlo move): positions, remainders, velocities, order, wrap counters
+    float4* savedPosq = nullptr; float4* savedPosqCorr = nullptr; double4* savedVelm = nullptr; int* savedAtomIndex = nullptr; int4* savedCellOffsets = nullptr;
+    bool savedValid = false; int64_t savedStepsSinceReorder = 0;
     int reorderInterval = 250;
     int64_t stepsSinceReorder = 0;
 

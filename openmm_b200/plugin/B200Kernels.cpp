@@ -258,6 +258,34 @@ void B200CalcPeriodicTorsionForceKernel::copyParametersToContext(ContextImpl&, c
     throw OpenMMException("The B200 platform does not support updateParametersInContext for PeriodicTorsionForce yet");
 }
 
+// ---------------------------------------------------------------------------------------------- Monte Carlo barostat
+void B200ApplyMonteCarloBarostatKernel::initialize(const System& system, const Force&, int comps, bool rigidMolecules) {
+    components = comps; rigid = rigidMolecules; numParticles = system.getNumParticles();
+    masses.resize(numParticles);
+    for (int i = 0; i < numParticles; i++) masses[i] = system.getParticleMass(i);
+}
+void B200ApplyMonteCarloBarostatKernel::computeKineticEnergy(ContextImpl& context, vector<double>& ke) {
+    // kinetic energy of the molecular centres of mass (rigid molecules) or of all particles, split as monteCarloBarostat.cc does:
+    // 1 component = total, 3 = per axis, 6 = all elements of the box tensor.  A cold path (instantaneous pressure): done on the host.
+    vector<double> v(3 * (size_t)numParticles);
+    check(b200_get_velocities(d.ctx, v.data()));
+    vector<vector<int> > molecules;
+    if (rigid) molecules = context.getMolecules();
+    else { molecules.resize(numParticles); for (int i = 0; i < numParticles; i++) molecules[i].push_back(i); }
+    ke.assign(components, 0.0);
+    for (const auto& mol : molecules) {
+        double m = 0, p[3] = {0, 0, 0};
+        for (int a : mol) { m += masses[a]; for (int k = 0; k < 3; k++) p[k] += masses[a] * v[3 * (size_t)a + k]; }
+        if (m == 0) continue;
+        const double vx = p[0] / m, vy = p[1] / m, vz = p[2] / m;
+        if (components == 1) ke[0] += 0.5 * m * (vx * vx + vy * vy + vz * vz);
+        else {
+            ke[0] += 0.5 * m * vx * vx; ke[1] += 0.5 * m * vy * vy; ke[2] += 0.5 * m * vz * vz;
+            if (components == 6) { ke[3] += 0.5 * m * vx * vy; ke[4] += 0.5 * m * vx * vz; ke[5] += 0.5 * m * vy * vz; }
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------- integrators
 void B200IntegrateLangevinMiddleStepKernel::initialize(const System&, const LangevinMiddleIntegrator& integrator) {
     int s = integrator.getRandomNumberSeed();

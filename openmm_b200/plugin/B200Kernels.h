@@ -130,6 +130,24 @@ private:
     PData& d;
 };
 
+// kernels.h:1723-1788 (MonteCarloBarostat: the Monte Carlo logic lives in MonteCarloBarostatImpl, the platform moves the molecules)
+class B200ApplyMonteCarloBarostatKernel : public OpenMM::ApplyMonteCarloBarostatKernel {
+public:
+    B200ApplyMonteCarloBarostatKernel(std::string name, const Platform& platform, PData& d) : ApplyMonteCarloBarostatKernel(name, platform), d(d) {}
+    void initialize(const System& system, const OpenMM::Force& barostat, int components, bool rigidMolecules = true) override;
+    void saveCoordinates(ContextImpl& context) override { check(b200_barostat_save(d.ctx)); }
+    void scaleCoordinates(ContextImpl& context, double scaleX, double scaleY, double scaleZ, double scaleXY = 0, double scaleXZ = 0, double scaleYZ = 0) override {
+        const double s[6] = {scaleX, scaleY, scaleZ, scaleXY, scaleXZ, scaleYZ};
+        check(b200_barostat_scale(d.ctx, s, rigid ? 1 : 0));
+    }
+    void restoreCoordinates(ContextImpl& context) override { check(b200_barostat_restore(d.ctx)); }
+    void computeKineticEnergy(ContextImpl& context, std::vector<double>& ke) override;
+private:
+    PData& d;
+    int components = 1; bool rigid = true; int numParticles = 0;
+    std::vector<double> masses;
+};
+
 // kernels.h:1392-1420
 class B200IntegrateLangevinMiddleStepKernel : public OpenMM::IntegrateLangevinMiddleStepKernel {
 public:

@@ -24,7 +24,8 @@ B200Platform::B200Platform() {
     for (const string& name : {CalcForcesAndEnergyKernel::Name(), UpdateStateDataKernel::Name(), ApplyConstraintsKernel::Name(),
                                VirtualSitesKernel::Name(), MinimizeKernel::Name(), CalcNonbondedForceKernel::Name(),
                                CalcHarmonicBondForceKernel::Name(), CalcHarmonicAngleForceKernel::Name(), CalcPeriodicTorsionForceKernel::Name(),
-                               RemoveCMMotionKernel::Name(), IntegrateLangevinMiddleStepKernel::Name(), IntegrateVerletStepKernel::Name()})
+                               RemoveCMMotionKernel::Name(), IntegrateLangevinMiddleStepKernel::Name(), IntegrateVerletStepKernel::Name(),
+                               ApplyMonteCarloBarostatKernel::Name()})
         registerKernelFactory(name, factory);
     platformProperties.push_back(DeviceIndex());
     platformProperties.push_back(Precision());
@@ -121,6 +122,7 @@ KernelImpl* B200KernelFactory::createKernelImpl(string name, const Platform& pla
     if (name == RemoveCMMotionKernel::Name()) return new B200RemoveCMMotionKernel(name, platform, d);
     if (name == IntegrateLangevinMiddleStepKernel::Name()) return new B200IntegrateLangevinMiddleStepKernel(name, platform, d);
     if (name == IntegrateVerletStepKernel::Name()) return new B200IntegrateVerletStepKernel(name, platform, d);
+    if (name == ApplyMonteCarloBarostatKernel::Name()) return new B200ApplyMonteCarloBarostatKernel(name, platform, d);
     throw OpenMMException("Tried to create kernel with illegal kernel name '" + name + "'");
 }
 

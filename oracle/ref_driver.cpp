@@ -255,12 +255,47 @@ static int cmdCheckpoint(int argc, char** argv) {
     return 0;
 }
 
+// MonteCarloBarostat on a deterministic integrator (Verlet): the sequence of box volumes depends only on the barostat's own random
+// stream (seeded) and on the energies before/after each trial move, so two platforms that agree on energies produce the same sequence.
+static int cmdNpt(int argc, char** argv) {
+    string sysPath = argv[2], platformName = "Reference"; vector<string> plugins; int steps = 40, frequency = 2;
+    for (int i = 3; i < argc; i++) {
+        string a = argv[i];
+        if (a == "--platform") platformName = argv[++i]; else if (a == "--plugin") plugins.push_back(argv[++i]);
+        else if (a == "--steps") steps = atoi(argv[++i]); else if (a == "--frequency") frequency = atoi(argv[++i]);
+    }
+    SystemFile s = readSystem(sysPath);
+    Platform& platform = pickPlatform(platformName, plugins);
+    System* sys = buildSystem(s, false);
+    MonteCarloBarostat* baro = new MonteCarloBarostat(1.0, 300.0, frequency);
+    baro->setRandomNumberSeed(7);
+    sys->addForce(baro);
+    VerletIntegrator integ(0.001);
+    integ.setConstraintTolerance(1e-6);
+    Context ctx(*sys, integ, platform);
+    ctx.setPositions(toVec3(s.pos)); ctx.setVelocities(toVec3(s.vel));
+    ctx.applyConstraints(1e-6);
+    printf("{\"platform\": \"%s\", \"n\": %d, \"volumes\": [", platformName.c_str(), s.N);
+    for (int i = 0; i < steps; i += frequency) {
+        integ.step(frequency);
+        Vec3 a, b, c; ctx.getState(0).getPeriodicBoxVectors(a, b, c);
+        printf("%s%.12g", i ? ", " : "", a[0] * b[1] * c[2]);
+    }
+    State st = ctx.getState(State::Positions | State::Energy, false);   // unwrapped: comparable between platforms
+    double cx = 0, cy = 0, cz = 0;
+    for (auto& p : st.getPositions()) { cx += p[0]; cy += p[1]; cz += p[2]; }
+    printf("], \"potential_energy\": %.10g, \"position_sum\": [%.8g, %.8g, %.8g]}\n", st.getPotentialEnergy(), cx, cy, cz);
+    delete sys;
+    return 0;
+}
+
 int main(int argc, char** argv) {
     try {
         if (argc >= 4 && string(argv[1]) == "eval") return cmdEval(argc, argv);
         if (argc >= 3 && string(argv[1]) == "compare") return cmdCompare(argc, argv);
         if (argc >= 3 && string(argv[1]) == "bench") return cmdBench(argc, argv);
         if (argc >= 3 && string(argv[1]) == "checkpoint") return cmdCheckpoint(argc, argv);
+        if (argc >= 3 && string(argv[1]) == "npt") return cmdNpt(argc, argv);
         fprintf(stderr, "usage: ref_driver eval|compare|bench ...\n");
         return 2;
     } catch (const exception& e) {

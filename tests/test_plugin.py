@@ -102,3 +102,23 @@ def test_checkpoint_round_trip_through_the_plugin():
     print(r)
     assert r["time_restored"] and r["final_time_equal"]
     assert r["max_position_difference"] < 1e-5 and r["max_velocity_difference"] < 1e-3
+
+
+@pytest.mark.gpu
+def test_monte_carlo_barostat_through_the_plugin():
+    # MonteCarloBarostat (ApplyMonteCarloBarostatKernel: save / scale molecule centres / restore) with a Verlet integrator on the B200
+    # platform and on the reference's Reference platform: same barostat seed, so the accepted and rejected volume moves must follow
+    # the same sequence as long as the energies agree (tests/TestMonteCarloBarostat.h checks the ensemble; this checks the mechanics)
+    sysd = workloads.water_box(1536, seed=3)
+    alpha, grid = b.pme_parameters(0.9, sysd["box"])
+    with tempfile.TemporaryDirectory() as td:
+        sp = os.path.join(td, "s.bin")
+        workloads.write_system_file(sp, sysd, 0.9, alpha, grid)
+        g = _driver(["npt", sp, "--platform", "B200", "--plugin", b.PLUGIN_PATH, "--steps", "24", "--frequency", "2"])
+        r = _driver(["npt", sp, "--platform", "Reference", "--steps", "24", "--frequency", "2"])
+    print(g["volumes"], r["volumes"])
+    v0 = float(np.prod([sysd["box"][0], sysd["box"][4], sysd["box"][8]]))
+    assert any(abs(v - v0) / v0 > 1e-6 for v in r["volumes"]), "no volume move was accepted: the test would be vacuous"
+    assert np.allclose(g["volumes"], r["volumes"], rtol=1e-7)
+    assert abs(g["potential_energy"] - r["potential_energy"]) / abs(r["potential_energy"]) < 1e-4
+    assert np.allclose(g["position_sum"], r["position_sum"], atol=2e-2)
