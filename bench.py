@@ -355,13 +355,22 @@ def main():
     e2e_steps = max(1, min(args.e2e_steps, args.steps))
 
     def e2e_loop(pos, k):
+        # multi-rank: ONE rank owns the host buffers (as one OpenMM Context would); it uploads once over PCIe and the positions reach
+        # the other GPUs over NVLink (b200_set_positions_root), the download happens on that rank only
+        root_io = world > 1
         ctx.get_positions(enforce_periodic=True, out=pos)
         barrier()
         t0 = time.perf_counter()
         for _ in range(k):
-            ctx.set_positions(pos)
+            if root_io:
+                ctx.set_positions_root(pos if rank == 0 else None)
+            else:
+                ctx.set_positions(pos)
             ctx.step(1)
-            ctx.get_positions(enforce_periodic=True, out=pos)
+            if root_io and rank != 0:
+                ctx.join_get_positions()
+            else:
+                ctx.get_positions(enforce_periodic=True, out=pos)
         barrier()
         return (time.perf_counter() - t0) * 1e3 / k
 
@@ -375,8 +384,10 @@ def main():
     npad = ((n + 31) // 32) * 32
     e2e = {"value": ns_per_day(e2e_ms), "unit": "ns/day", "ms_per_step": e2e_ms, "h2d_bytes_per_step": 24 * n, "d2h_bytes_per_step": 24 * n,
            "ms_per_step_pageable_buffers": e2e_pageable_ms,
-           "api": "b200_set_positions(host doubles, page-locked caller buffer) + b200_step(1) + b200_get_positions(host doubles); permutation and "
-                  "precision split on the GPU; pageable caller buffers go through a chunk-pipelined pinned staging area"}
+           "api": ("b200_set_positions(host doubles, page-locked caller buffer) + b200_step(1) + b200_get_positions(host doubles); permutation and "
+                   "precision split on the GPU; pageable caller buffers go through a chunk-pipelined pinned staging area") if world == 1 else
+                  ("rank 0: b200_set_positions_root(host doubles) [PCIe once, NVLink to the other ranks] + b200_step(1) + b200_get_positions(host doubles); "
+                   "other ranks take part in the collectives without host buffers")}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

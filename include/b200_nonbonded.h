@@ -109,6 +109,10 @@ int  b200_periodic_torsions_create(b200_ctx* ctx, int32_t n, const int32_t* atom
 /* ---- state I/O: UpdateStateDataKernel (kernels.h:132-246; CommonKernels.cpp:95-297).
  *      Host arrays are [3N] doubles in the caller's (original) particle order. */
 int  b200_set_positions(b200_ctx* ctx, const double* xyz);
+/* multi-GPU, collective: rank 0 passes the host array, uploads it once over PCIe and stores the converted positions into every rank's
+ * arrays over NVLink; the other ranks pass NULL.  (The reference's multi-GPU path uploads to every device from the host thread,
+ * CudaParallelKernels.cpp:183-207.)  b200_get_positions(ctx, NULL, ...) lets a rank take part in the collective gather without a download. */
+int  b200_set_positions_root(b200_ctx* ctx, const double* xyz);
 int  b200_get_positions(b200_ctx* ctx, double* xyz, int32_t enforce_periodic);
 int  b200_set_velocities(b200_ctx* ctx, const double* xyz);
 int  b200_get_velocities(b200_ctx* ctx, double* xyz);

@@ -61,7 +61,7 @@ class NblistStats(ctypes.Structure):
 EXPORTED_SYMBOLS = [
     "b200_context_create", "b200_context_destroy", "b200_last_error", "b200_device_count", "b200_nonbonded_create",
     "b200_nonbonded_update_parameters", "b200_nonbonded_get_pme_parameters", "b200_nonbonded_get_ljpme_parameters", "b200_harmonic_bonds_create",
-    "b200_harmonic_angles_create", "b200_periodic_torsions_create", "b200_set_positions", "b200_get_positions",
+    "b200_harmonic_angles_create", "b200_periodic_torsions_create", "b200_set_positions", "b200_set_positions_root", "b200_get_positions",
     "b200_set_velocities", "b200_get_velocities", "b200_get_forces", "b200_set_box", "b200_get_box", "b200_set_time",
     "b200_get_time", "b200_compute", "b200_compute_host", "b200_integrator_create", "b200_step", "b200_integrate",
     "b200_remove_cm_motion", "b200_apply_constraints",
@@ -230,6 +230,18 @@ class Context:
         a, p = _d(np.asarray(xyz).reshape(-1))
         assert a.size == 3 * self.n
         _check(self.lib.b200_set_positions(self.handle, p))
+
+    def set_positions_root(self, xyz=None):
+        """collective over the ranks of a communicator: rank 0 passes the array, the others pass None (positions travel over NVLink)"""
+        if xyz is None:
+            _check(self.lib.b200_set_positions_root(self.handle, None))
+            return
+        a, p = _d(np.asarray(xyz).reshape(-1))
+        _check(self.lib.b200_set_positions_root(self.handle, p))
+
+    def join_get_positions(self):
+        """collective counterpart of get_positions() for ranks that do not need the host copy"""
+        _check(self.lib.b200_get_positions(self.handle, None, 0))
 
     def get_positions(self, enforce_periodic=False, out=None):
         if out is None:

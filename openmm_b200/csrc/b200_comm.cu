@@ -198,6 +198,19 @@ void b200_peer_publish_positions(b200_ctx* c) {
     if (c->shardAtomEnd > c->shardAtomBegin) { peerPublishPositions<<<c->smCount * 2, 256, 0, c->stream>>>(c->peers, c->shardAtomBegin, c->shardAtomEnd); LAUNCH_COUNT(c, 1); }
 }
 
+// rank 0's freshly set positions (float part + remainder) -> every other rank (b200_set_positions_root)
+__global__ void __launch_bounds__(256) peerBroadcastPositions(PeerSet p, int N) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+        const float4 v = p.posq[p.rank][i], q = p.posqCorr[p.rank][i];
+        for (int r = 0; r < p.n; r++) if (r != p.rank) { p.posq[r][i] = v; p.posqCorr[r][i] = q; }
+    }
+}
+void b200_peer_broadcast_positions(b200_ctx* c) {
+    ScopedTimer tm(c, B200_T_COMM, c->stream);
+    peerBroadcastPositions<<<c->smCount * 2, 256, 0, c->stream>>>(c->peers, c->N);
+    LAUNCH_COUNT(c, 1);
+}
+
 static void peerSetup(b200_ctx* c) {
     c->peerMode = false;
     const int R = c->commRanks;

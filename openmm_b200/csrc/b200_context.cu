@@ -72,7 +72,8 @@ extern "C" int b200_context_create(const b200_system_desc* desc, b200_ctx** out)
     CUDA_CHECK(cudaGetDeviceProperties(&prop, desc->device));
     if (prop.major < 10) throw B200Error(B200_ERR_UNSUPPORTED, "the B200 platform needs a compute capability 10.x device");
     b200_ctx* c = new b200_ctx();
-    *out = c;
+    *out = nullptr;
+    struct Guard { b200_ctx* c; ~Guard() { if (c) b200_context_destroy(c); } } guard{c};    // a failure below must not leak the half-built context
     c->device = desc->device; c->smCount = prop.multiProcessorCount;
     c->N = desc->num_atoms; c->Npad = ((c->N + 31) / 32) * 32; c->B = c->Npad / 32; c->numSuper = (c->B + 31) / 32;
     c->usePmeStream = !(desc->flags & B200_CTX_DISABLE_PME_STREAM);
@@ -109,6 +110,8 @@ extern "C" int b200_context_create(const b200_system_desc* desc, b200_ctx** out)
     c->hostSlotOf = c->hostAtomIndex;
     CUDA_CHECK(cudaMemcpyAsync(c->atomIndex, c->hostAtomIndex.data(), sizeof(int) * P, cudaMemcpyHostToDevice, c->stream));
     CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    guard.c = nullptr;
+    *out = c;
     API_END
 }
 
@@ -291,9 +294,16 @@ extern "C" int b200_nonbonded_update_parameters(b200_ctx* c, const b200_nonbonde
         }
     }
     if (c->finalized && c->numExceptions > 0) {
-        std::vector<float4> xq;
-        for (size_t i = 0; i < c->excQQ.size(); i++) xq.push_back(make_float4((float)(B200_ONE_4PI_EPS0 * c->excQQ[i]), (float)c->excSig[i], (float)(4.0 * c->excEps[i]), 0.f));
+        // An exception belongs to two PARTICLES; after a re-sort they sit in the slots hostSlotOf[] says (identical molecules were
+        // exchanged), so both the parameters and the slot pair are written: a parameter change that concerns one of several formerly
+        // identical molecules lands on the molecule it was meant for.
+        std::vector<float4> xq; std::vector<int2> xp;
+        for (size_t i = 0; i < c->excQQ.size(); i++) {
+            xq.push_back(make_float4((float)(B200_ONE_4PI_EPS0 * c->excQQ[i]), (float)c->excSig[i], (float)(4.0 * c->excEps[i]), 0.f));
+            xp.push_back(make_int2(c->hostSlotOf[c->excPairs[2 * i]], c->hostSlotOf[c->excPairs[2 * i + 1]]));
+        }
         CUDA_CHECK(cudaMemcpy(c->dExcParams, xq.data(), sizeof(float4) * xq.size(), cudaMemcpyHostToDevice));
+        CUDA_CHECK(cudaMemcpy(c->dExcPairs, xp.data(), sizeof(int2) * xp.size(), cudaMemcpyHostToDevice));
     }
     c->forcesValid = false;
     API_END
@@ -687,18 +697,48 @@ __global__ void ioGetForces(double* __restrict__ stage, const int* __restrict__ 
     stage[3 * (size_t)o] = sc * (double)force[s]; stage[3 * (size_t)o + 1] = sc * (double)force[s + Npad]; stage[3 * (size_t)o + 2] = sc * (double)force[s + 2 * (size_t)Npad];
 }
 
-extern "C" int b200_set_positions(b200_ctx* c, const double* xyz) {
-    API_BEGIN
-    CUDA_CHECK(cudaSetDevice(c->device));
-    stageIn(c, xyz);
-    ioSetPositions<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->posq, c->posqCorr, c->cellOffsets);
-    LAUNCH_COUNT(c, 1);
-    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+static void afterSetPositions(b200_ctx* c) {
     c->forcesValid = false; c->dispChecked = false; c->listVerified = false;
     // Like ComputeContext::reorderAtoms the spatial sort is periodic, not forced by every setPositions: the displacement
     // check against the last list build decides on the device whether the neighbour list must be rebuilt.
     if (!c->positionsSet) c->stepsSinceReorder = -1;
     c->positionsSet = true;
+}
+
+// Multi-GPU, collective: rank 0 uploads the host array over PCIe once and stores the converted positions into every rank's arrays
+// over NVLink; the other ranks (xyz ignored, may be NULL) only wait.  The device order is the same on every rank (the re-sort is
+// deterministic), so slots correspond.  Without peer mapping every rank needs the array itself (b200_set_positions).
+extern "C" int b200_set_positions_root(b200_ctx* c, const double* xyz) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    if (!(c->peerMode && c->commRanks > 1)) {
+        if (!xyz) throw B200Error(B200_ERR_INVALID, "b200_set_positions_root: without peer mapping every rank must pass the array");
+        return b200_set_positions(c, xyz);
+    }
+    if (c->commRank == 0) {
+        if (!xyz) throw B200Error(B200_ERR_INVALID, "b200_set_positions_root: rank 0 needs the host array");
+        stageIn(c, xyz);
+        ioSetPositions<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->posq, c->posqCorr, c->cellOffsets);
+        LAUNCH_COUNT(c, 1);
+        b200_peer_broadcast_positions(c);
+    } else {
+        CUDA_CHECK(cudaMemsetAsync(c->cellOffsets, 0, sizeof(int4) * (size_t)c->Npad, c->stream));
+    }
+    b200_peer_barrier(c, PEER_SLOT_STATE);
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    afterSetPositions(c);
+    API_END
+}
+
+extern "C" int b200_set_positions(b200_ctx* c, const double* xyz) {
+    API_BEGIN
+    CUDA_CHECK(cudaSetDevice(c->device));
+    if (!xyz) throw B200Error(B200_ERR_INVALID, "b200_set_positions: null array");
+    stageIn(c, xyz);
+    ioSetPositions<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->posq, c->posqCorr, c->cellOffsets);
+    LAUNCH_COUNT(c, 1);
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    afterSetPositions(c);
     API_END
 }
 
@@ -706,6 +746,10 @@ extern "C" int b200_get_positions(b200_ctx* c, double* xyz, int32_t enforcePerio
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
     b200_peer_sync_state(c);
+    if (!xyz) {     // multi-GPU: a rank that does not need the host copy still takes part in the collective gather above
+        if (c->commRanks > 1) { CUDA_CHECK(cudaStreamSynchronize(c->stream)); return B200_OK; }
+        throw B200Error(B200_ERR_INVALID, "b200_get_positions: null array");
+    }
     ensureStaging(c);
     ioGetPositions<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->posq, c->posqCorr, c->cellOffsets, c->boxD, enforcePeriodic ? 0 : 1);
     LAUNCH_COUNT(c, 1);
@@ -1018,6 +1062,7 @@ extern "C" int b200_step(b200_ctx* c, int32_t nsteps) {
     b200_finalize(c);
     if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints that are neither rigid 3-site molecules (SETTLE) nor clusters of one central atom with up to three singly-constrained partners (SHAKE) are not implemented");
     // peer-memory step: the momentum bookkeeping inside the integration kernel is what keeps the ranks' momenta in step
+    { static const bool fp = getenv("B200_FUSED_PUBLISH") != nullptr; c->fusedPublish = fp; }
     c->peerStepActive = c->peerMode && c->commRanks > 1 && c->integ.remove_cm_every <= 1 && c->hasNonbonded && c->numShake == 0;   // (SHAKE clusters are not sharded yet)
     if (c->peerStepActive) {
         b200_peer_plan_shard(c);
@@ -1045,7 +1090,7 @@ extern "C" int b200_step(b200_ctx* c, int32_t nsteps) {
         b200_integrate_step(c);
         mark(4);
         if (c->peerStepActive) {
-            if (c->shardContiguous) b200_peer_publish_positions(c);           // all-gather
+            if (c->shardContiguous && !c->fusedPublish) b200_peer_publish_positions(c);           // all-gather
             mark(5);
             b200_peer_barrier(c, PEER_SLOT_POSITIONS);                        // every rank's slice of new positions has arrived everywhere
         }

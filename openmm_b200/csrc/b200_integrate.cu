@@ -63,7 +63,7 @@ __device__ __forceinline__ void storePosD(const IntegArgs& a, int i, V3 p) {
     const float w = a.posq[i].w;
     const float4 np = make_float4((float)p.x, (float)p.y, (float)p.z, w);
     a.posq[i] = np;
-    if (PEER && a.usePeers == 1) for (int r = 0; r < a.peers.n; r++) if (r != a.peers.rank) a.peers.posq[r][i] = np;      // the all-gather (scattered form)
+    if (PEER && (a.usePeers & 1)) for (int r = 0; r < a.peers.n; r++) if (r != a.peers.rank) a.peers.posq[r][i] = np;      // the all-gather, written where the position is produced
     a.posqCorr[i] = make_float4((float)(p.x - (double)(float)p.x), (float)(p.y - (double)(float)p.y), (float)(p.z - (double)(float)p.z), 0.f);
 }
 template <bool PEER = false>
@@ -480,7 +480,9 @@ void b200_integrate_step(b200_ctx* c) {
     if (c->peerStepActive) {
         // a.usePeers = 1: per-atom loads/stores through peer memory; 2: the forces of this slice were already reduced into the local
         // array and the positions are published afterwards by range copies (slice = one contiguous range of slots)
-        a.usePeers = c->shardContiguous ? 2 : 1; a.peers = c->peers; a.unitBegin = c->shardBegin; a.unitEnd = c->shardEnd;
+        // usePeers bit 0: new positions are stored into every rank's posq by the integration kernel itself (fire-and-forget NVLink stores);
+        // bit 1: the forces of this slice were already reduced into the local array (contiguous slice)
+        a.usePeers = c->shardContiguous ? (c->fusedPublish ? 3 : 2) : 1; a.peers = c->peers; a.unitBegin = c->shardBegin; a.unitEnd = c->shardEnd;
         const int mine = c->shardEnd - c->shardBegin;
         langevinMiddleStep<true><<<std::max(1, (mine + 127) / 128), 128, 0, s>>>(a, c->numSettle, c->settleAtoms, c->settleParams, c->numFree, c->freeAtoms);
         LAUNCH_COUNT(c, 1);

@@ -188,6 +188,7 @@ struct b200_ctx {
 
     // fused reduce + integrate + gather over peer memory (b200_comm.cu, b200_integrate.cu)
     bool peerMode = false;          // IPC mappings established on every rank
+    bool fusedPublish = false;      // B200_FUSED_PUBLISH=1: the integration kernel stores the new positions to the peers itself
     bool peerStepActive = false;    // inside b200_step in peer mode: no NCCL all-reduce of the forces
     bool shardsDirty = false;       // velm / posqCorr are current only for this rank's shard of the integration units
     PeerSet peers;
@@ -268,6 +269,7 @@ void b200_peer_barrier(b200_ctx* c, int slot);        // signal + wait on the co
 void b200_peer_sync_state(b200_ctx* c);
 void b200_peer_plan_shard(b200_ctx* c);               // unit slice of this rank and whether its atoms are one contiguous slot range
 void b200_peer_reduce_forces(b200_ctx* c);            // sum of all ranks' partial forces for this rank's atom range -> local force array
+void b200_peer_broadcast_positions(b200_ctx* c);      // rank 0's whole posq / posqCorr -> every rank
 void b200_peer_publish_positions(b200_ctx* c);        // this rank's slice of posq -> every rank               // all-gather of the sharded velocities / position remainders (collective)
 void b200_fft_make_plan(int n, FFTPlan1D& plan);
 void b200_fft_make_twiddle(int n, float2*& dTw, cudaStream_t s);

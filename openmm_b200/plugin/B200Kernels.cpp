@@ -230,7 +230,17 @@ void B200CalcNonbondedForceKernel::getLJPMEParameters(double& alpha, int& nx, in
 }
 
 // ---------------------------------------------------------------------------------------------- bonded forces
+// All terms of one kind are evaluated together under one group bit.  Several forces of the same kind are fine as long as they share
+// a force group; different groups (per-force energy decomposition) or periodic bonded forces would silently give wrong answers,
+// so they are refused.
+static void checkBondedForce(B200Platform::PlatformData& d, int kind, const Force& force, bool periodic, const char* name) {
+    if (periodic) throw OpenMMException(string("The B200 platform does not support periodic boundary conditions for ") + name);
+    if (d.bondedGroup[kind] >= 0 && d.bondedGroup[kind] != force.getForceGroup())
+        throw OpenMMException(string("The B200 platform evaluates all ") + name + " objects of a System together: they must share one force group");
+    d.bondedGroup[kind] = force.getForceGroup();
+}
 void B200CalcHarmonicBondForceKernel::initialize(const System&, const HarmonicBondForce& force) {
+    checkBondedForce(d, 0, force, force.usesPeriodicBoundaryConditions(), "HarmonicBondForce");
     const int n = force.getNumBonds();
     vector<int> atoms(2 * (size_t)n); vector<double> len(n), k(n);
     for (int i = 0; i < n; i++) force.getBondParameters(i, atoms[2 * i], atoms[2 * i + 1], len[i], k[i]);
@@ -240,6 +250,7 @@ void B200CalcHarmonicBondForceKernel::copyParametersToContext(ContextImpl&, cons
     throw OpenMMException("The B200 platform does not support updateParametersInContext for HarmonicBondForce yet");
 }
 void B200CalcHarmonicAngleForceKernel::initialize(const System&, const HarmonicAngleForce& force) {
+    checkBondedForce(d, 1, force, force.usesPeriodicBoundaryConditions(), "HarmonicAngleForce");
     const int n = force.getNumAngles();
     vector<int> atoms(3 * (size_t)n); vector<double> ang(n), k(n);
     for (int i = 0; i < n; i++) force.getAngleParameters(i, atoms[3 * i], atoms[3 * i + 1], atoms[3 * i + 2], ang[i], k[i]);
@@ -249,6 +260,7 @@ void B200CalcHarmonicAngleForceKernel::copyParametersToContext(ContextImpl&, con
     throw OpenMMException("The B200 platform does not support updateParametersInContext for HarmonicAngleForce yet");
 }
 void B200CalcPeriodicTorsionForceKernel::initialize(const System&, const PeriodicTorsionForce& force) {
+    checkBondedForce(d, 2, force, force.usesPeriodicBoundaryConditions(), "PeriodicTorsionForce");
     const int n = force.getNumTorsions();
     vector<int> atoms(4 * (size_t)n), per(n); vector<double> phase(n), k(n);
     for (int i = 0; i < n; i++) force.getTorsionParameters(i, atoms[4 * i], atoms[4 * i + 1], atoms[4 * i + 2], atoms[4 * i + 3], per[i], phase[i], k[i]);

@@ -18,6 +18,7 @@ public:
         b200_ctx* ctx = nullptr;
         unsigned pendingGroups = 0;            // force groups requested by the ForceImpls between begin/finishComputation
         bool positionsValid = false;
+        int bondedGroup[3] = {-1, -1, -1};      // force group of the HarmonicBond / HarmonicAngle / PeriodicTorsion terms already added
         std::map<std::string, std::string> properties;
         ~PlatformData() { if (ctx) b200_context_destroy(ctx); }
     };
