@@ -205,7 +205,7 @@ def multi_rank_identity_check(sysd, rank, world, local, dist, torch, b, workload
     return bool(t.item())
 
 
-def plugin_records(sysd, alpha, grid, args, n):
+def plugin_records(sysd, alpha, grid, args, n, devices=None):
     """The same system through an unmodified OpenMM Context + LangevinMiddleIntegrator + CMMotionRemover (oracle/_ref/ref_driver):
     `plugin` = this repository's libOpenMMB200.so selected by name ("B200"), `reference_gpu` = the reference's own CUDA platform
     when oracle/_ref holds a build of it.  Wall-clock around integ.step(K) + one getState, as examples/benchmarks/benchmark.py:99-108."""
@@ -218,18 +218,20 @@ def plugin_records(sysd, alpha, grid, args, n):
         sp = os.path.join(td, "system.bin")
         workloads.write_system_file(sp, sysd, 0.9, alpha, grid)
         k, w = max(args.steps, 100), max(args.warmup, 20)
+        dev = [] if not devices else [("DeviceIndex", ",".join(str(x) for x in devices))]
         if os.path.exists(PLUGIN_PATH):
-            r = run_ref_driver(sysd, alpha, grid, k, w, "B200", system_file=sp, extra_plugins=[PLUGIN_PATH])
-            r2 = run_ref_driver(sysd, alpha, grid, max(5, min(args.e2e_steps, 20)), 3, "B200", e2e=True, system_file=sp, extra_plugins=[PLUGIN_PATH])
+            r = run_ref_driver(sysd, alpha, grid, k, w, "B200", system_file=sp, extra_plugins=[PLUGIN_PATH], props=dev)
+            r2 = run_ref_driver(sysd, alpha, grid, max(5, min(args.e2e_steps, 20)), 3, "B200", e2e=True, system_file=sp, extra_plugins=[PLUGIN_PATH], props=dev)
             if r is not None:
                 plugin = {"value": r["ns_per_day"], "unit": "ns/day", "ms_per_step": r["ms_per_step"], "steps": r["steps"],
-                          "api": "OpenMM::Context(system, LangevinMiddleIntegrator, Platform::getPlatformByName(\"B200\")); integrator.step(K)",
+                          "api": "OpenMM::Context(system, LangevinMiddleIntegrator, Platform::getPlatformByName(\"B200\")" +
+                                 (", {DeviceIndex=" + dev[0][1] + "}" if dev else "") + "); integrator.step(K)",
                           "e2e": None if r2 is None else {"value": r2["ns_per_day"], "unit": "ns/day", "ms_per_step": r2["ms_per_step"],
                                                            "h2d_bytes_per_step": 24 * n, "d2h_bytes_per_step": 24 * n,
                                                            "api": "per step: Context::setPositions(vector<Vec3>) + step(1) + getState(Positions)"}}
         cuda_lib = os.path.join(REF_PLUGINS, "libOpenMMCUDA.so")
         if os.path.exists(cuda_lib):
-            r = run_ref_driver(sysd, alpha, grid, k, w, "CUDA", system_file=sp, extra_plugins=[cuda_lib], props=[("Precision", "mixed")])
+            r = run_ref_driver(sysd, alpha, grid, k, w, "CUDA", system_file=sp, extra_plugins=[cuda_lib], props=[("Precision", "mixed")] + dev)
             if r is not None:
                 ref_gpu = {"value": r["ns_per_day"], "unit": "ns/day", "ms_per_step": r["ms_per_step"], "steps": r["steps"],
                            "what": "the reference's own CUDA platform (unmodified OpenMM 8.6, Precision=mixed) on this GPU, same system file"}
@@ -404,7 +406,16 @@ def main():
         bit_identical = multi_rank_identity_check(sysd, rank, world, local, dist, torch, b, workloads)
     ctx.close()
     plugin = ref_gpu = None
-    if rank == 0 and world == 1 and not args.no_plugin:
+    if world > 1 and not args.no_plugin:
+        # the same N GPUs driven by ONE process through the plugin (DeviceIndex=0,...,N-1): the other ranks have released their GPUs
+        # and wait on the host (gloo) while rank 0 runs the reference's own Context/Integrator machinery on the B200 platform
+        torch.cuda.synchronize()
+        host_group = dist.new_group(backend="gloo")
+        dist.barrier(group=host_group)
+        if rank == 0:
+            plugin, ref_gpu = plugin_records(sysd, alpha, grid, args, n, devices=list(range(world)))
+        dist.barrier(group=host_group)
+    elif rank == 0 and not args.no_plugin:
         plugin, ref_gpu = plugin_records(sysd, alpha, grid, args, n)
     if rank == 0:
         line = {

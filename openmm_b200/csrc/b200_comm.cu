@@ -11,6 +11,7 @@
 // inside a torch process this binds to the NCCL that torch already loaded.
 #include "b200_internal.cuh"
 #include <dlfcn.h>
+#include <unistd.h>
 #include <cstdio>
 #include <algorithm>
 #include <cmath>
@@ -92,7 +93,9 @@ extern "C" int b200_set_partition(b200_ctx* c, int32_t rank, int32_t nranks) {
 // contributions of all ranks for its atoms straight out of their memories (the reduce-scatter), integrates and constrains,
 // and stores the new float4 positions into every rank's posq (the all-gather).  This replaces ncclAllReduce(25.6 MB for
 // STMV) + R redundant integrations.  The barriers are device-side flag exchanges in peer memory; the host never waits.
-struct IpcBundle { cudaIpcMemHandle_t h[6]; };
+// A rank in ANOTHER process is reached through CUDA IPC handles; a rank in the SAME process (one OpenMM Context driving several GPUs,
+// DeviceIndex=0,1,...) through its raw pointers after cudaDeviceEnablePeerAccess (IPC handles cannot be opened by their own process).
+struct IpcBundle { cudaIpcMemHandle_t h[6]; void* raw[6]; long long pid; int device; };
 
 // signal and wait in one launch: lane r tells rank r that this rank reached `seq`, then waits for rank r's flag
 __global__ void peerBarrierKernel(PeerSet p, unsigned long long* flags, int slot, unsigned long long seq, DevCounters* counters) {
@@ -220,7 +223,8 @@ static void peerSetup(b200_ctx* c) {
     dmalloc(c->peerFlags, (size_t)3 * B200_MAX_PEERS);
     CUDA_CHECK(cudaMemset(c->peerFlags, 0, sizeof(unsigned long long) * 3 * B200_MAX_PEERS));
     void* ptrs[6] = {c->force, c->posq, c->posqCorr, c->velm, c->counters, c->peerFlags};
-    for (int k = 0; k < 6; k++) if (cudaIpcGetMemHandle(&mine.h[k], ptrs[k]) != cudaSuccess) { cudaGetLastError(); ok = 0; }
+    for (int k = 0; k < 6; k++) { mine.raw[k] = ptrs[k]; if (cudaIpcGetMemHandle(&mine.h[k], ptrs[k]) != cudaSuccess) { cudaGetLastError(); ok = 0; } }
+    mine.pid = (long long)getpid(); mine.device = c->device;
     // exchange the handles (and whether everybody could export) through the communicator
     char* dSend = nullptr; char* dRecv = nullptr;
     const size_t rec = sizeof(IpcBundle) + 8;
@@ -240,7 +244,14 @@ static void peerSetup(b200_ctx* c) {
         if (r == c->commRank) { for (int k = 0; k < 6; k++) q[k] = ptrs[k]; }
         else {
             IpcBundle b; memcpy(&b, hostRecv.data() + r * rec, sizeof(b));
-            for (int k = 0; k < 6; k++) if (cudaIpcOpenMemHandle(&q[k], b.h[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; q[k] = nullptr; }
+            if (b.pid == mine.pid) {
+                int can = 0;
+                if (cudaDeviceCanAccessPeer(&can, c->device, b.device) != cudaSuccess || !can) { cudaGetLastError(); ok = 0; }
+                else { const cudaError_t e = cudaDeviceEnablePeerAccess(b.device, 0); if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) ok = 0; cudaGetLastError(); }
+                for (int k = 0; k < 6; k++) q[k] = ok ? b.raw[k] : nullptr;
+                c->peerInProcess = true;
+            }
+            else for (int k = 0; k < 6; k++) if (cudaIpcOpenMemHandle(&q[k], b.h[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; q[k] = nullptr; }
         }
         p.force[r] = (long long*)q[0]; p.posq[r] = (float4*)q[1]; p.posqCorr[r] = (float4*)q[2]; p.velm[r] = (double4*)q[3];
         p.counters[r] = (DevCounters*)q[4]; p.flags[r] = (unsigned long long*)q[5];
@@ -289,7 +300,7 @@ void b200_comm_destroy(b200_ctx* c) {
     if (c->peerMode) {
         cudaDeviceSynchronize();
         PeerSet& p = c->peers;
-        for (int r = 0; r < p.n; r++) if (r != p.rank) {
+        for (int r = 0; r < p.n && !c->peerInProcess; r++) if (r != p.rank) {
             void* q[6] = {p.force[r], p.posq[r], p.posqCorr[r], p.velm[r], p.counters[r], p.flags[r]};
             for (void* x : q) if (x) cudaIpcCloseMemHandle(x);
         }

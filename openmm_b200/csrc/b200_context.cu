@@ -773,6 +773,10 @@ extern "C" int b200_get_velocities(b200_ctx* c, double* xyz) {
     CUDA_CHECK(cudaSetDevice(c->device));
     b200_peer_sync_state(c);
     b200_flush_cm(c);
+    if (!xyz) {     // multi-GPU: collective part only
+        if (c->commRanks > 1) { CUDA_CHECK(cudaStreamSynchronize(c->stream)); return B200_OK; }
+        throw B200Error(B200_ERR_INVALID, "b200_get_velocities: null array");
+    }
     ensureStaging(c);
     ioGetVelocities<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->velm);
     LAUNCH_COUNT(c, 1);
@@ -783,6 +787,11 @@ extern "C" int b200_get_velocities(b200_ctx* c, double* xyz) {
 extern "C" int b200_get_forces(b200_ctx* c, double* xyz) {
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
+    b200_ensure_forces_reduced(c);
+    if (!xyz) {     // multi-GPU: a rank that does not need the host copy still takes part in the collective sum above
+        if (c->commRanks > 1) return B200_OK;
+        throw B200Error(B200_ERR_INVALID, "b200_get_forces: null array");
+    }
     ensureStaging(c);
     ioGetForces<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->Npad, c->force);
     LAUNCH_COUNT(c, 1);
@@ -956,7 +965,9 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     }
     if (c->partRank == 0 || c->commRanks > 1) b200_bonded_launch(c, groups, forces, energy);
     if (doRecip && usePmeStream) CUDA_CHECK(cudaStreamWaitEvent(s, c->evPmeDone, 0));
-    if (forces && c->commRanks > 1 && !c->peerStepActive) b200_comm_allreduce_forces(c);   // peer step: the integration kernel sums the ranks' forces itself
+    // With a communicator every rank now holds PARTIAL forces.  They are summed when somebody needs the total: the integration step
+    // reduce-scatters them over peer memory (b200_advance), b200_get_forces and the shifted kinetic energy all-reduce them.
+    c->forcesPartial = forces && c->commRanks > 1;
     if (energy && c->commRanks > 1) b200_comm_allreduce_energy(c);
     c->forcesValid = forces && groups == B200_GROUP_ALL;
     if (energy) {
@@ -1055,48 +1066,71 @@ extern "C" int b200_integrator_create(b200_ctx* c, const b200_integrator_desc* d
     API_END
 }
 
+void b200_ensure_forces_reduced(b200_ctx* c) {
+    if (!c->forcesPartial || c->commRanks < 2) return;
+    b200_comm_allreduce_forces(c);      // collective: every rank reaches this point (int64 sums: exact, order independent)
+    c->forcesPartial = false;
+}
+
+// Whether the integration runs sharded over peer memory (collective decision, cached): needs the peer mappings, slices that are
+// contiguous slot ranges, and no constraint kind that is not sharded yet.
+static bool peerStepPlan(b200_ctx* c) {
+    { static const bool fp = getenv("B200_FUSED_PUBLISH") != nullptr; c->fusedPublish = fp; }
+    bool active = c->peerMode && c->commRanks > 1 && c->integ.remove_cm_every <= 1 && c->hasNonbonded && c->numShake == 0;
+    if (active) {
+        b200_peer_plan_shard(c);
+        // Slices whose atoms are not one contiguous range of slots (units listed out of slot order) would need the per-atom peer
+        // accesses inside the integrator; that variant is compiled but has no multi-GPU test yet, so such systems take the
+        // all-reduce + replicated integration path (every rank reaches the same decision: the flag is all-reduced).
+        if (!c->shardContiguous) active = false;
+    }
+    return active;
+}
+
+// Everything of an MD step that follows the force evaluation: (multi-GPU: flag barrier, reduce-scatter of the partial forces) ->
+// integration with constraints -> (publication of the new positions, flag barrier) -> step bookkeeping.  Shared by b200_step and
+// by b200_integrate (the plugin's IntegrateLangevinMiddleStepKernel::execute), so both take the same path.
+void b200_advance(b200_ctx* c, cudaEvent_t* ev) {
+    auto mark = [&](int k) { if (ev) { cudaEventCreate(&ev[k]); cudaEventRecord(ev[k], c->stream); } };
+    c->peerStepActive = peerStepPlan(c);
+    if (c->peerStepActive) {
+        b200_peer_barrier(c, PEER_SLOT_FORCES);                           // every rank's partial forces are complete
+        mark(2);
+        b200_peer_reduce_forces(c);                                       // reduce-scatter over NVLink into the local array
+    } else {
+        if (c->commRanks > 1) { b200_peer_sync_state(c); b200_ensure_forces_reduced(c); }     // replicated integration on every rank
+        mark(2);
+    }
+    mark(3);
+    b200_integrate_step(c);
+    mark(4);
+    if (c->peerStepActive) {
+        if (!c->fusedPublish) b200_peer_publish_positions(c);             // all-gather
+        mark(5);
+        b200_peer_barrier(c, PEER_SLOT_POSITIONS);                        // every rank's slice of new positions has arrived everywhere
+    } else mark(5);
+    mark(6);
+    c->stepCount++; c->timePs += c->integ.dt; c->stepsSinceReorder++;
+    c->forcesValid = false; c->forcesPartial = false;
+    c->peerStepActive = false;
+}
+
 extern "C" int b200_step(b200_ctx* c, int32_t nsteps) {
     API_BEGIN
     if (!c->hasIntegrator) throw B200Error(B200_ERR_INVALID, "b200_step: no integrator");
     CUDA_CHECK(cudaSetDevice(c->device));
     b200_finalize(c);
     if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints that are neither rigid 3-site molecules (SETTLE) nor clusters of one central atom with up to three singly-constrained partners (SHAKE) are not implemented");
-    // peer-memory step: the momentum bookkeeping inside the integration kernel is what keeps the ranks' momenta in step
-    { static const bool fp = getenv("B200_FUSED_PUBLISH") != nullptr; c->fusedPublish = fp; }
-    c->peerStepActive = c->peerMode && c->commRanks > 1 && c->integ.remove_cm_every <= 1 && c->hasNonbonded && c->numShake == 0;   // (SHAKE clusters are not sharded yet)
-    if (c->peerStepActive) {
-        b200_peer_plan_shard(c);
-        // Slices whose atoms are not one contiguous range of slots (units listed out of slot order) would need the per-atom peer
-        // accesses inside the integrator; that variant is compiled but has no multi-GPU test yet, so such systems take the
-        // NCCL all-reduce + replicated integration path (every rank reaches the same decision: the flag is all-reduced).
-        if (!c->shardContiguous) c->peerStepActive = false;
-    }
     // B200_PEER_TRACE=1: event time line of the last step of this call (debug aid for the multi-GPU step)
     static const bool trace = getenv("B200_PEER_TRACE") != nullptr;
     cudaEvent_t ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     for (int i = 0; i < nsteps; i++) {
         const bool tr = trace && i == nsteps - 1 && nsteps > 1;
-        auto mark = [&](int k) { if (tr) { cudaEventCreate(&ev[k]); cudaEventRecord(ev[k], c->stream); } };
-        mark(0);
+        if (tr) { cudaEventCreate(&ev[0]); cudaEventRecord(ev[0], c->stream); }
         if (c->integ.remove_cm_every > 0 && c->stepCount % c->integ.remove_cm_every == 0) b200_request_cm_removal(c);
         computeImpl(c, B200_GROUP_ALL, true, false, nullptr, !c->listVerified || (c->stepCount & 63) == 0);
-        mark(1);
-        if (c->peerStepActive) {
-            b200_peer_barrier(c, PEER_SLOT_FORCES);                           // every rank's partial forces are complete
-            mark(2);
-            if (c->shardContiguous) b200_peer_reduce_forces(c);               // reduce-scatter over NVLink into the local array
-        }
-        mark(3);
-        b200_integrate_step(c);
-        mark(4);
-        if (c->peerStepActive) {
-            if (c->shardContiguous && !c->fusedPublish) b200_peer_publish_positions(c);           // all-gather
-            mark(5);
-            b200_peer_barrier(c, PEER_SLOT_POSITIONS);                        // every rank's slice of new positions has arrived everywhere
-        }
-        mark(6);
-        c->stepCount++; c->timePs += c->integ.dt; c->stepsSinceReorder++;
-        c->forcesValid = false;
+        if (tr) { cudaEventCreate(&ev[1]); cudaEventRecord(ev[1], c->stream); }
+        b200_advance(c, tr ? ev : nullptr);
         if (tr) {
             cudaStreamSynchronize(c->stream);
             float t[7] = {0, 0, 0, 0, 0, 0, 0};
@@ -1106,7 +1140,6 @@ extern "C" int b200_step(b200_ctx* c, int32_t nsteps) {
             for (auto& e : ev) if (e) { cudaEventDestroy(e); e = nullptr; }
         }
     }
-    c->peerStepActive = false;
     checkOverflow(c);
     if (c->countersHost->overflow) throw B200Error(B200_ERR_OVERFLOW, "neighbour list overflowed during b200_step; state is not trustworthy");
     API_END

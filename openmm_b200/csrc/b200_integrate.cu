@@ -441,8 +441,7 @@ void b200_flush_cm(b200_ctx* c) {
 extern "C" int b200_remove_cm_motion(b200_ctx* c) {
     try {
         CUDA_CHECK(cudaSetDevice(c->device));
-        if (c->commRanks > 1) { b200_peer_sync_state(c); removeCM(c); }   // velocities are sharded between steps: remove on the gathered copy
-        else b200_request_cm_removal(c);
+        b200_request_cm_removal(c);     // (multi-GPU: the momentum buffer is kept in step on every rank by the integration kernels)
         CUDA_CHECK(cudaGetLastError());
     }
     catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
@@ -454,12 +453,9 @@ extern "C" int b200_integrate(b200_ctx* c) {
     try {
         if (!c->hasIntegrator) throw B200Error(B200_ERR_INVALID, "b200_integrate: no integrator");
         CUDA_CHECK(cudaSetDevice(c->device));
-        b200_peer_sync_state(c);
         b200_finalize(c);
         if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints that are neither rigid 3-site molecules (SETTLE) nor SHAKE clusters are not implemented");
-        b200_integrate_step(c);            // the caller (CMMotionRemover's own kernel) decides when COM motion is removed
-        c->stepCount++; c->timePs += c->integ.dt; c->stepsSinceReorder++;
-        c->forcesValid = false;
+        b200_advance(c, nullptr);          // the caller (CMMotionRemover's own kernel) decides when COM motion is removed
     } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
     return B200_OK;
 }
@@ -557,6 +553,7 @@ extern "C" int b200_kinetic_energy_shifted(b200_ctx* c, double shift, double* ke
         b200_peer_sync_state(c);
         b200_finalize(c);
         b200_flush_cm(c);
+        b200_ensure_forces_reduced(c);
         cudaStream_t s = c->stream;
         CUDA_CHECK(cudaMemcpyAsync(c->velmTmp, c->velm, sizeof(double4) * c->Npad, cudaMemcpyDeviceToDevice, s));
         shiftVelocities<<<(c->N + 255) / 256, 256, 0, s>>>(c->velm, c->force, c->N, c->Npad, shift);

@@ -187,6 +187,7 @@ struct b200_ctx {
     int sparseMax = 5;             // j atoms reaching at most this many atoms of X are handled as sparse pairs
 
     // fused reduce + integrate + gather over peer memory (b200_comm.cu, b200_integrate.cu)
+    bool peerInProcess = false;     // the peers are contexts of this process (raw pointers + cudaDeviceEnablePeerAccess instead of IPC)
     bool peerMode = false;          // IPC mappings established on every rank
     bool fusedPublish = false;      // B200_FUSED_PUBLISH=1: the integration kernel stores the new positions to the peers itself
     bool peerStepActive = false;    // inside b200_step in peer mode: no NCCL all-reduce of the forces
@@ -214,6 +215,7 @@ struct b200_ctx {
     b200_integrator_desc integ;
     double timePs = 0; int64_t stepCount = 0;
     bool forcesValid = false;
+    bool forcesPartial = false;    // multi-GPU: the force buffer holds this rank's contribution only (summed on demand)
     bool cmValid = false;          // device momentum buffer cm[stepCount % 3] matches the current velocities
     bool cmDeferred = false;       // a COM-motion removal was requested; the next integration kernel subtracts it (b200_flush_cm applies it early)
     bool dispChecked = false;      // the last integration kernel already ran the displacement check on the current positions
@@ -260,6 +262,8 @@ void b200_bonded_upload(b200_ctx* c);
 void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy);
 void b200_integrate_setup(b200_ctx* c);
 void b200_integrate_step(b200_ctx* c);
+void b200_advance(b200_ctx* c, cudaEvent_t* traceEvents);   // after the forces: (barrier, reduce) integrate (publish, barrier), bookkeeping
+void b200_ensure_forces_reduced(b200_ctx* c);          // multi-GPU: all-reduce partial forces if nobody has summed them yet (collective)
 void b200_request_cm_removal(b200_ctx* c);           // RemoveCMMotion: deferred into the next integration kernel when possible
 void b200_flush_cm(b200_ctx* c);                        // apply a deferred COM-motion removal now (before anything reads the velocities)
 void b200_comm_allreduce_forces(b200_ctx* c);

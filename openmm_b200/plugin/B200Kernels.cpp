@@ -30,16 +30,19 @@ void B200CalcForcesAndEnergyKernel::beginComputation(ContextImpl&, bool, bool, i
 double B200CalcForcesAndEnergyKernel::finishComputation(ContextImpl&, bool includeForce, bool includeEnergy, int, bool& valid) {
     double energy = 0.0;
     // the force buffer is cleared by the computation even when no group is requested, as clearAutoclearBuffers does (CudaKernels.cpp:66)
-    check(b200_compute(d.ctx, d.pendingGroups, includeForce ? 1 : 0, includeEnergy ? 1 : 0, &energy));
+    // every rank evaluates its share (multi-GPU: the energies are all-reduced inside, the forces stay partial until someone needs them)
+    vector<double> e(max<size_t>(1, d.ranks.size()), 0.0);
+    d.all([&](b200_ctx* c, int r) { return b200_compute(c, d.pendingGroups, includeForce ? 1 : 0, includeEnergy ? 1 : 0, &e[r]); });
+    energy = e[0];
     valid = true;            // list growth/retry is handled inside the library (CudaNonbondedUtilities.cpp:441-479 does it by invalidating)
     return includeEnergy ? energy : 0.0;
 }
 
 // ---------------------------------------------------------------------------------------------- state
 double B200UpdateStateDataKernel::getTime(const ContextImpl&) const { double t; int64_t s; check(b200_get_time(d.ctx, &t, &s)); return t; }
-void B200UpdateStateDataKernel::setTime(ContextImpl&, double time) { double t; int64_t s; check(b200_get_time(d.ctx, &t, &s)); check(b200_set_time(d.ctx, time, s)); }
+void B200UpdateStateDataKernel::setTime(ContextImpl&, double time) { double t; int64_t s; check(b200_get_time(d.ctx, &t, &s)); d.all([&](b200_ctx* c, int) { return b200_set_time(c, time, s); }); }
 long long B200UpdateStateDataKernel::getStepCount(const ContextImpl&) const { double t; int64_t s; check(b200_get_time(d.ctx, &t, &s)); return s; }
-void B200UpdateStateDataKernel::setStepCount(const ContextImpl&, long long count) { double t; int64_t s; check(b200_get_time(d.ctx, &t, &s)); check(b200_set_time(d.ctx, t, count)); }
+void B200UpdateStateDataKernel::setStepCount(const ContextImpl&, long long count) { double t; int64_t s; check(b200_get_time(d.ctx, &t, &s)); d.all([&](b200_ctx* c, int) { return b200_set_time(c, t, count); }); }
 
 // A vector<Vec3> IS a contiguous double[3N] (Vec3 holds exactly three doubles, openmmapi/include/openmm/Vec3.h), so the C ABI
 // reads and writes the caller's vectors in place: no intermediate copy on the state I/O path.
@@ -49,20 +52,20 @@ static const double* asDoubles(const vector<Vec3>& v) { return reinterpret_cast<
 
 void B200UpdateStateDataKernel::getPositions(ContextImpl&, vector<Vec3>& positions, bool) {
     positions.resize(numParticles);
-    check(b200_get_positions(d.ctx, asDoubles(positions), 0));
+    d.all([&](b200_ctx* c, int r) { return b200_get_positions(c, r == 0 ? asDoubles(positions) : nullptr, 0); });   // rank 0 downloads, the others join the gather
 }
 void B200UpdateStateDataKernel::setPositions(ContextImpl&, const vector<Vec3>& positions) {
     if ((int)positions.size() != numParticles) throw OpenMMException("Called setPositions() on a Context with the wrong number of positions");
-    check(b200_set_positions(d.ctx, asDoubles(positions)));
+    d.all([&](b200_ctx* c, int) { return b200_set_positions(c, asDoubles(positions)); });
     d.positionsValid = true;
 }
 void B200UpdateStateDataKernel::getVelocities(ContextImpl&, vector<Vec3>& velocities) {
     velocities.resize(numParticles);
-    check(b200_get_velocities(d.ctx, asDoubles(velocities)));
+    d.all([&](b200_ctx* c, int r) { return b200_get_velocities(c, r == 0 ? asDoubles(velocities) : nullptr); });
 }
 void B200UpdateStateDataKernel::setVelocities(ContextImpl&, const vector<Vec3>& velocities) {
     if ((int)velocities.size() != numParticles) throw OpenMMException("Called setVelocities() on a Context with the wrong number of velocities");
-    check(b200_set_velocities(d.ctx, asDoubles(velocities)));
+    d.all([&](b200_ctx* c, int) { return b200_set_velocities(c, asDoubles(velocities)); });
 }
 void B200UpdateStateDataKernel::computeShiftedVelocities(ContextImpl& context, double timeShift, vector<Vec3>& velocities) {
     // v(t + shift) ~ v + shift * F/m with the forces currently in the buffer (IntegrationUtilities::computeShiftedVelocities;
@@ -76,7 +79,7 @@ void B200UpdateStateDataKernel::computeShiftedVelocities(ContextImpl& context, d
 }
 void B200UpdateStateDataKernel::getForces(ContextImpl&, vector<Vec3>& forces) {
     forces.resize(numParticles);
-    check(b200_get_forces(d.ctx, asDoubles(forces)));
+    d.all([&](b200_ctx* c, int r) { return b200_get_forces(c, r == 0 ? asDoubles(forces) : nullptr); });
 }
 void B200UpdateStateDataKernel::getPeriodicBoxVectors(ContextImpl&, Vec3& a, Vec3& b, Vec3& c) const {
     double box[9];
@@ -85,7 +88,7 @@ void B200UpdateStateDataKernel::getPeriodicBoxVectors(ContextImpl&, Vec3& a, Vec
 }
 void B200UpdateStateDataKernel::setPeriodicBoxVectors(ContextImpl&, const Vec3& a, const Vec3& b, const Vec3& c) {
     const double box[9] = {a[0], a[1], a[2], b[0], b[1], b[2], c[0], c[1], c[2]};
-    check(b200_set_box(d.ctx, box));
+    d.all([&](b200_ctx* c, int) { return b200_set_box(c, box); });
 }
 void B200UpdateStateDataKernel::createCheckpoint(ContextImpl& context, ostream& stream) {
     // platform-specific binary state, as in CommonKernels.cpp:354-382 (version, time, step, positions, velocities, box)
@@ -95,7 +98,8 @@ void B200UpdateStateDataKernel::createCheckpoint(ContextImpl& context, ostream& 
     check(b200_get_time(d.ctx, &t, &s));
     stream.write((const char*)&t, sizeof(double)); stream.write((const char*)&s, sizeof(int64_t));
     vector<double> p(3 * (size_t)numParticles), v(p.size());
-    check(b200_get_positions(d.ctx, p.data(), 0)); check(b200_get_velocities(d.ctx, v.data()));
+    d.all([&](b200_ctx* c, int r) { return b200_get_positions(c, r == 0 ? p.data() : nullptr, 0); });
+    d.all([&](b200_ctx* c, int r) { return b200_get_velocities(c, r == 0 ? v.data() : nullptr); });
     stream.write((const char*)p.data(), sizeof(double) * p.size()); stream.write((const char*)v.data(), sizeof(double) * v.size());
     double box[9]; check(b200_get_box(d.ctx, box));
     stream.write((const char*)box, sizeof(box));
@@ -109,8 +113,8 @@ void B200UpdateStateDataKernel::loadCheckpoint(ContextImpl& context, istream& st
     vector<double> p(3 * (size_t)numParticles), v(p.size());
     stream.read((char*)p.data(), sizeof(double) * p.size()); stream.read((char*)v.data(), sizeof(double) * v.size());
     double box[9]; stream.read((char*)box, sizeof(box));
-    check(b200_set_box(d.ctx, box)); check(b200_set_positions(d.ctx, p.data())); check(b200_set_velocities(d.ctx, v.data()));
-    check(b200_set_time(d.ctx, t, s));
+    d.all([&](b200_ctx* c, int) { int rc = b200_set_box(c, box); if (!rc) rc = b200_set_positions(c, p.data()); if (!rc) rc = b200_set_velocities(c, v.data());
+                                  if (!rc) rc = b200_set_time(c, t, s); return rc; });
 }
 
 void B200MinimizeKernel::execute(ContextImpl& context, double tolerance, int maxIterations, MinimizationReporter* reporter) {
@@ -196,14 +200,14 @@ void B200CalcNonbondedForceKernel::initialize(const System& system, const Nonbon
     for (int i = 0; i < force.getNumGlobalParameters(); i++) globals[force.getGlobalParameterName(i)] = force.getGlobalParameterDefaultValue(i);
     Params p;
     gather(system, force, p, globals);
-    check(b200_nonbonded_create(d.ctx, &p.desc));
+    d.all([&](b200_ctx* c, int) { return b200_nonbonded_create(c, &p.desc); });
 }
 
 double B200CalcNonbondedForceKernel::execute(ContextImpl& context, bool, bool, bool includeDirect, bool includeReciprocal) {
     if (hasOffsets) {   // a global parameter that moved since the last evaluation changes the effective parameters
         bool changed = false;
         for (auto& g : globals) { const double v = context.getParameter(g.first); if (v != g.second) { g.second = v; changed = true; } }
-        if (changed) { Params p; gather(*systemRef, *forceRef, p, globals); check(b200_nonbonded_update_parameters(d.ctx, &p.desc)); }
+        if (changed) { Params p; gather(*systemRef, *forceRef, p, globals); d.all([&](b200_ctx* c, int) { return b200_nonbonded_update_parameters(c, &p.desc); }); }
     }
     if (includeDirect) d.pendingGroups |= B200_GROUP_DIRECT;
     if (includeReciprocal) d.pendingGroups |= B200_GROUP_RECIPROCAL;
@@ -214,7 +218,7 @@ void B200CalcNonbondedForceKernel::copyParametersToContext(ContextImpl& context,
     Params p;
     for (auto& g : globals) g.second = context.getParameter(g.first);
     gather(context.getSystem(), force, p, globals);
-    check(b200_nonbonded_update_parameters(d.ctx, &p.desc));
+    d.all([&](b200_ctx* c, int) { return b200_nonbonded_update_parameters(c, &p.desc); });
 }
 
 void B200CalcNonbondedForceKernel::getPMEParameters(double& alpha, int& nx, int& ny, int& nz) const {
@@ -244,7 +248,7 @@ void B200CalcHarmonicBondForceKernel::initialize(const System&, const HarmonicBo
     const int n = force.getNumBonds();
     vector<int> atoms(2 * (size_t)n); vector<double> len(n), k(n);
     for (int i = 0; i < n; i++) force.getBondParameters(i, atoms[2 * i], atoms[2 * i + 1], len[i], k[i]);
-    check(b200_harmonic_bonds_create(d.ctx, n, atoms.data(), len.data(), k.data(), force.getForceGroup()));
+    d.all([&](b200_ctx* c, int) { return b200_harmonic_bonds_create(c, n, atoms.data(), len.data(), k.data(), force.getForceGroup()); });
 }
 void B200CalcHarmonicBondForceKernel::copyParametersToContext(ContextImpl&, const HarmonicBondForce&, int, int) {
     throw OpenMMException("The B200 platform does not support updateParametersInContext for HarmonicBondForce yet");
@@ -254,7 +258,7 @@ void B200CalcHarmonicAngleForceKernel::initialize(const System&, const HarmonicA
     const int n = force.getNumAngles();
     vector<int> atoms(3 * (size_t)n); vector<double> ang(n), k(n);
     for (int i = 0; i < n; i++) force.getAngleParameters(i, atoms[3 * i], atoms[3 * i + 1], atoms[3 * i + 2], ang[i], k[i]);
-    check(b200_harmonic_angles_create(d.ctx, n, atoms.data(), ang.data(), k.data(), force.getForceGroup()));
+    d.all([&](b200_ctx* c, int) { return b200_harmonic_angles_create(c, n, atoms.data(), ang.data(), k.data(), force.getForceGroup()); });
 }
 void B200CalcHarmonicAngleForceKernel::copyParametersToContext(ContextImpl&, const HarmonicAngleForce&, int, int) {
     throw OpenMMException("The B200 platform does not support updateParametersInContext for HarmonicAngleForce yet");
@@ -264,7 +268,7 @@ void B200CalcPeriodicTorsionForceKernel::initialize(const System&, const Periodi
     const int n = force.getNumTorsions();
     vector<int> atoms(4 * (size_t)n), per(n); vector<double> phase(n), k(n);
     for (int i = 0; i < n; i++) force.getTorsionParameters(i, atoms[4 * i], atoms[4 * i + 1], atoms[4 * i + 2], atoms[4 * i + 3], per[i], phase[i], k[i]);
-    check(b200_periodic_torsions_create(d.ctx, n, atoms.data(), per.data(), phase.data(), k.data(), force.getForceGroup()));
+    d.all([&](b200_ctx* c, int) { return b200_periodic_torsions_create(c, n, atoms.data(), per.data(), phase.data(), k.data(), force.getForceGroup()); });
 }
 void B200CalcPeriodicTorsionForceKernel::copyParametersToContext(ContextImpl&, const PeriodicTorsionForce&, int, int) {
     throw OpenMMException("The B200 platform does not support updateParametersInContext for PeriodicTorsionForce yet");
@@ -280,7 +284,7 @@ void B200ApplyMonteCarloBarostatKernel::computeKineticEnergy(ContextImpl& contex
     // kinetic energy of the molecular centres of mass (rigid molecules) or of all particles, split as monteCarloBarostat.cc does:
     // 1 component = total, 3 = per axis, 6 = all elements of the box tensor.  A cold path (instantaneous pressure): done on the host.
     vector<double> v(3 * (size_t)numParticles);
-    check(b200_get_velocities(d.ctx, v.data()));
+    d.all([&](b200_ctx* c, int r) { return b200_get_velocities(c, r == 0 ? v.data() : nullptr); });
     vector<vector<int> > molecules;
     if (rigid) molecules = context.getMolecules();
     else { molecules.resize(numParticles); for (int i = 0; i < numParticles; i++) molecules[i].push_back(i); }
@@ -305,22 +309,24 @@ void B200IntegrateLangevinMiddleStepKernel::initialize(const System&, const Lang
 }
 void B200IntegrateLangevinMiddleStepKernel::execute(ContextImpl&, const LangevinMiddleIntegrator& integrator) {
     b200_integrator_desc desc = {integrator.getStepSize(), integrator.getTemperature(), integrator.getFriction(), integrator.getConstraintTolerance(), seed, 0};
-    check(b200_integrator_create(d.ctx, &desc));
-    check(b200_integrate(d.ctx));
+    d.all([&](b200_ctx* c, int) { const int rc = b200_integrator_create(c, &desc); return rc ? rc : b200_integrate(c); });
 }
 double B200IntegrateLangevinMiddleStepKernel::computeKineticEnergy(ContextImpl&, const LangevinMiddleIntegrator&) {
-    double ke; check(b200_kinetic_energy(d.ctx, &ke)); return ke;
+    vector<double> ke(max<size_t>(1, d.ranks.size()), 0.0);
+    d.all([&](b200_ctx* c, int r) { return b200_kinetic_energy(c, &ke[r]); });
+    return ke[0];
 }
 void B200IntegrateVerletStepKernel::execute(ContextImpl&, const VerletIntegrator& integrator) {
     b200_integrator_desc desc = {integrator.getStepSize(), 0.0, 0.0, integrator.getConstraintTolerance(), 0, 0};
-    check(b200_integrator_create(d.ctx, &desc));
-    check(b200_integrate(d.ctx));
+    d.all([&](b200_ctx* c, int) { const int rc = b200_integrator_create(c, &desc); return rc ? rc : b200_integrate(c); });
 }
 double B200IntegrateVerletStepKernel::computeKineticEnergy(ContextImpl& context, const VerletIntegrator& integrator) {
     // leapfrog: the stored velocities are half a step behind the positions; report the energy of velocities shifted forward by dt/2
     // with the current forces and constrained again (CommonKernels.cpp:3117 -> IntegrationUtilities::computeKineticEnergy)
     context.calcForcesAndEnergy(true, false, integrator.getIntegrationForceGroups());
-    double ke; check(b200_kinetic_energy_shifted(d.ctx, 0.5 * integrator.getStepSize(), &ke)); return ke;
+    vector<double> ke(max<size_t>(1, d.ranks.size()), 0.0);
+    d.all([&](b200_ctx* c, int r) { return b200_kinetic_energy_shifted(c, 0.5 * integrator.getStepSize(), &ke[r]); });
+    return ke[0];
 }
 
 }  // namespace B200Plugin

@@ -51,8 +51,8 @@ class B200ApplyConstraintsKernel : public OpenMM::ApplyConstraintsKernel {
 public:
     B200ApplyConstraintsKernel(std::string name, const Platform& platform, PData& d) : ApplyConstraintsKernel(name, platform), d(d) {}
     void initialize(const System& system) override {}
-    void apply(ContextImpl& context, double tol) override { check(b200_apply_constraints(d.ctx, tol)); }
-    void applyToVelocities(ContextImpl& context, double tol) override { check(b200_apply_velocity_constraints(d.ctx, tol)); }
+    void apply(ContextImpl& context, double tol) override { d.all([&](b200_ctx* c, int) { return b200_apply_constraints(c, tol); }); }
+    void applyToVelocities(ContextImpl& context, double tol) override { d.all([&](b200_ctx* c, int) { return b200_apply_velocity_constraints(c, tol); }); }
 private:
     PData& d;
 };
@@ -125,7 +125,7 @@ class B200RemoveCMMotionKernel : public OpenMM::RemoveCMMotionKernel {
 public:
     B200RemoveCMMotionKernel(std::string name, const Platform& platform, PData& d) : RemoveCMMotionKernel(name, platform), d(d) {}
     void initialize(const System& system, const OpenMM::CMMotionRemover& force) override {}
-    void execute(ContextImpl& context) override { check(b200_remove_cm_motion(d.ctx)); }
+    void execute(ContextImpl& context) override { d.all([&](b200_ctx* c, int) { return b200_remove_cm_motion(c); }); }
 private:
     PData& d;
 };
@@ -135,12 +135,12 @@ class B200ApplyMonteCarloBarostatKernel : public OpenMM::ApplyMonteCarloBarostat
 public:
     B200ApplyMonteCarloBarostatKernel(std::string name, const Platform& platform, PData& d) : ApplyMonteCarloBarostatKernel(name, platform), d(d) {}
     void initialize(const System& system, const OpenMM::Force& barostat, int components, bool rigidMolecules = true) override;
-    void saveCoordinates(ContextImpl& context) override { check(b200_barostat_save(d.ctx)); }
+    void saveCoordinates(ContextImpl& context) override { d.all([&](b200_ctx* c, int) { return b200_barostat_save(c); }); }
     void scaleCoordinates(ContextImpl& context, double scaleX, double scaleY, double scaleZ, double scaleXY = 0, double scaleXZ = 0, double scaleYZ = 0) override {
         const double s[6] = {scaleX, scaleY, scaleZ, scaleXY, scaleXZ, scaleYZ};
-        check(b200_barostat_scale(d.ctx, s, rigid ? 1 : 0));
+        d.all([&](b200_ctx* c, int) { return b200_barostat_scale(c, s, rigid ? 1 : 0); });
     }
-    void restoreCoordinates(ContextImpl& context) override { check(b200_barostat_restore(d.ctx)); }
+    void restoreCoordinates(ContextImpl& context) override { d.all([&](b200_ctx* c, int) { return b200_barostat_restore(c); }); }
     void computeKineticEnergy(ContextImpl& context, std::vector<double>& ke) override;
 private:
     PData& d;

@@ -19,6 +19,46 @@ void check(int rc) {
     if (rc != B200_OK) throw OpenMMException(string(b200_last_error()));
 }
 
+// ---- RankPool
+RankPool::~RankPool() {
+    { std::lock_guard<std::mutex> l(m); stop = true; generation++; }
+    cvWork.notify_all();
+    for (auto& t : threads) t.join();
+}
+void RankPool::start(int numWorkers) {
+    rc.assign(numWorkers + 1, 0); err.assign(numWorkers + 1, string());
+    for (int w = 0; w < numWorkers; w++) threads.emplace_back([this, w] { loop(w); });
+}
+void RankPool::loop(int worker) {
+    long seen = 0;
+    const int rank = worker + 1;
+    for (;;) {
+        const std::function<int(int)>* f = nullptr;
+        {
+            std::unique_lock<std::mutex> l(m);
+            cvWork.wait(l, [&] { return generation != seen; });
+            seen = generation;
+            if (stop) return;
+            f = job;
+        }
+        int r = B200_ERR_INVALID; string msg;
+        try { r = (*f)(rank); if (r != B200_OK) msg = b200_last_error(); }      // the error text is thread local: fetch it here
+        catch (const std::exception& e) { msg = e.what(); }
+        { std::lock_guard<std::mutex> l(m); rc[rank] = r; err[rank] = msg; pending--; }
+        cvDone.notify_one();
+    }
+}
+void RankPool::run(int numRanks, const std::function<int(int)>& f) {
+    { std::lock_guard<std::mutex> l(m); job = &f; pending = numRanks - 1; generation++; }
+    cvWork.notify_all();
+    int r0 = B200_ERR_INVALID; string msg0;
+    try { r0 = f(0); if (r0 != B200_OK) msg0 = b200_last_error(); }
+    catch (const std::exception& e) { msg0 = e.what(); }
+    { std::unique_lock<std::mutex> l(m); cvDone.wait(l, [&] { return pending == 0; }); job = nullptr; }
+    if (r0 != B200_OK) throw OpenMMException(msg0);
+    for (int r = 1; r < numRanks; r++) if (rc[r] != B200_OK) throw OpenMMException(err[r]);
+}
+
 B200Platform::B200Platform() {
     B200KernelFactory* factory = new B200KernelFactory();   // owned (and deleted once) by Platform (olla/src/Platform.cpp:70-76)
     for (const string& name : {CalcForcesAndEnergyKernel::Name(), UpdateStateDataKernel::Name(), ApplyConstraintsKernel::Name(),
@@ -57,13 +97,20 @@ void B200Platform::contextCreated(ContextImpl& context, const map<string, string
         return it == properties.end() ? getPropertyDefaultValue(key) : it->second;
     };
     const string precision = lower(prop(Precision()));
-    if (precision != "mixed") throw OpenMMException("The B200 platform only implements Precision=mixed");
+    // "single" is served by the mixed-precision kernels (float pair math and positions with a float remainder, double velocities and
+    // integration, integer force sums): everything single precision asks for, at the same speed.  "double" (FP64 pair math and meshes,
+    // CudaContext.cpp:127-141) is not implemented.
+    if (precision != "mixed" && precision != "single") throw OpenMMException("The B200 platform implements Precision=mixed (also selected by 'single'); 'double' is not available");
     if (lower(prop(DeterministicForces())) != "true") throw OpenMMException("The B200 platform always computes deterministic forces; DeterministicForces must be 'true'");
-    const string devices = prop(DeviceIndex());
-    if (devices.find(',') != string::npos)
-        throw OpenMMException("The B200 platform runs one process per GPU (NCCL ranks); a DeviceIndex list is not supported inside one Context");
-    int device = 0;
-    stringstream(devices) >> device;
+    // DeviceIndex may list several GPUs ("0,1,2,3", CudaPlatform.cpp:116-141): one rank per device inside this process
+    vector<int> deviceList;
+    {
+        stringstream ss(prop(DeviceIndex())); string tok;
+        while (getline(ss, tok, ',')) if (!tok.empty()) deviceList.push_back(stoi(tok));
+        if (deviceList.empty()) deviceList.push_back(0);
+        if (deviceList.size() > 8) throw OpenMMException("The B200 platform supports at most 8 devices per Context");
+    }
+    const int device = deviceList[0];
     const System& system = context.getSystem();
     const int n = system.getNumParticles();
     for (int i = 0; i < n; i++)
@@ -88,13 +135,23 @@ void B200Platform::contextCreated(ContextImpl& context, const map<string, string
     desc.flags = lower(prop(DisablePmeStream())) == "true" ? B200_CTX_DISABLE_PME_STREAM : 0;
     PlatformData* d = new PlatformData();
     try {
-        check(b200_context_create(&desc, &d->ctx));
+        const int R = (int)deviceList.size();
+        d->ranks.assign(R, nullptr);
+        for (int r = 0; r < R; r++) { b200_system_desc dr = desc; dr.device = deviceList[r]; check(b200_context_create(&dr, &d->ranks[r])); }
+        d->ctx = d->ranks[0];
+        if (R > 1) {
+            // the direct-space rows are partitioned over the ranks; forces are reduce-scattered and positions all-gathered over peer memory
+            char id[128];
+            check(b200_nccl_unique_id(id));
+            d->pool.start(R - 1);
+            d->all([&](b200_ctx* c, int r) { return b200_comm_init(c, r, R, id); });
+        }
     } catch (...) {
         delete d;
         throw;   // lets ContextImpl's automatic selection fall through to the next platform (ContextImpl.cpp:147-163)
     }
-    d->properties[DeviceIndex()] = to_string(device);
-    d->properties[Precision()] = "mixed";
+    d->properties[DeviceIndex()] = prop(DeviceIndex());
+    d->properties[Precision()] = precision;
     d->properties[DeterministicForces()] = "true";
     d->properties[DisablePmeStream()] = desc.flags ? "true" : "false";
     context.setPlatformData(d);

@@ -6,21 +6,58 @@
 #include "openmm/System.h"
 #include "openmm/internal/ContextImpl.h"
 #include "b200_nonbonded.h"
+#include <condition_variable>
+#include <functional>
 #include <map>
+#include <mutex>
 #include <string>
+#include <thread>
+#include <vector>
 
 namespace B200Plugin {
+
+void check(int rc);   // turns a C-ABI error code into an OpenMMException carrying b200_last_error()
+
+// One persistent host thread per additional GPU of a Context (DeviceIndex=0,1,...), the counterpart of the reference's per-device
+// WorkThread (platforms/common/include/openmm/common/ComputeContext.h:667-700).  Every C-ABI call of the plugin is issued for all
+// ranks at once -- rank 0 on the caller's thread, rank r on worker r -- because the multi-GPU calls are collective (device-side flag
+// barriers, NCCL): a rank that was not driven concurrently would leave the others waiting.
+class RankPool {
+public:
+    ~RankPool();
+    void start(int numWorkers);
+    // runs f(rank) for every rank; returns normally when all returned B200_OK, otherwise throws OpenMMException with the first message
+    void run(int numRanks, const std::function<int(int)>& f);
+private:
+    void loop(int worker);
+    std::vector<std::thread> threads;
+    std::mutex m; std::condition_variable cvWork, cvDone;
+    const std::function<int(int)>* job = nullptr;
+    long generation = 0; int pending = 0; bool stop = false;
+    std::vector<int> rc; std::vector<std::string> err;
+};
 
 class B200Platform : public OpenMM::Platform {
 public:
     // per-Context state hung off ContextImpl::setPlatformData (freed in contextDestroyed)
     struct PlatformData {
-        b200_ctx* ctx = nullptr;
+        b200_ctx* ctx = nullptr;               // rank 0 (the only one in a single-GPU Context)
+        std::vector<b200_ctx*> ranks;          // every rank's context, ranks[0] == ctx
+        RankPool pool;
+        // issue a C-ABI call on every rank (collectives need all of them); f(context, rank) returns the call's return code
+        void all(const std::function<int(b200_ctx*, int)>& f) {
+            if (ranks.size() <= 1) { check(f(ctx, 0)); return; }
+            pool.run((int)ranks.size(), [&](int r) { return f(ranks[r], r); });
+        }
         unsigned pendingGroups = 0;            // force groups requested by the ForceImpls between begin/finishComputation
         bool positionsValid = false;
         int bondedGroup[3] = {-1, -1, -1};      // force group of the HarmonicBond / HarmonicAngle / PeriodicTorsion terms already added
         std::map<std::string, std::string> properties;
-        ~PlatformData() { if (ctx) b200_context_destroy(ctx); }
+        ~PlatformData() {
+            if (ranks.empty()) { if (ctx) b200_context_destroy(ctx); return; }
+            if (ranks.size() > 1) { try { pool.run((int)ranks.size(), [&](int r) { b200_context_destroy(ranks[r]); return 0; }); } catch (...) {} }
+            else b200_context_destroy(ranks[0]);
+        }
     };
     B200Platform();
     const std::string& getName() const override { static const std::string name = "B200"; return name; }
@@ -42,7 +79,5 @@ class B200KernelFactory : public OpenMM::KernelFactory {
 public:
     OpenMM::KernelImpl* createKernelImpl(std::string name, const OpenMM::Platform& platform, OpenMM::ContextImpl& context) const override;
 };
-
-void check(int rc);   // turns a C-ABI error code into an OpenMMException carrying b200_last_error()
 
 }  // namespace B200Plugin

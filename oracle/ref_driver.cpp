@@ -151,15 +151,16 @@ static double relRms(const vector<Vec3>& a, const vector<Vec3>& ref) {
 }
 
 static int cmdCompare(int argc, char** argv) {
-    string sysPath = argv[2], platformName = "B200", against = "Reference"; vector<string> plugins;
+    string sysPath = argv[2], platformName = "B200", against = "Reference"; vector<string> plugins; map<string, string> props;
     for (int i = 3; i < argc; i++) {
         string a = argv[i];
         if (a == "--platform") platformName = argv[++i]; else if (a == "--plugin") plugins.push_back(argv[++i]); else if (a == "--against") against = argv[++i];
+        else if (a == "--prop") { string kv = argv[++i]; size_t eq = kv.find('='); if (eq != string::npos) props[kv.substr(0, eq)] = kv.substr(eq + 1); }
     }
     SystemFile s = readSystem(sysPath);
     Platform& p = pickPlatform(platformName, plugins);
     Platform& r = Platform::getPlatformByName(against);
-    Eval a = evaluate(s, p, {}), b = evaluate(s, r, {});
+    Eval a = evaluate(s, p, props), b = evaluate(s, r, {});
     vector<Vec3> ta(s.N), tb(s.N);
     for (int i = 0; i < s.N; i++) { ta[i] = a.fDirect[i] + a.fRecip[i]; tb[i] = b.fDirect[i] + b.fRecip[i]; }
     printf("{\"platform\": \"%s\", \"against\": \"%s\", \"n\": %d, \"rel_rms_force_total\": %.3e, \"rel_rms_force_direct\": %.3e, \"rel_rms_force_recip\": %.3e, "

@@ -122,3 +122,24 @@ def test_monte_carlo_barostat_through_the_plugin():
     assert np.allclose(g["volumes"], r["volumes"], rtol=1e-7)
     assert abs(g["potential_energy"] - r["potential_energy"]) / abs(r["potential_energy"]) < 1e-4
     assert np.allclose(g["position_sum"], r["position_sum"], atol=2e-2)
+
+
+@pytest.mark.gpu
+def test_several_gpus_in_one_context_through_the_plugin():
+    # DeviceIndex=0,1 (platforms/cuda/src/CudaPlatform.cpp:116-141, CudaParallelKernels.cpp): one OpenMM Context drives two B200s from one
+    # process.  Forces and energies against the Reference platform, then dynamics against the one-GPU run of the same plugin (the
+    # integer force sums make the trajectories identical, so the potential energies after 100 steps agree to the last digit printed).
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    sysd = workloads.water_box(23558, seed=23558)
+    alpha, grid = b.pme_parameters(0.9, sysd["box"])
+    with tempfile.TemporaryDirectory() as td:
+        sp = os.path.join(td, "s.bin")
+        workloads.write_system_file(sp, sysd, 0.9, alpha, grid, dispersion=True)
+        r = _driver(["compare", sp, "--platform", "B200", "--plugin", b.PLUGIN_PATH, "--against", "Reference", "--prop", "DeviceIndex=0,1"])
+        g2 = _driver(["bench", sp, "--platform", "B200", "--plugin", b.PLUGIN_PATH, "--steps", "60", "--warmup", "40", "--prop", "DeviceIndex=0,1"])
+        g1 = _driver(["bench", sp, "--platform", "B200", "--plugin", b.PLUGIN_PATH, "--steps", "60", "--warmup", "40"])
+    print(r, g2, g1)
+    assert r["rel_rms_force_total"] < 1e-5 and r["rel_energy"] < 1e-5
+    assert g2["potential_energy"] == g1["potential_energy"]
