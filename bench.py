@@ -330,7 +330,7 @@ def main():
         pairs_total = pairs
     sparse_tiles = int(stats["num_sparse_tiles"])
     dense_tiles = int(stats["num_tiles"]) - 2 * sparse_tiles
-    dense_slots = dense_tiles * 1024      # (the exclusion tiles are members of the rows' work units and counted in num_tiles)
+    dense_slots = (dense_tiles + int(stats["num_exclusion_tiles"])) * 1024
     tile_ms, tile_n = fam["tile"]
     tile_avg_ms = tile_ms / max(tile_n, 1)
     hbm_gbs, sm_max_mhz, peak_kind = measured_peaks()

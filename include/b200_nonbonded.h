@@ -177,8 +177,7 @@ int  b200_direct_pairs(b200_ctx* ctx, int64_t* count, int32_t* pairs /*[2*capaci
  * mod 2^64 with i<j original indices (what tests/TestNonbondedForce.h testLargeSystem needs at a million atoms, where the list
  * itself is > 1 GB).  oracle/ref_driver.cpp --pair-hash computes the same number from computeNeighborListVoxelHash. */
 int  b200_direct_pairs_hash(b200_ctx* ctx, int64_t* count, uint64_t* hash);
-/* Neighbour-list statistics after the last build: tiles (the exclusion tiles, which lead their row's work unit, included), work units,
- * exclusion tiles, rebuild count. */
+/* Neighbour-list statistics after the last build: tiles, work units, j-slots, exclusion tiles, rebuild count. */
 typedef struct {
     int64_t num_blocks, num_tiles, num_units, num_exclusion_tiles, rebuilds, steps, reorders;
     int64_t tile_capacity, unit_capacity;

@@ -99,15 +99,13 @@ __device__ __forceinline__ float boxGap2(float4 cA, float4 hA, float4 cB, float4
 #define NB_SPARSE_TILES 4
 #define NB_SBUF (NB_SPARSE_TILES * 32 + 32)
 
-// descW: bits 8-15 = number of leading tiles of the unit that are exclusion tiles of row X (they need the exclusion flags),
-//        bits 16-31 = index of the first of them among the row's exclusion tiles; 0 for a unit of ordinary tiles
-__device__ __forceinline__ void flushDense(int X, int* buf, int ntiles, int descW, int lane, int4* units, int* jAtoms, unsigned unitCapacity, unsigned tileCapacity, DevCounters* counters) {
+__device__ __forceinline__ void flushDense(int X, int* buf, int ntiles, int lane, int4* units, int* jAtoms, unsigned unitCapacity, unsigned tileCapacity, DevCounters* counters) {
     unsigned tileBase = 0, unit = 0;
     if (lane == 0) { tileBase = atomicAdd(&counters->numTiles, (unsigned)ntiles); unit = atomicAdd(&counters->numUnits, 1u); }
     tileBase = __shfl_sync(0xffffffffu, tileBase, 0); unit = __shfl_sync(0xffffffffu, unit, 0);
     if (tileBase + ntiles <= tileCapacity && unit < unitCapacity) {
         for (int k = lane; k < ntiles * 32; k += 32) jAtoms[(size_t)tileBase * 32 + k] = buf[k];
-        if (lane == 0) units[unit] = make_int4(X, (int)tileBase, ntiles, descW);
+        if (lane == 0) units[unit] = make_int4(X, (int)tileBase, ntiles, 0);
     } else if (lane == 0) { counters->overflow = 1; if (unit < unitCapacity) units[unit] = make_int4(X, 0, 0, 0); }   // dropped: leave an empty descriptor, never a stale one
 }
 // Sparse tiles are written sorted by the number of atoms of X each j atom reaches (descending): the tile kernel gives one lane
@@ -144,7 +142,7 @@ __device__ __forceinline__ float2 nbSub2(float2 a, float2 b) { b.x = -b.x; b.y =
 // exact test of up to 32 queued candidate atoms (one per lane) against the 32 atoms of block X, then classification
 struct NbWarpBufs { int* dense; int* slots; int* masks; };
 __device__ __forceinline__ void nbProcessCandidates(int X, int lane, unsigned ltMask, bool have, int slot, float rx, float ry, float rz, const float4* sXw, const float4* sXp, bool single,
-                                                    const BoxF& box, float rcp2, int sparseMax, NbWarpBufs w, int& nbuf, int& nsp, int& descW,
+                                                    const BoxF& box, float rcp2, int sparseMax, NbWarpBufs w, int& nbuf, int& nsp,
                                                     int4* units, int* jAtoms, unsigned unitCapacity, unsigned tileCapacity, DevCounters* counters) {
     unsigned imask = 0;
     if (single) {
@@ -177,8 +175,7 @@ __device__ __forceinline__ void nbProcessCandidates(int X, int lane, unsigned lt
     nbuf += __popc(mD); nsp += __popc(mS);
     __syncwarp();
     if (nbuf >= B200_UNIT_TILES * 32) {   // flush one full dense work unit
-        flushDense(X, w.dense, B200_UNIT_TILES, descW, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
-        descW = 0;
+        flushDense(X, w.dense, B200_UNIT_TILES, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
         const int rest = nbuf - B200_UNIT_TILES * 32;
         int carry = 0;
         if (lane < rest) carry = w.dense[B200_UNIT_TILES * 32 + lane];
@@ -257,26 +254,6 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
         }
         const int exBegin = exclRowStart[X], exEnd = exclRowStart[X + 1];
         int nbuf = 0, nsp = 0, nq = 0;
-        // The row's exclusion tiles -- the diagonal tile (X,X) and every (X,Y) joined by an exclusion -- lead its first work unit(s):
-        // their j "lists" are simply the 32 slots of block Y.  They used to be work units of their own (one tile each, 45 % of all
-        // unit set-ups on a water box); as members of the row's unit they share its set-up and its i-force flush.
-        int descW = 0;
-        {
-            const int nEx = 1 + exEnd - exBegin;
-            for (int k = 0; k < nEx; k++) {
-                const int Y = k == 0 ? X : exclRowCols[exBegin + k - 1];
-                if (nbuf == 0) descW = k << 16;
-                sBuf[warp][nbuf + lane] = Y * 32 + lane;
-                nbuf += 32; descW += 1 << 8;
-                if (nbuf == B200_UNIT_TILES * 32) {
-                    __syncwarp();
-                    flushDense(X, sBuf[warp], B200_UNIT_TILES, descW, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
-                    nbuf = 0; descW = 0;
-                    __syncwarp();
-                }
-            }
-            __syncwarp();
-        }
         for (int s0 = (X >> 5) & ~31; s0 < numSuper; s0 += 32) {   // candidates Y > X live in super blocks >= X/32
             const int s = s0 + lane;
             bool sHit = false;
@@ -314,7 +291,7 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
                     __syncwarp();
                     if (nq >= 32) {
                         const float4 q = sQ[warp][lane];
-                        nbProcessCandidates(X, lane, ltMask, true, __float_as_int(q.w), q.x, q.y, q.z, sX[warp], sXp[warp], single, box, rcp2, sparseMax, wb, nbuf, nsp, descW,
+                        nbProcessCandidates(X, lane, ltMask, true, __float_as_int(q.w), q.x, q.y, q.z, sX[warp], sXp[warp], single, box, rcp2, sparseMax, wb, nbuf, nsp,
                                             units, jAtoms, unitCapacity, tileCapacity, counters);
                         const int rest = nq - 32;
                         float4 carry = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -329,14 +306,14 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
         }
         if (nq > 0) {
             const float4 q = lane < nq ? sQ[warp][lane] : make_float4(0.f, 0.f, 0.f, 0.f);
-            nbProcessCandidates(X, lane, ltMask, lane < nq, __float_as_int(q.w), q.x, q.y, q.z, sX[warp], sXp[warp], single, box, rcp2, sparseMax, wb, nbuf, nsp, descW,
+            nbProcessCandidates(X, lane, ltMask, lane < nq, __float_as_int(q.w), q.x, q.y, q.z, sX[warp], sXp[warp], single, box, rcp2, sparseMax, wb, nbuf, nsp,
                                 units, jAtoms, unitCapacity, tileCapacity, counters);
         }
         if (nbuf > 0) {
             const int nt = (nbuf + 31) >> 5;
             for (int k = nbuf + lane; k < nt * 32; k += 32) sBuf[warp][k] = -1;
             __syncwarp();
-            flushDense(X, sBuf[warp], nt, descW, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
+            flushDense(X, sBuf[warp], nt, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
         }
         if (nsp > 0) {
             const int nt = (nsp + 31) >> 5;
@@ -354,7 +331,7 @@ __global__ void nbSetRebuild(DevCounters* counters) { counters->rebuild = 1; }
 void b200_nblist_alloc(b200_ctx* c) {
     dfree(c->units); dfree(c->jAtoms);
     if (c->tileCapacity == 0) {
-        c->tileCapacity = (long long)c->B * 28 + c->numExclTiles + 1024;
+        c->tileCapacity = (long long)c->B * 28 + 1024;
     }
     c->unitCapacity = std::max(c->unitCapacity, 2 * (long long)c->B + c->tileCapacity / 4 + 64);
     dmalloc(c->units, (size_t)c->unitCapacity);

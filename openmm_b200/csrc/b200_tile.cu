@@ -41,12 +41,12 @@ struct TileArgs {
     const int2* __restrict__ exclTiles;
     const unsigned int* __restrict__ exclFlags;
     const int* __restrict__ atomIndex;
-    const int* __restrict__ exclRowStart;
     long long* force;
     DevCounters* counters;
     int2* pairOut; long long pairCapacity;
     int N, Npad;
     unsigned unitCapacity;
+    int exclBegin, exclEnd;      // exclusion tiles handled by this rank
     BoxF box; BoxD boxD;
     float rc2, rcPadded, alpha2, alpha3, alpha, kcoul;
     double rc2d;
@@ -385,7 +385,8 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
     constexpr bool PACKED = !EMIT && !EXACT && !(LJMODE & 2);   // (the switching-function variant uses the scalar loop)   // FFMA2 path for the single-periodic-copy force/energy variants
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpSmem& sm = smAll[warp];
-    const unsigned total = min(a.counters->numUnits, a.unitCapacity);   // (an overflowed build counts past its storage)
+    const unsigned numExclUnits = (unsigned)(a.exclEnd - a.exclBegin);
+    const unsigned total = numExclUnits + min(a.counters->numUnits, a.unitCapacity);   // (an overflowed build counts past its storage)
     long long eAcc = 0; PairAcc nPairs = make_ulonglong2(0ull, 0ull);
 
     // Work units are taken from a device-side queue.  The descriptor of the NEXT unit is fetched while the current one is
@@ -393,7 +394,8 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
     // (the j atom data) instead of three dependent ones (descriptor -> j index -> j atom data).
     auto loadDesc = [&](unsigned w) -> int4 {
         if (w >= total) return make_int4(0, 0, 0, 0);
-        return a.units[w];
+        if (w < numExclUnits) { const int2 t = a.exclTiles[a.exclBegin + w]; return make_int4(t.x, t.y, 1, 0); }
+        return a.units[w - numExclUnits];
     };
     unsigned u = 0;
     if (lane == 0) u = atomicAdd(&a.counters->workNext, 1u);
@@ -411,15 +413,16 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
         };
         auto hintNext = [&]() {
             if (uNext >= total) return;
+            const bool ex = uNext < numExclUnits;
             const void* p0 = &a.posq[descNext.x * 32 + lane];
-            const void* p1 = (const void*)&a.jAtoms[(size_t)descNext.y * 32 + lane];
+            const void* p1 = ex ? (const void*)&a.posq[descNext.y * 32 + lane] : (const void*)&a.jAtoms[(size_t)descNext.y * 32 + lane];
             asm volatile("prefetch.global.L1 [%0];" :: "l"(p0));
             asm volatile("prefetch.global.L1 [%0];" :: "l"(p1));
         };
-        // the leading `numExcl` tiles of a dense unit are exclusion tiles of row x (flags of the row's tile exclFirst + t)
-        const int x = desc.x, tileStart = desc.y, nTiles = desc.z, kind = desc.w & 0xff, numExcl = (desc.w >> 8) & 0xff;
-        const size_t exclFirst = numExcl ? (size_t)(x + a.exclRowStart[x] + (desc.w >> 16)) : 0;
-        unsigned exclBits = numExcl ? a.exclFlags[exclFirst * 32 + lane] : 0u;
+        const bool excl = u < numExclUnits;
+        const int x = desc.x, tileStart = excl ? 0 : desc.y, nTiles = desc.z, kind = desc.w, yBlock = desc.y;
+        unsigned exclBits = 0;
+        if (excl) exclBits = a.exclFlags[(size_t)(a.exclBegin + u) * 32 + lane];
         const int slotI = x * 32 + lane;
         const float4 pi = a.posq[slotI];
         const float2 pri = a.sigEps[slotI];
@@ -443,13 +446,11 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
             float2 gix = dup(0.f), giy = dup(0.f), giz = dup(0.f);   // packed path: +sum of d*s for atom i (two partial sums)
             // two-deep software pipeline over the unit's tiles: the index of tile t+2 and the atom data of tile t+1 are in
             // flight while tile t is computed, so neither load latency is exposed (padding slots read atom 0 and are masked)
-            int ja = a.jAtoms[(size_t)tileStart * 32 + lane];
+            int ja = excl ? yBlock * 32 + lane : a.jAtoms[(size_t)tileStart * 32 + lane];
             int jaNext = (nTiles > 1) ? a.jAtoms[(size_t)(tileStart + 1) * 32 + lane] : -1;
             float4 pj = a.posq[max(ja, 0)]; float2 prj = a.sigEps[max(ja, 0)];
             for (int t = 0; t < nTiles; t++) {
                 const int jaCur = ja;
-                const bool excl = t < numExcl;
-                const unsigned exclNext = (t + 1 < numExcl) ? a.exclFlags[(exclFirst + t + 1) * 32 + lane] : 0u;
                 if (jaCur < 0) { pj.w = 0.f; prj = make_float2(0.f, 0.f); }
                 {   // stage tile t
                     float xj = pj.x, yj = pj.y, zj = pj.z;
@@ -501,7 +502,6 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
                     eAcc += toFixed(es);
                     eTile = 0.f;
                 }
-                exclBits = exclNext;
             }
             if (PACKED) { fix -= gix.x + gix.y; fiy -= giy.x + giy.y; fiz -= giz.x + giz.y; }
             if (FORCES && validI) {
@@ -586,7 +586,9 @@ void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
     a.atomIndex = c->atomIndex; a.force = c->force; a.counters = c->counters;
     a.pairOut = c->pairOut; a.pairCapacity = c->pairCapacity;
     a.N = c->N; a.Npad = c->Npad; a.unitCapacity = (unsigned)c->unitCapacity;
-    a.exclRowStart = c->exclRowStart;     // exclusion tiles travel with their row: they lead the row's first work unit
+    // exclusion tiles are split by index over ranks (CudaNonbondedUtilities.cpp:704-708)
+    a.exclBegin = (int)llround(c->numExclTiles * c->partShareBegin);
+    a.exclEnd = (int)llround(c->numExclTiles * c->partShareEnd);
     a.box = c->boxF; a.boxD = c->boxD;
     const double rc = c->nb.cutoff, al = c->nb.ewald_alpha;
     a.rc2 = (float)(rc * rc); a.rc2d = rc * rc; a.rcPadded = (float)c->paddedCutoff;
