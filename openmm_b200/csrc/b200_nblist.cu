@@ -202,7 +202,7 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
         const float4* __restrict__ superCenter, const float4* __restrict__ superHalf,
         const int* __restrict__ exclRowStart, const int* __restrict__ exclRowCols,
         int4* __restrict__ units, int* __restrict__ jAtoms, unsigned unitCapacity, unsigned tileCapacity,
-        int partRank, b200_ctx::OwnerTable table, DevCounters* counters) {
+        int partRank, b200_ctx::OwnerTable table, int split, DevCounters* counters) {
     if (!counters->rebuild) return;
     __shared__ float4 sX[NB_WARPS][32];
     __shared__ float4 sXp[NB_WARPS][32];    // the same atoms packed in pairs (i, i+16) for the FP32x2 exact test
@@ -230,7 +230,11 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
     __syncthreads();
     const int numRes = sNumRes;
     if (numRes == 0) return;
-    for (int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; ; k += warpsPerGrid) {
+    // Small systems have fewer rows than the GPU has warp slots (DHFR: 737 rows for 9472 slots) and a row's sweep is serial, so a
+    // row is shared by `split` warps: warp `part` takes the candidate super blocks sb with sb % split == part and emits its own work
+    // units.  `split` depends on the number of blocks only, so the unit composition is the same on any number of GPUs.
+    for (int kk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; ; kk += warpsPerGrid) {
+        const int k = kk / split, part = kk - k * split;
         const int period = k / numRes;
         if (period * 64 >= B) break;
         const int X = period * 64 + sRes[k - period * numRes];
@@ -261,6 +265,7 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
             unsigned sMaskBits = __ballot_sync(0xffffffffu, sHit);
             while (sMaskBits) {
                 const int sb = s0 + __ffs(sMaskBits) - 1; sMaskBits &= sMaskBits - 1;
+                if (split > 1 && sb % split != part) continue;
                 const int Y = sb * 32 + lane;
                 bool bHit = false;
                 if (Y < B && Y > X) {
@@ -359,11 +364,15 @@ void b200_nblist_prepare(b200_ctx* c) {
     int owned = 0;
     for (int i = 0; i < 64; i++) owned += c->partTable.owner[i] == c->partRank ? 1 : 0;
     int rows = (int)(((long long)c->B * owned + 63) / 64) + 1;
+    // rows shared by several warps on small systems (see nbBuild); B200_NB_SPLIT overrides the rule
+    int split = c->B >= 8192 ? 1 : c->B >= 4096 ? 2 : c->B >= 1024 ? 4 : 8;
+    { static const char* e = getenv("B200_NB_SPLIT"); if (e) split = std::max(1, std::min(16, atoi(e))); }
+    rows *= split;
     int buildGrid = (rows + NB_WARPS - 1) / NB_WARPS;
     if (buildGrid > c->smCount * 16) buildGrid = c->smCount * 16;
     nbBuild<<<buildGrid, NB_THREADS, 0, c->stream>>>(c->posq, c->N, c->B, c->numSuper, nbBox, rcp * rcp, c->sparseMax,
         c->blockCenter, c->blockHalf, c->superCenter, c->superHalf, c->exclRowStart, c->exclRowCols,
-        c->units, c->jAtoms, (unsigned)c->unitCapacity, (unsigned)c->tileCapacity, c->partRank, c->partTable, c->counters);
+        c->units, c->jAtoms, (unsigned)c->unitCapacity, (unsigned)c->tileCapacity, c->partRank, c->partTable, split, c->counters);
     nbFinish<<<1, 1, 0, c->stream>>>(c->counters);
     LAUNCH_COUNT(c, 4);
     CUDA_CHECK(cudaGetLastError());

@@ -322,8 +322,9 @@ void B200IntegrateVerletStepKernel::execute(ContextImpl&, const VerletIntegrator
 }
 double B200IntegrateVerletStepKernel::computeKineticEnergy(ContextImpl& context, const VerletIntegrator& integrator) {
     // leapfrog: the stored velocities are half a step behind the positions; report the energy of velocities shifted forward by dt/2
-    // with the current forces and constrained again (CommonKernels.cpp:3117 -> IntegrationUtilities::computeKineticEnergy)
-    context.calcForcesAndEnergy(true, false, integrator.getIntegrationForceGroups());
+    // with the forces that are in the buffer (Context::getState evaluates them first because kineticEnergyRequiresForce() is true;
+    // they must not be recomputed here: getState reads them afterwards) and constrained again (CommonKernels.cpp:3117 ->
+    // IntegrationUtilities::computeKineticEnergy)
     vector<double> ke(max<size_t>(1, d.ranks.size()), 0.0);
     d.all([&](b200_ctx* c, int r) { return b200_kinetic_energy_shifted(c, 0.5 * integrator.getStepSize(), &ke[r]); });
     return ke[0];
