@@ -337,6 +337,39 @@ extern "C" int b200_periodic_torsions_create(b200_ctx* c, int32_t n, const int32
     API_END
 }
 
+// updateParametersInContext of the bonded forces (kernels.h:359,433,507 copyParametersToContext): new parameters for the terms
+// [first, first+n) of one kind (0 bonds: length,k; 1 angles: angle,k; 2 torsions: phase,k + periodicity); the atoms of a term may not change.
+// Molecules whose terms changed stop being exchangeable with their former twins, so their group leaves the re-sort.
+extern "C" int b200_bonded_update_parameters(b200_ctx* c, int32_t kind, int32_t first, int32_t n, const double* p0, const double* p1, const int32_t* periodicity) {
+    API_BEGIN
+    if (!c || kind < 0 || kind > 2 || first < 0 || n < 0) throw B200Error(B200_ERR_INVALID, "b200_bonded_update_parameters: bad arguments");
+    std::vector<double>& prm = kind == 0 ? c->hBondParams : kind == 1 ? c->hAngleParams : c->hTorsionParams;
+    const std::vector<int>& atoms = kind == 0 ? c->hBondAtoms : kind == 1 ? c->hAngleAtoms : c->hTorsionAtoms;
+    const int width = kind == 0 ? 2 : kind == 1 ? 3 : 4;
+    if ((size_t)(first + n) * 2 > prm.size()) throw B200Error(B200_ERR_INVALID, "updateParametersInContext: The number of terms has changed");
+    CUDA_CHECK(cudaSetDevice(c->device));
+    std::set<int> changedMols;
+    for (int i = 0; i < n; i++) {
+        const size_t t = (size_t)first + i;
+        const bool diff = prm[2 * t] != p0[i] || prm[2 * t + 1] != p1[i] || (kind == 2 && c->hTorsionPeriod[t] != periodicity[i]);
+        prm[2 * t] = p0[i]; prm[2 * t + 1] = p1[i];
+        if (kind == 2) c->hTorsionPeriod[t] = periodicity[i];
+        if (diff && c->finalized) changedMols.insert(c->molBaseOf[atoms[width * t]]);
+    }
+    if (!c->finalized) return B200_OK;      // nothing is on the device yet
+    for (size_t gi = 0; gi < c->groups.size() && !changedMols.empty();) {
+        bool hit = false;
+        for (int b : c->groups[gi].base) if (changedMols.count(b)) { hit = true; break; }
+        if (hit && c->groups[gi].numMols > 1) { dfree(c->groups[gi].dBase); c->groups.erase(c->groups.begin() + gi); } else gi++;
+    }
+    // re-upload the parameter arrays of this kind (the index arrays stay)
+    if (kind == 0) { std::vector<float2> v; for (size_t t = 0; t * 2 < prm.size(); t++) v.push_back(make_float2((float)prm[2 * t], (float)prm[2 * t + 1])); if (!v.empty()) CUDA_CHECK(cudaMemcpy(c->bondParams, v.data(), sizeof(float2) * v.size(), cudaMemcpyHostToDevice)); }
+    else if (kind == 1) { std::vector<float2> v; for (size_t t = 0; t * 2 < prm.size(); t++) v.push_back(make_float2((float)prm[2 * t], (float)prm[2 * t + 1])); if (!v.empty()) CUDA_CHECK(cudaMemcpy(c->angleParams, v.data(), sizeof(float2) * v.size(), cudaMemcpyHostToDevice)); }
+    else { std::vector<float4> v; for (size_t t = 0; t * 2 < prm.size(); t++) v.push_back(make_float4((float)c->hTorsionPeriod[t], (float)prm[2 * t], (float)prm[2 * t + 1], 0.f)); if (!v.empty()) CUDA_CHECK(cudaMemcpy(c->torsionParams, v.data(), sizeof(float4) * v.size(), cudaMemcpyHostToDevice)); }
+    c->forcesValid = false;
+    API_END
+}
+
 // ---------------------------------------------------------------------------------------------
 // finalize: molecules, identical-molecule groups, SETTLE clusters, exclusion tiles
 static int ufFind(std::vector<int>& p, int i) { while (p[i] != i) { p[i] = p[p[i]]; i = p[i]; } return i; }

@@ -249,9 +249,13 @@ void B200CalcHarmonicBondForceKernel::initialize(const System&, const HarmonicBo
     vector<int> atoms(2 * (size_t)n); vector<double> len(n), k(n);
     for (int i = 0; i < n; i++) force.getBondParameters(i, atoms[2 * i], atoms[2 * i + 1], len[i], k[i]);
     d.all([&](b200_ctx* c, int) { return b200_harmonic_bonds_create(c, n, atoms.data(), len.data(), k.data(), force.getForceGroup()); });
+    firstTerm = d.bondedCount[0]; numTerms = n; d.bondedCount[0] += n;
 }
-void B200CalcHarmonicBondForceKernel::copyParametersToContext(ContextImpl&, const HarmonicBondForce&, int, int) {
-    throw OpenMMException("The B200 platform does not support updateParametersInContext for HarmonicBondForce yet");
+void B200CalcHarmonicBondForceKernel::copyParametersToContext(ContextImpl&, const HarmonicBondForce& force, int, int) {
+    if (force.getNumBonds() != numTerms) throw OpenMMException("updateParametersInContext: The number of bonds has changed");
+    vector<double> len(numTerms), k(numTerms);
+    for (int i = 0; i < numTerms; i++) { int a, b; force.getBondParameters(i, a, b, len[i], k[i]); }
+    d.all([&](b200_ctx* c, int) { return b200_bonded_update_parameters(c, 0, firstTerm, numTerms, len.data(), k.data(), nullptr); });
 }
 void B200CalcHarmonicAngleForceKernel::initialize(const System&, const HarmonicAngleForce& force) {
     checkBondedForce(d, 1, force, force.usesPeriodicBoundaryConditions(), "HarmonicAngleForce");
@@ -259,9 +263,13 @@ void B200CalcHarmonicAngleForceKernel::initialize(const System&, const HarmonicA
     vector<int> atoms(3 * (size_t)n); vector<double> ang(n), k(n);
     for (int i = 0; i < n; i++) force.getAngleParameters(i, atoms[3 * i], atoms[3 * i + 1], atoms[3 * i + 2], ang[i], k[i]);
     d.all([&](b200_ctx* c, int) { return b200_harmonic_angles_create(c, n, atoms.data(), ang.data(), k.data(), force.getForceGroup()); });
+    firstTerm = d.bondedCount[1]; numTerms = n; d.bondedCount[1] += n;
 }
-void B200CalcHarmonicAngleForceKernel::copyParametersToContext(ContextImpl&, const HarmonicAngleForce&, int, int) {
-    throw OpenMMException("The B200 platform does not support updateParametersInContext for HarmonicAngleForce yet");
+void B200CalcHarmonicAngleForceKernel::copyParametersToContext(ContextImpl&, const HarmonicAngleForce& force, int, int) {
+    if (force.getNumAngles() != numTerms) throw OpenMMException("updateParametersInContext: The number of angles has changed");
+    vector<double> ang(numTerms), k(numTerms);
+    for (int i = 0; i < numTerms; i++) { int a, b, c2; force.getAngleParameters(i, a, b, c2, ang[i], k[i]); }
+    d.all([&](b200_ctx* c, int) { return b200_bonded_update_parameters(c, 1, firstTerm, numTerms, ang.data(), k.data(), nullptr); });
 }
 void B200CalcPeriodicTorsionForceKernel::initialize(const System&, const PeriodicTorsionForce& force) {
     checkBondedForce(d, 2, force, force.usesPeriodicBoundaryConditions(), "PeriodicTorsionForce");
@@ -269,9 +277,13 @@ void B200CalcPeriodicTorsionForceKernel::initialize(const System&, const Periodi
     vector<int> atoms(4 * (size_t)n), per(n); vector<double> phase(n), k(n);
     for (int i = 0; i < n; i++) force.getTorsionParameters(i, atoms[4 * i], atoms[4 * i + 1], atoms[4 * i + 2], atoms[4 * i + 3], per[i], phase[i], k[i]);
     d.all([&](b200_ctx* c, int) { return b200_periodic_torsions_create(c, n, atoms.data(), per.data(), phase.data(), k.data(), force.getForceGroup()); });
+    firstTerm = d.bondedCount[2]; numTerms = n; d.bondedCount[2] += n;
 }
-void B200CalcPeriodicTorsionForceKernel::copyParametersToContext(ContextImpl&, const PeriodicTorsionForce&, int, int) {
-    throw OpenMMException("The B200 platform does not support updateParametersInContext for PeriodicTorsionForce yet");
+void B200CalcPeriodicTorsionForceKernel::copyParametersToContext(ContextImpl&, const PeriodicTorsionForce& force, int, int) {
+    if (force.getNumTorsions() != numTerms) throw OpenMMException("updateParametersInContext: The number of torsions has changed");
+    vector<double> phase(numTerms), k(numTerms); vector<int> per(numTerms);
+    for (int i = 0; i < numTerms; i++) { int a, b, c2, e; force.getTorsionParameters(i, a, b, c2, e, per[i], phase[i], k[i]); }
+    d.all([&](b200_ctx* c, int) { return b200_bonded_update_parameters(c, 2, firstTerm, numTerms, phase.data(), k.data(), per.data()); });
 }
 
 // ---------------------------------------------------------------------------------------------- Monte Carlo barostat

@@ -100,6 +100,7 @@ public:
     void copyParametersToContext(ContextImpl& context, const OpenMM::HarmonicBondForce& force, int firstBond, int lastBond) override;
 private:
     PData& d;
+    int firstTerm = 0, numTerms = 0;
 };
 class B200CalcHarmonicAngleForceKernel : public OpenMM::CalcHarmonicAngleForceKernel {
 public:
@@ -109,6 +110,7 @@ public:
     void copyParametersToContext(ContextImpl& context, const OpenMM::HarmonicAngleForce& force, int firstAngle, int lastAngle) override;
 private:
     PData& d;
+    int firstTerm = 0, numTerms = 0;
 };
 class B200CalcPeriodicTorsionForceKernel : public OpenMM::CalcPeriodicTorsionForceKernel {
 public:
@@ -118,6 +120,7 @@ public:
     void copyParametersToContext(ContextImpl& context, const OpenMM::PeriodicTorsionForce& force, int firstTorsion, int lastTorsion) override;
 private:
     PData& d;
+    int firstTerm = 0, numTerms = 0;
 };
 
 // kernels.h:1793-1815

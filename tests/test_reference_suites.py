@@ -33,6 +33,12 @@ MUST_PASS = {
 }
 
 
+# further suites of the reference, run for the record (their failing tests name features outside the scope table: periodic bonded
+# forces, updateParametersInContext of bonded forces, general constraint topologies, ...); what passes today is asserted as well
+MUST_PASS.update({"suite_bonds": [], "suite_angles": [], "suite_torsions": [], "suite_verlet": [], "suite_langevinmiddle": [], "suite_settle": [],
+                  "suite_checkpoints": [], "suite_minimizer": []})
+
+
 @pytest.mark.parametrize("suite", sorted(MUST_PASS))
 def test_reference_suite_on_b200_platform(suite):
     exe = os.path.join(REF_DIR, suite)
