@@ -365,7 +365,7 @@ void b200_nblist_prepare(b200_ctx* c) {
     for (int i = 0; i < 64; i++) owned += c->partTable.owner[i] == c->partRank ? 1 : 0;
     int rows = (int)(((long long)c->B * owned + 63) / 64) + 1;
     // rows shared by several warps on small systems (see nbBuild); B200_NB_SPLIT overrides the rule
-    int split = c->B >= 8192 ? 1 : c->B >= 4096 ? 2 : c->B >= 1024 ? 4 : 8;
+    int split = c->B < 1536 ? 8 : 1;      // measured: DHFR (737 rows) 128 -> 116 us/step with 8; ApoA1 (2882 rows) and larger are best unsplit
     { static const char* e = getenv("B200_NB_SPLIT"); if (e) split = std::max(1, std::min(16, atoi(e))); }
     rows *= split;
     int buildGrid = (rows + NB_WARPS - 1) / NB_WARPS;

@@ -139,29 +139,24 @@ struct PlaneUnits {
     }
 };
 
-// Fast path for the usual case of an x plane of the tile holding at most 32*PLANE_SLOTS points: every lane precomputes, once,
-// the global offset (inside an x plane of the grid) of the plane entries lane, lane+32, ...; a plane is then moved with one
-// shared-memory access, one add and one global access per 32 points, all lanes busy.
-#define PLANE_SLOTS 16
-struct PlaneMap {
-    int off[PLANE_SLOTS];   // gy*nz + gz of plane entry lane + 32*m  (-1: beyond the plane)
-    int slots, planeSize, planeStride;
-    __device__ __forceinline__ bool init(const ChunkBox& box, const PmeArgs& a) {
-        const int ey = box.ext[1], ez = box.ext[2], lane = threadIdx.x & 31;
-        planeSize = ey * ez; planeStride = a.ny * a.nz; slots = (planeSize + 31) >> 5;
-        if (slots > PLANE_SLOTS) return false;
-        const float invEz = 1.0f / (float)ez;
-#pragma unroll
-        for (int m = 0; m < PLANE_SLOTS; m++) {
-            const int e = lane + 32 * m;
-            const int y = (int)(((float)e + 0.5f) * invEz), z = e - y * ez;     // exact for e < 2^20
-            int gy = box.org[1] + y; gy -= gy >= a.ny ? a.ny : 0;
-            int gz = box.org[2] + z; gz -= gz >= a.nz ? a.nz : 0;
-            off[m] = e < planeSize ? gy * a.nz + gz : -1;
-        }
-        return true;
+// Fast path for the usual case of an x plane of the tile holding at most PLANE_MAX points: the CTA computes, once, the global
+// offset (inside an x plane of the grid) of every entry of a tile plane into a small shared table.  A plane is then moved by a flat
+// loop -- one table look-up, one shared-memory access and one global access per point, no index arithmetic or predicates per point
+// (the round-1 version kept 16 offsets per lane in registers; ncu showed half of the kernel's instructions were the predicate and
+// integer bookkeeping around them: ISETP/IADD3/LOP3/LEA/P2R 47 % of the interpolation kernel, 6 % useful FFMA2).
+#define PLANE_MAX 640
+__device__ __forceinline__ bool planeOffsets(const ChunkBox& box, const PmeArgs& a, int* goff /*[PLANE_MAX] shared*/) {
+    const int ey = box.ext[1], ez = box.ext[2], planeSize = ey * ez;
+    if (planeSize > PLANE_MAX) return false;
+    const float invEz = 1.0f / (float)ez;
+    for (int e = threadIdx.x; e < planeSize; e += CHUNK) {
+        const int y = (int)(((float)e + 0.5f) * invEz), z = e - y * ez;     // exact for e < 2^20
+        int gy = box.org[1] + y; gy -= gy >= a.ny ? a.ny : 0;
+        int gz = box.org[2] + z; gz -= gz >= a.nz ? a.nz : 0;
+        goff[e] = gy * a.nz + gz;
     }
-};
+    return true;
+}
 
 // Bank-aware assignment of the chunk's atoms to threads.  Every thread walks the same 125 stencil offsets, so the shared-memory
 // bank a lane hits at each step is (its atom's base index + a common offset) mod 32: two lanes collide on ALL 125 accesses when
@@ -201,6 +196,7 @@ __global__ void __launch_bounds__(CHUNK) pmeSpreadChunks(const float4* __restric
     __shared__ int sh[10];
     __shared__ int binCount[32];
     __shared__ int perm[CHUNK];
+    __shared__ int goff[PLANE_MAX];
     int i = blockIdx.x * CHUNK + threadIdx.x;
     float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
     if (i < N) { p = posq[i]; if (sigEps) p.w = dispersionCoefficient(sigEps[i]); }
@@ -241,19 +237,19 @@ __global__ void __launch_bounds__(CHUNK) pmeSpreadChunks(const float4* __restric
                 }
             }
         }
+        const bool flat = planeOffsets(box, a, goff);
         __syncthreads();
-        PlaneMap pm;
-        if (pm.init(box, a)) {
-            const int lane = threadIdx.x & 31;
+        if (flat) {
+            const int lane = threadIdx.x & 31, planeSize = box.ext[1] * box.ext[2], planeStride = a.ny * a.nz;
             for (int x = threadIdx.x >> 5; x < box.ext[0]; x += CHUNK_WARPS) {
                 int gx = box.org[0] + x; gx -= gx >= a.nx ? a.nx : 0;
-                int* gp = grid + (size_t)gx * pm.planeStride;
-                const int* tp = tile + x * pm.planeSize + lane;
-                int v[PLANE_SLOTS];
-#pragma unroll
-                for (int m = 0; m < PLANE_SLOTS; m++) v[m] = (m < pm.slots && pm.off[m] >= 0) ? tp[32 * m] : 0;
-#pragma unroll
-                for (int m = 0; m < PLANE_SLOTS; m++) if (v[m] != 0) atomicAdd(gp + pm.off[m], v[m]);
+                int* gp = grid + (size_t)gx * planeStride;
+                const int* tp = tile + x * planeSize;
+#pragma unroll 4
+                for (int e = lane; e < planeSize; e += 32) {
+                    const int v = tp[e];
+                    if (v != 0) atomicAdd(gp + goff[e], v);
+                }
             }
         } else {
             int v[ROW_BATCH];
@@ -296,6 +292,7 @@ __global__ void __launch_bounds__(CHUNK, 6) pmeInterpolateChunks(const float4* _
     __shared__ int sh[10];
     __shared__ int binCount[32];
     __shared__ int perm[CHUNK];
+    __shared__ int goff[PLANE_MAX];
     int i = blockIdx.x * CHUNK + threadIdx.x;
     float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
     if (i < N) { p = posq[i]; if (sigEps) p.w = dispersionCoefficient(sigEps[i]); }
@@ -317,18 +314,21 @@ __global__ void __launch_bounds__(CHUNK, 6) pmeInterpolateChunks(const float4* _
     float wx[5], wy[5], wz[5], ex[5], ey5[5], ez5[5];
     float gx = 0.f, gy = 0.f, gz = 0.f;
     if (box.vol > 0) {
-        PlaneMap pm;
-        if (pm.init(box, a)) {
-            const int lane = threadIdx.x & 31;
+        const bool flat = planeOffsets(box, a, goff);
+        __syncthreads();
+        if (flat) {
+            const int lane = threadIdx.x & 31, planeSize = box.ext[1] * box.ext[2], planeStride = a.ny * a.nz;
             for (int x = threadIdx.x >> 5; x < box.ext[0]; x += CHUNK_WARPS) {
                 int gx = box.org[0] + x; gx -= gx >= a.nx ? a.nx : 0;
-                const float* gp = phi + (size_t)gx * pm.planeStride;
-                float* tp = tile + x * pm.planeSize + lane;
-                float v[PLANE_SLOTS];
+                const float* gp = phi + (size_t)gx * planeStride;
+                float* tp = tile + x * planeSize;
+                for (int e0 = lane; e0 < planeSize; e0 += 256) {      // eight independent loads in flight per lane
+                    float v[8];
 #pragma unroll
-                for (int m = 0; m < PLANE_SLOTS; m++) v[m] = (m < pm.slots && pm.off[m] >= 0) ? gp[pm.off[m]] : 0.f;
+                    for (int k = 0; k < 8; k++) { const int e = e0 + 32 * k; v[k] = e < planeSize ? gp[goff[e]] : 0.f; }
 #pragma unroll
-                for (int m = 0; m < PLANE_SLOTS; m++) if (m < pm.slots && pm.off[m] >= 0) tp[32 * m] = v[m];
+                    for (int k = 0; k < 8; k++) { const int e = e0 + 32 * k; if (e < planeSize) tp[e] = v[k]; }
+                }
             }
         } else {
             float v[ROW_BATCH];
