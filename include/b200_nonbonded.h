@@ -106,6 +106,8 @@ int  b200_harmonic_angles_create(b200_ctx* ctx, int32_t n, const int32_t* atoms 
 /* CalcPeriodicTorsionForceKernel::initialize (kernels.h:495), periodicTorsionForce.cc: E = k (1+cos(n phi - phi0)) */
 int  b200_periodic_torsions_create(b200_ctx* ctx, int32_t n, const int32_t* atoms /*[4n]*/, const int32_t* periodicity, const double* phase, const double* k, int32_t group);
 
+/* HarmonicBondForce/HarmonicAngleForce/PeriodicTorsionForce::setUsesPeriodicBoundaryConditions for all terms of one kind (0, 1, 2) */
+int  b200_bonded_set_periodic(b200_ctx* ctx, int32_t kind, int32_t periodic);
 /* copyParametersToContext of the three bonded kernels (kernels.h:359,433,507): new parameters for terms [first, first+n) of kind
  * 0 = bonds (p0 length, p1 k), 1 = angles (p0 angle, p1 k), 2 = torsions (p0 phase, p1 k, periodicity); term indices count over all
  * forces of that kind in the order they were created */

@@ -96,13 +96,16 @@ __global__ void __launch_bounds__(128) exceptions14(const float4* __restrict__ p
     if (wantEnergy) blockEnergy(e, &counters->energy[E_EXCEPT]);
 }
 
+// `periodic`: HarmonicBondForce::setUsesPeriodicBoundaryConditions -- every displacement is replaced by its nearest periodic image
+// (harmonicBondForce.cc APPLY_PERIODIC_TO_DELTA); likewise for angles and torsions below
 __global__ void __launch_bounds__(128) harmonicBonds(const float4* __restrict__ posq, const int2* __restrict__ atoms, const float2* __restrict__ params, int n,
-                                                      long long* force, int Npad, DevCounters* counters, int wantForce, int wantEnergy) {
+                                                      BoxD box, int periodic, long long* force, int Npad, DevCounters* counters, int wantForce, int wantEnergy) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     double e = 0;
     if (t < n) {
         const int2 a = atoms[t]; const float2 prm = params[t];   // (r0, k)
-        const D3 d = loadPos(posq, a.y) - loadPos(posq, a.x);
+        D3 d = loadPos(posq, a.y) - loadPos(posq, a.x);
+        if (periodic) imageDeltaD(d.x, d.y, d.z, box);
         const double r = sqrt(dot(d, d)), dr = r - prm.x;
         e = 0.5 * prm.y * dr * dr;
         if (wantForce && r > 0) {
@@ -115,13 +118,14 @@ __global__ void __launch_bounds__(128) harmonicBonds(const float4* __restrict__ 
 }
 
 __global__ void __launch_bounds__(128) harmonicAngles(const float4* __restrict__ posq, const int4* __restrict__ atoms, const float2* __restrict__ params, int n,
-                                                       long long* force, int Npad, DevCounters* counters, int wantForce, int wantEnergy) {
+                                                       BoxD box, int periodic, long long* force, int Npad, DevCounters* counters, int wantForce, int wantEnergy) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     double e = 0;
     if (t < n) {
         const int4 a = atoms[t]; const float2 prm = params[t];   // (theta0, k), atom y is the vertex
         const D3 pb = loadPos(posq, a.y);
-        const D3 v0 = loadPos(posq, a.x) - pb, v1 = loadPos(posq, a.z) - pb;
+        D3 v0 = loadPos(posq, a.x) - pb, v1 = loadPos(posq, a.z) - pb;
+        if (periodic) { imageDeltaD(v0.x, v0.y, v0.z, box); imageDeltaD(v1.x, v1.y, v1.z, box); }
         const D3 cp = cross(v0, v1);
         const double rp = fmax(sqrt(dot(cp, cp)), 1e-6), r0 = dot(v0, v0), r1 = dot(v1, v1);
         double c = dot(v0, v1) / sqrt(r0 * r1);
@@ -141,13 +145,14 @@ __global__ void __launch_bounds__(128) harmonicAngles(const float4* __restrict__
 }
 
 __global__ void __launch_bounds__(128) periodicTorsions(const float4* __restrict__ posq, const int4* __restrict__ atoms, const float4* __restrict__ params, int n,
-                                                         long long* force, int Npad, DevCounters* counters, int wantForce, int wantEnergy) {
+                                                         BoxD box, int periodic, long long* force, int Npad, DevCounters* counters, int wantForce, int wantEnergy) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     double e = 0;
     if (t < n) {
         const int4 a = atoms[t]; const float4 prm = params[t];   // (periodicity, phase, k)
         const D3 p1 = loadPos(posq, a.x), p2 = loadPos(posq, a.y), p3 = loadPos(posq, a.z), p4 = loadPos(posq, a.w);
-        const D3 b1 = p2 - p1, b2 = p3 - p2, b3 = p4 - p3;
+        D3 b1 = p2 - p1, b2 = p3 - p2, b3 = p4 - p3;
+        if (periodic) { imageDeltaD(b1.x, b1.y, b1.z, box); imageDeltaD(b2.x, b2.y, b2.z, box); imageDeltaD(b3.x, b3.y, b3.z, box); }
         const D3 n1 = cross(b1, b2), n2 = cross(b2, b3);
         const double lb2 = sqrt(dot(b2, b2));
         // IUPAC dihedral: phi = atan2(|b2| b1.(b2 x b3), (b1 x b2).(b2 x b3))
@@ -235,9 +240,9 @@ void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy) 
         if (c->numExceptions > 0) { exceptions14<<<(c->numExceptions + 127) / 128, 128, 0, s>>>(c->posq, c->dExcPairs, c->dExcParams, c->numExceptions, c->boxD, c->nb.exceptions_use_periodic, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
     }
     {
-        if (c->numBonds > 0 && (groups & B200_GROUP_BONDS)) { harmonicBonds<<<(c->numBonds + 127) / 128, 128, 0, s>>>(c->posq, c->bondAtoms, c->bondParams, c->numBonds, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
-        if (c->numAngles > 0 && (groups & B200_GROUP_ANGLES)) { harmonicAngles<<<(c->numAngles + 127) / 128, 128, 0, s>>>(c->posq, c->angleAtoms, c->angleParams, c->numAngles, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
-        if (c->numTorsions > 0 && (groups & B200_GROUP_TORSIONS)) { periodicTorsions<<<(c->numTorsions + 127) / 128, 128, 0, s>>>(c->posq, c->torsionAtoms, c->torsionParams, c->numTorsions, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
+        if (c->numBonds > 0 && (groups & B200_GROUP_BONDS)) { harmonicBonds<<<(c->numBonds + 127) / 128, 128, 0, s>>>(c->posq, c->bondAtoms, c->bondParams, c->numBonds, c->boxD, c->bondedPeriodic[0], c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
+        if (c->numAngles > 0 && (groups & B200_GROUP_ANGLES)) { harmonicAngles<<<(c->numAngles + 127) / 128, 128, 0, s>>>(c->posq, c->angleAtoms, c->angleParams, c->numAngles, c->boxD, c->bondedPeriodic[1], c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
+        if (c->numTorsions > 0 && (groups & B200_GROUP_TORSIONS)) { periodicTorsions<<<(c->numTorsions + 127) / 128, 128, 0, s>>>(c->posq, c->torsionAtoms, c->torsionParams, c->numTorsions, c->boxD, c->bondedPeriodic[2], c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
     }
     CUDA_CHECK(cudaGetLastError());
 }

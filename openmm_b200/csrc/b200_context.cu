@@ -126,6 +126,7 @@ extern "C" void b200_context_destroy(b200_ctx* c) {
     dfree(c->blockCenter); dfree(c->blockHalf); dfree(c->superCenter); dfree(c->superHalf); dfree(c->refPosq);
     dfree(c->units); dfree(c->jAtoms); dfree(c->pairOut);
     dfree(c->settleAtoms); dfree(c->settleParams); dfree(c->freeAtoms); dfree(c->shakeAtoms); dfree(c->shakeDist);
+    dfree(c->gcPairs); dfree(c->gcDist); dfree(c->gcColorStart); dfree(c->gcClusterColors); dfree(c->gcAtomStart); dfree(c->gcAtomList); dfree(c->gcDelta); dfree(c->gcOld);
     dfree(c->exclTiles); dfree(c->exclFlags); dfree(c->exclRowStart); dfree(c->exclRowCols); dfree(c->dExclPairs); dfree(c->dExcPairs); dfree(c->dExcParams);
     dfree(c->bondAtoms); dfree(c->bondParams); dfree(c->angleAtoms); dfree(c->angleParams); dfree(c->torsionAtoms); dfree(c->torsionParams);
     dfree(c->molStart); dfree(c->molSlots); dfree(c->savedPosq); dfree(c->savedPosqCorr); dfree(c->savedVelm); dfree(c->savedAtomIndex); dfree(c->savedCellOffsets);
@@ -337,6 +338,12 @@ extern "C" int b200_periodic_torsions_create(b200_ctx* c, int32_t n, const int32
     API_END
 }
 
+extern "C" int b200_bonded_set_periodic(b200_ctx* c, int32_t kind, int32_t periodic) {
+    if (!c || kind < 0 || kind > 2) { b200_set_error("b200_bonded_set_periodic: bad arguments"); return B200_ERR_INVALID; }
+    c->bondedPeriodic[kind] = periodic ? 1 : 0;
+    return B200_OK;
+}
+
 // updateParametersInContext of the bonded forces (kernels.h:359,433,507 copyParametersToContext): new parameters for the terms
 // [first, first+n) of one kind (0 bonds: length,k; 1 angles: angle,k; 2 torsions: phase,k + periodicity); the atoms of a term may not change.
 // Molecules whose terms changed stop being exchangeable with their former twins, so their group leaves the re-sort.
@@ -516,14 +523,54 @@ void b200_finalize(b200_ctx* c) {
                 CUDA_CHECK(cudaMemcpy(c->shakeDist, kd.data(), sizeof(float4) * kd.size(), cudaMemcpyHostToDevice));
             }
         }
-        std::vector<int> freeAtoms;
-        c->numOtherConstraints = 0;
-        for (int i = 0; i < N; i++) {
-            if (inCluster[i]) continue;
-            if (!con[i].empty()) c->numOtherConstraints += (int)con[i].size();
-            else if (c->mass[i] > 0) freeAtoms.push_back(i);
+        // ---- everything else: general clusters (connected components of the remaining constraints), solved iteratively by one CTA
+        // each with the constraints processed colour by colour (CCMA's job in the reference, integrationUtilities.cc:582-804)
+        {
+            std::vector<int> cp(N); std::iota(cp.begin(), cp.end(), 0);
+            std::vector<int> rest;
+            for (int k = 0; k < c->numConstraints; k++) {
+                const int a = c->conAtoms[2 * k], b = c->conAtoms[2 * k + 1];
+                if (inCluster[a] || inCluster[b]) continue;
+                rest.push_back(k);
+                int ra = ufFind(cp, a), rb = ufFind(cp, b); if (ra != rb) cp[std::max(ra, rb)] = std::min(ra, rb);
+            }
+            std::map<int, std::vector<int>> clusters;      // root atom -> constraint indices
+            for (int k : rest) clusters[ufFind(cp, c->conAtoms[2 * k])].push_back(k);
+            std::vector<int2> pairs; std::vector<double> dist; std::vector<int> colorStart, atomStart(1, 0), atomList; std::vector<int2> clusterColors;
+            for (auto& kv : clusters) {
+                // greedy colouring: a constraint takes the smallest colour none of its two atoms has used yet
+                std::map<int, std::set<int>> used; std::vector<int> colourOf(kv.second.size()); int ncol = 0;
+                for (size_t q = 0; q < kv.second.size(); q++) {
+                    const int a = c->conAtoms[2 * kv.second[q]], b = c->conAtoms[2 * kv.second[q] + 1];
+                    int col = 0; while (used[a].count(col) || used[b].count(col)) col++;
+                    used[a].insert(col); used[b].insert(col); colourOf[q] = col; ncol = std::max(ncol, col + 1);
+                }
+                clusterColors.push_back(make_int2((int)colorStart.size(), ncol));
+                for (int col = 0; col < ncol; col++) {
+                    colorStart.push_back((int)pairs.size());
+                    for (size_t q = 0; q < kv.second.size(); q++) if (colourOf[q] == col) {
+                        pairs.push_back(make_int2(c->conAtoms[2 * kv.second[q]], c->conAtoms[2 * kv.second[q] + 1])); dist.push_back(c->conDist[kv.second[q]]);
+                    }
+                }
+                colorStart.push_back((int)pairs.size());
+                for (auto& u : used) { atomList.push_back(u.first); inCluster[u.first] = 1; }
+                atomStart.push_back((int)atomList.size());
+            }
+            c->numGc = (int)pairs.size(); c->numGcClusters = (int)clusterColors.size();
+            if (c->numGc > 0) {
+                dmalloc(c->gcPairs, pairs.size()); dmalloc(c->gcDist, dist.size()); dmalloc(c->gcColorStart, colorStart.size()); dmalloc(c->gcClusterColors, clusterColors.size());
+                dmalloc(c->gcAtomStart, atomStart.size()); dmalloc(c->gcAtomList, atomList.size()); dmalloc(c->gcDelta, (size_t)c->Npad); dmalloc(c->gcOld, (size_t)c->Npad);
+                CUDA_CHECK(cudaMemcpy(c->gcPairs, pairs.data(), sizeof(int2) * pairs.size(), cudaMemcpyHostToDevice));
+                CUDA_CHECK(cudaMemcpy(c->gcDist, dist.data(), sizeof(double) * dist.size(), cudaMemcpyHostToDevice));
+                CUDA_CHECK(cudaMemcpy(c->gcColorStart, colorStart.data(), sizeof(int) * colorStart.size(), cudaMemcpyHostToDevice));
+                CUDA_CHECK(cudaMemcpy(c->gcClusterColors, clusterColors.data(), sizeof(int2) * clusterColors.size(), cudaMemcpyHostToDevice));
+                CUDA_CHECK(cudaMemcpy(c->gcAtomStart, atomStart.data(), sizeof(int) * atomStart.size(), cudaMemcpyHostToDevice));
+                CUDA_CHECK(cudaMemcpy(c->gcAtomList, atomList.data(), sizeof(int) * atomList.size(), cudaMemcpyHostToDevice));
+            }
         }
-        c->numOtherConstraints /= 2;
+        std::vector<int> freeAtoms;
+        c->numOtherConstraints = 0;      // every constraint now belongs to a SETTLE molecule, a SHAKE star or a general cluster
+        for (int i = 0; i < N; i++) if (!inCluster[i] && c->mass[i] > 0) freeAtoms.push_back(i);
         c->numFree = (int)freeAtoms.size();
         c->hFreeAtoms = freeAtoms;
         dmalloc(c->freeAtoms, freeAtoms.size());
@@ -1109,7 +1156,7 @@ void b200_ensure_forces_reduced(b200_ctx* c) {
 // contiguous slot ranges, and no constraint kind that is not sharded yet.
 static bool peerStepPlan(b200_ctx* c) {
     { static const bool fp = getenv("B200_FUSED_PUBLISH") != nullptr; c->fusedPublish = fp; }
-    bool active = c->peerMode && c->commRanks > 1 && c->integ.remove_cm_every <= 1 && c->hasNonbonded && c->numShake == 0;
+    bool active = c->peerMode && c->commRanks > 1 && c->integ.remove_cm_every <= 1 && c->hasNonbonded && c->numShake == 0 && c->numGc == 0;
     if (active) {
         b200_peer_plan_shard(c);
         // Slices whose atoms are not one contiguous range of slots (units listed out of slot order) would need the per-atom peer

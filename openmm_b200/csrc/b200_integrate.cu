@@ -325,6 +325,136 @@ __global__ void shakeOnly(IntegArgs a, int numShake, const int4* __restrict__ sh
     }
 }
 
+// ---- general constraint clusters.  Whatever is neither a rigid 3-site molecule nor a SHAKE star (all-bonds or angle constraints,
+// chains, rings) is solved the way CCMA is used in the reference (integrationUtilities.cc:582-804): iteratively to the tolerance.
+// One CTA owns one connected cluster; its constraints are ordered by colour (no two constraints of a colour share an atom), so the
+// threads of the CTA update a whole colour in parallel and a sweep over the colours is a Gauss-Seidel sweep over the cluster.  The
+// working copies (velocities in velm, displacements in gcDelta) live in global memory; __syncthreads orders the colours.
+#define GC_THREADS 128
+#define GC_MAX_ITER 500
+struct GcArgs { const int2* pairs; const double* dist; const int* colorStart; const int2* clusterColors; const int* atomStart; const int* atomList; double4* delta; double4* old; double tol; };
+
+__device__ __forceinline__ void gcVelocitySweeps(const IntegArgs& a, const GcArgs& g, int first, int ncol, int* flag) {
+    for (int it = 0; it < GC_MAX_ITER; it++) {
+        __syncthreads();
+        if (threadIdx.x == 0) *flag = 0;
+        __syncthreads();
+        for (int col = 0; col < ncol; col++) {
+            for (int q = g.colorStart[first + col] + threadIdx.x; q < g.colorStart[first + col + 1]; q += blockDim.x) {
+                const int2 p = g.pairs[q];
+                const V3 s = loadPosD(a, p.y) - loadPosD(a, p.x);
+                double4 vi = a.velm[p.x], vj = a.velm[p.y];
+                const double s2 = dot(s, s), vrel = (vj.x - vi.x) * s.x + (vj.y - vi.y) * s.y + (vj.z - vi.z) * s.z;
+                if (fabs(vrel) * (a.dt > 0 ? a.dt : 0.001) > g.tol * s2) *flag = 1;
+                const double lam = -vrel / ((vi.w + vj.w) * s2);
+                vj.x += s.x * lam * vj.w; vj.y += s.y * lam * vj.w; vj.z += s.z * lam * vj.w;
+                vi.x -= s.x * lam * vi.w; vi.y -= s.y * lam * vi.w; vi.z -= s.z * lam * vi.w;
+                a.velm[p.x] = vi; a.velm[p.y] = vj;
+            }
+            __syncthreads();
+        }
+        if (!*flag) break;
+    }
+}
+__device__ __forceinline__ void gcPositionSweeps(const IntegArgs& a, const GcArgs& g, int first, int ncol, int* flag) {
+    for (int it = 0; it < GC_MAX_ITER; it++) {
+        __syncthreads();
+        if (threadIdx.x == 0) *flag = 0;
+        __syncthreads();
+        for (int col = 0; col < ncol; col++) {
+            for (int q = g.colorStart[first + col] + threadIdx.x; q < g.colorStart[first + col + 1]; q += blockDim.x) {
+                const int2 p = g.pairs[q];
+                const V3 s = loadPosD(a, p.y) - loadPosD(a, p.x);
+                double4 di = g.delta[p.x], dj = g.delta[p.y];
+                const V3 sp = {s.x + dj.x - di.x, s.y + dj.y - di.y, s.z + dj.z - di.z};
+                const double imi = a.velm[p.x].w, imj = a.velm[p.y].w;
+                const double d2 = g.dist[q] * g.dist[q], diff = d2 - dot(sp, sp);
+                if (fabs(diff) > 2.0 * g.tol * d2) *flag = 1;
+                const double lam = diff / (2.0 * (imi + imj) * dot(s, sp));
+                dj.x += s.x * lam * imj; dj.y += s.y * lam * imj; dj.z += s.z * lam * imj;
+                di.x -= s.x * lam * imi; di.y -= s.y * lam * imi; di.z -= s.z * lam * imi;
+                g.delta[p.x] = di; g.delta[p.y] = dj;
+            }
+            __syncthreads();
+        }
+        if (!*flag) break;
+    }
+}
+
+// mode 0: full LangevinMiddle step of the cluster's atoms; 1: velocity constraints only; 2: position constraints only
+__global__ void __launch_bounds__(GC_THREADS) generalClusterStep(IntegArgs a, GcArgs g, int mode) {
+    __shared__ int flag;
+    const int k = blockIdx.x;
+    const int2 cc = g.clusterColors[k];
+    const int aBegin = g.atomStart[k], aEnd = g.atomStart[k + 1];
+    const double halfdt = 0.5 * a.dt, invDt = a.dt > 0 ? 1.0 / a.dt : 0.0;
+    V3 vcm = {0, 0, 0}, mom = {0, 0, 0};
+    bool moved = false;
+    if (mode == 0) {
+        if (a.fuseCM == 2) {
+            const double sc = a.invTotalMass / CM_SCALE;
+            vcm = {sc * (double)a.counters->cm[a.cmCur][0], sc * (double)a.counters->cm[a.cmCur][1], sc * (double)a.counters->cm[a.cmCur][2]};
+        }
+        for (int q = aBegin + threadIdx.x; q < aEnd; q += blockDim.x) {      // part 1: kick
+            const int i = g.atomList[q];
+            double4 vm = a.velm[i];
+            const V3 f = loadForce<false>(a, i);
+            vm.x += -vcm.x + f.x * a.dt * vm.w; vm.y += -vcm.y + f.y * a.dt * vm.w; vm.z += -vcm.z + f.z * a.dt * vm.w;
+            a.velm[i] = vm;
+        }
+    }
+    if (mode == 0 || mode == 1) gcVelocitySweeps(a, g, cc.x, cc.y, &flag);
+    if (mode == 1) return;
+    __syncthreads();
+    for (int q = aBegin + threadIdx.x; q < aEnd; q += blockDim.x) {          // part 2: drift, thermostat, drift (unconstrained displacement)
+        const int i = g.atomList[q];
+        V3 d = {0, 0, 0};
+        if (mode == 0) {
+            double4 vm = a.velm[i];
+            V3 v = {vm.x, vm.y, vm.z};
+            d = v * halfdt;
+            const V3 gs = gaussian3(a.seed, a.step, a.atomIndex[i]);
+            v = v * a.vscale + gs * (a.noisescale * sqrt(vm.w));
+            d = d + v * halfdt;
+            a.velm[i] = make_double4(v.x, v.y, v.z, vm.w);
+        }
+        g.delta[i] = make_double4(d.x, d.y, d.z, 0.0); g.old[i] = make_double4(d.x, d.y, d.z, 0.0);
+    }
+    gcPositionSweeps(a, g, cc.x, cc.y, &flag);
+    __syncthreads();
+    for (int q = aBegin + threadIdx.x; q < aEnd; q += blockDim.x) {          // part 3: constraint correction of the velocities, new positions
+        const int i = g.atomList[q];
+        const double4 d = g.delta[i], o = g.old[i];
+        if (mode == 0) {
+            double4 vm = a.velm[i];
+            vm.x += (d.x - o.x) * invDt; vm.y += (d.y - o.y) * invDt; vm.z += (d.z - o.z) * invDt;
+            a.velm[i] = vm;
+            if (vm.w != 0.0) mom = mom + V3{vm.x, vm.y, vm.z} * (1.0 / vm.w);
+        }
+        const V3 pn = loadPosD(a, i) + V3{d.x, d.y, d.z};
+        storePosD<false>(a, i, pn);
+        if (mode == 0) checkMoved(a, i, pn, moved);
+    }
+    if (mode != 0) return;
+    if (a.refPosq && __any_sync(0xffffffffu, moved) && (threadIdx.x & 31) == 0) a.counters->rebuild = 1;
+    if (a.fuseCM) {
+        __shared__ double red[3][GC_THREADS];
+        red[0][threadIdx.x] = mom.x; red[1][threadIdx.x] = mom.y; red[2][threadIdx.x] = mom.z;
+        __syncthreads();
+        for (int o = GC_THREADS / 2; o > 0; o >>= 1) {
+            if (threadIdx.x < o) for (int k2 = 0; k2 < 3; k2++) red[k2][threadIdx.x] += red[k2][threadIdx.x + o];
+            __syncthreads();
+        }
+        if (threadIdx.x < 3) atomicAddFixed(&a.counters->cm[a.cmNext][threadIdx.x], (long long)(red[threadIdx.x][0] * CM_SCALE));
+    }
+}
+
+static GcArgs makeGcArgs(b200_ctx* c, double tol) {
+    GcArgs g; g.pairs = c->gcPairs; g.dist = c->gcDist; g.colorStart = c->gcColorStart; g.clusterColors = c->gcClusterColors;
+    g.atomStart = c->gcAtomStart; g.atomList = c->gcAtomList; g.delta = c->gcDelta; g.old = c->gcOld; g.tol = tol;
+    return g;
+}
+
 // ---- centre-of-mass motion removal (platforms/common/src/kernels/removeCM.cc)
 __global__ void __launch_bounds__(256) cmMomentum(const double4* __restrict__ velm, int N, DevCounters* counters, int slot) {
     double px = 0, py = 0, pz = 0;
@@ -491,6 +621,10 @@ void b200_integrate_step(b200_ctx* c) {
         langevinMiddleShake<<<(c->numShake + 127) / 128, 128, 0, s>>>(a, c->numShake, c->shakeAtoms, c->shakeDist, c->integ.constraint_tol > 0 ? c->integ.constraint_tol : 1e-5);
         LAUNCH_COUNT(c, 1);
     }
+    if (c->numGcClusters > 0) {
+        generalClusterStep<<<c->numGcClusters, GC_THREADS, 0, s>>>(a, makeGcArgs(c, c->integ.constraint_tol > 0 ? c->integ.constraint_tol : 1e-5), 0);
+        LAUNCH_COUNT(c, 1);
+    }
     CUDA_CHECK(cudaGetLastError());
 }
 
@@ -502,6 +636,7 @@ extern "C" int b200_apply_constraints(b200_ctx* c, double tol) {
         if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints that are neither rigid 3-site molecules (SETTLE) nor SHAKE clusters are not implemented");
         if (c->numSettle > 0) { settleOnly<<<(c->numSettle + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, 0); LAUNCH_COUNT(c, 1); }
         if (c->numShake > 0) { shakeOnly<<<(c->numShake + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numShake, c->shakeAtoms, c->shakeDist, tol > 0 ? tol : 1e-5, 0); LAUNCH_COUNT(c, 1); }
+        if (c->numGcClusters > 0) { generalClusterStep<<<c->numGcClusters, GC_THREADS, 0, c->stream>>>(makeArgs(c), makeGcArgs(c, tol > 0 ? tol : 1e-5), 2); LAUNCH_COUNT(c, 1); }
         CUDA_CHECK(cudaStreamSynchronize(c->stream));
         c->stepsSinceReorder = -1; c->dispChecked = false; c->listVerified = false; c->forcesValid = false;
     } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
@@ -516,6 +651,7 @@ extern "C" int b200_apply_velocity_constraints(b200_ctx* c, double tol) {
         if (c->numOtherConstraints > 0) throw B200Error(B200_ERR_UNSUPPORTED, "constraints that are neither rigid 3-site molecules (SETTLE) nor SHAKE clusters are not implemented");
         if (c->numSettle > 0) { settleOnly<<<(c->numSettle + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, 1); LAUNCH_COUNT(c, 1); }
         if (c->numShake > 0) { shakeOnly<<<(c->numShake + 127) / 128, 128, 0, c->stream>>>(makeArgs(c), c->numShake, c->shakeAtoms, c->shakeDist, tol > 0 ? tol : 1e-5, 1); LAUNCH_COUNT(c, 1); }
+        if (c->numGcClusters > 0) { generalClusterStep<<<c->numGcClusters, GC_THREADS, 0, c->stream>>>(makeArgs(c), makeGcArgs(c, tol > 0 ? tol : 1e-5), 1); LAUNCH_COUNT(c, 1); }
         c->cmValid = false;
         CUDA_CHECK(cudaStreamSynchronize(c->stream));
     } catch (const B200Error& e) { b200_set_error(e.what()); return e.code; }
@@ -560,6 +696,7 @@ extern "C" int b200_kinetic_energy_shifted(b200_ctx* c, double shift, double* ke
         const double tol = c->hasIntegrator && c->integ.constraint_tol > 0 ? c->integ.constraint_tol : 1e-5;
         if (c->numSettle > 0) settleOnly<<<(c->numSettle + 127) / 128, 128, 0, s>>>(makeArgs(c), c->numSettle, c->settleAtoms, c->settleParams, 1);
         if (c->numShake > 0) shakeOnly<<<(c->numShake + 127) / 128, 128, 0, s>>>(makeArgs(c), c->numShake, c->shakeAtoms, c->shakeDist, tol, 1);
+        if (c->numGcClusters > 0) generalClusterStep<<<c->numGcClusters, GC_THREADS, 0, s>>>(makeArgs(c), makeGcArgs(c, tol), 1);
         keZero<<<1, 1, 0, s>>>(c->counters);
         kineticEnergy<<<c->smCount * 2, 256, 0, s>>>(c->velm, c->N, c->counters);
         CUDA_CHECK(cudaMemcpyAsync(c->velm, c->velmTmp, sizeof(double4) * c->Npad, cudaMemcpyDeviceToDevice, s));

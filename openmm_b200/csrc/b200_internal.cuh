@@ -144,6 +144,10 @@ struct b200_ctx {
     double totalMassCached = 0;
     std::vector<int> hSettleAtoms, hFreeAtoms;      // host copies (4 ints per cluster), used to plan the multi-GPU integration slices
     int numOtherConstraints = 0;
+    // general constraint clusters (anything that is neither SETTLE nor a SHAKE star): one CTA per connected cluster, constraints
+    // ordered by colour (no two constraints of a colour share an atom) -- b200_integrate.cu generalCluster*
+    int numGc = 0, numGcClusters = 0; int2* gcPairs = nullptr; double* gcDist = nullptr; int* gcColorStart = nullptr; int2* gcClusterColors = nullptr;
+    int* gcAtomStart = nullptr; int* gcAtomList = nullptr; double4* gcDelta = nullptr; double4* gcOld = nullptr;
 
     // molecules
     bool finalized = false;
@@ -209,6 +213,8 @@ struct b200_ctx {
     int numAngles = 0; int4* angleAtoms = nullptr; float2* angleParams = nullptr;
     int numTorsions = 0; int4* torsionAtoms = nullptr; float4* torsionParams = nullptr;
     std::vector<int> hBondAtoms, hAngleAtoms, hTorsionAtoms; std::vector<double> hBondParams, hAngleParams, hTorsionParams; std::vector<int> hTorsionPeriod;
+
+    int bondedPeriodic[3] = {0, 0, 0};   // bonds / angles / torsions use the nearest periodic image of every displacement
 
     // integrator
     bool hasIntegrator = false;

@@ -235,10 +235,13 @@ void B200CalcNonbondedForceKernel::getLJPMEParameters(double& alpha, int& nx, in
 
 // ---------------------------------------------------------------------------------------------- bonded forces
 // All terms of one kind are evaluated together under one group bit.  Several forces of the same kind are fine as long as they share
-// a force group; different groups (per-force energy decomposition) or periodic bonded forces would silently give wrong answers,
-// so they are refused.
+// a force group and the periodic-boundary setting; different groups (per-force energy decomposition) would silently give wrong
+// answers, so they are refused.
 static void checkBondedForce(B200Platform::PlatformData& d, int kind, const Force& force, bool periodic, const char* name) {
-    if (periodic) throw OpenMMException(string("The B200 platform does not support periodic boundary conditions for ") + name);
+    if (d.bondedGroup[kind] >= 0 && d.bondedPeriodic[kind] != (periodic ? 1 : 0))
+        throw OpenMMException(string("The B200 platform evaluates all ") + name + " objects of a System together: they must agree on periodic boundary conditions");
+    d.bondedPeriodic[kind] = periodic ? 1 : 0;
+    d.all([&](b200_ctx* c, int) { return b200_bonded_set_periodic(c, kind, periodic ? 1 : 0); });
     if (d.bondedGroup[kind] >= 0 && d.bondedGroup[kind] != force.getForceGroup())
         throw OpenMMException(string("The B200 platform evaluates all ") + name + " objects of a System together: they must share one force group");
     d.bondedGroup[kind] = force.getForceGroup();

@@ -52,6 +52,7 @@ public:
         unsigned pendingGroups = 0;            // force groups requested by the ForceImpls between begin/finishComputation
         bool positionsValid = false;
         int bondedCount[3] = {0, 0, 0};         // bonds / angles / torsions created so far (a force's terms start at the count it found)
+        int bondedPeriodic[3] = {0, 0, 0};
         int bondedGroup[3] = {-1, -1, -1};      // force group of the HarmonicBond / HarmonicAngle / PeriodicTorsion terms already added
         std::map<std::string, std::string> properties;
         ~PlatformData() {

@@ -317,3 +317,43 @@ def test_shake_clusters_hold_their_constraints_and_conserve_energy():
     p = ctx.get_positions()
     assert np.abs(np.linalg.norm(p[ca[:, 0]] - p[ca[:, 1]], axis=1) - 0.109).max() < 1e-6
     ctx.close()
+
+
+def test_general_constraint_clusters_chains():
+    # chains of six atoms with ALL bonds constrained (five constraints in a row: neither SETTLE nor a SHAKE star) and harmonic angles:
+    # the general cluster solver (one CTA per chain, colour-ordered Gauss-Seidel sweeps; the reference uses CCMA here,
+    # tests/TestVerletIntegrator.h testConstrainedChain) must hold every distance to the tolerance and conserve the energy
+    rng = np.random.default_rng(8)
+    nm, L = 30, 6
+    pos = []
+    for m in range(nm):
+        p = rng.random(3) * 6 + 2
+        chain = [p]
+        for k in range(L - 1):
+            d = rng.normal(size=3) + np.array([1.5, 0, 0]); d *= 0.15 / np.linalg.norm(d)
+            chain.append(chain[-1] + d)
+        pos += chain
+    pos = np.array(pos)
+    idx = np.arange(nm * L).reshape(nm, L)
+    con = np.concatenate([np.stack([idx[:, k], idx[:, k + 1]], 1) for k in range(L - 1)]).astype(np.int32)
+    angle_atoms = np.concatenate([np.stack([idx[:, k], idx[:, k + 1], idx[:, k + 2]], 1) for k in range(L - 2)])
+    masses = rng.uniform(1.0, 16.0, nm * L)
+    ctx = b.Context(masses, BOX, constraints=(con, np.full(len(con), 0.15)))
+    ctx.add_harmonic_angles(angle_atoms, np.full(len(angle_atoms), 1.9), np.full(len(angle_atoms), 400.0))
+    ctx.set_positions(pos)
+    ctx.set_velocities(rng.normal(size=pos.shape) * np.sqrt(2.494 / masses)[:, None])
+    ctx.apply_constraints(1e-7); ctx.apply_velocity_constraints(1e-7)
+    ctx.set_integrator(dt=0.001, temperature=0.0, friction=0.0, constraint_tol=1e-7, seed=1, remove_cm_every=0)
+    tot = []
+    for _ in range(6):
+        ctx.step(50)
+        tot.append(ctx.compute(b.GROUP_ANGLES) + ctx.kinetic_energy_shifted(0.0005))
+    p = ctx.get_positions()
+    d = np.linalg.norm(p[con[:, 0]] - p[con[:, 1]], axis=1)
+    assert np.abs(d - 0.15).max() < 1e-6
+    tot = np.array(tot)
+    print("general clusters: total energy", tot)
+    assert np.abs(tot - tot[0]).max() < 2e-3 * np.abs(tot).max()
+    v = ctx.get_velocities()
+    assert np.abs(np.einsum("ij,ij->i", p[con[:, 0]] - p[con[:, 1]], v[con[:, 0]] - v[con[:, 1]])).max() < 1e-3
+    ctx.close()
