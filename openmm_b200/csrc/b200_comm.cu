@@ -114,6 +114,16 @@ __global__ void peerBarrierKernel(PeerSet p, unsigned long long* flags, int slot
     }
 }
 
+// Signal only: "my work up to here is complete" to every rank (the waiting half lives in the consumer, see peerReduceForcesOrdered)
+__global__ void peerSignalKernel(PeerSet p, int slot, unsigned long long seq) {
+    if ((int)threadIdx.x < p.n) {
+        __threadfence_system();
+        volatile unsigned long long* out = p.flags[threadIdx.x] + slot * B200_MAX_PEERS + p.rank;
+        *out = seq;
+        __threadfence_system();
+    }
+}
+
 void b200_peer_barrier(b200_ctx* c, int slot) {
     ScopedTimer tm(c, B200_T_COMM, c->stream);
     const unsigned long long seq = ++c->peerSeq[slot];
@@ -187,6 +197,43 @@ __global__ void __launch_bounds__(256) peerReduceForces(PeerSet p, int Npad, int
 void b200_peer_reduce_forces(b200_ctx* c) {
     ScopedTimer tm(c, B200_T_COMM, c->stream);
     if (c->shardAtomEnd > c->shardAtomBegin) { peerReduceForces<<<c->smCount * 4, 256, 0, c->stream>>>(c->peers, c->Npad, c->shardAtomBegin, c->shardAtomEnd); LAUNCH_COUNT(c, 1); }
+}
+
+// Barrier and reduce-scatter in one kernel, peer by peer: the contribution of a rank is added as soon as THAT rank has signalled,
+// in the order "direct-space ranks first, rank 0 last".  With four or more ranks rank 0 only runs PME and is the last to finish;
+// the other ranks' contributions (the bulk of the traffic) are then already summed while everybody waits for it, and only rank 0's
+// slice remains to be added when its flag arrives.  Integer sums: the order does not change a bit of the result.
+__global__ void __launch_bounds__(256) peerReduceForcesOrdered(PeerSet p, const unsigned long long* flags, int slot, unsigned long long seq, int Npad, int aBegin, int aEnd, DevCounters* counters) {
+    const int count = aEnd - aBegin;
+    for (int k = 1; k <= p.n; k++) {
+        const int r = k < p.n ? k : 0;          // 1, 2, ..., n-1, 0
+        if (r == p.rank) continue;
+        if (threadIdx.x == 0) {
+            volatile const unsigned long long* f = flags + slot * B200_MAX_PEERS + r;
+            unsigned long long t0; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            while (*f < seq) {
+                unsigned long long t1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 20000000000ull) { counters->overflow = 2; break; }   // 20 s: a rank died; fail loudly instead of hanging the GPU
+            }
+            __threadfence_system();
+        }
+        __syncthreads();
+        const long long* src = p.force[r];
+        long long* dst = p.force[p.rank];
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 3 * count; i += gridDim.x * blockDim.x) {
+            const int comp = i / count, j = i - comp * count;
+            const size_t off = (size_t)comp * Npad + aBegin + j;
+            dst[off] += src[off];
+        }
+    }
+}
+// signal "my partial forces are complete", then reduce peer by peer as their signals arrive (replaces barrier + reduce)
+void b200_peer_signal_and_reduce_forces(b200_ctx* c) {
+    ScopedTimer tm(c, B200_T_COMM, c->stream);
+    const unsigned long long seq = ++c->peerSeq[PEER_SLOT_FORCES];
+    peerSignalKernel<<<1, 32, 0, c->stream>>>(c->peers, PEER_SLOT_FORCES, seq);
+    peerReduceForcesOrdered<<<c->smCount * 2, 256, 0, c->stream>>>(c->peers, c->peerFlags, PEER_SLOT_FORCES, seq, c->Npad, c->shardAtomBegin, c->shardAtomEnd, c->counters);
+    LAUNCH_COUNT(c, 2);
 }
 // the all-gather: one kernel stores this rank's range of posq into every other rank's array (coalesced 16-byte stores over
 // NVLink to all peers at once; three back-to-back DMA copies were measured at 38 us for 3 x 4.3 MB, launch-latency bound)

@@ -1174,9 +1174,15 @@ void b200_advance(b200_ctx* c, cudaEvent_t* ev) {
     auto mark = [&](int k) { if (ev) { cudaEventCreate(&ev[k]); cudaEventRecord(ev[k], c->stream); } };
     c->peerStepActive = peerStepPlan(c);
     if (c->peerStepActive) {
-        b200_peer_barrier(c, PEER_SLOT_FORCES);                           // every rank's partial forces are complete
-        mark(2);
-        b200_peer_reduce_forces(c);                                       // reduce-scatter over NVLink into the local array
+        static const bool separate = getenv("B200_SEPARATE_REDUCE") != nullptr;     // A/B switch: barrier kernel, then reduce kernel
+        if (separate) {
+            b200_peer_barrier(c, PEER_SLOT_FORCES);                       // every rank's partial forces are complete
+            mark(2);
+            b200_peer_reduce_forces(c);                                   // reduce-scatter over NVLink into the local array
+        } else {
+            mark(2);
+            b200_peer_signal_and_reduce_forces(c);                        // signal, then add every rank's slice as its signal arrives
+        }
     } else {
         if (c->commRanks > 1) { b200_peer_sync_state(c); b200_ensure_forces_reduced(c); }     // replicated integration on every rank
         mark(2);

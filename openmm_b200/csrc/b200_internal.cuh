@@ -278,7 +278,8 @@ void b200_comm_destroy(b200_ctx* c);
 void b200_peer_barrier(b200_ctx* c, int slot);        // signal + wait on the compute stream (device-side, no host sync)
 void b200_peer_sync_state(b200_ctx* c);
 void b200_peer_plan_shard(b200_ctx* c);               // unit slice of this rank and whether its atoms are one contiguous slot range
-void b200_peer_reduce_forces(b200_ctx* c);            // sum of all ranks' partial forces for this rank's atom range -> local force array
+void b200_peer_reduce_forces(b200_ctx* c);
+void b200_peer_signal_and_reduce_forces(b200_ctx* c); // barrier + reduce-scatter in one kernel, peers added in the order they finish            // sum of all ranks' partial forces for this rank's atom range -> local force array
 void b200_peer_broadcast_positions(b200_ctx* c);      // rank 0's whole posq / posqCorr -> every rank
 void b200_peer_publish_positions(b200_ctx* c);        // this rank's slice of posq -> every rank               // all-gather of the sharded velocities / position remainders (collective)
 void b200_fft_make_plan(int n, FFTPlan1D& plan);
