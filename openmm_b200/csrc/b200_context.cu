@@ -1174,7 +1174,7 @@ void b200_advance(b200_ctx* c, cudaEvent_t* ev) {
     auto mark = [&](int k) { if (ev) { cudaEventCreate(&ev[k]); cudaEventRecord(ev[k], c->stream); } };
     c->peerStepActive = peerStepPlan(c);
     if (c->peerStepActive) {
-        static const bool separate = getenv("B200_SEPARATE_REDUCE") != nullptr;     // A/B switch: barrier kernel, then reduce kernel
+        static const bool separate = getenv("B200_ORDERED_REDUCE") == nullptr;     // default: barrier kernel, then one-pass reduce kernel
         if (separate) {
             b200_peer_barrier(c, PEER_SLOT_FORCES);                       // every rank's partial forces are complete
             mark(2);

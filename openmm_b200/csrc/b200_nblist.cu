@@ -140,7 +140,7 @@ __device__ __forceinline__ float2 nbMul2(float2 a, float2 b) { unsigned long lon
 __device__ __forceinline__ float2 nbSub2(float2 a, float2 b) { b.x = -b.x; b.y = -b.y; unsigned long long d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b))); return *reinterpret_cast<float2*>(&d); }
 
 // exact test of up to 32 queued candidate atoms (one per lane) against the 32 atoms of block X, then classification
-struct NbWarpBufs { int* dense; int* slots; int* masks; };
+struct NbWarpBufs { int* dense; int* slots; int* masks; int unitTiles; };   // unitTiles <= B200_UNIT_TILES: tiles per dense work unit
 __device__ __forceinline__ void nbProcessCandidates(int X, int lane, unsigned ltMask, bool have, int slot, float rx, float ry, float rz, const float4* sXw, const float4* sXp, bool single,
                                                     const BoxF& box, float rcp2, int sparseMax, NbWarpBufs w, int& nbuf, int& nsp,
                                                     int4* units, int* jAtoms, unsigned unitCapacity, unsigned tileCapacity, DevCounters* counters) {
@@ -174,11 +174,11 @@ __device__ __forceinline__ void nbProcessCandidates(int X, int lane, unsigned lt
     if (sparse) { const int k = nsp + __popc(mS & ltMask); w.slots[k] = slot; w.masks[k] = (int)imask; }
     nbuf += __popc(mD); nsp += __popc(mS);
     __syncwarp();
-    if (nbuf >= B200_UNIT_TILES * 32) {   // flush one full dense work unit
-        flushDense(X, w.dense, B200_UNIT_TILES, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
-        const int rest = nbuf - B200_UNIT_TILES * 32;
+    while (nbuf >= w.unitTiles * 32) {   // flush full dense work units (at most two: at most 32 atoms were appended)
+        flushDense(X, w.dense, w.unitTiles, lane, units, jAtoms, unitCapacity, tileCapacity, counters);
+        const int rest = nbuf - w.unitTiles * 32;
         int carry = 0;
-        if (lane < rest) carry = w.dense[B200_UNIT_TILES * 32 + lane];
+        if (lane < rest) carry = w.dense[w.unitTiles * 32 + lane];
         __syncwarp();
         if (lane < rest) w.dense[lane] = carry;
         nbuf = rest;
@@ -202,7 +202,7 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
         const float4* __restrict__ superCenter, const float4* __restrict__ superHalf,
         const int* __restrict__ exclRowStart, const int* __restrict__ exclRowCols,
         int4* __restrict__ units, int* __restrict__ jAtoms, unsigned unitCapacity, unsigned tileCapacity,
-        int partRank, b200_ctx::OwnerTable table, int split, DevCounters* counters) {
+        int partRank, b200_ctx::OwnerTable table, int split, int unitTiles, DevCounters* counters) {
     if (!counters->rebuild) return;
     __shared__ float4 sX[NB_WARPS][32];
     __shared__ float4 sXp[NB_WARPS][32];    // the same atoms packed in pairs (i, i+16) for the FP32x2 exact test
@@ -214,7 +214,7 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
     const int warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     const unsigned ltMask = (1u << lane) - 1u;
     const float rcp = sqrtf(rcp2);
-    NbWarpBufs wb = {sBuf[warp], sSlot[warp], sMask[warp]};
+    NbWarpBufs wb = {sBuf[warp], sSlot[warp], sMask[warp], unitTiles};
     // rows are dealt (weighted) round-robin to ranks: every rank gets a statistically identical sample of the sweep.  The rows
     // this rank owns are enumerated densely (k-th owned row = 64*(k/m) + res[k%m], m owned residues of the period-64 table), so
     // that every warp of the grid has work whatever the share of the rank.
@@ -368,11 +368,15 @@ void b200_nblist_prepare(b200_ctx* c) {
     int split = c->B < 1536 ? 8 : 1;      // measured: DHFR (737 rows) 128 -> 116 us/step with 8; ApoA1 (2882 rows) and larger are best unsplit
     { static const char* e = getenv("B200_NB_SPLIT"); if (e) split = std::max(1, std::min(16, atoi(e))); }
     rows *= split;
+    // ... and smaller work units: with a few thousand units for 3552 resident warps the longest unit sets the tile kernel's time.
+    // (Both depend on the block count only, so the unit composition does not depend on the number of GPUs.)
+    int unitTiles = c->B < 1536 ? 2 : c->B < 6144 ? 4 : B200_UNIT_TILES;
+    { static const char* e = getenv("B200_UNIT_TILES_RT"); if (e) unitTiles = std::max(1, std::min(B200_UNIT_TILES, atoi(e))); }
     int buildGrid = (rows + NB_WARPS - 1) / NB_WARPS;
     if (buildGrid > c->smCount * 16) buildGrid = c->smCount * 16;
     nbBuild<<<buildGrid, NB_THREADS, 0, c->stream>>>(c->posq, c->N, c->B, c->numSuper, nbBox, rcp * rcp, c->sparseMax,
         c->blockCenter, c->blockHalf, c->superCenter, c->superHalf, c->exclRowStart, c->exclRowCols,
-        c->units, c->jAtoms, (unsigned)c->unitCapacity, (unsigned)c->tileCapacity, c->partRank, c->partTable, split, c->counters);
+        c->units, c->jAtoms, (unsigned)c->unitCapacity, (unsigned)c->tileCapacity, c->partRank, c->partTable, split, unitTiles, c->counters);
     nbFinish<<<1, 1, 0, c->stream>>>(c->counters);
     LAUNCH_COUNT(c, 4);
     CUDA_CHECK(cudaGetLastError());

@@ -200,11 +200,11 @@ static int cmdBench(int argc, char** argv) {
     t0 = chrono::steady_clock::now();
     if (!e2e) { integ.step(steps); ctx.getState(State::Energy); }   // benchmark.py:99-108
     else {                                                           // host buffers in and out every step: setPositions + step + getState(Positions)
-        pos = ctx.getState(State::Positions).getPositions();
+        State st = ctx.getState(State::Positions);               // (the State is kept alive: no extra copy of its position vector)
         for (int i = 0; i < steps; i++) {
-            ctx.setPositions(pos);
+            ctx.setPositions(st.getPositions());
             integ.step(1);
-            pos = ctx.getState(State::Positions).getPositions();
+            st = ctx.getState(State::Positions);
         }
     }
     double secs = chrono::duration<double>(chrono::steady_clock::now() - t0).count();
