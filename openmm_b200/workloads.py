@@ -221,18 +221,25 @@ def write_system_file(path, sysd, cutoff, alpha, grid, method=4, dispersion=Fals
         vel = sysd.get("velocities")
         f.write(np.asarray(vel if vel is not None else np.zeros((n, 3)), dtype="<f8").reshape(-1).tobytes())
         excl = np.asarray(sysd["exclusions"], dtype=np.int32).reshape(-1, 2)
-        xp = {} if exc is None else {(int(a), int(b)): (q, s, e) for (a, b), q, s, e in zip(np.asarray(exc[0]).reshape(-1, 2), exc[1], exc[2], exc[3])}
+        rec = np.zeros(len(excl), dtype=[("i", "<i4"), ("j", "<i4"), ("qq", "<f8"), ("sig", "<f8"), ("eps", "<f8")])
+        rec["i"], rec["j"], rec["sig"] = excl[:, 0], excl[:, 1], 1.0
+        if exc is not None and len(exc[1]) > 0:      # exceptions with parameters: find their rows among the exclusions
+            key = excl[:, 0].astype(np.int64) * n + excl[:, 1]
+            order = np.argsort(key)
+            xpairs = np.asarray(exc[0]).reshape(-1, 2)
+            rows = order[np.searchsorted(key[order], xpairs[:, 0].astype(np.int64) * n + xpairs[:, 1])]
+            rec["qq"][rows], rec["sig"][rows], rec["eps"][rows] = exc[1], exc[2], exc[3]
         f.write(struct.pack("<i", len(excl)))
-        for a, b in excl:
-            q, s, e = xp.get((int(a), int(b)), (0.0, 1.0, 0.0))
-            f.write(struct.pack("<iiddd", int(a), int(b), q, s, e))
+        f.write(rec.tobytes())
         con = sysd.get("constraints")
         if con is None or len(con[1]) == 0:
             f.write(struct.pack("<i", 0))
         else:
-            f.write(struct.pack("<i", len(con[1])))
-            for (a, b), d in zip(np.asarray(con[0]).reshape(-1, 2), con[1]):
-                f.write(struct.pack("<iid", int(a), int(b), float(d)))
+            ca = np.asarray(con[0], dtype=np.int32).reshape(-1, 2)
+            crec = np.zeros(len(ca), dtype=[("i", "<i4"), ("j", "<i4"), ("d", "<f8")])
+            crec["i"], crec["j"], crec["d"] = ca[:, 0], ca[:, 1], np.asarray(con[1], dtype=np.float64)
+            f.write(struct.pack("<i", len(ca)))
+            f.write(crec.tobytes())
 
 
 def read_eval_file(path, n):
