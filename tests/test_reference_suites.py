@@ -33,10 +33,19 @@ MUST_PASS = {
 }
 
 
-# further suites of the reference, run for the record (their failing tests name features outside the scope table: periodic bonded
-# forces, updateParametersInContext of bonded forces, general constraint topologies, ...); what passes today is asserted as well
-MUST_PASS.update({"suite_bonds": [], "suite_angles": [], "suite_torsions": [], "suite_verlet": [], "suite_langevinmiddle": [], "suite_settle": [],
-                  "suite_checkpoints": [], "suite_minimizer": []})
+# further suites of the reference; the tests that pass are asserted.  Not passing: the testForceGroups / testSetState / testReporter cases
+# need kernels outside the scope table (CustomExternalForce, ...), the minimizer's testForceGroups puts two HarmonicBondForces in
+# different force groups, testLargeForces minimises from 1e6 kJ/mol/nm forces
+MUST_PASS.update({
+    "suite_bonds": ["testBonds()", "testPeriodic()"],
+    "suite_angles": ["testAngles()", "testPeriodic()"],
+    "suite_torsions": ["testPeriodicTorsions()", "testPeriodic()"],
+    "suite_verlet": ["testSingleBond()", "testConstraints()", "testConstrainedClusters()", "testConstrainedMasslessParticles()", "testConstrainedChain(10)", "testInitialTemperature()"],
+    "suite_langevinmiddle": ["testSingleBond()", "testTemperature()", "testConstraints()", "testConstrainedMasslessParticles()", "testRandomSeed()", "testInitialTemperature()"],
+    "suite_settle": ["testConstraints()"],
+    "suite_checkpoints": [],
+    "suite_minimizer": ["testHarmonicBonds()", "testLargeSystem()", "testMasslessParticles()"],
+})
 
 
 @pytest.mark.parametrize("suite", sorted(MUST_PASS))
