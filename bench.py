@@ -98,13 +98,27 @@ def measured_traffic(workload):
 
 
 def build_system(workload):
+    """the synthetic TIP3P box of a BASELINE.json configuration; "apoa1ljpme" = the ApoA1-size box with NonbondedForce::LJPME (second, 45^3 mesh)"""
     from openmm_b200 import workloads
+    if workload == "apoa1ljpme":
+        sysd = workloads.cached_water_box(workloads.WORKLOADS["apoa1"], ljpme=True)
+        sysd["ljpme"] = True
+        return sysd
     return workloads.cached_water_box(workloads.WORKLOADS[workload])
+
+
+def sysfile_kw(sysd):
+    """extra arguments of write_system_file for this system (the LJPME method with its dispersion mesh)"""
+    if not sysd.get("ljpme"):
+        return {}
+    import openmm_b200 as b
+    lj_alpha, lj_grid = b.pme_parameters(0.9, sysd["box"], lj=True)
+    return dict(method=5, lj_alpha=lj_alpha, lj_grid=lj_grid)
 
 
 def workload_string(name, n, alpha, grid):
     """one description of the system, shared by both arms (the driver compares the two `config.workload` strings)"""
-    return (f"{name}: {n} atoms TIP3P water box at 100 atoms/nm^3, PME cutoff 0.9 nm, alpha {alpha:.5f}, grid {list(grid)}, "
+    return (f"{name}: {n} atoms TIP3P water box at 100 atoms/nm^3, {'LJPME' if name.endswith('ljpme') else 'PME'} cutoff 0.9 nm, alpha {alpha:.5f}, grid {list(grid)}, "
             "LangevinMiddle 300 K 1/ps 2 fs, rigid water, CMMotionRemover")
 
 
@@ -120,7 +134,7 @@ def run_ref_driver(sysd, alpha, grid, steps, warmup, platform="CPU", threads=0, 
         sp = system_file
         if sp is None:
             sp = os.path.join(td, "system.bin")
-            workloads.write_system_file(sp, sysd, 0.9, alpha, grid)
+            workloads.write_system_file(sp, sysd, 0.9, alpha, grid, **sysfile_kw(sysd))
         cmd = [REF_DRIVER, "bench", sp, "--platform", platform, "--steps", str(steps), "--warmup", str(warmup), "--dt", str(DT_PS)]
         if platform == "CPU":
             cmd += ["--plugin", os.path.join(REF_PLUGINS, "libOpenMMCPU.so"), "--plugin", os.path.join(REF_PLUGINS, "libOpenMMPME.so")]
@@ -180,7 +194,7 @@ def reference_arm(args):
 
 def multi_rank_identity_check(sysd, rank, world, local, dist, torch, b, workloads, steps=12):
     def make(comm):
-        c = workloads.make_context(sysd, device=local)
+        c = workloads.make_context(sysd, device=local, ljpme=bool(sysd.get("ljpme")))
         if comm:
             ids = [b.nccl_unique_id() if rank == 0 else None]
             dist.broadcast_object_list(ids, src=0)
@@ -216,7 +230,7 @@ def plugin_records(sysd, alpha, grid, args, n, devices=None):
     plugin = ref_gpu = None
     with tempfile.TemporaryDirectory() as td:
         sp = os.path.join(td, "system.bin")
-        workloads.write_system_file(sp, sysd, 0.9, alpha, grid)
+        workloads.write_system_file(sp, sysd, 0.9, alpha, grid, **sysfile_kw(sysd))
         k, w = max(args.steps, 100), max(args.warmup, 20)
         dev = [] if not devices else [("DeviceIndex", ",".join(str(x) for x in devices))]
         if os.path.exists(PLUGIN_PATH):
@@ -243,7 +257,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=30)
-    ap.add_argument("--workload", default="stmv", choices=["dhfr", "apoa1", "cellulose", "stmv"])
+    ap.add_argument("--workload", default="stmv", choices=["dhfr", "apoa1", "apoa1ljpme", "cellulose", "stmv"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=20)
@@ -264,7 +278,7 @@ def main():
     sysd = build_system(args.workload)
     n = sysd["n"]
     alpha, grid = b.pme_parameters(0.9, sysd["box"])
-    ctx = workloads.make_context(sysd, device=local)
+    ctx = workloads.make_context(sysd, device=local, ljpme=bool(sysd.get("ljpme")))
     if world > 1:
         ids = [b.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
@@ -340,6 +354,9 @@ def main():
     achieved_tflops = FLOP_PER_PAIR * pairs / (tile_avg_ms * 1e-3) / 1e12 if tile_avg_ms > 0 else 0.0
     G = grid[0] * grid[1] * grid[2]
     pme_bytes = 36.0 * G + 72.0 * n
+    if sysd.get("ljpme"):      # LJPME adds the same traffic for its own (smaller) mesh, SURVEY.md 8d
+        lg = sysfile_kw(sysd)["lj_grid"]
+        pme_bytes += 36.0 * lg[0] * lg[1] * lg[2] + 72.0 * n
     pme_ms = sum(fam[k][0] for k in ("spread", "fft", "convolve", "interpolate")) / max(prof_steps, 1)
     tile_traffic = measured_traffic(args.workload)
     roofline = {"kernel": "tileKernel<forces>", "bound": "fp32", "achieved": achieved_tflops, "peak": fp32_peak, "unit": "TFLOP/s",

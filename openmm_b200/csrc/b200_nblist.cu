@@ -370,7 +370,7 @@ void b200_nblist_prepare(b200_ctx* c) {
     rows *= split;
     // ... and smaller work units: with a few thousand units for 3552 resident warps the longest unit sets the tile kernel's time.
     // (Both depend on the block count only, so the unit composition does not depend on the number of GPUs.)
-    int unitTiles = c->B < 6144 ? 2 : c->B < 16384 ? 4 : B200_UNIT_TILES;   // measured (tile kernel, us): DHFR 62 -> 43, ApoA1 119 -> 92 with 2; Cellulose 351 -> 336 with 4
+    int unitTiles = c->B < 6144 ? 2 : 4;   // measured (tile kernel, us): DHFR 62 -> 43, ApoA1 119 -> 92 with 2; Cellulose 351 -> 336, STMV 824 -> 814 with 4
     { static const char* e = getenv("B200_UNIT_TILES_RT"); if (e) unitTiles = std::max(1, std::min(B200_UNIT_TILES, atoi(e))); }
     int buildGrid = (rows + NB_WARPS - 1) / NB_WARPS;
     if (buildGrid > c->smCount * 16) buildGrid = c->smCount * 16;
