@@ -330,7 +330,8 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
     }
 }
 
-__global__ void nbFinish(DevCounters* counters) { counters->rebuild = 0; }
+// last kernel of the list phase (every step): clears the rebuild request and rewinds the tile kernel's work queue
+__global__ void nbFinish(DevCounters* counters) { counters->rebuild = 0; counters->workNext = 0; }
 __global__ void nbSetRebuild(DevCounters* counters) { counters->rebuild = 1; }
 
 void b200_nblist_alloc(b200_ctx* c) {

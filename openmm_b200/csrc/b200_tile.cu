@@ -568,7 +568,6 @@ __global__ void __launch_bounds__(TILE_THREADS, TILE_MIN_BLOCKS) tileKernel(cons
     }
 }
 
-__global__ void resetWorkQueue(DevCounters* c) { c->workNext = 0; }
 
 template <bool EXACT, int LJMODE>
 static void launchTile(b200_ctx* c, const TileArgs& a, bool forces, bool energy, bool emitPairs) {
@@ -605,7 +604,7 @@ void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
         a.krf = (float)(pow(rc, -3.0) * (eps - 1.0) / (2.0 * eps + 1.0)); a.crf = (float)((1.0 / rc) * 3.0 * eps / (2.0 * eps + 1.0));
     }
     if (method == B200_NB_NOCUTOFF) { a.rc2 = INFINITY; a.rc2d = INFINITY; a.rcPadded = INFINITY; a.borderTol = 0.f; }
-    resetWorkQueue<<<1, 1, 0, c->stream>>>(c->counters);
+    // (the work queue head was rewound by nbFinish, the last kernel of b200_nblist_prepare, which precedes every tile launch)
     ScopedTimer tm(c, B200_T_TILE, c->stream);
     a.ljAlpha2 = a.invCut6 = a.ljShift = 0.f;
     if (c->ljpme) {
@@ -620,6 +619,6 @@ void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
     else if (c->nb.use_switch) { if (c->exactEwald) launchTile<true, 2>(c, a, forces, energy, emitPairs); else launchTile<false, 2>(c, a, forces, energy, emitPairs); }
     else if (c->exactEwald) launchTile<true, 0>(c, a, forces, energy, emitPairs);
     else launchTile<false, 0>(c, a, forces, energy, emitPairs);
-    LAUNCH_COUNT(c, 2);
+    LAUNCH_COUNT(c, 1);
     CUDA_CHECK(cudaGetLastError());
 }
