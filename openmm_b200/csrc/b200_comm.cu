@@ -56,6 +56,7 @@ extern "C" int b200_nccl_unique_id(char* id128) {
 }
 
 extern "C" int b200_set_partition(b200_ctx* c, int32_t rank, int32_t nranks) {
+    b200_graph_invalidate(c);
     if (!c || nranks < 1 || rank < 0 || rank >= nranks) { b200_set_error("b200_set_partition: bad rank"); return B200_ERR_INVALID; }
     c->partRank = rank; c->partRanks = nranks;
     // Rank 0 also runs PME, the exclusion corrections and the bonded terms, so it takes a smaller share s0 of the direct-space
@@ -68,6 +69,7 @@ extern "C" int b200_set_partition(b200_ctx* c, int32_t rank, int32_t nranks) {
     if (nranks > 1 && c->commRanks > 1) {   // only with a communicator: logical ranks on one device are plain equal shares
         const double s0 = std::max(0.0, (1.0 - (nranks - 1) * rho) / nranks);
         share[0] = s0;
+        c->rank0PmeOnly = s0 == 0.0;
         for (int r = 1; r < nranks; r++) share[r] = (1.0 - s0) / (nranks - 1);
     }
     // weighted round-robin over a period of 64 rows (largest-remainder / Bresenham spreading)
@@ -95,7 +97,7 @@ extern "C" int b200_set_partition(b200_ctx* c, int32_t rank, int32_t nranks) {
 // STMV) + R redundant integrations.  The barriers are device-side flag exchanges in peer memory; the host never waits.
 // A rank in ANOTHER process is reached through CUDA IPC handles; a rank in the SAME process (one OpenMM Context driving several GPUs,
 // DeviceIndex=0,1,...) through its raw pointers after cudaDeviceEnablePeerAccess (IPC handles cannot be opened by their own process).
-struct IpcBundle { cudaIpcMemHandle_t h[6]; void* raw[6]; long long pid; int device; };
+struct IpcBundle { cudaIpcMemHandle_t h[7]; void* raw[7]; long long pid; int device; };
 
 // signal and wait in one launch: lane r tells rank r that this rank reached `seq`, then waits for rank r's flag
 __global__ void peerBarrierKernel(PeerSet p, unsigned long long* flags, int slot, unsigned long long seq, DevCounters* counters) {
@@ -170,6 +172,21 @@ void b200_peer_plan_shard(b200_ctx* c) {
     }
     int contiguous = (cnt == 0) || (hi - lo + 1 == cnt);
     c->shardAtomBegin = cnt ? (int)lo : 0; c->shardAtomEnd = cnt ? (int)hi + 1 : 0;
+    // Atom range of EVERY rank (for the reciprocal-force push): usable when the ranges follow each other in rank order and cover
+    // all N atoms.  Each rank evaluates the same host tables, so all ranks reach the same verdict.
+    bool tiles = true; int next = 0;
+    for (int r = 0; r < R; r++) {
+        const int ub = std::min(units, 128 * (int)(((long long)nblk * r) / R)), ue = std::min(units, 128 * (int)(((long long)nblk * (r + 1)) / R));
+        long long l = 1LL << 40, h = -1, n = 0;
+        for (int t = ub; t < ue; t++) {
+            if (t < c->numSettle) for (int k = 0; k < 3; k++) { const long long a = c->hSettleAtoms[4 * (size_t)t + k]; l = std::min(l, a); h = std::max(h, a); n++; }
+            else { const long long a = c->hFreeAtoms[t - c->numSettle]; l = std::min(l, a); h = std::max(h, a); n++; }
+        }
+        c->shardAtomBounds[r] = next;
+        if (n > 0) { if (l != next || h - l + 1 != n) tiles = false; next = (int)h + 1; }
+    }
+    c->shardAtomBounds[R] = next;
+    c->pushPlanOk = tiles && next == c->N;
     // every rank must take the same code path
     long long* d = nullptr; dmalloc(d, 1);
     long long v = contiguous ? 0 : 1;
@@ -197,6 +214,45 @@ __global__ void __launch_bounds__(256) peerReduceForces(PeerSet p, int Npad, int
 void b200_peer_reduce_forces(b200_ctx* c) {
     ScopedTimer tm(c, B200_T_COMM, c->stream);
     if (c->shardAtomEnd > c->shardAtomBegin) { peerReduceForces<<<c->smCount * 4, 256, 0, c->stream>>>(c->peers, c->Npad, c->shardAtomBegin, c->shardAtomEnd); LAUNCH_COUNT(c, 1); }
+}
+
+// The reciprocal forces arrive separately: rank 0's interpolation kernel stored them into this rank's landing buffer (PmePush) and
+// then raised PEER_SLOT_RECIP.  Wait for the flag, add the slice.  Integer addition: the total equals the all-in-one sum bit for bit.
+// The wait is a kernel of its own with ONE warp: a spinning grid that fills every SM (as the adding kernel would) can keep a block of
+// the reciprocal pipeline that needs a whole SM's registers from ever being scheduled on this GPU -- the flag would never be raised
+// (seen as a 20 s time-out on two GPUs, whenever the compute stream reached this point before the PME stream had finished).
+__global__ void peerWaitRecip(const unsigned long long* flags, unsigned long long seq, DevCounters* counters) {
+    if (threadIdx.x == 0) {
+        volatile const unsigned long long* f = flags + PEER_SLOT_RECIP * B200_MAX_PEERS + 0;
+        unsigned long long t0; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while (*f < seq) {
+            unsigned long long t1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > 20000000000ull) { counters->overflow = 2; break; }   // 20 s: a rank died; fail loudly instead of hanging the GPU
+        }
+        __threadfence_system();
+    }
+}
+__global__ void __launch_bounds__(256) peerAddRecip(long long* __restrict__ force, const long long* __restrict__ recip, int Npad, int aBegin, int aEnd) {
+    const int count = aEnd - aBegin;
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < 3 * count; k += gridDim.x * blockDim.x) {
+        const int comp = k / count, j = k - comp * count;
+        const size_t off = (size_t)comp * Npad + aBegin + j;
+        force[off] += __ldcv(recip + off);
+    }
+}
+void b200_peer_signal_recip(b200_ctx* c, cudaStream_t s) {
+    peerSignalKernel<<<1, 32, 0, s>>>(c->peers, PEER_SLOT_RECIP, c->peerSeq[PEER_SLOT_RECIP]);
+    LAUNCH_COUNT(c, 1);
+}
+void b200_peer_add_recip(b200_ctx* c) {
+    if (!c->recipPending) return;
+    ScopedTimer tm(c, B200_T_COMM, c->stream);
+    const int b = c->shardAtomBounds[c->commRank], e = c->shardAtomBounds[c->commRank + 1];
+    // the wait is launched even for an empty slice: every rank consumes the signal before the next evaluation overwrites the buffers
+    peerWaitRecip<<<1, 32, 0, c->stream>>>(c->peerFlags, c->peerSeq[PEER_SLOT_RECIP], c->counters);
+    if (e > b) peerAddRecip<<<c->smCount * 2, 256, 0, c->stream>>>(c->force, c->recipIn, c->Npad, b, e);
+    LAUNCH_COUNT(c, e > b ? 2 : 1);
+    c->recipPending = false;
 }
 
 // Barrier and reduce-scatter in one kernel, in two phases (opt-in, B200_ORDERED_REDUCE=1): first the contributions of the
@@ -276,10 +332,13 @@ static void peerSetup(b200_ctx* c) {
     if (R < 2 || R > B200_MAX_PEERS || getenv("B200_NO_PEER") || !g_nccl.AllGather) return;
     int ok = 1;
     IpcBundle mine; memset(&mine, 0, sizeof(mine));
-    dmalloc(c->peerFlags, (size_t)3 * B200_MAX_PEERS);
-    CUDA_CHECK(cudaMemset(c->peerFlags, 0, sizeof(unsigned long long) * 3 * B200_MAX_PEERS));
-    void* ptrs[6] = {c->force, c->posq, c->posqCorr, c->velm, c->counters, c->peerFlags};
-    for (int k = 0; k < 6; k++) { mine.raw[k] = ptrs[k]; if (cudaIpcGetMemHandle(&mine.h[k], ptrs[k]) != cudaSuccess) { cudaGetLastError(); ok = 0; } }
+    dmalloc(c->peerFlags, (size_t)PEER_NUM_SLOTS * B200_MAX_PEERS);
+    CUDA_CHECK(cudaMemset(c->peerFlags, 0, sizeof(unsigned long long) * PEER_NUM_SLOTS * B200_MAX_PEERS));
+    dmalloc(c->recipIn, (size_t)3 * c->Npad);
+    CUDA_CHECK(cudaMemset(c->recipIn, 0, sizeof(long long) * 3 * (size_t)c->Npad));
+    constexpr int NP = 7;
+    void* ptrs[NP] = {c->force, c->posq, c->posqCorr, c->velm, c->counters, c->peerFlags, c->recipIn};
+    for (int k = 0; k < NP; k++) { mine.raw[k] = ptrs[k]; if (cudaIpcGetMemHandle(&mine.h[k], ptrs[k]) != cudaSuccess) { cudaGetLastError(); ok = 0; } }
     mine.pid = (long long)getpid(); mine.device = c->device;
     // exchange the handles (and whether everybody could export) through the communicator
     char* dSend = nullptr; char* dRecv = nullptr;
@@ -296,21 +355,21 @@ static void peerSetup(b200_ctx* c) {
     PeerSet& p = c->peers; memset(&p, 0, sizeof(p));
     p.n = R; p.rank = c->commRank;
     if (ok) for (int r = 0; r < R; r++) {
-        void* q[6];
-        if (r == c->commRank) { for (int k = 0; k < 6; k++) q[k] = ptrs[k]; }
+        void* q[NP];
+        if (r == c->commRank) { for (int k = 0; k < NP; k++) q[k] = ptrs[k]; }
         else {
             IpcBundle b; memcpy(&b, hostRecv.data() + r * rec, sizeof(b));
             if (b.pid == mine.pid) {
                 int can = 0;
                 if (cudaDeviceCanAccessPeer(&can, c->device, b.device) != cudaSuccess || !can) { cudaGetLastError(); ok = 0; }
                 else { const cudaError_t e = cudaDeviceEnablePeerAccess(b.device, 0); if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) ok = 0; cudaGetLastError(); }
-                for (int k = 0; k < 6; k++) q[k] = ok ? b.raw[k] : nullptr;
+                for (int k = 0; k < NP; k++) q[k] = ok ? b.raw[k] : nullptr;
                 c->peerInProcess = true;
             }
-            else for (int k = 0; k < 6; k++) if (cudaIpcOpenMemHandle(&q[k], b.h[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; q[k] = nullptr; }
+            else for (int k = 0; k < NP; k++) if (cudaIpcOpenMemHandle(&q[k], b.h[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; q[k] = nullptr; }
         }
         p.force[r] = (long long*)q[0]; p.posq[r] = (float4*)q[1]; p.posqCorr[r] = (float4*)q[2]; p.velm[r] = (double4*)q[3];
-        p.counters[r] = (DevCounters*)q[4]; p.flags[r] = (unsigned long long*)q[5];
+        p.counters[r] = (DevCounters*)q[4]; p.flags[r] = (unsigned long long*)q[5]; p.recip[r] = (long long*)q[6];
     }
     // all ranks must agree: one more exchange of the outcome
     {
@@ -328,6 +387,7 @@ static void peerSetup(b200_ctx* c) {
 }
 
 extern "C" int b200_comm_init(b200_ctx* c, int32_t rank, int32_t nranks, const char* id128) {
+    b200_graph_invalidate(c);
     try {
         loadNccl();
         CUDA_CHECK(cudaSetDevice(c->device));
@@ -357,12 +417,12 @@ void b200_comm_destroy(b200_ctx* c) {
         cudaDeviceSynchronize();
         PeerSet& p = c->peers;
         for (int r = 0; r < p.n && !c->peerInProcess; r++) if (r != p.rank) {
-            void* q[6] = {p.force[r], p.posq[r], p.posqCorr[r], p.velm[r], p.counters[r], p.flags[r]};
+            void* q[7] = {p.force[r], p.posq[r], p.posqCorr[r], p.velm[r], p.counters[r], p.flags[r], p.recip[r]};
             for (void* x : q) if (x) cudaIpcCloseMemHandle(x);
         }
         c->peerMode = false;
     }
-    dfree(c->peerFlags);
+    dfree(c->peerFlags); dfree(c->recipIn);
     if (c->ncclComm && g_nccl.CommDestroy) g_nccl.CommDestroy((ncclComm_t)c->ncclComm);
     c->ncclComm = nullptr;
 }

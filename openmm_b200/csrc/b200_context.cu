@@ -119,6 +119,7 @@ extern "C" void b200_context_destroy(b200_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
+    b200_graph_invalidate(c);
     b200_comm_destroy(c);
     b200_pme_destroy(c);
     dfree(c->posq); dfree(c->posqCorr); dfree(c->velm); dfree(c->sigEps); dfree(c->atomIndex); dfree(c->cellOffsets); dfree(c->force); dfree(c->counters);
@@ -243,6 +244,7 @@ extern "C" int b200_nonbonded_get_ljpme_parameters(const b200_ctx* c, double* al
 // CalcNonbondedForceKernel::copyParametersToContext (CommonCalcNonbondedForce.cpp:1119-1254): per-particle charge/sigma/epsilon
 // and exception parameters may change; the set of exceptions may not.
 extern "C" int b200_nonbonded_update_parameters(b200_ctx* c, const b200_nonbonded_desc* d) {
+    b200_graph_invalidate(c);
     API_BEGIN
     if (!c || !d || !c->hasNonbonded) throw B200Error(B200_ERR_INVALID, "b200_nonbonded_update_parameters: no NonbondedForce in this context");
     if (d->num_exclusions * 2 != (int)c->exclPairs.size() || d->num_exceptions != (int)c->excQQ.size())
@@ -340,7 +342,7 @@ extern "C" int b200_periodic_torsions_create(b200_ctx* c, int32_t n, const int32
 
 extern "C" int b200_bonded_set_periodic(b200_ctx* c, int32_t kind, int32_t periodic) {
     if (!c || kind < 0 || kind > 2) { b200_set_error("b200_bonded_set_periodic: bad arguments"); return B200_ERR_INVALID; }
-    c->bondedPeriodic[kind] = periodic ? 1 : 0;
+    c->bondedPeriodic[kind] = periodic ? 1 : 0; b200_graph_invalidate(c);
     return B200_OK;
 }
 
@@ -348,6 +350,7 @@ extern "C" int b200_bonded_set_periodic(b200_ctx* c, int32_t kind, int32_t perio
 // [first, first+n) of one kind (0 bonds: length,k; 1 angles: angle,k; 2 torsions: phase,k + periodicity); the atoms of a term may not change.
 // Molecules whose terms changed stop being exchangeable with their former twins, so their group leaves the re-sort.
 extern "C" int b200_bonded_update_parameters(b200_ctx* c, int32_t kind, int32_t first, int32_t n, const double* p0, const double* p1, const int32_t* periodicity) {
+    b200_graph_invalidate(c);
     API_BEGIN
     if (!c || kind < 0 || kind > 2 || first < 0 || n < 0) throw B200Error(B200_ERR_INVALID, "b200_bonded_update_parameters: bad arguments");
     std::vector<double>& prm = kind == 0 ? c->hBondParams : kind == 1 ? c->hAngleParams : c->hTorsionParams;
@@ -880,6 +883,7 @@ extern "C" int b200_get_forces(b200_ctx* c, double* xyz) {
 }
 
 extern "C" int b200_set_box(b200_ctx* c, const double* box9) {
+    b200_graph_invalidate(c);
     API_BEGIN
     b200_box_set(c, box9);
     c->forcesValid = false; c->dispChecked = false; c->listVerified = false;
@@ -944,6 +948,7 @@ extern "C" int b200_barostat_save(b200_ctx* c) {
 }
 
 extern "C" int b200_barostat_scale(b200_ctx* c, const double* scale6, int32_t rigidMolecules) {
+    b200_graph_invalidate(c);
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
     if (!c->positionsSet) throw B200Error(B200_ERR_INVALID, "Particle positions have not been set");
@@ -959,6 +964,7 @@ extern "C" int b200_barostat_scale(b200_ctx* c, const double* scale6, int32_t ri
 }
 
 extern "C" int b200_barostat_restore(b200_ctx* c) {
+    b200_graph_invalidate(c);
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
     if (!c->savedValid) throw B200Error(B200_ERR_INVALID, "b200_barostat_restore: nothing was saved");
@@ -998,6 +1004,7 @@ static void prepareLists(b200_ctx* c, bool verify) {
         checkOverflow(c);
         if (c->countersHost->overflow) {
             nbClearOverflow<<<1, 1, 0, c->stream>>>(c->counters);
+            if (c->countersHost->overflow == 2) throw B200Error(B200_ERR_OVERFLOW, "a wait for another rank's flag timed out (20 s) during an earlier step; the state computed since the last check is not trustworthy");
             throw B200Error(B200_ERR_OVERFLOW, "the neighbour list overflowed during an earlier, unverified force evaluation; the state computed since the last check is not trustworthy");
         }
     }
@@ -1020,31 +1027,87 @@ static void prepareLists(b200_ctx* c, bool verify) {
     throw B200Error(B200_ERR_OVERFLOW, "neighbour list kept overflowing");
 }
 
+void b200_graph_invalidate(b200_ctx* c) {
+    if (c->stepGraph) { cudaSetDevice(c->device); cudaStreamSynchronize(c->stream); cudaGraphExecDestroy(c->stepGraph); c->stepGraph = nullptr; }
+}
+
 static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, double* energyOut, bool verify) {
     CUDA_CHECK(cudaSetDevice(c->device));
     if (!c->positionsSet) throw B200Error(B200_ERR_INVALID, "Particle positions have not been set");
     b200_finalize(c);
-    if (c->stepsSinceReorder < 0 || c->stepsSinceReorder >= c->reorderInterval) { b200_peer_sync_state(c); b200_reorder(c); }   // the sort moves whole-state rows
     cudaStream_t s = c->stream;
+    // a pushed evaluation nobody consumed: its PME stream may still be reading the arrays the work below rewrites
+    if (c->recipPending && c->partRank == 0 && c->usePmeStream && !c->timing) CUDA_CHECK(cudaStreamWaitEvent(s, c->evPmeDone, 0));
+    if (c->stepsSinceReorder < 0 || c->stepsSinceReorder >= c->reorderInterval) { b200_peer_sync_state(c); b200_reorder(c); }   // the sort moves whole-state rows
     c->computeCount++;
-    if (forces) CUDA_CHECK(cudaMemsetAsync(c->force, 0, sizeof(long long) * 3 * (size_t)c->Npad, s));
-    if (energy) { zeroEnergy<<<1, 1, 0, s>>>(c->counters); LAUNCH_COUNT(c, 1); }
+    // The plain force evaluation of an MD step (forces only, no host read-back, one rank) is a fixed sequence of launches on two
+    // streams with constant arguments -- the list kernels decide on the device whether they have work -- so it is captured once as a
+    // CUDA graph and replayed: one launch per evaluation instead of ~15 (the reference submits each kernel, CommonKernels.cpp:3139-3206).
+    // Anything that changes an argument (box, parameters, list storage, streams) drops the graph, see b200_graph_invalidate.
+    static const bool graphOff = getenv("B200_NO_GRAPH") != nullptr;
+    const bool graphable = !graphOff && forces && !energy && !verify && c->commRanks == 1 && c->partRanks == 1 && !c->timing && c->hasNonbonded
+                           && c->computeCount > 4 && c->graphCaptures < 32;
+    const bool dispAtEntry = c->dispChecked;
+    if (graphable && c->stepGraph && c->stepGraphGroups == groups && c->stepGraphDisp == dispAtEntry) {
+        CUDA_CHECK(cudaGraphLaunch(c->stepGraph, s));
+        c->launchCount += c->stepGraphLaunches;
+        c->dispChecked = true; c->forcesPartial = false; c->recipPending = false;
+        c->forcesValid = groups == B200_GROUP_ALL;
+        return;
+    }
+    const bool capturing = graphable;
+    const long long launchesAtEntry = c->launchCount;
+    if (capturing) { b200_graph_invalidate(c); CUDA_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal)); }
     const bool doRecip = c->hasNonbonded && c->nb.method >= B200_NB_EWALD && (groups & B200_GROUP_RECIPROCAL) && c->partRank == 0;
     const bool doDirect = c->hasNonbonded && (groups & B200_GROUP_DIRECT);
     // per-family event timing needs the families serialised: overlapping streams would charge waiting time to the wrong family
     const bool usePmeStream = c->usePmeStream && !c->timing;
     cudaStream_t ps = usePmeStream ? c->pmeStream : s;
+    // Multi-GPU over peer memory, plain PME, forces only: rank 0 stores the reciprocal forces into the landing buffers of the ranks
+    // that integrate the atoms and raises a flag, instead of adding them to its own force array; its compute stream does not wait for
+    // the PME stream, so the barrier / reduce-scatter of the direct-space forces overlaps the end of the reciprocal pipeline.
+    // Every rank takes the same decision (same arguments, same host tables) and counts the evaluation.
+    bool push = false;
+    if (forces && !energy && c->peerMode && c->commRanks > 1 && c->hasNonbonded && c->nb.method == B200_NB_PME && (groups & B200_GROUP_RECIPROCAL)) {
+        // Worth it when rank 0 runs nothing but PME (4 ranks and more: it then finishes last).  With 2 ranks rank 0 also owns direct-space
+        // rows, its PME stream finishes first and the push only adds two launches (measured 0.927 against 0.906 ms/step on STMV).
+        // B200_RECIP_PUSH=1 / 0 forces it on / off (the 2-GPU tests run it on).
+        static const char* env = getenv("B200_RECIP_PUSH");
+        const bool on = env ? atoi(env) != 0 : c->rank0PmeOnly;
+        if (on) { b200_peer_plan_shard(c); push = c->pushPlanOk; }
+    }
+    if (push) { ++c->peerSeq[PEER_SLOT_RECIP]; c->recipPending = true; }
+    else if (forces) c->recipPending = false;
+    try {
+    if (forces) CUDA_CHECK(cudaMemsetAsync(c->force, 0, sizeof(long long) * 3 * (size_t)c->Npad, s));
+    if (energy) { zeroEnergy<<<1, 1, 0, s>>>(c->counters); LAUNCH_COUNT(c, 1); }
     if (doRecip) {
+        c->recipPushNow = push;
         if (usePmeStream) { CUDA_CHECK(cudaEventRecord(c->evFork, s)); CUDA_CHECK(cudaStreamWaitEvent(ps, c->evFork, 0)); }
         if (c->nb.method == B200_NB_EWALD) b200_ewald_launch(c, ps, forces, energy); else b200_pme_launch(c, ps, forces, energy);
         if (usePmeStream) CUDA_CHECK(cudaEventRecord(c->evPmeDone, ps));
+        c->recipPushNow = false;
     }
     if (doDirect) {
         prepareLists(c, verify);
         b200_tile_launch(c, forces, energy, false);
     }
     if (c->partRank == 0 || c->commRanks > 1) b200_bonded_launch(c, groups, forces, energy);
-    if (doRecip && usePmeStream) CUDA_CHECK(cudaStreamWaitEvent(s, c->evPmeDone, 0));
+    static const bool pushJoin = getenv("B200_PUSH_JOIN") != nullptr;     // debug: keep the data path of the push, give up the overlap
+    if (doRecip && usePmeStream && (!push || pushJoin)) CUDA_CHECK(cudaStreamWaitEvent(s, c->evPmeDone, 0));
+    } catch (...) {
+        if (capturing) { cudaGraph_t g = nullptr; cudaStreamEndCapture(s, &g); if (g) cudaGraphDestroy(g); cudaGetLastError(); c->graphCaptures = 1 << 20; }
+        throw;
+    }
+    if (capturing) {
+        cudaGraph_t g = nullptr;
+        CUDA_CHECK(cudaStreamEndCapture(s, &g));
+        c->graphCaptures++;
+        CUDA_CHECK(cudaGraphInstantiate(&c->stepGraph, g, 0));
+        cudaGraphDestroy(g);
+        c->stepGraphLaunches = c->launchCount - launchesAtEntry; c->stepGraphGroups = groups; c->stepGraphDisp = dispAtEntry;
+        CUDA_CHECK(cudaGraphLaunch(c->stepGraph, s));
+    }
     // With a communicator every rank now holds PARTIAL forces.  They are summed when somebody needs the total: the integration step
     // reduce-scatters them over peer memory (b200_advance), b200_get_forces and the shifted kinetic energy all-reduce them.
     c->forcesPartial = forces && c->commRanks > 1;
@@ -1101,6 +1164,7 @@ extern "C" int b200_compute_host(b200_ctx* c, const double* xyzIn, uint32_t grou
 }
 
 extern "C" int b200_direct_pairs(b200_ctx* c, int64_t* count, int32_t* pairs, int64_t capacity) {
+    b200_graph_invalidate(c);
     API_BEGIN
     CUDA_CHECK(cudaSetDevice(c->device));
     if (!c->positionsSet || !c->hasNonbonded) throw B200Error(B200_ERR_INVALID, "b200_direct_pairs: positions and a NonbondedForce are required");
@@ -1122,6 +1186,7 @@ extern "C" int b200_direct_pairs(b200_ctx* c, int64_t* count, int32_t* pairs, in
 }
 
 extern "C" int b200_direct_pairs_hash(b200_ctx* c, int64_t* count, uint64_t* hash) {
+    b200_graph_invalidate(c);
     API_BEGIN
     int rc = b200_direct_pairs(c, count, nullptr, 0); if (rc) return rc;
     *hash = (uint64_t)c->countersHost->pairHash;
@@ -1148,6 +1213,7 @@ extern "C" int b200_integrator_create(b200_ctx* c, const b200_integrator_desc* d
 
 void b200_ensure_forces_reduced(b200_ctx* c) {
     if (!c->forcesPartial || c->commRanks < 2) return;
+    b200_peer_add_recip(c);             // pushed reciprocal forces: each rank adds its landing slice to its own partial forces first
     b200_comm_allreduce_forces(c);      // collective: every rank reaches this point (int64 sums: exact, order independent)
     c->forcesPartial = false;
 }
@@ -1183,6 +1249,7 @@ void b200_advance(b200_ctx* c, cudaEvent_t* ev) {
             mark(2);
             b200_peer_signal_and_reduce_forces(c);                        // signal, then add every rank's slice as its signal arrives
         }
+        b200_peer_add_recip(c);                                           // + the reciprocal forces rank 0 pushed into this rank's landing buffer
     } else {
         if (c->commRanks > 1) { b200_peer_sync_state(c); b200_ensure_forces_reduced(c); }     // replicated integration on every rank
         mark(2);
@@ -1227,6 +1294,7 @@ extern "C" int b200_step(b200_ctx* c, int32_t nsteps) {
         }
     }
     checkOverflow(c);
+    if (c->countersHost->overflow == 2) throw B200Error(B200_ERR_OVERFLOW, "a wait for another rank's flag timed out (20 s) during b200_step; state is not trustworthy");
     if (c->countersHost->overflow) throw B200Error(B200_ERR_OVERFLOW, "neighbour list overflowed during b200_step; state is not trustworthy");
     API_END
 }

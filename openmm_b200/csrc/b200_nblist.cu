@@ -335,6 +335,7 @@ __global__ void nbFinish(DevCounters* counters) { counters->rebuild = 0; counter
 __global__ void nbSetRebuild(DevCounters* counters) { counters->rebuild = 1; }
 
 void b200_nblist_alloc(b200_ctx* c) {
+    b200_graph_invalidate(c);     // the list arrays are kernel arguments of the captured evaluation
     dfree(c->units); dfree(c->jAtoms);
     if (c->tileCapacity == 0) {
         c->tileCapacity = (long long)c->B * 28 + 1024;

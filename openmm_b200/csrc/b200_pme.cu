@@ -287,7 +287,7 @@ __device__ __forceinline__ float2 pmeFma2(float v, float2 w, float2 acc) {
     return *reinterpret_cast<float2*>(&d);
 }
 
-__global__ void __launch_bounds__(CHUNK, 6) pmeInterpolateChunks(const float4* __restrict__ posq, const float2* __restrict__ sigEps, int N, int Npad, PmeArgs a, const float* __restrict__ phi, long long* __restrict__ force) {
+__global__ void __launch_bounds__(CHUNK, 6) pmeInterpolateChunks(const float4* __restrict__ posq, const float2* __restrict__ sigEps, int N, int Npad, PmeArgs a, const float* __restrict__ phi, long long* __restrict__ force, PmePush push) {
     __shared__ float tile[TILE_MAX];
     __shared__ int sh[10];
     __shared__ int binCount[32];
@@ -378,12 +378,21 @@ __global__ void __launch_bounds__(CHUNK, 6) pmeInterpolateChunks(const float4* _
             }
         }
     }
-    if (!valid) return;
+    if (!valid && (push.n == 0 || i >= N)) return;
     const float q = p.w;
     const float tx = gx * a.nx, ty = gy * a.ny, tz = gz * a.nz;
     const float fx = -q * (tx * (float)a.r0x);
     const float fy = -q * (tx * (float)a.r1x + ty * (float)a.r1y);
     const float fz = -q * (tx * (float)a.r2x + ty * (float)a.r2y + tz * (float)a.r2z);
+    if (push.n > 0) {
+        // multi-GPU: the force goes straight to the rank that integrates atom i (plain 8-byte stores into its landing buffer, over
+        // NVLink for the other ranks); atoms without a coefficient store zeros, so every entry of a slice is rewritten each time
+        int r = 0;
+        while (r < push.n - 1 && i >= push.bounds[r + 1]) r++;
+        long long* dst = push.dst[r];
+        dst[i] = valid ? toFixed(fx) : 0; dst[i + Npad] = valid ? toFixed(fy) : 0; dst[i + 2 * Npad] = valid ? toFixed(fz) : 0;
+        return;
+    }
     atomicAddFixed(&force[i], toFixed(fx));
     atomicAddFixed(&force[i + Npad], toFixed(fy));
     atomicAddFixed(&force[i + 2 * Npad], toFixed(fz));
@@ -485,8 +494,15 @@ static void meshLaunch(b200_ctx* c, PmeMesh& m, cudaStream_t s, bool forces, boo
     { ScopedTimer tm(c, B200_T_FFT, s); b200_fft3d_reciprocal(c, m, s, a, energy, forces); }
     if (forces) {
         ScopedTimer tm(c, B200_T_INTERPOLATE, s);
-        pmeInterpolateChunks<<<chunks, CHUNK, 0, s>>>(c->posq, coef, c->N, c->Npad, a, m.gridReal, c->force);
+        PmePush push; memset(&push, 0, sizeof(push));
+        if (c->recipPushNow && &m == &c->mesh[0]) {
+            push.n = c->commRanks;
+            for (int r = 0; r < c->commRanks; r++) { push.bounds[r] = c->shardAtomBounds[r]; push.dst[r] = c->peers.recip[r]; }
+            push.bounds[c->commRanks] = c->shardAtomBounds[c->commRanks];
+        }
+        pmeInterpolateChunks<<<chunks, CHUNK, 0, s>>>(c->posq, coef, c->N, c->Npad, a, m.gridReal, c->force, push);
         LAUNCH_COUNT(c, 1);
+        if (push.n > 0) b200_peer_signal_recip(c, s);
     }
     CUDA_CHECK(cudaGetLastError());
 }

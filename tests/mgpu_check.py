@@ -39,9 +39,17 @@ e2 = multi.compute()
 f2 = multi.get_forces().copy()
 ok_force = np.array_equal(f1, f2)
 ok_energy = e1 == e2
+# forces-only evaluation (with B200_RECIP_PUSH=1, or four ranks and more, rank 0 pushes the reciprocal forces into the owners'
+# landing buffers) read back through the all-reduce path
+single.compute(energy=False); multi.compute(energy=False)
+ok_force = ok_force and np.array_equal(single.get_forces(), multi.get_forces())
+# two b200_step calls with a state read in between (the second call starts on an idle GPU with hosts out of step)
 single.step(60); multi.step(60)
 p1, p2 = single.get_positions(), multi.get_positions()
 ok_traj = np.array_equal(p1, p2)
+single.step(40); multi.step(40)
+p1, p2 = single.get_positions(), multi.get_positions()
+ok_traj = ok_traj and np.array_equal(p1, p2)
 flags = torch.tensor([int(ok_force), int(ok_energy), int(ok_traj)], device="cuda")
 dist.all_reduce(flags, op=dist.ReduceOp.MIN)
 # every rank must hold the same state
@@ -50,7 +58,7 @@ hmax, hmin = h.clone(), h.clone()
 dist.all_reduce(hmax, op=dist.ReduceOp.MAX); dist.all_reduce(hmin, op=dist.ReduceOp.MIN)
 if rank == 0:
     print(f"mgpu_check world={world}: forces bit-identical to 1 rank: {bool(flags[0])}, energy identical: {bool(flags[1])}, "
-          f"60-step trajectory identical: {bool(flags[2])}, ranks agree: {hmax.item() == hmin.item()}, e={e2:.6f}")
+          f"100-step trajectory identical: {bool(flags[2])}, ranks agree: {hmax.item() == hmin.item()}, e={e2:.6f}")
     assert flags.min().item() == 1 and hmax.item() == hmin.item()
 single.close(); multi.close()
 dist.destroy_process_group()
