@@ -217,8 +217,7 @@ void b200_bonded_upload(b200_ctx* c) {
     }
 }
 
-void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy) {
-    cudaStream_t s = c->stream;
+void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy, cudaStream_t s) {
     ScopedTimer tm(c, B200_T_BONDED, s);
     const int wf = forces ? 1 : 0, we = energy ? 1 : 0;
     // with a communicator the excluded-pair corrections are split over the ranks like the direct-space rows (the energies are

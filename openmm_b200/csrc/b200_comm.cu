@@ -216,8 +216,8 @@ void b200_peer_reduce_forces(b200_ctx* c) {
     if (c->shardAtomEnd > c->shardAtomBegin) { peerReduceForces<<<c->smCount * 4, 256, 0, c->stream>>>(c->peers, c->Npad, c->shardAtomBegin, c->shardAtomEnd); LAUNCH_COUNT(c, 1); }
 }
 
-// The reciprocal forces arrive separately: rank 0's interpolation kernel stored them into this rank's landing buffer (PmePush) and
-// then raised PEER_SLOT_RECIP.  Wait for the flag, add the slice.  Integer addition: the total equals the all-in-one sum bit for bit.
+// The reciprocal forces arrive separately: rank 0's interpolation kernel stored them as floats in its recipF (PmePush) and then
+// raised PEER_SLOT_RECIP.  Wait for the flag, fetch and add the slice.  Integer addition: the total equals the all-in-one sum bit for bit.
 // The wait is a kernel of its own with ONE warp: a spinning grid that fills every SM (as the adding kernel would) can keep a block of
 // the reciprocal pipeline that needs a whole SM's registers from ever being scheduled on this GPU -- the flag would never be raised
 // (seen as a 20 s time-out on two GPUs, whenever the compute stream reached this point before the PME stream had finished).
@@ -232,12 +232,14 @@ __global__ void peerWaitRecip(const unsigned long long* flags, unsigned long lon
         __threadfence_system();
     }
 }
-__global__ void __launch_bounds__(256) peerAddRecip(long long* __restrict__ force, const long long* __restrict__ recip, int Npad, int aBegin, int aEnd) {
+// fetch this rank's slice of the PME rank's float forces (remote loads for every rank but rank 0), convert exactly as the
+// interpolation kernel would have (toFixed of the same float: the same bits) and add
+__global__ void __launch_bounds__(256) peerAddRecip(long long* __restrict__ force, const float* __restrict__ recip, int Npad, int aBegin, int aEnd) {
     const int count = aEnd - aBegin;
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < 3 * count; k += gridDim.x * blockDim.x) {
         const int comp = k / count, j = k - comp * count;
         const size_t off = (size_t)comp * Npad + aBegin + j;
-        force[off] += __ldcv(recip + off);
+        force[off] += toFixed(__ldcv(recip + off));
     }
 }
 void b200_peer_signal_recip(b200_ctx* c, cudaStream_t s) {
@@ -250,7 +252,7 @@ void b200_peer_add_recip(b200_ctx* c) {
     const int b = c->shardAtomBounds[c->commRank], e = c->shardAtomBounds[c->commRank + 1];
     // the wait is launched even for an empty slice: every rank consumes the signal before the next evaluation overwrites the buffers
     peerWaitRecip<<<1, 32, 0, c->stream>>>(c->peerFlags, c->peerSeq[PEER_SLOT_RECIP], c->counters);
-    if (e > b) peerAddRecip<<<c->smCount * 2, 256, 0, c->stream>>>(c->force, c->recipIn, c->Npad, b, e);
+    if (e > b) peerAddRecip<<<c->smCount * 2, 256, 0, c->stream>>>(c->force, c->peers.recip[0], c->Npad, b, e);
     LAUNCH_COUNT(c, e > b ? 2 : 1);
     c->recipPending = false;
 }
@@ -334,10 +336,10 @@ static void peerSetup(b200_ctx* c) {
     IpcBundle mine; memset(&mine, 0, sizeof(mine));
     dmalloc(c->peerFlags, (size_t)PEER_NUM_SLOTS * B200_MAX_PEERS);
     CUDA_CHECK(cudaMemset(c->peerFlags, 0, sizeof(unsigned long long) * PEER_NUM_SLOTS * B200_MAX_PEERS));
-    dmalloc(c->recipIn, (size_t)3 * c->Npad);
-    CUDA_CHECK(cudaMemset(c->recipIn, 0, sizeof(long long) * 3 * (size_t)c->Npad));
+    dmalloc(c->recipF, (size_t)3 * c->Npad);
+    CUDA_CHECK(cudaMemset(c->recipF, 0, sizeof(float) * 3 * (size_t)c->Npad));
     constexpr int NP = 7;
-    void* ptrs[NP] = {c->force, c->posq, c->posqCorr, c->velm, c->counters, c->peerFlags, c->recipIn};
+    void* ptrs[NP] = {c->force, c->posq, c->posqCorr, c->velm, c->counters, c->peerFlags, c->recipF};
     for (int k = 0; k < NP; k++) { mine.raw[k] = ptrs[k]; if (cudaIpcGetMemHandle(&mine.h[k], ptrs[k]) != cudaSuccess) { cudaGetLastError(); ok = 0; } }
     mine.pid = (long long)getpid(); mine.device = c->device;
     // exchange the handles (and whether everybody could export) through the communicator
@@ -369,7 +371,7 @@ static void peerSetup(b200_ctx* c) {
             else for (int k = 0; k < NP; k++) if (cudaIpcOpenMemHandle(&q[k], b.h[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; q[k] = nullptr; }
         }
         p.force[r] = (long long*)q[0]; p.posq[r] = (float4*)q[1]; p.posqCorr[r] = (float4*)q[2]; p.velm[r] = (double4*)q[3];
-        p.counters[r] = (DevCounters*)q[4]; p.flags[r] = (unsigned long long*)q[5]; p.recip[r] = (long long*)q[6];
+        p.counters[r] = (DevCounters*)q[4]; p.flags[r] = (unsigned long long*)q[5]; p.recip[r] = (float*)q[6];
     }
     // all ranks must agree: one more exchange of the outcome
     {
@@ -422,7 +424,7 @@ void b200_comm_destroy(b200_ctx* c) {
         }
         c->peerMode = false;
     }
-    dfree(c->peerFlags); dfree(c->recipIn);
+    dfree(c->peerFlags); dfree(c->recipF);
     if (c->ncclComm && g_nccl.CommDestroy) g_nccl.CommDestroy((ncclComm_t)c->ncclComm);
     c->ncclComm = nullptr;
 }

@@ -1063,14 +1063,15 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     // per-family event timing needs the families serialised: overlapping streams would charge waiting time to the wrong family
     const bool usePmeStream = c->usePmeStream && !c->timing;
     cudaStream_t ps = usePmeStream ? c->pmeStream : s;
-    // Multi-GPU over peer memory, plain PME, forces only: rank 0 stores the reciprocal forces into the landing buffers of the ranks
-    // that integrate the atoms and raises a flag, instead of adding them to its own force array; its compute stream does not wait for
-    // the PME stream, so the barrier / reduce-scatter of the direct-space forces overlaps the end of the reciprocal pipeline.
+    // Multi-GPU over peer memory, plain PME, forces only: rank 0 keeps the reciprocal forces out of its fixed-point force array; its
+    // interpolation kernel stores them as floats in a hand-over buffer and raises a flag, and every rank fetches the slice it
+    // integrates after the reduce-scatter.  Rank 0's compute stream does not wait for the PME stream, so the barrier / reduce-scatter
+    // of the direct-space forces overlaps the end of the reciprocal pipeline, and the last transfer is 12 instead of 24 bytes per atom.
     // Every rank takes the same decision (same arguments, same host tables) and counts the evaluation.
     bool push = false;
     if (forces && !energy && c->peerMode && c->commRanks > 1 && c->hasNonbonded && c->nb.method == B200_NB_PME && (groups & B200_GROUP_RECIPROCAL)) {
         // Worth it when rank 0 runs nothing but PME (4 ranks and more: it then finishes last).  With 2 ranks rank 0 also owns direct-space
-        // rows, its PME stream finishes first and the push only adds two launches (measured 0.927 against 0.906 ms/step on STMV).
+        // rows, its PME stream finishes first and the hand-over only adds launches (measured 0.927 against 0.906 ms/step on STMV).
         // B200_RECIP_PUSH=1 / 0 forces it on / off (the 2-GPU tests run it on).
         static const char* env = getenv("B200_RECIP_PUSH");
         const bool on = env ? atoi(env) != 0 : c->rank0PmeOnly;
@@ -1078,12 +1079,17 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     }
     if (push) { ++c->peerSeq[PEER_SLOT_RECIP]; c->recipPending = true; }
     else if (forces) c->recipPending = false;
+    static const bool bondedMain = getenv("B200_BONDED_MAIN") != nullptr;      // A/B switch
+    const bool bondedOnPme = !bondedMain && doRecip && usePmeStream && c->commRanks == 1 && c->partRanks == 1 && c->B < 6144;   // (STMV size: 1 % slower there)
     try {
     if (forces) CUDA_CHECK(cudaMemsetAsync(c->force, 0, sizeof(long long) * 3 * (size_t)c->Npad, s));
     if (energy) { zeroEnergy<<<1, 1, 0, s>>>(c->counters); LAUNCH_COUNT(c, 1); }
     if (doRecip) {
         c->recipPushNow = push;
         if (usePmeStream) { CUDA_CHECK(cudaEventRecord(c->evFork, s)); CUDA_CHECK(cudaStreamWaitEvent(ps, c->evFork, 0)); }
+        // one rank, small systems (latency-bound kernels): the exclusion corrections and bonded terms (short kernels, integer force sums)
+        // ride on the PME stream, off the longer list -> tile chain of the compute stream
+        if (bondedOnPme) b200_bonded_launch(c, groups, forces, energy, ps);
         if (c->nb.method == B200_NB_EWALD) b200_ewald_launch(c, ps, forces, energy); else b200_pme_launch(c, ps, forces, energy);
         if (usePmeStream) CUDA_CHECK(cudaEventRecord(c->evPmeDone, ps));
         c->recipPushNow = false;
@@ -1092,7 +1098,7 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
         prepareLists(c, verify);
         b200_tile_launch(c, forces, energy, false);
     }
-    if (c->partRank == 0 || c->commRanks > 1) b200_bonded_launch(c, groups, forces, energy);
+    if (!bondedOnPme && (c->partRank == 0 || c->commRanks > 1)) b200_bonded_launch(c, groups, forces, energy, s);
     static const bool pushJoin = getenv("B200_PUSH_JOIN") != nullptr;     // debug: keep the data path of the push, give up the overlap
     if (doRecip && usePmeStream && (!push || pushJoin)) CUDA_CHECK(cudaStreamWaitEvent(s, c->evPmeDone, 0));
     } catch (...) {
@@ -1213,7 +1219,7 @@ extern "C" int b200_integrator_create(b200_ctx* c, const b200_integrator_desc* d
 
 void b200_ensure_forces_reduced(b200_ctx* c) {
     if (!c->forcesPartial || c->commRanks < 2) return;
-    b200_peer_add_recip(c);             // pushed reciprocal forces: each rank adds its landing slice to its own partial forces first
+    b200_peer_add_recip(c);             // reciprocal forces handed over separately: each rank adds its slice to its own partial forces first
     b200_comm_allreduce_forces(c);      // collective: every rank reaches this point (int64 sums: exact, order independent)
     c->forcesPartial = false;
 }
@@ -1249,7 +1255,7 @@ void b200_advance(b200_ctx* c, cudaEvent_t* ev) {
             mark(2);
             b200_peer_signal_and_reduce_forces(c);                        // signal, then add every rank's slice as its signal arrives
         }
-        b200_peer_add_recip(c);                                           // + the reciprocal forces rank 0 pushed into this rank's landing buffer
+        b200_peer_add_recip(c);                                           // + this rank's slice of the reciprocal forces from rank 0's hand-over buffer
     } else {
         if (c->commRanks > 1) { b200_peer_sync_state(c); b200_ensure_forces_reduced(c); }     // replicated integration on every rank
         mark(2);

@@ -78,16 +78,16 @@ struct FFTPlan1D {
 struct PeerSet {
     long long* force[B200_MAX_PEERS]; float4* posq[B200_MAX_PEERS]; float4* posqCorr[B200_MAX_PEERS]; double4* velm[B200_MAX_PEERS];
     struct DevCounters* counters[B200_MAX_PEERS]; unsigned long long* flags[B200_MAX_PEERS];
-    long long* recip[B200_MAX_PEERS];     // per-rank landing buffer for the reciprocal-space forces of its own atoms
+    float* recip[B200_MAX_PEERS];         // per-rank buffer of reciprocal-space forces (only rank 0's, the PME rank's, is filled)
     int n, rank;
 };
-// where the interpolation kernel of the PME rank stores the reciprocal forces: n == 0 -> added to the local force array;
-// n > 0 -> atom i belongs to the rank r with bounds[r] <= i < bounds[r+1] and its force is stored into dst[r] (peer memory)
-struct PmePush { int n; int bounds[B200_MAX_PEERS + 1]; long long* dst[B200_MAX_PEERS]; };
+// where the interpolation kernel stores the reciprocal forces: dst == nullptr -> added to the local fixed-point force array;
+// otherwise stored as plain floats (x | y | z, Npad apart) for the owning ranks to fetch (multi-GPU, see computeImpl)
+struct PmePush { float* dst; };
 #define PEER_SLOT_FORCES 0      // "my forces of step seq are complete"
 #define PEER_SLOT_POSITIONS 1   // "my shard of step seq is integrated and written to every rank"
 #define PEER_SLOT_STATE 2       // "my shard's velocities / position remainders are written to every rank"
-#define PEER_SLOT_RECIP 3       // rank 0: "the reciprocal-space forces of evaluation seq are stored in every owner's landing buffer"
+#define PEER_SLOT_RECIP 3       // rank 0: "the reciprocal-space forces of evaluation seq are in my hand-over buffer"
 #define PEER_NUM_SLOTS 4
 
 // one reciprocal-space mesh with its transforms
@@ -207,13 +207,14 @@ struct b200_ctx {
     unsigned long long peerSeq[PEER_NUM_SLOTS] = {0, 0, 0, 0};
     int shardBegin = 0, shardEnd = 0;   // this rank's range of integration units (SETTLE clusters, then free atoms)
     int shardAtomBegin = 0, shardAtomEnd = 0; bool shardContiguous = false; int shardUnitsFor = -1;   // atoms of those units, when they form one slot range
-    // Reciprocal forces pushed to their owners: rank 0's interpolation kernel stores each atom's force straight into the landing
-    // buffer of the rank that integrates the atom (peer stores over NVLink), so the direct-space reduce-scatter no longer waits for PME.
-    long long* recipIn = nullptr;   // landing buffer, 3 * Npad (only this rank's slice is ever written)
+    // Reciprocal forces handed over separately: rank 0's interpolation kernel stores them as floats in recipF and raises a flag; every
+    // rank fetches the slice it integrates (NVLink loads, 12 bytes per atom instead of the 24 of the fixed-point array) after the
+    // reduce-scatter of the direct-space forces, which therefore no longer waits for the PME stream.
+    float* recipF = nullptr;        // 3 * Npad floats
     int shardAtomBounds[B200_MAX_PEERS + 1] = {0}; bool pushPlanOk = false;   // every rank's atom range; valid when the ranges tile [0, N) in rank order
     bool rank0PmeOnly = false;      // rank 0 owns no direct-space rows (4 ranks and more): the push pays off, see computeImpl
     bool recipPushNow = false;      // set around b200_pme_launch: this evaluation pushes
-    bool recipPending = false;      // the force arrays lack the reciprocal part; it is (or will be) in the owners' landing buffers
+    bool recipPending = false;      // the force arrays lack the reciprocal part; it is (or will be) in rank 0's hand-over buffer
 
     // the captured force evaluation (computeImpl): replayed while nothing that feeds a kernel argument has changed
     cudaGraphExec_t stepGraph = nullptr; long long stepGraphLaunches = 0; unsigned stepGraphGroups = 0; bool stepGraphDisp = false; int graphCaptures = 0;
@@ -281,7 +282,7 @@ void b200_pme_rescale(b200_ctx* c);
 void b200_pme_launch(b200_ctx* c, cudaStream_t s, bool forces, bool energy);
 void b200_ewald_launch(b200_ctx* c, cudaStream_t s, bool forces, bool energy);   // NonbondedForce::Ewald reciprocal sum (b200_ewald.cu)
 void b200_bonded_upload(b200_ctx* c);
-void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy);
+void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy, cudaStream_t s);
 void b200_integrate_setup(b200_ctx* c);
 void b200_integrate_step(b200_ctx* c);
 void b200_advance(b200_ctx* c, cudaEvent_t* traceEvents);   // after the forces: (barrier, reduce) integrate (publish, barrier), bookkeeping
@@ -296,8 +297,8 @@ void b200_peer_barrier(b200_ctx* c, int slot);        // signal + wait on the co
 void b200_peer_sync_state(b200_ctx* c);
 void b200_peer_plan_shard(b200_ctx* c);               // unit slice of this rank and whether its atoms are one contiguous slot range
 void b200_peer_reduce_forces(b200_ctx* c);
-void b200_peer_signal_recip(b200_ctx* c, cudaStream_t s);   // rank 0, after the interpolation kernel: "landing buffers are written"
-void b200_peer_add_recip(b200_ctx* c);                // wait for that signal, add this rank's slice of its landing buffer to its force array
+void b200_peer_signal_recip(b200_ctx* c, cudaStream_t s);   // rank 0, after the interpolation kernel: "hand-over buffer is written"
+void b200_peer_add_recip(b200_ctx* c);                // wait for that signal, fetch this rank's slice from rank 0 and add it to the force array
 void b200_peer_signal_and_reduce_forces(b200_ctx* c); // barrier + reduce-scatter in one kernel, peers added in the order they finish            // sum of all ranks' partial forces for this rank's atom range -> local force array
 void b200_peer_broadcast_positions(b200_ctx* c);      // rank 0's whole posq / posqCorr -> every rank
 void b200_peer_publish_positions(b200_ctx* c);        // this rank's slice of posq -> every rank               // all-gather of the sharded velocities / position remainders (collective)

@@ -378,19 +378,16 @@ __global__ void __launch_bounds__(CHUNK, 6) pmeInterpolateChunks(const float4* _
             }
         }
     }
-    if (!valid && (push.n == 0 || i >= N)) return;
+    if (!valid && (push.dst == nullptr || i >= N)) return;
     const float q = p.w;
     const float tx = gx * a.nx, ty = gy * a.ny, tz = gz * a.nz;
     const float fx = -q * (tx * (float)a.r0x);
     const float fy = -q * (tx * (float)a.r1x + ty * (float)a.r1y);
     const float fz = -q * (tx * (float)a.r2x + ty * (float)a.r2y + tz * (float)a.r2z);
-    if (push.n > 0) {
-        // multi-GPU: the force goes straight to the rank that integrates atom i (plain 8-byte stores into its landing buffer, over
-        // NVLink for the other ranks); atoms without a coefficient store zeros, so every entry of a slice is rewritten each time
-        int r = 0;
-        while (r < push.n - 1 && i >= push.bounds[r + 1]) r++;
-        long long* dst = push.dst[r];
-        dst[i] = valid ? toFixed(fx) : 0; dst[i + Npad] = valid ? toFixed(fy) : 0; dst[i + 2 * Npad] = valid ? toFixed(fz) : 0;
+    if (push.dst) {
+        // multi-GPU: plain float stores into this (the PME) rank's hand-over buffer; the owning ranks fetch their slices.  Atoms
+        // without a coefficient store zeros, so every entry is rewritten by every evaluation.
+        push.dst[i] = valid ? fx : 0.f; push.dst[i + Npad] = valid ? fy : 0.f; push.dst[i + 2 * Npad] = valid ? fz : 0.f;
         return;
     }
     atomicAddFixed(&force[i], toFixed(fx));
@@ -494,15 +491,10 @@ static void meshLaunch(b200_ctx* c, PmeMesh& m, cudaStream_t s, bool forces, boo
     { ScopedTimer tm(c, B200_T_FFT, s); b200_fft3d_reciprocal(c, m, s, a, energy, forces); }
     if (forces) {
         ScopedTimer tm(c, B200_T_INTERPOLATE, s);
-        PmePush push; memset(&push, 0, sizeof(push));
-        if (c->recipPushNow && &m == &c->mesh[0]) {
-            push.n = c->commRanks;
-            for (int r = 0; r < c->commRanks; r++) { push.bounds[r] = c->shardAtomBounds[r]; push.dst[r] = c->peers.recip[r]; }
-            push.bounds[c->commRanks] = c->shardAtomBounds[c->commRanks];
-        }
+        PmePush push; push.dst = (c->recipPushNow && &m == &c->mesh[0]) ? c->recipF : nullptr;
         pmeInterpolateChunks<<<chunks, CHUNK, 0, s>>>(c->posq, coef, c->N, c->Npad, a, m.gridReal, c->force, push);
         LAUNCH_COUNT(c, 1);
-        if (push.n > 0) b200_peer_signal_recip(c, s);
+        if (push.dst) b200_peer_signal_recip(c, s);
     }
     CUDA_CHECK(cudaGetLastError());
 }
