@@ -69,7 +69,6 @@ extern "C" int b200_set_partition(b200_ctx* c, int32_t rank, int32_t nranks) {
     if (nranks > 1 && c->commRanks > 1) {   // only with a communicator: logical ranks on one device are plain equal shares
         const double s0 = std::max(0.0, (1.0 - (nranks - 1) * rho) / nranks);
         share[0] = s0;
-        c->rank0PmeOnly = s0 == 0.0;
         for (int r = 1; r < nranks; r++) share[r] = (1.0 - s0) / (nranks - 1);
     }
     // weighted round-robin over a period of 64 rows (largest-remainder / Bresenham spreading)
@@ -241,6 +240,11 @@ __global__ void __launch_bounds__(256) peerAddRecip(long long* __restrict__ forc
         const size_t off = (size_t)comp * Npad + aBegin + j;
         force[off] += toFixed(__ldcv(recip + off));
     }
+}
+// "my forces of the coming barrier are complete", raised ahead of the barrier kernel (which repeats the same value and then waits)
+void b200_peer_signal_forces_early(b200_ctx* c) {
+    peerSignalKernel<<<1, 32, 0, c->stream>>>(c->peers, PEER_SLOT_FORCES, c->peerSeq[PEER_SLOT_FORCES] + 1);
+    LAUNCH_COUNT(c, 1);
 }
 void b200_peer_signal_recip(b200_ctx* c, cudaStream_t s) {
     peerSignalKernel<<<1, 32, 0, s>>>(c->peers, PEER_SLOT_RECIP, c->peerSeq[PEER_SLOT_RECIP]);

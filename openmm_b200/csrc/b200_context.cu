@@ -1070,11 +1070,12 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     // Every rank takes the same decision (same arguments, same host tables) and counts the evaluation.
     bool push = false;
     if (forces && !energy && c->peerMode && c->commRanks > 1 && c->hasNonbonded && c->nb.method == B200_NB_PME && (groups & B200_GROUP_RECIPROCAL)) {
-        // Worth it when rank 0 runs nothing but PME (4 ranks and more: it then finishes last).  With 2 ranks rank 0 also owns direct-space
-        // rows, its PME stream finishes first and the hand-over only adds launches (measured 0.927 against 0.906 ms/step on STMV).
-        // B200_RECIP_PUSH=1 / 0 forces it on / off (the 2-GPU tests run it on).
+        // Opt-in (B200_RECIP_PUSH=1; the 2-GPU tests run it both ways): measured on STMV it does not pay.  2 GPUs 0.927-0.943 against
+        // 0.906 ms/step (rank 0 also owns direct-space rows, its PME stream finishes first anyway); 8 GPUs 0.516 against 0.512-0.521
+        // (whatever runs beside the interpolation kernel on the PME rank -- its own barrier spin and reduce, the peers' reads -- delays
+        // the reciprocal pipeline by about what the overlap saves).
         static const char* env = getenv("B200_RECIP_PUSH");
-        const bool on = env ? atoi(env) != 0 : c->rank0PmeOnly;
+        const bool on = env && atoi(env) != 0;
         if (on) { b200_peer_plan_shard(c); push = c->pushPlanOk; }
     }
     if (push) { ++c->peerSeq[PEER_SLOT_RECIP]; c->recipPending = true; }
@@ -1247,6 +1248,13 @@ void b200_advance(b200_ctx* c, cudaEvent_t* ev) {
     c->peerStepActive = peerStepPlan(c);
     if (c->peerStepActive) {
         static const bool separate = getenv("B200_ORDERED_REDUCE") == nullptr;     // default: barrier kernel, then one-pass reduce kernel
+        if (separate && c->recipPending && c->partRank == 0 && c->usePmeStream && !c->timing) {
+            // The PME rank with the reciprocal forces handed over separately: its fixed-point array is complete, so the others are told
+            // at once, but its own barrier spin and reduce kernel wait for the PME stream -- measured on 8 GPUs, running them beside the
+            // interpolation kernel delayed the reciprocal pipeline, which everybody waits for, by ~45 us.
+            b200_peer_signal_forces_early(c);
+            CUDA_CHECK(cudaStreamWaitEvent(c->stream, c->evPmeDone, 0));
+        }
         if (separate) {
             b200_peer_barrier(c, PEER_SLOT_FORCES);                       // every rank's partial forces are complete
             mark(2);

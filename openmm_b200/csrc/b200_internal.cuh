@@ -212,7 +212,6 @@ struct b200_ctx {
     // reduce-scatter of the direct-space forces, which therefore no longer waits for the PME stream.
     float* recipF = nullptr;        // 3 * Npad floats
     int shardAtomBounds[B200_MAX_PEERS + 1] = {0}; bool pushPlanOk = false;   // every rank's atom range; valid when the ranges tile [0, N) in rank order
-    bool rank0PmeOnly = false;      // rank 0 owns no direct-space rows (4 ranks and more): the push pays off, see computeImpl
     bool recipPushNow = false;      // set around b200_pme_launch: this evaluation pushes
     bool recipPending = false;      // the force arrays lack the reciprocal part; it is (or will be) in rank 0's hand-over buffer
 
@@ -297,6 +296,7 @@ void b200_peer_barrier(b200_ctx* c, int slot);        // signal + wait on the co
 void b200_peer_sync_state(b200_ctx* c);
 void b200_peer_plan_shard(b200_ctx* c);               // unit slice of this rank and whether its atoms are one contiguous slot range
 void b200_peer_reduce_forces(b200_ctx* c);
+void b200_peer_signal_forces_early(b200_ctx* c);
 void b200_peer_signal_recip(b200_ctx* c, cudaStream_t s);   // rank 0, after the interpolation kernel: "hand-over buffer is written"
 void b200_peer_add_recip(b200_ctx* c);                // wait for that signal, fetch this rank's slice from rank 0 and add it to the force array
 void b200_peer_signal_and_reduce_forces(b200_ctx* c); // barrier + reduce-scatter in one kernel, peers added in the order they finish            // sum of all ranks' partial forces for this rank's atom range -> local force array

@@ -10,9 +10,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("world,push", [(2, "0"), (2, "1"), (4, None)])
+@pytest.mark.parametrize("world,push", [(2, None), (2, "1"), (4, None), (4, "1")])
 def test_multi_gpu_step_is_bit_identical_to_one_rank(world, push):
-    # push: B200_RECIP_PUSH (reciprocal forces stored straight into the owners' landing buffers); default on from four ranks
+    # push: B200_RECIP_PUSH (reciprocal forces stored straight into the owners' landing buffers); opt-in
     import torch
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs, this box has {torch.cuda.device_count()}")
