@@ -108,6 +108,10 @@ int  b200_periodic_torsions_create(b200_ctx* ctx, int32_t n, const int32_t* atom
 
 /* HarmonicBondForce/HarmonicAngleForce/PeriodicTorsionForce::setUsesPeriodicBoundaryConditions for all terms of one kind (0, 1, 2) */
 int  b200_bonded_set_periodic(b200_ctx* ctx, int32_t kind, int32_t periodic);
+/* Which terms of one kind the following b200_compute calls evaluate: nranges pairs (first, count) over the creation order, or
+ * nranges = 0 for all of them.  Lets several forces of one kind live in different force groups (ContextImpl::calcForcesAndEnergy
+ * calls only the kernels of the requested groups, ContextImpl.cpp; the reference keeps one kernel object per force). */
+int  b200_bonded_set_active(b200_ctx* ctx, int32_t kind, int32_t nranges, const int32_t* first_count /*[2 nranges]*/);
 /* copyParametersToContext of the three bonded kernels (kernels.h:359,433,507): new parameters for terms [first, first+n) of kind
  * 0 = bonds (p0 length, p1 k), 1 = angles (p0 angle, p1 k), 2 = torsions (p0 phase, p1 k, periodicity); term indices count over all
  * forces of that kind in the order they were created */

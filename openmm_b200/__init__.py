@@ -61,7 +61,7 @@ class NblistStats(ctypes.Structure):
 EXPORTED_SYMBOLS = [
     "b200_context_create", "b200_context_destroy", "b200_last_error", "b200_device_count", "b200_nonbonded_create",
     "b200_nonbonded_update_parameters", "b200_nonbonded_get_pme_parameters", "b200_nonbonded_get_ljpme_parameters", "b200_harmonic_bonds_create",
-    "b200_harmonic_angles_create", "b200_periodic_torsions_create", "b200_bonded_update_parameters", "b200_bonded_set_periodic", "b200_set_positions", "b200_set_positions_root", "b200_get_positions",
+    "b200_harmonic_angles_create", "b200_periodic_torsions_create", "b200_bonded_update_parameters", "b200_bonded_set_periodic", "b200_bonded_set_active", "b200_set_positions", "b200_set_positions_root", "b200_get_positions",
     "b200_set_velocities", "b200_get_velocities", "b200_get_forces", "b200_set_box", "b200_get_box", "b200_set_time",
     "b200_get_time", "b200_compute", "b200_compute_host", "b200_integrator_create", "b200_step", "b200_integrate",
     "b200_remove_cm_motion", "b200_apply_constraints",
@@ -224,6 +224,12 @@ class Context:
     def add_periodic_torsions(self, atoms, periodicity, phase, k):
         a, ap = _i(np.asarray(atoms).reshape(-1)); n, np_ = _i(periodicity); p, pp = _d(phase); kk, kp = _d(k)
         _check(self.lib.b200_periodic_torsions_create(self.handle, len(p), ap, np_, pp, kp, 0))
+
+    def bonded_set_active(self, kind, ranges=()):
+        """terms of kind 0 bonds / 1 angles / 2 torsions evaluated by the following compute() calls: (first, count) pairs over the
+        creation order, or nothing for all (several forces of one kind in different force groups)"""
+        r = np.asarray(ranges, dtype=np.int32).reshape(-1)
+        _check(self.lib.b200_bonded_set_active(self.handle, int(kind), r.size // 2, r.ctypes.data_as(c_int32_p) if r.size else None))
 
     # UpdateStateDataKernel
     def set_positions(self, xyz):

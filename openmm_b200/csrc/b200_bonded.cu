@@ -239,9 +239,18 @@ void b200_bonded_launch(b200_ctx* c, unsigned groups, bool forces, bool energy, 
         if (c->numExceptions > 0) { exceptions14<<<(c->numExceptions + 127) / 128, 128, 0, s>>>(c->posq, c->dExcPairs, c->dExcParams, c->numExceptions, c->boxD, c->nb.exceptions_use_periodic, c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
     }
     {
-        if (c->numBonds > 0 && (groups & B200_GROUP_BONDS)) { harmonicBonds<<<(c->numBonds + 127) / 128, 128, 0, s>>>(c->posq, c->bondAtoms, c->bondParams, c->numBonds, c->boxD, c->bondedPeriodic[0], c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
-        if (c->numAngles > 0 && (groups & B200_GROUP_ANGLES)) { harmonicAngles<<<(c->numAngles + 127) / 128, 128, 0, s>>>(c->posq, c->angleAtoms, c->angleParams, c->numAngles, c->boxD, c->bondedPeriodic[1], c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
-        if (c->numTorsions > 0 && (groups & B200_GROUP_TORSIONS)) { periodicTorsions<<<(c->numTorsions + 127) / 128, 128, 0, s>>>(c->posq, c->torsionAtoms, c->torsionParams, c->numTorsions, c->boxD, c->bondedPeriodic[2], c->force, c->Npad, c->counters, wf, we); LAUNCH_COUNT(c, 1); }
+        // every term of a kind, or the ranges selected by b200_bonded_set_active (forces of one kind in different force groups)
+        auto ranges = [&](int kind, int total, auto launch) {
+            const std::vector<int>& r = c->bondedActive[kind];
+            if (r.empty()) { if (total > 0) { launch(0, total); LAUNCH_COUNT(c, 1); } return; }
+            for (size_t k = 0; k + 1 < r.size(); k += 2) if (r[k + 1] > 0) { launch(r[k], r[k + 1]); LAUNCH_COUNT(c, 1); }
+        };
+        if (groups & B200_GROUP_BONDS) ranges(0, c->numBonds, [&](int first, int n) {
+            harmonicBonds<<<(n + 127) / 128, 128, 0, s>>>(c->posq, c->bondAtoms + first, c->bondParams + first, n, c->boxD, c->bondedPeriodic[0], c->force, c->Npad, c->counters, wf, we); });
+        if (groups & B200_GROUP_ANGLES) ranges(1, c->numAngles, [&](int first, int n) {
+            harmonicAngles<<<(n + 127) / 128, 128, 0, s>>>(c->posq, c->angleAtoms + first, c->angleParams + first, n, c->boxD, c->bondedPeriodic[1], c->force, c->Npad, c->counters, wf, we); });
+        if (groups & B200_GROUP_TORSIONS) ranges(2, c->numTorsions, [&](int first, int n) {
+            periodicTorsions<<<(n + 127) / 128, 128, 0, s>>>(c->posq, c->torsionAtoms + first, c->torsionParams + first, n, c->boxD, c->bondedPeriodic[2], c->force, c->Npad, c->counters, wf, we); });
     }
     CUDA_CHECK(cudaGetLastError());
 }

@@ -79,6 +79,7 @@ extern "C" int b200_context_create(const b200_system_desc* desc, b200_ctx** out)
     c->usePmeStream = !(desc->flags & B200_CTX_DISABLE_PME_STREAM);
     CUDA_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CUDA_CHECK(cudaStreamCreateWithFlags(&c->pmeStream, cudaStreamNonBlocking));
+    CUDA_CHECK(cudaStreamCreateWithFlags(&c->auxStream, cudaStreamNonBlocking));
     CUDA_CHECK(cudaEventCreateWithFlags(&c->evFork, cudaEventDisableTiming));
     CUDA_CHECK(cudaEventCreateWithFlags(&c->evPmeDone, cudaEventDisableTiming));
     memset(c->partTable.owner, 0, sizeof(c->partTable.owner));
@@ -139,7 +140,7 @@ extern "C" void b200_context_destroy(b200_ctx* c) {
     dfree(c->dStage);
     for (auto& t : c->timers) for (auto& p : t.pending) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     cudaEventDestroy(c->evFork); cudaEventDestroy(c->evPmeDone);
-    cudaStreamDestroy(c->stream); cudaStreamDestroy(c->pmeStream);
+    cudaStreamDestroy(c->stream); cudaStreamDestroy(c->pmeStream); cudaStreamDestroy(c->auxStream);
     delete c;
 }
 
@@ -338,6 +339,16 @@ extern "C" int b200_periodic_torsions_create(b200_ctx* c, int32_t n, const int32
     if (c->finalized) throw B200Error(B200_ERR_INVALID, "forces must be created before the first computation");
     for (int i = 0; i < n; i++) { for (int j = 0; j < 4; j++) c->hTorsionAtoms.push_back(atoms[4 * i + j]); c->hTorsionPeriod.push_back(periodicity[i]); c->hTorsionParams.push_back(phase[i]); c->hTorsionParams.push_back(k[i]); }
     API_END
+}
+
+extern "C" int b200_bonded_set_active(b200_ctx* c, int32_t kind, int32_t nranges, const int32_t* firstCount) {
+    if (!c || kind < 0 || kind > 2 || nranges < 0 || (nranges > 0 && !firstCount)) { b200_set_error("b200_bonded_set_active: bad arguments"); return B200_ERR_INVALID; }
+    const int total = kind == 0 ? (int)c->hBondParams.size() / 2 : kind == 1 ? (int)c->hAngleParams.size() / 2 : (int)c->hTorsionPeriod.size();
+    std::vector<int> r(firstCount, firstCount + 2 * (size_t)nranges);
+    for (int k = 0; k < nranges; k++)
+        if (r[2 * k] < 0 || r[2 * k + 1] < 0 || (long long)r[2 * k] + r[2 * k + 1] > total) { b200_set_error("b200_bonded_set_active: range outside the terms of this kind"); return B200_ERR_INVALID; }
+    if (r != c->bondedActive[kind]) { b200_graph_invalidate(c); c->bondedActive[kind] = r; }     // the ranges are kernel arguments of the captured evaluation
+    return B200_OK;
 }
 
 extern "C" int b200_bonded_set_periodic(b200_ctx* c, int32_t kind, int32_t periodic) {
@@ -1057,7 +1068,7 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     }
     const bool capturing = graphable;
     const long long launchesAtEntry = c->launchCount;
-    if (capturing) { b200_graph_invalidate(c); CUDA_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal)); }
+    if (capturing) { b200_graph_invalidate(c); CUDA_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal)); c->capturing = true; }
     const bool doRecip = c->hasNonbonded && c->nb.method >= B200_NB_EWALD && (groups & B200_GROUP_RECIPROCAL) && c->partRank == 0;
     const bool doDirect = c->hasNonbonded && (groups & B200_GROUP_DIRECT);
     // per-family event timing needs the families serialised: overlapping streams would charge waiting time to the wrong family
@@ -1103,11 +1114,12 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     static const bool pushJoin = getenv("B200_PUSH_JOIN") != nullptr;     // debug: keep the data path of the push, give up the overlap
     if (doRecip && usePmeStream && (!push || pushJoin)) CUDA_CHECK(cudaStreamWaitEvent(s, c->evPmeDone, 0));
     } catch (...) {
-        if (capturing) { cudaGraph_t g = nullptr; cudaStreamEndCapture(s, &g); if (g) cudaGraphDestroy(g); cudaGetLastError(); c->graphCaptures = 1 << 20; }
+        if (capturing) { c->capturing = false; cudaGraph_t g = nullptr; cudaStreamEndCapture(s, &g); if (g) cudaGraphDestroy(g); cudaGetLastError(); c->graphCaptures = 1 << 20; }
         throw;
     }
     if (capturing) {
         cudaGraph_t g = nullptr;
+        c->capturing = false;
         CUDA_CHECK(cudaStreamEndCapture(s, &g));
         c->graphCaptures++;
         CUDA_CHECK(cudaGraphInstantiate(&c->stepGraph, g, 0));

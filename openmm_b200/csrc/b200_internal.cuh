@@ -50,6 +50,8 @@ struct DevCounters {
     unsigned long long pairHash;   // order-independent hash of the emitted pair set (parity probe)
     long long    energy[8];     // fixed point 2^32: 0 direct tiles, 1 exclusion corr, 2 exceptions, 3 reciprocal, 4 bonded, 5 kinetic*2
     long long    cm[4][4];      // fixed point 2^20: sum m v (x,y,z); slots 0-2 rotate through the fused stepping loop, slot 3 is the stand-alone pass
+    int          rebuildNow;    // the list phase in progress rebuilds (copy of `rebuild` taken by nbBegin, which clears the request)
+    int          pad0;
 };
 #define E_DIRECT 0
 #define E_EXCLCORR 1
@@ -113,7 +115,7 @@ struct TimerSlot {
 struct b200_ctx {
     int device = 0;
     int N = 0, Npad = 0, B = 0, numSuper = 0;
-    cudaStream_t stream = nullptr, pmeStream = nullptr;
+    cudaStream_t stream = nullptr, pmeStream = nullptr, auxStream = nullptr;   // aux: records the conditional body of the captured evaluation
     cudaEvent_t evFork = nullptr, evPmeDone = nullptr;
     bool usePmeStream = true;
     BoxD boxD; BoxF boxF;
@@ -216,6 +218,7 @@ struct b200_ctx {
     bool recipPending = false;      // the force arrays lack the reciprocal part; it is (or will be) in rank 0's hand-over buffer
 
     // the captured force evaluation (computeImpl): replayed while nothing that feeds a kernel argument has changed
+    bool capturing = false;         // computeImpl is recording the evaluation: b200_nblist_prepare puts the rebuild kernels into a conditional node
     cudaGraphExec_t stepGraph = nullptr; long long stepGraphLaunches = 0; unsigned stepGraphGroups = 0; bool stepGraphDisp = false; int graphCaptures = 0;
 
     // PME: mesh[0] = Coulomb, mesh[1] = dispersion (LJPME only)
@@ -225,6 +228,7 @@ struct b200_ctx {
     double ljSelfEnergy = 0;        // + alpha_d^6/12 * sum c6_i^2 (ReferenceLJCoulombIxn.cpp:224-227)
 
     // bonded
+    std::vector<int> bondedActive[3];       // (first, count) pairs selected by b200_bonded_set_active; empty = every term of the kind
     int numBonds = 0; int2* bondAtoms = nullptr; float2* bondParams = nullptr;
     int numAngles = 0; int4* angleAtoms = nullptr; float2* angleParams = nullptr;
     int numTorsions = 0; int4* torsionAtoms = nullptr; float4* torsionParams = nullptr;

@@ -7,7 +7,8 @@
 // block and 32 consecutive blocks a compact "super block"; the build is a two-level bounding-box sweep
 // followed by an exact per-atom test against the 32 atoms of block X and a ballot/popc compaction of the
 // surviving j atoms into work units of up to 8 tiles.  Everything is decided on the device: the kernels
-// are launched every step and return immediately unless counters->rebuild is set.
+// are launched every step; nbBegin takes the rebuild request (counters->rebuild -> rebuildNow) and the
+// others return immediately unless it found one.
 #include "b200_internal.cuh"
 #include <algorithm>
 
@@ -30,7 +31,7 @@ __global__ void nbCheckDisplacement(const float4* __restrict__ posq, const float
 // ---- per-block bounding boxes (findBlockBounds, findInteractingBlocks.cu:41-102), one warp per block
 __global__ void nbBlockBounds(const float4* __restrict__ posq, float4* __restrict__ refPosq, int N, int B, BoxF box,
                               float4* __restrict__ blockCenter, float4* __restrict__ blockHalf, DevCounters* counters) {
-    if (!counters->rebuild) return;
+    if (!counters->rebuildNow) return;
     const int lane = threadIdx.x & 31;
     const int warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     if (blockIdx.x == 0 && threadIdx.x == 0) { counters->numUnits = 0; counters->numTiles = 0; counters->numSparseTiles = 0; counters->rebuildCount++; }
@@ -60,7 +61,7 @@ __global__ void nbBlockBounds(const float4* __restrict__ posq, float4* __restric
 // ---- bounding boxes of groups of 32 consecutive blocks ("large blocks", findInteractingBlocks.cu:138-175)
 __global__ void nbSuperBounds(const float4* __restrict__ blockCenter, const float4* __restrict__ blockHalf, int B, int numSuper, BoxF box,
                               float4* __restrict__ superCenter, float4* __restrict__ superHalf, const DevCounters* counters) {
-    if (!counters->rebuild) return;
+    if (!counters->rebuildNow) return;
     const int lane = threadIdx.x & 31;
     const int warpsPerGrid = (gridDim.x * blockDim.x) >> 5;
     for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < numSuper; s += warpsPerGrid) {
@@ -203,7 +204,7 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
         const int* __restrict__ exclRowStart, const int* __restrict__ exclRowCols,
         int4* __restrict__ units, int* __restrict__ jAtoms, unsigned unitCapacity, unsigned tileCapacity,
         int partRank, b200_ctx::OwnerTable table, int split, int unitTiles, DevCounters* counters) {
-    if (!counters->rebuild) return;
+    if (!counters->rebuildNow) return;
     __shared__ float4 sX[NB_WARPS][32];
     __shared__ float4 sXp[NB_WARPS][32];    // the same atoms packed in pairs (i, i+16) for the FP32x2 exact test
     __shared__ float4 sQ[NB_WARPS][64];     // queue of candidate atoms that passed the box test: (rel. position, slot)
@@ -330,8 +331,14 @@ __global__ void __launch_bounds__(NB_THREADS) nbBuild(
     }
 }
 
-// last kernel of the list phase (every step): clears the rebuild request and rewinds the tile kernel's work queue
-__global__ void nbFinish(DevCounters* counters) { counters->rebuild = 0; counters->workNext = 0; }
+// First kernel of the list phase (every step): takes the rebuild request (set by the integration kernel's displacement check, by
+// nbCheckDisplacement or by the host), clears it and rewinds the tile kernel's work queue.  Inside the captured evaluation it also
+// sets the condition of the graph's IF node that holds the three rebuild kernels, so a step that keeps its list launches none of them.
+__global__ void nbBegin(DevCounters* counters, cudaGraphConditionalHandle handle, int useHandle) {
+    const int r = counters->rebuild;
+    counters->rebuildNow = r; counters->rebuild = 0; counters->workNext = 0;
+    if (useHandle) cudaGraphSetConditional(handle, r ? 1u : 0u);
+}
 __global__ void nbSetRebuild(DevCounters* counters) { counters->rebuild = 1; }
 
 void b200_nblist_alloc(b200_ctx* c) {
@@ -360,8 +367,34 @@ void b200_nblist_prepare(b200_ctx* c) {
         nbBox.ax = nbBox.by = nbBox.cz = 1.0e18f; nbBox.bx = nbBox.cx = nbBox.cy = 0.f; nbBox.iax = nbBox.iby = nbBox.icz = 1.0e-18f; nbBox.triclinic = 0;
     }
     if (!c->dispChecked) { nbCheckDisplacement<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, maxDisp * maxDisp, c->counters); LAUNCH_COUNT(c, 1); }
-    nbBlockBounds<<<grid, 256, 0, c->stream>>>(c->posq, c->refPosq, c->N, c->B, nbBox, c->blockCenter, c->blockHalf, c->counters);
-    nbSuperBounds<<<(c->numSuper + 7) / 8, 256, 0, c->stream>>>(c->blockCenter, c->blockHalf, c->B, c->numSuper, nbBox, c->superCenter, c->superHalf, c->counters);
+    // The three rebuild kernels.  Launched one by one they return at once unless nbBegin found a rebuild request; while computeImpl
+    // records the evaluation as a CUDA graph they go into the body of a conditional IF node instead (recorded on the aux stream with
+    // cudaStreamBeginCaptureToGraph), so that a replayed step which keeps its list does not launch them at all (DHFR-size: 3 + 3 + 7 us
+    // of empty launches on two steps out of three).  Opt-in with B200_GRAPH_COND=1: measured, the IF node costs what it saves.
+    cudaStream_t st = c->stream;
+    cudaGraphConditionalHandle handle = 0;
+    cudaGraph_t bodyGraph = nullptr; cudaGraphNode_t condNode = nullptr;
+    static const bool useCond = getenv("B200_GRAPH_COND") != nullptr;     // opt-in, see DESIGN.md (the IF node costs about what it saves)
+    const bool conditional = c->capturing && useCond;
+    if (conditional) {
+        cudaStreamCaptureStatus status; cudaGraph_t graph = nullptr; const cudaGraphNode_t* deps = nullptr; size_t numDeps = 0;
+        CUDA_CHECK(cudaStreamGetCaptureInfo(c->stream, &status, nullptr, &graph, &deps, &numDeps));
+        if (status != cudaStreamCaptureStatusActive || !graph) throw B200Error(B200_ERR_CUDA, "b200_nblist_prepare: the compute stream is not being captured");
+        CUDA_CHECK(cudaGraphConditionalHandleCreate(&handle, graph, 0, cudaGraphCondAssignDefault));
+        nbBegin<<<1, 1, 0, c->stream>>>(c->counters, handle, 1);
+        CUDA_CHECK(cudaStreamGetCaptureInfo(c->stream, &status, nullptr, &graph, &deps, &numDeps));
+        cudaGraphNodeParams np = {};
+        np.type = cudaGraphNodeTypeConditional;
+        np.conditional.handle = handle; np.conditional.type = cudaGraphCondTypeIf; np.conditional.size = 1;
+        CUDA_CHECK(cudaGraphAddNode(&condNode, graph, deps, numDeps, &np));
+        bodyGraph = np.conditional.phGraph_out[0];
+        CUDA_CHECK(cudaStreamBeginCaptureToGraph(c->auxStream, bodyGraph, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+        st = c->auxStream;
+    } else {
+        nbBegin<<<1, 1, 0, c->stream>>>(c->counters, handle, 0);
+    }
+    nbBlockBounds<<<grid, 256, 0, st>>>(c->posq, c->refPosq, c->N, c->B, nbBox, c->blockCenter, c->blockHalf, c->counters);
+    nbSuperBounds<<<(c->numSuper + 7) / 8, 256, 0, st>>>(c->blockCenter, c->blockHalf, c->B, c->numSuper, nbBox, c->superCenter, c->superHalf, c->counters);
     const float rcp = (float)c->paddedCutoff;
     int owned = 0;
     for (int i = 0; i < 64; i++) owned += c->partTable.owner[i] == c->partRank ? 1 : 0;
@@ -376,10 +409,15 @@ void b200_nblist_prepare(b200_ctx* c) {
     { static const char* e = getenv("B200_UNIT_TILES_RT"); if (e) unitTiles = std::max(1, std::min(B200_UNIT_TILES, atoi(e))); }
     int buildGrid = (rows + NB_WARPS - 1) / NB_WARPS;
     if (buildGrid > c->smCount * 16) buildGrid = c->smCount * 16;
-    nbBuild<<<buildGrid, NB_THREADS, 0, c->stream>>>(c->posq, c->N, c->B, c->numSuper, nbBox, rcp * rcp, c->sparseMax,
+    nbBuild<<<buildGrid, NB_THREADS, 0, st>>>(c->posq, c->N, c->B, c->numSuper, nbBox, rcp * rcp, c->sparseMax,
         c->blockCenter, c->blockHalf, c->superCenter, c->superHalf, c->exclRowStart, c->exclRowCols,
         c->units, c->jAtoms, (unsigned)c->unitCapacity, (unsigned)c->tileCapacity, c->partRank, c->partTable, split, unitTiles, c->counters);
-    nbFinish<<<1, 1, 0, c->stream>>>(c->counters);
-    LAUNCH_COUNT(c, 4);
+    if (conditional) {
+        cudaGraph_t done = nullptr;
+        CUDA_CHECK(cudaStreamEndCapture(c->auxStream, &done));
+        // what follows on the compute stream (the tile kernel) depends on the IF node
+        CUDA_CHECK(cudaStreamUpdateCaptureDependencies(c->stream, &condNode, 1, cudaStreamSetCaptureDependencies));
+        LAUNCH_COUNT(c, 1);      // the body's kernels are not counted: most replays skip them
+    } else LAUNCH_COUNT(c, 4);
     CUDA_CHECK(cudaGetLastError());
 }

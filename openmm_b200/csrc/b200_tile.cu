@@ -604,7 +604,7 @@ void b200_tile_launch(b200_ctx* c, bool forces, bool energy, bool emitPairs) {
         a.krf = (float)(pow(rc, -3.0) * (eps - 1.0) / (2.0 * eps + 1.0)); a.crf = (float)((1.0 / rc) * 3.0 * eps / (2.0 * eps + 1.0));
     }
     if (method == B200_NB_NOCUTOFF) { a.rc2 = INFINITY; a.rc2d = INFINITY; a.rcPadded = INFINITY; a.borderTol = 0.f; }
-    // (the work queue head was rewound by nbFinish, the last kernel of b200_nblist_prepare, which precedes every tile launch)
+    // (the work queue head was rewound by nbBegin, the first kernel of b200_nblist_prepare, which precedes every tile launch)
     ScopedTimer tm(c, B200_T_TILE, c->stream);
     a.ljAlpha2 = a.invCut6 = a.ljShift = 0.f;
     if (c->ljpme) {

@@ -25,6 +25,7 @@ namespace B200Plugin {
 // ---------------------------------------------------------------------------------------------- forces and energy
 void B200CalcForcesAndEnergyKernel::beginComputation(ContextImpl&, bool, bool, int) {
     d.pendingGroups = 0;   // every ForceImpl that takes part in this evaluation adds its bit from its kernel's execute()
+    for (auto& r : d.bondedActive) r.clear();
 }
 
 double B200CalcForcesAndEnergyKernel::finishComputation(ContextImpl&, bool includeForce, bool includeEnergy, int, bool& valid) {
@@ -32,6 +33,17 @@ double B200CalcForcesAndEnergyKernel::finishComputation(ContextImpl&, bool inclu
     // the force buffer is cleared by the computation even when no group is requested, as clearAutoclearBuffers does (CudaKernels.cpp:66)
     // every rank evaluates its share (multi-GPU: the energies are all-reduced inside, the forces stay partial until someone needs them)
     vector<double> e(max<size_t>(1, d.ranks.size()), 0.0);
+    // Forces of one kind in different force groups: ContextImpl ran only the kernels of the requested groups, and each left its range
+    // of terms; when that is not every force of the kind, the library is told which ranges to evaluate (b200_bonded_set_active).
+    static const unsigned kindBit[3] = {B200_GROUP_BONDS, B200_GROUP_ANGLES, B200_GROUP_TORSIONS};
+    for (int kind = 0; kind < 3; kind++) {
+        if (!(d.pendingGroups & kindBit[kind])) continue;
+        const bool subset = (int)d.bondedActive[kind].size() / 2 != d.bondedForces[kind];
+        if (!subset && !d.bondedRestricted[kind]) continue;
+        const vector<int>& r = d.bondedActive[kind];
+        d.all([&](b200_ctx* c, int) { return b200_bonded_set_active(c, kind, subset ? (int)r.size() / 2 : 0, subset ? r.data() : nullptr); });
+        d.bondedRestricted[kind] = subset;
+    }
     d.all([&](b200_ctx* c, int r) { return b200_compute(c, d.pendingGroups, includeForce ? 1 : 0, includeEnergy ? 1 : 0, &e[r]); });
     energy = e[0];
     valid = true;            // list growth/retry is handled inside the library (CudaNonbondedUtilities.cpp:441-479 does it by invalidating)
@@ -234,17 +246,15 @@ void B200CalcNonbondedForceKernel::getLJPMEParameters(double& alpha, int& nx, in
 }
 
 // ---------------------------------------------------------------------------------------------- bonded forces
-// All terms of one kind are evaluated together under one group bit.  Several forces of the same kind are fine as long as they share
-// a force group and the periodic-boundary setting; different groups (per-force energy decomposition) would silently give wrong
-// answers, so they are refused.
+// All terms of one kind live in one device list; each force remembers its range of terms.  Forces of the same kind may sit in different
+// force groups (the per-force energy decomposition idiom): an evaluation then covers the ranges of the forces whose kernels ran (see
+// finishComputation).  They must still agree on the periodic-boundary setting, which is one flag per kind.
 static void checkBondedForce(B200Platform::PlatformData& d, int kind, const Force& force, bool periodic, const char* name) {
-    if (d.bondedGroup[kind] >= 0 && d.bondedPeriodic[kind] != (periodic ? 1 : 0))
+    if (d.bondedForces[kind] > 0 && d.bondedPeriodic[kind] != (periodic ? 1 : 0))
         throw OpenMMException(string("The B200 platform evaluates all ") + name + " objects of a System together: they must agree on periodic boundary conditions");
     d.bondedPeriodic[kind] = periodic ? 1 : 0;
     d.all([&](b200_ctx* c, int) { return b200_bonded_set_periodic(c, kind, periodic ? 1 : 0); });
-    if (d.bondedGroup[kind] >= 0 && d.bondedGroup[kind] != force.getForceGroup())
-        throw OpenMMException(string("The B200 platform evaluates all ") + name + " objects of a System together: they must share one force group");
-    d.bondedGroup[kind] = force.getForceGroup();
+    d.bondedForces[kind]++;
 }
 void B200CalcHarmonicBondForceKernel::initialize(const System&, const HarmonicBondForce& force) {
     checkBondedForce(d, 0, force, force.usesPeriodicBoundaryConditions(), "HarmonicBondForce");

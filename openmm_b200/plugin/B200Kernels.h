@@ -96,7 +96,7 @@ class B200CalcHarmonicBondForceKernel : public OpenMM::CalcHarmonicBondForceKern
 public:
     B200CalcHarmonicBondForceKernel(std::string name, const Platform& platform, PData& d) : CalcHarmonicBondForceKernel(name, platform), d(d) {}
     void initialize(const System& system, const OpenMM::HarmonicBondForce& force) override;
-    double execute(ContextImpl& context, bool includeForces, bool includeEnergy) override { d.pendingGroups |= B200_GROUP_BONDS; return 0.0; }
+    double execute(ContextImpl& context, bool includeForces, bool includeEnergy) override { d.requestBonded(0, B200_GROUP_BONDS, firstTerm, numTerms); return 0.0; }
     void copyParametersToContext(ContextImpl& context, const OpenMM::HarmonicBondForce& force, int firstBond, int lastBond) override;
 private:
     PData& d;
@@ -106,7 +106,7 @@ class B200CalcHarmonicAngleForceKernel : public OpenMM::CalcHarmonicAngleForceKe
 public:
     B200CalcHarmonicAngleForceKernel(std::string name, const Platform& platform, PData& d) : CalcHarmonicAngleForceKernel(name, platform), d(d) {}
     void initialize(const System& system, const OpenMM::HarmonicAngleForce& force) override;
-    double execute(ContextImpl& context, bool includeForces, bool includeEnergy) override { d.pendingGroups |= B200_GROUP_ANGLES; return 0.0; }
+    double execute(ContextImpl& context, bool includeForces, bool includeEnergy) override { d.requestBonded(1, B200_GROUP_ANGLES, firstTerm, numTerms); return 0.0; }
     void copyParametersToContext(ContextImpl& context, const OpenMM::HarmonicAngleForce& force, int firstAngle, int lastAngle) override;
 private:
     PData& d;
@@ -116,7 +116,7 @@ class B200CalcPeriodicTorsionForceKernel : public OpenMM::CalcPeriodicTorsionFor
 public:
     B200CalcPeriodicTorsionForceKernel(std::string name, const Platform& platform, PData& d) : CalcPeriodicTorsionForceKernel(name, platform), d(d) {}
     void initialize(const System& system, const OpenMM::PeriodicTorsionForce& force) override;
-    double execute(ContextImpl& context, bool includeForces, bool includeEnergy) override { d.pendingGroups |= B200_GROUP_TORSIONS; return 0.0; }
+    double execute(ContextImpl& context, bool includeForces, bool includeEnergy) override { d.requestBonded(2, B200_GROUP_TORSIONS, firstTerm, numTerms); return 0.0; }
     void copyParametersToContext(ContextImpl& context, const OpenMM::PeriodicTorsionForce& force, int firstTorsion, int lastTorsion) override;
 private:
     PData& d;

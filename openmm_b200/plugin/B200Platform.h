@@ -53,7 +53,11 @@ public:
         bool positionsValid = false;
         int bondedCount[3] = {0, 0, 0};         // bonds / angles / torsions created so far (a force's terms start at the count it found)
         int bondedPeriodic[3] = {0, 0, 0};
-        int bondedGroup[3] = {-1, -1, -1};      // force group of the HarmonicBond / HarmonicAngle / PeriodicTorsion terms already added
+        int bondedForces[3] = {0, 0, 0};        // HarmonicBond / HarmonicAngle / PeriodicTorsion objects in the System
+        std::vector<int> bondedActive[3];       // (first term, count) of the forces of each kind whose kernels ran in this evaluation
+        bool bondedRestricted[3] = {false, false, false};   // a subset is currently selected in the library
+        // a bonded kernel's execute(): this force takes part in the evaluation in progress
+        void requestBonded(int kind, unsigned groupBit, int first, int count) { pendingGroups |= groupBit; bondedActive[kind].push_back(first); bondedActive[kind].push_back(count); }
         std::map<std::string, std::string> properties;
         ~PlatformData() {
             if (ranks.empty()) { if (ctx) b200_context_destroy(ctx); return; }

@@ -121,6 +121,38 @@ def test_bonded_terms_vs_numpy_restatement():
     ctx.close()
 
 
+def test_bonded_forces_of_one_kind_in_different_groups():
+    # two HarmonicBondForce objects (and two torsion forces) created one after the other, as the plugin does for forces of the same kind
+    # in different force groups; b200_bonded_set_active selects the ranges of the forces whose kernels ran in an evaluation
+    rng = np.random.default_rng(9)
+    n = 60
+    pos = (rng.random((n, 3)) * 3 + 3).astype(np.float32).astype(np.float64)
+    b1 = (np.stack([np.arange(0, 20), np.arange(1, 21)], 1), rng.uniform(0.5, 1.5, 20), rng.uniform(10, 50, 20))
+    b2 = (np.stack([np.arange(30, 55), np.arange(31, 56)], 1), rng.uniform(0.5, 1.5, 25), rng.uniform(10, 50, 25))
+    t1 = (np.stack([np.arange(0, 10), np.arange(1, 11), np.arange(2, 12), np.arange(3, 13)], 1), rng.integers(1, 4, 10), rng.uniform(0, 3, 10), rng.uniform(1, 9, 10))
+    t2 = (np.stack([np.arange(20, 27), np.arange(21, 28), np.arange(22, 29), np.arange(23, 30)], 1), rng.integers(1, 4, 7), rng.uniform(0, 3, 7), rng.uniform(1, 9, 7))
+    none = (np.zeros((0, 2), int), np.zeros(0), np.zeros(0)); nona = (np.zeros((0, 3), int), np.zeros(0), np.zeros(0)); nont = (np.zeros((0, 4), int), np.zeros(0, int), np.zeros(0), np.zeros(0))
+    ctx = bare_context(n, 12.0)
+    ctx.add_harmonic_bonds(*b1); ctx.add_harmonic_bonds(*b2); ctx.add_periodic_torsions(*t1); ctx.add_periodic_torsions(*t2)
+    ctx.set_positions(pos)
+    e_all = ctx.compute(b.GROUP_BONDS | b.GROUP_TORSIONS)
+    assert abs(e_all - (bonded_energy(pos, b1, nona, t1) + bonded_energy(pos, b2, nona, t2))) / abs(e_all) < 1e-6
+    ctx.bonded_set_active(0, [(0, 20)])
+    e = ctx.compute(b.GROUP_BONDS); f = ctx.get_forces()
+    assert abs(e - bonded_energy(pos, b1, nona, nont)) / abs(e) < 1e-6
+    assert np.all(f[22:] == 0) and np.abs(f[:21]).max() > 0       # only the first force's atoms feel anything
+    ctx.bonded_set_active(0, [(20, 25)])
+    assert abs(ctx.compute(b.GROUP_BONDS) - bonded_energy(pos, b2, nona, nont)) / abs(e) < 1e-6
+    ctx.bonded_set_active(2, [(10, 7)])
+    e = ctx.compute(b.GROUP_BONDS | b.GROUP_TORSIONS)
+    assert abs(e - bonded_energy(pos, b2, nona, t2)) / abs(e) < 1e-6
+    ctx.bonded_set_active(0, [(0, 20), (20, 25)]); ctx.bonded_set_active(2)
+    assert abs(ctx.compute(b.GROUP_BONDS | b.GROUP_TORSIONS) - e_all) / abs(e_all) < 1e-9
+    with pytest.raises(b.B200Error, match="outside the terms"):
+        ctx.bonded_set_active(0, [(40, 10)])
+    ctx.close()
+
+
 def test_exclusions_and_14_known_answers():
     # tests/TestNonbondedForce.h:98-179 testExclusionsAnd14 restated for the PME method: five particles in a row; 1-2 and 1-3 pairs are
     # excluded, 1-4 pairs carry scaled parameters.  Checked against the oracle (exceptions are plain Coulomb + LJ without cutoff,

@@ -34,8 +34,8 @@ MUST_PASS = {
 
 
 # further suites of the reference; the tests that pass are asserted.  Not passing: the testForceGroups / testSetState / testReporter cases
-# need kernels outside the scope table (CustomExternalForce, ...), the minimizer's testForceGroups puts two HarmonicBondForces in
-# different force groups, testLargeForces minimises from 1e6 kJ/mol/nm forces
+# need kernels outside the scope table (CustomExternalForce, ...), testLargeForces minimises from 1e6 kJ/mol/nm forces.  (The minimizer's
+# testForceGroups puts two HarmonicBondForces in different force groups: b200_bonded_set_active.)
 MUST_PASS.update({
     "suite_bonds": ["testBonds()", "testPeriodic()"],
     "suite_angles": ["testAngles()", "testPeriodic()"],
@@ -44,7 +44,7 @@ MUST_PASS.update({
     "suite_langevinmiddle": ["testSingleBond()", "testTemperature()", "testConstraints()", "testConstrainedMasslessParticles()", "testRandomSeed()", "testInitialTemperature()"],
     "suite_settle": ["testConstraints()"],
     "suite_checkpoints": [],
-    "suite_minimizer": ["testHarmonicBonds()", "testLargeSystem()", "testMasslessParticles()"],
+    "suite_minimizer": ["testHarmonicBonds()", "testLargeSystem()", "testForceGroups()", "testMasslessParticles()"],
 })
 
 
