@@ -120,7 +120,7 @@ extern "C" void b200_context_destroy(b200_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
-    b200_graph_invalidate(c);
+    if (c->stepGraph) { cudaGraphExecDestroy(c->stepGraph); c->stepGraph = nullptr; }
     b200_comm_destroy(c);
     b200_pme_destroy(c);
     dfree(c->posq); dfree(c->posqCorr); dfree(c->velm); dfree(c->sigEps); dfree(c->atomIndex); dfree(c->cellOffsets); dfree(c->force); dfree(c->counters);
@@ -1039,7 +1039,7 @@ static void prepareLists(b200_ctx* c, bool verify) {
 }
 
 void b200_graph_invalidate(b200_ctx* c) {
-    if (c->stepGraph) { cudaSetDevice(c->device); cudaStreamSynchronize(c->stream); cudaGraphExecDestroy(c->stepGraph); c->stepGraph = nullptr; }
+    c->stepGraphStale = true;      // the next plain evaluation is recorded again; the executable graph is updated in place when the topology still matches
 }
 
 static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, double* energyOut, bool verify) {
@@ -1054,13 +1054,14 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     // The plain force evaluation of an MD step (forces only, no host read-back, one rank) is a fixed sequence of launches on two
     // streams with constant arguments -- the list kernels decide on the device whether they have work -- so it is captured once as a
     // CUDA graph and replayed: one launch per evaluation instead of ~15 (the reference submits each kernel, CommonKernels.cpp:3139-3206).
-    // Anything that changes an argument (box, parameters, list storage, streams) drops the graph, see b200_graph_invalidate.
+    // Anything that changes an argument (box, parameters, list storage) marks the capture stale, see b200_graph_invalidate.
     static const bool graphOff = getenv("B200_NO_GRAPH") != nullptr;
     const bool graphable = !graphOff && forces && !energy && !verify && c->commRanks == 1 && c->partRanks == 1 && !c->timing && c->hasNonbonded
-                           && c->computeCount > 4 && c->graphCaptures < 32;
+                           && c->computeCount > 4 && c->graphCaptures < 32 && c->computeCount >= c->graphSkipUntil;
     const bool dispAtEntry = c->dispChecked;
-    if (graphable && c->stepGraph && c->stepGraphGroups == groups && c->stepGraphDisp == dispAtEntry) {
+    if (graphable && c->stepGraph && !c->stepGraphStale && c->stepGraphGroups == groups && c->stepGraphDisp == dispAtEntry) {
         CUDA_CHECK(cudaGraphLaunch(c->stepGraph, s));
+        c->graphReplays++;
         c->launchCount += c->stepGraphLaunches;
         c->dispChecked = true; c->forcesPartial = false; c->recipPending = false;
         c->forcesValid = groups == B200_GROUP_ALL;
@@ -1068,7 +1069,15 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     }
     const bool capturing = graphable;
     const long long launchesAtEntry = c->launchCount;
-    if (capturing) { b200_graph_invalidate(c); CUDA_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal)); c->capturing = true; }
+    if (capturing) {
+        // something that invalidates the capture every few evaluations (parameters changed every step, say) would make recording cost
+        // more than replaying saves: after three short-lived captures in a row the launch-by-launch path is used for a while
+        c->graphPenalty = (c->stepGraph && c->graphReplays < 8) ? c->graphPenalty + 1 : 0;
+        c->graphReplays = 0;
+        if (c->graphPenalty >= 3) { c->graphPenalty = 0; c->graphSkipUntil = c->computeCount + 256; }
+    }
+    const bool record = capturing && c->computeCount >= c->graphSkipUntil;
+    if (record) { CUDA_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal)); c->capturing = true; }
     const bool doRecip = c->hasNonbonded && c->nb.method >= B200_NB_EWALD && (groups & B200_GROUP_RECIPROCAL) && c->partRank == 0;
     const bool doDirect = c->hasNonbonded && (groups & B200_GROUP_DIRECT);
     // per-family event timing needs the families serialised: overlapping streams would charge waiting time to the wrong family
@@ -1114,16 +1123,23 @@ static void computeImpl(b200_ctx* c, unsigned groups, bool forces, bool energy, 
     static const bool pushJoin = getenv("B200_PUSH_JOIN") != nullptr;     // debug: keep the data path of the push, give up the overlap
     if (doRecip && usePmeStream && (!push || pushJoin)) CUDA_CHECK(cudaStreamWaitEvent(s, c->evPmeDone, 0));
     } catch (...) {
-        if (capturing) { c->capturing = false; cudaGraph_t g = nullptr; cudaStreamEndCapture(s, &g); if (g) cudaGraphDestroy(g); cudaGetLastError(); c->graphCaptures = 1 << 20; }
+        if (record) { c->capturing = false; cudaGraph_t g = nullptr; cudaStreamEndCapture(s, &g); if (g) cudaGraphDestroy(g); cudaGetLastError(); c->graphCaptures = 1 << 20; }
         throw;
     }
-    if (capturing) {
+    if (record) {
         cudaGraph_t g = nullptr;
         c->capturing = false;
         CUDA_CHECK(cudaStreamEndCapture(s, &g));
-        c->graphCaptures++;
-        CUDA_CHECK(cudaGraphInstantiate(&c->stepGraph, g, 0));
+        // same topology as the executable graph at hand (a box or parameter change): update it in place, far cheaper than instantiating
+        bool reused = false;
+        if (c->stepGraph) {
+            cudaGraphExecUpdateResultInfo info;
+            if (cudaGraphExecUpdate(c->stepGraph, g, &info) == cudaSuccess) reused = true;
+            else { cudaGetLastError(); cudaStreamSynchronize(s); cudaGraphExecDestroy(c->stepGraph); c->stepGraph = nullptr; }
+        }
+        if (!reused) { c->graphCaptures++; CUDA_CHECK(cudaGraphInstantiate(&c->stepGraph, g, 0)); }
         cudaGraphDestroy(g);
+        c->stepGraphStale = false;
         c->stepGraphLaunches = c->launchCount - launchesAtEntry; c->stepGraphGroups = groups; c->stepGraphDisp = dispAtEntry;
         CUDA_CHECK(cudaGraphLaunch(c->stepGraph, s));
     }

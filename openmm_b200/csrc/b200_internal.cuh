@@ -220,6 +220,8 @@ struct b200_ctx {
     // the captured force evaluation (computeImpl): replayed while nothing that feeds a kernel argument has changed
     bool capturing = false;         // computeImpl is recording the evaluation: b200_nblist_prepare puts the rebuild kernels into a conditional node
     cudaGraphExec_t stepGraph = nullptr; long long stepGraphLaunches = 0; unsigned stepGraphGroups = 0; bool stepGraphDisp = false; int graphCaptures = 0;
+    bool stepGraphStale = false;                 // an argument changed: record again and update the executable graph in place (cudaGraphExecUpdate)
+    int graphReplays = 0, graphPenalty = 0; long long graphSkipUntil = 0;   // back-off when something invalidates the capture every few evaluations
 
     // PME: mesh[0] = Coulomb, mesh[1] = dispersion (LJPME only)
     PmeMesh mesh[2];

@@ -27,6 +27,16 @@ box = np.array(sysd["box"], dtype=np.float64) * 1.002
 ctx.set_box(box)
 ctx.step(40)
 h.update(ctx.get_positions().tobytes())
+# barostat-like: a box change every 12 steps (each one re-records the evaluation and updates the executable graph in place)
+for k in range(6):
+    ctx.set_box(box * (1.0 + 0.0005 * (k % 3)))
+    ctx.step(12)
+h.update(ctx.get_positions().tobytes())
+# ... and a change on every third step (short-lived captures: the back-off to launch-by-launch must not change the result either)
+for k in range(12):
+    ctx.set_box(box * (1.0 + 0.0002 * (k % 2)))
+    ctx.step(3)
+h.update(ctx.get_positions().tobytes())
 q = np.array(sysd["charge"], dtype=np.float64) * 0.98
 ctx.update_nonbonded_parameters(q, sysd["sigma"], sysd["epsilon"], len(sysd["exclusions"]))
 ctx.step(40)
