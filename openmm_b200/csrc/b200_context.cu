@@ -1008,7 +1008,9 @@ static void prepareLists(b200_ctx* c, bool verify) {
     // Runs the (device-decided) rebuild.  When `verify` is set the host also reads the list counters: an overflow flag that is
     // ALREADY set belongs to an earlier, unverified evaluation whose forces were incomplete -> error, never cleared silently.
     // Otherwise the storage follows the measured need: it grows (25 % head room) when the build overflowed and also as soon as
-    // the list fills more than 80 % of it, so that an overflow between two checks would take a 25 % jump within 64 steps.
+    // the list fills more than 90 % of it, so that an overflow between two checks would take an 11 % jump within 64 steps.  (The
+    // threshold used to be 80 %, i.e. exactly the fill of freshly sized storage: an equilibrating system whose list grew by half a
+    // per cent re-allocated at its first check, ~10 ms of cudaFree/cudaMalloc inside a timed run.)
     // Unverified evaluations stay memory-safe (the builder writes an empty descriptor for a dropped unit, the tile kernel
     // clamps the unit count).  (Host-side analogue of CudaNonbondedUtilities::updateNeighborListSize, CudaNonbondedUtilities.cpp:441-479.)
     if (verify) {
@@ -1026,7 +1028,7 @@ static void prepareLists(b200_ctx* c, bool verify) {
         checkOverflow(c);
         const DevCounters& h = *c->countersHost;
         const bool over = h.overflow != 0;
-        const bool tight = (long long)h.numTiles * 5 > c->tileCapacity * 4 || (long long)h.numUnits * 5 > c->unitCapacity * 4;
+        const bool tight = (long long)h.numTiles * 10 > c->tileCapacity * 9 || (long long)h.numUnits * 10 > c->unitCapacity * 9;
         c->listVerified = true;
         if (!over && !tight) return;
         c->tileCapacity = std::max(c->tileCapacity, (long long)h.numTiles * 5 / 4 + 1024);
