@@ -128,6 +128,10 @@ int  b200_get_positions(b200_ctx* ctx, double* xyz, int32_t enforce_periodic);
 int  b200_set_velocities(b200_ctx* ctx, const double* xyz);
 int  b200_get_velocities(b200_ctx* ctx, double* xyz);
 int  b200_get_forces(b200_ctx* ctx, double* xyz);
+/* Adds forces computed elsewhere (kJ/mol/nm, particle order, doubles) to the force buffer, the way every ForceImpl of a Context adds
+ * into the shared fixed-point buffer (ContextImpl::calcForcesAndEnergy, ContextImpl.cpp; CudaContext's long long force array).  The
+ * plugin uses it for a second NonbondedForce, which is evaluated in a context of its own.  One rank only. */
+int  b200_add_forces(b200_ctx* ctx, const double* xyz);
 int  b200_set_box(b200_ctx* ctx, const double* box9);
 int  b200_get_box(const b200_ctx* ctx, double* box9);
 int  b200_set_time(b200_ctx* ctx, double time_ps, int64_t step_count);

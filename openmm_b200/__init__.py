@@ -62,7 +62,7 @@ EXPORTED_SYMBOLS = [
     "b200_context_create", "b200_context_destroy", "b200_last_error", "b200_device_count", "b200_nonbonded_create",
     "b200_nonbonded_update_parameters", "b200_nonbonded_get_pme_parameters", "b200_nonbonded_get_ljpme_parameters", "b200_harmonic_bonds_create",
     "b200_harmonic_angles_create", "b200_periodic_torsions_create", "b200_bonded_update_parameters", "b200_bonded_set_periodic", "b200_bonded_set_active", "b200_set_positions", "b200_set_positions_root", "b200_get_positions",
-    "b200_set_velocities", "b200_get_velocities", "b200_get_forces", "b200_set_box", "b200_get_box", "b200_set_time",
+    "b200_set_velocities", "b200_get_velocities", "b200_get_forces", "b200_add_forces", "b200_set_box", "b200_get_box", "b200_set_time",
     "b200_get_time", "b200_compute", "b200_compute_host", "b200_integrator_create", "b200_step", "b200_integrate",
     "b200_remove_cm_motion", "b200_apply_constraints",
     "b200_apply_velocity_constraints", "b200_kinetic_energy", "b200_kinetic_energy_shifted", "b200_synchronize", "b200_barostat_save", "b200_barostat_scale", "b200_barostat_restore", "b200_direct_pairs", "b200_direct_pairs_hash", "b200_nblist_get_stats",
@@ -264,6 +264,11 @@ class Context:
         out = np.empty(3 * self.n)
         _check(self.lib.b200_get_velocities(self.handle, out.ctypes.data_as(c_double_p)))
         return out.reshape(-1, 3)
+
+    def add_forces(self, xyz):
+        a, p = _d(np.asarray(xyz).reshape(-1))
+        assert a.size == 3 * self.n
+        _check(self.lib.b200_add_forces(self.handle, p))
 
     def get_forces(self):
         out = np.empty(3 * self.n)

@@ -791,6 +791,15 @@ __global__ void ioGetForces(double* __restrict__ stage, const int* __restrict__ 
     stage[3 * (size_t)o] = sc * (double)force[s]; stage[3 * (size_t)o + 1] = sc * (double)force[s + Npad]; stage[3 * (size_t)o + 2] = sc * (double)force[s + 2 * (size_t)Npad];
 }
 
+__global__ void ioAddForces(const double* __restrict__ stage, const int* __restrict__ atomIndex, int N, int Npad, long long* __restrict__ force) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= N) return;
+    const int o = atomIndex[s];
+    force[s] += __double2ll_rn(stage[3 * (size_t)o] * B200_FORCE_SCALE);
+    force[s + Npad] += __double2ll_rn(stage[3 * (size_t)o + 1] * B200_FORCE_SCALE);
+    force[s + 2 * (size_t)Npad] += __double2ll_rn(stage[3 * (size_t)o + 2] * B200_FORCE_SCALE);
+}
+
 static void afterSetPositions(b200_ctx* c) {
     c->forcesValid = false; c->dispChecked = false; c->listVerified = false;
     // Like ComputeContext::reorderAtoms the spatial sort is periodic, not forced by every setPositions: the displacement
@@ -890,6 +899,18 @@ extern "C" int b200_get_forces(b200_ctx* c, double* xyz) {
     ioGetForces<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->Npad, c->force);
     LAUNCH_COUNT(c, 1);
     stageOut(c, xyz);
+    API_END
+}
+
+extern "C" int b200_add_forces(b200_ctx* c, const double* xyz) {
+    API_BEGIN
+    if (!xyz) throw B200Error(B200_ERR_INVALID, "b200_add_forces: null array");
+    if (c->commRanks > 1) throw B200Error(B200_ERR_UNSUPPORTED, "b200_add_forces: not available with a communicator (the force arrays hold partial sums)");
+    CUDA_CHECK(cudaSetDevice(c->device));
+    stageIn(c, xyz);
+    ioAddForces<<<(c->N + 255) / 256, 256, 0, c->stream>>>(c->dStage, c->atomIndex, c->N, c->Npad, c->force);
+    LAUNCH_COUNT(c, 1);
+    CUDA_CHECK(cudaStreamSynchronize(c->stream));     // the caller's buffer may be pageable and reused at once
     API_END
 }
 

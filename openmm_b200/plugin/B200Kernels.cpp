@@ -26,6 +26,7 @@ namespace B200Plugin {
 void B200CalcForcesAndEnergyKernel::beginComputation(ContextImpl&, bool, bool, int) {
     d.pendingGroups = 0;   // every ForceImpl that takes part in this evaluation adds its bit from its kernel's execute()
     for (auto& r : d.bondedActive) r.clear();
+    for (auto* x : d.extras) x->pending = 0;
 }
 
 double B200CalcForcesAndEnergyKernel::finishComputation(ContextImpl&, bool includeForce, bool includeEnergy, int, bool& valid) {
@@ -46,6 +47,18 @@ double B200CalcForcesAndEnergyKernel::finishComputation(ContextImpl&, bool inclu
     }
     d.all([&](b200_ctx* c, int r) { return b200_compute(c, d.pendingGroups, includeForce ? 1 : 0, includeEnergy ? 1 : 0, &e[r]); });
     energy = e[0];
+    // further NonbondedForce objects: each in its own context, on the positions and box of the main one; forces added to the main buffer
+    for (auto* x : d.extras) {
+        if (!x->pending) continue;
+        vector<double> buf(3 * d.masses.size());
+        double box[9], ex = 0.0;
+        check(b200_get_positions(d.ctx, buf.data(), 0)); check(b200_get_box(d.ctx, box));
+        check(b200_set_box(x->ctx, box)); check(b200_set_positions(x->ctx, buf.data()));
+        check(b200_compute(x->ctx, x->pending, includeForce ? 1 : 0, includeEnergy ? 1 : 0, &ex));
+        energy += ex;
+        if (includeForce) { check(b200_get_forces(x->ctx, buf.data())); check(b200_add_forces(d.ctx, buf.data())); }
+        x->pending = 0;
+    }
     valid = true;            // list growth/retry is handled inside the library (CudaNonbondedUtilities.cpp:441-479 does it by invalidating)
     return includeEnergy ? energy : 0.0;
 }
@@ -212,17 +225,29 @@ void B200CalcNonbondedForceKernel::initialize(const System& system, const Nonbon
     for (int i = 0; i < force.getNumGlobalParameters(); i++) globals[force.getGlobalParameterName(i)] = force.getGlobalParameterDefaultValue(i);
     Params p;
     gather(system, force, p, globals);
+    if (d.hasNonbonded) {
+        if (d.ranks.size() > 1) throw OpenMMException("The B200 platform supports a second NonbondedForce in a System on one device only");
+        extra = d.addExtraNonbonded();
+        check(b200_nonbonded_create(extra->ctx, &p.desc));
+        return;
+    }
     d.all([&](b200_ctx* c, int) { return b200_nonbonded_create(c, &p.desc); });
+    d.hasNonbonded = true;
 }
 
 double B200CalcNonbondedForceKernel::execute(ContextImpl& context, bool, bool, bool includeDirect, bool includeReciprocal) {
     if (hasOffsets) {   // a global parameter that moved since the last evaluation changes the effective parameters
         bool changed = false;
         for (auto& g : globals) { const double v = context.getParameter(g.first); if (v != g.second) { g.second = v; changed = true; } }
-        if (changed) { Params p; gather(*systemRef, *forceRef, p, globals); d.all([&](b200_ctx* c, int) { return b200_nonbonded_update_parameters(c, &p.desc); }); }
+        if (changed) {
+            Params p; gather(*systemRef, *forceRef, p, globals);
+            if (extra) check(b200_nonbonded_update_parameters(extra->ctx, &p.desc));
+            else d.all([&](b200_ctx* c, int) { return b200_nonbonded_update_parameters(c, &p.desc); });
+        }
     }
-    if (includeDirect) d.pendingGroups |= B200_GROUP_DIRECT;
-    if (includeReciprocal) d.pendingGroups |= B200_GROUP_RECIPROCAL;
+    unsigned& pending = extra ? extra->pending : d.pendingGroups;
+    if (includeDirect) pending |= B200_GROUP_DIRECT;
+    if (includeReciprocal) pending |= B200_GROUP_RECIPROCAL;
     return 0.0;   // the energy of this force is returned by CalcForcesAndEnergyKernel::finishComputation
 }
 
@@ -230,17 +255,18 @@ void B200CalcNonbondedForceKernel::copyParametersToContext(ContextImpl& context,
     Params p;
     for (auto& g : globals) g.second = context.getParameter(g.first);
     gather(context.getSystem(), force, p, globals);
+    if (extra) { check(b200_nonbonded_update_parameters(extra->ctx, &p.desc)); return; }
     d.all([&](b200_ctx* c, int) { return b200_nonbonded_update_parameters(c, &p.desc); });
 }
 
 void B200CalcNonbondedForceKernel::getPMEParameters(double& alpha, int& nx, int& ny, int& nz) const {
     int32_t x, y, z;
-    check(b200_nonbonded_get_pme_parameters(d.ctx, &alpha, &x, &y, &z));
+    check(b200_nonbonded_get_pme_parameters(extra ? extra->ctx : d.ctx, &alpha, &x, &y, &z));
     nx = x; ny = y; nz = z;
 }
 void B200CalcNonbondedForceKernel::getLJPMEParameters(double& alpha, int& nx, int& ny, int& nz) const {
     int32_t x, y, z;
-    if (b200_nonbonded_get_ljpme_parameters(d.ctx, &alpha, &x, &y, &z) != B200_OK)
+    if (b200_nonbonded_get_ljpme_parameters(extra ? extra->ctx : d.ctx, &alpha, &x, &y, &z) != B200_OK)
         throw OpenMMException("getPMEParametersInContext: This Context is not using PME");   // message of CommonCalcNonbondedForce.cpp:1267
     nx = x; ny = y; nz = z;
 }

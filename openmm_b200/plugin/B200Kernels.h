@@ -89,6 +89,7 @@ private:
     const OpenMM::NonbondedForce* forceRef = nullptr; const System* systemRef = nullptr;
     bool hasOffsets = false;
     std::map<std::string, double> globals;      // global parameters of the force and the values the device parameters were computed with
+    PData::ExtraNonbonded* extra = nullptr;       // set for a second NonbondedForce of the System: it lives in a context of its own
 };
 
 // kernels.h:334-366, 408-440, 482-514

@@ -134,6 +134,7 @@ void B200Platform::contextCreated(ContextImpl& context, const map<string, string
     desc.device = device;
     desc.flags = lower(prop(DisablePmeStream())) == "true" ? B200_CTX_DISABLE_PME_STREAM : 0;
     PlatformData* d = new PlatformData();
+    d->masses = mass; copy(box, box + 9, d->defaultBox); d->device = device; d->flags = desc.flags;
     try {
         const int R = (int)deviceList.size();
         d->ranks.assign(R, nullptr);

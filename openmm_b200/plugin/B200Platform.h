@@ -50,6 +50,23 @@ public:
             pool.run((int)ranks.size(), [&](int r) { return f(ranks[r], r); });
         }
         unsigned pendingGroups = 0;            // force groups requested by the ForceImpls between begin/finishComputation
+        // A second (third, ...) NonbondedForce of the System is evaluated in a context of its own: positions and box are copied over
+        // before each of its evaluations and its forces are added to the main buffer (b200_add_forces).  Host round trips: meant for
+        // the rare System that splits its nonbonded interactions over several forces, not for speed.  One device only.
+        struct ExtraNonbonded { b200_ctx* ctx = nullptr; unsigned pending = 0; };
+        std::vector<ExtraNonbonded*> extras;
+        bool hasNonbonded = false;
+        std::vector<double> masses; double defaultBox[9] = {0}; int device = 0; unsigned flags = 0;   // what an extra context is created from
+        ExtraNonbonded* addExtraNonbonded() {
+            b200_system_desc desc = {};
+            desc.num_atoms = (int)masses.size(); desc.mass = masses.data();
+            for (int i = 0; i < 9; i++) desc.box[i] = defaultBox[i];
+            desc.device = device; desc.flags = flags;
+            ExtraNonbonded* x = new ExtraNonbonded();
+            extras.push_back(x);
+            check(b200_context_create(&desc, &x->ctx));
+            return x;
+        }
         bool positionsValid = false;
         int bondedCount[3] = {0, 0, 0};         // bonds / angles / torsions created so far (a force's terms start at the count it found)
         int bondedPeriodic[3] = {0, 0, 0};
@@ -60,6 +77,7 @@ public:
         void requestBonded(int kind, unsigned groupBit, int first, int count) { pendingGroups |= groupBit; bondedActive[kind].push_back(first); bondedActive[kind].push_back(count); }
         std::map<std::string, std::string> properties;
         ~PlatformData() {
+            for (ExtraNonbonded* x : extras) { if (x->ctx) b200_context_destroy(x->ctx); delete x; }
             if (ranks.empty()) { if (ctx) b200_context_destroy(ctx); return; }
             if (ranks.size() > 1) { try { pool.run((int)ranks.size(), [&](int r) { b200_context_destroy(ranks[r]); return 0; }); } catch (...) {} }
             else b200_context_destroy(ranks[0]);

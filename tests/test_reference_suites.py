@@ -15,13 +15,13 @@ from oracle_lib import ROOT
 pytestmark = pytest.mark.gpu
 REF_DIR = os.path.join(ROOT, "oracle", "_ref")
 
-# every test*() of the three suites passes on a B200 except testTwoForces (two NonbondedForce objects in one System, which the
-# platform refuses); the lists below are asserted so that a regression in any of them fails the run
+# every test*() of the three suites passes on a B200 (testTwoForces: the second NonbondedForce of a System is evaluated in a context of
+# its own, plugin/B200Kernels.cpp); the lists below are asserted so that a regression in any of them fails the run
 MUST_PASS = {
     "suite_nonbonded": ["testCoulomb()", "testLJ()", "testExclusionsAnd14()", "testCutoff()", "testCutoff14()", "testPeriodic()", "testPeriodicExceptions()",
                         "testTriclinic()", "testLargeSystem()", "testDispersionCorrection()", "testChangingParameters()",
                         "testSwitchingFunction(NonbondedForce::CutoffNonPeriodic)", "testSwitchingFunction(NonbondedForce::PME)", "testParameterOffsets()",
-                        "testEwaldExceptions()", "testDirectAndReciprocal()", "testReordering()"],
+                        "testEwaldExceptions()", "testDirectAndReciprocal()", "testReordering()", "testTwoForces()"],
     "suite_ewald": ["testEwaldExact()", "testEwaldPME(false)", "testEwaldPME(true)", "testTriclinic()", "testTriclinic2()",
                     "testErrorTolerance(NonbondedForce::Ewald)", "testErrorTolerance(NonbondedForce::PME)", "testPMEParameters()",
                     "testNeutralizingPlasmaCorrection(NonbondedForce::Ewald, false)", "testNeutralizingPlasmaCorrection(NonbondedForce::PME, false)",
