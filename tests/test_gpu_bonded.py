@@ -121,6 +121,21 @@ def test_bonded_terms_vs_numpy_restatement():
     ctx.close()
 
 
+def test_add_forces_accumulates_into_the_fixed_point_buffer():
+    # b200_add_forces: forces computed elsewhere (the plugin's second NonbondedForce) join the int64 buffer at its 2^-32 resolution
+    ctx = bare_context(3)
+    ctx.add_harmonic_bonds([[0, 1], [1, 2]], [1.5, 1.2], [0.8, 0.7])
+    ctx.set_positions(np.array([[0, 2, 0], [0, 0, 0], [1, 0, 0]], dtype=float))
+    ctx.compute(b.GROUP_BONDS, energy=False)
+    f0 = ctx.get_forces().copy()
+    extra = np.array([[1.25, -3.5, 0.125], [1e-3, 2e-3, -7e-3], [100.0, -200.0, 300.0]])
+    ctx.add_forces(extra)
+    assert np.abs(ctx.get_forces() - (f0 + extra)).max() < 1e-9
+    ctx.add_forces(-extra)
+    assert np.abs(ctx.get_forces() - f0).max() < 1e-9
+    ctx.close()
+
+
 def test_bonded_forces_of_one_kind_in_different_groups():
     # two HarmonicBondForce objects (and two torsion forces) created one after the other, as the plugin does for forces of the same kind
     # in different force groups; b200_bonded_set_active selects the ranges of the forces whose kernels ran in an evaluation
